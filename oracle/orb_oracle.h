@@ -1,0 +1,77 @@
+/* TEST INFRASTRUCTURE ONLY (oracle/).  CPU restatement of the reference hot path:
+ * ORBextractor::operator() and the Hamming core of ORBmatcher
+ * (QiuYue-bit/ORB-SLAM2-noted; file:line citations are relative to /root/reference).
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+ * legs may load this library.  The product (liborbx.so) never links or calls it.
+ *
+ * PARITY PINNING: the reference has no tests/golden vectors for this path and cannot be
+ * compiled here (needs OpenCV C++ headers).  The third-party arithmetic it calls
+ * (cv::resize, cv::GaussianBlur, cv::FAST, cv::fastAtan2, cv::copyMakeBorder, libm
+ * cosf/sinf) is pinned against the executable copies in this image (cv2 4.13.0,
+ * glibc 2.39) by tests/golden fixtures generated with tools/gen_golden.py; the glue
+ * (cells, quadtree, ordering) is pinned against an independent Python restatement that
+ * calls cv2 for every primitive.  The quadtree tie-break is canonicalised (see
+ * orc_distribute_octree) because the reference's is heap-address dependent.
+ */
+#ifndef ORB_ORACLE_H
+#define ORB_ORACLE_H
+#include <stdint.h>
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORC_MAX_LEVELS 16
+#define ORC_EDGE_THRESHOLD 19 /* src/ORBextractor.cc:81 */
+#define ORC_HALF_PATCH 15     /* :80 */
+#define ORC_PATCH 31          /* :79 */
+
+typedef struct { float x, y, size, angle, response; int32_t octave, class_id; } orc_keypoint; /* == cv::KeyPoint, 28 B */
+
+typedef struct {
+    int nfeatures, nlevels, ini_th, min_th;
+    float scale_factor;
+    float scale[ORC_MAX_LEVELS], inv_scale[ORC_MAX_LEVELS];
+    float sigma2[ORC_MAX_LEVELS], inv_sigma2[ORC_MAX_LEVELS];
+    int nfeat_level[ORC_MAX_LEVELS];
+    int umax[ORC_HALF_PATCH + 1];
+    int blur_ksize; /* 9 in this fork (src/ORBextractor.cc:1622); 7 upstream */
+} orc_params;
+
+/* ctor tables, src/ORBextractor.cc:471-579 */
+int orc_params_init(orc_params* p, int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th);
+/* level sizes, src/ORBextractor.cc:1669-1672 */
+void orc_level_size(const orc_params* p, int level, int w0, int h0, int* w, int* h);
+
+/* primitives (third-party OpenCV arithmetic restated; pinned vs cv2 4.13 goldens) */
+void orc_resize_linear(const uint8_t* src, int sw, int sh, size_t sstride, uint8_t* dst, int dw, int dh, size_t dstride);
+void orc_border_reflect101(const uint8_t* src, int w, int h, size_t sstride, uint8_t* dst, size_t dstride, int border);
+void orc_gauss_blur(const uint8_t* src, int w, int h, size_t sstride, uint8_t* dst, size_t dstride, int ksize);
+float orc_fast_atan2(float y, float x);
+int orc_fast_score(const uint8_t* center, size_t stride, int threshold);
+/* cv::FAST(roi, kps, th, nms=true) on a w x h ROI: writes (x,y,score) triplets, returns count */
+int orc_fast_roi(const uint8_t* roi, int w, int h, size_t stride, int threshold, int* xys, int cap);
+float orc_sinf(float x);
+float orc_cosf(float x);
+
+/* stages */
+/* FAST over all cells of one level (src/ORBextractor.cc:1058-1153): window-relative x,y and response */
+int orc_detect_level(const orc_params* p, const uint8_t* img, int w, int h, size_t stride, orc_keypoint* out, int cap);
+/* DistributeOctTree :696-1042 (canonical tie-break). in: window-relative kps in detection order */
+int orc_distribute_octree(const orc_keypoint* in, int n, int minX, int maxX, int minY, int maxY, int N, orc_keypoint* out, int cap);
+float orc_ic_angle(const uint8_t* img, size_t stride, int cx, int cy, const int* umax); /* :94-141 */
+void orc_brief(const uint8_t* blurred, size_t stride, int cx, int cy, float angle_deg, uint8_t* desc32); /* :153-204 */
+
+/* full operator(): returns number of keypoints (<= cap), or <0 on error.
+ * pyr (optional) receives the un-bordered levels packed back to back (sum w_l*h_l bytes). */
+int orc_extract(const orc_params* p, const uint8_t* img, int w, int h, size_t stride,
+                orc_keypoint* kps, uint8_t* desc, int cap, uint8_t* pyr);
+
+/* ---- matcher side (orb_match.c) ---- */
+int orc_descriptor_distance(const uint8_t* a, const uint8_t* b); /* src/ORBmatcher.cc:2123-2143 */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

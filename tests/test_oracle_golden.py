@@ -1,0 +1,75 @@
+"""CPU: the oracle (oracle/*.c) against golden vectors made with the real cv2 4.13 / libm
+primitives (tools/gen_golden.py).  This is what pins the oracle; see oracle/orb_oracle.h."""
+import hashlib, os
+import numpy as np
+import pytest
+import synth, oracle_lib as O
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.fixture(scope="module")
+def prim():
+    return np.load(os.path.join(G, "primitives.npz"))
+
+
+def test_resize_matches_cv2(prim):
+    img = synth.frame(11, 213, 160)
+    for key in prim.files:
+        if key.startswith("resize_"):
+            dw, dh = map(int, key[7:].split("x"))
+            assert np.array_equal(O.resize(img, dw, dh), prim[key]), key
+
+
+def test_blur_border_match_cv2(prim):
+    img = synth.frame(11, 213, 160)
+    assert np.array_equal(O.blur(img, 9), prim["blur9"])
+    assert np.array_equal(O.blur(img, 7), prim["blur7"])
+    assert np.array_equal(O.border(img, 19), prim["border19"])
+
+
+def test_fast_atan2_matches_cv2(prim):
+    out = np.array([O.lib().orc_fast_atan2(float(y), float(x)) for y, x in prim["atan2_in"]], np.float32)
+    assert np.array_equal(out.view(np.uint32), prim["atan2_out"].view(np.uint32))
+
+
+def test_fast_roi_matches_cv2(prim):
+    for th in (7, 20):
+        for seed, kind in [(21, "texture"), (22, "noise"), (23, "gradient")]:
+            roi = synth.frame(seed, 43, 41, kind)
+            assert np.array_equal(O.fast_roi(roi, th), prim[f"fast_{kind}_{th}"]), (kind, th)
+
+
+CASES = ["tum", "euroc", "kitti", "grad", "noise", "black", "small"]
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_extract_matches_cv2_pipeline(name):
+    g = np.load(os.path.join(G, f"extract_{name}.npz"))
+    img = synth.frame(int(g["seed"]), int(g["w"]), int(g["h"]), str(g["kind"]))
+    assert sha(img) == str(g["image_sha"]), "synthetic generator drifted"
+    p = O.params(int(g["nfeatures"]))
+    kps, desc, pyr = O.extract(p, img, want_pyr=True)
+    o = 0
+    for (w, h), want in zip(O.level_sizes(p, img.shape[1], img.shape[0]), g["pyr_sha"]):
+        assert sha(pyr[o:o + w * h]) == str(want)
+        o += w * h
+    kp = g["kp"]
+    assert len(kps) == len(kp)
+    for i, f in enumerate(("x", "y", "size", "angle", "response")):
+        assert np.array_equal(kps[f].view(np.uint32), kp[:, i].view(np.uint32)), f
+    assert np.array_equal(kps["octave"], g["octave"])
+    assert np.array_equal(desc, g["desc"])
+    assert (kps["class_id"] == -1).all()
+
+
+def test_ctor_tables():
+    p = O.params(1000)
+    assert list(p.nfeat_level)[:8] == [217, 181, 151, 126, 105, 87, 73, 60]
+    assert list(p.umax) == [15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3]
+    assert O.level_sizes(p, 640, 480) == [(640, 480), (533, 400), (444, 333), (370, 278), (309, 231), (257, 193), (214, 161), (179, 134)]
+    assert list(O.params(4000).nfeat_level)[:8] == [869, 724, 603, 503, 419, 349, 291, 242]

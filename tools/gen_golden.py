@@ -1,0 +1,52 @@
+#!/usr/bin/env python3
+"""Generate tests/golden/*.npz with the REAL third-party primitives (cv2 4.13, host libm).
+
+Run in the build container only (cv2 present):  python tools/gen_golden.py
+Fixtures pin the oracle (oracle/) to executable copies of the arithmetic the reference
+calls: cv::resize, cv::GaussianBlur, cv::FAST per ROI, cv::fastAtan2, cv::copyMakeBorder,
+and the whole operator() through tools/pyref_orb.py (cv2 primitives + restated control flow).
+Inputs come from tests/synth.py seeds, so only outputs are stored.
+"""
+import os, sys, hashlib
+import numpy as np, cv2
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tests")); sys.path.insert(0, os.path.join(ROOT, "tools"))
+import synth, pyref_orb as R
+G = os.path.join(ROOT, "tests", "golden")
+os.makedirs(G, exist_ok=True)
+
+def sha(a): return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+# --- primitives ---
+prim = {}
+img = synth.frame(11, 213, 160)
+for (dw, dh) in [(178, 133), (200, 150), (107, 80), (300, 231)]:
+    prim[f"resize_{dw}x{dh}"] = cv2.resize(img, (dw, dh), interpolation=cv2.INTER_LINEAR)
+prim["blur9"] = cv2.GaussianBlur(img, (9, 9), 2, sigmaY=2, borderType=cv2.BORDER_REFLECT_101)
+prim["blur7"] = cv2.GaussianBlur(img, (7, 7), 2, sigmaY=2, borderType=cv2.BORDER_REFLECT_101)
+prim["border19"] = cv2.copyMakeBorder(img, 19, 19, 19, 19, cv2.BORDER_REFLECT_101)
+rng = np.random.default_rng(5)
+yx = rng.integers(-2000000, 2000000, size=(4000, 2)).astype(np.float32)
+yx[:8] = [[0, 0], [0, 1], [1, 0], [0, -1], [-1, 0], [5, 5], [-5, 5], [3, -3]]
+prim["atan2_in"] = yx
+prim["atan2_out"] = np.array([cv2.fastAtan2(float(a), float(b)) for a, b in yx], np.float32)
+for th in (7, 20):
+    for k, (seed, kind) in enumerate([(21, "texture"), (22, "noise"), (23, "gradient")]):
+        roi = synth.frame(seed, 43, 41, kind)
+        kp = cv2.FastFeatureDetector_create(th, True).detect(roi)
+        prim[f"fast_{kind}_{th}"] = np.array([[int(q.pt[0]), int(q.pt[1]), int(q.response)] for q in kp], np.int32).reshape(-1, 3)
+np.savez_compressed(os.path.join(G, "primitives.npz"), **prim)
+
+# --- whole operator() ---
+pat = R.load_pattern(os.path.join(ROOT, "oracle", "brief_pattern.inc"))
+cases = [("tum", 0, 640, 480, 1000, "texture"), ("euroc", 1, 752, 480, 1200, "texture"),
+         ("kitti", 4, 1241, 376, 2000, "texture"), ("grad", 2, 320, 240, 500, "gradient"),
+         ("noise", 3, 640, 480, 1000, "noise"), ("black", 0, 160, 120, 300, "black"),
+         ("small", 6, 96, 80, 200, "texture")]
+for name, seed, w, h, nf, kind in cases:
+    im = synth.frame(seed, w, h, kind)
+    kp, octv, desc, pyr, cands = R.extract(im, R.Params(nf, 1.2, 8, 20, 7), pat)
+    np.savez_compressed(os.path.join(G, f"extract_{name}.npz"), seed=seed, w=w, h=h, nfeatures=nf, kind=kind,
+                        image_sha=sha(im), kp=kp, octave=octv, desc=desc,
+                        pyr_sha=np.array([sha(x) for x in pyr]), ncand=np.array([len(c) for c in cands]))
+    print(name, len(kp), [len(c) for c in cands])
