@@ -1,0 +1,106 @@
+/* orbx -- B200-native ORB front end: C ABI (the drop-in boundary).
+ *
+ * Everything the reference's ORBextractor / ORBmatcher hot path needs, as plain-C entry points
+ * (pointers + sizes, no C++/torch types).  The reference-compatible C++ classes in
+ * include/ORBextractor.h / include/ORBmatcher.h are thin wrappers over these.
+ * Citations are relative to the reference checkout (QiuYue-bit/ORB-SLAM2-noted).
+ *
+ * Conventions: every call returns ORBX_OK (0) or a negative orbx_status; nothing throws or aborts.
+ * The caller owns all in/out buffers; a ctx owns its device memory and one CUDA stream.  A ctx is
+ * used by one thread at a time; distinct ctxs are independent (the reference runs two extractor
+ * instances concurrently for stereo, src/Frame.cc:144-153).  There is NO CPU fallback: without a
+ * CUDA device orbx_create fails with ORBX_E_CUDA.
+ */
+#ifndef ORBX_H
+#define ORBX_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct orbx_ctx orbx_ctx;
+
+/* Binary layout of cv::KeyPoint (28 bytes), as filled by src/ORBextractor.cc:1141-1186,1642-1656 */
+typedef struct { float x, y, size, angle, response; int32_t octave, class_id; } orbx_keypoint;
+
+typedef enum {
+    ORBX_OK = 0,
+    ORBX_E_INVALID = -1,     /* bad argument */
+    ORBX_E_CUDA = -2,        /* CUDA runtime error (see orbx_last_cuda_error) */
+    ORBX_E_NOMEM = -3,
+    ORBX_E_CAPACITY = -4,    /* caller buffer too small / batch or image larger than the ctx was created for */
+    ORBX_E_UNSUPPORTED = -5  /* geometry the reference itself cannot process (e.g. width/height < 0.5) */
+} orbx_status;
+
+enum { ORBX_IN_DEVICE = 1, ORBX_OUT_DEVICE = 2 }; /* flags: where image / result buffers live */
+
+#define ORBX_MAX_LEVELS 16
+
+/* ---- lifetime.  Replaces ORBextractor::ORBextractor, src/ORBextractor.cc:471-579 ---- */
+int orbx_create(orbx_ctx** out, int device, int nfeatures, float scale_factor, int nlevels,
+                int ini_th_fast, int min_th_fast, int max_w, int max_h, int max_batch);
+void orbx_destroy(orbx_ctx* ctx);
+const char* orbx_strerror(int status);
+const char* orbx_last_cuda_error(const orbx_ctx* ctx);
+
+/* ---- getters.  Replace GetLevels/GetScaleFactor(s)/GetInverseScaleFactors/GetScaleSigmaSquares/
+ *      GetInverseScaleSigmaSquares, include/ORBextractor.h:115-149.  Arrays hold nlevels entries. ---- */
+int orbx_get_levels(const orbx_ctx* ctx);
+float orbx_get_scale_factor(const orbx_ctx* ctx);
+int orbx_get_tables(const orbx_ctx* ctx, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                    int* features_per_level);
+/* per-frame cap that can never overflow: sum over levels of (quota + 3), rounded up to 32 */
+int orbx_max_keypoints(const orbx_ctx* ctx);
+
+/* ---- extraction.  Replaces ORBextractor::operator(), src/ORBextractor.cc:1543-1658
+ *      (ComputePyramid :1664-1733, ComputeKeyPointsOctTree :1046-1195, DistributeOctTree :696-1042,
+ *       IC_Angle :94-141, GaussianBlur :1617-1625, computeOrbDescriptor :153-204). ----
+ * img: 8-bit single channel, `stride` bytes per row.  kps/desc receive n_out keypoints in the reference's
+ * order (level 0..L-1, quadtree list order inside a level); desc is n x 32 bytes.  An empty image
+ * (w or h == 0, or img == NULL) leaves outputs untouched and sets *n_out = 0, like :1547. */
+int orbx_extract(orbx_ctx* ctx, const uint8_t* img, int w, int h, size_t stride, int flags,
+                 orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out);
+/* B frames of identical geometry, frame b at imgs + b*frame_stride.  Results for frame b are written at
+ * kps + b*cap_per_frame, desc + b*cap_per_frame*32, n_out[b].  With ORBX_OUT_DEVICE the call is
+ * asynchronous on the ctx stream (use orbx_sync). */
+int orbx_extract_batch(orbx_ctx* ctx, const uint8_t* imgs, int batch, int w, int h, size_t stride,
+                       size_t frame_stride, int flags, orbx_keypoint* kps, uint8_t* desc,
+                       int cap_per_frame, int* n_out);
+/* Level image of frame `frame` of the LAST extract call (mvImagePyramid, include/ORBextractor.h:158).
+ * border = 0: the w x h level; border = 19: with the reflect-101 frame of src/ORBextractor.cc:1704-1727.
+ * dst is host memory unless flags has ORBX_OUT_DEVICE. */
+int orbx_pyramid_level(orbx_ctx* ctx, int frame, int level, int border, int flags, uint8_t* dst,
+                       size_t dst_stride, int* w, int* h);
+int orbx_level_size(const orbx_ctx* ctx, int level, int w0, int h0, int* w, int* h);
+
+/* ---- stream / instrumentation (used by bench.py and tests; not part of the reference surface) ---- */
+int orbx_sync(orbx_ctx* ctx);
+void* orbx_stream(orbx_ctx* ctx);                 /* cudaStream_t */
+int orbx_set_profiling(orbx_ctx* ctx, int on);     /* record CUDA events around every stage */
+/* stage names: "pyramid","fast","octree","blur","describe","h2d","d2h","hamming", ... */
+int orbx_stage_count(void);
+const char* orbx_stage_name(int i);
+int orbx_stage_stats(orbx_ctx* ctx, int i, double* total_ms, long long* launches); /* syncs; since last reset */
+int orbx_reset_stats(orbx_ctx* ctx);
+long long orbx_kernel_launches(const orbx_ctx* ctx); /* kernels launched by this ctx since creation */
+
+/* ---- 256-bit Hamming matching.  Replaces ORBmatcher::DescriptorDistance src/ORBmatcher.cc:2123-2143
+ *      and the best/second-best inner loops of the Search* functions. ---- */
+/* Pairwise distances for n pairs (host or device pointers per flags). */
+int orbx_descriptor_distance(orbx_ctx* ctx, const uint8_t* a, const uint8_t* b, int n, int flags, int32_t* dist);
+/* Many-vs-many, segmented: query i in segment s is compared with every train j of the same segment
+ * (segments = BoW nodes / row bands / the whole set when nseg == 1); q_seg/t_seg are CSR offsets
+ * (nseg+1 entries) into q_idx/t_idx index lists (NULL lists = identity).  For each query row the
+ * best (lowest distance, first train in list order on ties) and second-best distances are returned:
+ * exactly the state of the loops at src/ORBmatcher.cc:325-345 before acceptance.
+ * t_valid (optional, per train descriptor, 0 = skip) models the `continue`s at :323,:822-826. */
+int orbx_hamming_best2(orbx_ctx* ctx, const uint8_t* q_desc, int nq, const uint8_t* t_desc, int nt,
+                       const int32_t* q_seg, const int32_t* q_idx, const int32_t* t_seg, const int32_t* t_idx,
+                       int nseg, const uint8_t* t_valid, int flags,
+                       int32_t* best_idx, int32_t* best_dist, int32_t* second_dist);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

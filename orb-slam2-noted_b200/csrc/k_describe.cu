@@ -1,0 +1,208 @@
+// K4a + K5 -- IC_Angle (src/ORBextractor.cc:94-141, cv::fastAtan2) and computeOrbDescriptor (:153-204),
+// fused: one warp per selected keypoint.  Also performs the final assembly of operator() (:1595-1656):
+// level-major concatenation, pt *= scale for level > 0.
+//
+// Bit-exactness notes (all float ops are explicit round-to-nearest intrinsics, never contracted to FMA,
+// because the reference is built for baseline x86-64 without FMA, CMakeLists.txt:16-22):
+//  * moments are int32 sums (exact, any reduction order);
+//  * fastAtan2 is the scalar OpenCV polynomial evaluated with __fmul_rn/__fadd_rn/__fdiv_rn;
+//  * cos/sin follow glibc 2.39's sinf/cosf (__sinf_fma/__cosf_fma variants): double-precision
+//    reduction + polynomial with exactly the FMA contraction pattern of that build;
+//  * sample coordinates use cvRound = round-half-even = __float2int_rn.
+#include "orbx_internal.h"
+
+namespace orbx {
+
+__device__ __align__(16) const signed char kBriefPattern[1024] = {
+#include "brief_pattern.inc"
+};
+
+__device__ __forceinline__ float fastAtan2Dev(float y, float x)
+{
+    const float k = (float)(180 / 3.14159265358979323846);
+    const float p1 = 0.9997878412794807f * k, p3 = -0.3258083974640975f * k;   // constant-folded in fp32
+    const float p5 = 0.1555786518463281f * k, p7 = -0.04432655554792128f * k;
+    const float ax = fabsf(x), ay = fabsf(y);
+    const float eps = (float)2.2204460492503131e-16; // (float)DBL_EPSILON
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+// glibc 2.39 sincosf polynomial; n even: sine, n odd: cosine; neg: coefficients of table[1]
+__device__ __forceinline__ float glibcPoly(double x, double x2, int n, bool neg)
+{
+    const double S1 = -0x1.555545995a603p-3, S2 = 0x1.1107605230bc4p-7, S3 = -0x1.994eb3774cf24p-13;
+    const double C0 = 0x1p0, C1 = -0x1.ffffffd0c621cp-2, C2 = 0x1.55553e1068f19p-5,
+                 C3 = -0x1.6c087e89a359dp-10, C4 = 0x1.99343027bf8c3p-16;
+    if ((n & 1) == 0) {
+        const double x3 = __dmul_rn(x, x2);
+        const double s1 = __fma_rn(S3, x2, S2);
+        const double x7 = __dmul_rn(x3, x2);
+        const double s = __fma_rn(x3, S1, x);
+        return __double2float_rn(__fma_rn(s1, x7, s));
+    }
+    const double sg = neg ? -1.0 : 1.0;
+    const double x4 = __dmul_rn(x2, x2);
+    const double c2 = __fma_rn(sg * C4, x2, sg * C3);
+    const double c1 = __fma_rn(sg * C1, x2, sg * C0);
+    const double x6 = __dmul_rn(x4, x2);
+    const double c = __fma_rn(x4, sg * C2, c1);
+    return __double2float_rn(__fma_rn(c2, x6, c));
+}
+
+__device__ __forceinline__ void glibcSinCosf(float y, float& s, float& c)
+{
+    const uint32_t top = (__float_as_uint(y) >> 20) & 0x7ff;
+    double x = (double)y;
+    if (top < 0x3f4) {
+        const double x2 = __dmul_rn(x, x);
+        if (top <= 0x397) { s = y; c = 1.0f; return; }
+        s = glibcPoly(x, x2, 0, false);
+        c = glibcPoly(x, x2, 1, false);
+        return;
+    }
+    const double r = __dmul_rn(x, 0x1.45F306DC9C883p+23);
+    const int n = (__double2int_rz(r) + 0x800000) >> 24;
+    x = __fma_rn(-(double)n, 0x1.921FB54442D18p0, x);
+    const double sign = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;
+    const double xs = __dmul_rn(x, sign), x2 = __dmul_rn(x, x);
+    const bool neg = (n & 2) != 0;
+    s = glibcPoly(xs, x2, n, neg);
+    c = glibcPoly(xs, x2, n ^ 1, neg);
+}
+
+// exported for the exhaustive device-vs-libm test
+__global__ void sincosfProbeKernel(uint32_t firstBits, uint32_t count, float* s, float* c)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    glibcSinCosf(__uint_as_float(firstBits + i), s[i], c[i]);
+}
+
+__global__ void atan2ProbeKernel(const float* yx, int n, float* out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = fastAtan2Dev(yx[2 * i], yx[2 * i + 1]);
+}
+
+constexpr int kDescWarps = 8;
+
+__global__ void __launch_bounds__(kDescWarps * 32)
+describeKernel(const GeomSet* __restrict__ G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
+               const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
+               const orbx_keypoint* __restrict__ selAll, const int* __restrict__ selCount,
+               orbx_keypoint* __restrict__ outKp, uint8_t* __restrict__ outDesc, int cap, int* __restrict__ outN,
+               int* __restrict__ err)
+{
+    const int lane = threadIdx.x & 31;
+    const int slot = blockIdx.x * kDescWarps + (threadIdx.x >> 5);
+    const int frame = blockIdx.y;
+    if (slot >= G->selPerFrame) return;
+    int level = 0;
+    while (level + 1 < G->nlevels && slot >= G->lv[level + 1].outBase) ++level;
+    const LevelGeom& g = G->lv[level];
+    const int pos = slot - g.outBase;
+    const int* cnts = selCount + frame * G->nlevels;
+    int before = 0, total = 0;
+    for (int l = 0; l < G->nlevels; ++l) { const int c = cnts[l]; if (l < level) before += c; total += c; }
+    if (slot == 0 && lane == 0) outN[frame] = min(total, cap);
+    if (pos >= cnts[level]) return;
+    const int idx = before + pos;
+    if (idx >= cap) { if (lane == 0) atomicExch(err, 5); return; }
+
+    orbx_keypoint kp = selAll[(size_t)frame * G->selPerFrame + slot];
+    const int cx = __float2int_rn(kp.x), cy = __float2int_rn(kp.y);
+    const uint8_t* img; size_t pitch;
+    if (level == 0) { img = lvl0 + (size_t)frame * lvl0Frame; pitch = lvl0Pitch; }
+    else { img = pyr + g.planeOff + (size_t)frame * g.pitch * g.h; pitch = (size_t)g.pitch; }
+
+    // ---- IC_Angle: lane v-row of the 31-row disc ----
+    int m10 = 0, m01 = 0;
+    if (lane < 2 * kHalfPatch + 1) {
+        const int v = lane - kHalfPatch;
+        const int d = G->umax[v < 0 ? -v : v];
+        const uint8_t* row = img + (size_t)(cy + v) * pitch + cx;
+        int rs = 0;
+        for (int u = -d; u <= d; ++u) { const int p = row[u]; rs += p; m10 += u * p; }
+        m01 = v * rs;
+    }
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { m10 += __shfl_xor_sync(0xffffffffu, m10, o); m01 += __shfl_xor_sync(0xffffffffu, m01, o); }
+    const float angle = fastAtan2Dev((float)m01, (float)m10);
+
+    // ---- steered BRIEF on the blurred level: lane = descriptor byte ----
+    const float factorPI = (float)(3.14159265358979323846 / 180.f);
+    float a, b;
+    glibcSinCosf(__fmul_rn(angle, factorPI), b, a); // a = cos, b = sin  (:158)
+    const uint8_t* bl = blur + g.blurOff + (size_t)frame * g.pitch * g.h + (size_t)cy * g.pitch + cx;
+    const int bp = g.pitch;
+    const char4* pat = reinterpret_cast<const char4*>(kBriefPattern) + lane * 8;
+    int val = 0;
+    #pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const char4 q = pat[k];
+        const float x0 = (float)q.x, y0 = (float)q.y, x1 = (float)q.z, y1 = (float)q.w;
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
+        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        const int t0 = bl[r0 * bp + c0], t1 = bl[r1 * bp + c1];
+        val |= (t0 < t1) << k;
+    }
+    outDesc[((size_t)frame * cap + idx) * 32 + lane] = (uint8_t)val;
+    if (lane == 0) {
+        kp.angle = angle;
+        if (level != 0) { kp.x = __fmul_rn(kp.x, g.scale); kp.y = __fmul_rn(kp.y, g.scale); }
+        outKp[(size_t)frame * cap + idx] = kp;
+    }
+}
+
+int launchDescribe(Ctx* c, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN)
+{
+    const GeomSet& g = c->geom;
+    stageBegin(c, ST_DESCRIBE);
+    dim3 grid((g.selPerFrame + kDescWarps - 1) / kDescWarps, batch), block(kDescWarps * 32);
+    describeKernel<<<grid, block, 0, c->stream>>>(c->dGeom, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur,
+                                                 c->dSel, c->dSelCount, dKps, dDesc, capPerFrame, dN, c->dErr);
+    stageEnd(c, ST_DESCRIBE, 1);
+    ORBX_CUDA(c, cudaGetLastError());
+    return ORBX_OK;
+}
+
+} // namespace orbx
+
+// ---- test probes (C ABI, declared in include/orbx_test.h) ----
+extern "C" int orbx_test_sincosf(uint32_t first_bits, uint32_t count, float* h_sin, float* h_cos)
+{
+    float *ds = nullptr, *dc = nullptr;
+    if (cudaMalloc(&ds, sizeof(float) * (size_t)count) != cudaSuccess) return ORBX_E_CUDA;
+    if (cudaMalloc(&dc, sizeof(float) * (size_t)count) != cudaSuccess) { cudaFree(ds); return ORBX_E_CUDA; }
+    orbx::sincosfProbeKernel<<<(count + 255) / 256, 256>>>(first_bits, count, ds, dc);
+    cudaError_t e = cudaMemcpy(h_sin, ds, sizeof(float) * (size_t)count, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(h_cos, dc, sizeof(float) * (size_t)count, cudaMemcpyDeviceToHost);
+    cudaFree(ds); cudaFree(dc);
+    return e == cudaSuccess ? ORBX_OK : ORBX_E_CUDA;
+}
+
+extern "C" int orbx_test_fast_atan2(const float* h_yx, int n, float* h_out)
+{
+    float *d = nullptr, *o = nullptr;
+    if (cudaMalloc(&d, sizeof(float) * 2 * (size_t)n) != cudaSuccess) return ORBX_E_CUDA;
+    if (cudaMalloc(&o, sizeof(float) * (size_t)n) != cudaSuccess) { cudaFree(d); return ORBX_E_CUDA; }
+    cudaMemcpy(d, h_yx, sizeof(float) * 2 * (size_t)n, cudaMemcpyHostToDevice);
+    orbx::atan2ProbeKernel<<<(n + 255) / 256, 256>>>(d, n, o);
+    cudaError_t e = cudaMemcpy(h_out, o, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost);
+    cudaFree(d); cudaFree(o);
+    return e == cudaSuccess ? ORBX_OK : ORBX_E_CUDA;
+}

@@ -1,0 +1,180 @@
+// K6 -- 256-bit Hamming core of ORBmatcher (DescriptorDistance, src/ORBmatcher.cc:2123-2143) as a
+// segmented many-vs-many XOR+POPC kernel with running best / second-best (the inner loops at
+// :325-345, :828-843, :1013-1052; Frame::ComputeStereoMatches src/Frame.cc:937-978).
+//
+// Integer/POPC-pipe bound by design (8 x POPC32 per descriptor pair); no tensor cores.
+// One CTA = up to 256 query rows of one segment (2 per thread, descriptors held in 16 registers);
+// train descriptors stream through shared memory in 128-descriptor chunks and are read as
+// warp-broadcast 128-bit loads, so each LDS feeds 2 x 4 POPCs per thread.
+#include "orbx_internal.h"
+
+namespace orbx {
+
+constexpr int kHamThreads = 128, kHamQPT = 2, kHamChunk = 128;
+
+__device__ __forceinline__ int dist256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
+{
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+__global__ void pairDistanceKernel(const uint4* __restrict__ a, const uint4* __restrict__ b, int n, int32_t* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = dist256(a[2 * i], a[2 * i + 1], b[2 * i], b[2 * i + 1]);
+}
+
+__global__ void __launch_bounds__(kHamThreads)
+hammingBest2Kernel(const uint4* __restrict__ qDesc, const uint4* __restrict__ tDesc,
+                   const int32_t* __restrict__ qSeg, const int32_t* __restrict__ qIdx,
+                   const int32_t* __restrict__ tSeg, const int32_t* __restrict__ tIdx,
+                   const int32_t* __restrict__ blockPrefix, int nseg, const uint8_t* __restrict__ tValid,
+                   int32_t* __restrict__ bestIdx, int32_t* __restrict__ bestDist, int32_t* __restrict__ secondDist)
+{
+    __shared__ uint4 sT[kHamChunk * 2];
+    __shared__ int sTi[kHamChunk]; // train descriptor index, or -1 when masked out
+    // segment of this CTA: largest s with blockPrefix[s] <= blockIdx.x
+    int lo = 0, hi = nseg;
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (blockPrefix[mid] <= (int)blockIdx.x) lo = mid; else hi = mid; }
+    const int seg = lo;
+    const int qb = (blockIdx.x - blockPrefix[seg]) * (kHamThreads * kHamQPT);
+    const int q0 = qSeg[seg], q1 = qSeg[seg + 1], t0 = tSeg[seg], t1 = tSeg[seg + 1];
+
+    uint4 qa[kHamQPT], qbv[kHamQPT];
+    int row[kHamQPT], b1[kHamQPT], b2[kHamQPT], bi[kHamQPT];
+    #pragma unroll
+    for (int k = 0; k < kHamQPT; ++k) {
+        row[k] = q0 + qb + k * kHamThreads + threadIdx.x;
+        b1[k] = 256; b2[k] = 256; bi[k] = -1;
+        if (row[k] < q1) {
+            const int qi = qIdx ? qIdx[row[k]] : row[k];
+            qa[k] = qDesc[2 * qi]; qbv[k] = qDesc[2 * qi + 1];
+        } else { qa[k] = make_uint4(0, 0, 0, 0); qbv[k] = qa[k]; }
+    }
+    for (int c = t0; c < t1; c += kHamChunk) {
+        const int m = min(kHamChunk, t1 - c);
+        __syncthreads();
+        for (int i = threadIdx.x; i < m; i += kHamThreads) {
+            const int ti = tIdx ? tIdx[c + i] : c + i;
+            const bool ok = !tValid || tValid[ti];
+            sTi[i] = ok ? ti : -1;
+            sT[2 * i] = tDesc[2 * ti]; sT[2 * i + 1] = tDesc[2 * ti + 1];
+        }
+        __syncthreads();
+        for (int i = 0; i < m; ++i) {
+            const int ti = sTi[i];
+            if (ti < 0) continue; // uniform across the CTA
+            const uint4 ta = sT[2 * i], tb = sT[2 * i + 1];
+            #pragma unroll
+            for (int k = 0; k < kHamQPT; ++k) {
+                const int d = dist256(qa[k], qbv[k], ta, tb);
+                if (d < b1[k]) { b2[k] = b1[k]; b1[k] = d; bi[k] = ti; }
+                else if (d < b2[k]) b2[k] = d;
+            }
+        }
+    }
+    #pragma unroll
+    for (int k = 0; k < kHamQPT; ++k)
+        if (row[k] < q1) { bestIdx[row[k]] = bi[k]; bestDist[row[k]] = b1[k]; secondDist[row[k]] = b2[k]; }
+}
+
+} // namespace orbx
+using namespace orbx;
+
+extern "C" int orbx_descriptor_distance(orbx_ctx* h, const uint8_t* a, const uint8_t* b, int n, int flags, int32_t* dist)
+{
+    if (!h || n < 0 || (n > 0 && (!a || !b || !dist))) return ORBX_E_INVALID;
+    if (n == 0) return ORBX_OK;
+    Ctx* c = &h->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    const uint4 *da = (const uint4*)a, *db = (const uint4*)b; int32_t* dd = dist;
+    const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
+    if (!inDev || !outDev) {
+        int rc = ensureScratch(c, (size_t)n * 68);
+        if (rc) return rc;
+        uint8_t* s = (uint8_t*)c->dScratch;
+        if (!inDev) {
+            ORBX_CUDA(c, cudaMemcpyAsync(s, a, (size_t)n * 32, cudaMemcpyHostToDevice, c->stream));
+            ORBX_CUDA(c, cudaMemcpyAsync(s + (size_t)n * 32, b, (size_t)n * 32, cudaMemcpyHostToDevice, c->stream));
+            da = (const uint4*)s; db = (const uint4*)(s + (size_t)n * 32);
+        }
+        if (!outDev) dd = (int32_t*)(s + (size_t)n * 64);
+    }
+    stageBegin(c, ST_HAMMING);
+    pairDistanceKernel<<<(n + 255) / 256, 256, 0, c->stream>>>(da, db, n, dd);
+    stageEnd(c, ST_HAMMING, 1);
+    ORBX_CUDA(c, cudaGetLastError());
+    if (!outDev) {
+        ORBX_CUDA(c, cudaMemcpyAsync(dist, dd, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return ORBX_OK;
+}
+
+// q_seg / t_seg are always HOST arrays (nseg+1 CSR offsets); everything else follows `flags`.
+extern "C" int orbx_hamming_best2(orbx_ctx* h, const uint8_t* q_desc, int nq, const uint8_t* t_desc, int nt,
+                                  const int32_t* q_seg, const int32_t* q_idx, const int32_t* t_seg, const int32_t* t_idx,
+                                  int nseg, const uint8_t* t_valid, int flags,
+                                  int32_t* best_idx, int32_t* best_dist, int32_t* second_dist)
+{
+    if (!h || nq < 0 || nt < 0 || nseg < 1 || !q_seg || !t_seg || !best_idx || !best_dist || !second_dist) return ORBX_E_INVALID;
+    if ((nq > 0 && !q_desc) || (nt > 0 && !t_desc)) return ORBX_E_INVALID;
+    Ctx* c = &h->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    const int nrowQ = q_seg[nseg], nrowT = t_seg[nseg];
+    if (nrowQ == 0) return ORBX_OK;
+    std::vector<int32_t> prefix((size_t)nseg + 1);
+    const int per = kHamThreads * kHamQPT;
+    prefix[0] = 0;
+    for (int s = 0; s < nseg; ++s) {
+        if (q_seg[s + 1] < q_seg[s] || t_seg[s + 1] < t_seg[s]) return ORBX_E_INVALID;
+        prefix[s + 1] = prefix[s] + (q_seg[s + 1] - q_seg[s] + per - 1) / per;
+    }
+    const int nblocks = prefix[nseg];
+    const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
+    // scratch layout: [prefix | qSeg | tSeg | (host inputs) | (host outputs)]
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t oPrefix = take(sizeof(int32_t) * (nseg + 1)), oQs = take(sizeof(int32_t) * (nseg + 1)), oTs = take(sizeof(int32_t) * (nseg + 1));
+    size_t oQ = 0, oT = 0, oQi = 0, oTi = 0, oTv = 0, oOut = 0;
+    if (!inDev) {
+        oQ = take((size_t)nq * 32); oT = take((size_t)nt * 32);
+        if (q_idx) oQi = take(sizeof(int32_t) * (size_t)nrowQ);
+        if (t_idx) oTi = take(sizeof(int32_t) * (size_t)nrowT);
+        if (t_valid) oTv = take((size_t)nt);
+    }
+    if (!outDev) oOut = take(sizeof(int32_t) * 3 * (size_t)nrowQ);
+    int rc = ensureScratch(c, off);
+    if (rc) return rc;
+    uint8_t* S = (uint8_t*)c->dScratch;
+    stageBegin(c, ST_H2D);
+    ORBX_CUDA(c, cudaMemcpyAsync(S + oPrefix, prefix.data(), sizeof(int32_t) * (nseg + 1), cudaMemcpyHostToDevice, c->stream));
+    ORBX_CUDA(c, cudaMemcpyAsync(S + oQs, q_seg, sizeof(int32_t) * (nseg + 1), cudaMemcpyHostToDevice, c->stream));
+    ORBX_CUDA(c, cudaMemcpyAsync(S + oTs, t_seg, sizeof(int32_t) * (nseg + 1), cudaMemcpyHostToDevice, c->stream));
+    const uint4 *dq = (const uint4*)q_desc, *dt = (const uint4*)t_desc;
+    const int32_t *dqi = q_idx, *dti = t_idx; const uint8_t* dtv = t_valid;
+    if (!inDev) {
+        ORBX_CUDA(c, cudaMemcpyAsync(S + oQ, q_desc, (size_t)nq * 32, cudaMemcpyHostToDevice, c->stream)); dq = (const uint4*)(S + oQ);
+        ORBX_CUDA(c, cudaMemcpyAsync(S + oT, t_desc, (size_t)nt * 32, cudaMemcpyHostToDevice, c->stream)); dt = (const uint4*)(S + oT);
+        if (q_idx) { ORBX_CUDA(c, cudaMemcpyAsync(S + oQi, q_idx, sizeof(int32_t) * (size_t)nrowQ, cudaMemcpyHostToDevice, c->stream)); dqi = (const int32_t*)(S + oQi); }
+        if (t_idx) { ORBX_CUDA(c, cudaMemcpyAsync(S + oTi, t_idx, sizeof(int32_t) * (size_t)nrowT, cudaMemcpyHostToDevice, c->stream)); dti = (const int32_t*)(S + oTi); }
+        if (t_valid) { ORBX_CUDA(c, cudaMemcpyAsync(S + oTv, t_valid, (size_t)nt, cudaMemcpyHostToDevice, c->stream)); dtv = S + oTv; }
+    }
+    stageEnd(c, ST_H2D, 0);
+    int32_t *dbi = best_idx, *dbd = best_dist, *dsd = second_dist;
+    if (!outDev) { dbi = (int32_t*)(S + oOut); dbd = dbi + nrowQ; dsd = dbd + nrowQ; }
+    stageBegin(c, ST_HAMMING);
+    hammingBest2Kernel<<<nblocks, kHamThreads, 0, c->stream>>>(dq, dt, (const int32_t*)(S + oQs), dqi, (const int32_t*)(S + oTs), dti,
+                                                               (const int32_t*)(S + oPrefix), nseg, dtv, dbi, dbd, dsd);
+    stageEnd(c, ST_HAMMING, 1);
+    ORBX_CUDA(c, cudaGetLastError());
+    if (!outDev) {
+        stageBegin(c, ST_D2H);
+        ORBX_CUDA(c, cudaMemcpyAsync(best_idx, dbi, sizeof(int32_t) * (size_t)nrowQ, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaMemcpyAsync(best_dist, dbd, sizeof(int32_t) * (size_t)nrowQ, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaMemcpyAsync(second_dist, dsd, sizeof(int32_t) * (size_t)nrowQ, cudaMemcpyDeviceToHost, c->stream));
+        stageEnd(c, ST_D2H, 0);
+        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return ORBX_OK;
+}

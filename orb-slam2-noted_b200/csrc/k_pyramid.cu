@@ -1,0 +1,85 @@
+// K1 -- ComputePyramid (src/ORBextractor.cc:1664-1733): chained 8-bit bilinear resize with the
+// exact fixed-point arithmetic of cv::resize(INTER_LINEAR) (11-bit weights, (b*(T>>4))>>16, +2>>2),
+// plus the reflect-101 border copy used only when a caller asks for mvImagePyramid with its frame.
+// HBM-streaming integer kernel: 4 output pixels per thread, one 32-bit store, taps from a tiny
+// per-level table (L1/L2 resident).  Level l is produced from level l-1, so levels are separate
+// launches; the batch dimension provides the parallelism (grid.z = frames).
+#include "orbx_internal.h"
+
+namespace orbx {
+
+__global__ void __launch_bounds__(128)
+resizeLinearKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sFrame, int sw, int sh,
+                   uint8_t* __restrict__ dst, size_t dPitch, size_t dFrame, int dw, int dh,
+                   const ResizeTap* __restrict__ tapX, const ResizeTap* __restrict__ tapY)
+{
+    const int y = blockIdx.y;
+    const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (x0 >= dw) return;
+    const ResizeTap ty = tapY[y];
+    int r0 = ty.s, r1 = ty.s + 1;           // rows are clipped, weights kept (OpenCV VResize)
+    r1 = r1 > sh - 1 ? sh - 1 : r1;
+    const uint8_t* S0 = src + (size_t)blockIdx.z * sFrame + (size_t)r0 * sPitch;
+    const uint8_t* S1 = src + (size_t)blockIdx.z * sFrame + (size_t)r1 * sPitch;
+    const int b0 = ty.c0, b1 = ty.c1;
+    uint32_t packed = 0;
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int x = x0 + i;
+        if (x < dw) {
+            const ResizeTap tx = tapX[x];
+            const int sx = tx.s, sx1 = min(sx + 1, sw - 1);
+            const int t0 = (int)S0[sx] * tx.c0 + (int)S0[sx1] * tx.c1;
+            const int t1 = (int)S1[sx] * tx.c0 + (int)S1[sx1] * tx.c1;
+            const int v = (((b0 * (t0 >> 4)) >> 16) + ((b1 * (t1 >> 4)) >> 16) + 2) >> 2;
+            packed |= (uint32_t)(v & 0xff) << (8 * i);
+        }
+    }
+    // rows are padded to a multiple of 16 bytes, so the 4-byte store never leaves the row
+    *reinterpret_cast<uint32_t*>(dst + (size_t)blockIdx.z * dFrame + (size_t)y * dPitch + x0) = packed;
+}
+
+int launchPyramid(Ctx* c, int batch)
+{
+    const GeomSet& g = c->geom;
+    stageBegin(c, ST_PYRAMID);
+    int launches = 0;
+    for (int l = 1; l < g.nlevels; ++l) {
+        const LevelGeom& d = g.lv[l];
+        const LevelGeom& s = g.lv[l - 1];
+        const uint8_t* src; size_t sp, sf;
+        if (l == 1) { src = c->lvl0; sp = c->lvl0Pitch; sf = c->lvl0FrameStride; }
+        else { src = c->dPyr + s.planeOff; sp = (size_t)s.pitch; sf = (size_t)s.pitch * s.h; }
+        dim3 grid((d.w + 511) / 512, d.h, batch), block(128);
+        resizeLinearKernel<<<grid, block, 0, c->stream>>>(src, sp, sf, s.w, s.h, c->dPyr + d.planeOff, (size_t)d.pitch,
+                                                         (size_t)d.pitch * d.h, d.w, d.h, c->dTapX[l], c->dTapY[l]);
+        ++launches;
+    }
+    stageEnd(c, ST_PYRAMID, launches);
+    ORBX_CUDA(c, cudaGetLastError());
+    return ORBX_OK;
+}
+
+// reflect-101 frame (cv::copyMakeBorder, src/ORBextractor.cc:1704-1727): on demand only, the
+// extraction kernels never read the border (FAST/IC/BRIEF stay >= 1 px inside the level).
+__global__ void borderCopyKernel(const uint8_t* __restrict__ src, int w, int h, size_t pitch,
+                                 uint8_t* __restrict__ dst, size_t dpitch, int border)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+    if (x >= w + 2 * border) return;
+    int sx = x - border, sy = y - border;
+    if (w == 1) sx = 0; else { while (sx < 0 || sx >= w) sx = sx < 0 ? -sx : 2 * (w - 1) - sx; }
+    if (h == 1) sy = 0; else { while (sy < 0 || sy >= h) sy = sy < 0 ? -sy : 2 * (h - 1) - sy; }
+    dst[(size_t)y * dpitch + x] = src[(size_t)sy * pitch + sx];
+}
+
+int launchBorderCopy(Ctx* c, const uint8_t* src, int w, int h, size_t pitch, uint8_t* dst, size_t dpitch, int border)
+{
+    dim3 grid((w + 2 * border + 127) / 128, h + 2 * border), block(128);
+    borderCopyKernel<<<grid, block, 0, c->stream>>>(src, w, h, pitch, dst, dpitch, border);
+    c->kernelLaunches++;
+    ORBX_CUDA(c, cudaGetLastError());
+    return ORBX_OK;
+}
+
+} // namespace orbx

@@ -1,0 +1,461 @@
+// Host side of the C ABI (include/orbx.h): context, constructor tables, per-size geometry, the
+// extraction pipeline (H2D -> K1 pyramid -> K2 FAST cells -> K3 quadtree -> K4b blur -> K4a/K5 describe
+// -> D2H), instrumentation.  No CPU fallback anywhere: every stage is a CUDA kernel on ctx->stream.
+#include "orbx_internal.h"
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+#include <new>
+
+namespace orbx {
+
+static const char* kStageNames[ST_COUNT] = {"pyramid", "fast", "octree", "blur", "describe", "h2d", "d2h",
+                                            "hamming", "match", "stereo", "bow"};
+
+int cudaFail(Ctx* c, cudaError_t e, const char* what)
+{
+    if (c) { c->lastCudaError = std::string(what) + ": " + cudaGetErrorString(e); }
+    return ORBX_E_CUDA;
+}
+
+static cudaEvent_t takeEvent(Ctx* c)
+{
+    if (!c->eventPool.empty()) { cudaEvent_t e = c->eventPool.back(); c->eventPool.pop_back(); return e; }
+    cudaEvent_t e = nullptr; cudaEventCreate(&e); return e;
+}
+
+void stageBegin(Ctx* c, int stage)
+{
+    if (!c->profiling) return;
+    cudaEvent_t a = takeEvent(c), b = takeEvent(c);
+    cudaEventRecord(a, c->stream);
+    c->pendingEvents.push_back({stage, {a, b}});
+}
+
+void stageEnd(Ctx* c, int stage, int launches)
+{
+    c->kernelLaunches += launches;
+    c->stageLaunches[stage] += launches;
+    if (!c->profiling) return;
+    cudaEventRecord(c->pendingEvents.back().second.second, c->stream);
+}
+
+static void drainEvents(Ctx* c)
+{
+    for (auto& pe : c->pendingEvents) {
+        float ms = 0.f;
+        cudaEventSynchronize(pe.second.second);
+        if (cudaEventElapsedTime(&ms, pe.second.first, pe.second.second) == cudaSuccess) c->stageMs[pe.first] += ms;
+        c->eventPool.push_back(pe.second.first); c->eventPool.push_back(pe.second.second);
+    }
+    c->pendingEvents.clear();
+}
+
+int ensureScratch(Ctx* c, size_t bytes)
+{
+    if (bytes <= c->scratchBytes) return ORBX_OK;
+    if (c->dScratch) { cudaStreamSynchronize(c->stream); cudaFree(c->dScratch); c->dScratch = nullptr; c->scratchBytes = 0; }
+    bytes = (bytes + (1u << 20)) & ~(size_t)((1u << 20) - 1);
+    ORBX_CUDA(c, cudaMalloc(&c->dScratch, bytes));
+    c->scratchBytes = bytes;
+    return ORBX_OK;
+}
+
+// cvRound(float): round half to even under the default rounding mode
+static inline int cvRoundF(float v) { return (int)lrintf(v); }
+static inline int cvRoundD(double v) { return (int)lrint(v); }
+
+// Constructor tables -- same formulas, same float/double mix as src/ORBextractor.cc:471-579.
+static void initTables(Ctx* c)
+{
+    const int L = c->nlevels;
+    c->scale[0] = 1.0f; c->sigma2[0] = 1.0f;
+    for (int i = 1; i < L; ++i) { c->scale[i] = c->scale[i - 1] * c->scaleFactor; c->sigma2[i] = c->scale[i] * c->scale[i]; }
+    for (int i = 0; i < L; ++i) { c->invScale[i] = 1.0f / c->scale[i]; c->invSigma2[i] = 1.0f / c->sigma2[i]; }
+    const float factor = 1.0f / c->scaleFactor;
+    float nd = (float)c->nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)L));
+    int sum = 0;
+    for (int l = 0; l < L - 1; ++l) { c->nfeatLevel[l] = cvRoundF(nd); sum += c->nfeatLevel[l]; nd *= factor; }
+    c->nfeatLevel[L - 1] = c->nfeatures - sum > 0 ? c->nfeatures - sum : 0;
+    int v, v0;
+    const int vmax = (int)floor(kHalfPatch * sqrt(2.f) / 2 + 1), vmin = (int)ceil(kHalfPatch * sqrt(2.f) / 2);
+    const double hp2 = kHalfPatch * kHalfPatch;
+    for (v = 0; v <= vmax; ++v) c->umax[v] = cvRoundD(sqrt(hp2 - v * v));
+    for (v = kHalfPatch, v0 = 0; v >= vmin; --v) { while (c->umax[v0] == c->umax[v0 + 1]) ++v0; c->umax[v] = v0; ++v0; }
+}
+
+static void levelSize(const Ctx* c, int l, int w0, int h0, int* w, int* h)
+{   // src/ORBextractor.cc:1669-1672
+    *w = cvRoundF((float)w0 * c->invScale[l]);
+    *h = cvRoundF((float)h0 * c->invScale[l]);
+}
+
+// cv::resize INTER_LINEAR coefficient tables (OpenCV resize.cpp), computed once per geometry on the host
+static void buildTaps(int dn, int sn, bool clampF, std::vector<ResizeTap>& t)
+{
+    t.resize(dn);
+    const double scale = 1.0 / ((double)dn / (double)sn);
+    for (int d = 0; d < dn; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)floorf(f);
+        f -= (float)s;
+        if (clampF) { if (s < 0) { f = 0; s = 0; } if (s >= sn - 1) { f = 0; s = sn - 1; } }
+        else { if (s < 0) s = 0; if (s > sn - 1) s = sn - 1; } // rows: index clipped, weights kept (downscale: s>=0 always)
+        const int a = cvRoundF((1.f - f) * 2048.f), b = cvRoundF(f * 2048.f);
+        t[d].s = (uint16_t)s; t[d].c0 = (int16_t)a; t[d].c1 = (int16_t)b; t[d].pad = 0;
+    }
+}
+
+static void freeGeometry(Ctx* c)
+{
+    for (int l = 0; l < kMaxLevels; ++l) {
+        if (c->dTapX[l]) cudaFree(c->dTapX[l]);
+        if (c->dTapY[l]) cudaFree(c->dTapY[l]);
+        c->dTapX[l] = c->dTapY[l] = nullptr;
+    }
+}
+
+// (Re)compute everything that depends on the image size.  Arenas are sized for maxW x maxH x maxBatch once.
+static int configure(Ctx* c, int w, int h)
+{
+    if (w == c->curW && h == c->curH) return ORBX_OK;
+    GeomSet& g = c->geom;
+    memset(&g, 0, sizeof(g));
+    g.nlevels = c->nlevels; g.iniTh = c->iniTh; g.minTh = c->minTh;
+    for (int i = 0; i < 16; ++i) g.umax[i] = c->umax[i];
+    size_t planeOff = 0, blurOff = 0;
+    int cellBase = 0, candBase = 0, outBase = 0, tileBase = 0;
+    for (int l = 0; l < c->nlevels; ++l) {
+        LevelGeom& q = g.lv[l];
+        levelSize(c, l, w, h, &q.w, &q.h);
+        if (q.w < 1 || q.h < 1 || q.w > 65535 || q.h > 32767) return ORBX_E_UNSUPPORTED;
+        q.pitch = (q.w + 15) & ~15;
+        q.scale = c->scale[l];
+        q.patchSize = (float)(int)((float)kPatch * c->scale[l]);
+        q.quota = c->nfeatLevel[l];
+        const int minB = kWinOff, maxBX = q.w - kEdge + 3, maxBY = q.h - kEdge + 3;
+        const float width = (float)(maxBX - minB), height = (float)(maxBY - minB);
+        const int nCols = (int)(width / 30.f), nRows = (int)(height / 30.f); // :1076-1077
+        if (nCols >= 1 && nRows >= 1) {
+            q.nCols = nCols; q.nRows = nRows;
+            q.wCell = (int)ceilf(width / nCols); q.hCell = (int)ceilf(height / nRows); // :1080-1081
+            const int nIni = (int)roundf((float)(maxBX - minB) / (float)(maxBY - minB)); // :703
+            if (nIni < 1 || nIni > 8) return ORBX_E_UNSUPPORTED; // nIni == 0: the reference divides by zero
+            q.nIni = nIni; q.hX = (float)(maxBX - minB) / (float)nIni;                   // :706
+            if (q.wCell >= 64 || q.hCell >= 64) return ORBX_E_UNSUPPORTED;
+        } else { q.nCols = q.nRows = 0; q.wCell = q.hCell = 1; q.nIni = 1; q.hX = 1.f; } // reference: UB; here: no keypoints
+        q.cellBase = cellBase; cellBase += q.nCols * q.nRows;
+        // NMS survivors are never 8-adjacent: at most ceil(w/2)*ceil(h/2) per cell
+        q.candCap = q.nCols * q.nRows * ((q.wCell + 1) / 2) * ((q.hCell + 1) / 2);
+        q.candBase = candBase; candBase += (q.candCap + 3) & ~3;
+        q.outCap = q.quota + 4 * q.nIni + 4;
+        q.outBase = outBase; outBase += q.outCap;
+        q.planeOff = planeOff; planeOff += (size_t)q.pitch * q.h * c->maxBatch; planeOff = (planeOff + 255) & ~(size_t)255;
+        q.blurOff = blurOff; blurOff += (size_t)q.pitch * q.h * c->maxBatch; blurOff = (blurOff + 255) & ~(size_t)255;
+        q.tilesX = (q.w + 63) / 64; q.tilesY = (q.h + 31) / 32;
+        q.tileBase = tileBase; tileBase += q.tilesX * q.tilesY;
+    }
+    g.cellsPerFrame = cellBase; g.candPerFrame = candBase; g.selPerFrame = outBase; g.blurTilesPerFrame = tileBase;
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    // arenas only ever grow (sized for max_w x max_h x max_batch at creation)
+    if (planeOff > c->pyrBytes) { if (c->dPyr) cudaFree(c->dPyr); c->dPyr = nullptr; ORBX_CUDA(c, cudaMalloc(&c->dPyr, planeOff)); c->pyrBytes = planeOff; }
+    if (blurOff > c->blurBytes) { if (c->dBlur) cudaFree(c->dBlur); c->dBlur = nullptr; ORBX_CUDA(c, cudaMalloc(&c->dBlur, blurOff)); c->blurBytes = blurOff; }
+    const size_t candNeed = (size_t)candBase * c->maxBatch;
+    if (candNeed > c->candRecs) { if (c->dCand) cudaFree(c->dCand); c->dCand = nullptr; ORBX_CUDA(c, cudaMalloc(&c->dCand, candNeed * sizeof(unsigned long long))); c->candRecs = candNeed; }
+    const size_t selNeed = (size_t)outBase * c->maxBatch;
+    if (selNeed > c->selRecs) { if (c->dSel) cudaFree(c->dSel); c->dSel = nullptr; ORBX_CUDA(c, cudaMalloc(&c->dSel, selNeed * sizeof(orbx_keypoint))); c->selRecs = selNeed; }
+    freeGeometry(c);
+    for (int l = 1; l < c->nlevels; ++l) {
+        std::vector<ResizeTap> tx, ty;
+        buildTaps(g.lv[l].w, g.lv[l - 1].w, true, tx);
+        buildTaps(g.lv[l].h, g.lv[l - 1].h, false, ty);
+        ORBX_CUDA(c, cudaMalloc(&c->dTapX[l], sizeof(ResizeTap) * tx.size()));
+        ORBX_CUDA(c, cudaMalloc(&c->dTapY[l], sizeof(ResizeTap) * ty.size()));
+        ORBX_CUDA(c, cudaMemcpy(c->dTapX[l], tx.data(), sizeof(ResizeTap) * tx.size(), cudaMemcpyHostToDevice));
+        ORBX_CUDA(c, cudaMemcpy(c->dTapY[l], ty.data(), sizeof(ResizeTap) * ty.size(), cudaMemcpyHostToDevice));
+    }
+    ORBX_CUDA(c, cudaMemcpy(c->dGeom, &g, sizeof(g), cudaMemcpyHostToDevice));
+    c->curW = w; c->curH = h;
+    return ORBX_OK;
+}
+
+} // namespace orbx
+using namespace orbx;
+
+extern "C" {
+
+const char* orbx_strerror(int s)
+{
+    switch (s) {
+    case ORBX_OK: return "ok";
+    case ORBX_E_INVALID: return "invalid argument";
+    case ORBX_E_CUDA: return "CUDA error";
+    case ORBX_E_NOMEM: return "out of memory";
+    case ORBX_E_CAPACITY: return "capacity exceeded";
+    case ORBX_E_UNSUPPORTED: return "unsupported geometry";
+    default: return "unknown status";
+    }
+}
+
+const char* orbx_last_cuda_error(const orbx_ctx* ctx) { return ctx ? ctx->c.lastCudaError.c_str() : ""; }
+
+int orbx_create(orbx_ctx** out, int device, int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th,
+                int max_w, int max_h, int max_batch)
+{
+    if (!out) return ORBX_E_INVALID;
+    *out = nullptr;
+    if (nfeatures < 0 || nlevels < 1 || nlevels > kMaxLevels || !(scale_factor > 1.0f) || ini_th < 1 || min_th < 1 ||
+        min_th > ini_th || ini_th > 254 || max_w < 1 || max_h < 1 || max_batch < 1)
+        return ORBX_E_INVALID;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return ORBX_E_CUDA; // no CPU fallback
+    orbx_ctx* h = new (std::nothrow) orbx_ctx();
+    if (!h) return ORBX_E_NOMEM;
+    Ctx* c = &h->c;
+    c->device = device; c->nfeatures = nfeatures; c->scaleFactor = scale_factor; c->nlevels = nlevels;
+    c->iniTh = ini_th; c->minTh = min_th; c->maxW = max_w; c->maxH = max_h; c->maxBatch = max_batch;
+    initTables(c);
+    int rc = ORBX_OK;
+    do {
+        if (cudaSetDevice(device) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
+        if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
+        if (cudaMalloc(&c->dGeom, sizeof(GeomSet)) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
+        if (cudaMalloc(&c->dCandCount, sizeof(int) * (size_t)max_batch * kMaxLevels) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
+        if (cudaMalloc(&c->dSelCount, sizeof(int) * (size_t)max_batch * kMaxLevels) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
+        if (cudaMalloc(&c->dErr, sizeof(int)) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
+        cudaMemset(c->dErr, 0, sizeof(int));
+        rc = configure(c, max_w, max_h);
+    } while (0);
+    if (rc != ORBX_OK) { orbx_destroy(h); return rc; }
+    *out = h;
+    return ORBX_OK;
+}
+
+void orbx_destroy(orbx_ctx* h)
+{
+    if (!h) return;
+    Ctx* c = &h->c;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    drainEvents(c);
+    for (cudaEvent_t e : c->eventPool) cudaEventDestroy(e);
+    freeGeometry(c);
+    void* ptrs[] = {c->dGeom, c->dPyr, c->dBlur, c->dCand, c->dCandCount, c->dSel, c->dSelCount, c->dErr,
+                    c->dOutKp, c->dOutDesc, c->dOutN, c->dIn, c->dScratch};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    if (c->hPinned) cudaFreeHost(c->hPinned);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete h;
+}
+
+int orbx_get_levels(const orbx_ctx* h) { return h ? h->c.nlevels : 0; }
+float orbx_get_scale_factor(const orbx_ctx* h) { return h ? h->c.scaleFactor : 0.f; }
+
+int orbx_get_tables(const orbx_ctx* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2, int* fpl)
+{
+    if (!h) return ORBX_E_INVALID;
+    const Ctx* c = &h->c;
+    for (int i = 0; i < c->nlevels; ++i) {
+        if (scale) scale[i] = c->scale[i];
+        if (inv_scale) inv_scale[i] = c->invScale[i];
+        if (sigma2) sigma2[i] = c->sigma2[i];
+        if (inv_sigma2) inv_sigma2[i] = c->invSigma2[i];
+        if (fpl) fpl[i] = c->nfeatLevel[i];
+    }
+    return ORBX_OK;
+}
+
+int orbx_max_keypoints(const orbx_ctx* h)
+{
+    if (!h) return 0;
+    int s = 0;
+    for (int l = 0; l < h->c.nlevels; ++l) s += h->c.nfeatLevel[l] + 36; // quota + 4*nIni(<=8) + 4 per level
+    return (s + 31) & ~31;
+}
+
+int orbx_level_size(const orbx_ctx* h, int level, int w0, int h0, int* w, int* hh)
+{
+    if (!h || level < 0 || level >= h->c.nlevels || !w || !hh) return ORBX_E_INVALID;
+    levelSize(&h->c, level, w0, h0, w, hh);
+    return ORBX_OK;
+}
+
+int orbx_sync(orbx_ctx* h)
+{
+    if (!h) return ORBX_E_INVALID;
+    Ctx* c = &h->c;
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    drainEvents(c);
+    return ORBX_OK;
+}
+
+void* orbx_stream(orbx_ctx* h) { return h ? (void*)h->c.stream : nullptr; }
+int orbx_set_profiling(orbx_ctx* h, int on) { if (!h) return ORBX_E_INVALID; orbx_sync(h); h->c.profiling = on != 0; return ORBX_OK; }
+int orbx_stage_count(void) { return ST_COUNT; }
+const char* orbx_stage_name(int i) { return (i >= 0 && i < ST_COUNT) ? kStageNames[i] : ""; }
+
+int orbx_stage_stats(orbx_ctx* h, int i, double* total_ms, long long* launches)
+{
+    if (!h || i < 0 || i >= ST_COUNT) return ORBX_E_INVALID;
+    int rc = orbx_sync(h);
+    if (rc) return rc;
+    if (total_ms) *total_ms = h->c.stageMs[i];
+    if (launches) *launches = h->c.stageLaunches[i];
+    return ORBX_OK;
+}
+
+int orbx_reset_stats(orbx_ctx* h)
+{
+    if (!h) return ORBX_E_INVALID;
+    int rc = orbx_sync(h);
+    if (rc) return rc;
+    for (int i = 0; i < ST_COUNT; ++i) { h->c.stageMs[i] = 0; h->c.stageLaunches[i] = 0; }
+    return ORBX_OK;
+}
+
+long long orbx_kernel_launches(const orbx_ctx* h) { return h ? h->c.kernelLaunches : 0; }
+
+} // extern "C"
+
+namespace orbx {
+
+static int checkDeviceError(Ctx* c)
+{
+    int e = 0;
+    ORBX_CUDA(c, cudaMemcpyAsync(&e, c->dErr, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (e != 0) {
+        cudaMemsetAsync(c->dErr, 0, sizeof(int), c->stream);
+        c->lastCudaError = "device-side error flag " + std::to_string(e);
+        return e == 5 ? ORBX_E_CAPACITY : ORBX_E_CUDA;
+    }
+    return ORBX_OK;
+}
+
+static int ensureOutStaging(Ctx* c, int cap)
+{
+    if (cap <= c->outCap && c->dOutKp) return ORBX_OK;
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->dOutKp) cudaFree(c->dOutKp);
+    if (c->dOutDesc) cudaFree(c->dOutDesc);
+    if (c->dOutN) cudaFree(c->dOutN);
+    c->dOutKp = nullptr; c->dOutDesc = nullptr; c->dOutN = nullptr; c->outCap = 0;
+    ORBX_CUDA(c, cudaMalloc(&c->dOutKp, sizeof(orbx_keypoint) * (size_t)cap * c->maxBatch));
+    ORBX_CUDA(c, cudaMalloc(&c->dOutDesc, (size_t)32 * cap * c->maxBatch));
+    ORBX_CUDA(c, cudaMalloc(&c->dOutN, sizeof(int) * (size_t)c->maxBatch));
+    c->outCap = cap;
+    return ORBX_OK;
+}
+
+} // namespace orbx
+
+extern "C" {
+
+int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int hgt, size_t stride, size_t frame_stride,
+                       int flags, orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out)
+{
+    if (!h || batch < 0 || !n_out) return ORBX_E_INVALID;
+    Ctx* c = &h->c;
+    if (!imgs || w <= 0 || hgt <= 0 || batch == 0) { // empty image: outputs untouched (src/ORBextractor.cc:1547)
+        if (!(flags & ORBX_OUT_DEVICE)) for (int b = 0; b < batch; ++b) n_out[b] = 0;
+        return ORBX_OK;
+    }
+    if (!kps || !desc || cap < 1 || stride < (size_t)w) return ORBX_E_INVALID;
+    if (batch > 1 && frame_stride < stride * (size_t)hgt) return ORBX_E_INVALID;
+    if (batch > c->maxBatch) return ORBX_E_CAPACITY;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    int rc = configure(c, w, hgt);
+    if (rc) return rc;
+    const GeomSet& g = c->geom;
+
+    if (flags & ORBX_IN_DEVICE) {
+        c->lvl0 = imgs; c->lvl0Pitch = stride; c->lvl0FrameStride = frame_stride;
+    } else {
+        stageBegin(c, ST_H2D);
+        uint8_t* d0 = c->dPyr + g.lv[0].planeOff;
+        const size_t dp = (size_t)g.lv[0].pitch;
+        if (batch == 1 || frame_stride == stride * (size_t)hgt) {
+            ORBX_CUDA(c, cudaMemcpy2DAsync(d0, dp, imgs, stride, (size_t)w, (size_t)hgt * batch, cudaMemcpyHostToDevice, c->stream));
+        } else {
+            for (int b = 0; b < batch; ++b)
+                ORBX_CUDA(c, cudaMemcpy2DAsync(d0 + (size_t)b * dp * hgt, dp, imgs + (size_t)b * frame_stride, stride, (size_t)w,
+                                               (size_t)hgt, cudaMemcpyHostToDevice, c->stream));
+        }
+        stageEnd(c, ST_H2D, 0);
+        c->lvl0 = d0; c->lvl0Pitch = dp; c->lvl0FrameStride = dp * hgt;
+    }
+    c->lastBatch = batch;
+
+    orbx_keypoint* dK = kps; uint8_t* dD = desc; int* dN = n_out;
+    if (!(flags & ORBX_OUT_DEVICE)) {
+        rc = ensureOutStaging(c, cap);
+        if (rc) return rc;
+        dK = c->dOutKp; dD = c->dOutDesc; dN = c->dOutN;
+    }
+    if ((rc = launchPyramid(c, batch))) return rc;
+    if ((rc = launchFast(c, batch))) return rc;
+    if ((rc = launchOctree(c, batch))) return rc;
+    if ((rc = launchBlur(c, batch))) return rc;
+    if ((rc = launchDescribe(c, batch, dK, dD, (flags & ORBX_OUT_DEVICE) ? cap : c->outCap, dN))) return rc;
+    if (flags & ORBX_OUT_DEVICE) return ORBX_OK; // asynchronous; orbx_sync() reports device-side errors
+
+    stageBegin(c, ST_D2H);
+    const int sc = c->outCap; // staging capacity per frame (>= cap)
+    ORBX_CUDA(c, cudaMemcpyAsync(n_out, dN, sizeof(int) * (size_t)batch, cudaMemcpyDeviceToHost, c->stream));
+    if (sc == cap) {
+        ORBX_CUDA(c, cudaMemcpyAsync(kps, dK, sizeof(orbx_keypoint) * (size_t)cap * batch, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaMemcpyAsync(desc, dD, (size_t)32 * cap * batch, cudaMemcpyDeviceToHost, c->stream));
+    } else {
+        ORBX_CUDA(c, cudaMemcpy2DAsync(kps, sizeof(orbx_keypoint) * (size_t)cap, dK, sizeof(orbx_keypoint) * (size_t)sc,
+                                       sizeof(orbx_keypoint) * (size_t)cap, (size_t)batch, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaMemcpy2DAsync(desc, (size_t)32 * cap, dD, (size_t)32 * sc, (size_t)32 * cap, (size_t)batch,
+                                       cudaMemcpyDeviceToHost, c->stream));
+    }
+    stageEnd(c, ST_D2H, 0);
+    rc = checkDeviceError(c);
+    if (rc) return rc;
+    for (int b = 0; b < batch; ++b) if (n_out[b] > cap) return ORBX_E_CAPACITY;
+    return ORBX_OK;
+}
+
+int orbx_extract(orbx_ctx* h, const uint8_t* img, int w, int hgt, size_t stride, int flags, orbx_keypoint* kps,
+                 uint8_t* desc, int cap, int* n_out)
+{
+    return orbx_extract_batch(h, img, 1, w, hgt, stride, stride * (size_t)(hgt > 0 ? hgt : 0), flags, kps, desc, cap, n_out);
+}
+
+int orbx_pyramid_level(orbx_ctx* h, int frame, int level, int border, int flags, uint8_t* dst, size_t dst_stride, int* w, int* hh)
+{
+    if (!h || !dst) return ORBX_E_INVALID;
+    Ctx* c = &h->c;
+    if (level < 0 || level >= c->nlevels || frame < 0 || frame >= c->lastBatch || border < 0 || border > 64) return ORBX_E_INVALID;
+    const LevelGeom& q = c->geom.lv[level];
+    const int ow = q.w + 2 * border, oh = q.h + 2 * border;
+    if (dst_stride < (size_t)ow) return ORBX_E_INVALID;
+    if (w) *w = ow;
+    if (hh) *hh = oh;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    const uint8_t* src; size_t pitch;
+    if (level == 0) { src = c->lvl0 + (size_t)frame * c->lvl0FrameStride; pitch = c->lvl0Pitch; }
+    else { src = c->dPyr + q.planeOff + (size_t)frame * q.pitch * q.h; pitch = (size_t)q.pitch; }
+    if (border == 0) {
+        ORBX_CUDA(c, cudaMemcpy2DAsync(dst, dst_stride, src, pitch, (size_t)q.w, (size_t)q.h,
+                                       (flags & ORBX_OUT_DEVICE) ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+        return ORBX_OK;
+    }
+    if (flags & ORBX_OUT_DEVICE) {
+        int rc = launchBorderCopy(c, src, q.w, q.h, pitch, dst, dst_stride, border);
+        if (rc) return rc;
+        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+        return ORBX_OK;
+    }
+    int rc = ensureScratch(c, (size_t)ow * oh);
+    if (rc) return rc;
+    if ((rc = launchBorderCopy(c, src, q.w, q.h, pitch, (uint8_t*)c->dScratch, (size_t)ow, border))) return rc;
+    ORBX_CUDA(c, cudaMemcpy2DAsync(dst, dst_stride, c->dScratch, (size_t)ow, (size_t)ow, (size_t)oh, cudaMemcpyDeviceToHost, c->stream));
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return ORBX_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,111 @@
+// Internal declarations shared by the orbx CUDA translation units (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <string>
+#include <vector>
+#include "../../include/orbx.h"
+
+namespace orbx {
+
+constexpr int kEdge = 19;        // EDGE_THRESHOLD, src/ORBextractor.cc:81
+constexpr int kHalfPatch = 15;   // HALF_PATCH_SIZE :80
+constexpr int kPatch = 31;       // PATCH_SIZE :79
+constexpr int kWinOff = 16;      // minBorderX = EDGE_THRESHOLD-3 :1061
+constexpr int kMaxLevels = ORBX_MAX_LEVELS;
+
+enum Stage { ST_PYRAMID = 0, ST_FAST, ST_OCTREE, ST_BLUR, ST_DESCRIBE, ST_H2D, ST_D2H, ST_HAMMING, ST_MATCH, ST_STEREO, ST_BOW, ST_COUNT };
+
+// Per-level geometry, identical for every frame of a batch (device copy lives in __constant__).
+struct LevelGeom {
+    int w, h;            // level size (:1672)
+    int pitch;           // bytes per row of the internal plane (multiple of 16)
+    int nCols, nRows;    // FAST cell grid (:1076-1077); 0 when the window is narrower than a cell
+    int wCell, hCell;    // :1080-1081
+    int cellBase;        // first cell index of this level in the per-frame cell table
+    int candCap;         // candidate capacity per frame (can never overflow, see host)
+    int candBase;        // offset (in records) of this level inside a frame's candidate block
+    int quota;           // mnFeaturesPerLevel[level] :521-531
+    int nIni;            // quadtree roots :703
+    float hX;            // root width :706
+    int outCap;          // quota + slack: max nodes the quadtree can return
+    int outBase;         // offset of this level inside a frame's selected-keypoint block
+    float scale;         // mvScaleFactor[level]
+    float patchSize;     // (int)(31*scale) as float :1168
+    size_t planeOff;     // byte offset of this level's [B][h][pitch] block inside the pyramid arena
+    size_t blurOff;      // same for the blurred arena
+    int tileBase, tilesX, tilesY; // blur tile table
+};
+
+struct ResizeTap { uint16_t s; int16_t c0, c1; uint16_t pad; }; // source index + 11-bit fixed-point weights
+
+struct GeomSet {            // what kernels need, uploaded to constant memory on (re)configuration
+    LevelGeom lv[kMaxLevels];
+    int nlevels;
+    int cellsPerFrame;
+    int candPerFrame;
+    int selPerFrame;
+    int blurTilesPerFrame;
+    int iniTh, minTh;
+    int umax[16];
+};
+
+struct Ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int nfeatures = 0, nlevels = 0, iniTh = 0, minTh = 0;
+    float scaleFactor = 0;
+    float scale[kMaxLevels], invScale[kMaxLevels], sigma2[kMaxLevels], invSigma2[kMaxLevels];
+    int nfeatLevel[kMaxLevels];
+    int umax[16];
+    int maxW = 0, maxH = 0, maxBatch = 0;
+    // current geometry
+    int curW = 0, curH = 0;
+    GeomSet geom;
+    GeomSet* dGeom = nullptr;            // device copy (global memory; kernels read via __ldg / constant cache)
+    ResizeTap* dTapX[kMaxLevels] = {};   // per-level tables (level l = taps from level l-1)
+    ResizeTap* dTapY[kMaxLevels] = {};
+    // arenas
+    uint8_t* dPyr = nullptr; size_t pyrBytes = 0;      // levels (level 0 too unless used in place)
+    uint8_t* dBlur = nullptr; size_t blurBytes = 0;
+    unsigned long long* dCand = nullptr; size_t candRecs = 0; // [B][candPerFrame]
+    int* dCandCount = nullptr;           // [B][nlevels]
+    orbx_keypoint* dSel = nullptr; size_t selRecs = 0; // [B][selPerFrame] level-coord keypoints after the quadtree
+    int* dSelCount = nullptr;            // [B][nlevels]
+    int* dErr = nullptr;                 // device error flag
+    orbx_keypoint* dOutKp = nullptr; uint8_t* dOutDesc = nullptr; int* dOutN = nullptr; int outCap = 0; // staging for host outputs
+    uint8_t* hPinned = nullptr; size_t hPinnedBytes = 0;
+    uint8_t* dIn = nullptr; size_t dInBytes = 0;       // H2D staging for level 0 when input is on host
+    const uint8_t* lvl0 = nullptr; size_t lvl0Pitch = 0, lvl0FrameStride = 0; // where level 0 of the last batch lives
+    int lastBatch = 0;
+    // instrumentation
+    bool profiling = false;
+    double stageMs[ST_COUNT] = {};
+    long long stageLaunches[ST_COUNT] = {};
+    long long kernelLaunches = 0;
+    std::vector<std::pair<int, std::pair<cudaEvent_t, cudaEvent_t>>> pendingEvents;
+    std::vector<cudaEvent_t> eventPool;
+    std::string lastCudaError;
+    // matcher scratch
+    void* dScratch = nullptr; size_t scratchBytes = 0;
+};
+
+// RAII-free helpers -----------------------------------------------------------------------------
+int cudaFail(Ctx* c, cudaError_t e, const char* what);
+#define ORBX_CUDA(c, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return orbx::cudaFail((c), e_, #call); } while (0)
+void stageBegin(Ctx* c, int stage);
+void stageEnd(Ctx* c, int stage, int launches);
+int ensureScratch(Ctx* c, size_t bytes);
+
+// kernels (one launcher per stage; all asynchronous on c->stream) -------------------------------
+int launchPyramid(Ctx* c, int batch);
+int launchFast(Ctx* c, int batch);
+int launchOctree(Ctx* c, int batch);
+int launchBlur(Ctx* c, int batch);
+int launchDescribe(Ctx* c, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN);
+int launchBorderCopy(Ctx* c, const uint8_t* src, int w, int h, size_t pitch, uint8_t* dst, size_t dpitch, int border);
+
+} // namespace orbx
+
+struct orbx_ctx { orbx::Ctx c; };

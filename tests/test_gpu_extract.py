@@ -1,0 +1,130 @@
+"""GPU parity: CUDA path (through the C ABI) vs the CPU oracle and the committed cv2 goldens.
+Bit-exact on x, y, size, angle, response, octave and every descriptor byte."""
+import os
+import numpy as np
+import pytest
+import synth, oracle_lib as O
+from gpu_util import pkg, assert_kps_equal
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def P():
+    return pkg()
+
+
+def test_ctor_tables_match_oracle(P):
+    for nf, sc, nl in [(1000, 1.2, 8), (2000, 1.2, 8), (1200, 1.2, 8), (4000, 1.2, 8), (500, 1.5, 5), (300, 2.0, 4)]:
+        ex = P.ORBextractor(nf, sc, nl, 20, 7, max_w=64, max_h=64)
+        p = O.params(nf, sc, nl)
+        assert ex.GetLevels() == nl and np.float32(sc) == np.float32(ex.GetScaleFactor())
+        assert np.array_equal(ex.GetScaleFactors().view(np.uint32), np.array(p.scale[:nl], np.float32).view(np.uint32))
+        assert np.array_equal(ex.GetInverseScaleFactors().view(np.uint32), np.array(p.inv_scale[:nl], np.float32).view(np.uint32))
+        assert np.array_equal(ex.GetScaleSigmaSquares().view(np.uint32), np.array(p.sigma2[:nl], np.float32).view(np.uint32))
+        assert np.array_equal(ex.GetInverseScaleSigmaSquares().view(np.uint32), np.array(p.inv_sigma2[:nl], np.float32).view(np.uint32))
+        assert list(ex.features_per_level()) == list(p.nfeat_level[:nl])
+        ex.close()
+
+
+def test_pyramid_levels_bit_exact(P):
+    img = synth.frame(7, 640, 480)
+    ex = P.ORBextractor(1000, 1.2, 8, 20, 7, max_w=640, max_h=480)
+    ex(img)
+    p = O.params(1000)
+    _, _, pyr = O.extract(p, img, want_pyr=True)
+    o = 0
+    for l, (w, h) in enumerate(O.level_sizes(p, 640, 480)):
+        want = pyr[o:o + w * h].reshape(h, w)
+        o += w * h
+        assert np.array_equal(ex.pyramid_level(l), want), l
+        assert np.array_equal(ex.mvImagePyramid[l], want)
+        assert np.array_equal(ex.pyramid_level(l, border=19), O.border(want, 19)), ("border", l)
+
+
+CASES = ["tum", "euroc", "kitti", "grad", "noise", "black", "small"]
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_extract_matches_golden_and_oracle(P, name):
+    g = np.load(os.path.join(G, f"extract_{name}.npz"))
+    w, h, nf = int(g["w"]), int(g["h"]), int(g["nfeatures"])
+    img = synth.frame(int(g["seed"]), w, h, str(g["kind"]))
+    ex = P.ORBextractor(nf, 1.2, 8, 20, 7, max_w=w, max_h=h)
+    kps, desc = ex(img)
+    okps, odesc = O.extract(O.params(nf), img)
+    assert_kps_equal(kps, okps, desc, odesc, name)
+    kp = g["kp"]
+    assert len(kps) == len(kp)
+    for i, f in enumerate(("x", "y", "size", "angle", "response")):
+        assert np.array_equal(kps[f].view(np.uint32), kp[:, i].view(np.uint32)), f
+    assert np.array_equal(desc, g["desc"])
+
+
+def test_empty_image_leaves_outputs(P):
+    ex = P.ORBextractor(1000, 1.2, 8, 20, 7, max_w=64, max_h=64)
+    kps, desc = ex(np.zeros((0, 0), np.uint8))
+    assert len(kps) == 0 and desc.shape == (0, 32)
+
+
+def test_strided_input_and_size_change(P):
+    ex = P.ORBextractor(800, 1.2, 8, 20, 7, max_w=800, max_h=600)
+    big = synth.frame(9, 800, 600)
+    for (x0, y0, w, h) in [(0, 0, 800, 600), (13, 7, 500, 333), (100, 50, 641, 479)]:
+        view = big[y0:y0 + h, x0:x0 + w]          # non-contiguous rows
+        kps, desc = ex(view)
+        okps, odesc = O.extract(O.params(800), np.ascontiguousarray(view))
+        assert_kps_equal(kps, okps, desc, odesc, (w, h))
+
+
+def test_batch_equals_single(P):
+    B = 6
+    imgs = np.stack([synth.frame(100 + i, 640, 480, "texture" if i % 3 else "noise") for i in range(B)])
+    ex = P.ORBextractor(1000, 1.2, 8, 20, 7, max_w=640, max_h=480, max_batch=B)
+    res = ex.extract_batch(imgs)
+    p = O.params(1000)
+    for b in range(B):
+        okps, odesc = O.extract(p, imgs[b])
+        assert_kps_equal(res[b][0], okps, res[b][1], odesc, b)
+
+
+def test_configs_geometry_1080p(P):
+    img = synth.frame(5, 1920, 1080)
+    ex = P.ORBextractor(4000, 1.2, 8, 20, 7, max_w=1920, max_h=1080)
+    kps, desc = ex(img)
+    okps, odesc = O.extract(O.params(4000), img)
+    assert_kps_equal(kps, okps, desc, odesc, "1080p")
+
+
+def test_idempotent_and_deterministic(P):
+    img = synth.frame(3, 752, 480)
+    ex = P.ORBextractor(1200, 1.2, 8, 20, 7, max_w=752, max_h=480)
+    a = ex(img)
+    for _ in range(3):
+        b = ex(img)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+def test_device_sincosf_and_atan2_exact(P):
+    """Device glibc-sincosf port vs the oracle restatement on 64 Mi consecutive floats per band, and
+    fastAtan2 vs the oracle on random integer moments."""
+    import ctypes
+    L = P.lib()
+    n = 1 << 24
+    lib = O.lib()
+    for first in (0x00000000, 0x3A000000, 0x3F000000, 0x3F490000, 0x40000000, 0x40400000, 0x40C00000 - n + 0x100000):
+        s = np.empty(n, np.float32); c = np.empty(n, np.float32)
+        assert L.orbx_test_sincosf(first, n, s.ctypes.data, c.ctypes.data) == 0
+        x = (np.arange(n, dtype=np.uint32) + np.uint32(first)).view(np.float32)
+        idx = np.random.default_rng(first).integers(0, n, 20000)
+        for i in idx[:4000]:
+            assert np.float32(lib.orc_sinf(float(x[i]))).view(np.uint32) == s[i].view(np.uint32), (first, i)
+            assert np.float32(lib.orc_cosf(float(x[i]))).view(np.uint32) == c[i].view(np.uint32), (first, i)
+    rng = np.random.default_rng(1)
+    yx = rng.integers(-3000000, 3000000, size=(200000, 2)).astype(np.float32)
+    yx[:4] = [[0, 0], [0, 5], [5, 0], [-5, -5]]
+    out = np.empty(len(yx), np.float32)
+    assert L.orbx_test_fast_atan2(yx.ctypes.data, len(yx), out.ctypes.data) == 0
+    want = np.array([lib.orc_fast_atan2(float(a), float(b)) for a, b in yx[:50000]], np.float32)
+    assert np.array_equal(out[:50000].view(np.uint32), want.view(np.uint32))
