@@ -178,3 +178,45 @@ extern "C" int orbx_hamming_best2(orbx_ctx* h, const uint8_t* q_desc, int nq, co
     }
     return ORBX_OK;
 }
+
+// ---- POPC-pipe peak micro-benchmark (roofline denominator for K6; MEASURED_PEAKS.json has no integer peak) ----
+namespace orbx {
+__global__ void __launch_bounds__(256) popcPeakKernel(uint32_t* out, int iters)
+{
+    uint32_t a[8], s[8];
+    #pragma unroll
+    for (int j = 0; j < 8; ++j) { a[j] = (threadIdx.x + 1u) * 2654435761u + j * 0x9E3779B9u + blockIdx.x; s[j] = 0; }
+    for (int i = 0; i < iters; ++i) {
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) { s[j] += __popc(a[j]); a[j] ^= s[j]; } // 8 independent POPC chains per thread
+    }
+    uint32_t r = 0;
+    #pragma unroll
+    for (int j = 0; j < 8; ++j) r += s[j];
+    if (r == 0xffffffffu) out[0] = r; // never true in practice; keeps the loop alive
+}
+}
+
+extern "C" int orbx_test_popc_peak(int device, int iters, double* popc_per_s, double* ms_out)
+{
+    if (cudaSetDevice(device) != cudaSuccess) return ORBX_E_CUDA;
+    uint32_t* d = nullptr;
+    if (cudaMalloc(&d, 64) != cudaSuccess) return ORBX_E_CUDA;
+    cudaDeviceProp p; cudaGetDeviceProperties(&p, device);
+    const int blocks = p.multiProcessorCount * 8;
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    orbx::popcPeakKernel<<<blocks, 256>>>(d, iters / 8); // warm-up
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; ++rep) {
+        cudaEventRecord(e0);
+        orbx::popcPeakKernel<<<blocks, 256>>>(d, iters);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(d); return ORBX_E_CUDA; }
+        float ms; cudaEventElapsedTime(&ms, e0, e1);
+        if (ms < best) best = ms;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    if (popc_per_s) *popc_per_s = (double)blocks * 256.0 * 8.0 * (double)iters / (best * 1e-3);
+    if (ms_out) *ms_out = best;
+    return ORBX_OK;
+}
