@@ -100,6 +100,84 @@ int orbx_hamming_best2(orbx_ctx* ctx, const uint8_t* q_desc, int nq, const uint8
                        int nseg, const uint8_t* t_valid, int flags,
                        int32_t* best_idx, int32_t* best_dist, int32_t* second_dist);
 
+/* ---- DBoW2 vocabulary + transform (feeds SearchByBoW).  Replaces TemplatedVocabulary::transform,
+ *      Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1145-1221,1255-1306 (FORB::distance, FORB.cpp:81-101). ----
+ * The tree is passed flattened: node 0 = root; children of node i are child[child_off[i] .. child_off[i+1]) in file
+ * order; a node without children is a leaf (word).  Vocabulary TRAINING (create/k-means) is out of scope. */
+typedef struct orbx_vocab orbx_vocab;
+int orbx_vocab_create(orbx_ctx* ctx, int k, int L, int nnodes, const int32_t* child_off, const int32_t* child,
+                      const uint8_t* node_desc, const int32_t* word_id, const float* weight, orbx_vocab** out);
+/* ORBvoc text format (TemplatedVocabulary::loadFromTextFile, TemplatedVocabulary.h:1385-1487) */
+int orbx_vocab_load_text(orbx_ctx* ctx, const char* path, orbx_vocab** out);
+void orbx_vocab_destroy(orbx_vocab* v);
+int orbx_vocab_info(const orbx_vocab* v, int* k, int* L, int* nnodes, int* nwords);
+/* Per feature: leaf word id, leaf weight, and the node id at level L - levelsup (0 = root when levelsup >= L). */
+int orbx_bow_transform(orbx_ctx* ctx, const orbx_vocab* v, const uint8_t* desc, int n, int levelsup, int flags,
+                       int32_t* word, float* weight, int32_t* node);
+/* FeatureVector (FeatureVector.cpp:37-54) as CSR from the per-feature node ids (features with weight <= 0 dropped,
+ * TemplatedVocabulary.h:1184): ascending node id, ascending feature index inside a node.  Host index glue.
+ * node_id[nn], node_off[nn+1], feat[<= n]; returns nn through *nnodes. */
+int orbx_feature_vector(const int32_t* node, const float* weight, int n, int32_t* node_id, int32_t* node_off,
+                        int32_t* feat, int* nnodes);
+
+/* ---- greedy BoW matchers.  Replace ORBmatcher::SearchByBoW(KeyFrame*,Frame&,..) src/ORBmatcher.cc:255-419,
+ *      SearchByBoW(KeyFrame*,KeyFrame*,..) :760-903 and SearchForTriangulation :915-1127 (CheckDistEpipolarLine
+ *      :213-240, ComputeThreeMaxima :2076-2118), bit-equal including the order-dependent masking. ---- */
+enum { ORBX_BOW_KF_FRAME = 0, ORBX_BOW_KF_KF = 1, ORBX_BOW_TRIANGULATE = 2 };
+typedef struct {          /* one side of a match job; all pointers host or device per `flags` */
+    const uint8_t* desc;          /* n x 32 */
+    const orbx_keypoint* keys;    /* mvKeysUn: angle (all modes); x, y, octave (triangulation) */
+    const uint8_t* has_point;     /* per feature: holds a good MapPoint (NULL = none do) */
+    const float* uright;          /* mvuRight, or NULL for monocular */
+    int n;
+    int nnodes;                   /* FeatureVector CSR (orbx_feature_vector layout) */
+    const int32_t* node_id; const int32_t* node_off; const int32_t* feat;
+} orbx_bow_side;
+typedef struct {          /* SearchForTriangulation geometry, computed by the caller as at :920-929 */
+    float F12[9];                 /* row-major */
+    float ex, ey;                 /* epipole of KF1's centre in KF2 */
+    float scale2[ORBX_MAX_LEVELS], sigma2_2[ORBX_MAX_LEVELS]; /* pKF2->mvScaleFactors / mvLevelSigma2 */
+    int only_stereo;
+} orbx_triangulation;
+/* match: KF_FRAME -> indexed by side-2 (Frame) feature, value = side-1 (KeyFrame) feature whose MapPoint was
+ * assigned (vpMapPointMatches), -1 = none.  KF_KF / TRIANGULATE -> indexed by side-1 feature, value = side-2
+ * feature (vpMatches12 / vMatches12), -1 = none.  Node lists are always HOST arrays. */
+int orbx_match_bow(orbx_ctx* ctx, int mode, const orbx_bow_side* s1, const orbx_bow_side* s2,
+                   const orbx_triangulation* tri, float nnratio, int check_orientation, int flags,
+                   int32_t* match, int* nmatches);
+
+/* ---- window (projection) matchers.  Replace the four ORBmatcher::SearchByProjection overloads
+ *      (src/ORBmatcher.cc:78-191, :431-560, :1741-1910, :1922-2065) after the caller's projection step,
+ *      Frame::GetFeaturesInArea src/Frame.cc:590-671 / KeyFrame::GetFeaturesInArea src/KeyFrame.cc:794-838 and
+ *      Frame::AssignFeaturesToGrid src/Frame.cc:398-422,682-698. ---- */
+typedef struct {
+    float u, v;            /* projected pixel */
+    float radius;          /* search half-window (already multiplied by th and the level scale) */
+    float ur;              /* projected right coordinate (used when the frame has uright > 0) */
+    float angle;           /* keypoint angle of the source observation (rotation histogram) */
+    int32_t min_level, max_level; /* octave filter, max_level < 0 = unbounded (GetFeaturesInArea semantics) */
+    int32_t reserved;
+    uint8_t desc[32];
+} orbx_proj_query;
+typedef struct { float min_x, min_y, inv_w, inv_h; int cols, rows; } orbx_grid; /* mnMinX.. FRAME_GRID_COLS/ROWS */
+enum { ORBX_PROJ_RATIO_SAME_LEVEL = 1,  /* keep best/second-best + the bestLevel==bestLevel2 ratio rule (:177-186) */
+       ORBX_PROJ_CHECK_URIGHT = 2 };    /* |ur - uright[i]| > radius rejects (:141-151, :1846-1852) */
+int orbx_assign_grid(orbx_ctx* ctx, const orbx_keypoint* keys, int n, const orbx_grid* g, int flags,
+                     int32_t* cell_off /* cols*rows+1 */, int32_t* cell_idx /* n */);
+/* Queries are processed in order; a keypoint taken by an earlier query (or with occupied[i] != 0 on entry) is
+ * skipped by later ones, exactly like the reference's writes to mvpMapPoints / vpMatched.
+ * assign[i] = query index matched to keypoint i, or -1. */
+int orbx_search_by_projection(orbx_ctx* ctx, const orbx_proj_query* q, int nq, const orbx_keypoint* keys,
+                              const uint8_t* desc, const float* uright, int n, const orbx_grid* g,
+                              const uint8_t* occupied, int mode_flags, int th_dist, float nnratio,
+                              int check_orientation, int flags, int32_t* assign, int* nmatches);
+
+/* ---- stereo.  Replaces Frame::ComputeStereoMatches, src/Frame.cc:831-1128.  left/right are the two extractor
+ *      contexts whose LAST orbx_extract call produced the keypoints (their pyramids are read on the device). ---- */
+int orbx_stereo_match(orbx_ctx* left, orbx_ctx* right, int frame, const orbx_keypoint* kps_l, const uint8_t* desc_l,
+                      int n_l, const orbx_keypoint* kps_r, const uint8_t* desc_r, int n_r, float bf, float b,
+                      int flags, float* u_right, float* depth, int* n_matched);
+
 #ifdef __cplusplus
 }
 #endif

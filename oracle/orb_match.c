@@ -1,10 +1,21 @@
 /* TEST INFRASTRUCTURE ONLY (oracle/) -- see orb_oracle.h.
- * CPU restatement of the Hamming core of ORBmatcher (src/ORBmatcher.cc). */
+ * CPU restatement of the Hamming side of the reference: ORBmatcher (src/ORBmatcher.cc),
+ * Frame::ComputeStereoMatches / GetFeaturesInArea / AssignFeaturesToGrid (src/Frame.cc) and the
+ * DBoW2 tree descent (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h, FORB.cpp, FeatureVector.cpp).
+ * SLAM objects (MapPoint*, KeyFrame*, cv::Mat) are flattened to plain arrays; every loop keeps the
+ * reference's iteration order, tie rules and float/double mix.  Compile with -ffp-contract=off. */
 #include "orb_oracle.h"
+#include <limits.h>
+#include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
-/* DescriptorDistance: src/ORBmatcher.cc:2123-2143 (8 x 32-bit bit-hack popcount) */
+#define TH_HIGH 100     /* src/ORBmatcher.cc:56 */
+#define TH_LOW 50       /* :57 */
+#define HISTO_LENGTH 30 /* :58 */
+
+/* DescriptorDistance: src/ORBmatcher.cc:2123-2143 (8 x 32-bit bit-hack popcount); FORB::distance
+ * (Thirdparty/DBoW2/DBoW2/FORB.cpp:81-101) is the same arithmetic. */
 int orc_descriptor_distance(const uint8_t* a, const uint8_t* b)
 {
     int dist = 0;
@@ -17,4 +28,501 @@ int orc_descriptor_distance(const uint8_t* a, const uint8_t* b)
         dist += (int)((((v + (v >> 4)) & 0xF0F0F0Fu) * 0x1010101u) >> 24);
     }
     return dist;
+}
+
+/* ComputeThreeMaxima: src/ORBmatcher.cc:2076-2118 (on bin counts) */
+void orc_three_maxima(const int* count, int L, int* ind1, int* ind2, int* ind3)
+{
+    int max1 = 0, max2 = 0, max3 = 0;
+    *ind1 = *ind2 = *ind3 = -1;
+    for (int i = 0; i < L; i++) {
+        const int s = count[i];
+        if (s > max1) { max3 = max2; max2 = max1; max1 = s; *ind3 = *ind2; *ind2 = *ind1; *ind1 = i; }
+        else if (s > max2) { max3 = max2; max2 = s; *ind3 = *ind2; *ind2 = i; }
+        else if (s > max3) { max3 = s; *ind3 = i; }
+    }
+    if ((float)max2 < 0.1f * (float)max1) { *ind2 = -1; *ind3 = -1; }
+    else if ((float)max3 < 0.1f * (float)max1) { *ind3 = -1; }
+}
+
+/* rotation bin: src/ORBmatcher.cc:364-371 (factor = HISTO_LENGTH/360.0f in this fork, :275) */
+static int rot_bin(float a1, float a2)
+{
+    const float factor = HISTO_LENGTH / 360.0f;
+    float rot = a1 - a2;
+    if (rot < 0.0) rot += 360.0f;
+    int bin = (int)roundf(rot * factor);
+    if (bin == HISTO_LENGTH) bin = 0;
+    return bin;
+}
+
+typedef struct { int* v; int n, cap; } ivec;
+static void ipush(ivec* a, int x)
+{
+    if (a->n == a->cap) { a->cap = a->cap ? 2 * a->cap : 64; a->v = (int*)realloc(a->v, sizeof(int) * (size_t)a->cap); }
+    a->v[a->n++] = x;
+}
+
+/* ---------------- DBoW2 ---------------- */
+/* TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup), TemplatedVocabulary.h:1255-1306 */
+void orc_bow_transform(const orc_vocab* V, const uint8_t* desc, int n, int levelsup, int32_t* word, float* weight, int32_t* node)
+{
+    const int nid_level = V->L - levelsup;
+    for (int f = 0; f < n; ++f) {
+        const uint8_t* d = desc + 32 * (size_t)f;
+        int nid = 0, final_id = 0, level = 0;
+        do {
+            ++level;
+            const int c0 = V->child_off[final_id], c1 = V->child_off[final_id + 1];
+            final_id = V->child[c0];
+            double best = (double)orc_descriptor_distance(d, V->desc + 32 * (size_t)final_id);
+            for (int c = c0 + 1; c < c1; ++c) {
+                const int id = V->child[c];
+                const double dd = (double)orc_descriptor_distance(d, V->desc + 32 * (size_t)id);
+                if (dd < best) { best = dd; final_id = id; }
+            }
+            if (level == nid_level) nid = final_id;
+        } while (V->child_off[final_id + 1] > V->child_off[final_id]); /* !isLeaf() */
+        word[f] = V->word_id[final_id];
+        weight[f] = V->weight[final_id];
+        node[f] = nid;
+    }
+}
+
+/* FeatureVector::addFeature (FeatureVector.cpp:37-54) for every feature with weight > 0
+ * (TemplatedVocabulary.h:1184-1189): std::map order = ascending node id, features ascending.
+ * Returns number of nodes; node_id[nn], node_off[nn+1], feat[n_kept]. */
+int orc_feature_vector(const int32_t* node, const float* weight, int n, int32_t* node_id, int32_t* node_off, int32_t* feat)
+{
+    int* order = (int*)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1));
+    int m = 0;
+    for (int i = 0; i < n; ++i) if (weight[i] > 0) order[m++] = i;
+    /* stable insertion by node id (n is small in tests; oracle clarity over speed) -> merge sort */
+    int* tmp = (int*)malloc(sizeof(int) * (size_t)(m > 0 ? m : 1));
+    for (int w = 1; w < m; w *= 2) {
+        for (int lo = 0; lo < m; lo += 2 * w) {
+            int mid = lo + w < m ? lo + w : m, hi = lo + 2 * w < m ? lo + 2 * w : m;
+            int a = lo, b = mid, k = lo;
+            while (a < mid && b < hi) tmp[k++] = node[order[b]] < node[order[a]] ? order[b++] : order[a++];
+            while (a < mid) tmp[k++] = order[a++];
+            while (b < hi) tmp[k++] = order[b++];
+        }
+        memcpy(order, tmp, sizeof(int) * (size_t)m);
+    }
+    int nn = 0;
+    for (int i = 0; i < m; ++i) {
+        if (i == 0 || node[order[i]] != node[order[i - 1]]) { node_id[nn] = node[order[i]]; node_off[nn] = i; ++nn; }
+        feat[i] = order[i];
+    }
+    node_off[nn] = m;
+    free(order); free(tmp);
+    return nn;
+}
+
+/* merge-join of two FeatureVectors (the while/lower_bound loops, e.g. src/ORBmatcher.cc:285-390) */
+#define FOR_SHARED_NODES(A, B, ia, ib) \
+    for (int ia = 0, ib = 0; ia < (A)->nnodes && ib < (B)->nnodes;) \
+        if ((A)->node_id[ia] < (B)->node_id[ib]) ++ia; else if ((A)->node_id[ia] > (B)->node_id[ib]) ++ib; else
+
+/* SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches): src/ORBmatcher.cc:255-419.
+ * kf->valid[i] = KF feature i has a good MapPoint.  match_f[F.N] receives the KF feature index whose
+ * MapPoint was assigned to F feature j (vpMapPointMatches[j]), or -1. */
+int orc_search_by_bow_kf_f(const orc_bowframe* kf, const orc_bowframe* F, float nnratio, int check_ori, int32_t* match_f)
+{
+    ivec hist[HISTO_LENGTH]; memset(hist, 0, sizeof(hist));
+    int nmatches = 0;
+    for (int j = 0; j < F->n; ++j) match_f[j] = -1;
+    FOR_SHARED_NODES(kf, F, ia, ib) {
+        for (int a = kf->node_off[ia]; a < kf->node_off[ia + 1]; ++a) {
+            const int iKF = kf->feat[a];
+            if (!kf->valid[iKF]) continue;                                     /* :307-313 */
+            const uint8_t* dKF = kf->desc + 32 * (size_t)iKF;
+            int best1 = 256, best2 = 256, bestIdx = -1;
+            for (int b = F->node_off[ib]; b < F->node_off[ib + 1]; ++b) {
+                const int iF = F->feat[b];
+                if (match_f[iF] >= 0) continue;                                /* :323 */
+                const int dist = orc_descriptor_distance(dKF, F->desc + 32 * (size_t)iF);
+                if (dist < best1) { best2 = best1; best1 = dist; bestIdx = iF; }
+                else if (dist < best2) best2 = dist;
+            }
+            if (best1 <= TH_LOW && (float)best1 < nnratio * (float)best2) {    /* :348-351 */
+                match_f[bestIdx] = iKF;
+                if (check_ori) ipush(&hist[rot_bin(kf->keys[iKF].angle, F->keys[bestIdx].angle)], bestIdx);
+                ++nmatches;
+            }
+        }
+        ++ia; ++ib;
+    }
+    if (check_ori) {
+        int cnt[HISTO_LENGTH], i1, i2, i3;
+        for (int i = 0; i < HISTO_LENGTH; ++i) cnt[i] = hist[i].n;
+        orc_three_maxima(cnt, HISTO_LENGTH, &i1, &i2, &i3);
+        for (int i = 0; i < HISTO_LENGTH; ++i) {
+            if (i == i1 || i == i2 || i == i3) continue;
+            for (int j = 0; j < hist[i].n; ++j) { match_f[hist[i].v[j]] = -1; --nmatches; }
+        }
+    }
+    for (int i = 0; i < HISTO_LENGTH; ++i) free(hist[i].v);
+    return nmatches;
+}
+
+/* SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12): src/ORBmatcher.cc:760-903.
+ * match12[KF1.N] receives the KF2 feature index (whose MapPoint is stored in vpMatches12[idx1]) or -1. */
+int orc_search_by_bow_kf_kf(const orc_bowframe* k1, const orc_bowframe* k2, float nnratio, int check_ori, int32_t* match12)
+{
+    ivec hist[HISTO_LENGTH]; memset(hist, 0, sizeof(hist));
+    uint8_t* matched2 = (uint8_t*)calloc((size_t)(k2->n > 0 ? k2->n : 1), 1);
+    int nmatches = 0;
+    for (int j = 0; j < k1->n; ++j) match12[j] = -1;
+    FOR_SHARED_NODES(k1, k2, ia, ib) {
+        for (int a = k1->node_off[ia]; a < k1->node_off[ia + 1]; ++a) {
+            const int idx1 = k1->feat[a];
+            if (!k1->valid[idx1]) continue;
+            const uint8_t* d1 = k1->desc + 32 * (size_t)idx1;
+            int best1 = 256, best2 = 256, bestIdx2 = -1;
+            for (int b = k2->node_off[ib]; b < k2->node_off[ib + 1]; ++b) {
+                const int idx2 = k2->feat[b];
+                if (matched2[idx2] || !k2->valid[idx2]) continue;              /* :822-826 */
+                const int dist = orc_descriptor_distance(d1, k2->desc + 32 * (size_t)idx2);
+                if (dist < best1) { best2 = best1; best1 = dist; bestIdx2 = idx2; }
+                else if (dist < best2) best2 = dist;
+            }
+            if (best1 < TH_LOW && (float)best1 < nnratio * (float)best2) {     /* :845-847 (strict) */
+                match12[idx1] = bestIdx2;
+                matched2[bestIdx2] = 1;
+                if (check_ori) ipush(&hist[rot_bin(k1->keys[idx1].angle, k2->keys[bestIdx2].angle)], idx1);
+                ++nmatches;
+            }
+        }
+        ++ia; ++ib;
+    }
+    if (check_ori) {
+        int cnt[HISTO_LENGTH], i1, i2, i3;
+        for (int i = 0; i < HISTO_LENGTH; ++i) cnt[i] = hist[i].n;
+        orc_three_maxima(cnt, HISTO_LENGTH, &i1, &i2, &i3);
+        for (int i = 0; i < HISTO_LENGTH; ++i) {
+            if (i == i1 || i == i2 || i == i3) continue;
+            for (int j = 0; j < hist[i].n; ++j) { match12[hist[i].v[j]] = -1; --nmatches; }
+        }
+    }
+    for (int i = 0; i < HISTO_LENGTH; ++i) free(hist[i].v);
+    free(matched2);
+    return nmatches;
+}
+
+/* CheckDistEpipolarLine: src/ORBmatcher.cc:213-240.  F12 row-major 3x3 float. */
+static int check_epipolar(const orc_keypoint* kp1, const orc_keypoint* kp2, const float* F12, const float* sigma2)
+{
+    const float a = kp1->x * F12[0] + kp1->y * F12[3] + F12[6];
+    const float b = kp1->x * F12[1] + kp1->y * F12[4] + F12[7];
+    const float c = kp1->x * F12[2] + kp1->y * F12[5] + F12[8];
+    const float num = a * kp2->x + b * kp2->y + c;
+    const float den = a * a + b * b;
+    if (den == 0) return 0;
+    const float dsqr = num * num / den;
+    return dsqr < 3.84 * sigma2[kp2->octave];
+}
+
+/* SearchForTriangulation: src/ORBmatcher.cc:915-1127.  valid[i] = feature i already HAS a MapPoint
+ * (those are skipped, :981,:1011).  (ex,ey) = epipole of KF1's centre in KF2 (:927-929, computed by
+ * the caller).  match12[KF1.N] = KF2 index or -1 (vMatches12); pairs are its non-negative entries. */
+int orc_search_for_triangulation(const orc_bowframe* k1, const orc_bowframe* k2, const float* F12, float ex, float ey,
+                                 const float* scale2, const float* sigma2_2, int only_stereo, int check_ori, int32_t* match12)
+{
+    ivec hist[HISTO_LENGTH]; memset(hist, 0, sizeof(hist));
+    uint8_t* matched2 = (uint8_t*)calloc((size_t)(k2->n > 0 ? k2->n : 1), 1);
+    int nmatches = 0;
+    for (int j = 0; j < k1->n; ++j) match12[j] = -1;
+    FOR_SHARED_NODES(k1, k2, ia, ib) {
+        for (int a = k1->node_off[ia]; a < k1->node_off[ia + 1]; ++a) {
+            const int idx1 = k1->feat[a];
+            if (k1->valid[idx1]) continue;                                     /* :981 */
+            const int stereo1 = k1->uright && k1->uright[idx1] >= 0;
+            if (only_stereo && !stereo1) continue;
+            const orc_keypoint* kp1 = &k1->keys[idx1];
+            const uint8_t* d1 = k1->desc + 32 * (size_t)idx1;
+            int bestDist = TH_LOW, bestIdx2 = -1;
+            for (int b = k2->node_off[ib]; b < k2->node_off[ib + 1]; ++b) {
+                const int idx2 = k2->feat[b];
+                if (matched2[idx2] || k2->valid[idx2]) continue;               /* :1011 */
+                const int stereo2 = k2->uright && k2->uright[idx2] >= 0;
+                if (only_stereo && !stereo2) continue;
+                const int dist = orc_descriptor_distance(d1, k2->desc + 32 * (size_t)idx2);
+                if (dist > TH_LOW || dist > bestDist) continue;                /* :1026 */
+                const orc_keypoint* kp2 = &k2->keys[idx2];
+                if (!stereo1 && !stereo2) {                                    /* :1034-1044 */
+                    const float distex = ex - kp2->x, distey = ey - kp2->y;
+                    if (distex * distex + distey * distey < 100 * scale2[kp2->octave]) continue;
+                }
+                if (check_epipolar(kp1, kp2, F12, sigma2_2)) { bestIdx2 = idx2; bestDist = dist; }
+            }
+            if (bestIdx2 >= 0) {
+                match12[idx1] = bestIdx2;
+                matched2[bestIdx2] = 1;                                        /* fork-specific, :1061 */
+                ++nmatches;
+                if (check_ori) ipush(&hist[rot_bin(kp1->angle, k2->keys[bestIdx2].angle)], idx1);
+            }
+        }
+        ++ia; ++ib;
+    }
+    if (check_ori) {
+        int cnt[HISTO_LENGTH], i1, i2, i3;
+        for (int i = 0; i < HISTO_LENGTH; ++i) cnt[i] = hist[i].n;
+        orc_three_maxima(cnt, HISTO_LENGTH, &i1, &i2, &i3);
+        for (int i = 0; i < HISTO_LENGTH; ++i) {
+            if (i == i1 || i == i2 || i == i3) continue;
+            for (int j = 0; j < hist[i].n; ++j) { match12[hist[i].v[j]] = -1; --nmatches; } /* :1108 also clears vbMatched2 */
+        }
+    }
+    for (int i = 0; i < HISTO_LENGTH; ++i) free(hist[i].v);
+    free(matched2);
+    return nmatches;
+}
+
+/* ---------------- Frame grid ---------------- */
+/* Frame::AssignFeaturesToGrid + PosInGrid: src/Frame.cc:398-422, 682-698.  CSR over cells, cell = ix*ROWS+iy. */
+void orc_assign_grid(const orc_keypoint* keys, int n, const orc_grid* g, int32_t* cell_off, int32_t* cell_idx)
+{
+    const int nc = ORC_GRID_COLS * ORC_GRID_ROWS;
+    int* cell = (int*)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1));
+    memset(cell_off, 0, sizeof(int32_t) * (size_t)(nc + 1));
+    for (int i = 0; i < n; ++i) {
+        const int px = (int)roundf((keys[i].x - g->min_x) * g->inv_w);
+        const int py = (int)roundf((keys[i].y - g->min_y) * g->inv_h);
+        cell[i] = (px < 0 || px >= ORC_GRID_COLS || py < 0 || py >= ORC_GRID_ROWS) ? -1 : px * ORC_GRID_ROWS + py;
+        if (cell[i] >= 0) cell_off[cell[i] + 1]++;
+    }
+    for (int c = 0; c < nc; ++c) cell_off[c + 1] += cell_off[c];
+    int* fill = (int*)calloc((size_t)nc, sizeof(int));
+    for (int i = 0; i < n; ++i) if (cell[i] >= 0) cell_idx[cell_off[cell[i]] + fill[cell[i]]++] = i;
+    free(fill); free(cell);
+}
+
+/* Frame::GetFeaturesInArea: src/Frame.cc:590-671 (KeyFrame::GetFeaturesInArea, src/KeyFrame.cc:794-838, is the
+ * same without the level filter: pass min_level = -1, max_level = -1). Returns count; out in visit order. */
+int orc_features_in_area(const orc_keypoint* keys, const orc_grid* g, const int32_t* cell_off, const int32_t* cell_idx,
+                         float x, float y, float r, int min_level, int max_level, int32_t* out)
+{
+    int n = 0;
+    int c0 = (int)floorf((x - g->min_x - r) * g->inv_w); if (c0 < 0) c0 = 0;
+    if (c0 >= ORC_GRID_COLS) return 0;
+    int c1 = (int)ceilf((x - g->min_x + r) * g->inv_w); if (c1 > ORC_GRID_COLS - 1) c1 = ORC_GRID_COLS - 1;
+    if (c1 < 0) return 0;
+    int r0 = (int)floorf((y - g->min_y - r) * g->inv_h); if (r0 < 0) r0 = 0;
+    if (r0 >= ORC_GRID_ROWS) return 0;
+    int r1 = (int)ceilf((y - g->min_y + r) * g->inv_h); if (r1 > ORC_GRID_ROWS - 1) r1 = ORC_GRID_ROWS - 1;
+    if (r1 < 0) return 0;
+    const int check = (min_level > 0) || (max_level >= 0);
+    for (int ix = c0; ix <= c1; ++ix)
+        for (int iy = r0; iy <= r1; ++iy) {
+            const int c = ix * ORC_GRID_ROWS + iy;
+            for (int j = cell_off[c]; j < cell_off[c + 1]; ++j) {
+                const orc_keypoint* kp = &keys[cell_idx[j]];
+                if (check) {
+                    if (kp->octave < min_level) continue;
+                    if (max_level >= 0 && kp->octave > max_level) continue;
+                }
+                const float dx = kp->x - x, dy = kp->y - y;
+                if (fabsf(dx) < r && fabsf(dy) < r) out[n++] = cell_idx[j];
+            }
+        }
+    return n;
+}
+
+/* SearchByProjection(Frame&, vector<MapPoint*>&, th): src/ORBmatcher.cc:78-191 + RadiusByViewingCos :194-201.
+ * pts: the visible, good map points in caller order (mbTrackInView && !isBad).  occupied[j] != 0: frame
+ * keypoint j already holds a MapPoint with Observations() > 0 (:136-138); it is updated as matches are made
+ * (the reference writes F.mvpMapPoints[bestIdx] = pMP and the candidate points are observed map points).
+ * assign[j] = index of the point matched to keypoint j, or -1. */
+int orc_search_by_projection_points(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
+                                    const float* uright, const float* scale, const orc_grid* g, const int32_t* cell_off,
+                                    const int32_t* cell_idx, const uint8_t* occupied_in, float th, float nnratio, int32_t* assign)
+{
+    uint8_t* occ = (uint8_t*)malloc((size_t)(n > 0 ? n : 1));
+    int32_t* cand = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    for (int j = 0; j < n; ++j) { occ[j] = occupied_in ? occupied_in[j] : 0; assign[j] = -1; }
+    int nmatches = 0;
+    const int bFactor = th != 1.0;
+    for (int i = 0; i < npts; ++i) {
+        const orc_projpoint* p = &pts[i];
+        const int lvl = p->level;
+        float r = p->view_cos > 0.998 ? 2.5f : 4.0f;
+        if (bFactor) r *= th;
+        const int nc = orc_features_in_area(keys, g, cell_off, cell_idx, p->u, p->v, r * scale[lvl], lvl - 1, lvl, cand);
+        if (nc == 0) continue;
+        int best = 256, bestLevel = -1, best2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (int k = 0; k < nc; ++k) {
+            const int idx = cand[k];
+            if (occ[idx]) continue;
+            if (uright && uright[idx] > 0) {
+                const float er = fabsf(p->ur - uright[idx]);
+                if (er > r * scale[lvl]) continue;
+            }
+            const int dist = orc_descriptor_distance(p->desc, desc + 32 * (size_t)idx);
+            if (dist < best) { best2 = best; best = dist; bestLevel2 = bestLevel; bestLevel = keys[idx].octave; bestIdx = idx; }
+            else if (dist < best2) { bestLevel2 = keys[idx].octave; best2 = dist; }
+        }
+        if (best <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && (float)best > nnratio * (float)best2) continue;
+            assign[bestIdx] = i; occ[bestIdx] = 1;
+            ++nmatches;
+        }
+    }
+    free(occ); free(cand);
+    return nmatches;
+}
+
+/* SearchByProjection(Frame& Cur, const Frame& Last, th, bMono): src/ORBmatcher.cc:1741-1910, after the
+ * projection (:1784-1808, done by the caller): pts[i] = (u, v, ur = u - mbf*invzc, level = nLastOctave,
+ * angle = LastFrame.mvKeysUn[i].angle, desc).  motion: 0 = neither, 1 = forward, 2 = backward (:1768-1769). */
+int orc_search_by_projection_frame(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
+                                   const float* uright, const float* scale, const orc_grid* g, const int32_t* cell_off,
+                                   const int32_t* cell_idx, const uint8_t* occupied_in, float th, int motion, int check_ori,
+                                   int32_t* assign)
+{
+    ivec hist[HISTO_LENGTH]; memset(hist, 0, sizeof(hist));
+    uint8_t* occ = (uint8_t*)malloc((size_t)(n > 0 ? n : 1));
+    int32_t* cand = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    for (int j = 0; j < n; ++j) { occ[j] = occupied_in ? occupied_in[j] : 0; assign[j] = -1; }
+    int nmatches = 0;
+    for (int i = 0; i < npts; ++i) {
+        const orc_projpoint* p = &pts[i];
+        const int lo = p->level;
+        const float radius = th * scale[lo];
+        int nc;
+        if (motion == 1) nc = orc_features_in_area(keys, g, cell_off, cell_idx, p->u, p->v, radius, lo, -1, cand);
+        else if (motion == 2) nc = orc_features_in_area(keys, g, cell_off, cell_idx, p->u, p->v, radius, 0, lo, cand);
+        else nc = orc_features_in_area(keys, g, cell_off, cell_idx, p->u, p->v, radius, lo - 1, lo + 1, cand);
+        if (nc == 0) continue;
+        int best = 256, bestIdx2 = -1;
+        for (int k = 0; k < nc; ++k) {
+            const int i2 = cand[k];
+            if (occ[i2]) continue;
+            if (uright && uright[i2] > 0) {
+                const float er = fabsf(p->ur - uright[i2]);
+                if (er > radius) continue;
+            }
+            const int dist = orc_descriptor_distance(p->desc, desc + 32 * (size_t)i2);
+            if (dist < best) { best = dist; bestIdx2 = i2; }
+        }
+        if (best <= TH_HIGH) {
+            assign[bestIdx2] = i; occ[bestIdx2] = 1;
+            ++nmatches;
+            if (check_ori) ipush(&hist[rot_bin(p->angle, keys[bestIdx2].angle)], bestIdx2);
+        }
+    }
+    if (check_ori) {
+        int cnt[HISTO_LENGTH], i1, i2, i3;
+        for (int i = 0; i < HISTO_LENGTH; ++i) cnt[i] = hist[i].n;
+        orc_three_maxima(cnt, HISTO_LENGTH, &i1, &i2, &i3);
+        for (int i = 0; i < HISTO_LENGTH; ++i) {
+            if (i == i1 || i == i2 || i == i3) continue;
+            for (int j = 0; j < hist[i].n; ++j) { assign[hist[i].v[j]] = -1; --nmatches; }
+        }
+    }
+    for (int i = 0; i < HISTO_LENGTH; ++i) free(hist[i].v);
+    free(occ); free(cand);
+    return nmatches;
+}
+
+/* ---------------- Frame::ComputeStereoMatches: src/Frame.cc:831-1128 ----------------
+ * pyrL/pyrR: un-bordered level images packed back to back (level l at lvl_off[l], size lvl_w[l] x lvl_h[l]). */
+typedef struct { int d, i; } distidx;
+static int cmp_distidx(const void* a, const void* b)
+{
+    const distidx *x = (const distidx*)a, *y = (const distidx*)b;
+    if (x->d != y->d) return x->d < y->d ? -1 : 1;
+    return x->i < y->i ? -1 : (x->i > y->i);
+}
+
+int orc_stereo_matches(const orc_keypoint* kL, const uint8_t* dL, int N, const orc_keypoint* kR, const uint8_t* dR, int Nr,
+                       const uint8_t* pyrL, const uint8_t* pyrR, const int* lvl_w, const int* lvl_h, const size_t* lvl_off,
+                       const float* scale, const float* inv_scale, float mbf, float mb, float* uRight, float* depth)
+{
+    const int nRows = lvl_h[0];
+    ivec* rows = (ivec*)calloc((size_t)nRows, sizeof(ivec));
+    for (int i = 0; i < N; ++i) { uRight[i] = -1.0f; depth[i] = -1.0f; }
+    for (int iR = 0; iR < Nr; ++iR) {                                          /* :869-888 */
+        const float kpY = kR[iR].y;
+        const float r = 2.0f * scale[kR[iR].octave];
+        const int maxr = (int)ceilf(kpY + r), minr = (int)floorf(kpY - r);
+        for (int yi = minr; yi <= maxr; ++yi) if (yi >= 0 && yi < nRows) ipush(&rows[yi], iR);
+    }
+    const float minZ = mb, minD = 0, maxD = mbf / minZ;
+    distidx* vd = (distidx*)malloc(sizeof(distidx) * (size_t)(N > 0 ? N : 1));
+    int nvd = 0;
+    const int thOrbDist = (TH_HIGH + TH_LOW) / 2;
+    for (int iL = 0; iL < N; ++iL) {
+        const orc_keypoint* kpL = &kL[iL];
+        const int levelL = kpL->octave;
+        const float vL = kpL->y, uL = kpL->x;
+        const ivec* cands = &rows[(size_t)vL];
+        if (cands->n == 0) continue;
+        const float minU = uL - maxD, maxU = uL - minD;
+        if (maxU < 0) continue;
+        int bestDist = TH_HIGH; int bestIdxR = 0;
+        for (int c = 0; c < cands->n; ++c) {
+            const int iR = cands->v[c];
+            const orc_keypoint* kpR = &kR[iR];
+            if (kpR->octave < levelL - 1 || kpR->octave > levelL + 1) continue;
+            const float uR = kpR->x;
+            if (uR >= minU && uR <= maxU) {
+                const int dist = orc_descriptor_distance(dL + 32 * (size_t)iL, dR + 32 * (size_t)iR);
+                if (dist < bestDist) { bestDist = dist; bestIdxR = iR; }
+            }
+        }
+        if (bestDist < thOrbDist) {
+            const float uR0 = kR[bestIdxR].x;
+            const float sf = inv_scale[kpL->octave];
+            const float scaleduL = roundf(kpL->x * sf), scaledvL = roundf(kpL->y * sf), scaleduR0 = roundf(uR0 * sf);
+            const int w = 5, L = 5;
+            const int lw = lvl_w[kpL->octave];
+            const uint8_t* IL = pyrL + lvl_off[kpL->octave];
+            const uint8_t* IR = pyrR + lvl_off[kpL->octave];
+            const int y0 = (int)(scaledvL - w), xl0 = (int)(scaleduL - w);
+            int best = INT_MAX, bestinc = 0;
+            float vDists[11];
+            const float iniu = scaleduR0 - L - w, endu = scaleduR0 + L + w + 1;   /* fork: - L - w, :1025 */
+            if (iniu < 0 || endu >= (float)lw) continue;
+            const float cL = (float)IL[(size_t)(y0 + w) * lw + xl0 + w];
+            for (int inc = -L; inc <= L; ++inc) {
+                const int xr0 = (int)(scaleduR0 + (float)inc - w);
+                const float cR = (float)IR[(size_t)(y0 + w) * lw + xr0 + w];
+                double s = 0;                                                   /* cv::norm L1 accumulates in double */
+                for (int yy = 0; yy < 2 * w + 1; ++yy)
+                    for (int xx = 0; xx < 2 * w + 1; ++xx) {
+                        const float a = (float)IL[(size_t)(y0 + yy) * lw + xl0 + xx] - cL;
+                        const float b = (float)IR[(size_t)(y0 + yy) * lw + xr0 + xx] - cR;
+                        s += fabs((double)(a - b));
+                    }
+                const float dist = (float)s;
+                if (dist < (float)best) { best = (int)dist; bestinc = inc; }
+                vDists[L + inc] = dist;
+            }
+            if (bestinc == -L || bestinc == L) continue;
+            const float d1 = vDists[L + bestinc - 1], d2 = vDists[L + bestinc], d3 = vDists[L + bestinc + 1];
+            const float deltaR = (d1 - d3) / (2.0f * (d1 + d3 - 2.0f * d2));
+            if (deltaR < -1 || deltaR > 1) continue;
+            float bestuR = scale[kpL->octave] * ((float)scaleduR0 + (float)bestinc + deltaR);
+            float disparity = uL - bestuR;
+            if (disparity >= minD && disparity < maxD) {
+                if (disparity <= 0) { disparity = 0.01; bestuR = uL - 0.01; }
+                depth[iL] = mbf / disparity;
+                uRight[iL] = bestuR;
+                vd[nvd].d = best; vd[nvd].i = iL; ++nvd;
+            }
+        }
+    }
+    if (nvd > 0) {                                                             /* :1112-1127 (reference: UB when empty) */
+        qsort(vd, (size_t)nvd, sizeof(distidx), cmp_distidx);
+        const float median = (float)vd[nvd / 2].d;
+        const float thDist = 1.5f * 1.4f * median;
+        for (int i = nvd - 1; i >= 0; --i) {
+            if ((float)vd[i].d < thDist) break;
+            uRight[vd[i].i] = -1; depth[vd[i].i] = -1;
+        }
+    }
+    for (int i = 0; i < nRows; ++i) free(rows[i].v);
+    free(rows); free(vd);
+    return nvd;
 }

@@ -70,6 +70,53 @@ int orc_extract(const orc_params* p, const uint8_t* img, int w, int h, size_t st
 
 /* ---- matcher side (orb_match.c) ---- */
 int orc_descriptor_distance(const uint8_t* a, const uint8_t* b); /* src/ORBmatcher.cc:2123-2143 */
+void orc_three_maxima(const int* count, int L, int* ind1, int* ind2, int* ind3); /* :2076-2118 */
+
+/* DBoW2 vocabulary tree flattened: node 0 = root; children of node i = child[child_off[i]..child_off[i+1])
+ * in file order (TemplatedVocabulary.h:1385-1487); leaf <=> no children. */
+typedef struct {
+    int k, L, nnodes;
+    const int32_t* child_off; const int32_t* child;
+    const uint8_t* desc;       /* nnodes x 32 */
+    const int32_t* word_id;    /* leaves only */
+    const float* weight;
+} orc_vocab;
+void orc_bow_transform(const orc_vocab* V, const uint8_t* desc, int n, int levelsup, int32_t* word, float* weight, int32_t* node);
+int orc_feature_vector(const int32_t* node, const float* weight, int n, int32_t* node_id, int32_t* node_off, int32_t* feat);
+
+/* one (key)frame as the BoW matchers see it */
+typedef struct {
+    int n;
+    const uint8_t* desc;        /* n x 32 */
+    const orc_keypoint* keys;   /* mvKeysUn */
+    const uint8_t* valid;       /* per feature: has a good MapPoint */
+    const float* uright;        /* mvuRight or NULL (monocular) */
+    int nnodes;                 /* FeatureVector in CSR, ascending node id */
+    const int32_t* node_id; const int32_t* node_off; const int32_t* feat;
+} orc_bowframe;
+int orc_search_by_bow_kf_f(const orc_bowframe* kf, const orc_bowframe* F, float nnratio, int check_ori, int32_t* match_f);
+int orc_search_by_bow_kf_kf(const orc_bowframe* k1, const orc_bowframe* k2, float nnratio, int check_ori, int32_t* match12);
+int orc_search_for_triangulation(const orc_bowframe* k1, const orc_bowframe* k2, const float* F12, float ex, float ey,
+                                 const float* scale2, const float* sigma2_2, int only_stereo, int check_ori, int32_t* match12);
+
+#define ORC_GRID_COLS 64 /* include/Frame.h:55 */
+#define ORC_GRID_ROWS 48 /* include/Frame.h:60 */
+typedef struct { float min_x, min_y, inv_w, inv_h; } orc_grid; /* mnMinX, mnMinY, mfGridElementWidthInv/HeightInv */
+void orc_assign_grid(const orc_keypoint* keys, int n, const orc_grid* g, int32_t* cell_off, int32_t* cell_idx);
+int orc_features_in_area(const orc_keypoint* keys, const orc_grid* g, const int32_t* cell_off, const int32_t* cell_idx,
+                         float x, float y, float r, int min_level, int max_level, int32_t* out);
+/* a projected map point (MapPoint::mTrackProjX/Y/XR, mnTrackScaleLevel, mTrackViewCos, GetDescriptor) */
+typedef struct { float u, v, ur, view_cos, angle; int32_t level; uint8_t desc[32]; } orc_projpoint;
+int orc_search_by_projection_points(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
+                                    const float* uright, const float* scale, const orc_grid* g, const int32_t* cell_off,
+                                    const int32_t* cell_idx, const uint8_t* occupied_in, float th, float nnratio, int32_t* assign);
+int orc_search_by_projection_frame(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
+                                   const float* uright, const float* scale, const orc_grid* g, const int32_t* cell_off,
+                                   const int32_t* cell_idx, const uint8_t* occupied_in, float th, int motion, int check_ori,
+                                   int32_t* assign);
+int orc_stereo_matches(const orc_keypoint* kL, const uint8_t* dL, int N, const orc_keypoint* kR, const uint8_t* dR, int Nr,
+                       const uint8_t* pyrL, const uint8_t* pyrR, const int* lvl_w, const int* lvl_h, const size_t* lvl_off,
+                       const float* scale, const float* inv_scale, float mbf, float mb, float* uRight, float* depth);
 
 #ifdef __cplusplus
 }

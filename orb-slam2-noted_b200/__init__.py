@@ -11,5 +11,9 @@ The package directory has a hyphen (the repository's naming contract); import it
 from .binding import (KP_DTYPE, OrbxError, lib, lib_path, ORBextractor, descriptor_distance, hamming_best2,
                       stage_names)
 
-__all__ = ["KP_DTYPE", "OrbxError", "lib", "lib_path", "ORBextractor", "descriptor_distance", "hamming_best2",
+from .matcher import (ORBmatcher, Vocabulary, FrameView, feature_vector, assign_features_to_grid, compute_stereo_matches,
+                      PROJ_QUERY_DTYPE)
+
+__all__ = ["ORBmatcher", "Vocabulary", "FrameView", "feature_vector", "assign_features_to_grid", "compute_stereo_matches",
+           "PROJ_QUERY_DTYPE", "KP_DTYPE", "OrbxError", "lib", "lib_path", "ORBextractor", "descriptor_distance", "hamming_best2",
            "stage_names"]

@@ -1,36 +1,65 @@
-"""Build liborbx.so (all CUDA kernels + the C ABI) for sm_100a, in-tree, with plain nvcc."""
+"""Build liborbx.so (all CUDA kernels + the C ABI) for sm_100a, in-tree, with plain nvcc.
+One object per .cu (compiled in parallel, rebuilt only when stale), then one link step."""
 import glob, os, subprocess, sys
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
+OBJ = os.path.join(HERE, "build")
 OUT = os.path.join(HERE, "liborbx.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-         "-Xcompiler", "-fPIC,-ffp-contract=off,-Wall", "-shared"]
+         "-Xcompiler", "-fPIC,-ffp-contract=off,-Wall"]
 
 
 def sources():
     return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
 
 
-def needs_build():
-    if not os.path.exists(OUT):
-        return True
-    t = os.path.getmtime(OUT)
-    deps = sources() + glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.inc")) + \
+def headers():
+    return glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.inc")) + \
         glob.glob(os.path.join(HERE, "..", "include", "*.h"))
+
+
+def _obj(src):
+    return os.path.join(OBJ, os.path.basename(src)[:-3] + ".o")
+
+
+def _stale(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
     return any(os.path.getmtime(d) > t for d in deps)
+
+
+def needs_build():
+    return _stale(OUT, sources() + headers())
+
+
+def _compile(src, verbose):
+    cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", _obj(src), src]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    return src, r
 
 
 def build(force=False, verbose=False):
     if not force and not needs_build():
         return OUT
-    cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT] + sources()
-    r = subprocess.run(cmd, capture_output=True, text=True)
-    if verbose or r.returncode:
-        sys.stderr.write(r.stdout + r.stderr)
+    os.makedirs(OBJ, exist_ok=True)
+    hdrs = headers()
+    todo = [s for s in sources() if force or _stale(_obj(s), [s] + hdrs)]
+    with ThreadPoolExecutor(max_workers=min(8, max(1, len(todo)))) as ex:
+        for src, r in ex.map(lambda s: _compile(s, verbose), todo):
+            if verbose or r.returncode:
+                sys.stderr.write(f"== {os.path.basename(src)}\n" + r.stdout + r.stderr)
+            if r.returncode:
+                raise RuntimeError(f"nvcc failed on {src}")
+    objs = [_obj(s) for s in sources()]
+    r = subprocess.run([NVCC, "-shared", "-o", OUT] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"],
+                       capture_output=True, text=True)
     if r.returncode:
-        raise RuntimeError("nvcc failed building liborbx.so")
+        sys.stderr.write(r.stdout + r.stderr)
+        raise RuntimeError("nvcc link failed for liborbx.so")
     return OUT
 
 

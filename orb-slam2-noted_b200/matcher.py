@@ -1,0 +1,215 @@
+"""Host-side mirror of ORB_SLAM2::ORBmatcher (include/ORBmatcher.h:48-264), the DBoW2 vocabulary transform and
+Frame::ComputeStereoMatches over the C ABI (include/orbx.h).  SLAM objects are replaced by plain arrays:
+
+  FrameView   what the matchers read from a Frame / KeyFrame: descriptors (N x 32), undistorted keypoints
+              (KP_DTYPE), per-feature "has a good MapPoint" flags, mvuRight, and the FeatureVector in CSR form.
+
+All compute runs in liborbx.so (CUDA); nothing here falls back to the CPU.
+"""
+import ctypes
+import numpy as np
+from .binding import KP_DTYPE, OrbxError, lib, _np
+
+MAX_LEVELS = 16
+BOW_KF_FRAME, BOW_KF_KF, BOW_TRIANGULATE = 0, 1, 2
+PROJ_RATIO_SAME_LEVEL, PROJ_CHECK_URIGHT = 1, 2
+FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48  # include/Frame.h:55,60
+
+PROJ_QUERY_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("radius", "<f4"), ("ur", "<f4"), ("angle", "<f4"),
+                             ("min_level", "<i4"), ("max_level", "<i4"), ("reserved", "<i4"), ("desc", "u1", (32,))])
+assert PROJ_QUERY_DTYPE.itemsize == 64
+
+
+class _BowSide(ctypes.Structure):
+    _fields_ = [("desc", ctypes.c_void_p), ("keys", ctypes.c_void_p), ("has_point", ctypes.c_void_p), ("uright", ctypes.c_void_p),
+                ("n", ctypes.c_int), ("nnodes", ctypes.c_int), ("node_id", ctypes.c_void_p), ("node_off", ctypes.c_void_p),
+                ("feat", ctypes.c_void_p)]
+
+
+class _Triangulation(ctypes.Structure):
+    _fields_ = [("F12", ctypes.c_float * 9), ("ex", ctypes.c_float), ("ey", ctypes.c_float),
+                ("scale2", ctypes.c_float * MAX_LEVELS), ("sigma2_2", ctypes.c_float * MAX_LEVELS), ("only_stereo", ctypes.c_int)]
+
+
+class _Grid(ctypes.Structure):
+    _fields_ = [("min_x", ctypes.c_float), ("min_y", ctypes.c_float), ("inv_w", ctypes.c_float), ("inv_h", ctypes.c_float),
+                ("cols", ctypes.c_int), ("rows", ctypes.c_int)]
+
+
+_ready = False
+
+
+def _mlib():
+    global _ready
+    L = lib()
+    if _ready:
+        return L
+    vp, ci, cf = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
+    ip = ctypes.POINTER(ci)
+    L.orbx_vocab_create.argtypes = [vp, ci, ci, ci, vp, vp, vp, vp, vp, ctypes.POINTER(vp)]
+    L.orbx_vocab_load_text.argtypes = [vp, ctypes.c_char_p, ctypes.POINTER(vp)]
+    L.orbx_vocab_destroy.argtypes = [vp]
+    L.orbx_vocab_destroy.restype = None
+    L.orbx_vocab_info.argtypes = [vp, ip, ip, ip, ip]
+    L.orbx_bow_transform.argtypes = [vp, vp, vp, ci, ci, ci, vp, vp, vp]
+    L.orbx_feature_vector.argtypes = [vp, vp, ci, vp, vp, vp, ip]
+    L.orbx_match_bow.argtypes = [vp, ci, ctypes.POINTER(_BowSide), ctypes.POINTER(_BowSide), ctypes.POINTER(_Triangulation), cf, ci,
+                                 ci, vp, ip]
+    L.orbx_assign_grid.argtypes = [vp, vp, ci, ctypes.POINTER(_Grid), ci, vp, vp]
+    L.orbx_search_by_projection.argtypes = [vp, vp, ci, vp, vp, vp, ci, ctypes.POINTER(_Grid), vp, ci, ci, cf, ci, ci, vp, ip]
+    L.orbx_stereo_match.argtypes = [vp, vp, ci, vp, vp, ci, vp, vp, ci, cf, cf, ci, vp, vp, ip]
+    _ready = True
+    return L
+
+
+def _chk(ex, rc, what):
+    if rc:
+        L = lib()
+        raise OrbxError(f"{what}: {L.orbx_strerror(rc).decode()} ({rc}) {L.orbx_last_cuda_error(ex._h).decode()}")
+
+
+class Vocabulary:
+    """ORBVocabulary (DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB>): load + transform only."""
+
+    def __init__(self, ex, k=None, L=None, child_off=None, child=None, desc=None, word_id=None, weight=None, path=None):
+        self._ex, self._v = ex, ctypes.c_void_p()
+        M = _mlib()
+        if path is not None:
+            _chk(ex, M.orbx_vocab_load_text(ex._h, path.encode(), ctypes.byref(self._v)), "orbx_vocab_load_text")
+        else:
+            a = [np.ascontiguousarray(child_off, np.int32), np.ascontiguousarray(child, np.int32), np.ascontiguousarray(desc, np.uint8),
+                 np.ascontiguousarray(word_id, np.int32), np.ascontiguousarray(weight, np.float32)]
+            _chk(ex, M.orbx_vocab_create(ex._h, k, L, len(a[3]), *[_np(x) for x in a], ctypes.byref(self._v)), "orbx_vocab_create")
+
+    def info(self):
+        v = [ctypes.c_int() for _ in range(4)]
+        _mlib().orbx_vocab_info(self._v, *[ctypes.byref(x) for x in v])
+        return tuple(x.value for x in v)  # k, L, nnodes, nwords
+
+    def transform(self, desc, levelsup=4):
+        """-> (word_id, weight, node_id) per feature; see feature_vector() for the FeatureVector."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(desc)
+        word, weight, node = np.empty(n, np.int32), np.empty(n, np.float32), np.empty(n, np.int32)
+        _chk(self._ex, _mlib().orbx_bow_transform(self._ex._h, self._v, _np(desc), n, levelsup, 0, _np(word), _np(weight), _np(node)),
+             "orbx_bow_transform")
+        return word, weight, node
+
+    def close(self):
+        if self._v:
+            _mlib().orbx_vocab_destroy(self._v)
+            self._v = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def feature_vector(node, weight=None):
+    node = np.ascontiguousarray(node, np.int32)
+    n = len(node)
+    w = None if weight is None else np.ascontiguousarray(weight, np.float32)
+    nid, noff, feat = np.empty(n + 1, np.int32), np.empty(n + 2, np.int32), np.empty(n + 1, np.int32)
+    nn = ctypes.c_int()
+    rc = _mlib().orbx_feature_vector(_np(node), _np(w), n, _np(nid), _np(noff), _np(feat), ctypes.byref(nn))
+    if rc:
+        raise OrbxError(f"orbx_feature_vector: {rc}")
+    return nid[:nn.value].copy(), noff[:nn.value + 1].copy(), feat[:noff[nn.value]].copy()
+
+
+class FrameView:
+    def __init__(self, desc, keys, has_point=None, uright=None, node_id=None, node_off=None, feat=None):
+        self.desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        self.keys = np.ascontiguousarray(keys, KP_DTYPE)
+        self.has_point = None if has_point is None else np.ascontiguousarray(has_point, np.uint8)
+        self.uright = None if uright is None else np.ascontiguousarray(uright, np.float32)
+        self.node_id = None if node_id is None else np.ascontiguousarray(node_id, np.int32)
+        self.node_off = None if node_off is None else np.ascontiguousarray(node_off, np.int32)
+        self.feat = None if feat is None else np.ascontiguousarray(feat, np.int32)
+
+    @property
+    def N(self):
+        return len(self.desc)
+
+    def _c(self):
+        return _BowSide(self.desc.ctypes.data, self.keys.ctypes.data, None if self.has_point is None else self.has_point.ctypes.data,
+                        None if self.uright is None else self.uright.ctypes.data, self.N, 0 if self.node_id is None else len(self.node_id),
+                        None if self.node_id is None else self.node_id.ctypes.data, None if self.node_off is None else self.node_off.ctypes.data,
+                        None if self.feat is None else self.feat.ctypes.data)
+
+
+class ORBmatcher:
+    """ORBmatcher(nnratio=0.6, checkOri=True), include/ORBmatcher.h:57."""
+    TH_LOW, TH_HIGH, HISTO_LENGTH = 50, 100, 30  # src/ORBmatcher.cc:56-58
+
+    def __init__(self, ctx, nnratio=0.6, checkOri=True):
+        self._ex, self.mfNNratio, self.mbCheckOrientation = ctx, float(nnratio), bool(checkOri)
+
+    def _bow(self, mode, s1, s2, tri=None):
+        a, b = s1._c(), s2._c()
+        out = np.empty(s2.N if mode == BOW_KF_FRAME else s1.N, np.int32)
+        n = ctypes.c_int()
+        rc = _mlib().orbx_match_bow(self._ex._h, mode, ctypes.byref(a), ctypes.byref(b), None if tri is None else ctypes.byref(tri),
+                                    self.mfNNratio, int(self.mbCheckOrientation), 0, _np(out), ctypes.byref(n))
+        _chk(self._ex, rc, "orbx_match_bow")
+        return out, n.value
+
+    def SearchByBoW(self, kf, other, other_is_keyframe=False):
+        """SearchByBoW(KeyFrame*, Frame&, ..) src/ORBmatcher.cc:255 -> (vpMapPointMatches as KF feature index per F feature, n);
+        SearchByBoW(KeyFrame*, KeyFrame*, ..) :760 -> (vpMatches12 as KF2 feature index per KF1 feature, n)."""
+        return self._bow(BOW_KF_KF if other_is_keyframe else BOW_KF_FRAME, kf, other)
+
+    def SearchForTriangulation(self, kf1, kf2, F12, epipole, scale_factors2, level_sigma2_2, bOnlyStereo=False):
+        """src/ORBmatcher.cc:915 -> (vMatches12, n); matched pairs are (i, vMatches12[i]) for vMatches12[i] >= 0."""
+        t = _Triangulation()
+        F = np.ascontiguousarray(F12, np.float32).reshape(9)
+        for i in range(9):
+            t.F12[i] = float(F[i])
+        t.ex, t.ey = float(epipole[0]), float(epipole[1])
+        for i, (s, g) in enumerate(zip(scale_factors2, level_sigma2_2)):
+            t.scale2[i], t.sigma2_2[i] = float(s), float(g)
+        t.only_stereo = int(bOnlyStereo)
+        return self._bow(BOW_TRIANGULATE, kf1, kf2, t)
+
+    def SearchByProjection(self, frame, queries, grid, th_dist, occupied=None, ratio_same_level=False, check_uright=True,
+                           check_ori=None, grid_dims=(FRAME_GRID_COLS, FRAME_GRID_ROWS)):
+        """The window search shared by the four SearchByProjection overloads after their projection step.
+        queries: PROJ_QUERY_DTYPE array in the reference's point order; grid = (mnMinX, mnMinY, widthInv, heightInv).
+        Returns (assign, n): assign[i] = query matched to frame keypoint i or -1."""
+        q = np.ascontiguousarray(queries, PROJ_QUERY_DTYPE)
+        g = _Grid(float(grid[0]), float(grid[1]), float(grid[2]), float(grid[3]), grid_dims[0], grid_dims[1])
+        out = np.empty(frame.N, np.int32)
+        n = ctypes.c_int()
+        occ = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+        mode = (PROJ_RATIO_SAME_LEVEL if ratio_same_level else 0) | (PROJ_CHECK_URIGHT if check_uright and frame.uright is not None else 0)
+        co = self.mbCheckOrientation if check_ori is None else check_ori
+        rc = _mlib().orbx_search_by_projection(self._ex._h, _np(q), len(q), _np(frame.keys), _np(frame.desc), _np(frame.uright), frame.N,
+                                               ctypes.byref(g), _np(occ), mode, int(th_dist), self.mfNNratio, int(co), 0, _np(out),
+                                               ctypes.byref(n))
+        _chk(self._ex, rc, "orbx_search_by_projection")
+        return out, n.value
+
+
+def assign_features_to_grid(ex, keys, grid, grid_dims=(FRAME_GRID_COLS, FRAME_GRID_ROWS)):
+    """Frame::AssignFeaturesToGrid (src/Frame.cc:398-422) -> CSR (cell_off, cell_idx), cell = ix*rows + iy."""
+    keys = np.ascontiguousarray(keys, KP_DTYPE)
+    g = _Grid(float(grid[0]), float(grid[1]), float(grid[2]), float(grid[3]), grid_dims[0], grid_dims[1])
+    off = np.empty(grid_dims[0] * grid_dims[1] + 1, np.int32)
+    idx = np.empty(max(len(keys), 1), np.int32)
+    _chk(ex, _mlib().orbx_assign_grid(ex._h, _np(keys), len(keys), ctypes.byref(g), 0, _np(off), _np(idx)), "orbx_assign_grid")
+    return off, idx[:off[-1]].copy()
+
+
+def compute_stereo_matches(left, right, kps_l, desc_l, kps_r, desc_r, bf, b, frame=0):
+    """Frame::ComputeStereoMatches (src/Frame.cc:831-1128): left/right are the two ORBextractor objects that just
+    extracted kps_l / kps_r (their device pyramids are used).  Returns (mvuRight, mvDepth)."""
+    kps_l, kps_r = np.ascontiguousarray(kps_l, KP_DTYPE), np.ascontiguousarray(kps_r, KP_DTYPE)
+    desc_l, desc_r = np.ascontiguousarray(desc_l, np.uint8), np.ascontiguousarray(desc_r, np.uint8)
+    ur, z = np.empty(len(kps_l), np.float32), np.empty(len(kps_l), np.float32)
+    n = ctypes.c_int()
+    rc = _mlib().orbx_stereo_match(left._h, right._h, frame, _np(kps_l), _np(desc_l), len(kps_l), _np(kps_r), _np(desc_r), len(kps_r),
+                                   float(bf), float(b), 0, _np(ur), _np(z), ctypes.byref(n))
+    _chk(left, rc, "orbx_stereo_match")
+    return ur, z

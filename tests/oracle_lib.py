@@ -146,3 +146,174 @@ def extract(p, img, cap=None, want_pyr=False):
     if want_pyr:
         return kps[:n].copy(), desc[:n].copy(), pyr
     return kps[:n].copy(), desc[:n].copy()
+
+
+# ---------------------------------------------------------------- matcher side (oracle/orb_match.c)
+class Vocab(ctypes.Structure):
+    _fields_ = [("k", ctypes.c_int), ("L", ctypes.c_int), ("nnodes", ctypes.c_int), ("child_off", ctypes.c_void_p),
+                ("child", ctypes.c_void_p), ("desc", ctypes.c_void_p), ("word_id", ctypes.c_void_p), ("weight", ctypes.c_void_p)]
+
+
+class BowFrame(ctypes.Structure):
+    _fields_ = [("n", ctypes.c_int), ("desc", ctypes.c_void_p), ("keys", ctypes.c_void_p), ("valid", ctypes.c_void_p),
+                ("uright", ctypes.c_void_p), ("nnodes", ctypes.c_int), ("node_id", ctypes.c_void_p),
+                ("node_off", ctypes.c_void_p), ("feat", ctypes.c_void_p)]
+
+
+class Grid(ctypes.Structure):
+    _fields_ = [("min_x", ctypes.c_float), ("min_y", ctypes.c_float), ("inv_w", ctypes.c_float), ("inv_h", ctypes.c_float)]
+
+
+PROJ_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("ur", "<f4"), ("view_cos", "<f4"), ("angle", "<f4"), ("level", "<i4"),
+                       ("desc", "u1", (32,))])
+assert PROJ_DTYPE.itemsize == 56
+GRID_COLS, GRID_ROWS = 64, 48
+
+
+def _mlib():
+    L = lib()
+    if getattr(L, "_match_ready", False):
+        return L
+    vp, ci, cf = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
+    L.orc_three_maxima.argtypes = [vp, ci, vp, vp, vp]
+    L.orc_bow_transform.argtypes = [ctypes.POINTER(Vocab), vp, ci, ci, vp, vp, vp]
+    L.orc_feature_vector.argtypes = [vp, vp, ci, vp, vp, vp]
+    L.orc_search_by_bow_kf_f.argtypes = [ctypes.POINTER(BowFrame), ctypes.POINTER(BowFrame), cf, ci, vp]
+    L.orc_search_by_bow_kf_kf.argtypes = [ctypes.POINTER(BowFrame), ctypes.POINTER(BowFrame), cf, ci, vp]
+    L.orc_search_for_triangulation.argtypes = [ctypes.POINTER(BowFrame), ctypes.POINTER(BowFrame), vp, cf, cf, vp, vp, ci, ci, vp]
+    L.orc_assign_grid.argtypes = [vp, ci, ctypes.POINTER(Grid), vp, vp]
+    L.orc_features_in_area.argtypes = [vp, ctypes.POINTER(Grid), vp, vp, cf, cf, cf, ci, ci, vp]
+    L.orc_search_by_projection_points.argtypes = [vp, ci, vp, vp, ci, vp, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, cf, vp]
+    L.orc_search_by_projection_frame.argtypes = [vp, ci, vp, vp, ci, vp, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, ci, ci, vp]
+    L.orc_stereo_matches.argtypes = [vp, vp, ci, vp, vp, ci, vp, vp, vp, vp, vp, vp, vp, cf, cf, vp, vp]
+    L._match_ready = True
+    return L
+
+
+def three_maxima(counts):
+    counts = np.ascontiguousarray(counts, np.int32)
+    a, b, c = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    _mlib().orc_three_maxima(_p(counts), len(counts), ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
+    return a.value, b.value, c.value
+
+
+class VocabArrays:
+    """Flattened vocabulary tree (see orc_vocab)."""
+
+    def __init__(self, k, L, child_off, child, desc, word_id, weight):
+        self.k, self.L = k, L
+        self.child_off = np.ascontiguousarray(child_off, np.int32)
+        self.child = np.ascontiguousarray(child, np.int32)
+        self.desc = np.ascontiguousarray(desc, np.uint8)
+        self.word_id = np.ascontiguousarray(word_id, np.int32)
+        self.weight = np.ascontiguousarray(weight, np.float32)
+        self.nnodes = len(self.word_id)
+
+    def c(self):
+        return Vocab(self.k, self.L, self.nnodes, self.child_off.ctypes.data, self.child.ctypes.data, self.desc.ctypes.data,
+                     self.word_id.ctypes.data, self.weight.ctypes.data)
+
+
+def bow_transform(voc, desc, levelsup):
+    desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(desc)
+    word, weight, node = np.empty(n, np.int32), np.empty(n, np.float32), np.empty(n, np.int32)
+    v = voc.c()
+    _mlib().orc_bow_transform(ctypes.byref(v), _p(desc), n, levelsup, _p(word), _p(weight), _p(node))
+    return word, weight, node
+
+
+def feature_vector(node, weight):
+    n = len(node)
+    node = np.ascontiguousarray(node, np.int32)
+    weight = np.ascontiguousarray(weight, np.float32)
+    nid, noff, feat = np.empty(n + 1, np.int32), np.empty(n + 2, np.int32), np.empty(n + 1, np.int32)
+    nn = _mlib().orc_feature_vector(_p(node), _p(weight), n, _p(nid), _p(noff), _p(feat))
+    return nid[:nn].copy(), noff[:nn + 1].copy(), feat[:noff[nn]].copy()
+
+
+class Side:
+    """One (key)frame for the BoW matchers; keeps the numpy arrays alive."""
+
+    def __init__(self, desc, keys, valid, uright, node_id, node_off, feat):
+        self.desc = np.ascontiguousarray(desc, np.uint8)
+        self.keys = np.ascontiguousarray(keys)
+        self.valid = np.ascontiguousarray(valid, np.uint8)
+        self.uright = None if uright is None else np.ascontiguousarray(uright, np.float32)
+        self.node_id = np.ascontiguousarray(node_id, np.int32)
+        self.node_off = np.ascontiguousarray(node_off, np.int32)
+        self.feat = np.ascontiguousarray(feat, np.int32)
+
+    def c(self):
+        return BowFrame(len(self.desc), self.desc.ctypes.data, self.keys.ctypes.data, self.valid.ctypes.data,
+                        None if self.uright is None else self.uright.ctypes.data, len(self.node_id),
+                        self.node_id.ctypes.data, self.node_off.ctypes.data, self.feat.ctypes.data)
+
+
+def search_by_bow(s1, s2, nnratio, check_ori, kf_kf):
+    a, b = s1.c(), s2.c()
+    out = np.empty(len(s1.desc) if kf_kf else len(s2.desc), np.int32)
+    fn = _mlib().orc_search_by_bow_kf_kf if kf_kf else _mlib().orc_search_by_bow_kf_f
+    n = fn(ctypes.byref(a), ctypes.byref(b), nnratio, int(check_ori), _p(out))
+    return out, n
+
+
+def search_for_triangulation(s1, s2, F12, ex, ey, scale2, sigma2, only_stereo, check_ori):
+    a, b = s1.c(), s2.c()
+    F12 = np.ascontiguousarray(F12, np.float32).reshape(9)
+    scale2 = np.ascontiguousarray(scale2, np.float32)
+    sigma2 = np.ascontiguousarray(sigma2, np.float32)
+    out = np.empty(len(s1.desc), np.int32)
+    n = _mlib().orc_search_for_triangulation(ctypes.byref(a), ctypes.byref(b), _p(F12), ex, ey, _p(scale2), _p(sigma2),
+                                             int(only_stereo), int(check_ori), _p(out))
+    return out, n
+
+
+def assign_grid(keys, grid):
+    keys = np.ascontiguousarray(keys)
+    off = np.empty(GRID_COLS * GRID_ROWS + 1, np.int32)
+    idx = np.empty(max(len(keys), 1), np.int32)
+    g = Grid(*grid)
+    _mlib().orc_assign_grid(_p(keys), len(keys), ctypes.byref(g), _p(off), _p(idx))
+    return off, idx[:off[-1]].copy()
+
+
+def search_by_projection(pts, keys, desc, uright, scale, grid, occupied, th, nnratio=None, motion=0, check_ori=True):
+    """nnratio given -> SearchByProjection(Frame, MapPoints) (a15); else the Frame/Frame variant (a16)."""
+    pts = np.ascontiguousarray(pts)
+    keys = np.ascontiguousarray(keys)
+    desc = np.ascontiguousarray(desc, np.uint8)
+    scale = np.ascontiguousarray(scale, np.float32)
+    off, idx = assign_grid(keys, grid)
+    idx = np.ascontiguousarray(np.concatenate([idx, np.zeros(1, np.int32)]))
+    g = Grid(*grid)
+    out = np.empty(len(keys), np.int32)
+    ur = None if uright is None else np.ascontiguousarray(uright, np.float32)
+    occ = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+    if nnratio is not None:
+        n = _mlib().orc_search_by_projection_points(_p(pts), len(pts), _p(keys), _p(desc), len(keys), None if ur is None else _p(ur),
+                                                    _p(scale), ctypes.byref(g), _p(off), _p(idx), None if occ is None else _p(occ),
+                                                    th, nnratio, _p(out))
+    else:
+        n = _mlib().orc_search_by_projection_frame(_p(pts), len(pts), _p(keys), _p(desc), len(keys), None if ur is None else _p(ur),
+                                                   _p(scale), ctypes.byref(g), _p(off), _p(idx), None if occ is None else _p(occ),
+                                                   th, motion, int(check_ori), _p(out))
+    return out, n
+
+
+def stereo_matches(kL, dL, kR, dR, pyrL, pyrR, sizes, scale, inv_scale, mbf, mb):
+    kL, kR = np.ascontiguousarray(kL), np.ascontiguousarray(kR)
+    dL, dR = np.ascontiguousarray(dL, np.uint8), np.ascontiguousarray(dR, np.uint8)
+    w = np.array([s[0] for s in sizes], np.int32)
+    h = np.array([s[1] for s in sizes], np.int32)
+    off = np.zeros(len(sizes), np.uint64)
+    o = 0
+    for i, (a, b) in enumerate(sizes):
+        off[i] = o
+        o += a * b
+    scale = np.ascontiguousarray(scale, np.float32)
+    inv_scale = np.ascontiguousarray(inv_scale, np.float32)
+    ur, z = np.empty(len(kL), np.float32), np.empty(len(kL), np.float32)
+    n = _mlib().orc_stereo_matches(_p(kL), _p(dL), len(kL), _p(kR), _p(dR), len(kR), _p(pyrL), _p(pyrR), _p(w), _p(h), _p(off),
+                                   _p(scale), _p(inv_scale), mbf, mb, _p(ur), _p(z))
+    return ur, z, n

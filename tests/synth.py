@@ -52,3 +52,79 @@ def descriptors(seed, n, flip_p=None, base=None):
     bits = np.unpackbits(base[:n], axis=1)
     flips = (rng.random(bits.shape) < flip_p).astype(np.uint8)
     return np.packbits(bits ^ flips, axis=1)
+
+
+def vocabulary(seed, k=10, L=3):
+    """Synthetic DBoW2 tree in flattened form (child_off, child, desc, word_id, weight), node ids in the
+    ORBvoc text-file order used by the reference's own vocabularies (breadth-first creation order is not
+    required by the loader; we emit depth-first like DBoW2's saver).  Children are perturbed copies of their
+    parent so that descents are meaningful; a few leaves get weight 0 (stop words)."""
+    rng = np.random.default_rng(seed)
+    parent, desc, leaf = [-1], [np.zeros(32, np.uint8)], [0]
+
+    def grow(pid, level, base):
+        for _ in range(k):
+            bits = np.unpackbits(base)
+            flips = (rng.random(256) < (0.5 if level == 1 else 0.18)).astype(np.uint8)
+            d = np.packbits(bits ^ flips)
+            nid = len(parent)
+            parent.append(pid); desc.append(d); leaf.append(1 if level == L else 0)
+            if level < L:
+                grow(nid, level + 1, d)
+    grow(0, 1, rng.integers(0, 256, 32, dtype=np.uint8))
+    n = len(parent)
+    parent = np.array(parent)
+    off = np.zeros(n + 1, np.int32)
+    for i in range(1, n):
+        off[parent[i] + 1] += 1
+    off = np.cumsum(off).astype(np.int32)
+    fill = off[:-1].copy()
+    child = np.zeros(n - 1, np.int32)
+    for i in range(1, n):
+        child[fill[parent[i]]] = i
+        fill[parent[i]] += 1
+    word = np.zeros(n, np.int32)
+    weight = np.zeros(n, np.float32)
+    w = 0
+    for i in range(1, n):
+        if leaf[i]:
+            word[i] = w
+            w += 1
+            weight[i] = 0.0 if rng.random() < 0.02 else np.float32(rng.random() * 3 + 0.01)
+    return dict(k=k, L=L, child_off=off, child=child, desc=np.stack(desc), word_id=word, weight=weight, parent=parent, leaf=np.array(leaf))
+
+
+def vocabulary_text(v):
+    """ORBvoc text format (TemplatedVocabulary.h:1385-1487)."""
+    lines = [f"{v['k']} {v['L']} 0 0"]
+    for i in range(1, len(v["parent"])):
+        lines.append(f"{v['parent'][i]} {v['leaf'][i]} " + " ".join(str(int(b)) for b in v["desc"][i]) + f" {float(v['weight'][i])!r}")
+    return "\n".join(lines) + "\n"
+
+
+def keypoints(seed, n, w=640, h=480, nlevels=8, dtype=None):
+    """Random undistorted keypoints (x, y, angle, octave) for matcher tests."""
+    rng = np.random.default_rng(seed)
+    k = np.zeros(n, dtype)
+    k["x"] = (rng.random(n) * (w - 40) + 20).astype(np.float32)
+    k["y"] = (rng.random(n) * (h - 40) + 20).astype(np.float32)
+    k["angle"] = (rng.random(n) * 360).astype(np.float32)
+    k["octave"] = rng.integers(0, nlevels, n)
+    k["size"] = 31
+    k["class_id"] = -1
+    return k
+
+
+def stereo_pair(seed, w, h, max_disp=40):
+    """Rectified synthetic pair: the right image is the left one shifted by a disparity that is
+    constant inside 40-row bands (so corners survive), plus +-2 grey levels of noise."""
+    rng = np.random.default_rng(seed + 7919)
+    base = frame(seed, w + 2 * max_disp + 8, h)
+    left = np.ascontiguousarray(base[:, max_disp:max_disp + w])
+    right = np.empty_like(left)
+    for y0 in range(0, h, 40):
+        d = int(rng.integers(3, max_disp))
+        right[y0:y0 + 40] = base[y0:y0 + 40, max_disp + d:max_disp + d + w]
+    noise = rng.integers(-2, 3, size=right.shape)
+    right = np.clip(right.astype(np.int32) + noise, 0, 255).astype(np.uint8)
+    return left, np.ascontiguousarray(right)

@@ -1,0 +1,208 @@
+"""GPU parity of the Hamming side (through the C ABI) vs the CPU oracle (oracle/orb_match.c):
+DBoW2 transform, both SearchByBoW overloads, SearchForTriangulation, the window (projection) search,
+AssignFeaturesToGrid and ComputeStereoMatches.  Every output index must be identical."""
+import os
+import numpy as np
+import pytest
+import synth, oracle_lib as O
+from gpu_util import pkg
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def P():
+    return pkg()
+
+
+@pytest.fixture(scope="module")
+def ctx(P):
+    return P.ORBextractor(1000, 1.2, 8, 20, 7, max_w=64, max_h=64)
+
+
+def make_pair(seed, n1, n2, flip=0.08, dup=0.0, nlevels=8, KP=None):
+    """Two feature sets with true correspondences: set 2 = perturbed, shuffled subset of set 1 + random rest."""
+    rng = np.random.default_rng(seed)
+    d1 = synth.descriptors(seed, n1)
+    if dup > 0:  # many identical descriptors: forces claimed-entry handling and node rescans
+        src = rng.integers(0, max(1, int(n1 * (1 - dup))), n1)
+        d1 = d1[src]
+    m = min(n1, n2) * 3 // 4
+    pick = rng.permutation(n1)[:m]
+    d2 = np.concatenate([synth.descriptors(seed + 1, m, flip, d1[pick]), synth.descriptors(seed + 2, n2 - m)])
+    k1 = synth.keypoints(seed + 3, n1, dtype=KP)
+    k2 = synth.keypoints(seed + 4, n2, dtype=KP)
+    rot = np.float32(37.5)
+    k2["angle"][:m] = np.mod(k1["angle"][pick] - rot + rng.normal(0, 3, m).astype(np.float32), np.float32(360)).astype(np.float32)
+    k2["x"][:m] = k1["x"][pick] + rng.normal(0, 2, m).astype(np.float32)
+    k2["y"][:m] = k1["y"][pick] + rng.normal(0, 2, m).astype(np.float32)
+    k2["octave"][:m] = k1["octave"][pick]
+    perm = rng.permutation(n2)
+    return d1, k1, d2[perm], k2[perm]
+
+
+def sides(P, voc_o, voc_g, d1, k1, d2, k2, levelsup, seed, p_has=0.7, stereo=False):
+    rng = np.random.default_rng(seed)
+    out_o, out_g = [], []
+    for d, k in ((d1, k1), (d2, k2)):
+        w, wt, nd = O.bow_transform(voc_o, d, levelsup)
+        gw, gwt, gnd = voc_g.transform(d, levelsup)
+        assert np.array_equal(w, gw) and np.array_equal(nd, gnd) and np.array_equal(wt.view(np.uint32), gwt.view(np.uint32))
+        nid, noff, feat = O.feature_vector(nd, wt)
+        gnid, gnoff, gfeat = P.feature_vector(gnd, gwt)
+        assert np.array_equal(nid, gnid) and np.array_equal(noff, gnoff) and np.array_equal(feat, gfeat)
+        has = (rng.random(len(d)) < p_has).astype(np.uint8)
+        ur = None
+        if stereo:
+            ur = np.where(rng.random(len(d)) < 0.5, k["x"] - 5, -1).astype(np.float32)
+        out_o.append(O.Side(d, k, has, ur, nid, noff, feat))
+        out_g.append(P.FrameView(d, k, has, ur, nid, noff, feat))
+    return out_o, out_g
+
+
+@pytest.fixture(scope="module")
+def vocs(P, ctx):
+    v = synth.vocabulary(0, 10, 3)
+    vo = O.VocabArrays(v["k"], v["L"], v["child_off"], v["child"], v["desc"], v["word_id"], v["weight"])
+    vg = P.Vocabulary(ctx, v["k"], v["L"], v["child_off"], v["child"], v["desc"], v["word_id"], v["weight"])
+    return v, vo, vg
+
+
+def test_vocab_text_loader_and_transform(P, ctx, vocs, tmp_path):
+    v, vo, vg = vocs
+    path = tmp_path / "voc.txt"
+    path.write_text(synth.vocabulary_text(v))
+    vt = P.Vocabulary(ctx, path=str(path))
+    assert vt.info() == vg.info() == (10, 3, 1111, 1000)
+    d = synth.descriptors(5, 3000)
+    for levelsup in (0, 1, 2, 3, 4):
+        a = O.bow_transform(vo, d, levelsup)
+        b = vg.transform(d, levelsup)
+        c = vt.transform(d, levelsup)
+        for x, y, z in zip(a, b, c):
+            assert np.array_equal(x.view(np.uint32), y.view(np.uint32)) and np.array_equal(y.view(np.uint32), z.view(np.uint32))
+
+
+CASES = [(1, 1500, 1400, 0.08, 0.0, 1), (2, 2000, 2000, 0.12, 0.0, 2), (3, 1200, 900, 0.05, 0.6, 1), (4, 700, 1800, 0.10, 0.3, 3),
+         (5, 3000, 3000, 0.10, 0.0, 4), (6, 40, 35, 0.05, 0.0, 2), (7, 2500, 2500, 0.02, 0.9, 3)]
+
+
+@pytest.mark.parametrize("seed,n1,n2,flip,dup,levelsup", CASES)
+@pytest.mark.parametrize("kf_kf", [False, True])
+def test_search_by_bow_matches_oracle(P, ctx, vocs, seed, n1, n2, flip, dup, levelsup, kf_kf):
+    _, vo, vg = vocs
+    d1, k1, d2, k2 = make_pair(seed, n1, n2, flip, dup, KP=P.KP_DTYPE)
+    so, sg = sides(P, vo, vg, d1, k1, d2, k2, levelsup, seed)
+    for nnratio, ori in ((0.7, True), (0.9, False), (0.75, True)):
+        want, nw = O.search_by_bow(so[0], so[1], nnratio, ori, kf_kf)
+        got, ng = P.ORBmatcher(ctx, nnratio, ori).SearchByBoW(sg[0], sg[1], kf_kf)
+        assert np.array_equal(want, got), (int((want != got).sum()), nw, ng)
+        assert nw == ng
+    assert nw > 0 or n1 < 100
+
+
+@pytest.mark.parametrize("seed,n1,n2,flip,dup,levelsup", CASES)
+@pytest.mark.parametrize("only_stereo", [False, True])
+def test_search_for_triangulation_matches_oracle(P, ctx, vocs, seed, n1, n2, flip, dup, levelsup, only_stereo):
+    _, vo, vg = vocs
+    d1, k1, d2, k2 = make_pair(seed + 100, n1, n2, flip, dup, KP=P.KP_DTYPE)
+    so, sg = sides(P, vo, vg, d1, k1, d2, k2, levelsup, seed, p_has=0.4, stereo=True)
+    # a fundamental matrix for a near-pure horizontal translation: epipolar lines ~ horizontal through kp1.y
+    F12 = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32) + np.float32(1e-4) * np.random.default_rng(seed).normal(size=(3, 3)).astype(np.float32)
+    p = O.params(1000)
+    scale = np.array(p.scale[:8], np.float32)
+    sigma2 = np.array(p.sigma2[:8], np.float32)
+    sc16 = np.zeros(16, np.float32); sc16[:8] = scale
+    sg16 = np.zeros(16, np.float32); sg16[:8] = sigma2 * 9  # loose enough that the +-2 px jitter passes sometimes
+    want, nw = O.search_for_triangulation(so[0], so[1], F12, 300.0, 200.0, sc16, sg16, only_stereo, True)
+    got, ng = P.ORBmatcher(ctx, 0.6, True).SearchForTriangulation(sg[0], sg[1], F12, (300.0, 200.0), sc16, sg16, only_stereo)
+    assert np.array_equal(want, got), (int((want != got).sum()), nw, ng)
+    assert nw == ng
+
+
+def test_assign_grid_matches_oracle(P, ctx):
+    for seed, n in ((1, 1000), (2, 4000), (3, 0), (4, 17)):
+        k = synth.keypoints(seed, n, 640, 480, dtype=P.KP_DTYPE)
+        if n:
+            k["x"][:3] = [-5, 700, 320]  # outside the grid -> dropped
+        grid = (0.0, 0.0, np.float32(64) / np.float32(640), np.float32(48) / np.float32(480))
+        off, idx = O.assign_grid(k, grid)
+        goff, gidx = P.assign_features_to_grid(ctx, k, grid)
+        assert np.array_equal(off, goff) and np.array_equal(idx, gidx)
+
+
+def proj_scene(P, seed, n, nq):
+    rng = np.random.default_rng(seed)
+    keys = synth.keypoints(seed, n, 640, 480, dtype=P.KP_DTYPE)
+    desc = synth.descriptors(seed + 1, n)
+    src = rng.integers(0, n, nq)
+    pts = np.zeros(nq, O.PROJ_DTYPE)
+    pts["u"] = keys["x"][src] + rng.normal(0, 3, nq).astype(np.float32)
+    pts["v"] = keys["y"][src] + rng.normal(0, 3, nq).astype(np.float32)
+    pts["u"][:4] = [-30, 900, 100, 320]; pts["v"][:4] = [100, 100, -50, 700]
+    pts["level"] = np.clip(keys["octave"][src] + rng.integers(-1, 2, nq), 0, 7)
+    pts["view_cos"] = np.where(rng.random(nq) < 0.5, 0.9995, 0.9).astype(np.float32)
+    pts["angle"] = np.mod(keys["angle"][src] + 20 + rng.normal(0, 4, nq), 360).astype(np.float32)
+    pts["desc"] = synth.descriptors(seed + 2, nq, 0.12, desc[src])
+    uright = np.where(rng.random(n) < 0.6, keys["x"] - 8, -1).astype(np.float32)
+    pts["ur"] = pts["u"] - 8 + rng.normal(0, 6, nq).astype(np.float32)
+    occupied = (rng.random(n) < 0.1).astype(np.uint8)
+    return keys, desc, uright, occupied, pts
+
+
+@pytest.mark.parametrize("seed,n,nq", [(1, 1000, 600), (2, 2000, 2500), (3, 300, 50), (4, 4000, 4000)])
+def test_search_by_projection_matches_oracle(P, ctx, seed, n, nq):
+    keys, desc, uright, occupied, pts = proj_scene(P, seed, n, nq)
+    p = O.params(1000)
+    scale = np.array(p.scale[:8], np.float32)
+    grid = (0.0, 0.0, np.float32(64) / np.float32(640), np.float32(48) / np.float32(480))
+    fv = P.FrameView(desc, keys, None, uright)
+    # (a15) SearchByProjection(Frame, MapPoints, th): src/ORBmatcher.cc:78-191
+    for th, nnratio in ((1.0, 0.8), (3.0, 0.8), (5.0, 0.6)):
+        want, nw = O.search_by_projection(pts, keys, desc, uright, scale, grid, occupied, th, nnratio=nnratio)
+        q = np.zeros(nq, P.PROJ_QUERY_DTYPE)
+        r = np.where(pts["view_cos"] > np.float32(0.998), np.float32(2.5), np.float32(4.0)).astype(np.float32)
+        if th != 1.0:
+            r = (r * np.float32(th)).astype(np.float32)
+        q["u"], q["v"], q["ur"], q["angle"], q["desc"] = pts["u"], pts["v"], pts["ur"], pts["angle"], pts["desc"]
+        q["radius"] = (r * scale[pts["level"]]).astype(np.float32)
+        q["min_level"], q["max_level"] = pts["level"] - 1, pts["level"]
+        got, ng = P.ORBmatcher(ctx, nnratio, True).SearchByProjection(fv, q, grid, 100, occupied, ratio_same_level=True, check_ori=False)
+        assert np.array_equal(want, got), (th, int((want != got).sum()), nw, ng)
+        assert nw == ng
+    # (a16) SearchByProjection(Frame, Frame, th, mono): src/ORBmatcher.cc:1741-1910
+    for th, motion in ((15.0, 0), (7.0, 1), (15.0, 2)):
+        want, nw = O.search_by_projection(pts, keys, desc, uright, scale, grid, occupied, th, motion=motion, check_ori=True)
+        q = np.zeros(nq, P.PROJ_QUERY_DTYPE)
+        q["u"], q["v"], q["ur"], q["angle"], q["desc"] = pts["u"], pts["v"], pts["ur"], pts["angle"], pts["desc"]
+        q["radius"] = (np.float32(th) * scale[pts["level"]]).astype(np.float32)
+        if motion == 1:
+            q["min_level"], q["max_level"] = pts["level"], -1
+        elif motion == 2:
+            q["min_level"], q["max_level"] = 0, pts["level"]
+        else:
+            q["min_level"], q["max_level"] = pts["level"] - 1, pts["level"] + 1
+        got, ng = P.ORBmatcher(ctx, 0.9, True).SearchByProjection(fv, q, grid, 100, occupied)
+        assert np.array_equal(want, got), (th, motion, int((want != got).sum()), nw, ng)
+        assert nw == ng and nw > 0
+
+
+@pytest.mark.parametrize("w,h,nf,seed", [(752, 480, 1200, 3), (1241, 376, 2000, 4)])
+def test_stereo_matches_oracle(P, w, h, nf, seed):
+    left, right = synth.stereo_pair(seed, w, h)
+    exl = P.ORBextractor(nf, 1.2, 8, 20, 7, max_w=w, max_h=h)
+    exr = P.ORBextractor(nf, 1.2, 8, 20, 7, max_w=w, max_h=h)
+    kl, dl = exl(left)
+    kr, dr = exr(right)
+    p = O.params(nf)
+    okl, odl, pyl = O.extract(p, left, want_pyr=True)
+    okr, odr, pyr = O.extract(p, right, want_pyr=True)
+    assert np.array_equal(kl, okl) and np.array_equal(kr, okr)
+    sizes = O.level_sizes(p, w, h)
+    bf, b = 386.1448, 386.1448 / 718.856  # Examples/Stereo/KITTI00-02.yaml: Camera.bf, fx -> mb = mbf / fx
+    want_u, want_z, nv = O.stereo_matches(okl, odl, okr, odr, pyl, pyr, sizes, np.array(p.scale[:8], np.float32),
+                                          np.array(p.inv_scale[:8], np.float32), bf, b)
+    got_u, got_z = P.compute_stereo_matches(exl, exr, kl, dl, kr, dr, bf, b)
+    assert np.array_equal(want_u.view(np.uint32), got_u.view(np.uint32)), int((want_u != got_u).sum())
+    assert np.array_equal(want_z.view(np.uint32), got_z.view(np.uint32))
+    assert (got_u >= 0).sum() > 100, (int((got_u >= 0).sum()), nv)
