@@ -1,58 +1,100 @@
 // K2 -- per-cell FAST-9/16 with the iniThFAST -> minThFAST retry
 // (ComputeKeyPointsOctTree cell loop, src/ORBextractor.cc:1058-1153; cv::FAST(roi, th, nms=true)).
 //
-// One CTA per (cell, frame); all levels of all frames in ONE launch (cell table in GeomSet).
-//   phase 0  stage the (wCell+6) x (hCell+6) tile in shared memory (coalesced row loads)
-//   phase 1  every candidate pixel: 16-bit brighter/darker ring masks at minTh, 9-contiguous test;
-//            corners are compacted into a shared list (no divergent heavy work)
-//   phase 2  list entries: exact OpenCV cornerScore (max over the 16 arcs of the arc's min margin, -1),
-//            which does not depend on the threshold for a detected corner -> u8 score map with a zero apron
-//   phase 3  3x3 strict-> NMS inside the cell only (neighbours outside the cell's candidate region count 0,
-//            exactly like the per-ROI cv::FAST calls), count survivors with score >= iniTh;
-//            the cell keeps {survivors >= iniTh} if that set is non-empty, else all survivors (the retry).
+// One CTA per STRIP = one cell-row of one level of one frame, split into segments of whole cells so the tile fits in
+// shared memory; all levels and frames in ONE launch.  The candidate regions of the reference's cells tile the
+// detection window without overlap, the FAST score does not depend on the threshold for a detected corner, and NMS at
+// iniTh equals {NMS survivors at minTh with score >= iniTh}; so one pass at minTh serves both thresholds and the
+// per-cell retry (:1128) becomes a per-cell choice between two subsets of the same survivors.
+//   stage   rows of the strip (+3 px apron) are brought into shared memory with 1-D bulk async copies
+//           (cp.async.bulk -> UBLKCP, completion on an mbarrier); plain loads when the source is not 16-byte aligned
+//   phase 1 4 pixels per thread step, byte-parallel in 32-bit registers: brighter/darker flags of the 16 ring pixels
+//           by SWAR unsigned-byte compares (3 LOP3/IADD per flag word), 9-contiguity as bit-sliced AND/OR trees
+//           (no per-pixel branches, no divergence); corners are appended to a shared list
+//   phase 2 list entries: exact OpenCV cornerScore (max over the 16 arcs of the arc's min margin, -1) -> u8 score map
+//   phase 3 3x3 strict-> NMS inside the pixel's own cell (neighbours outside the cell count 0, exactly like the per-ROI
+//           cv::FAST calls), per-cell counts of survivors and of survivors >= iniTh
+//   phase 4 emit: a cell keeps {survivors >= iniTh} if that set is non-empty, else all survivors (the retry)
 // Output records are order-independent: key = (cell, ly, lx) reproduces the reference's push_back order
 // (cell-row-major, then pixel-row-major :1084-1149) whenever an ordered view is needed.
 #include "orbx_internal.h"
 
 namespace orbx {
 
-__device__ __forceinline__ bool nineContiguous(uint32_t m16)
+constexpr int kFastThreads = 256;
+constexpr int kCornerCap = 2048;                 // pixels per row chunk (and capacity of a corner list)
+constexpr int kGroupCap = kCornerCap / 4;        // 4-pixel groups per row chunk
+constexpr int kMaxCellsPerStrip = 32;
+constexpr int kStripMaxWidth = 320;              // candidate columns per strip (host: cellsPerSeg)
+
+__device__ __forceinline__ uint32_t smemAddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// per-byte unsigned a > b, result in bit 7 of each byte (other bits undefined); nb7 = ~b & 0x7f7f7f7f
+__device__ __forceinline__ uint32_t gtu4(uint32_t a, uint32_t b, uint32_t nb7)
 {
-    uint32_t m = m16 | (m16 << 16);
-    uint32_t a = m & (m >> 1);
-    a &= a >> 2;
-    a &= a >> 4;      // runs of 8
-    a &= m >> 8;      // runs of 9
-    return (a & 0xffffu) != 0;
+    const uint32_t x = (a & 0x7f7f7f7fu) + nb7;
+    return (a & ~b) | (~(a ^ b) & x);
+}
+// per-byte unsigned a < b; b7 = b & 0x7f7f7f7f
+__device__ __forceinline__ uint32_t ltu4(uint32_t a, uint32_t b, uint32_t b7)
+{
+    const uint32_t x = b7 + (~a & 0x7f7f7f7fu);
+    return (b & ~a) | (~(a ^ b) & x);
 }
 
-constexpr int kFastThreads = 256;
-
-__global__ void __launch_bounds__(kFastThreads)
-fastCellsKernel(const GeomSet* __restrict__ G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
-                const uint8_t* __restrict__ pyr, unsigned long long* __restrict__ cand, int* __restrict__ candCount,
-                int tilePitchMax)
+__device__ __forceinline__ uint32_t nineOfSixteen(const uint32_t (&f)[16])
 {
-    extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ int sListN, sNms, sIni, sBase;
-    __shared__ int sLevel;
+    uint32_t a3[16];
+    #pragma unroll
+    for (int k = 0; k < 16; ++k) a3[k] = f[k] & f[(k + 1) & 15] & f[(k + 2) & 15];
+    uint32_t r = 0;
+    #pragma unroll
+    for (int k = 0; k < 16; ++k) r |= a3[k] & a3[(k + 3) & 15] & a3[(k + 6) & 15];
+    return r;
+}
+
+// bit 7 flags of the bytes whose candidate column lx0 + b lies in [0, rw)
+__device__ __forceinline__ uint32_t validBytes(int lx0, int rw)
+{
+    uint32_t m = 0x80808080u;
+    if (lx0 < 0) m = lx0 <= -4 ? 0u : m & (0xffffffffu << (8 * -lx0));
+    if (lx0 + 3 >= rw) { const int k = lx0 + 4 - rw; m = k >= 4 ? 0u : m & (0xffffffffu >> (8 * k)); }
+    return m;
+}
+
+// warp-aggregated append of `cnt` items per lane; returns the lane's first slot
+__device__ __forceinline__ int warpAppend(int* counter, int cnt)
+{
+    const int lane = threadIdx.x & 31;
+    int incl = cnt;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    int base = 0;
+    if (lane == 31) base = atomicAdd(counter, total);
+    base = __shfl_sync(0xffffffffu, base, 31);
+    return base + incl - cnt;
+}
+
+__global__ void __launch_bounds__(kFastThreads, 3)
+fastStripKernel(const GeomSet* __restrict__ G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
+                const uint8_t* __restrict__ pyr, unsigned long long* __restrict__ cand, int* __restrict__ candCount,
+                int tilePitchMax, int tileRowsMax, int scorePitchMax)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) unsigned long long sBar;
+    __shared__ int sGroupN, sCornerN[2], sOutN, sBase;
+    __shared__ int sNms[kMaxCellsPerStrip], sIni[kMaxCellsPerStrip];
 
     const int frame = blockIdx.y;
-    // locate level of this cell (<= 16 levels: linear scan by one thread)
-    if (threadIdx.x == 0) {
-        int l = 0;
-        const int cell = blockIdx.x;
-        while (l + 1 < G->nlevels && cell >= G->lv[l + 1].cellBase) ++l;
-        sLevel = l; sListN = 0; sNms = 0; sIni = 0;
-    }
-    __syncthreads();
-    const int level = sLevel;
+    int level = 0;
+    while (level + 1 < G->nlevels && (int)blockIdx.x >= G->lv[level + 1].stripBase) ++level;
     const LevelGeom& g = G->lv[level];
-    const int cellIdx = blockIdx.x - g.cellBase;
-    const int ci = cellIdx / g.nCols, cj = cellIdx - ci * g.nCols;
-    // candidate region in level coordinates
-    const int cx0 = kEdge + cj * g.wCell, cy0 = kEdge + ci * g.hCell;
-    const int cx1 = min(cx0 + g.wCell, g.w - kEdge), cy1 = min(cy0 + g.hCell, g.h - kEdge);
+    const int sIdx = blockIdx.x - g.stripBase;
+    const int ci = sIdx / g.segsPerRow, seg = sIdx - ci * g.segsPerRow;
+    const int j0 = seg * g.cellsPerSeg, j1 = min(j0 + g.cellsPerSeg, g.nCols);
+    const int cx0 = kEdge + j0 * g.wCell, cy0 = kEdge + ci * g.hCell;
+    const int cx1 = min(kEdge + j1 * g.wCell, g.w - kEdge), cy1 = min(cy0 + g.hCell, g.h - kEdge);
     const int rw = cx1 - cx0, rh = cy1 - cy0;
     if (rw <= 0 || rh <= 0) return; // skipped cells (:1094,:1112) have an empty candidate region
 
@@ -60,129 +102,250 @@ fastCellsKernel(const GeomSet* __restrict__ G, const uint8_t* __restrict__ lvl0,
     if (level == 0) { img = lvl0 + (size_t)frame * lvl0Frame; pitch = lvl0Pitch; }
     else { img = pyr + g.planeOff + (size_t)frame * g.pitch * g.h; pitch = (size_t)g.pitch; }
 
-    const int tw = rw + 6, th = rh + 6;
-    const int tp = tilePitchMax;                       // shared tile pitch (bytes)
-    uint8_t* tile = smem;                              // th x tp
-    uint8_t* score = smem + (size_t)tp * (g.hCell + 6); // (rh+2) x sp, zero apron
-    const int sp = g.wCell + 2;
-    uint16_t* list = reinterpret_cast<uint16_t*>(score + (((size_t)sp * (g.hCell + 2) + 15) & ~(size_t)15));
+    const int TP = tilePitchMax, SP = scorePitchMax;               // bytes per tile / score row
+    uint8_t* tile = smem;                                           // (rh + 6) rows
+    uint8_t* score = smem + (size_t)TP * tileRowsMax;               // (rh + 2) x SP, zero apron
+    uint32_t* nmsBits = reinterpret_cast<uint32_t*>(score + (size_t)SP * (tileRowsMax - 4));
+    uint16_t* cornerList = reinterpret_cast<uint16_t*>(nmsBits + ((tileRowsMax - 6) * SP + 31) / 32 + 1); // 2 x kCornerCap
+    uint16_t* groupList = cornerList + 2 * kCornerCap;              // kGroupCap
+    uint8_t* colCell = reinterpret_cast<uint8_t*>(groupList + kGroupCap); // SP entries: cell column of candidate column lx
+    const int TH = rh + 6;
+    const bool aligned = ((((size_t)img) | pitch) & 15) == 0;
+    const int xa = aligned ? ((cx0 - 4) & ~15) : (cx0 - 4) & ~3;    // image column of tile column 0 (>= 4 px left of cx0)
+    const int off0 = cx0 - xa;                                      // tile column of the first candidate pixel (>= 4)
 
-    // phase 0: tile + zeroed score map
-    for (int i = threadIdx.x; i < tw * th; i += kFastThreads) {
-        const int y = i / tw, x = i - y * tw;
-        tile[y * tp + x] = img[(size_t)(cy0 - 3 + y) * pitch + (cx0 - 3 + x)];
+    if (threadIdx.x == 0) { sGroupN = 0; sCornerN[0] = 0; sCornerN[1] = 0; sOutN = 0; }
+    if (threadIdx.x < kMaxCellsPerStrip) { sNms[threadIdx.x] = 0; sIni[threadIdx.x] = 0; }
+    if (aligned) {
+        const int xb = min((cx1 + 3 + 15) & ~15, (int)pitch);
+        const uint32_t rowBytes = (uint32_t)(xb - xa);
+        const uint32_t bar = smemAddr(&sBar);
+        if (threadIdx.x == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+        if (threadIdx.x == 0)
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(rowBytes * (uint32_t)TH) : "memory");
+        if ((int)threadIdx.x < TH) {
+            const uint8_t* src = img + (size_t)(cy0 - 3 + threadIdx.x) * pitch + xa;
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                         ::"r"(smemAddr(tile + (size_t)threadIdx.x * TP)), "l"(src), "r"(rowBytes), "r"(bar) : "memory");
+        }
+    } else {
+        const int tw = min(cx1 + 3, (int)g.w) - xa;
+        for (int i = threadIdx.x; i < TH * tw; i += kFastThreads) {
+            const int y = i / tw, x = i - y * tw;
+            tile[y * TP + x] = img[(size_t)(cy0 - 3 + y) * pitch + xa + x];
+        }
     }
-    for (int i = threadIdx.x; i < sp * (rh + 2); i += kFastThreads) score[i] = 0;
+    // zero the score map and NMS bitmap, build the column table while the copies are in flight
+    {
+        uint32_t* z = reinterpret_cast<uint32_t*>(score);
+        const int nz = (SP * (rh + 2) + 3) / 4;
+        for (int i = threadIdx.x; i < nz; i += kFastThreads) z[i] = 0;
+        const int nb = (rh * SP + 31) / 32 + 1;
+        for (int i = threadIdx.x; i < nb; i += kFastThreads) nmsBits[i] = 0;
+        for (int i = threadIdx.x; i < rw; i += kFastThreads) colCell[i] = (uint8_t)(i / g.wCell);
+    }
+    if (aligned) {
+        const uint32_t bar = smemAddr(&sBar);
+        uint32_t done = 0;
+        while (!done)
+            asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                         : "=r"(done) : "r"(bar) : "memory");
+    }
     __syncthreads();
 
-    const int o[16] = {3 * tp, 3 * tp + 1, 2 * tp + 2, tp + 3, 3, -tp + 3, -2 * tp + 2, -3 * tp + 1,
-                       -3 * tp, -3 * tp - 1, -2 * tp - 2, -tp - 3, -3, tp - 3, 2 * tp - 2, 3 * tp - 1};
     const int tmin = G->minTh, tini = G->iniTh;
+    const uint32_t T4 = (uint32_t)tmin * 0x01010101u;
+    const int g0 = off0 >> 2, g1 = (off0 + rw + 3) >> 2;            // word columns holding candidate pixels
+    const int ng = g1 - g0;
+    const int wp = TP >> 2;
+    const int wCell = g.wCell;
+    const uint32_t* W = reinterpret_cast<const uint32_t*>(tile);
+    const int o[16] = {3 * TP, 3 * TP + 1, 2 * TP + 2, TP + 3, 3, -TP + 3, -2 * TP + 2, -3 * TP + 1,
+                       -3 * TP, -3 * TP - 1, -2 * TP - 2, -TP - 3, -3, TP - 3, 2 * TP - 2, 3 * TP - 1};
+    const int rowsPerChunk = max(1, kCornerCap / (ng * 4));
 
-    // phase 1: corner test at minTh
-    for (int i = threadIdx.x; i < rw * rh; i += kFastThreads) {
-        const int ly = i / rw, lx = i - ly * rw;
-        const uint8_t* c = tile + (ly + 3) * tp + (lx + 3);
-        const int v = c[0];
-        const int lo = v - tmin, hi = v + tmin;
-        // any 9-arc contains ring pixel k or k+8: two cheap rejections first
-        int p0 = c[o[0]], p8 = c[o[8]];
-        if (!((p0 > hi) | (p0 < lo) | (p8 > hi) | (p8 < lo))) continue;
-        int p4 = c[o[4]], p12 = c[o[12]];
-        if (!((p4 > hi) | (p4 < lo) | (p12 > hi) | (p12 < lo))) continue;
-        uint32_t br = 0, dk = 0;
-        #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            const int p = c[o[k]];
-            br |= (uint32_t)(p > hi) << k;
-            dk |= (uint32_t)(p < lo) << k;
+    // NMS of one corner-list buffer (strict >, 8 neighbours, zero outside the pixel's own cell)
+    auto nmsPass = [&](const uint16_t* lst, int n) {
+        for (int i = threadIdx.x; i < n; i += kFastThreads) {
+            const int code = lst[i], ly = code >> 10, lx = code & 1023;
+            const uint8_t* r = score + (ly + 1) * SP + (lx + 1);
+            const int s = r[0];
+            const int cj = colCell[lx], cx = lx - cj * wCell;
+            bool keep = s > r[-SP] && s > r[SP];
+            if (cx > 0) keep = keep && s > r[-1] && s > r[-SP - 1] && s > r[SP - 1];
+            if (cx < wCell - 1) keep = keep && s > r[1] && s > r[-SP + 1] && s > r[SP + 1];
+            if (keep) {
+                atomicAdd(&sNms[cj], 1);
+                if (s >= tini) atomicAdd(&sIni[cj], 1);
+                atomicOr(&nmsBits[(ly * SP + lx) >> 5], 1u << ((ly * SP + lx) & 31));
+            }
         }
-        if (nineContiguous(br) || nineContiguous(dk)) {
-            const int slot = atomicAdd(&sListN, 1);
-            list[slot] = (uint16_t)(ly * 64 + lx);
+    };
+
+    int cur = 0, nPrev = 0;
+    for (int yc = 0; yc < rh; yc += rowsPerChunk, cur ^= 1) {
+        const int yEnd = min(rh, yc + rowsPerChunk);
+        const int nGroups = (yEnd - yc) * ng;
+        // ---- pass 0: quick rejection, 4 pixels per step.  A 9-arc contains two adjacent compass pixels, i.e. one of
+        //      {0, 8} and one of {4, 12}, all brighter or all darker. ----
+        for (int ib = 0; ib < nGroups; ib += kFastThreads) {      // uniform trip count: full-warp votes below
+            const int i = ib + threadIdx.x;
+            uint32_t q = 0; int code = 0;
+            if (i < nGroups) {
+                const int yy = i / ng, gg = i - yy * ng;
+                const int y = yc + yy, gw = g0 + gg;
+                const uint32_t* c = W + (y + 3) * wp + gw;
+                const uint32_t v = c[0], up = c[-3 * wp], dn = c[3 * wp];
+                const uint32_t p4 = __funnelshift_r(v, c[1], 24), p12 = __funnelshift_r(c[-1], v, 8);
+                const uint32_t hi = __vaddus4(v, T4), lo = __vsubus4(v, T4);
+                const uint32_t nh7 = ~hi & 0x7f7f7f7fu, lo7 = lo & 0x7f7f7f7fu;
+                const uint32_t b = (gtu4(dn, hi, nh7) | gtu4(up, hi, nh7)) & (gtu4(p4, hi, nh7) | gtu4(p12, hi, nh7));
+                const uint32_t d = (ltu4(dn, lo, lo7) | ltu4(up, lo, lo7)) & (ltu4(p4, lo, lo7) | ltu4(p12, lo, lo7));
+                q = (b | d) & validBytes(gw * 4 - off0, rw);
+                code = (y << 10) | gw;
+            }
+            if (__any_sync(0xffffffffu, q != 0)) {
+                const int slot = warpAppend(&sGroupN, q != 0);
+                if (q) groupList[slot] = (uint16_t)code;
+            }
         }
+        __syncthreads();
+        // ---- pass 1: full test of the surviving groups: brighter/darker flags of the 16 ring pixels, 9-contiguity ----
+        const int nG = sGroupN;
+        for (int ib = 0; ib < nG; ib += kFastThreads) {
+            const int i = ib + threadIdx.x;
+            uint32_t nib = 0; int y = 0, lx0 = 0;
+            if (i < nG) {
+                const int code = groupList[i], gw = code & 1023;
+                y = code >> 10; lx0 = gw * 4 - off0;
+                const uint32_t* c = W + (y + 3) * wp + gw;
+                uint32_t a[7][3];
+                #pragma unroll
+                for (int r = 0; r < 7; ++r) { a[r][0] = c[(r - 3) * wp - 1]; a[r][1] = c[(r - 3) * wp]; a[r][2] = c[(r - 3) * wp + 1]; }
+                const uint32_t v = a[3][1];
+                const uint32_t hi = __vaddus4(v, T4), lo = __vsubus4(v, T4);    // min(v + t, 255), max(v - t, 0) per byte
+                const uint32_t nh7 = ~hi & 0x7f7f7f7fu, lo7 = lo & 0x7f7f7f7fu;
+                uint32_t p[16];
+                p[0] = a[6][1];                                   // ( 0, 3)
+                p[1] = __funnelshift_r(a[6][1], a[6][2], 8);      // ( 1, 3)
+                p[2] = __funnelshift_r(a[5][1], a[5][2], 16);     // ( 2, 2)
+                p[3] = __funnelshift_r(a[4][1], a[4][2], 24);     // ( 3, 1)
+                p[4] = __funnelshift_r(a[3][1], a[3][2], 24);     // ( 3, 0)
+                p[5] = __funnelshift_r(a[2][1], a[2][2], 24);     // ( 3,-1)
+                p[6] = __funnelshift_r(a[1][1], a[1][2], 16);     // ( 2,-2)
+                p[7] = __funnelshift_r(a[0][1], a[0][2], 8);      // ( 1,-3)
+                p[8] = a[0][1];                                   // ( 0,-3)
+                p[9] = __funnelshift_r(a[0][0], a[0][1], 24);     // (-1,-3)
+                p[10] = __funnelshift_r(a[1][0], a[1][1], 16);    // (-2,-2)
+                p[11] = __funnelshift_r(a[2][0], a[2][1], 8);     // (-3,-1)
+                p[12] = __funnelshift_r(a[3][0], a[3][1], 8);     // (-3, 0)
+                p[13] = __funnelshift_r(a[4][0], a[4][1], 8);     // (-3, 1)
+                p[14] = __funnelshift_r(a[5][0], a[5][1], 16);    // (-2, 2)
+                p[15] = __funnelshift_r(a[6][0], a[6][1], 24);    // (-1, 3)
+                uint32_t fb[16], fd[16];
+                #pragma unroll
+                for (int k = 0; k < 16; ++k) { fb[k] = gtu4(p[k], hi, nh7); fd[k] = ltu4(p[k], lo, lo7); }
+                const uint32_t corner = (nineOfSixteen(fb) | nineOfSixteen(fd)) & validBytes(lx0, rw);
+                nib = ((corner >> 7) & 1u) | ((corner >> 14) & 2u) | ((corner >> 21) & 4u) | ((corner >> 28) & 8u);
+            }
+            if (__any_sync(0xffffffffu, nib != 0)) {
+                int slot = warpAppend(&sCornerN[cur], __popc(nib));
+                uint16_t* lst = cornerList + cur * kCornerCap;
+                #pragma unroll
+                for (int b = 0; b < 4; ++b)
+                    if ((nib >> b) & 1u) lst[slot++] = (uint16_t)((y << 10) | (lx0 + b));
+            }
+        }
+        __syncthreads();
+        // ---- pass 2: exact score of this chunk's corners ----
+        const int nCur = sCornerN[cur];
+        if (threadIdx.x == 0) sGroupN = 0;   // every thread read it before the barrier above
+        {
+            const uint16_t* lst = cornerList + cur * kCornerCap;
+            for (int i = threadIdx.x; i < nCur; i += kFastThreads) {
+                const int code = lst[i], ly = code >> 10, lx = code & 1023;
+                const uint8_t* c = tile + (ly + 3) * TP + (lx + off0);
+                const int v = c[0];
+                int d[16];
+                #pragma unroll
+                for (int k = 0; k < 16; ++k) d[k] = v - (int)c[o[k]];
+                int mn2[16], mx2[16];
+                #pragma unroll
+                for (int k = 0; k < 16; ++k) { mn2[k] = min(d[k], d[(k + 1) & 15]); mx2[k] = max(d[k], d[(k + 1) & 15]); }
+                int mn4[16], mx4[16];
+                #pragma unroll
+                for (int k = 0; k < 16; ++k) { mn4[k] = min(mn2[k], mn2[(k + 2) & 15]); mx4[k] = max(mx2[k], mx2[(k + 2) & 15]); }
+                int a0 = -255, b0 = 255;
+                #pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    const int mn9 = min(min(mn4[k], mn4[(k + 4) & 15]), d[(k + 8) & 15]);
+                    const int mx9 = max(max(mx4[k], mx4[(k + 4) & 15]), d[(k + 8) & 15]);
+                    a0 = max(a0, mn9);
+                    b0 = min(b0, mx9);
+                }
+                score[(ly + 1) * SP + (lx + 1)] = (uint8_t)(max(a0, -b0) - 1); // > minTh-1 >= 0 for a detected corner
+            }
+        }
+        __syncthreads();
+        // ---- pass 3: NMS of the PREVIOUS chunk's corners (all their neighbours are scored now) ----
+        if (threadIdx.x == 0) sCornerN[cur ^ 1] = 0;
+        nmsPass(cornerList + (cur ^ 1) * kCornerCap, nPrev);
+        nPrev = nCur;
+        // the next chunk's pass 0 does not touch the lists; its sync orders pass 1's writes after this pass's reads
     }
     __syncthreads();
-    const int nList = sListN;
-
-    // phase 2: exact score for the listed corners
-    for (int i = threadIdx.x; i < nList; i += kFastThreads) {
-        const int code = list[i], ly = code >> 6, lx = code & 63;
-        const uint8_t* c = tile + (ly + 3) * tp + (lx + 3);
-        const int v = c[0];
-        int d[16];
-        #pragma unroll
-        for (int k = 0; k < 16; ++k) d[k] = v - (int)c[o[k]];
-        int mn2[16], mx2[16];
-        #pragma unroll
-        for (int k = 0; k < 16; ++k) { mn2[k] = min(d[k], d[(k + 1) & 15]); mx2[k] = max(d[k], d[(k + 1) & 15]); }
-        int mn4[16], mx4[16];
-        #pragma unroll
-        for (int k = 0; k < 16; ++k) { mn4[k] = min(mn2[k], mn2[(k + 2) & 15]); mx4[k] = max(mx2[k], mx2[(k + 2) & 15]); }
-        int a0 = -255, b0 = 255;
-        #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            const int mn9 = min(min(mn4[k], mn4[(k + 4) & 15]), d[(k + 8) & 15]);
-            const int mx9 = max(max(mx4[k], mx4[(k + 4) & 15]), d[(k + 8) & 15]);
-            a0 = max(a0, mn9);
-            b0 = min(b0, mx9);
-        }
-        const int s = max(a0, -b0) - 1;  // > minTh-1 >= 0 for a detected corner
-        score[(ly + 1) * sp + (lx + 1)] = (uint8_t)s;
-    }
+    nmsPass(cornerList + (cur ^ 1) * kCornerCap, nPrev);
     __syncthreads();
-
-    // phase 3: NMS (strict >, 8 neighbours, zero outside the cell)
-    for (int i = threadIdx.x; i < nList; i += kFastThreads) {
-        const int code = list[i], ly = code >> 6, lx = code & 63;
-        const uint8_t* r = score + (ly + 1) * sp + (lx + 1);
-        const int s = r[0];
-        const bool keep = s > r[-1] && s > r[1] && s > r[-sp - 1] && s > r[-sp] && s > r[-sp + 1] &&
-                          s > r[sp - 1] && s > r[sp] && s > r[sp + 1];
-        if (keep) { atomicAdd(&sNms, 1); if (s >= tini) atomicAdd(&sIni, 1); }
-        else list[i] = 0xffff;
+    // ---- pass 4: per-cell retry decision and output ----
+    const int nc = j1 - j0;
+    if (threadIdx.x == 0) {
+        int tot = 0;
+        for (int c = 0; c < nc; ++c) tot += sIni[c] > 0 ? sIni[c] : sNms[c];
+        sBase = tot ? atomicAdd(&candCount[frame * G->nlevels + level], tot) : 0;
     }
-    __syncthreads();
-    const int nIni = sIni;
-    const int nOut = nIni > 0 ? nIni : sNms;
-    if (nOut == 0) return;
-    if (threadIdx.x == 0) { sBase = atomicAdd(&candCount[frame * G->nlevels + level], nOut); sNms = 0; }
     __syncthreads();
     unsigned long long* out = cand + (size_t)frame * G->candPerFrame + g.candBase + sBase;
-    for (int i = threadIdx.x; i < nList; i += kFastThreads) {
-        const int code = list[i];
-        if (code == 0xffff) continue;
-        const int ly = code >> 6, lx = code & 63;
-        const int s = score[(ly + 1) * sp + (lx + 1)];
-        if (nIni > 0 && s < tini) continue;
-        const int slot = atomicAdd(&sNms, 1);
-        const uint32_t key = ((uint32_t)cellIdx << 12) | (uint32_t)code;
-        out[slot] = ((unsigned long long)((uint32_t)s << 24) << 32) | key; // hi = score<<24 | node(0), lo = key
+    const int nw = (rh * SP + 31) / 32;
+    for (int i = threadIdx.x; i < nw; i += kFastThreads) {
+        uint32_t bits = nmsBits[i];
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            const int idx = i * 32 + b, ly = idx / SP, lx = idx - ly * SP;
+            const int s = score[(ly + 1) * SP + (lx + 1)];
+            const int cj = colCell[lx], cx = lx - cj * wCell;
+            if (sIni[cj] > 0 && s < tini) continue;
+            const int slot = atomicAdd(&sOutN, 1);
+            const uint32_t key = ((uint32_t)(ci * g.nCols + j0 + cj) << 12) | (uint32_t)(ly << 6) | (uint32_t)cx;
+            out[slot] = ((unsigned long long)((uint32_t)s << 24) << 32) | key; // hi = score<<24 | node(0), lo = key
+        }
     }
 }
 
 int launchFast(Ctx* c, int batch)
 {
     const GeomSet& g = c->geom;
-    int maxW = 0, maxH = 0;
-    for (int l = 0; l < g.nlevels; ++l) if (g.lv[l].nCols > 0) { maxW = max(maxW, g.lv[l].wCell); maxH = max(maxH, g.lv[l].hCell); }
     stageBegin(c, ST_FAST);
     ORBX_CUDA(c, cudaMemsetAsync(c->dCandCount, 0, sizeof(int) * (size_t)batch * g.nlevels, c->stream));
     int launches = 0;
-    if (g.cellsPerFrame > 0) {
-        const int tp = (maxW + 6 + 3) & ~3;
-        size_t smem = (size_t)tp * (maxH + 6);
-        smem += (((size_t)(maxW + 2) * (maxH + 2) + 15) & ~(size_t)15);
-        smem += sizeof(uint16_t) * (size_t)maxW * maxH; // worst case list (every pixel); NMS-free bound
-        smem = (smem + 15) & ~(size_t)15;
+    if (g.stripsPerFrame > 0) {
+        const int TP = g.fastTilePitch, TR = g.fastTileRows, SP = g.fastScorePitch;
+        size_t smem = (size_t)TP * TR + (size_t)SP * (TR - 4);
+        smem += sizeof(uint32_t) * (size_t)(((TR - 6) * SP + 31) / 32 + 1);
+        smem += sizeof(uint16_t) * (2 * kCornerCap + kGroupCap) + (size_t)SP;
+        smem = (smem + 127) & ~(size_t)127;
         static size_t configured = 0;
         if (smem > 48 * 1024 && smem > configured) {
-            ORBX_CUDA(c, cudaFuncSetAttribute(fastCellsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            ORBX_CUDA(c, cudaFuncSetAttribute(fastStripKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             configured = smem;
         }
-        dim3 grid(g.cellsPerFrame, batch), block(kFastThreads);
-        fastCellsKernel<<<grid, block, smem, c->stream>>>(c->dGeom, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr,
-                                                         c->dCand, c->dCandCount, tp);
+        dim3 grid(g.stripsPerFrame, batch), block(kFastThreads);
+        fastStripKernel<<<grid, block, smem, c->stream>>>(c->dGeom, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr,
+                                                         c->dCand, c->dCandCount, TP, TR, SP);
         launches = 1;
     }
     stageEnd(c, ST_FAST, launches);

@@ -8,35 +8,56 @@
 
 namespace orbx {
 
+constexpr int kResizeRows = 8;   // destination rows per thread: taps stay in registers, the horizontal pass of a source
+                                 // row is reused by the next destination row (scale 1.2: ~1.2 row passes per row, not 2)
+
+__device__ __forceinline__ void hpass(const uint8_t* __restrict__ S, const int (&sx)[4], const int (&sx1)[4],
+                                      const int (&c0)[4], const int (&c1)[4], int (&t)[4])
+{
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) t[i] = ((int)__ldg(S + sx[i]) * c0[i] + (int)__ldg(S + sx1[i]) * c1[i]) >> 4;
+}
+
 __global__ void __launch_bounds__(128)
 resizeLinearKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sFrame, int sw, int sh,
                    uint8_t* __restrict__ dst, size_t dPitch, size_t dFrame, int dw, int dh,
                    const ResizeTap* __restrict__ tapX, const ResizeTap* __restrict__ tapY)
 {
-    const int y = blockIdx.y;
     const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (x0 >= dw) return;
-    const ResizeTap ty = tapY[y];
-    int r0 = ty.s, r1 = ty.s + 1;           // rows are clipped, weights kept (OpenCV VResize)
-    r1 = r1 > sh - 1 ? sh - 1 : r1;
-    const uint8_t* S0 = src + (size_t)blockIdx.z * sFrame + (size_t)r0 * sPitch;
-    const uint8_t* S1 = src + (size_t)blockIdx.z * sFrame + (size_t)r1 * sPitch;
-    const int b0 = ty.c0, b1 = ty.c1;
-    uint32_t packed = 0;
+    int sx[4], sx1[4], c0[4], c1[4];
     #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const int x = x0 + i;
-        if (x < dw) {
-            const ResizeTap tx = tapX[x];
-            const int sx = tx.s, sx1 = min(sx + 1, sw - 1);
-            const int t0 = (int)S0[sx] * tx.c0 + (int)S0[sx1] * tx.c1;
-            const int t1 = (int)S1[sx] * tx.c0 + (int)S1[sx1] * tx.c1;
-            const int v = (((b0 * (t0 >> 4)) >> 16) + ((b1 * (t1 >> 4)) >> 16) + 2) >> 2;
+        const ResizeTap tx = tapX[min(x0 + i, dw - 1)];
+        sx[i] = tx.s; sx1[i] = min(tx.s + 1, sw - 1); c0[i] = tx.c0; c1[i] = tx.c1;
+    }
+    const uint8_t* S = src + (size_t)blockIdx.z * sFrame;
+    uint8_t* D = dst + (size_t)blockIdx.z * dFrame;
+    const int yb = blockIdx.y * kResizeRows, ye = min(yb + kResizeRows, dh);
+    int rowA = -1, rowB = -1, tA[4] = {0, 0, 0, 0}, tB[4] = {0, 0, 0, 0};
+    for (int y = yb; y < ye; ++y) {
+        const ResizeTap ty = tapY[y];
+        const int r0 = ty.s, r1 = min(ty.s + 1, sh - 1);   // rows are clipped, weights kept (OpenCV VResize)
+        if (r0 == rowB) {
+            #pragma unroll
+            for (int i = 0; i < 4; ++i) tA[i] = tB[i];
+            rowA = rowB;
+        } else if (r0 != rowA) { hpass(S + (size_t)r0 * sPitch, sx, sx1, c0, c1, tA); rowA = r0; }
+        if (r1 == rowA) {
+            #pragma unroll
+            for (int i = 0; i < 4; ++i) tB[i] = tA[i];
+            rowB = rowA;
+        } else { hpass(S + (size_t)r1 * sPitch, sx, sx1, c0, c1, tB); rowB = r1; }
+        const int b0 = ty.c0, b1 = ty.c1;
+        uint32_t packed = 0;
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int v = (((b0 * tA[i]) >> 16) + ((b1 * tB[i]) >> 16) + 2) >> 2;
             packed |= (uint32_t)(v & 0xff) << (8 * i);
         }
+        // rows are padded to a multiple of 16 bytes, so the 4-byte store never leaves the row
+        *reinterpret_cast<uint32_t*>(D + (size_t)y * dPitch + x0) = packed;
     }
-    // rows are padded to a multiple of 16 bytes, so the 4-byte store never leaves the row
-    *reinterpret_cast<uint32_t*>(dst + (size_t)blockIdx.z * dFrame + (size_t)y * dPitch + x0) = packed;
 }
 
 int launchPyramid(Ctx* c, int batch)
@@ -50,7 +71,7 @@ int launchPyramid(Ctx* c, int batch)
         const uint8_t* src; size_t sp, sf;
         if (l == 1) { src = c->lvl0; sp = c->lvl0Pitch; sf = c->lvl0FrameStride; }
         else { src = c->dPyr + s.planeOff; sp = (size_t)s.pitch; sf = (size_t)s.pitch * s.h; }
-        dim3 grid((d.w + 511) / 512, d.h, batch), block(128);
+        dim3 grid((d.w + 511) / 512, (d.h + kResizeRows - 1) / kResizeRows, batch), block(128);
         resizeLinearKernel<<<grid, block, 0, c->stream>>>(src, sp, sf, s.w, s.h, c->dPyr + d.planeOff, (size_t)d.pitch,
                                                          (size_t)d.pitch * d.h, d.w, d.h, c->dTapX[l], c->dTapY[l]);
         ++launches;

@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <new>
+#include <algorithm>
 
 namespace orbx {
 
@@ -124,7 +125,7 @@ static int configure(Ctx* c, int w, int h)
     g.nlevels = c->nlevels; g.iniTh = c->iniTh; g.minTh = c->minTh;
     for (int i = 0; i < 16; ++i) g.umax[i] = c->umax[i];
     size_t planeOff = 0, blurOff = 0;
-    int cellBase = 0, candBase = 0, outBase = 0, tileBase = 0;
+    int cellBase = 0, candBase = 0, outBase = 0, tileBase = 0, stripBase = 0, maxRw = 0, maxHc = 0;
     for (int l = 0; l < c->nlevels; ++l) {
         LevelGeom& q = g.lv[l];
         levelSize(c, l, w, h, &q.w, &q.h);
@@ -152,9 +153,20 @@ static int configure(Ctx* c, int w, int h)
         q.outBase = outBase; outBase += q.outCap;
         q.planeOff = planeOff; planeOff += (size_t)q.pitch * q.h * c->maxBatch; planeOff = (planeOff + 255) & ~(size_t)255;
         q.blurOff = blurOff; blurOff += (size_t)q.pitch * q.h * c->maxBatch; blurOff = (blurOff + 255) & ~(size_t)255;
-        q.tilesX = (q.w + 63) / 64; q.tilesY = (q.h + 31) / 32;
+        q.tilesX = (q.w + 127) / 128; q.tilesY = (q.h + 63) / 64; // blur tiles (k_blur.cu)
         q.tileBase = tileBase; tileBase += q.tilesX * q.tilesY;
+        // FAST strips: segments of whole cells, at most 320 candidate columns and 32 cells each (k_fast.cu)
+        q.stripBase = stripBase; q.segsPerRow = 0; q.cellsPerSeg = 1;
+        if (q.nCols > 0) {
+            const int maxCells = std::max(1, std::min(32, 320 / q.wCell));
+            q.segsPerRow = (q.nCols + maxCells - 1) / maxCells;
+            q.cellsPerSeg = (q.nCols + q.segsPerRow - 1) / q.segsPerRow;
+            stripBase += q.segsPerRow * q.nRows;
+            maxRw = std::max(maxRw, q.cellsPerSeg * q.wCell); maxHc = std::max(maxHc, q.hCell);
+        }
     }
+    g.stripsPerFrame = stripBase;
+    g.fastTilePitch = ((maxRw + 37 + 15) & ~15) + 16; g.fastTileRows = maxHc + 6; g.fastScorePitch = (maxRw + 2 + 3) & ~3;
     g.cellsPerFrame = cellBase; g.candPerFrame = candBase; g.selPerFrame = outBase; g.blurTilesPerFrame = tileBase;
     ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
     // arenas only ever grow (sized for max_w x max_h x max_batch at creation)

@@ -36,6 +36,7 @@ struct LevelGeom {
     size_t planeOff;     // byte offset of this level's [B][h][pitch] block inside the pyramid arena
     size_t blurOff;      // same for the blurred arena
     int tileBase, tilesX, tilesY; // blur tile table
+    int stripBase, segsPerRow, cellsPerSeg; // FAST strips: one cell-row, split into segments of whole cells
 };
 
 struct ResizeTap { uint16_t s; int16_t c0, c1; uint16_t pad; }; // source index + 11-bit fixed-point weights
@@ -47,6 +48,7 @@ struct GeomSet {            // what kernels need, uploaded to constant memory on
     int candPerFrame;
     int selPerFrame;
     int blurTilesPerFrame;
+    int stripsPerFrame, fastTilePitch, fastTileRows, fastScorePitch;
     int iniTh, minTh;
     int umax[16];
 };

@@ -1,0 +1,39 @@
+"""GPU: the C++ drop-in class ORB_SLAM2::ORBextractor (include/ORBextractor.h, host/ORBextractor.cc) called the way
+Frame::ExtractORB calls it, against the oracle: keypoints, descriptors and the bordered mvImagePyramid."""
+import os, subprocess
+import numpy as np
+import pytest
+import synth, oracle_lib as O
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_cpp_dropin_extractor(tmp_path):
+    subprocess.run(["make", "-C", os.path.join(ROOT, "host"), "-s"], check=True)
+    w, h, nf = 752, 480, 1200
+    img = synth.frame(12, w, h)
+    raw, out = tmp_path / "in.raw", tmp_path / "out.bin"
+    img.tofile(raw)
+    r = subprocess.run([os.path.join(ROOT, "host", "orbx_cpp_driver"), str(raw), str(w), str(h), str(nf), str(out)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    b = open(out, "rb").read()
+    n = int(np.frombuffer(b, np.int32, 1, 0)[0])
+    o = 4
+    kps = np.frombuffer(b, O.KP_DTYPE, n, o); o += 28 * n
+    desc = np.frombuffer(b, np.uint8, 32 * n, o).reshape(n, 32); o += 32 * n
+    L = int(np.frombuffer(b, np.int32, 1, o)[0]); o += 4
+    sf = np.frombuffer(b, np.float32, L, o); o += 4 * L
+    p = O.params(nf)
+    okps, odesc, pyr = O.extract(p, img, want_pyr=True)
+    assert n == len(okps) and np.array_equal(kps, okps) and np.array_equal(desc, odesc)
+    assert np.array_equal(sf.view(np.uint32), np.array(p.scale[:L], np.float32).view(np.uint32))
+    po = 0
+    for l, (lw, lh) in enumerate(O.level_sizes(p, w, h)):
+        cw, ch = np.frombuffer(b, np.int32, 2, o); o += 8
+        assert (cw, ch) == (lw, lh)
+        got = np.frombuffer(b, np.uint8, (lw + 38) * (lh + 38), o).reshape(lh + 38, lw + 38); o += (lw + 38) * (lh + 38)
+        want = O.border(pyr[po:po + lw * lh].reshape(lh, lw), 19); po += lw * lh
+        assert np.array_equal(got, want), l
+    assert o == len(b)

@@ -43,7 +43,7 @@ def test_pyramid_levels_bit_exact(P):
         assert np.array_equal(ex.pyramid_level(l, border=19), O.border(want, 19)), ("border", l)
 
 
-CASES = ["tum", "euroc", "kitti", "grad", "noise", "black", "small"]
+CASES = ["tum", "euroc", "kitti", "grad", "noise", "black", "small", "blocks"]
 
 
 @pytest.mark.parametrize("name", CASES)

@@ -18,7 +18,7 @@ def prim():
 
 
 def test_resize_matches_cv2(prim):
-    img = synth.frame(11, 213, 160)
+    img = synth.frame(11, 213, 160, "blocks")
     for key in prim.files:
         if key.startswith("resize_"):
             dw, dh = map(int, key[7:].split("x"))
@@ -26,7 +26,7 @@ def test_resize_matches_cv2(prim):
 
 
 def test_blur_border_match_cv2(prim):
-    img = synth.frame(11, 213, 160)
+    img = synth.frame(11, 213, 160, "blocks")
     assert np.array_equal(O.blur(img, 9), prim["blur9"])
     assert np.array_equal(O.blur(img, 7), prim["blur7"])
     assert np.array_equal(O.border(img, 19), prim["border19"])
@@ -44,7 +44,7 @@ def test_fast_roi_matches_cv2(prim):
             assert np.array_equal(O.fast_roi(roi, th), prim[f"fast_{kind}_{th}"]), (kind, th)
 
 
-CASES = ["tum", "euroc", "kitti", "grad", "noise", "black", "small"]
+CASES = ["tum", "euroc", "kitti", "grad", "noise", "black", "small", "blocks"]
 
 
 @pytest.mark.parametrize("name", CASES)

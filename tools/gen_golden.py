@@ -19,7 +19,7 @@ def sha(a): return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 
 # --- primitives ---
 prim = {}
-img = synth.frame(11, 213, 160)
+img = synth.frame(11, 213, 160, "blocks")
 for (dw, dh) in [(178, 133), (200, 150), (107, 80), (300, 231)]:
     prim[f"resize_{dw}x{dh}"] = cv2.resize(img, (dw, dh), interpolation=cv2.INTER_LINEAR)
 prim["blur9"] = cv2.GaussianBlur(img, (9, 9), 2, sigmaY=2, borderType=cv2.BORDER_REFLECT_101)
@@ -42,7 +42,7 @@ pat = R.load_pattern(os.path.join(ROOT, "oracle", "brief_pattern.inc"))
 cases = [("tum", 0, 640, 480, 1000, "texture"), ("euroc", 1, 752, 480, 1200, "texture"),
          ("kitti", 4, 1241, 376, 2000, "texture"), ("grad", 2, 320, 240, 500, "gradient"),
          ("noise", 3, 640, 480, 1000, "noise"), ("black", 0, 160, 120, 300, "black"),
-         ("small", 6, 96, 80, 200, "texture")]
+         ("small", 6, 96, 80, 200, "texture"), ("blocks", 8, 640, 480, 1000, "blocks")]
 for name, seed, w, h, nf, kind in cases:
     im = synth.frame(seed, w, h, kind)
     kp, octv, desc, pyr, cands = R.extract(im, R.Params(nf, 1.2, 8, 20, 7), pat)
