@@ -13,7 +13,7 @@
 
 namespace orbx {
 
-__device__ __align__(16) const signed char kBriefPattern[1024] = {
+__device__ __align__(16) const float kBriefPatternF[1024] = {   // (x0, y0, x1, y1) per test, src/ORBextractor.cc:209-467
 #include "brief_pattern.inc"
 };
 
@@ -97,9 +97,10 @@ __global__ void atan2ProbeKernel(const float* yx, int n, float* out)
 }
 
 constexpr int kDescWarps = 8;
+constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitchW = 11;   // 37 rows x 44 bytes per warp
 
 __global__ void __launch_bounds__(kDescWarps * 32)
-describeKernel(const GeomSet* __restrict__ G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
+describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
                const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                const orbx_keypoint* __restrict__ selAll, const int* __restrict__ selCount,
                orbx_keypoint* __restrict__ outKp, uint8_t* __restrict__ outDesc, int cap, int* __restrict__ outN,
@@ -108,56 +109,79 @@ describeKernel(const GeomSet* __restrict__ G, const uint8_t* __restrict__ lvl0, 
     const int lane = threadIdx.x & 31;
     const int slot = blockIdx.x * kDescWarps + (threadIdx.x >> 5);
     const int frame = blockIdx.y;
-    if (slot >= G->selPerFrame) return;
+    if (slot >= G.selPerFrame) return;
     int level = 0;
-    while (level + 1 < G->nlevels && slot >= G->lv[level + 1].outBase) ++level;
-    const LevelGeom& g = G->lv[level];
+    while (level + 1 < G.nlevels && slot >= G.lv[level + 1].outBase) ++level;
+    const LevelGeom& g = G.lv[level];
     const int pos = slot - g.outBase;
-    const int* cnts = selCount + frame * G->nlevels;
+    const int* cnts = selCount + frame * G.nlevels;
     int before = 0, total = 0;
-    for (int l = 0; l < G->nlevels; ++l) { const int c = cnts[l]; if (l < level) before += c; total += c; }
+    for (int l = 0; l < G.nlevels; ++l) { const int c = cnts[l]; if (l < level) before += c; total += c; }
     if (slot == 0 && lane == 0) outN[frame] = min(total, cap);
     if (pos >= cnts[level]) return;
     const int idx = before + pos;
     if (idx >= cap) { if (lane == 0) atomicExch(err, 5); return; }
 
-    orbx_keypoint kp = selAll[(size_t)frame * G->selPerFrame + slot];
+    orbx_keypoint kp = selAll[(size_t)frame * G.selPerFrame + slot];
     const int cx = __float2int_rn(kp.x), cy = __float2int_rn(kp.y);
     const uint8_t* img; size_t pitch;
     if (level == 0) { img = lvl0 + (size_t)frame * lvl0Frame; pitch = lvl0Pitch; }
     else { img = pyr + g.planeOff + (size_t)frame * g.pitch * g.h; pitch = (size_t)g.pitch; }
 
-    // ---- IC_Angle: lane v-row of the 31-row disc ----
+    // ---- IC_Angle: lane = column u of the disc, unrolled over its 31 rows, so one warp load reads one image row
+    //      segment (1-2 sectors) instead of 31 different rows ----
     int m10 = 0, m01 = 0;
     if (lane < 2 * kHalfPatch + 1) {
-        const int v = lane - kHalfPatch;
-        const int d = G->umax[v < 0 ? -v : v];
-        const uint8_t* row = img + (size_t)(cy + v) * pitch + cx;
-        int rs = 0;
-        for (int u = -d; u <= d; ++u) { const int p = row[u]; rs += p; m10 += u * p; }
-        m01 = v * rs;
+        const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
+        const uint8_t* col = img + (size_t)(cy - kHalfPatch) * pitch + cx + u;
+        int cs = 0;
+        #pragma unroll
+        for (int vi = 0; vi <= 2 * kHalfPatch; ++vi) {
+            const int v = vi - kHalfPatch;
+            if (au <= G.umax[v < 0 ? -v : v]) { const int p = __ldg(col + (size_t)vi * pitch); cs += p; m01 += v * p; }
+        }
+        m10 = u * cs;
     }
     #pragma unroll
     for (int o = 16; o > 0; o >>= 1) { m10 += __shfl_xor_sync(0xffffffffu, m10, o); m01 += __shfl_xor_sync(0xffffffffu, m01, o); }
     const float angle = fastAtan2Dev((float)m01, (float)m10);
 
-    // ---- steered BRIEF on the blurred level: lane = descriptor byte ----
+    // ---- stage the 37 x 37 blurred patch (rotated pattern points stay within +-18) in shared memory: 10 aligned
+    //      words per row, 3 rows per warp load ----
+    __shared__ uint32_t sPatch[kDescWarps][kPatchRows * kPatchPitchW];
+    uint32_t* patch = sPatch[threadIdx.x >> 5];
+    const uint8_t* blurPlane = blur + g.blurOff + (size_t)frame * g.pitch * g.h;
+    const int bp = g.pitch;
+    const int a0 = (cx - kPatchR) & ~3;                         // aligned first column
+    const int offc = (cx - kPatchR) - a0 + kPatchR;             // byte column of the patch centre inside a staged row
+    #pragma unroll
+    for (int t = 0; t < (kPatchRows * 10 + 31) / 32; ++t) {
+        const int i = t * 32 + lane;
+        if (i < kPatchRows * 10) {
+            const int r = i / 10, k = i - r * 10;
+            const int col = a0 + 4 * k;
+            uint32_t w = 0;
+            if (col + 3 < bp) w = __ldg(reinterpret_cast<const uint32_t*>(blurPlane + (size_t)(cy - kPatchR + r) * bp + col));
+            patch[r * kPatchPitchW + k] = w;
+        }
+    }
+    __syncwarp();
+
+    // ---- steered BRIEF on the blurred patch: lane = descriptor byte ----
     const float factorPI = (float)(3.14159265358979323846 / 180.f);
     float a, b;
     glibcSinCosf(__fmul_rn(angle, factorPI), b, a); // a = cos, b = sin  (:158)
-    const uint8_t* bl = blur + g.blurOff + (size_t)frame * g.pitch * g.h + (size_t)cy * g.pitch + cx;
-    const int bp = g.pitch;
-    const char4* pat = reinterpret_cast<const char4*>(kBriefPattern) + lane * 8;
+    const uint8_t* pc = reinterpret_cast<const uint8_t*>(patch) + kPatchR * (kPatchPitchW * 4) + offc;
+    const float4* pat = reinterpret_cast<const float4*>(kBriefPatternF) + lane * 8;
     int val = 0;
     #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const char4 q = pat[k];
-        const float x0 = (float)q.x, y0 = (float)q.y, x1 = (float)q.z, y1 = (float)q.w;
-        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
-        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-        const int t0 = bl[r0 * bp + c0], t1 = bl[r1 * bp + c1];
+        const float4 q = __ldg(pat + k);
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(q.x, b), __fmul_rn(q.y, a)));
+        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(q.x, a), __fmul_rn(q.y, b)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(q.z, b), __fmul_rn(q.w, a)));
+        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(q.z, a), __fmul_rn(q.w, b)));
+        const int t0 = pc[r0 * (kPatchPitchW * 4) + c0], t1 = pc[r1 * (kPatchPitchW * 4) + c1];
         val |= (t0 < t1) << k;
     }
     outDesc[((size_t)frame * cap + idx) * 32 + lane] = (uint8_t)val;
@@ -173,7 +197,7 @@ int launchDescribe(Ctx* c, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int c
     const GeomSet& g = c->geom;
     stageBegin(c, ST_DESCRIBE);
     dim3 grid((g.selPerFrame + kDescWarps - 1) / kDescWarps, batch), block(kDescWarps * 32);
-    describeKernel<<<grid, block, 0, c->stream>>>(c->dGeom, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur,
+    describeKernel<<<grid, block, 0, c->stream>>>(c->geom, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur,
                                                  c->dSel, c->dSelCount, dKps, dDesc, capPerFrame, dN, c->dErr);
     stageEnd(c, ST_DESCRIBE, 1);
     ORBX_CUDA(c, cudaGetLastError());

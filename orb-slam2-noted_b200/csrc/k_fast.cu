@@ -22,10 +22,9 @@
 namespace orbx {
 
 constexpr int kFastThreads = 256;
-constexpr int kCornerCap = 2048;                 // pixels per row chunk (and capacity of a corner list)
-constexpr int kGroupCap = kCornerCap / 4;        // 4-pixel groups per row chunk
+constexpr int kCornerCap = 4096;                 // corner list capacity (scored in bulk whenever the next batch could overflow it)
+constexpr int kGroupBatch = 512;                 // 4-pixel groups per full-test batch (<= 2048 new corners)
 constexpr int kMaxCellsPerStrip = 32;
-constexpr int kStripMaxWidth = 320;              // candidate columns per strip (host: cellsPerSeg)
 
 __device__ __forceinline__ uint32_t smemAddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -76,20 +75,20 @@ __device__ __forceinline__ int warpAppend(int* counter, int cnt)
     return base + incl - cnt;
 }
 
-__global__ void __launch_bounds__(kFastThreads, 3)
-fastStripKernel(const GeomSet* __restrict__ G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
+__global__ void __launch_bounds__(kFastThreads, 4)
+fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
                 const uint8_t* __restrict__ pyr, unsigned long long* __restrict__ cand, int* __restrict__ candCount,
                 int tilePitchMax, int tileRowsMax, int scorePitchMax)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) unsigned long long sBar;
-    __shared__ int sGroupN, sCornerN[2], sOutN, sBase;
+    __shared__ int sGroupN, sCornerN, sOutN, sBase;
     __shared__ int sNms[kMaxCellsPerStrip], sIni[kMaxCellsPerStrip];
 
     const int frame = blockIdx.y;
     int level = 0;
-    while (level + 1 < G->nlevels && (int)blockIdx.x >= G->lv[level + 1].stripBase) ++level;
-    const LevelGeom& g = G->lv[level];
+    while (level + 1 < G.nlevels && (int)blockIdx.x >= G.lv[level + 1].stripBase) ++level;
+    const LevelGeom& g = G.lv[level];
     const int sIdx = blockIdx.x - g.stripBase;
     const int ci = sIdx / g.segsPerRow, seg = sIdx - ci * g.segsPerRow;
     const int j0 = seg * g.cellsPerSeg, j1 = min(j0 + g.cellsPerSeg, g.nCols);
@@ -103,18 +102,21 @@ fastStripKernel(const GeomSet* __restrict__ G, const uint8_t* __restrict__ lvl0,
     else { img = pyr + g.planeOff + (size_t)frame * g.pitch * g.h; pitch = (size_t)g.pitch; }
 
     const int TP = tilePitchMax, SP = scorePitchMax;               // bytes per tile / score row
+    const int BP = (SP + 31) >> 5;                                  // bitmap words per row
+    const int maxRh = tileRowsMax - 6;
     uint8_t* tile = smem;                                           // (rh + 6) rows
     uint8_t* score = smem + (size_t)TP * tileRowsMax;               // (rh + 2) x SP, zero apron
-    uint32_t* nmsBits = reinterpret_cast<uint32_t*>(score + (size_t)SP * (tileRowsMax - 4));
-    uint16_t* cornerList = reinterpret_cast<uint16_t*>(nmsBits + ((tileRowsMax - 6) * SP + 31) / 32 + 1); // 2 x kCornerCap
-    uint16_t* groupList = cornerList + 2 * kCornerCap;              // kGroupCap
-    uint8_t* colCell = reinterpret_cast<uint8_t*>(groupList + kGroupCap); // SP entries: cell column of candidate column lx
+    uint32_t* cornerBits = reinterpret_cast<uint32_t*>(score + (size_t)SP * (maxRh + 2)); // rh x BP
+    uint32_t* nmsBits = cornerBits + maxRh * BP;
+    uint16_t* cornerList = reinterpret_cast<uint16_t*>(nmsBits + maxRh * BP);             // kCornerCap
+    uint16_t* groupList = cornerList + kCornerCap;                  // up to maxRh * (SP/4 + 2) groups
+    uint8_t* colCell = reinterpret_cast<uint8_t*>(groupList + maxRh * ((SP >> 2) + 2));   // cell column of candidate column lx
     const int TH = rh + 6;
     const bool aligned = ((((size_t)img) | pitch) & 15) == 0;
     const int xa = aligned ? ((cx0 - 4) & ~15) : (cx0 - 4) & ~3;    // image column of tile column 0 (>= 4 px left of cx0)
     const int off0 = cx0 - xa;                                      // tile column of the first candidate pixel (>= 4)
 
-    if (threadIdx.x == 0) { sGroupN = 0; sCornerN[0] = 0; sCornerN[1] = 0; sOutN = 0; }
+    if (threadIdx.x == 0) { sGroupN = 0; sCornerN = 0; sOutN = 0; }
     if (threadIdx.x < kMaxCellsPerStrip) { sNms[threadIdx.x] = 0; sIni[threadIdx.x] = 0; }
     if (aligned) {
         const int xb = min((cx1 + 3 + 15) & ~15, (int)pitch);
@@ -139,13 +141,12 @@ fastStripKernel(const GeomSet* __restrict__ G, const uint8_t* __restrict__ lvl0,
             tile[y * TP + x] = img[(size_t)(cy0 - 3 + y) * pitch + xa + x];
         }
     }
-    // zero the score map and NMS bitmap, build the column table while the copies are in flight
+    // zero the score map and bitmaps, build the column table while the copies are in flight
     {
         uint32_t* z = reinterpret_cast<uint32_t*>(score);
         const int nz = (SP * (rh + 2) + 3) / 4;
         for (int i = threadIdx.x; i < nz; i += kFastThreads) z[i] = 0;
-        const int nb = (rh * SP + 31) / 32 + 1;
-        for (int i = threadIdx.x; i < nb; i += kFastThreads) nmsBits[i] = 0;
+        for (int i = threadIdx.x; i < 2 * maxRh * BP; i += kFastThreads) cornerBits[i] = 0;   // cornerBits + nmsBits
         for (int i = threadIdx.x; i < rw; i += kFastThreads) colCell[i] = (uint8_t)(i / g.wCell);
     }
     if (aligned) {
@@ -157,47 +158,27 @@ fastStripKernel(const GeomSet* __restrict__ G, const uint8_t* __restrict__ lvl0,
     }
     __syncthreads();
 
-    const int tmin = G->minTh, tini = G->iniTh;
+    const int tmin = G.minTh, tini = G.iniTh;
     const uint32_t T4 = (uint32_t)tmin * 0x01010101u;
     const int g0 = off0 >> 2, g1 = (off0 + rw + 3) >> 2;            // word columns holding candidate pixels
     const int ng = g1 - g0;
+    const uint32_t rcpNg = 0xffffffffu / (uint32_t)ng + 1u;         // i / ng == umulhi(i, rcpNg) for i < 65536
+    const uint32_t rcpBP = 0xffffffffu / (uint32_t)BP + 1u;
     const int wp = TP >> 2;
     const int wCell = g.wCell;
     const uint32_t* W = reinterpret_cast<const uint32_t*>(tile);
     const int o[16] = {3 * TP, 3 * TP + 1, 2 * TP + 2, TP + 3, 3, -TP + 3, -2 * TP + 2, -3 * TP + 1,
                        -3 * TP, -3 * TP - 1, -2 * TP - 2, -TP - 3, -3, TP - 3, 2 * TP - 2, 3 * TP - 1};
-    const int rowsPerChunk = max(1, kCornerCap / (ng * 4));
 
-    // NMS of one corner-list buffer (strict >, 8 neighbours, zero outside the pixel's own cell)
-    auto nmsPass = [&](const uint16_t* lst, int n) {
-        for (int i = threadIdx.x; i < n; i += kFastThreads) {
-            const int code = lst[i], ly = code >> 10, lx = code & 1023;
-            const uint8_t* r = score + (ly + 1) * SP + (lx + 1);
-            const int s = r[0];
-            const int cj = colCell[lx], cx = lx - cj * wCell;
-            bool keep = s > r[-SP] && s > r[SP];
-            if (cx > 0) keep = keep && s > r[-1] && s > r[-SP - 1] && s > r[SP - 1];
-            if (cx < wCell - 1) keep = keep && s > r[1] && s > r[-SP + 1] && s > r[SP + 1];
-            if (keep) {
-                atomicAdd(&sNms[cj], 1);
-                if (s >= tini) atomicAdd(&sIni[cj], 1);
-                atomicOr(&nmsBits[(ly * SP + lx) >> 5], 1u << ((ly * SP + lx) & 31));
-            }
-        }
-    };
-
-    int cur = 0, nPrev = 0;
-    for (int yc = 0; yc < rh; yc += rowsPerChunk, cur ^= 1) {
-        const int yEnd = min(rh, yc + rowsPerChunk);
-        const int nGroups = (yEnd - yc) * ng;
-        // ---- pass 0: quick rejection, 4 pixels per step.  A 9-arc contains two adjacent compass pixels, i.e. one of
-        //      {0, 8} and one of {4, 12}, all brighter or all darker. ----
+    // ---- pass 0: quick rejection over the whole strip, 4 pixels per step.  A 9-arc contains two adjacent compass
+    //      pixels, i.e. one of {0, 8} and one of {4, 12}, all brighter or all darker. ----
+    {
+        const int nGroups = rh * ng;
         for (int ib = 0; ib < nGroups; ib += kFastThreads) {      // uniform trip count: full-warp votes below
             const int i = ib + threadIdx.x;
             uint32_t q = 0; int code = 0;
             if (i < nGroups) {
-                const int yy = i / ng, gg = i - yy * ng;
-                const int y = yc + yy, gw = g0 + gg;
+                const int y = (int)__umulhi((uint32_t)i, rcpNg), gw = g0 + i - y * ng;
                 const uint32_t* c = W + (y + 3) * wp + gw;
                 const uint32_t v = c[0], up = c[-3 * wp], dn = c[3 * wp];
                 const uint32_t p4 = __funnelshift_r(v, c[1], 24), p12 = __funnelshift_r(c[-1], v, 8);
@@ -213,13 +194,45 @@ fastStripKernel(const GeomSet* __restrict__ G, const uint8_t* __restrict__ lvl0,
                 if (q) groupList[slot] = (uint16_t)code;
             }
         }
-        __syncthreads();
-        // ---- pass 1: full test of the surviving groups: brighter/darker flags of the 16 ring pixels, 9-contiguity ----
-        const int nG = sGroupN;
-        for (int ib = 0; ib < nG; ib += kFastThreads) {
+    }
+    __syncthreads();
+    const int nG = sGroupN;
+
+    // exact score of the listed corners
+    auto scorePass = [&](int n) {
+        for (int i = threadIdx.x; i < n; i += kFastThreads) {
+            const int code = cornerList[i], ly = code >> 10, lx = code & 1023;
+            const uint8_t* c = tile + (ly + 3) * TP + (lx + off0);
+            const int v = c[0];
+            int d[16];
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) d[k] = v - (int)c[o[k]];
+            int mn2[16], mx2[16];
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) { mn2[k] = min(d[k], d[(k + 1) & 15]); mx2[k] = max(d[k], d[(k + 1) & 15]); }
+            int mn4[16], mx4[16];
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) { mn4[k] = min(mn2[k], mn2[(k + 2) & 15]); mx4[k] = max(mx2[k], mx2[(k + 2) & 15]); }
+            int a0 = -255, b0 = 255;
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const int mn9 = min(min(mn4[k], mn4[(k + 4) & 15]), d[(k + 8) & 15]);
+                const int mx9 = max(max(mx4[k], mx4[(k + 4) & 15]), d[(k + 8) & 15]);
+                a0 = max(a0, mn9);
+                b0 = min(b0, mx9);
+            }
+            score[(ly + 1) * SP + (lx + 1)] = (uint8_t)(max(a0, -b0) - 1); // > minTh-1 >= 0 for a detected corner
+        }
+    };
+
+    // ---- pass 1: full test of the surviving groups in batches: brighter/darker flags of the 16 ring pixels,
+    //      9-contiguity as bit-sliced AND/OR trees; corners go to the list and the corner bitmap ----
+    for (int gb = 0; gb < nG; gb += kGroupBatch) {
+        const int gEnd = min(nG, gb + kGroupBatch);
+        for (int ib = gb; ib < gEnd; ib += kFastThreads) {
             const int i = ib + threadIdx.x;
             uint32_t nib = 0; int y = 0, lx0 = 0;
-            if (i < nG) {
+            if (i < gEnd) {
                 const int code = groupList[i], gw = code & 1023;
                 y = code >> 10; lx0 = gw * 4 - off0;
                 const uint32_t* c = W + (y + 3) * wp + gw;
@@ -246,76 +259,82 @@ fastStripKernel(const GeomSet* __restrict__ G, const uint8_t* __restrict__ lvl0,
                 p[13] = __funnelshift_r(a[4][0], a[4][1], 8);     // (-3, 1)
                 p[14] = __funnelshift_r(a[5][0], a[5][1], 16);    // (-2, 2)
                 p[15] = __funnelshift_r(a[6][0], a[6][1], 24);    // (-1, 3)
-                uint32_t fb[16], fd[16];
+                uint32_t f[16];
                 #pragma unroll
-                for (int k = 0; k < 16; ++k) { fb[k] = gtu4(p[k], hi, nh7); fd[k] = ltu4(p[k], lo, lo7); }
-                const uint32_t corner = (nineOfSixteen(fb) | nineOfSixteen(fd)) & validBytes(lx0, rw);
+                for (int k = 0; k < 16; ++k) f[k] = gtu4(p[k], hi, nh7);
+                uint32_t corner = nineOfSixteen(f);
+                #pragma unroll
+                for (int k = 0; k < 16; ++k) f[k] = ltu4(p[k], lo, lo7);
+                corner = (corner | nineOfSixteen(f)) & validBytes(lx0, rw);
                 nib = ((corner >> 7) & 1u) | ((corner >> 14) & 2u) | ((corner >> 21) & 4u) | ((corner >> 28) & 8u);
             }
             if (__any_sync(0xffffffffu, nib != 0)) {
-                int slot = warpAppend(&sCornerN[cur], __popc(nib));
-                uint16_t* lst = cornerList + cur * kCornerCap;
-                #pragma unroll
-                for (int b = 0; b < 4; ++b)
-                    if ((nib >> b) & 1u) lst[slot++] = (uint16_t)((y << 10) | (lx0 + b));
-            }
-        }
-        __syncthreads();
-        // ---- pass 2: exact score of this chunk's corners ----
-        const int nCur = sCornerN[cur];
-        if (threadIdx.x == 0) sGroupN = 0;   // every thread read it before the barrier above
-        {
-            const uint16_t* lst = cornerList + cur * kCornerCap;
-            for (int i = threadIdx.x; i < nCur; i += kFastThreads) {
-                const int code = lst[i], ly = code >> 10, lx = code & 1023;
-                const uint8_t* c = tile + (ly + 3) * TP + (lx + off0);
-                const int v = c[0];
-                int d[16];
-                #pragma unroll
-                for (int k = 0; k < 16; ++k) d[k] = v - (int)c[o[k]];
-                int mn2[16], mx2[16];
-                #pragma unroll
-                for (int k = 0; k < 16; ++k) { mn2[k] = min(d[k], d[(k + 1) & 15]); mx2[k] = max(d[k], d[(k + 1) & 15]); }
-                int mn4[16], mx4[16];
-                #pragma unroll
-                for (int k = 0; k < 16; ++k) { mn4[k] = min(mn2[k], mn2[(k + 2) & 15]); mx4[k] = max(mx2[k], mx2[(k + 2) & 15]); }
-                int a0 = -255, b0 = 255;
-                #pragma unroll
-                for (int k = 0; k < 16; ++k) {
-                    const int mn9 = min(min(mn4[k], mn4[(k + 4) & 15]), d[(k + 8) & 15]);
-                    const int mx9 = max(max(mx4[k], mx4[(k + 4) & 15]), d[(k + 8) & 15]);
-                    a0 = max(a0, mn9);
-                    b0 = min(b0, mx9);
+                int slot = warpAppend(&sCornerN, __popc(nib));
+                if (nib) {
+                    #pragma unroll
+                    for (int b = 0; b < 4; ++b)
+                        if ((nib >> b) & 1u) cornerList[slot++] = (uint16_t)((y << 10) | (lx0 + b));
+                    // the 4 pixels may straddle two bitmap words
+                    const int lxa = max(lx0, 0);
+                    const uint32_t bitsA = (lx0 >= 0 ? nib : nib >> (-lx0));
+                    const int wA = y * BP + (lxa >> 5), sh = lxa & 31;
+                    atomicOr(&cornerBits[wA], bitsA << sh);
+                    if (sh > 28 && (bitsA >> (32 - sh))) atomicOr(&cornerBits[wA + 1], bitsA >> (32 - sh));
                 }
-                score[(ly + 1) * SP + (lx + 1)] = (uint8_t)(max(a0, -b0) - 1); // > minTh-1 >= 0 for a detected corner
             }
         }
         __syncthreads();
-        // ---- pass 3: NMS of the PREVIOUS chunk's corners (all their neighbours are scored now) ----
-        if (threadIdx.x == 0) sCornerN[cur ^ 1] = 0;
-        nmsPass(cornerList + (cur ^ 1) * kCornerCap, nPrev);
-        nPrev = nCur;
-        // the next chunk's pass 0 does not touch the lists; its sync orders pass 1's writes after this pass's reads
+        if (sCornerN > kCornerCap - 4 * kGroupBatch || gEnd == nG) {   // uniform: score in bulk before the list could overflow
+            const int n = sCornerN;
+            scorePass(n);
+            __syncthreads();
+            if (threadIdx.x == 0) sCornerN = 0;
+            __syncthreads();
+        }
     }
-    __syncthreads();
-    nmsPass(cornerList + (cur ^ 1) * kCornerCap, nPrev);
+
+    // ---- pass 3: NMS over the corner bitmap (strict >, 8 neighbours, zero outside the pixel's own cell) ----
+    for (int w = threadIdx.x; w < rh * BP; w += kFastThreads) {
+        uint32_t bits = cornerBits[w];
+        if (!bits) continue;
+        const int ly = (int)__umulhi((uint32_t)w, rcpBP), lxb = (w - ly * BP) << 5;
+        uint32_t keepBits = 0;
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            const int lx = lxb + b;
+            const uint8_t* r = score + (ly + 1) * SP + (lx + 1);
+            const int s = r[0];
+            const int cj = colCell[lx], cx = lx - cj * wCell;
+            bool keep = s > r[-SP] && s > r[SP];
+            if (cx > 0) keep = keep && s > r[-1] && s > r[-SP - 1] && s > r[SP - 1];
+            if (cx < wCell - 1) keep = keep && s > r[1] && s > r[-SP + 1] && s > r[SP + 1];
+            if (keep) {
+                atomicAdd(&sNms[cj], 1);
+                if (s >= tini) atomicAdd(&sIni[cj], 1);
+                keepBits |= 1u << b;
+            }
+        }
+        nmsBits[w] = keepBits;
+    }
     __syncthreads();
     // ---- pass 4: per-cell retry decision and output ----
     const int nc = j1 - j0;
     if (threadIdx.x == 0) {
         int tot = 0;
         for (int c = 0; c < nc; ++c) tot += sIni[c] > 0 ? sIni[c] : sNms[c];
-        sBase = tot ? atomicAdd(&candCount[frame * G->nlevels + level], tot) : 0;
+        sBase = tot ? atomicAdd(&candCount[frame * G.nlevels + level], tot) : 0;
     }
     __syncthreads();
-    unsigned long long* out = cand + (size_t)frame * G->candPerFrame + g.candBase + sBase;
-    const int nw = (rh * SP + 31) / 32;
-    for (int i = threadIdx.x; i < nw; i += kFastThreads) {
-        uint32_t bits = nmsBits[i];
+    unsigned long long* out = cand + (size_t)frame * G.candPerFrame + g.candBase + sBase;
+    for (int w = threadIdx.x; w < rh * BP; w += kFastThreads) {
+        uint32_t bits = nmsBits[w];
+        if (!bits) continue;
+        const int ly = (int)__umulhi((uint32_t)w, rcpBP), lxb = (w - ly * BP) << 5;
         while (bits) {
             const int b = __ffs(bits) - 1;
             bits &= bits - 1;
-            const int idx = i * 32 + b, ly = idx / SP, lx = idx - ly * SP;
+            const int lx = lxb + b;
             const int s = score[(ly + 1) * SP + (lx + 1)];
             const int cj = colCell[lx], cx = lx - cj * wCell;
             if (sIni[cj] > 0 && s < tini) continue;
@@ -334,9 +353,10 @@ int launchFast(Ctx* c, int batch)
     int launches = 0;
     if (g.stripsPerFrame > 0) {
         const int TP = g.fastTilePitch, TR = g.fastTileRows, SP = g.fastScorePitch;
-        size_t smem = (size_t)TP * TR + (size_t)SP * (TR - 4);
-        smem += sizeof(uint32_t) * (size_t)(((TR - 6) * SP + 31) / 32 + 1);
-        smem += sizeof(uint16_t) * (2 * kCornerCap + kGroupCap) + (size_t)SP;
+        const int maxRh = TR - 6, BP = (SP + 31) / 32;
+        size_t smem = (size_t)TP * TR + (size_t)SP * (maxRh + 2);
+        smem += sizeof(uint32_t) * 2 * (size_t)maxRh * BP;
+        smem += sizeof(uint16_t) * ((size_t)kCornerCap + (size_t)maxRh * ((SP >> 2) + 2)) + (size_t)SP;
         smem = (smem + 127) & ~(size_t)127;
         static size_t configured = 0;
         if (smem > 48 * 1024 && smem > configured) {
@@ -344,7 +364,7 @@ int launchFast(Ctx* c, int batch)
             configured = smem;
         }
         dim3 grid(g.stripsPerFrame, batch), block(kFastThreads);
-        fastStripKernel<<<grid, block, smem, c->stream>>>(c->dGeom, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr,
+        fastStripKernel<<<grid, block, smem, c->stream>>>(c->geom, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr,
                                                          c->dCand, c->dCandCount, TP, TR, SP);
         launches = 1;
     }

@@ -68,7 +68,7 @@ __device__ __forceinline__ int quadrant(const Box& b, int x, int y)
 }
 
 __global__ void __launch_bounds__(kOctThreads)
-octreeKernel(const GeomSet* __restrict__ G, unsigned long long* __restrict__ candAll, const int* __restrict__ candCount,
+octreeKernel(const __grid_constant__ GeomSet G, unsigned long long* __restrict__ candAll, const int* __restrict__ candCount,
              orbx_keypoint* __restrict__ selAll, int* __restrict__ selCount, int M, int* __restrict__ err)
 {
     extern __shared__ __align__(16) uint8_t smemRaw[];
@@ -76,11 +76,11 @@ octreeKernel(const GeomSet* __restrict__ G, unsigned long long* __restrict__ can
     __shared__ int sL, sNSplit, sC, sFinish, sMode;
 
     const int level = blockIdx.x, frame = blockIdx.y;
-    const LevelGeom& g = G->lv[level];
-    const int n = candCount[frame * G->nlevels + level];
+    const LevelGeom& g = G.lv[level];
+    const int n = candCount[frame * G.nlevels + level];
     const int N = g.quota;
-    if (n == 0) { if (threadIdx.x == 0) selCount[frame * G->nlevels + level] = 0; return; }
-    unsigned long long* rec = candAll + (size_t)frame * G->candPerFrame + g.candBase;
+    if (n == 0) { if (threadIdx.x == 0) selCount[frame * G.nlevels + level] = 0; return; }
+    unsigned long long* rec = candAll + (size_t)frame * G.candPerFrame + g.candBase;
     uint32_t* recHi = reinterpret_cast<uint32_t*>(rec) + 1; // little endian: hi word = score<<24 | pos
     const uint32_t* recLo = reinterpret_cast<const uint32_t*>(rec);
 
@@ -252,7 +252,7 @@ octreeKernel(const GeomSet* __restrict__ G, unsigned long long* __restrict__ can
         atomicMax(&best[h & 0xffffffu], v);
     }
     __syncthreads();
-    orbx_keypoint* sel = selAll + (size_t)frame * G->selPerFrame + g.outBase;
+    orbx_keypoint* sel = selAll + (size_t)frame * G.selPerFrame + g.outBase;
     for (int p = tid; p < L; p += T) {
         const unsigned long long v = best[p];
         int x, y; decodeKey(g, ~(uint32_t)v, x, y);
@@ -262,7 +262,7 @@ octreeKernel(const GeomSet* __restrict__ G, unsigned long long* __restrict__ can
         kp.octave = level; kp.class_id = -1;
         if (p < g.outCap) sel[p] = kp; else atomicExch(err, 4);
     }
-    if (tid == 0) selCount[frame * G->nlevels + level] = min(L, g.outCap);
+    if (tid == 0) selCount[frame * G.nlevels + level] = min(L, g.outCap);
 }
 
 static size_t octreeSmem(int M) { return (size_t)M * (8 + 8 + 4 + 4 + 16 + 4 + 4 + 4 + 8) + 64; }
@@ -282,7 +282,7 @@ int launchOctree(Ctx* c, int batch)
     }
     stageBegin(c, ST_OCTREE);
     dim3 grid(g.nlevels, batch), block(kOctThreads);
-    octreeKernel<<<grid, block, smem, c->stream>>>(c->dGeom, c->dCand, c->dCandCount, c->dSel, c->dSelCount, M, c->dErr);
+    octreeKernel<<<grid, block, smem, c->stream>>>(c->geom, c->dCand, c->dCandCount, c->dSel, c->dSelCount, M, c->dErr);
     stageEnd(c, ST_OCTREE, 1);
     ORBX_CUDA(c, cudaGetLastError());
     return ORBX_OK;
