@@ -97,7 +97,8 @@ __global__ void atan2ProbeKernel(const float* yx, int n, float* out)
 }
 
 constexpr int kDescWarps = 8;
-constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitchW = 11;   // 37 rows x 44 bytes per warp
+constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitchW = 11;   // blurred patch: 37 rows x 44 bytes per warp
+constexpr int kRawRows = 2 * kHalfPatch + 1, kRawPitchW = 9;                   // raw patch: 31 rows x 36 bytes per warp
 
 __global__ void __launch_bounds__(kDescWarps * 32)
 describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
@@ -128,44 +129,78 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
     if (level == 0) { img = lvl0 + (size_t)frame * lvl0Frame; pitch = lvl0Pitch; }
     else { img = pyr + g.planeOff + (size_t)frame * g.pitch * g.h; pitch = (size_t)g.pitch; }
 
-    // ---- IC_Angle: lane = column u of the disc, unrolled over its 31 rows, so one warp load reads one image row
-    //      segment (1-2 sectors) instead of 31 different rows ----
+    // ---- stage both patches in shared memory with aligned word loads issued back to back (one memory round trip):
+    //      the 37 x 37 blurred patch for BRIEF (rotated pattern points stay within +-18; 10 words per row: 4 rows x 8
+    //      words per warp load + a 2-word tail) and the 31 x 31 raw patch for IC_Angle (9 words per row, 3 rows per load).
+    //      All later accesses are shared-memory loads with compile-time offsets. ----
+    __shared__ uint32_t sPatch[kDescWarps][kPatchRows * kPatchPitchW];
+    __shared__ uint32_t sRaw[kDescWarps][kRawRows * kRawPitchW];
+    uint32_t* patch = sPatch[threadIdx.x >> 5];
+    uint32_t* rawp = sRaw[threadIdx.x >> 5];
+    const int bp = g.pitch;
+    const int a0 = (cx - kPatchR) & ~3;                         // aligned first column of the blurred patch
+    const int offc = (cx - kPatchR) - a0 + kPatchR;             // byte column of the patch centre inside a staged row
+    const uint8_t* bsrc = blur + g.blurOff + (size_t)frame * g.pitch * g.h + (size_t)(cy - kPatchR) * bp + a0;
+    {
+        const int lr = lane >> 3, lk = lane & 7;
+        const uint8_t* p0 = bsrc + (size_t)lr * bp + 4 * lk;
+        #pragma unroll
+        for (int t = 0; t < (kPatchRows + 3) / 4; ++t) {        // words 0..7 of rows 4t + lr
+            const int r = 4 * t + lr;
+            uint32_t w = 0;
+            if (r < kPatchRows) w = __ldg(reinterpret_cast<const uint32_t*>(p0 + (size_t)(4 * t) * bp));
+            if (r < kPatchRows) patch[r * kPatchPitchW + lk] = w;
+        }
+        const int tr = lane >> 1, tk = 8 + (lane & 1);
+        const bool tailOk = a0 + 4 * tk + 3 < bp;               // the last word may start beyond the padded row: never used then
+        const uint8_t* p1 = bsrc + (size_t)tr * bp + 4 * tk;
+        #pragma unroll
+        for (int t = 0; t < (kPatchRows + 15) / 16; ++t) {      // words 8..9 of rows 16t + tr
+            const int r = 16 * t + tr;
+            uint32_t w = 0;
+            if (r < kPatchRows && tailOk) w = __ldg(reinterpret_cast<const uint32_t*>(p1 + (size_t)(16 * t) * bp));
+            if (r < kPatchRows) patch[r * kPatchPitchW + tk] = w;
+        }
+    }
+    const int ra0 = (cx - kHalfPatch) & ~3;
+    const int offr = (cx - kHalfPatch) - ra0 + kHalfPatch;      // byte column of the centre inside a staged raw row
+    const bool rawWords = ((((size_t)img) | pitch) & 3) == 0;
+    if (rawWords) {
+        const int lr = lane / 9, lk = lane - lr * 9;
+        const uint8_t* p0 = img + (size_t)(cy - kHalfPatch + lr) * pitch + ra0 + 4 * lk;
+        const bool ok = lane < 27 && (size_t)(ra0 + 4 * lk + 3) < pitch;
+        #pragma unroll
+        for (int t = 0; t < (kRawRows + 2) / 3; ++t) {          // rows 3t + lr
+            const int r = 3 * t + lr;
+            uint32_t w = 0;
+            if (ok && r < kRawRows) w = __ldg(reinterpret_cast<const uint32_t*>(p0 + (size_t)(3 * t) * pitch));
+            if (lane < 27 && r < kRawRows) rawp[r * kRawPitchW + lk] = w;
+        }
+    } else {                                                     // unaligned caller image (level 0 only): byte loads
+        uint8_t* rb = reinterpret_cast<uint8_t*>(rawp);
+        for (int i = lane; i < kRawRows * 31; i += 32) {
+            const int r = i / 31, c = i - r * 31;
+            rb[r * (kRawPitchW * 4) + (offr - kHalfPatch) + c] = img[(size_t)(cy - kHalfPatch + r) * pitch + cx - kHalfPatch + c];
+        }
+    }
+    __syncwarp();
+
+    // ---- IC_Angle: lane = column u of the disc, its 31 rows at compile-time offsets ----
     int m10 = 0, m01 = 0;
     if (lane < 2 * kHalfPatch + 1) {
         const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
-        const uint8_t* col = img + (size_t)(cy - kHalfPatch) * pitch + cx + u;
+        const uint8_t* col = reinterpret_cast<const uint8_t*>(rawp) + offr + u;
         int cs = 0;
         #pragma unroll
         for (int vi = 0; vi <= 2 * kHalfPatch; ++vi) {
             const int v = vi - kHalfPatch;
-            if (au <= G.umax[v < 0 ? -v : v]) { const int p = __ldg(col + (size_t)vi * pitch); cs += p; m01 += v * p; }
+            if (au <= G.umax[v < 0 ? -v : v]) { const int p = col[vi * (kRawPitchW * 4)]; cs += p; m01 += v * p; }
         }
         m10 = u * cs;
     }
     #pragma unroll
     for (int o = 16; o > 0; o >>= 1) { m10 += __shfl_xor_sync(0xffffffffu, m10, o); m01 += __shfl_xor_sync(0xffffffffu, m01, o); }
     const float angle = fastAtan2Dev((float)m01, (float)m10);
-
-    // ---- stage the 37 x 37 blurred patch (rotated pattern points stay within +-18) in shared memory: 10 aligned
-    //      words per row, 3 rows per warp load ----
-    __shared__ uint32_t sPatch[kDescWarps][kPatchRows * kPatchPitchW];
-    uint32_t* patch = sPatch[threadIdx.x >> 5];
-    const uint8_t* blurPlane = blur + g.blurOff + (size_t)frame * g.pitch * g.h;
-    const int bp = g.pitch;
-    const int a0 = (cx - kPatchR) & ~3;                         // aligned first column
-    const int offc = (cx - kPatchR) - a0 + kPatchR;             // byte column of the patch centre inside a staged row
-    #pragma unroll
-    for (int t = 0; t < (kPatchRows * 10 + 31) / 32; ++t) {
-        const int i = t * 32 + lane;
-        if (i < kPatchRows * 10) {
-            const int r = i / 10, k = i - r * 10;
-            const int col = a0 + 4 * k;
-            uint32_t w = 0;
-            if (col + 3 < bp) w = __ldg(reinterpret_cast<const uint32_t*>(blurPlane + (size_t)(cy - kPatchR + r) * bp + col));
-            patch[r * kPatchPitchW + k] = w;
-        }
-    }
-    __syncwarp();
 
     // ---- steered BRIEF on the blurred patch: lane = descriptor byte ----
     const float factorPI = (float)(3.14159265358979323846 / 180.f);
