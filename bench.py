@@ -47,9 +47,9 @@ def algorithmic_bytes():
             "describe": NFEAT * (749 + 512 + 28 + 32), "octree": 0}
 
 
-def make_frames(n):
+def make_frames(n, first=0):
     import synth
-    return np.stack([synth.frame(1000 + i, W, H) for i in range(n)])
+    return np.stack([synth.frame(1000 + first + i, W, H) for i in range(n)])
 
 
 class ClockSampler(threading.Thread):
@@ -132,6 +132,36 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def hamming_gmatch(P, ex, dev, n=10000, pairs=16, reps=3):
+    """K6 many-vs-many (segments = keyframe pairs of n x n descriptors, device resident): GMatch/s on this rank."""
+    import torch
+    L = P.lib()
+    g = torch.Generator(device="cpu").manual_seed(1234)
+    q = torch.randint(0, 256, (pairs * n, 32), dtype=torch.uint8, generator=g).to(dev)
+    t = torch.randint(0, 256, (pairs * n, 32), dtype=torch.uint8, generator=g).to(dev)
+    seg = np.arange(pairs + 1, dtype=np.int32) * n
+    out = [torch.empty(pairs * n, dtype=torch.int32, device=dev) for _ in range(3)]
+    vp = ctypes.c_void_p
+
+    def call():
+        rc = L.orbx_hamming_best2(ex._h, vp(q.data_ptr()), pairs * n, vp(t.data_ptr()), pairs * n, seg.ctypes.data_as(vp), None,
+                                  seg.ctypes.data_as(vp), None, pairs, None, 3, vp(out[0].data_ptr()), vp(out[1].data_ptr()),
+                                  vp(out[2].data_ptr()))
+        assert rc == 0, rc
+    call()
+    ex.sync()
+    ex.set_profiling(True)
+    ex.reset_stats()
+    for _ in range(reps):
+        call()
+    ex.sync()
+    ms = ex.stage_stats()["hamming"][0] / reps
+    ex.set_profiling(False)
+    peak, pms = ctypes.c_double(), ctypes.c_double()
+    L.orbx_test_popc_peak(dev.index or 0, 1 << 16, ctypes.byref(peak), ctypes.byref(pms))
+    return pairs * n * n / (ms * 1e-3) / 1e9, ms, peak.value, reps
+
+
 def run_orbx(args, rank, world):
     import torch
     import torch.distributed as dist
@@ -142,7 +172,7 @@ def run_orbx(args, rank, world):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     B = args.batch
-    frames = make_frames(DISTINCT)
+    frames = make_frames(DISTINCT, rank * DISTINCT)   # every rank extracts its own frames
     reps = (B + DISTINCT - 1) // DISTINCT
     host = torch.from_numpy(np.concatenate([frames] * reps)[:B]).contiguous().pin_memory()
     ex = P.ORBextractor(NFEAT, SCALE, NLEVELS, INI, MINTH, device=local, max_w=W, max_h=H, max_batch=B)
@@ -152,6 +182,7 @@ def run_orbx(args, rank, world):
     d_desc = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
     d_n = torch.zeros(B, dtype=torch.int32, device=dev)
     stream = torch.cuda.ExternalStream(ex.stream(), device=dev)
+    sh = importlib.import_module("orb-slam2-noted_b200.sharding")
     gather = None
     if world > 1:  # final gather of keypoint/descriptor records over NVLink (fixed padded records)
         gather = [torch.empty((world * B, cap, 28), dtype=torch.uint8, device=dev),
@@ -162,9 +193,7 @@ def run_orbx(args, rank, world):
         ex.extract_batch_device(d_img, d_kps, d_desc, d_n)
         if gather is not None:
             with torch.cuda.stream(stream):
-                dist.all_gather_into_tensor(gather[0], d_kps)
-                dist.all_gather_into_tensor(gather[1], d_desc)
-                dist.all_gather_into_tensor(gather[2], d_n)
+                sh.gather_frames(d_kps, d_desc, d_n, world, out=gather)
 
     def barrier():
         torch.cuda.synchronize()
@@ -226,6 +255,14 @@ def run_orbx(args, rank, world):
         e2e_s = float(t.item())
     e2e = world * B * e2e_steps / e2e_s
 
+    gm, gm_ms, popc_peak, gm_reps = hamming_gmatch(P, ex, dev)
+    if world > 1:
+        t = torch.tensor([gm], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        gm_total = float(t.item())
+    else:
+        gm_total = gm
+
     if rank == 0:
         peaks = {}
         try:
@@ -240,6 +277,12 @@ def run_orbx(args, rank, world):
         launches_per_step = 7 if dom == "pyramid" else 1
         ach = alg[dom] * B / launches_per_step / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms > 0 else 0.0
         total_alg = sum(alg.values())
+        traffic = None
+        try:  # dram__bytes_read.sum + dram__bytes_write.sum per frame from the committed ncu --set full capture
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+            traffic = tr["bytes_per_frame"].get(dom) * B / launches_per_step
+        except Exception:
+            pass
         stage_ms = {k: round(v[0] / args.steps, 4) for k, v in stats.items() if v[0] > 0}
         cores = os.cpu_count() or 1
         cpu = None
@@ -251,14 +294,21 @@ def run_orbx(args, rank, world):
                 "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": {"workload": f"{W}x{H} gray, {NFEAT} features, {NLEVELS} levels, scale {SCALE}, FAST {INI}/{MINTH}",
+                           "frames": "tests/synth.py kind=texture (scene-like: multi-octave shading + rotated rectangles + noise; "
+                                     "~3% of pixels are FAST corners at threshold 7)",
                            "batch_per_gpu": B, "distinct_frames": DISTINCT, "keypoints_per_frame": nkp / B,
                            "l2": f"per-step working set {B * (total_alg + W * H) / 1e6:.0f} MB > 126 MB L2 (no flush needed)",
                            "parallelism": f"frames sharded, {world} rank(s)" + (", NCCL all_gather of results" if world > 1 else "")},
                 "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
-                             "traffic": None, "peak_source": "measured" if peaks else "fallback",
+                             "traffic": traffic, "peak_source": "measured" if peaks else "fallback",
                              "algorithmic_bytes_per_frame": alg[dom], "ms_per_launch": per_launch_ms,
                              "pipeline_frac": total_alg * value / world / 1e9 / hbm, "stage_ms_per_step": stage_ms},
                 "cpu_baseline": cpu,
+                "hamming": {"metric": "hamming_gmatch_per_s", "value": gm_total, "unit": "GMatch/s", "per_gpu": gm,
+                            "workload": "brute force 10000 x 10000 descriptors per keyframe pair, 16 pairs per GPU per call, device resident",
+                            "ms_per_call": gm_ms, "calls": gm_reps,
+                            "roofline": {"bound": "popc", "achieved": gm * 8.0, "peak": popc_peak / 1e9, "unit": "GPOPC32/s",
+                                         "frac": gm * 8e9 / popc_peak, "peak_source": "measured in this run (orbx_test_popc_peak)"}},
                 "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": B * W * H,
                         "d2h_bytes_per_step": B * cap * 60 + 4 * B, "steps": e2e_steps},
                 "gpu_launches": int(launches), "clocks": sampler.summary()}

@@ -74,6 +74,11 @@ int orbx_pyramid_level(orbx_ctx* ctx, int frame, int level, int border, int flag
                        size_t dst_stride, int* w, int* h);
 int orbx_level_size(const orbx_ctx* ctx, int level, int w0, int h0, int* w, int* h);
 
+/* Frames per pipeline chunk of orbx_extract_batch when the images are HOST buffers (default 64, env ORBX_CHUNK; 0 = whole
+ * batch in one pass): the H2D of chunk i+1 and the D2H of chunk i-1 overlap the kernels of chunk i.  Device-resident
+ * batches always run in one pass. */
+int orbx_set_chunk(orbx_ctx* ctx, int frames);
+
 /* ---- stream / instrumentation (used by bench.py and tests; not part of the reference surface) ---- */
 int orbx_sync(orbx_ctx* ctx);
 void* orbx_stream(orbx_ctx* ctx);                 /* cudaStream_t */

@@ -46,6 +46,7 @@ def lib():
     L.orbx_pyramid_level.argtypes = [vp, ci, ci, ci, ci, vp, sz, ip, ip]
     L.orbx_level_size.argtypes = [vp, ci, ci, ci, ip, ip]
     L.orbx_sync.argtypes = [vp]
+    L.orbx_set_chunk.argtypes = [vp, ci]
     L.orbx_stream.argtypes = [vp]
     L.orbx_stream.restype = vp
     L.orbx_set_profiling.argtypes = [vp, ci]
@@ -193,6 +194,10 @@ class ORBextractor:
         rc = self._lib.orbx_extract_batch(self._h, _ptr(images), B, w, h, images.stride(1), images.stride(0), flags,
                                           _ptr(kps), _ptr(desc), cap, _ptr(n_out))
         self._check(rc, "orbx_extract_batch(device)")
+
+    def set_chunk(self, frames):
+        """Frames per pipeline chunk of extract_batch (0 = whole batch at once)."""
+        self._check(self._lib.orbx_set_chunk(self._h, int(frames)), "orbx_set_chunk")
 
     def sync(self):
         self._check(self._lib.orbx_sync(self._h), "orbx_sync")

@@ -26,7 +26,7 @@ gauss9Kernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0
 {
     __shared__ __align__(16) uint32_t raw[kRawH][kRawW / 4];
     __shared__ __align__(16) uint2 hsum[kRawH][kBlurTW / 4];   // 4 x u16 per entry
-    const int frame = blockIdx.y;
+    const int frame = blockIdx.y + G.frame0;
     int level = 0;
     while (level + 1 < G.nlevels && (int)blockIdx.x >= G.lv[level + 1].tileBase) ++level;
     const LevelGeom& g = G.lv[level];
@@ -103,12 +103,13 @@ gauss9Kernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0
     }
 }
 
-int launchBlur(Ctx* c, int batch)
+int launchBlur(Ctx* c, int frame0, int batch)
 {
-    const GeomSet& g = c->geom;
+    GeomSet g = c->geom;
+    g.frame0 = frame0;
     stageBegin(c, ST_BLUR);
     dim3 grid(g.blurTilesPerFrame, batch), block(kBlurThreads);
-    gauss9Kernel<<<grid, block, 0, c->stream>>>(c->geom, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur);
+    gauss9Kernel<<<grid, block, 0, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur);
     stageEnd(c, ST_BLUR, 1);
     ORBX_CUDA(c, cudaGetLastError());
     return ORBX_OK;

@@ -109,7 +109,7 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
 {
     const int lane = threadIdx.x & 31;
     const int slot = blockIdx.x * kDescWarps + (threadIdx.x >> 5);
-    const int frame = blockIdx.y;
+    const int frame = blockIdx.y + G.frame0;
     if (slot >= G.selPerFrame) return;
     int level = 0;
     while (level + 1 < G.nlevels && slot >= G.lv[level + 1].outBase) ++level;
@@ -227,12 +227,13 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
     }
 }
 
-int launchDescribe(Ctx* c, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN)
+int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN)
 {
-    const GeomSet& g = c->geom;
+    GeomSet g = c->geom;
+    g.frame0 = frame0;
     stageBegin(c, ST_DESCRIBE);
     dim3 grid((g.selPerFrame + kDescWarps - 1) / kDescWarps, batch), block(kDescWarps * 32);
-    describeKernel<<<grid, block, 0, c->stream>>>(c->geom, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur,
+    describeKernel<<<grid, block, 0, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur,
                                                  c->dSel, c->dSelCount, dKps, dDesc, capPerFrame, dN, c->dErr);
     stageEnd(c, ST_DESCRIBE, 1);
     ORBX_CUDA(c, cudaGetLastError());

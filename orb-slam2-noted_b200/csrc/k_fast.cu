@@ -85,7 +85,7 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     __shared__ int sGroupN, sCornerN, sOutN, sBase;
     __shared__ int sNms[kMaxCellsPerStrip], sIni[kMaxCellsPerStrip];
 
-    const int frame = blockIdx.y;
+    const int frame = blockIdx.y + G.frame0;
     int level = 0;
     while (level + 1 < G.nlevels && (int)blockIdx.x >= G.lv[level + 1].stripBase) ++level;
     const LevelGeom& g = G.lv[level];
@@ -345,11 +345,12 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     }
 }
 
-int launchFast(Ctx* c, int batch)
+int launchFast(Ctx* c, int frame0, int batch)
 {
-    const GeomSet& g = c->geom;
+    GeomSet g = c->geom;
+    g.frame0 = frame0;
     stageBegin(c, ST_FAST);
-    ORBX_CUDA(c, cudaMemsetAsync(c->dCandCount, 0, sizeof(int) * (size_t)batch * g.nlevels, c->stream));
+    ORBX_CUDA(c, cudaMemsetAsync(c->dCandCount + (size_t)frame0 * g.nlevels, 0, sizeof(int) * (size_t)batch * g.nlevels, c->stream));
     int launches = 0;
     if (g.stripsPerFrame > 0) {
         const int TP = g.fastTilePitch, TR = g.fastTileRows, SP = g.fastScorePitch;
@@ -364,7 +365,7 @@ int launchFast(Ctx* c, int batch)
             configured = smem;
         }
         dim3 grid(g.stripsPerFrame, batch), block(kFastThreads);
-        fastStripKernel<<<grid, block, smem, c->stream>>>(c->geom, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr,
+        fastStripKernel<<<grid, block, smem, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr,
                                                          c->dCand, c->dCandCount, TP, TR, SP);
         launches = 1;
     }

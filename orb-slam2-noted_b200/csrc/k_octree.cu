@@ -75,7 +75,7 @@ octreeKernel(const __grid_constant__ GeomSet G, unsigned long long* __restrict__
     __shared__ int warpSums[kOctThreads / 32];
     __shared__ int sL, sNSplit, sC, sFinish, sMode;
 
-    const int level = blockIdx.x, frame = blockIdx.y;
+    const int level = blockIdx.x, frame = blockIdx.y + G.frame0;
     const LevelGeom& g = G.lv[level];
     const int n = candCount[frame * G.nlevels + level];
     const int N = g.quota;
@@ -267,9 +267,10 @@ octreeKernel(const __grid_constant__ GeomSet G, unsigned long long* __restrict__
 
 static size_t octreeSmem(int M) { return (size_t)M * (8 + 8 + 4 + 4 + 16 + 4 + 4 + 4 + 8) + 64; }
 
-int launchOctree(Ctx* c, int batch)
+int launchOctree(Ctx* c, int frame0, int batch)
 {
-    const GeomSet& g = c->geom;
+    GeomSet g = c->geom;
+    g.frame0 = frame0;
     int M = 0;
     for (int l = 0; l < g.nlevels; ++l) M = max(M, g.lv[l].outCap);
     M = (M + 7) & ~7;
@@ -282,7 +283,7 @@ int launchOctree(Ctx* c, int batch)
     }
     stageBegin(c, ST_OCTREE);
     dim3 grid(g.nlevels, batch), block(kOctThreads);
-    octreeKernel<<<grid, block, smem, c->stream>>>(c->geom, c->dCand, c->dCandCount, c->dSel, c->dSelCount, M, c->dErr);
+    octreeKernel<<<grid, block, smem, c->stream>>>(g, c->dCand, c->dCandCount, c->dSel, c->dSelCount, M, c->dErr);
     stageEnd(c, ST_OCTREE, 1);
     ORBX_CUDA(c, cudaGetLastError());
     return ORBX_OK;

@@ -21,7 +21,7 @@ __device__ __forceinline__ void hpass(const uint8_t* __restrict__ S, const int (
 __global__ void __launch_bounds__(128)
 resizeLinearKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sFrame, int sw, int sh,
                    uint8_t* __restrict__ dst, size_t dPitch, size_t dFrame, int dw, int dh,
-                   const ResizeTap* __restrict__ tapX, const ResizeTap* __restrict__ tapY)
+                   const ResizeTap* __restrict__ tapX, const ResizeTap* __restrict__ tapY, int frame0)
 {
     const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (x0 >= dw) return;
@@ -31,8 +31,8 @@ resizeLinearKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sFrame
         const ResizeTap tx = tapX[min(x0 + i, dw - 1)];
         sx[i] = tx.s; sx1[i] = min(tx.s + 1, sw - 1); c0[i] = tx.c0; c1[i] = tx.c1;
     }
-    const uint8_t* S = src + (size_t)blockIdx.z * sFrame;
-    uint8_t* D = dst + (size_t)blockIdx.z * dFrame;
+    const uint8_t* S = src + (size_t)(blockIdx.z + frame0) * sFrame;
+    uint8_t* D = dst + (size_t)(blockIdx.z + frame0) * dFrame;
     const int yb = blockIdx.y * kResizeRows, ye = min(yb + kResizeRows, dh);
     int rowA = -1, rowB = -1, tA[4] = {0, 0, 0, 0}, tB[4] = {0, 0, 0, 0};
     for (int y = yb; y < ye; ++y) {
@@ -60,7 +60,7 @@ resizeLinearKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sFrame
     }
 }
 
-int launchPyramid(Ctx* c, int batch)
+int launchPyramid(Ctx* c, int frame0, int batch)
 {
     const GeomSet& g = c->geom;
     stageBegin(c, ST_PYRAMID);
@@ -73,7 +73,7 @@ int launchPyramid(Ctx* c, int batch)
         else { src = c->dPyr + s.planeOff; sp = (size_t)s.pitch; sf = (size_t)s.pitch * s.h; }
         dim3 grid((d.w + 511) / 512, (d.h + kResizeRows - 1) / kResizeRows, batch), block(128);
         resizeLinearKernel<<<grid, block, 0, c->stream>>>(src, sp, sf, s.w, s.h, c->dPyr + d.planeOff, (size_t)d.pitch,
-                                                         (size_t)d.pitch * d.h, d.w, d.h, c->dTapX[l], c->dTapY[l]);
+                                                         (size_t)d.pitch * d.h, d.w, d.h, c->dTapX[l], c->dTapY[l], frame0);
         ++launches;
     }
     stageEnd(c, ST_PYRAMID, launches);

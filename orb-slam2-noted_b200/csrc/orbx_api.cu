@@ -5,6 +5,7 @@
 #include <math.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 #include <new>
 #include <algorithm>
 
@@ -231,6 +232,9 @@ int orbx_create(orbx_ctx** out, int device, int nfeatures, float scale_factor, i
     do {
         if (cudaSetDevice(device) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
+        if (cudaStreamCreateWithFlags(&c->sIn, cudaStreamNonBlocking) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
+        if (cudaStreamCreateWithFlags(&c->sOut, cudaStreamNonBlocking) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
+        if (const char* e = getenv("ORBX_CHUNK")) c->chunk = atoi(e);
         if (cudaMalloc(&c->dGeom, sizeof(GeomSet)) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (cudaMalloc(&c->dCandCount, sizeof(int) * (size_t)max_batch * kMaxLevels) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (cudaMalloc(&c->dSelCount, sizeof(int) * (size_t)max_batch * kMaxLevels) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
@@ -256,6 +260,11 @@ void orbx_destroy(orbx_ctx* h)
                     c->dOutKp, c->dOutDesc, c->dOutN, c->dIn, c->dScratch};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->hPinned) cudaFreeHost(c->hPinned);
+    if (c->evFence) cudaEventDestroy(c->evFence);
+    for (cudaEvent_t e : c->evIn) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->evDone) cudaEventDestroy(e);
+    if (c->sIn) cudaStreamDestroy(c->sIn);
+    if (c->sOut) cudaStreamDestroy(c->sOut);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete h;
 }
@@ -380,53 +389,90 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
     if (rc) return rc;
     const GeomSet& g = c->geom;
 
-    if (flags & ORBX_IN_DEVICE) {
-        c->lvl0 = imgs; c->lvl0Pitch = stride; c->lvl0FrameStride = frame_stride;
-    } else {
-        stageBegin(c, ST_H2D);
-        uint8_t* d0 = c->dPyr + g.lv[0].planeOff;
-        const size_t dp = (size_t)g.lv[0].pitch;
-        if (batch == 1 || frame_stride == stride * (size_t)hgt) {
-            ORBX_CUDA(c, cudaMemcpy2DAsync(d0, dp, imgs, stride, (size_t)w, (size_t)hgt * batch, cudaMemcpyHostToDevice, c->stream));
-        } else {
-            for (int b = 0; b < batch; ++b)
-                ORBX_CUDA(c, cudaMemcpy2DAsync(d0 + (size_t)b * dp * hgt, dp, imgs + (size_t)b * frame_stride, stride, (size_t)w,
-                                               (size_t)hgt, cudaMemcpyHostToDevice, c->stream));
-        }
-        stageEnd(c, ST_H2D, 0);
-        c->lvl0 = d0; c->lvl0Pitch = dp; c->lvl0FrameStride = dp * hgt;
-    }
+    const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
+    uint8_t* d0 = c->dPyr + g.lv[0].planeOff;
+    const size_t dp = (size_t)g.lv[0].pitch;
+    if (inDev) { c->lvl0 = imgs; c->lvl0Pitch = stride; c->lvl0FrameStride = frame_stride; }
+    else { c->lvl0 = d0; c->lvl0Pitch = dp; c->lvl0FrameStride = dp * hgt; }
     c->lastBatch = batch;
 
     orbx_keypoint* dK = kps; uint8_t* dD = desc; int* dN = n_out;
-    if (!(flags & ORBX_OUT_DEVICE)) {
+    if (!outDev) {
         rc = ensureOutStaging(c, cap);
         if (rc) return rc;
         dK = c->dOutKp; dD = c->dOutDesc; dN = c->dOutN;
     }
-    if ((rc = launchPyramid(c, batch))) return rc;
-    if ((rc = launchFast(c, batch))) return rc;
-    if ((rc = launchOctree(c, batch))) return rc;
-    if ((rc = launchBlur(c, batch))) return rc;
-    if ((rc = launchDescribe(c, batch, dK, dD, (flags & ORBX_OUT_DEVICE) ? cap : c->outCap, dN))) return rc;
-    if (flags & ORBX_OUT_DEVICE) return ORBX_OK; // asynchronous; orbx_sync() reports device-side errors
+    const int sc = outDev ? cap : c->outCap; // capacity per frame of the buffers the kernels write (>= cap)
 
-    stageBegin(c, ST_D2H);
-    const int sc = c->outCap; // staging capacity per frame (>= cap)
-    ORBX_CUDA(c, cudaMemcpyAsync(n_out, dN, sizeof(int) * (size_t)batch, cudaMemcpyDeviceToHost, c->stream));
-    if (sc == cap) {
-        ORBX_CUDA(c, cudaMemcpyAsync(kps, dK, sizeof(orbx_keypoint) * (size_t)cap * batch, cudaMemcpyDeviceToHost, c->stream));
-        ORBX_CUDA(c, cudaMemcpyAsync(desc, dD, (size_t)32 * cap * batch, cudaMemcpyDeviceToHost, c->stream));
-    } else {
-        ORBX_CUDA(c, cudaMemcpy2DAsync(kps, sizeof(orbx_keypoint) * (size_t)cap, dK, sizeof(orbx_keypoint) * (size_t)sc,
-                                       sizeof(orbx_keypoint) * (size_t)cap, (size_t)batch, cudaMemcpyDeviceToHost, c->stream));
-        ORBX_CUDA(c, cudaMemcpy2DAsync(desc, (size_t)32 * cap, dD, (size_t)32 * sc, (size_t)32 * cap, (size_t)batch,
-                                       cudaMemcpyDeviceToHost, c->stream));
+    // Chunked pipeline: the stages of one chunk run back to back (its pyramid/blur planes stay in the 126 MB L2), and
+    // with host buffers the H2D of chunk i+1 and the D2H of chunk i-1 overlap the kernels of chunk i.
+    // device-resident input: one pass over the whole batch (larger launches are more efficient and there is no copy to hide)
+    const int chunk = (!inDev && c->chunk > 0) ? c->chunk : batch;
+    if (!outDev && c->hPinnedBytes < sizeof(int) * (size_t)c->maxBatch) {   // pinned landing zone for n_out: keeps the D2H asynchronous
+        if (c->hPinned) cudaFreeHost(c->hPinned);
+        c->hPinned = nullptr; c->hPinnedBytes = 0;
+        ORBX_CUDA(c, cudaMallocHost((void**)&c->hPinned, sizeof(int) * (size_t)c->maxBatch));
+        c->hPinnedBytes = sizeof(int) * (size_t)c->maxBatch;
     }
-    stageEnd(c, ST_D2H, 0);
+    int* hN = reinterpret_cast<int*>(c->hPinned);
+    const int nChunks = (batch + chunk - 1) / chunk;
+    while ((int)c->evIn.size() < nChunks) { cudaEvent_t e; ORBX_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); c->evIn.push_back(e); }
+    while ((int)c->evDone.size() < nChunks) { cudaEvent_t e; ORBX_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); c->evDone.push_back(e); }
+    if (!inDev) {
+        if (!c->evFence) ORBX_CUDA(c, cudaEventCreateWithFlags(&c->evFence, cudaEventDisableTiming));
+        ORBX_CUDA(c, cudaEventRecord(c->evFence, c->stream));
+        ORBX_CUDA(c, cudaStreamWaitEvent(c->sIn, c->evFence, 0));
+    }
+    for (int i = 0; i < nChunks; ++i) {
+        const int f0 = i * chunk, n = std::min(chunk, batch - f0);
+        if (!inDev) {
+            if (frame_stride == stride * (size_t)hgt || n == 1) {
+                ORBX_CUDA(c, cudaMemcpy2DAsync(d0 + (size_t)f0 * dp * hgt, dp, imgs + (size_t)f0 * frame_stride, stride, (size_t)w,
+                                               (size_t)hgt * n, cudaMemcpyHostToDevice, c->sIn));
+            } else {
+                for (int b = f0; b < f0 + n; ++b)
+                    ORBX_CUDA(c, cudaMemcpy2DAsync(d0 + (size_t)b * dp * hgt, dp, imgs + (size_t)b * frame_stride, stride, (size_t)w,
+                                                   (size_t)hgt, cudaMemcpyHostToDevice, c->sIn));
+            }
+            ORBX_CUDA(c, cudaEventRecord(c->evIn[i], c->sIn));
+            ORBX_CUDA(c, cudaStreamWaitEvent(c->stream, c->evIn[i], 0));
+        }
+        if ((rc = launchPyramid(c, f0, n))) return rc;
+        if ((rc = launchFast(c, f0, n))) return rc;
+        if ((rc = launchOctree(c, f0, n))) return rc;
+        if ((rc = launchBlur(c, f0, n))) return rc;
+        if ((rc = launchDescribe(c, f0, n, dK, dD, sc, dN))) return rc;
+        if (!outDev) {
+            ORBX_CUDA(c, cudaEventRecord(c->evDone[i], c->stream));
+            ORBX_CUDA(c, cudaStreamWaitEvent(c->sOut, c->evDone[i], 0));
+            ORBX_CUDA(c, cudaMemcpyAsync(hN + f0, dN + f0, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, c->sOut));
+            if (sc == cap) {
+                ORBX_CUDA(c, cudaMemcpyAsync(kps + (size_t)f0 * cap, dK + (size_t)f0 * cap, sizeof(orbx_keypoint) * (size_t)cap * n,
+                                             cudaMemcpyDeviceToHost, c->sOut));
+                ORBX_CUDA(c, cudaMemcpyAsync(desc + (size_t)32 * f0 * cap, dD + (size_t)32 * f0 * cap, (size_t)32 * cap * n,
+                                             cudaMemcpyDeviceToHost, c->sOut));
+            } else {
+                ORBX_CUDA(c, cudaMemcpy2DAsync(kps + (size_t)f0 * cap, sizeof(orbx_keypoint) * (size_t)cap, dK + (size_t)f0 * sc,
+                                               sizeof(orbx_keypoint) * (size_t)sc, sizeof(orbx_keypoint) * (size_t)cap, (size_t)n,
+                                               cudaMemcpyDeviceToHost, c->sOut));
+                ORBX_CUDA(c, cudaMemcpy2DAsync(desc + (size_t)32 * f0 * cap, (size_t)32 * cap, dD + (size_t)32 * f0 * sc, (size_t)32 * sc,
+                                               (size_t)32 * cap, (size_t)n, cudaMemcpyDeviceToHost, c->sOut));
+            }
+        }
+    }
+    if (outDev) return ORBX_OK; // asynchronous; orbx_sync() reports device-side errors
+    ORBX_CUDA(c, cudaStreamSynchronize(c->sOut));
+    memcpy(n_out, hN, sizeof(int) * (size_t)batch);
     rc = checkDeviceError(c);
     if (rc) return rc;
     for (int b = 0; b < batch; ++b) if (n_out[b] > cap) return ORBX_E_CAPACITY;
+    return ORBX_OK;
+}
+
+int orbx_set_chunk(orbx_ctx* h, int frames)
+{
+    if (!h || frames < 0) return ORBX_E_INVALID;
+    h->c.chunk = frames;
     return ORBX_OK;
 }
 

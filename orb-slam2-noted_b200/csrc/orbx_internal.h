@@ -49,6 +49,7 @@ struct GeomSet {            // what kernels need, uploaded to constant memory on
     int selPerFrame;
     int blurTilesPerFrame;
     int stripsPerFrame, fastTilePitch, fastTileRows, fastScorePitch;
+    int frame0;                 // first frame of this launch (chunked pipeline); frame = blockIdx.y + frame0
     int iniTh, minTh;
     int umax[16];
 };
@@ -56,6 +57,10 @@ struct GeomSet {            // what kernels need, uploaded to constant memory on
 struct Ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t sIn = nullptr, sOut = nullptr;   // copy streams of the chunked pipeline (H2D / D2H overlap compute)
+    std::vector<cudaEvent_t> evIn, evDone;
+    cudaEvent_t evFence = nullptr;                // orders a new call's H2D after the previous call's kernels
+    int chunk = 64;                               // frames per pipeline chunk (stages of a chunk stay L2-resident)
     int nfeatures = 0, nlevels = 0, iniTh = 0, minTh = 0;
     float scaleFactor = 0;
     float scale[kMaxLevels], invScale[kMaxLevels], sigma2[kMaxLevels], invSigma2[kMaxLevels];
@@ -101,11 +106,12 @@ void stageEnd(Ctx* c, int stage, int launches);
 int ensureScratch(Ctx* c, size_t bytes);
 
 // kernels (one launcher per stage; all asynchronous on c->stream) -------------------------------
-int launchPyramid(Ctx* c, int batch);
-int launchFast(Ctx* c, int batch);
-int launchOctree(Ctx* c, int batch);
-int launchBlur(Ctx* c, int batch);
-int launchDescribe(Ctx* c, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN);
+// frames [frame0, frame0 + batch) of the current batch
+int launchPyramid(Ctx* c, int frame0, int batch);
+int launchFast(Ctx* c, int frame0, int batch);
+int launchOctree(Ctx* c, int frame0, int batch);
+int launchBlur(Ctx* c, int frame0, int batch);
+int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN);
 int launchBorderCopy(Ctx* c, const uint8_t* src, int w, int h, size_t pitch, uint8_t* dst, size_t dpitch, int border);
 
 } // namespace orbx
