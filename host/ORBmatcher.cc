@@ -1,0 +1,252 @@
+// Host glue of the drop-in ORB_SLAM2::ORBmatcher (include/ORBmatcher.h) over the C ABI (include/orbx.h).
+// Replaces the bodies of the reference's src/ORBmatcher.cc named below; every Hamming distance, best/second-best
+// decision, claim, ratio test and rotation-histogram vote runs on the GPU (csrc/k_match.cu, csrc/k_project.cu).
+#include "ORBmatcher.h"
+#include "orbx.h"
+#include <cmath>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+
+namespace ORB_SLAM2
+{
+
+const int ORBmatcher::TH_HIGH = 100;     // src/ORBmatcher.cc:56
+const int ORBmatcher::TH_LOW = 50;       // :57
+const int ORBmatcher::HISTO_LENGTH = 30; // :58
+
+namespace {
+struct CtxHolder {
+    orbx_ctx* ctx = nullptr;
+    ~CtxHolder() { if (ctx) orbx_destroy(ctx); }
+};
+void check(int rc, const char* what)
+{
+    if (rc != ORBX_OK) throw std::runtime_error(std::string(what) + ": " + orbx_strerror(rc));
+}
+static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_keypoint), "cv::KeyPoint must be the 28-byte POD the kernels read");
+
+// DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) -> CSR in map order (ascending node id)
+struct FlatFeatureVector {
+    std::vector<int32_t> node_id, node_off, feat;
+    explicit FlatFeatureVector(const DBoW2::FeatureVector& fv)
+    {
+        node_off.push_back(0);
+        for (DBoW2::FeatureVector::const_iterator it = fv.begin(); it != fv.end(); ++it) {
+            node_id.push_back((int32_t)it->first);
+            for (size_t k = 0; k < it->second.size(); ++k) feat.push_back((int32_t)it->second[k]);
+            node_off.push_back((int32_t)feat.size());
+        }
+    }
+};
+
+// descriptors of a Frame / KeyFrame are rows of an N x 32 CV_8U Mat; the kernels want them contiguous
+const uint8_t* contiguous(const cv::Mat& d, std::vector<uint8_t>& tmp)
+{
+    if (d.isContinuous()) return d.data;
+    tmp.resize((size_t)d.rows * 32);
+    for (int i = 0; i < d.rows; ++i) memcpy(&tmp[(size_t)i * 32], d.ptr<uint8_t>(i), 32);
+    return tmp.data();
+}
+
+orbx_bow_side makeSide(const cv::Mat& desc, std::vector<uint8_t>& tmp, const std::vector<cv::KeyPoint>& keys,
+                       const std::vector<uint8_t>* has, const std::vector<float>* uright, int N, const FlatFeatureVector& fv)
+{
+    orbx_bow_side s;
+    s.desc = contiguous(desc, tmp);
+    s.keys = reinterpret_cast<const orbx_keypoint*>(keys.data());
+    s.has_point = has ? has->data() : nullptr;
+    s.uright = (uright && !uright->empty()) ? uright->data() : nullptr;
+    s.n = N;
+    s.nnodes = (int)fv.node_id.size();
+    s.node_id = fv.node_id.data(); s.node_off = fv.node_off.data(); s.feat = fv.feat.data();
+    return s;
+}
+} // namespace
+
+orbx_ctx* ORBmatcher::Context()
+{
+    static thread_local CtxHolder holder;
+    if (!holder.ctx) check(orbx_create(&holder.ctx, 0, 1000, 1.2f, 8, 20, 7, 64, 64, 1), "orbx_create (ORBmatcher)");
+    return holder.ctx;
+}
+
+ORBmatcher::ORBmatcher(float nnratio, bool checkOri) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+
+int ORBmatcher::DescriptorDistance(const cv::Mat& a, const cv::Mat& b)
+{
+    const uint32_t* pa = a.ptr<uint32_t>();
+    const uint32_t* pb = b.ptr<uint32_t>();
+    int dist = 0;
+    for (int i = 0; i < 8; ++i) dist += __builtin_popcount(pa[i] ^ pb[i]);
+    return dist;
+}
+
+float ORBmatcher::RadiusByViewingCos(const float& viewCos) { return viewCos > 0.998 ? 2.5f : 4.0f; } // :194-201
+
+int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches)
+{
+    const std::vector<MapPoint*> vpMapPointsKF = pKF->GetMapPointMatches();
+    vpMapPointMatches = std::vector<MapPoint*>(F.N, static_cast<MapPoint*>(NULL));
+    std::vector<uint8_t> has(pKF->N, 0), t1, t2;
+    for (int i = 0; i < pKF->N; ++i) has[i] = vpMapPointsKF[i] && !vpMapPointsKF[i]->isBad();     // :307-313
+    const FlatFeatureVector fvKF(pKF->mFeatVec), fvF(F.mFeatVec);
+    const orbx_bow_side s1 = makeSide(pKF->mDescriptors, t1, pKF->mvKeysUn, &has, nullptr, pKF->N, fvKF);
+    const orbx_bow_side s2 = makeSide(F.mDescriptors, t2, F.mvKeys, nullptr, nullptr, F.N, fvF);   // F.mvKeys[..].angle, :362
+    std::vector<int32_t> match(F.N > 0 ? F.N : 1);
+    int n = 0;
+    check(orbx_match_bow(Context(), ORBX_BOW_KF_FRAME, &s1, &s2, nullptr, mfNNratio, mbCheckOrientation, 0, match.data(), &n),
+          "orbx_match_bow");
+    for (int j = 0; j < F.N; ++j) if (match[j] >= 0) vpMapPointMatches[j] = vpMapPointsKF[match[j]];
+    return n;
+}
+
+int ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12)
+{
+    const std::vector<MapPoint*> vpMapPoints1 = pKF1->GetMapPointMatches();
+    const std::vector<MapPoint*> vpMapPoints2 = pKF2->GetMapPointMatches();
+    vpMatches12 = std::vector<MapPoint*>(vpMapPoints1.size(), static_cast<MapPoint*>(NULL));
+    std::vector<uint8_t> has1(pKF1->N, 0), has2(pKF2->N, 0), t1, t2;
+    for (int i = 0; i < pKF1->N; ++i) has1[i] = vpMapPoints1[i] && !vpMapPoints1[i]->isBad();
+    for (int i = 0; i < pKF2->N; ++i) has2[i] = vpMapPoints2[i] && !vpMapPoints2[i]->isBad();
+    const FlatFeatureVector fv1(pKF1->mFeatVec), fv2(pKF2->mFeatVec);
+    const orbx_bow_side s1 = makeSide(pKF1->mDescriptors, t1, pKF1->mvKeysUn, &has1, nullptr, pKF1->N, fv1);
+    const orbx_bow_side s2 = makeSide(pKF2->mDescriptors, t2, pKF2->mvKeysUn, &has2, nullptr, pKF2->N, fv2);
+    std::vector<int32_t> match(pKF1->N > 0 ? pKF1->N : 1);
+    int n = 0;
+    check(orbx_match_bow(Context(), ORBX_BOW_KF_KF, &s1, &s2, nullptr, mfNNratio, mbCheckOrientation, 0, match.data(), &n),
+          "orbx_match_bow");
+    for (int i = 0; i < pKF1->N; ++i) if (match[i] >= 0) vpMatches12[i] = vpMapPoints2[match[i]];
+    return n;
+}
+
+int ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12,
+                                       std::vector<std::pair<size_t, size_t> >& vMatchedPairs, const bool bOnlyStereo)
+{
+    // epipole of KF1's centre in KF2, src/ORBmatcher.cc:920-929 (plain float arithmetic on the 3x3 / 3x1 matrices)
+    cv::Mat Cw = pKF1->GetCameraCenter(), R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();
+    float C2[3];
+    for (int r = 0; r < 3; ++r)
+        C2[r] = R2w.at<float>(r, 0) * Cw.at<float>(0) + R2w.at<float>(r, 1) * Cw.at<float>(1) + R2w.at<float>(r, 2) * Cw.at<float>(2) + t2w.at<float>(r);
+    const float invz = 1.0f / C2[2];
+    orbx_triangulation tri;
+    memset(&tri, 0, sizeof(tri));
+    tri.ex = pKF2->fx * C2[0] * invz + pKF2->cx;
+    tri.ey = pKF2->fy * C2[1] * invz + pKF2->cy;
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) tri.F12[3 * r + c] = F12.at<float>(r, c);
+    for (size_t l = 0; l < pKF2->mvScaleFactors.size() && l < ORBX_MAX_LEVELS; ++l) {
+        tri.scale2[l] = pKF2->mvScaleFactors[l]; tri.sigma2_2[l] = pKF2->mvLevelSigma2[l];
+    }
+    tri.only_stereo = bOnlyStereo ? 1 : 0;
+    std::vector<uint8_t> has1(pKF1->N, 0), has2(pKF2->N, 0), t1, t2;
+    for (int i = 0; i < pKF1->N; ++i) has1[i] = pKF1->GetMapPoint(i) != NULL;      // :981 (any MapPoint, bad or not)
+    for (int i = 0; i < pKF2->N; ++i) has2[i] = pKF2->GetMapPoint(i) != NULL;      // :1011
+    const FlatFeatureVector fv1(pKF1->mFeatVec), fv2(pKF2->mFeatVec);
+    const orbx_bow_side s1 = makeSide(pKF1->mDescriptors, t1, pKF1->mvKeysUn, &has1, &pKF1->mvuRight, pKF1->N, fv1);
+    const orbx_bow_side s2 = makeSide(pKF2->mDescriptors, t2, pKF2->mvKeysUn, &has2, &pKF2->mvuRight, pKF2->N, fv2);
+    std::vector<int32_t> match(pKF1->N > 0 ? pKF1->N : 1);
+    int n = 0;
+    check(orbx_match_bow(Context(), ORBX_BOW_TRIANGULATE, &s1, &s2, &tri, mfNNratio, mbCheckOrientation, 0, match.data(), &n),
+          "orbx_match_bow");
+    vMatchedPairs.clear();
+    vMatchedPairs.reserve(n);
+    for (int i = 0; i < pKF1->N; ++i) if (match[i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)match[i])); // :1116-1124
+    return n;
+}
+
+namespace {
+int projectionSearch(orbx_ctx* ctx, Frame& F, const std::vector<orbx_proj_query>& q, const std::vector<MapPoint*>& src, int modeFlags,
+                     int thDist, float nnratio, bool checkOri)
+{
+    std::vector<uint8_t> occupied(F.N, 0), tmp;
+    for (int i = 0; i < F.N; ++i) occupied[i] = F.mvpMapPoints[i] && F.mvpMapPoints[i]->Observations() > 0;   // :136-138
+    const orbx_grid g = {Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, FRAME_GRID_COLS, FRAME_GRID_ROWS};
+    std::vector<int32_t> assign(F.N > 0 ? F.N : 1);
+    int n = 0;
+    const bool stereo = !F.mvuRight.empty();
+    check(orbx_search_by_projection(ctx, q.data(), (int)q.size(), reinterpret_cast<const orbx_keypoint*>(F.mvKeysUn.data()),
+                                    contiguous(F.mDescriptors, tmp), stereo ? F.mvuRight.data() : nullptr, F.N, &g, occupied.data(),
+                                    modeFlags | (stereo ? ORBX_PROJ_CHECK_URIGHT : 0), thDist, nnratio, checkOri ? 1 : 0, 0,
+                                    assign.data(), &n), "orbx_search_by_projection");
+    for (int i = 0; i < F.N; ++i) if (assign[i] >= 0) F.mvpMapPoints[i] = src[assign[i]];
+    return n;
+}
+} // namespace
+
+int ORBmatcher::SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th)
+{
+    const bool bFactor = th != 1.0;
+    std::vector<orbx_proj_query> q;
+    std::vector<MapPoint*> src;
+    q.reserve(vpMapPoints.size());
+    for (size_t iMP = 0; iMP < vpMapPoints.size(); iMP++) {
+        MapPoint* pMP = vpMapPoints[iMP];
+        if (!pMP->mbTrackInView) continue;
+        if (pMP->isBad()) continue;
+        const int nPredictedLevel = pMP->mnTrackScaleLevel;
+        float r = RadiusByViewingCos(pMP->mTrackViewCos);
+        if (bFactor) r *= th;
+        orbx_proj_query e;
+        memset(&e, 0, sizeof(e));
+        e.u = pMP->mTrackProjX; e.v = pMP->mTrackProjY; e.ur = pMP->mTrackProjXR;
+        e.radius = r * F.mvScaleFactors[nPredictedLevel];
+        e.min_level = nPredictedLevel - 1; e.max_level = nPredictedLevel;
+        const cv::Mat d = pMP->GetDescriptor();
+        memcpy(e.desc, d.ptr<uint8_t>(), 32);
+        q.push_back(e); src.push_back(pMP);
+    }
+    return projectionSearch(Context(), F, q, src, ORBX_PROJ_RATIO_SAME_LEVEL, TH_HIGH, mfNNratio, false);
+}
+
+int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono)
+{
+    // projection step of src/ORBmatcher.cc:1756-1808 on the host (plain float arithmetic, row . vector + t)
+    const cv::Mat& Tc = CurrentFrame.mTcw; const cv::Mat& Tl = LastFrame.mTcw;
+    float Rcw[9], tcw[3], Rlw[9], tlw[3], twc[3], tlc[3];
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) { Rcw[3 * r + c] = Tc.at<float>(r, c); Rlw[3 * r + c] = Tl.at<float>(r, c); }
+        tcw[r] = Tc.at<float>(r, 3); tlw[r] = Tl.at<float>(r, 3);
+    }
+    for (int r = 0; r < 3; ++r) twc[r] = -(Rcw[r] * tcw[0] + Rcw[3 + r] * tcw[1] + Rcw[6 + r] * tcw[2]);        // -Rcw^T tcw
+    for (int r = 0; r < 3; ++r) tlc[r] = Rlw[3 * r] * twc[0] + Rlw[3 * r + 1] * twc[1] + Rlw[3 * r + 2] * twc[2] + tlw[r];
+    const bool bForward = tlc[2] > CurrentFrame.mb && !bMono;
+    const bool bBackward = -tlc[2] > CurrentFrame.mb && !bMono;
+    std::vector<orbx_proj_query> q;
+    std::vector<MapPoint*> src;
+    for (int i = 0; i < LastFrame.N; i++) {
+        MapPoint* pMP = LastFrame.mvpMapPoints[i];
+        if (!pMP || LastFrame.mvbOutlier[i]) continue;
+        cv::Mat X = pMP->GetWorldPos();
+        const float x = X.at<float>(0), y = X.at<float>(1), z = X.at<float>(2);
+        const float xc = Rcw[0] * x + Rcw[1] * y + Rcw[2] * z + tcw[0];
+        const float yc = Rcw[3] * x + Rcw[4] * y + Rcw[5] * z + tcw[1];
+        const float invzc = 1.0 / (Rcw[6] * x + Rcw[7] * y + Rcw[8] * z + tcw[2]);
+        if (invzc < 0) continue;
+        const float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+        const float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+        if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+        if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+        const int nLastOctave = LastFrame.mvKeys[i].octave;
+        orbx_proj_query e;
+        memset(&e, 0, sizeof(e));
+        e.u = u; e.v = v; e.radius = th * CurrentFrame.mvScaleFactors[nLastOctave];
+        e.ur = u - CurrentFrame.mbf * invzc;
+        e.angle = LastFrame.mvKeysUn[i].angle;
+        if (bForward) { e.min_level = nLastOctave; e.max_level = -1; }
+        else if (bBackward) { e.min_level = 0; e.max_level = nLastOctave; }
+        else { e.min_level = nLastOctave - 1; e.max_level = nLastOctave + 1; }
+        const cv::Mat d = pMP->GetDescriptor();
+        memcpy(e.desc, d.ptr<uint8_t>(), 32);
+        q.push_back(e); src.push_back(pMP);
+    }
+    return projectionSearch(Context(), CurrentFrame, q, src, 0, TH_HIGH, mfNNratio, mbCheckOrientation);
+}
+
+// static members of the compat Frame stand-in (the reference defines them in src/Frame.cc:38-42)
+#ifdef ORBX_COMPAT_SLAM_FRAME_H
+float Frame::fx, Frame::fy, Frame::cx, Frame::cy;
+float Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY;
+float Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv;
+#endif
+
+} // namespace ORB_SLAM2

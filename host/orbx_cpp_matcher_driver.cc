@@ -1,0 +1,109 @@
+// Test driver for the C++ drop-in ORB_SLAM2::ORBmatcher (host/ORBmatcher.cc) built against the compat stand-ins.
+//   orbx_cpp_matcher_driver <in.bin> <out.bin>
+// in.bin: a sequence of arrays, each "int32 nbytes, bytes" (see tests/test_gpu_cpp.py); out.bin likewise.
+#include "ORBmatcher.h"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+using namespace ORB_SLAM2;
+
+static std::vector<std::vector<char> > readAll(const char* path)
+{
+    std::vector<std::vector<char> > out;
+    FILE* f = fopen(path, "rb");
+    if (!f) { fprintf(stderr, "cannot open %s\n", path); exit(2); }
+    int n;
+    while (fread(&n, 4, 1, f) == 1) { std::vector<char> b(n); if (n && fread(b.data(), 1, n, f) != (size_t)n) exit(2); out.push_back(b); }
+    fclose(f);
+    return out;
+}
+template <typename T> static const T* as(const std::vector<char>& b) { return reinterpret_cast<const T*>(b.data()); }
+static void put(FILE* f, const void* p, int nbytes) { fwrite(&nbytes, 4, 1, f); fwrite(p, 1, nbytes, f); }
+
+static void fillFeatVec(DBoW2::FeatureVector& fv, const int* node, int n)
+{
+    for (int i = 0; i < n; ++i) if (node[i] >= 0) fv[(unsigned)node[i]].push_back((unsigned)i);
+}
+
+int main(int argc, char** argv)
+{
+    if (argc < 3) return 2;
+    std::vector<std::vector<char> > in = readAll(argv[1]);
+    // 0: params float[16]: nnratio, checkOri, onlyStereo, fx, fy, cx, cy, th, gridInvW, gridInvH, minX, minY, maxX, maxY
+    const float* P = as<float>(in[0]);
+    std::vector<MapPoint> pool1, pool2;
+    KeyFrame k1, k2;
+    KeyFrame* ks[2] = {&k1, &k2};
+    std::vector<MapPoint>* pools[2] = {&pool1, &pool2};
+    for (int s = 0; s < 2; ++s) {            // 1..5 / 6..10: desc, keys, has, uright, node
+        const std::vector<char>&d = in[1 + 5 * s], &k = in[2 + 5 * s], &h = in[3 + 5 * s], &u = in[4 + 5 * s], &nd = in[5 + 5 * s];
+        KeyFrame& K = *ks[s];
+        K.N = (int)d.size() / 32;
+        K.mDescriptors = cv::Mat(K.N, 32, CV_8U);
+        memcpy(K.mDescriptors.data, d.data(), d.size());
+        K.mvKeysUn.assign(as<cv::KeyPoint>(k), as<cv::KeyPoint>(k) + K.N);
+        K.mvuRight.assign(as<float>(u), as<float>(u) + K.N);
+        pools[s]->resize(K.N);
+        K.mvpMapPoints.assign(K.N, (MapPoint*)NULL);
+        for (int i = 0; i < K.N; ++i) if (h[i]) K.mvpMapPoints[i] = &(*pools[s])[i];
+        fillFeatVec(K.mFeatVec, as<int>(nd), K.N);
+        K.fx = P[3]; K.fy = P[4]; K.cx = P[5]; K.cy = P[6];
+        K.mvScaleFactors.assign(as<float>(in[11]), as<float>(in[11]) + 8);
+        K.mvLevelSigma2.assign(as<float>(in[12]), as<float>(in[12]) + 8);
+    }
+    // 13: F12 (9 floats), 14: Ow (3), R2w = I, t2w = 0
+    cv::Mat F12(3, 3, CV_32F); memcpy(F12.data, in[13].data(), 36);
+    k1.Ow = cv::Mat(3, 1, CV_32F); memcpy(k1.Ow.data, in[14].data(), 12);
+    k2.Rcw = cv::Mat::zeros(3, 3, CV_32F); for (int i = 0; i < 3; ++i) k2.Rcw.at<float>(i, i) = 1.f;
+    k2.tcw = cv::Mat::zeros(3, 1, CV_32F);
+    FILE* o = fopen(argv[2], "wb");
+    try {
+        ORBmatcher m(P[0], P[1] != 0);
+        // (a) SearchByBoW(KF, F): the Frame is side 2
+        Frame F;
+        F.N = k2.N; F.mDescriptors = k2.mDescriptors; F.mvKeys = k2.mvKeysUn; F.mvKeysUn = k2.mvKeysUn; F.mFeatVec = k2.mFeatVec;
+        std::vector<MapPoint*> mm;
+        int n = m.SearchByBoW(&k1, F, mm);
+        std::vector<int> res(F.N, -1);
+        for (int j = 0; j < F.N; ++j) if (mm[j]) res[j] = (int)(mm[j] - pool1.data());
+        put(o, &n, 4); put(o, res.data(), 4 * F.N);
+        // (b) SearchByBoW(KF, KF)
+        n = m.SearchByBoW(&k1, &k2, mm);
+        res.assign(k1.N, -1);
+        for (int i = 0; i < k1.N; ++i) if (mm[i]) res[i] = (int)(mm[i] - pool2.data());
+        put(o, &n, 4); put(o, res.data(), 4 * k1.N);
+        // (c) SearchForTriangulation
+        std::vector<std::pair<size_t, size_t> > pairs;
+        n = m.SearchForTriangulation(&k1, &k2, F12, pairs, P[2] != 0);
+        res.assign(k1.N, -1);
+        for (size_t i = 0; i < pairs.size(); ++i) res[pairs[i].first] = (int)pairs[i].second;
+        put(o, &n, 4); put(o, res.data(), 4 * k1.N);
+        // (d) SearchByProjection(Frame, MapPoints, th): 15: points (u, v, ur, viewCos, level as float), 16: their descriptors,
+        //     17: occupied flags of the frame keypoints
+        const int np = (int)in[15].size() / 20;
+        std::vector<MapPoint> pts(np);
+        std::vector<MapPoint*> vp(np);
+        for (int i = 0; i < np; ++i) {
+            const float* q = as<float>(in[15]) + 5 * i;
+            pts[i].mbTrackInView = true; pts[i].mTrackProjX = q[0]; pts[i].mTrackProjY = q[1]; pts[i].mTrackProjXR = q[2];
+            pts[i].mTrackViewCos = q[3]; pts[i].mnTrackScaleLevel = (int)q[4];
+            pts[i].mDescriptor = cv::Mat(1, 32, CV_8U); memcpy(pts[i].mDescriptor.data, in[16].data() + 32 * i, 32);
+            vp[i] = &pts[i];
+        }
+        Frame::mnMinX = P[10]; Frame::mnMinY = P[11]; Frame::mnMaxX = P[12]; Frame::mnMaxY = P[13];
+        Frame::mfGridElementWidthInv = P[8]; Frame::mfGridElementHeightInv = P[9];
+        F.mvScaleFactors = k2.mvScaleFactors; F.mvuRight = k2.mvuRight;
+        MapPoint occupiedMP;
+        F.mvpMapPoints.assign(F.N, (MapPoint*)NULL);
+        for (int i = 0; i < F.N; ++i) if (in[17][i]) F.mvpMapPoints[i] = &occupiedMP;
+        n = ORBmatcher(P[0], true).SearchByProjection(F, vp, P[7]);
+        res.assign(F.N, -1);
+        for (int i = 0; i < F.N; ++i) if (F.mvpMapPoints[i] && F.mvpMapPoints[i] != &occupiedMP) res[i] = (int)(F.mvpMapPoints[i] - pts.data());
+        put(o, &n, 4); put(o, res.data(), 4 * F.N);
+        int dd = ORBmatcher::DescriptorDistance(k1.mDescriptors.row(0), k2.mDescriptors.row(0));
+        put(o, &dd, 4);
+    } catch (const std::exception& e) { fprintf(stderr, "error: %s\n", e.what()); return 1; }
+    fclose(o);
+    return 0;
+}

@@ -1,0 +1,56 @@
+// Drop-in replacement for the reference's include/ORBmatcher.h (QiuYue-bit/ORB-SLAM2-noted, :48-264): same namespace,
+// class, constructor, static members and method signatures, so Tracking / LocalMapping / LoopClosing call it unchanged.
+// The Hamming work runs in hand-written sm_100a CUDA kernels behind the C ABI (include/orbx.h); the bodies in
+// host/ORBmatcher.cc only flatten the SLAM objects.  Implemented here: DescriptorDistance, both SearchByBoW overloads,
+// SearchForTriangulation, SearchByProjection(Frame&, vector<MapPoint*>&, th) and SearchByProjection(Frame&, const
+// Frame&, th, bMono).  The remaining overloads (SearchByProjection with KeyFrame / Sim3, SearchForInitialization,
+// SearchBySim3, Fuse x2) are the "next" rows of SURVEY.md 8(f): they keep the reference's own bodies until then.
+#ifndef ORBMATCHER_H
+#define ORBMATCHER_H
+
+#include <vector>
+#include <opencv2/core/core.hpp>
+#include <opencv2/features2d/features2d.hpp>
+
+#include "MapPoint.h"
+#include "KeyFrame.h"
+#include "Frame.h"
+
+struct orbx_ctx;
+
+namespace ORB_SLAM2
+{
+
+class ORBmatcher
+{
+public:
+    ORBmatcher(float nnratio = 0.6, bool checkOri = true);
+
+    // reference src/ORBmatcher.cc:2123-2143 (computed on the host: one pair is not worth a launch)
+    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b);
+
+    int SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th = 3);                // :78-191
+    int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);          // :1741-1910
+    int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);                            // :255-419
+    int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);                           // :760-903
+    int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12,
+                               std::vector<std::pair<size_t, size_t> >& vMatchedPairs, const bool bOnlyStereo);     // :915-1127
+
+public:
+    static const int TH_LOW;
+    static const int TH_HIGH;
+    static const int HISTO_LENGTH;
+
+    // the per-thread CUDA context the matcher calls run on (matchers are constructed on the stack at every call site and
+    // used from the tracking, mapping and loop-closing threads concurrently)
+    static orbx_ctx* Context();
+
+protected:
+    float RadiusByViewingCos(const float& viewCos);
+    float mfNNratio;
+    bool mbCheckOrientation;
+};
+
+} // namespace ORB_SLAM2
+
+#endif // ORBMATCHER_H

@@ -37,3 +37,85 @@ def test_cpp_dropin_extractor(tmp_path):
         want = O.border(pyr[po:po + lw * lh].reshape(lh, lw), 19); po += lw * lh
         assert np.array_equal(got, want), l
     assert o == len(b)
+
+
+def _arr(f, a):
+    b = np.ascontiguousarray(a).tobytes()
+    f.write(np.int32(len(b)).tobytes()); f.write(b)
+
+
+def _read_all(path):
+    b = open(path, "rb").read()
+    out, o = [], 0
+    while o < len(b):
+        n = int(np.frombuffer(b, np.int32, 1, o)[0]); o += 4
+        out.append(b[o:o + n]); o += n
+    return out
+
+
+def test_cpp_dropin_matcher(tmp_path):
+    """ORB_SLAM2::ORBmatcher (include/ORBmatcher.h, host/ORBmatcher.cc) over stand-in Frame/KeyFrame/MapPoint objects:
+    SearchByBoW x2, SearchForTriangulation and SearchByProjection(Frame, MapPoints) against the oracle."""
+    from test_gpu_match import make_pair, proj_scene
+    subprocess.run(["make", "-C", os.path.join(ROOT, "host"), "-s"], check=True)
+    seed, n1, n2 = 11, 1500, 1300
+    d1, k1, d2, k2 = make_pair(seed, n1, n2, 0.08, 0.2, KP=O.KP_DTYPE)
+    v = synth.vocabulary(0, 10, 3)
+    vo = O.VocabArrays(v["k"], v["L"], v["child_off"], v["child"], v["desc"], v["word_id"], v["weight"])
+    rng = np.random.default_rng(seed)
+    sides, nodes = [], []
+    for d, k in ((d1, k1), (d2, k2)):
+        w, wt, nd = O.bow_transform(vo, d, 2)
+        nid, noff, feat = O.feature_vector(nd, wt)
+        has = (rng.random(len(d)) < 0.6).astype(np.uint8)
+        ur = np.where(rng.random(len(d)) < 0.5, k["x"] - 5, -1).astype(np.float32)
+        sides.append((d, k, has, ur, nid, noff, feat))
+        nodes.append(np.where(wt > 0, nd, -1).astype(np.int32))
+    p = O.params(1000)
+    scale = np.array(p.scale[:8], np.float32); sigma2 = (np.array(p.sigma2[:8], np.float32) * 9).astype(np.float32)
+    F12 = (np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32) + np.float32(1e-4) * rng.normal(size=(3, 3)).astype(np.float32))
+    fx, fy, cx, cy = np.float32(520.9), np.float32(521.0), np.float32(325.1), np.float32(249.7)
+    Ow = np.array([0.3, -0.1, 2.0], np.float32)
+    invz = np.float32(1.0) / Ow[2]
+    ex = np.float32(np.float32(np.float32(fx * Ow[0]) * invz) + cx); ey = np.float32(np.float32(np.float32(fy * Ow[1]) * invz) + cy)
+    nnratio, th = np.float32(0.7), np.float32(3.0)
+    grid = (np.float32(0), np.float32(0), np.float32(64) / np.float32(640), np.float32(48) / np.float32(480))
+    # projection scene on side 2's keypoints
+    keys, desc, uright, occupied, pts = proj_scene(pkg_mod(), seed + 5, n2, 900)
+    keys = k2.copy(); desc = d2
+    pts["desc"] = synth.descriptors(seed + 9, len(pts), 0.12, desc[rng.integers(0, n2, len(pts))])
+    src = rng.integers(0, n2, len(pts))
+    pts["u"] = keys["x"][src] + rng.normal(0, 3, len(pts)).astype(np.float32)
+    pts["v"] = keys["y"][src] + rng.normal(0, 3, len(pts)).astype(np.float32)
+    pts["level"] = np.clip(keys["octave"][src] + rng.integers(-1, 2, len(pts)), 0, 7)
+    uright = sides[1][3]
+    inp, outp = tmp_path / "m_in.bin", tmp_path / "m_out.bin"
+    with open(inp, "wb") as f:
+        _arr(f, np.array([nnratio, 1, 0, fx, fy, cx, cy, th, grid[2], grid[3], 0, 0, 640, 480, 0, 0], np.float32))
+        for (d, k, has, ur, _, _, _), nd in zip(sides, nodes):
+            _arr(f, d); _arr(f, k); _arr(f, has); _arr(f, ur); _arr(f, nd)
+        _arr(f, scale); _arr(f, sigma2); _arr(f, F12); _arr(f, Ow)
+        _arr(f, np.stack([pts["u"], pts["v"], pts["ur"], pts["view_cos"], pts["level"].astype(np.float32)], 1).astype(np.float32))
+        _arr(f, pts["desc"]); _arr(f, occupied)
+    r = subprocess.run([os.path.join(ROOT, "host", "orbx_cpp_matcher_driver"), str(inp), str(outp)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    out = _read_all(outp)
+    so = [O.Side(*s) for s in sides]
+    want, nw = O.search_by_bow(so[0], so[1], float(nnratio), True, False)
+    assert int(np.frombuffer(out[0], np.int32)[0]) == nw and np.array_equal(np.frombuffer(out[1], np.int32), want)
+    want, nw = O.search_by_bow(so[0], so[1], float(nnratio), True, True)
+    assert int(np.frombuffer(out[2], np.int32)[0]) == nw and np.array_equal(np.frombuffer(out[3], np.int32), want)
+    sc16 = np.zeros(16, np.float32); sc16[:8] = scale
+    sg16 = np.zeros(16, np.float32); sg16[:8] = sigma2
+    want, nw = O.search_for_triangulation(so[0], so[1], F12, float(ex), float(ey), sc16, sg16, False, True)
+    assert int(np.frombuffer(out[4], np.int32)[0]) == nw and np.array_equal(np.frombuffer(out[5], np.int32), want)
+    assert nw > 0
+    want, nw = O.search_by_projection(pts, keys, desc, uright, scale, grid, occupied, float(th), nnratio=float(nnratio))
+    assert int(np.frombuffer(out[6], np.int32)[0]) == nw and np.array_equal(np.frombuffer(out[7], np.int32), want)
+    assert nw > 0
+    assert int(np.frombuffer(out[8], np.int32)[0]) == int(np.unpackbits(d1[0] ^ d2[0]).sum())
+
+
+def pkg_mod():
+    from gpu_util import pkg
+    return pkg()
