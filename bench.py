@@ -323,7 +323,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--batch", type=int, default=1024)
     ap.add_argument("--impl", default="orbx", choices=["orbx", "reference"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))

@@ -3,21 +3,23 @@
 //
 // One CTA per STRIP = one cell-row of one level of one frame, split into segments of whole cells so the tile fits in
 // shared memory; all levels and frames in ONE launch.  The candidate regions of the reference's cells tile the
-// detection window without overlap, the FAST score does not depend on the threshold for a detected corner, and NMS at
-// iniTh equals {NMS survivors at minTh with score >= iniTh}; so one pass at minTh serves both thresholds and the
-// per-cell retry (:1128) becomes a per-cell choice between two subsets of the same survivors.
+// detection window without overlap, so a strip is detected as one image with per-cell NMS boundaries.
 //   stage   rows of the strip (+3 px apron) are brought into shared memory with 1-D bulk async copies
 //           (cp.async.bulk -> UBLKCP, completion on an mbarrier); plain loads when the source is not 16-byte aligned
-//   phase 1 4 pixels per thread step, byte-parallel in 32-bit registers: brighter/darker flags of the 16 ring pixels
-//           by SWAR unsigned-byte compares (3 LOP3/IADD per flag word), 9-contiguity as bit-sliced AND/OR trees
-//           (no per-pixel branches, no divergence); corners are appended to a shared list
-//   phase 2 list entries: exact OpenCV cornerScore (max over the 16 arcs of the arc's min margin, -1) -> u8 score map
-//   phase 3 3x3 strict-> NMS inside the pixel's own cell (neighbours outside the cell count 0, exactly like the per-ROI
-//           cv::FAST calls), per-cell counts of survivors and of survivors >= iniTh
-//   phase 4 emit: a cell keeps {survivors >= iniTh} if that set is non-empty, else all survivors (the retry)
+//   sweep 0 detects the whole strip at iniTh; sweep 1 (only if some cell kept nothing, :1128) detects those cells again
+//           at minTh.  Each sweep:
+//     pass 0  quick rejection, 4 pixels per thread step, byte-parallel in 32-bit registers; surviving groups -> list
+//     pass 1  full test of the listed groups: brighter/darker flags of the 16 ring pixels by SWAR unsigned-byte compares
+//             (3 LOP3/IADD per flag word), 9-contiguity as bit-sliced AND/OR trees (no per-pixel branches); corners go
+//             to a list and a bitmap
+//     score   list entries: exact OpenCV cornerScore (max over the 16 arcs of the arc's min margin, -1) -> u8 score map
+//     nms     3x3 strict-> NMS inside the pixel's own cell (neighbours outside the cell count 0, exactly like the per-ROI
+//             cv::FAST calls); survivors -> compact list, per-cell survivor counts (the retry decision)
+//     emit    survivors -> global candidate records
 // Output records are order-independent: key = (cell, ly, lx) reproduces the reference's push_back order
 // (cell-row-major, then pixel-row-major :1084-1149) whenever an ordered view is needed.
 #include "orbx_internal.h"
+#include <algorithm>
 
 namespace orbx {
 
@@ -46,19 +48,13 @@ __device__ __forceinline__ uint32_t nineOfSixteen(const uint32_t (&f)[16])
     uint32_t a3[16];
     #pragma unroll
     for (int k = 0; k < 16; ++k) a3[k] = f[k] & f[(k + 1) & 15] & f[(k + 2) & 15];
-    uint32_t r = 0;
+    uint32_t a9[16];
     #pragma unroll
-    for (int k = 0; k < 16; ++k) r |= a3[k] & a3[(k + 3) & 15] & a3[(k + 6) & 15];
-    return r;
-}
-
-// bit 7 flags of the bytes whose candidate column lx0 + b lies in [0, rw)
-__device__ __forceinline__ uint32_t validBytes(int lx0, int rw)
-{
-    uint32_t m = 0x80808080u;
-    if (lx0 < 0) m = lx0 <= -4 ? 0u : m & (0xffffffffu << (8 * -lx0));
-    if (lx0 + 3 >= rw) { const int k = lx0 + 4 - rw; m = k >= 4 ? 0u : m & (0xffffffffu >> (8 * k)); }
-    return m;
+    for (int k = 0; k < 16; ++k) a9[k] = a3[k] & a3[(k + 3) & 15] & a3[(k + 6) & 15];
+    // OR tree in 3-input steps
+    const uint32_t t0 = a9[0] | a9[1] | a9[2], t1 = a9[3] | a9[4] | a9[5], t2 = a9[6] | a9[7] | a9[8];
+    const uint32_t t3 = a9[9] | a9[10] | a9[11], t4 = a9[12] | a9[13] | a9[14];
+    return (t0 | t1 | t2) | (t3 | t4 | a9[15]);
 }
 
 // warp-aggregated append of `cnt` items per lane; returns the lane's first slot
@@ -75,15 +71,19 @@ __device__ __forceinline__ int warpAppend(int* counter, int cnt)
     return base + incl - cnt;
 }
 
+// upper bound of NMS survivors in a strip: no two 8-neighbours inside one cell both survive
+__host__ __device__ inline int fastSurvivorCap(int maxRw, int maxRh) { return ((maxRw + kMaxCellsPerStrip) / 2 + 1) * ((maxRh + 1) / 2); }
+
 __global__ void __launch_bounds__(kFastThreads, 4)
 fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
                 const uint8_t* __restrict__ pyr, unsigned long long* __restrict__ cand, int* __restrict__ candCount,
-                int tilePitchMax, int tileRowsMax, int scorePitchMax)
+                int tilePitchMax, int tileRowsMax, int scorePitchMax, int listBytes, uint32_t rcpBP4)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) unsigned long long sBar;
-    __shared__ int sGroupN, sCornerN, sOutN, sBase;
-    __shared__ int sNms[kMaxCellsPerStrip], sIni[kMaxCellsPerStrip];
+    __shared__ int sGroupN, sCornerN, sSurvN, sBase;
+    __shared__ uint32_t sRetry;
+    __shared__ int sCellCnt[kMaxCellsPerStrip];
 
     const int frame = blockIdx.y + G.frame0;
     int level = 0;
@@ -104,20 +104,23 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     const int TP = tilePitchMax, SP = scorePitchMax;               // bytes per tile / score row
     const int BP = (SP + 31) >> 5;                                  // bitmap words per row
     const int maxRh = tileRowsMax - 6;
+    const int wp = TP >> 2;
     uint8_t* tile = smem;                                           // (rh + 6) rows
     uint8_t* score = smem + (size_t)TP * tileRowsMax;               // (rh + 2) x SP, zero apron
     uint32_t* cornerBits = reinterpret_cast<uint32_t*>(score + (size_t)SP * (maxRh + 2)); // rh x BP
-    uint32_t* nmsBits = cornerBits + maxRh * BP;
-    uint16_t* cornerList = reinterpret_cast<uint16_t*>(nmsBits + maxRh * BP);             // kCornerCap
+    uint32_t* colValid = cornerBits + maxRh * BP;                   // per tile word column: bit 7 of the bytes to detect
+    uint16_t* cornerList = reinterpret_cast<uint16_t*>(colValid + wp);                    // kCornerCap
     uint16_t* groupList = cornerList + kCornerCap;                  // up to maxRh * (SP/4 + 2) groups
-    uint8_t* colCell = reinterpret_cast<uint8_t*>(groupList + maxRh * ((SP >> 2) + 2));   // cell column of candidate column lx
+    uint32_t* survList = reinterpret_cast<uint32_t*>(cornerList);   // reuses both lists once the scores are in
+    uint8_t* colCell = reinterpret_cast<uint8_t*>(cornerList) + listBytes;                // cell column of candidate column lx
     const int TH = rh + 6;
     const bool aligned = ((((size_t)img) | pitch) & 15) == 0;
     const int xa = aligned ? ((cx0 - 4) & ~15) : (cx0 - 4) & ~3;    // image column of tile column 0 (>= 4 px left of cx0)
     const int off0 = cx0 - xa;                                      // tile column of the first candidate pixel (>= 4)
+    const int nc = j1 - j0;
 
-    if (threadIdx.x == 0) { sGroupN = 0; sCornerN = 0; sOutN = 0; }
-    if (threadIdx.x < kMaxCellsPerStrip) { sNms[threadIdx.x] = 0; sIni[threadIdx.x] = 0; }
+    if (threadIdx.x == 0) { sGroupN = 0; sCornerN = 0; sSurvN = 0; }
+    if (threadIdx.x < kMaxCellsPerStrip) sCellCnt[threadIdx.x] = 0;
     if (aligned) {
         const int xb = min((cx1 + 3 + 15) & ~15, (int)pitch);
         const uint32_t rowBytes = (uint32_t)(xb - xa);
@@ -141,13 +144,20 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
             tile[y * TP + x] = img[(size_t)(cy0 - 3 + y) * pitch + xa + x];
         }
     }
-    // zero the score map and bitmaps, build the column table while the copies are in flight
+    // zero the score map and the bitmap, build the column tables while the copies are in flight
     {
         uint32_t* z = reinterpret_cast<uint32_t*>(score);
         const int nz = (SP * (rh + 2) + 3) / 4;
         for (int i = threadIdx.x; i < nz; i += kFastThreads) z[i] = 0;
-        for (int i = threadIdx.x; i < 2 * maxRh * BP; i += kFastThreads) cornerBits[i] = 0;   // cornerBits + nmsBits
+        for (int i = threadIdx.x; i < maxRh * BP; i += kFastThreads) cornerBits[i] = 0;
         for (int i = threadIdx.x; i < rw; i += kFastThreads) colCell[i] = (uint8_t)(i / g.wCell);
+        for (int i = threadIdx.x; i < wp; i += kFastThreads) {
+            const int lx0 = i * 4 - off0;
+            uint32_t m = 0;
+            #pragma unroll
+            for (int b = 0; b < 4; ++b) if (lx0 + b >= 0 && lx0 + b < rw) m |= 0x80u << (8 * b);
+            colValid[i] = m;
+        }
     }
     if (aligned) {
         const uint32_t bar = smemAddr(&sBar);
@@ -159,44 +169,13 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     __syncthreads();
 
     const int tmin = G.minTh, tini = G.iniTh;
-    const uint32_t T4 = (uint32_t)tmin * 0x01010101u;
     const int g0 = off0 >> 2, g1 = (off0 + rw + 3) >> 2;            // word columns holding candidate pixels
     const int ng = g1 - g0;
     const uint32_t rcpNg = 0xffffffffu / (uint32_t)ng + 1u;         // i / ng == umulhi(i, rcpNg) for i < 65536
-    const uint32_t rcpBP = 0xffffffffu / (uint32_t)BP + 1u;
-    const int wp = TP >> 2;
     const int wCell = g.wCell;
     const uint32_t* W = reinterpret_cast<const uint32_t*>(tile);
     const int o[16] = {3 * TP, 3 * TP + 1, 2 * TP + 2, TP + 3, 3, -TP + 3, -2 * TP + 2, -3 * TP + 1,
                        -3 * TP, -3 * TP - 1, -2 * TP - 2, -TP - 3, -3, TP - 3, 2 * TP - 2, 3 * TP - 1};
-
-    // ---- pass 0: quick rejection over the whole strip, 4 pixels per step.  A 9-arc contains two adjacent compass
-    //      pixels, i.e. one of {0, 8} and one of {4, 12}, all brighter or all darker. ----
-    {
-        const int nGroups = rh * ng;
-        for (int ib = 0; ib < nGroups; ib += kFastThreads) {      // uniform trip count: full-warp votes below
-            const int i = ib + threadIdx.x;
-            uint32_t q = 0; int code = 0;
-            if (i < nGroups) {
-                const int y = (int)__umulhi((uint32_t)i, rcpNg), gw = g0 + i - y * ng;
-                const uint32_t* c = W + (y + 3) * wp + gw;
-                const uint32_t v = c[0], up = c[-3 * wp], dn = c[3 * wp];
-                const uint32_t p4 = __funnelshift_r(v, c[1], 24), p12 = __funnelshift_r(c[-1], v, 8);
-                const uint32_t hi = __vaddus4(v, T4), lo = __vsubus4(v, T4);
-                const uint32_t nh7 = ~hi & 0x7f7f7f7fu, lo7 = lo & 0x7f7f7f7fu;
-                const uint32_t b = (gtu4(dn, hi, nh7) | gtu4(up, hi, nh7)) & (gtu4(p4, hi, nh7) | gtu4(p12, hi, nh7));
-                const uint32_t d = (ltu4(dn, lo, lo7) | ltu4(up, lo, lo7)) & (ltu4(p4, lo, lo7) | ltu4(p12, lo, lo7));
-                q = (b | d) & validBytes(gw * 4 - off0, rw);
-                code = (y << 10) | gw;
-            }
-            if (__any_sync(0xffffffffu, q != 0)) {
-                const int slot = warpAppend(&sGroupN, q != 0);
-                if (q) groupList[slot] = (uint16_t)code;
-            }
-        }
-    }
-    __syncthreads();
-    const int nG = sGroupN;
 
     // exact score of the listed corners
     auto scorePass = [&](int n) {
@@ -221,127 +200,168 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
                 a0 = max(a0, mn9);
                 b0 = min(b0, mx9);
             }
-            score[(ly + 1) * SP + (lx + 1)] = (uint8_t)(max(a0, -b0) - 1); // > minTh-1 >= 0 for a detected corner
+            score[(ly + 1) * SP + (lx + 1)] = (uint8_t)(max(a0, -b0) - 1); // > th-1 >= 0 for a detected corner
         }
     };
 
-    // ---- pass 1: full test of the surviving groups in batches: brighter/darker flags of the 16 ring pixels,
-    //      9-contiguity as bit-sliced AND/OR trees; corners go to the list and the corner bitmap ----
-    for (int gb = 0; gb < nG; gb += kGroupBatch) {
-        const int gEnd = min(nG, gb + kGroupBatch);
-        for (int ib = gb; ib < gEnd; ib += kFastThreads) {
-            const int i = ib + threadIdx.x;
-            uint32_t nib = 0; int y = 0, lx0 = 0;
-            if (i < gEnd) {
-                const int code = groupList[i], gw = code & 1023;
-                y = code >> 10; lx0 = gw * 4 - off0;
-                const uint32_t* c = W + (y + 3) * wp + gw;
-                uint32_t a[7][3];
-                #pragma unroll
-                for (int r = 0; r < 7; ++r) { a[r][0] = c[(r - 3) * wp - 1]; a[r][1] = c[(r - 3) * wp]; a[r][2] = c[(r - 3) * wp + 1]; }
-                const uint32_t v = a[3][1];
-                const uint32_t hi = __vaddus4(v, T4), lo = __vsubus4(v, T4);    // min(v + t, 255), max(v - t, 0) per byte
-                const uint32_t nh7 = ~hi & 0x7f7f7f7fu, lo7 = lo & 0x7f7f7f7fu;
-                uint32_t p[16];
-                p[0] = a[6][1];                                   // ( 0, 3)
-                p[1] = __funnelshift_r(a[6][1], a[6][2], 8);      // ( 1, 3)
-                p[2] = __funnelshift_r(a[5][1], a[5][2], 16);     // ( 2, 2)
-                p[3] = __funnelshift_r(a[4][1], a[4][2], 24);     // ( 3, 1)
-                p[4] = __funnelshift_r(a[3][1], a[3][2], 24);     // ( 3, 0)
-                p[5] = __funnelshift_r(a[2][1], a[2][2], 24);     // ( 3,-1)
-                p[6] = __funnelshift_r(a[1][1], a[1][2], 16);     // ( 2,-2)
-                p[7] = __funnelshift_r(a[0][1], a[0][2], 8);      // ( 1,-3)
-                p[8] = a[0][1];                                   // ( 0,-3)
-                p[9] = __funnelshift_r(a[0][0], a[0][1], 24);     // (-1,-3)
-                p[10] = __funnelshift_r(a[1][0], a[1][1], 16);    // (-2,-2)
-                p[11] = __funnelshift_r(a[2][0], a[2][1], 8);     // (-3,-1)
-                p[12] = __funnelshift_r(a[3][0], a[3][1], 8);     // (-3, 0)
-                p[13] = __funnelshift_r(a[4][0], a[4][1], 8);     // (-3, 1)
-                p[14] = __funnelshift_r(a[5][0], a[5][1], 16);    // (-2, 2)
-                p[15] = __funnelshift_r(a[6][0], a[6][1], 24);    // (-1, 3)
-                uint32_t f[16];
-                #pragma unroll
-                for (int k = 0; k < 16; ++k) f[k] = gtu4(p[k], hi, nh7);
-                uint32_t corner = nineOfSixteen(f);
-                #pragma unroll
-                for (int k = 0; k < 16; ++k) f[k] = ltu4(p[k], lo, lo7);
-                corner = (corner | nineOfSixteen(f)) & validBytes(lx0, rw);
-                nib = ((corner >> 7) & 1u) | ((corner >> 14) & 2u) | ((corner >> 21) & 4u) | ((corner >> 28) & 8u);
+    unsigned long long* out = cand + (size_t)frame * G.candPerFrame + g.candBase;
+    const uint8_t* cornerBytes = reinterpret_cast<const uint8_t*>(cornerBits);
+    const int nGroups = rh * ng;
+
+    for (int sweep = 0; sweep < 2; ++sweep) {
+        const int th = sweep ? tmin : tini;
+        if (sweep) {
+            // the retry set (:1128): cells of this strip that kept nothing at iniTh
+            if (threadIdx.x < 32) {
+                const uint32_t m = __ballot_sync(0xffffffffu, (int)threadIdx.x < nc && sCellCnt[threadIdx.x] == 0);
+                if (threadIdx.x == 0) { sRetry = m; sGroupN = 0; sCornerN = 0; sSurvN = 0; }
             }
-            if (__any_sync(0xffffffffu, nib != 0)) {
-                int slot = warpAppend(&sCornerN, __popc(nib));
-                if (nib) {
+            __syncthreads();
+            const uint32_t retry = sRetry;
+            if (!retry || tmin == tini) break;
+            for (int i = threadIdx.x; i < wp; i += kFastThreads) {
+                const int lx0 = i * 4 - off0;
+                uint32_t m = 0;
+                #pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const int lx = lx0 + b;
+                    if (lx >= 0 && lx < rw && ((retry >> colCell[lx]) & 1u)) m |= 0x80u << (8 * b);
+                }
+                colValid[i] = m;
+            }
+            for (int i = threadIdx.x; i < rh * BP; i += kFastThreads) cornerBits[i] = 0;
+            if (tmin > tini) {   // scores in [iniTh, minTh) are not corners of this sweep
+                uint32_t* z = reinterpret_cast<uint32_t*>(score);
+                const int nz = (SP * (rh + 2) + 3) / 4;
+                for (int i = threadIdx.x; i < nz; i += kFastThreads) z[i] = 0;
+            }
+            __syncthreads();
+        }
+        const uint32_t T4 = (uint32_t)th * 0x01010101u;
+
+        // ---- pass 0: quick rejection, 4 pixels per step.  A 9-arc contains two adjacent compass pixels, i.e. one of
+        //      {0, 8} and one of {4, 12}, all brighter or all darker. ----
+        for (int i = threadIdx.x; i < nGroups; i += kFastThreads) {
+            const int y = (int)__umulhi((uint32_t)i, rcpNg), gw = g0 + i - y * ng;
+            const uint32_t vm = colValid[gw];
+            if (!vm) continue;
+            const uint32_t* c = W + (y + 3) * wp + gw;
+            const uint32_t v = c[0], up = c[-3 * wp], dn = c[3 * wp];
+            const uint32_t p4 = __funnelshift_r(v, c[1], 24), p12 = __funnelshift_r(c[-1], v, 8);
+            const uint32_t hi = __vaddus4(v, T4), lo = __vsubus4(v, T4);
+            const uint32_t nh7 = ~hi & 0x7f7f7f7fu, lo7 = lo & 0x7f7f7f7fu;
+            const uint32_t b = (gtu4(dn, hi, nh7) | gtu4(up, hi, nh7)) & (gtu4(p4, hi, nh7) | gtu4(p12, hi, nh7));
+            const uint32_t d = (ltu4(dn, lo, lo7) | ltu4(up, lo, lo7)) & (ltu4(p4, lo, lo7) | ltu4(p12, lo, lo7));
+            if ((b | d) & vm) groupList[atomicAdd(&sGroupN, 1)] = (uint16_t)((y << 10) | gw);   // aggregated per warp by the compiler
+        }
+        __syncthreads();
+        const int nG = sGroupN;
+
+        // ---- pass 1: full test of the surviving groups in batches; corners go to the list and the corner bitmap ----
+        for (int gb = 0; gb < nG; gb += kGroupBatch) {
+            const int gEnd = min(nG, gb + kGroupBatch);
+            for (int ib = gb; ib < gEnd; ib += kFastThreads) {
+                const int i = ib + threadIdx.x;
+                uint32_t nib = 0; int y = 0, lx0 = 0;
+                if (i < gEnd) {
+                    const int code = groupList[i], gw = code & 1023;
+                    y = code >> 10; lx0 = gw * 4 - off0;
+                    const uint32_t* c = W + (y + 3) * wp + gw;
+                    uint32_t a[7][3];
                     #pragma unroll
-                    for (int b = 0; b < 4; ++b)
-                        if ((nib >> b) & 1u) cornerList[slot++] = (uint16_t)((y << 10) | (lx0 + b));
-                    // the 4 pixels may straddle two bitmap words
-                    const int lxa = max(lx0, 0);
-                    const uint32_t bitsA = (lx0 >= 0 ? nib : nib >> (-lx0));
-                    const int wA = y * BP + (lxa >> 5), sh = lxa & 31;
-                    atomicOr(&cornerBits[wA], bitsA << sh);
-                    if (sh > 28 && (bitsA >> (32 - sh))) atomicOr(&cornerBits[wA + 1], bitsA >> (32 - sh));
+                    for (int r = 0; r < 7; ++r) { a[r][0] = c[(r - 3) * wp - 1]; a[r][1] = c[(r - 3) * wp]; a[r][2] = c[(r - 3) * wp + 1]; }
+                    const uint32_t v = a[3][1];
+                    const uint32_t hi = __vaddus4(v, T4), lo = __vsubus4(v, T4);    // min(v + t, 255), max(v - t, 0) per byte
+                    const uint32_t nh7 = ~hi & 0x7f7f7f7fu, lo7 = lo & 0x7f7f7f7fu;
+                    uint32_t p[16];
+                    p[0] = a[6][1];                                   // ( 0, 3)
+                    p[1] = __funnelshift_r(a[6][1], a[6][2], 8);      // ( 1, 3)
+                    p[2] = __funnelshift_r(a[5][1], a[5][2], 16);     // ( 2, 2)
+                    p[3] = __funnelshift_r(a[4][1], a[4][2], 24);     // ( 3, 1)
+                    p[4] = __funnelshift_r(a[3][1], a[3][2], 24);     // ( 3, 0)
+                    p[5] = __funnelshift_r(a[2][1], a[2][2], 24);     // ( 3,-1)
+                    p[6] = __funnelshift_r(a[1][1], a[1][2], 16);     // ( 2,-2)
+                    p[7] = __funnelshift_r(a[0][1], a[0][2], 8);      // ( 1,-3)
+                    p[8] = a[0][1];                                   // ( 0,-3)
+                    p[9] = __funnelshift_r(a[0][0], a[0][1], 24);     // (-1,-3)
+                    p[10] = __funnelshift_r(a[1][0], a[1][1], 16);    // (-2,-2)
+                    p[11] = __funnelshift_r(a[2][0], a[2][1], 8);     // (-3,-1)
+                    p[12] = __funnelshift_r(a[3][0], a[3][1], 8);     // (-3, 0)
+                    p[13] = __funnelshift_r(a[4][0], a[4][1], 8);     // (-3, 1)
+                    p[14] = __funnelshift_r(a[5][0], a[5][1], 16);    // (-2, 2)
+                    p[15] = __funnelshift_r(a[6][0], a[6][1], 24);    // (-1, 3)
+                    uint32_t f[16];
+                    #pragma unroll
+                    for (int k = 0; k < 16; ++k) f[k] = gtu4(p[k], hi, nh7);
+                    uint32_t corner = nineOfSixteen(f);
+                    #pragma unroll
+                    for (int k = 0; k < 16; ++k) f[k] = ltu4(p[k], lo, lo7);
+                    corner = (corner | nineOfSixteen(f)) & colValid[gw];
+                    nib = ((corner >> 7) & 1u) | ((corner >> 14) & 2u) | ((corner >> 21) & 4u) | ((corner >> 28) & 8u);
+                }
+                const uint32_t m = __ballot_sync(0xffffffffu, nib != 0);
+                if (m) {
+                    // few lanes hold corners in scene-like frames: direct shared atomics; dense warps use the scan
+                    int slot = 0;
+                    if (__popc(m) <= 6) { if (nib) slot = atomicAdd(&sCornerN, __popc(nib)); }
+                    else slot = warpAppend(&sCornerN, __popc(nib));
+                    if (nib) {
+                        #pragma unroll
+                        for (int b = 0; b < 4; ++b)
+                            if ((nib >> b) & 1u) cornerList[slot++] = (uint16_t)((y << 10) | (lx0 + b));
+                        // the 4 pixels may straddle two bitmap words
+                        const int lxa = max(lx0, 0);
+                        const uint32_t bitsA = (lx0 >= 0 ? nib : nib >> (-lx0));
+                        const int wA = y * BP + (lxa >> 5), sh = lxa & 31;
+                        atomicOr(&cornerBits[wA], bitsA << sh);
+                        if (sh > 28 && (bitsA >> (32 - sh))) atomicOr(&cornerBits[wA + 1], bitsA >> (32 - sh));
+                    }
+                }
+            }
+            __syncthreads();
+            if (sCornerN > kCornerCap - 4 * kGroupBatch || gEnd == nG) {   // uniform: score in bulk before the list could overflow
+                const int n = sCornerN;
+                scorePass(n);
+                __syncthreads();
+                if (threadIdx.x == 0) sCornerN = 0;
+                __syncthreads();
+            }
+        }
+
+        // ---- nms: 8 bitmap columns per step (strict >, 8 neighbours, zero outside the pixel's own cell) ----
+        for (int it = threadIdx.x; it < rh * BP * 4; it += kFastThreads) {
+            uint32_t bits = cornerBytes[it];
+            if (!bits) continue;
+            const int ly = (int)__umulhi((uint32_t)it, rcpBP4), lxb = (it - ly * BP * 4) << 3;
+            while (bits) {
+                const int b = __ffs(bits) - 1;
+                bits &= bits - 1;
+                const int lx = lxb + b;
+                const uint8_t* r = score + (ly + 1) * SP + (lx + 1);
+                const int s = r[0];
+                const int cj = colCell[lx], cx = lx - cj * wCell;
+                bool keep = s > r[-SP] && s > r[SP];
+                if (cx > 0) keep = keep && s > r[-1] && s > r[-SP - 1] && s > r[SP - 1];
+                if (cx < wCell - 1) keep = keep && s > r[1] && s > r[-SP + 1] && s > r[SP + 1];
+                if (keep) {
+                    survList[atomicAdd(&sSurvN, 1)] = ((uint32_t)s << 16) | (uint32_t)(ly << 10) | (uint32_t)lx;
+                    if (!sweep) atomicAdd(&sCellCnt[cj], 1);
                 }
             }
         }
         __syncthreads();
-        if (sCornerN > kCornerCap - 4 * kGroupBatch || gEnd == nG) {   // uniform: score in bulk before the list could overflow
-            const int n = sCornerN;
-            scorePass(n);
-            __syncthreads();
-            if (threadIdx.x == 0) sCornerN = 0;
-            __syncthreads();
-        }
-    }
-
-    // ---- pass 3: NMS over the corner bitmap (strict >, 8 neighbours, zero outside the pixel's own cell) ----
-    for (int w = threadIdx.x; w < rh * BP; w += kFastThreads) {
-        uint32_t bits = cornerBits[w];
-        if (!bits) continue;
-        const int ly = (int)__umulhi((uint32_t)w, rcpBP), lxb = (w - ly * BP) << 5;
-        uint32_t keepBits = 0;
-        while (bits) {
-            const int b = __ffs(bits) - 1;
-            bits &= bits - 1;
-            const int lx = lxb + b;
-            const uint8_t* r = score + (ly + 1) * SP + (lx + 1);
-            const int s = r[0];
+        // ---- emit ----
+        const int nS = sSurvN;
+        if (threadIdx.x == 0) sBase = nS ? atomicAdd(&candCount[frame * G.nlevels + level], nS) : 0;
+        __syncthreads();
+        for (int i = threadIdx.x; i < nS; i += kFastThreads) {
+            const uint32_t r = survList[i];
+            const int s = r >> 16, ly = (r >> 10) & 63, lx = r & 1023;
             const int cj = colCell[lx], cx = lx - cj * wCell;
-            bool keep = s > r[-SP] && s > r[SP];
-            if (cx > 0) keep = keep && s > r[-1] && s > r[-SP - 1] && s > r[SP - 1];
-            if (cx < wCell - 1) keep = keep && s > r[1] && s > r[-SP + 1] && s > r[SP + 1];
-            if (keep) {
-                atomicAdd(&sNms[cj], 1);
-                if (s >= tini) atomicAdd(&sIni[cj], 1);
-                keepBits |= 1u << b;
-            }
-        }
-        nmsBits[w] = keepBits;
-    }
-    __syncthreads();
-    // ---- pass 4: per-cell retry decision and output ----
-    const int nc = j1 - j0;
-    if (threadIdx.x == 0) {
-        int tot = 0;
-        for (int c = 0; c < nc; ++c) tot += sIni[c] > 0 ? sIni[c] : sNms[c];
-        sBase = tot ? atomicAdd(&candCount[frame * G.nlevels + level], tot) : 0;
-    }
-    __syncthreads();
-    unsigned long long* out = cand + (size_t)frame * G.candPerFrame + g.candBase + sBase;
-    for (int w = threadIdx.x; w < rh * BP; w += kFastThreads) {
-        uint32_t bits = nmsBits[w];
-        if (!bits) continue;
-        const int ly = (int)__umulhi((uint32_t)w, rcpBP), lxb = (w - ly * BP) << 5;
-        while (bits) {
-            const int b = __ffs(bits) - 1;
-            bits &= bits - 1;
-            const int lx = lxb + b;
-            const int s = score[(ly + 1) * SP + (lx + 1)];
-            const int cj = colCell[lx], cx = lx - cj * wCell;
-            if (sIni[cj] > 0 && s < tini) continue;
-            const int slot = atomicAdd(&sOutN, 1);
             const uint32_t key = ((uint32_t)(ci * g.nCols + j0 + cj) << 12) | (uint32_t)(ly << 6) | (uint32_t)cx;
-            out[slot] = ((unsigned long long)((uint32_t)s << 24) << 32) | key; // hi = score<<24 | node(0), lo = key
+            out[sBase + i] = ((unsigned long long)((uint32_t)s << 24) << 32) | key; // hi = score<<24 | node(0), lo = key
         }
+        __syncthreads();
     }
 }
 
@@ -355,18 +375,23 @@ int launchFast(Ctx* c, int frame0, int batch)
     if (g.stripsPerFrame > 0) {
         const int TP = g.fastTilePitch, TR = g.fastTileRows, SP = g.fastScorePitch;
         const int maxRh = TR - 6, BP = (SP + 31) / 32;
+        // corner list + group list, reused as the survivor list (u32 records)
+        size_t listBytes = sizeof(uint16_t) * ((size_t)kCornerCap + (size_t)maxRh * ((SP >> 2) + 2));
+        listBytes = std::max(listBytes, sizeof(uint32_t) * (size_t)fastSurvivorCap(SP, maxRh));
+        listBytes = (listBytes + 3) & ~(size_t)3;
         size_t smem = (size_t)TP * TR + (size_t)SP * (maxRh + 2);
-        smem += sizeof(uint32_t) * 2 * (size_t)maxRh * BP;
-        smem += sizeof(uint16_t) * ((size_t)kCornerCap + (size_t)maxRh * ((SP >> 2) + 2)) + (size_t)SP;
+        smem += sizeof(uint32_t) * ((size_t)maxRh * BP + (size_t)(TP >> 2));
+        smem += listBytes + (size_t)SP;
         smem = (smem + 127) & ~(size_t)127;
         static size_t configured = 0;
         if (smem > 48 * 1024 && smem > configured) {
             ORBX_CUDA(c, cudaFuncSetAttribute(fastStripKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             configured = smem;
         }
+        const uint32_t rcpBP4 = 0xffffffffu / (uint32_t)(BP * 4) + 1u;
         dim3 grid(g.stripsPerFrame, batch), block(kFastThreads);
         fastStripKernel<<<grid, block, smem, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr,
-                                                         c->dCand, c->dCandCount, TP, TR, SP);
+                                                         c->dCand, c->dCandCount, TP, TR, SP, (int)listBytes, rcpBP4);
         launches = 1;
     }
     stageEnd(c, ST_FAST, launches);
