@@ -154,7 +154,7 @@ static int configure(Ctx* c, int w, int h)
         q.outBase = outBase; outBase += q.outCap;
         q.planeOff = planeOff; planeOff += (size_t)q.pitch * q.h * c->maxBatch; planeOff = (planeOff + 255) & ~(size_t)255;
         q.blurOff = blurOff; blurOff += (size_t)q.pitch * q.h * c->maxBatch; blurOff = (blurOff + 255) & ~(size_t)255;
-        q.tilesX = (q.w + 127) / 128; q.tilesY = (q.h + 63) / 64; // blur tiles (k_blur.cu)
+        q.tilesX = (q.w + kBlurTW - 1) / kBlurTW; q.tilesY = (q.h + kBlurTH - 1) / kBlurTH; // blur tiles (k_blur.cu)
         q.tileBase = tileBase; tileBase += q.tilesX * q.tilesY;
         // FAST strips: segments of whole cells, at most 320 candidate columns and 32 cells each (k_fast.cu)
         q.stripBase = stripBase; q.segsPerRow = 0; q.cellsPerSeg = 1;
