@@ -60,6 +60,81 @@ resizeLinearKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sFrame
     }
 }
 
+
+// Fast path (scale <= ~1.33, word-aligned source): the 4 destination pixels of a thread read at most 8 consecutive
+// source bytes counted from an aligned word, so one horizontal pass is 3 aligned 32-bit loads, and per pixel one
+// funnel shift (bytes s, s+1 into the low half) and one IDP.2A against the (c0, c1) weight pair.
+constexpr int kResizeRowsFast = 16;
+
+__global__ void __launch_bounds__(128)
+resizeLinearWordKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sFrame, int sw, int sh,
+                       uint8_t* __restrict__ dst, size_t dPitch, size_t dFrame, int dw, int dh,
+                       const ResizeTap* __restrict__ tapX, const ResizeTap* __restrict__ tapY, int frame0)
+{
+    const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (x0 >= dw) return;
+    uint32_t cpair[4], shift[4]; bool second[4];
+    int base = 0;
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const ResizeTap tx = tapX[min(x0 + i, dw - 1)];
+        if (i == 0) base = tx.s >> 2;
+        const int off = tx.s - 4 * base;                    // 0..7 (checked on the host)
+        second[i] = off >= 4; shift[i] = 8u * (off & 3);
+        cpair[i] = (uint32_t)(uint16_t)tx.c0 | ((uint32_t)(uint16_t)tx.c1 << 16);
+    }
+    const int lastWord = (int)(sPitch >> 2) - 1;
+    const int i0 = base, i1 = min(base + 1, lastWord), i2 = min(base + 2, lastWord);
+    const uint8_t* S = src + (size_t)(blockIdx.z + frame0) * sFrame;
+    uint8_t* D = dst + (size_t)(blockIdx.z + frame0) * dFrame + x0;
+    const int yb = blockIdx.y * kResizeRowsFast, ye = min(yb + kResizeRowsFast, dh);
+    // Source rows are walked once, four at a time (12 independent loads in flight per thread); a destination row is
+    // written as soon as its second source row has been reduced horizontally.
+    auto hcompute = [&](const uint32_t (&w)[3], uint32_t (&t)[4]) {
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t lo = second[i] ? w[1] : w[0], hi = second[i] ? w[2] : w[1];
+            t[i] = __dp2a_lo(cpair[i], __funnelshift_r(lo, hi, shift[i]), 0u) >> 4;
+        }
+    };
+    auto loadRow = [&](int r, uint32_t (&w)[3]) {
+        const uint32_t* row = reinterpret_cast<const uint32_t*>(S + (size_t)min(r, sh - 1) * sPitch);   // rows are clipped, weights kept (OpenCV VResize)
+        w[0] = __ldg(row + i0); w[1] = __ldg(row + i1); w[2] = __ldg(row + i2);
+    };
+    int y = yb;
+    ResizeTap ty = tapY[y];
+    uint32_t tp[4];
+    {
+        uint32_t w[3];
+        loadRow(ty.s, w);
+        hcompute(w, tp);
+    }
+    for (int rb = ty.s + 1; y < ye; rb += 4) {
+        uint32_t w[4][3];
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) loadRow(rb + k, w[k]);
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint32_t tc[4];
+            hcompute(w[k], tc);
+            while (y < ye && ty.s == rb + k - 1) {          // rows (rb+k-1, rb+k) are this destination row's pair
+                // (b * t) >> 16 as the high word of (b << 16) * t: weights and sums are non-negative
+                const uint32_t b0 = (uint32_t)ty.c0 << 16, b1 = (uint32_t)ty.c1 << 16;
+                uint32_t packed = 0;
+                #pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t v = (__umulhi(b0, tp[i]) + __umulhi(b1, tc[i]) + 2u) >> 2;
+                    packed |= (v & 0xffu) << (8 * i);
+                }
+                *reinterpret_cast<uint32_t*>(D + (size_t)y * dPitch) = packed;
+                if (++y < ye) ty = tapY[y];
+            }
+            #pragma unroll
+            for (int i = 0; i < 4; ++i) tp[i] = tc[i];
+        }
+    }
+}
+
 int launchPyramid(Ctx* c, int frame0, int batch)
 {
     const GeomSet& g = c->geom;
@@ -71,9 +146,16 @@ int launchPyramid(Ctx* c, int frame0, int batch)
         const uint8_t* src; size_t sp, sf;
         if (l == 1) { src = c->lvl0; sp = c->lvl0Pitch; sf = c->lvl0FrameStride; }
         else { src = c->dPyr + s.planeOff; sp = (size_t)s.pitch; sf = (size_t)s.pitch * s.h; }
-        dim3 grid((d.w + 511) / 512, (d.h + kResizeRows - 1) / kResizeRows, batch), block(128);
-        resizeLinearKernel<<<grid, block, 0, c->stream>>>(src, sp, sf, s.w, s.h, c->dPyr + d.planeOff, (size_t)d.pitch,
-                                                         (size_t)d.pitch * d.h, d.w, d.h, c->dTapX[l], c->dTapY[l], frame0);
+        const bool wordOk = c->resizeWordOk[l] && ((((size_t)src) | sp | sf) & 3) == 0;
+        if (wordOk) {
+            dim3 grid((d.w + 511) / 512, (d.h + kResizeRowsFast - 1) / kResizeRowsFast, batch), block(128);
+            resizeLinearWordKernel<<<grid, block, 0, c->stream>>>(src, sp, sf, s.w, s.h, c->dPyr + d.planeOff, (size_t)d.pitch,
+                                                                 (size_t)d.pitch * d.h, d.w, d.h, c->dTapX[l], c->dTapY[l], frame0);
+        } else {
+            dim3 grid((d.w + 511) / 512, (d.h + kResizeRows - 1) / kResizeRows, batch), block(128);
+            resizeLinearKernel<<<grid, block, 0, c->stream>>>(src, sp, sf, s.w, s.h, c->dPyr + d.planeOff, (size_t)d.pitch,
+                                                             (size_t)d.pitch * d.h, d.w, d.h, c->dTapX[l], c->dTapY[l], frame0);
+        }
         ++launches;
     }
     stageEnd(c, ST_PYRAMID, launches);

@@ -182,6 +182,14 @@ static int configure(Ctx* c, int w, int h)
         std::vector<ResizeTap> tx, ty;
         buildTaps(g.lv[l].w, g.lv[l - 1].w, true, tx);
         buildTaps(g.lv[l].h, g.lv[l - 1].h, false, ty);
+        bool wordOk = true;
+        for (size_t x = 0; x < tx.size(); x += 4) {
+            const int last = tx[std::min(x + 3, tx.size() - 1)].s, first = tx[x].s;
+            if (last < first || last - (first & ~3) > 7) wordOk = false;
+        }
+        for (const ResizeTap& t : tx) if (t.c0 < 0 || t.c1 < 0) wordOk = false;
+        for (const ResizeTap& t : ty) if (t.c0 < 0 || t.c1 < 0) wordOk = false;
+        c->resizeWordOk[l] = wordOk;
         ORBX_CUDA(c, cudaMalloc(&c->dTapX[l], sizeof(ResizeTap) * tx.size()));
         ORBX_CUDA(c, cudaMalloc(&c->dTapY[l], sizeof(ResizeTap) * ty.size()));
         ORBX_CUDA(c, cudaMemcpy(c->dTapX[l], tx.data(), sizeof(ResizeTap) * tx.size(), cudaMemcpyHostToDevice));

@@ -74,6 +74,7 @@ struct Ctx {
     GeomSet* dGeom = nullptr;            // device copy (global memory; kernels read via __ldg / constant cache)
     ResizeTap* dTapX[kMaxLevels] = {};   // per-level tables (level l = taps from level l-1)
     ResizeTap* dTapY[kMaxLevels] = {};
+    bool resizeWordOk[kMaxLevels] = {};  // level l: every 4-pixel group reads <= 8 source bytes from an aligned word (k_pyramid.cu fast path)
     // arenas
     uint8_t* dPyr = nullptr; size_t pyrBytes = 0;      // levels (level 0 too unless used in place)
     uint8_t* dBlur = nullptr; size_t blurBytes = 0;
