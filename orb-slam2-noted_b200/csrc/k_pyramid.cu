@@ -73,62 +73,68 @@ resizeLinearWordKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sF
 {
     const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (x0 >= dw) return;
-    uint32_t cpair[4], shift[4]; bool second[4];
+    uint32_t cpair[4], shift[4], pick[4];       // pick = all ones when the pixel's byte pair starts in the second word
     int base = 0;
     #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const ResizeTap tx = tapX[min(x0 + i, dw - 1)];
         if (i == 0) base = tx.s >> 2;
         const int off = tx.s - 4 * base;                    // 0..7 (checked on the host)
-        second[i] = off >= 4; shift[i] = 8u * (off & 3);
+        pick[i] = off >= 4 ? 0xffffffffu : 0u; shift[i] = 8u * (off & 3);
         cpair[i] = (uint32_t)(uint16_t)tx.c0 | ((uint32_t)(uint16_t)tx.c1 << 16);
     }
-    const int lastWord = (int)(sPitch >> 2) - 1;
-    const int i0 = base, i1 = min(base + 1, lastWord), i2 = min(base + 2, lastWord);
-    const uint8_t* S = src + (size_t)(blockIdx.z + frame0) * sFrame;
-    uint8_t* D = dst + (size_t)(blockIdx.z + frame0) * dFrame + x0;
+    const int pw = (int)(sPitch >> 2);
+    const bool has1 = base + 1 < pw, has2 = base + 2 < pw;   // words past the row end only ever meet zero weights
     const int yb = blockIdx.y * kResizeRowsFast, ye = min(yb + kResizeRowsFast, dh);
+    int y = yb;
+    ResizeTap ty = tapY[y];
+    int r = ty.s;                                             // source row the pointer is on
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(src + (size_t)(blockIdx.z + frame0) * sFrame + (size_t)r * sPitch) + base;
+    uint8_t* D = dst + (size_t)(blockIdx.z + frame0) * dFrame + (size_t)y * dPitch + x0;
+
     // Source rows are walked once, four at a time (12 independent loads in flight per thread); a destination row is
     // written as soon as its second source row has been reduced horizontally.
     auto hcompute = [&](const uint32_t (&w)[3], uint32_t (&t)[4]) {
+        const uint32_t x01 = w[0] ^ w[1], x12 = w[1] ^ w[2];
         #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const uint32_t lo = second[i] ? w[1] : w[0], hi = second[i] ? w[2] : w[1];
+            const uint32_t lo = w[0] ^ (x01 & pick[i]), hi = w[1] ^ (x12 & pick[i]);
             t[i] = __dp2a_lo(cpair[i], __funnelshift_r(lo, hi, shift[i]), 0u) >> 4;
         }
     };
-    auto loadRow = [&](int r, uint32_t (&w)[3]) {
-        const uint32_t* row = reinterpret_cast<const uint32_t*>(S + (size_t)min(r, sh - 1) * sPitch);   // rows are clipped, weights kept (OpenCV VResize)
-        w[0] = __ldg(row + i0); w[1] = __ldg(row + i1); w[2] = __ldg(row + i2);
+    auto loadRow = [&](uint32_t (&w)[3]) {                    // loads the row under the pointer, then steps down
+        w[0] = __ldg(p);
+        w[1] = has1 ? __ldg(p + 1) : w[0];
+        w[2] = has2 ? __ldg(p + 2) : w[1];
+        if (r < sh - 1) p += pw;                              // rows are clipped, weights kept (OpenCV VResize)
+        ++r;
     };
-    int y = yb;
-    ResizeTap ty = tapY[y];
     uint32_t tp[4];
     {
         uint32_t w[3];
-        loadRow(ty.s, w);
+        loadRow(w);
         hcompute(w, tp);
     }
-    for (int rb = ty.s + 1; y < ye; rb += 4) {
+    int rb = ty.s;                                            // tp holds row rb
+    while (y < ye) {
         uint32_t w[4][3];
         #pragma unroll
-        for (int k = 0; k < 4; ++k) loadRow(rb + k, w[k]);
+        for (int k = 0; k < 4; ++k) loadRow(w[k]);
         #pragma unroll
         for (int k = 0; k < 4; ++k) {
             uint32_t tc[4];
-            hcompute(w[k], tc);
-            while (y < ye && ty.s == rb + k - 1) {          // rows (rb+k-1, rb+k) are this destination row's pair
+            hcompute(w[k], tc);                               // row rb + 1
+            while (y < ye && ty.s == rb) {                    // rows (rb, rb+1) are this destination row's pair
                 // (b * t) >> 16 as the high word of (b << 16) * t: weights and sums are non-negative
                 const uint32_t b0 = (uint32_t)ty.c0 << 16, b1 = (uint32_t)ty.c1 << 16;
-                uint32_t packed = 0;
+                uint32_t v[4];
                 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const uint32_t v = (__umulhi(b0, tp[i]) + __umulhi(b1, tc[i]) + 2u) >> 2;
-                    packed |= (v & 0xffu) << (8 * i);
-                }
-                *reinterpret_cast<uint32_t*>(D + (size_t)y * dPitch) = packed;
+                for (int i = 0; i < 4; ++i) v[i] = (__umulhi(b0, tp[i]) + __umulhi(b1, tc[i]) + 2u) >> 2;   // <= 255
+                *reinterpret_cast<uint32_t*>(D) = (v[0] + (v[1] << 8)) + ((v[2] << 16) + (v[3] << 24));
+                D += dPitch;
                 if (++y < ye) ty = tapY[y];
             }
+            ++rb;
             #pragma unroll
             for (int i = 0; i < 4; ++i) tp[i] = tc[i];
         }
