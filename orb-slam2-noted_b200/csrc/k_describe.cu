@@ -10,6 +10,7 @@
 //    reduction + polynomial with exactly the FMA contraction pattern of that build;
 //  * sample coordinates use cvRound = round-half-even = __float2int_rn.
 #include "orbx_internal.h"
+#include <algorithm>
 
 namespace orbx {
 
@@ -97,8 +98,16 @@ __global__ void atan2ProbeKernel(const float* yx, int n, float* out)
 }
 
 constexpr int kDescWarps = 8;
-constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitchW = 11;   // blurred patch: 37 rows x 44 bytes per warp
-constexpr int kRawRows = 2 * kHalfPatch + 1, kRawPitchW = 9;                   // raw patch: 31 rows x 36 bytes per warp
+constexpr int kKpPerWarp = 4;                                                  // consecutive keypoints per warp, patches double-buffered
+constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitchW = 11;   // blurred patch: 37 rows x 44 bytes
+constexpr int kRawRows = 2 * kHalfPatch + 1, kRawPitchW = 9;                   // raw patch: 31 rows x 36 bytes
+constexpr int kPatchWords = kPatchRows * kPatchPitchW, kRawWords = kRawRows * kRawPitchW;
+constexpr int kBufWords = kPatchWords + kRawWords;
+
+__device__ __forceinline__ void cpAsync4(uint32_t dst, const void* src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
 
 __global__ void __launch_bounds__(kDescWarps * 32)
 describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
@@ -107,123 +116,133 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
                orbx_keypoint* __restrict__ outKp, uint8_t* __restrict__ outDesc, int cap, int* __restrict__ outN,
                int* __restrict__ err)
 {
-    const int lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * kDescWarps + (threadIdx.x >> 5);
+    __shared__ __align__(16) uint32_t sBuf[kDescWarps][2][kBufWords];
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
     const int frame = blockIdx.y + G.frame0;
-    if (slot >= G.selPerFrame) return;
-    int level = 0;
-    while (level + 1 < G.nlevels && slot >= G.lv[level + 1].outBase) ++level;
-    const LevelGeom& g = G.lv[level];
-    const int pos = slot - g.outBase;
-    const int* cnts = selCount + frame * G.nlevels;
-    int before = 0, total = 0;
-    for (int l = 0; l < G.nlevels; ++l) { const int c = cnts[l]; if (l < level) before += c; total += c; }
-    if (slot == 0 && lane == 0) outN[frame] = min(total, cap);
-    if (pos >= cnts[level]) return;
-    const int idx = before + pos;
-    if (idx >= cap) { if (lane == 0) atomicExch(err, 5); return; }
 
-    orbx_keypoint kp = selAll[(size_t)frame * G.selPerFrame + slot];
-    const int cx = __float2int_rn(kp.x), cy = __float2int_rn(kp.y);
-    const uint8_t* img; size_t pitch;
-    if (level == 0) { img = lvl0 + (size_t)frame * lvl0Frame; pitch = lvl0Pitch; }
-    else { img = pyr + g.planeOff + (size_t)frame * g.pitch * g.h; pitch = (size_t)g.pitch; }
+    // level-major output index = running count over the levels (final assembly of operator(), :1595-1656)
+    const int cnt = lane < G.nlevels ? selCount[frame * G.nlevels + lane] : 0;
+    int incl = cnt;
+    #pragma unroll
+    for (int o = 1; o < kMaxLevels; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    const int total = __shfl_sync(0xffffffffu, incl, G.nlevels - 1);
+    if (blockIdx.x == 0 && threadIdx.x == 0) outN[frame] = min(total, cap);
+    const int i0 = (blockIdx.x * kDescWarps + wrp) * kKpPerWarp;
+    if (i0 >= total) return;
+    if (total > cap) { if (lane == 0) atomicExch(err, 5); if (i0 >= cap) return; }
+    const int nkp = min(kKpPerWarp, min(total, cap) - i0);
 
-    // ---- stage both patches in shared memory with aligned word loads issued back to back (one memory round trip):
-    //      the 37 x 37 blurred patch for BRIEF (rotated pattern points stay within +-18; 10 words per row: 4 rows x 8
-    //      words per warp load + a 2-word tail) and the 31 x 31 raw patch for IC_Angle (9 words per row, 3 rows per load).
-    //      All later accesses are shared-memory loads with compile-time offsets. ----
-    __shared__ uint32_t sPatch[kDescWarps][kPatchRows * kPatchPitchW];
-    __shared__ uint32_t sRaw[kDescWarps][kRawRows * kRawPitchW];
-    uint32_t* patch = sPatch[threadIdx.x >> 5];
-    uint32_t* rawp = sRaw[threadIdx.x >> 5];
-    const int bp = g.pitch;
-    const int a0 = (cx - kPatchR) & ~3;                         // aligned first column of the blurred patch
-    const int offc = (cx - kPatchR) - a0 + kPatchR;             // byte column of the patch centre inside a staged row
-    const uint8_t* bsrc = blur + g.blurOff + (size_t)frame * g.pitch * g.h + (size_t)(cy - kPatchR) * bp + a0;
+    // lane k < nkp owns keypoint i0 + k: its level, its record
+    int myLevel = 0; orbx_keypoint kp = {};
     {
-        const int lr = lane >> 3, lk = lane & 7;
-        const uint8_t* p0 = bsrc + (size_t)lr * bp + 4 * lk;
+        const int i = i0 + min(lane, nkp - 1);
         #pragma unroll
-        for (int t = 0; t < (kPatchRows + 3) / 4; ++t) {        // words 0..7 of rows 4t + lr
-            const int r = 4 * t + lr;
-            uint32_t w = 0;
-            if (r < kPatchRows) w = __ldg(reinterpret_cast<const uint32_t*>(p0 + (size_t)(4 * t) * bp));
-            if (r < kPatchRows) patch[r * kPatchPitchW + lk] = w;
-        }
-        const int tr = lane >> 1, tk = 8 + (lane & 1);
-        const bool tailOk = a0 + 4 * tk + 3 < bp;               // the last word may start beyond the padded row: never used then
-        const uint8_t* p1 = bsrc + (size_t)tr * bp + 4 * tk;
-        #pragma unroll
-        for (int t = 0; t < (kPatchRows + 15) / 16; ++t) {      // words 8..9 of rows 16t + tr
-            const int r = 16 * t + tr;
-            uint32_t w = 0;
-            if (r < kPatchRows && tailOk) w = __ldg(reinterpret_cast<const uint32_t*>(p1 + (size_t)(16 * t) * bp));
-            if (r < kPatchRows) patch[r * kPatchPitchW + tk] = w;
-        }
+        for (int l = 0; l < kMaxLevels; ++l) myLevel += (l < G.nlevels - 1 && __shfl_sync(0xffffffffu, incl, l) <= i) ? 1 : 0;
+        const int before = __shfl_sync(0xffffffffu, incl - cnt, myLevel);
+        if (lane < nkp) kp = selAll[(size_t)frame * G.selPerFrame + G.lv[myLevel].outBase + (i - before)];
     }
-    const int ra0 = (cx - kHalfPatch) & ~3;
-    const int offr = (cx - kHalfPatch) - ra0 + kHalfPatch;      // byte column of the centre inside a staged raw row
-    const bool rawWords = ((((size_t)img) | pitch) & 3) == 0;
-    if (rawWords) {
-        const int lr = lane / 9, lk = lane - lr * 9;
-        const uint8_t* p0 = img + (size_t)(cy - kHalfPatch + lr) * pitch + ra0 + 4 * lk;
-        const bool ok = lane < 27 && (size_t)(ra0 + 4 * lk + 3) < pitch;
-        #pragma unroll
-        for (int t = 0; t < (kRawRows + 2) / 3; ++t) {          // rows 3t + lr
-            const int r = 3 * t + lr;
-            uint32_t w = 0;
-            if (ok && r < kRawRows) w = __ldg(reinterpret_cast<const uint32_t*>(p0 + (size_t)(3 * t) * pitch));
-            if (lane < 27 && r < kRawRows) rawp[r * kRawPitchW + lk] = w;
-        }
-    } else {                                                     // unaligned caller image (level 0 only): byte loads
-        uint8_t* rb = reinterpret_cast<uint8_t*>(rawp);
-        for (int i = lane; i < kRawRows * 31; i += 32) {
-            const int r = i / 31, c = i - r * 31;
-            rb[r * (kRawPitchW * 4) + (offr - kHalfPatch) + c] = img[(size_t)(cy - kHalfPatch + r) * pitch + cx - kHalfPatch + c];
-        }
-    }
-    __syncwarp();
 
-    // ---- IC_Angle: lane = column u of the disc, its 31 rows at compile-time offsets ----
-    int m10 = 0, m01 = 0;
-    if (lane < 2 * kHalfPatch + 1) {
-        const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
-        const uint8_t* col = reinterpret_cast<const uint8_t*>(rawp) + offr + u;
-        int cs = 0;
-        #pragma unroll
-        for (int vi = 0; vi <= 2 * kHalfPatch; ++vi) {
-            const int v = vi - kHalfPatch;
-            if (au <= G.umax[v < 0 ? -v : v]) { const int p = col[vi * (kRawPitchW * 4)]; cs += p; m01 += v * p; }
+    // ---- patches come into shared memory as 4-byte async copies, one commit group per keypoint, two keypoints in
+    //      flight: the 37 x 37 blurred patch for BRIEF (rotated pattern points stay within +-18; 10 words per row) and
+    //      the 31 x 31 raw patch for IC_Angle (9 words per row).  All later accesses are shared-memory loads. ----
+    auto issue = [&](int k) {
+        const int level = __shfl_sync(0xffffffffu, myLevel, k);
+        const int cx = __float2int_rn(__shfl_sync(0xffffffffu, kp.x, k)), cy = __float2int_rn(__shfl_sync(0xffffffffu, kp.y, k));
+        const LevelGeom& g = G.lv[level];
+        uint32_t* buf = sBuf[wrp][k & 1];
+        const int bp = g.pitch;
+        {
+            const int a0 = (cx - kPatchR) & ~3;                     // aligned first column of the blurred patch
+            const int lr = lane / 10, lk = lane - lr * 10;          // 3 rows x 10 words per step
+            const bool ok = lane < 30 && a0 + 4 * lk + 3 < bp;      // a word starting beyond the padded row is never used
+            const uint8_t* src = blur + g.blurOff + ((size_t)frame * g.h + (cy - kPatchR + lr)) * bp + a0 + 4 * lk;
+            uint32_t dst = (uint32_t)__cvta_generic_to_shared(buf + lr * kPatchPitchW + lk);
+            #pragma unroll
+            for (int t = 0; t < (kPatchRows + 2) / 3; ++t) {
+                if (ok && 3 * t + lr < kPatchRows) cpAsync4(dst, src);
+                src += 3 * bp; dst += 3 * kPatchPitchW * 4;
+            }
         }
-        m10 = u * cs;
-    }
-    #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { m10 += __shfl_xor_sync(0xffffffffu, m10, o); m01 += __shfl_xor_sync(0xffffffffu, m01, o); }
-    const float angle = fastAtan2Dev((float)m01, (float)m10);
+        const uint8_t* img; int pitch;
+        if (level == 0) { img = lvl0 + (size_t)frame * lvl0Frame; pitch = (int)lvl0Pitch; }
+        else { img = pyr + g.planeOff + (size_t)frame * g.pitch * g.h; pitch = g.pitch; }
+        const int ra0 = (cx - kHalfPatch) & ~3;
+        if (((((size_t)img) | (size_t)pitch) & 3) == 0) {
+            const int lr = lane / 9, lk = lane - lr * 9;            // 3 rows x 9 words per step
+            const bool ok = lane < 27 && ra0 + 4 * lk + 3 < pitch;
+            const uint8_t* src = img + (size_t)(cy - kHalfPatch + lr) * pitch + ra0 + 4 * lk;
+            uint32_t dst = (uint32_t)__cvta_generic_to_shared(buf + kPatchWords + lr * kRawPitchW + lk);
+            #pragma unroll
+            for (int t = 0; t < (kRawRows + 2) / 3; ++t) {
+                if (ok && 3 * t + lr < kRawRows) cpAsync4(dst, src);
+                src += 3 * pitch; dst += 3 * kRawPitchW * 4;
+            }
+        } else {                                                     // unaligned caller image (level 0 only): byte loads
+            uint8_t* rb = reinterpret_cast<uint8_t*>(buf + kPatchWords);
+            const int offr = (cx - kHalfPatch) - ra0;
+            for (int i = lane; i < kRawRows * 31; i += 32) {
+                const int r = i / 31, c = i - r * 31;
+                rb[r * (kRawPitchW * 4) + offr + c] = img[(size_t)(cy - kHalfPatch + r) * pitch + cx - kHalfPatch + c];
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
 
-    // ---- steered BRIEF on the blurred patch: lane = descriptor byte ----
-    const float factorPI = (float)(3.14159265358979323846 / 180.f);
-    float a, b;
-    glibcSinCosf(__fmul_rn(angle, factorPI), b, a); // a = cos, b = sin  (:158)
-    const uint8_t* pc = reinterpret_cast<const uint8_t*>(patch) + kPatchR * (kPatchPitchW * 4) + offc;
-    const float4* pat = reinterpret_cast<const float4*>(kBriefPatternF) + lane * 8;
-    int val = 0;
-    #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const float4 q = __ldg(pat + k);
-        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(q.x, b), __fmul_rn(q.y, a)));
-        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(q.x, a), __fmul_rn(q.y, b)));
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(q.z, b), __fmul_rn(q.w, a)));
-        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(q.z, a), __fmul_rn(q.w, b)));
-        const int t0 = pc[r0 * (kPatchPitchW * 4) + c0], t1 = pc[r1 * (kPatchPitchW * 4) + c1];
-        val |= (t0 < t1) << k;
-    }
-    outDesc[((size_t)frame * cap + idx) * 32 + lane] = (uint8_t)val;
-    if (lane == 0) {
-        kp.angle = angle;
-        if (level != 0) { kp.x = __fmul_rn(kp.x, g.scale); kp.y = __fmul_rn(kp.y, g.scale); }
-        outKp[(size_t)frame * cap + idx] = kp;
+    issue(0);
+    if (nkp > 1) issue(1);
+    for (int k = 0; k < nkp; ++k) {
+        if (k + 1 < nkp) asm volatile("cp.async.wait_group 1;" ::: "memory");
+        else asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
+        const int level = __shfl_sync(0xffffffffu, myLevel, k);
+        const int cx = __float2int_rn(__shfl_sync(0xffffffffu, kp.x, k));
+        const uint32_t* buf = sBuf[wrp][k & 1];
+
+        // ---- IC_Angle: lane = column u of the disc, its 31 rows at compile-time offsets ----
+        int m10 = 0, m01 = 0;
+        if (lane < 2 * kHalfPatch + 1) {
+            const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
+            const int offr = (cx - kHalfPatch) - ((cx - kHalfPatch) & ~3) + kHalfPatch;   // byte column of the centre inside a staged raw row
+            const uint8_t* col = reinterpret_cast<const uint8_t*>(buf + kPatchWords) + offr + u;
+            int cs = 0;
+            #pragma unroll
+            for (int vi = 0; vi <= 2 * kHalfPatch; ++vi) {
+                const int v = vi - kHalfPatch;
+                if (au <= G.umax[v < 0 ? -v : v]) { const int p = col[vi * (kRawPitchW * 4)]; cs += p; m01 += v * p; }
+            }
+            m10 = u * cs;
+        }
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { m10 += __shfl_xor_sync(0xffffffffu, m10, o); m01 += __shfl_xor_sync(0xffffffffu, m01, o); }
+        const float angle = fastAtan2Dev((float)m01, (float)m10);
+
+        // ---- steered BRIEF on the blurred patch: lane = descriptor byte ----
+        const float factorPI = (float)(3.14159265358979323846 / 180.f);
+        float a, b;
+        glibcSinCosf(__fmul_rn(angle, factorPI), b, a); // a = cos, b = sin  (:158)
+        const int offc = (cx - kPatchR) - ((cx - kPatchR) & ~3) + kPatchR;                 // byte column of the patch centre
+        const uint8_t* pc = reinterpret_cast<const uint8_t*>(buf) + kPatchR * (kPatchPitchW * 4) + offc;
+        const float4* pat = reinterpret_cast<const float4*>(kBriefPatternF) + lane * 8;
+        int val = 0;
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float4 q = __ldg(pat + j);
+            const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(q.x, b), __fmul_rn(q.y, a)));
+            const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(q.x, a), __fmul_rn(q.y, b)));
+            const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(q.z, b), __fmul_rn(q.w, a)));
+            const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(q.z, a), __fmul_rn(q.w, b)));
+            const int t0 = pc[r0 * (kPatchPitchW * 4) + c0], t1 = pc[r1 * (kPatchPitchW * 4) + c1];
+            val |= (t0 < t1) << j;
+        }
+        const int idx = i0 + k;
+        outDesc[((size_t)frame * cap + idx) * 32 + lane] = (uint8_t)val;
+        if (lane == k) {
+            kp.angle = angle;
+            if (level != 0) { const float sc = G.lv[level].scale; kp.x = __fmul_rn(kp.x, sc); kp.y = __fmul_rn(kp.y, sc); }
+            outKp[(size_t)frame * cap + idx] = kp;
+        }
+        __syncwarp();                                              // everyone is done with this buffer
+        if (k + 2 < nkp) issue(k + 2);
     }
 }
 
@@ -232,7 +251,8 @@ int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* 
     GeomSet g = c->geom;
     g.frame0 = frame0;
     stageBegin(c, ST_DESCRIBE);
-    dim3 grid((g.selPerFrame + kDescWarps - 1) / kDescWarps, batch), block(kDescWarps * 32);
+    const int perBlock = kDescWarps * kKpPerWarp;
+    dim3 grid((std::min(g.selPerFrame, capPerFrame) + perBlock - 1) / perBlock, batch), block(kDescWarps * 32);
     describeKernel<<<grid, block, 0, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur,
                                                  c->dSel, c->dSelCount, dKps, dDesc, capPerFrame, dN, c->dErr);
     stageEnd(c, ST_DESCRIBE, 1);
