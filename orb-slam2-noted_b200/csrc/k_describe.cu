@@ -188,6 +188,19 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
 
+    // IC_Angle row mask of this lane (row v = lane - 15): bytes t = u + 15 with |u| <= umax[|v|]
+    uint32_t icMask[8];
+    {
+        const int v = lane - kHalfPatch, d = lane < 2 * kHalfPatch + 1 ? G.umax[v < 0 ? -v : v] : -1;
+        const int lo = kHalfPatch - d, hi = kHalfPatch + d;            // inclusive byte range (empty when d < 0)
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            uint32_t m = 0;
+            #pragma unroll
+            for (int b2 = 0; b2 < 4; ++b2) if (4 * j + b2 >= lo && 4 * j + b2 <= hi) m |= 0xffu << (8 * b2);
+            icMask[j] = m;
+        }
+    }
     issue(0);
     if (nkp > 1) issue(1);
     for (int k = 0; k < nkp; ++k) {
@@ -198,22 +211,29 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
         const int cx = __float2int_rn(__shfl_sync(0xffffffffu, kp.x, k));
         const uint32_t* buf = sBuf[wrp][k & 1];
 
-        // ---- IC_Angle: lane = column u of the disc, its 31 rows at compile-time offsets ----
+        // ---- IC_Angle: lane = row v of the disc.  The row's 31 bytes are aligned into 8 words, bytes outside
+        //      |u| <= umax[|v|] are masked off, and IDP.4A gives the row sum (m01 = v * sum) and sum of u * p. ----
         int m10 = 0, m01 = 0;
         if (lane < 2 * kHalfPatch + 1) {
-            const int u = lane - kHalfPatch, au = u < 0 ? -u : u;
-            const int offr = (cx - kHalfPatch) - ((cx - kHalfPatch) & ~3) + kHalfPatch;   // byte column of the centre inside a staged raw row
-            const uint8_t* col = reinterpret_cast<const uint8_t*>(buf + kPatchWords) + offr + u;
+            const uint32_t* row = buf + kPatchWords + lane * kRawPitchW;
+            const uint32_t sh = 8u * (uint32_t)((cx - kHalfPatch) & 3);         // byte column of u = -15 inside the staged row
+            uint32_t w[kRawPitchW];
+            #pragma unroll
+            for (int j = 0; j < kRawPitchW; ++j) w[j] = row[j];
             int cs = 0;
             #pragma unroll
-            for (int vi = 0; vi <= 2 * kHalfPatch; ++vi) {
-                const int v = vi - kHalfPatch;
-                if (au <= G.umax[v < 0 ? -v : v]) { const int p = col[vi * (kRawPitchW * 4)]; cs += p; m01 += v * p; }
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t x = __funnelshift_r(w[j], w[j + 1], sh) & icMask[j];
+                // signed weights u = 4j-15 .. 4j-12 of the word's four bytes
+                const int uw = (int)(((uint32_t)(uint8_t)(4 * j - 15)) | ((uint32_t)(uint8_t)(4 * j - 14) << 8) |
+                                     ((uint32_t)(uint8_t)(4 * j - 13) << 16) | ((uint32_t)(uint8_t)(4 * j - 12) << 24));
+                cs = (int)__dp4a(x, 0x01010101u, (uint32_t)cs);
+                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(x), "r"(uw));
             }
-            m10 = u * cs;
+            m01 = (lane - kHalfPatch) * cs;
         }
-        #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) { m10 += __shfl_xor_sync(0xffffffffu, m10, o); m01 += __shfl_xor_sync(0xffffffffu, m01, o); }
+        m10 = __reduce_add_sync(0xffffffffu, m10);      // REDUX: exact integer sums, any order
+        m01 = __reduce_add_sync(0xffffffffu, m01);
         const float angle = fastAtan2Dev((float)m01, (float)m10);
 
         // ---- steered BRIEF on the blurred patch: lane = descriptor byte ----

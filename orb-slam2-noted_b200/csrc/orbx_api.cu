@@ -196,7 +196,7 @@ static int configure(Ctx* c, int w, int h)
         ORBX_CUDA(c, cudaMemcpy(c->dTapY[l], ty.data(), sizeof(ResizeTap) * ty.size(), cudaMemcpyHostToDevice));
     }
     ORBX_CUDA(c, cudaMemcpy(c->dGeom, &g, sizeof(g), cudaMemcpyHostToDevice));
-    c->curW = w; c->curH = h;
+    c->curW = w; c->curH = h; c->geomStamp++;
     return ORBX_OK;
 }
 
@@ -265,7 +265,7 @@ void orbx_destroy(orbx_ctx* h)
     for (cudaEvent_t e : c->eventPool) cudaEventDestroy(e);
     freeGeometry(c);
     void* ptrs[] = {c->dGeom, c->dPyr, c->dBlur, c->dCand, c->dCandCount, c->dSel, c->dSelCount, c->dErr,
-                    c->dOutKp, c->dOutDesc, c->dOutN, c->dIn, c->dScratch};
+                    c->dOutKp, c->dOutDesc, c->dOutN, c->dIn, c->dScratch, c->dTensorMaps};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->hPinned) cudaFreeHost(c->hPinned);
     if (c->evFence) cudaEventDestroy(c->evFence);

@@ -74,6 +74,8 @@ struct Ctx {
     GeomSet* dGeom = nullptr;            // device copy (global memory; kernels read via __ldg / constant cache)
     ResizeTap* dTapX[kMaxLevels] = {};   // per-level tables (level l = taps from level l-1)
     ResizeTap* dTapY[kMaxLevels] = {};
+    int geomStamp = 0;                   // bumped whenever the geometry / arenas change
+    void* dTensorMaps = nullptr; int mapsStamp = -1;   // CUtensorMap[2][kMaxLevels] of the blurred / pyramid planes (k_describe.cu)
     bool resizeWordOk[kMaxLevels] = {};  // level l: every 4-pixel group reads <= 8 source bytes from an aligned word (k_pyramid.cu fast path)
     // arenas
     uint8_t* dPyr = nullptr; size_t pyrBytes = 0;      // levels (level 0 too unless used in place)
