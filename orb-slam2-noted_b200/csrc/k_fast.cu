@@ -83,6 +83,7 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     __shared__ __align__(8) unsigned long long sBar;
     __shared__ int sGroupN, sCornerN, sSurvN, sBase;
     __shared__ uint32_t sRetry;
+    __shared__ int sRegG0[kMaxCellsPerStrip], sRegNg[kMaxCellsPerStrip], sNgMax;   // pass-0 regions: first group column, group columns
     __shared__ int sCellCnt[kMaxCellsPerStrip];
 
     const int frame = blockIdx.y + G.frame0;
@@ -111,7 +112,7 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     uint32_t* colValid = cornerBits + maxRh * BP;                   // per tile word column: bit 7 of the bytes to detect
     uint16_t* cornerList = reinterpret_cast<uint16_t*>(colValid + wp);                    // kCornerCap
     uint16_t* groupList = cornerList + kCornerCap;                  // up to maxRh * (SP/4 + 2) groups
-    uint32_t* survList = reinterpret_cast<uint32_t*>(cornerList);   // reuses both lists once the scores are in
+    uint32_t* survList = reinterpret_cast<uint32_t*>(groupList);    // reuses the group list once pass 1 is over
     uint8_t* colCell = reinterpret_cast<uint8_t*>(cornerList) + listBytes;                // cell column of candidate column lx
     const int TH = rh + 6;
     const bool aligned = ((((size_t)img) | pitch) & 15) == 0;
@@ -119,7 +120,10 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     const int off0 = cx0 - xa;                                      // tile column of the first candidate pixel (>= 4)
     const int nc = j1 - j0;
 
-    if (threadIdx.x == 0) { sGroupN = 0; sCornerN = 0; sSurvN = 0; }
+    if (threadIdx.x == 0) {
+        sGroupN = 0; sCornerN = 0; sSurvN = 0;
+        sRegG0[0] = off0 >> 2; sRegNg[0] = ((off0 + rw + 3) >> 2) - (off0 >> 2);
+    }
     if (threadIdx.x < kMaxCellsPerStrip) sCellCnt[threadIdx.x] = 0;
     if (aligned) {
         const int xb = min((cx1 + 3 + 15) & ~15, (int)pitch);
@@ -171,7 +175,6 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     const int tmin = G.minTh, tini = G.iniTh;
     const int g0 = off0 >> 2, g1 = (off0 + rw + 3) >> 2;            // word columns holding candidate pixels
     const int ng = g1 - g0;
-    const uint32_t rcpNg = 0xffffffffu / (uint32_t)ng + 1u;         // i / ng == umulhi(i, rcpNg) for i < 65536
     const int wCell = g.wCell;
     const uint32_t* W = reinterpret_cast<const uint32_t*>(tile);
     const int o[16] = {3 * TP, 3 * TP + 1, 2 * TP + 2, TP + 3, 3, -TP + 3, -2 * TP + 2, -3 * TP + 1,
@@ -206,19 +209,29 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
 
     unsigned long long* out = cand + (size_t)frame * G.candPerFrame + g.candBase;
     const uint8_t* cornerBytes = reinterpret_cast<const uint8_t*>(cornerBits);
-    const int nGroups = rh * ng;
 
     for (int sweep = 0; sweep < 2; ++sweep) {
         const int th = sweep ? tmin : tini;
+        int nReg = 1, ngMax = ng;                                   // sweep 0: one region, the whole strip
         if (sweep) {
-            // the retry set (:1128): cells of this strip that kept nothing at iniTh
+            // the retry set (:1128): cells of this strip that kept nothing at iniTh; each becomes a pass-0 region
             if (threadIdx.x < 32) {
-                const uint32_t m = __ballot_sync(0xffffffffu, (int)threadIdx.x < nc && sCellCnt[threadIdx.x] == 0);
-                if (threadIdx.x == 0) { sRetry = m; sGroupN = 0; sCornerN = 0; sSurvN = 0; }
+                const int j = threadIdx.x;
+                const bool mine = j < nc && sCellCnt[j] == 0;
+                const uint32_t m = __ballot_sync(0xffffffffu, mine);
+                int gFirst = (off0 + j * wCell) >> 2;
+                const int gLast = (off0 + min((j + 1) * wCell, rw) - 1) >> 2;
+                // a group column shared with a retry cell on the left is enumerated by that cell
+                if (j > 0 && ((m >> (j - 1)) & 1u) && ((off0 + j * wCell - 1) >> 2) == gFirst) ++gFirst;
+                const int n = mine ? gLast - gFirst + 1 : 0;
+                const int mx = __reduce_max_sync(0xffffffffu, n);
+                if (mine) { const int slot = __popc(m & ((1u << j) - 1u)); sRegG0[slot] = gFirst; sRegNg[slot] = n; }
+                if (j == 0) { sRetry = m; sNgMax = mx; sGroupN = 0; sCornerN = 0; sSurvN = 0; }
             }
             __syncthreads();
             const uint32_t retry = sRetry;
             if (!retry || tmin == tini) break;
+            nReg = __popc(retry); ngMax = max(sNgMax, 1);
             for (int i = threadIdx.x; i < wp; i += kFastThreads) {
                 const int lx0 = i * 4 - off0;
                 uint32_t m = 0;
@@ -241,8 +254,13 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
 
         // ---- pass 0: quick rejection, 4 pixels per step.  A 9-arc contains two adjacent compass pixels, i.e. one of
         //      {0, 8} and one of {4, 12}, all brighter or all darker. ----
-        for (int i = threadIdx.x; i < nGroups; i += kFastThreads) {
-            const int y = (int)__umulhi((uint32_t)i, rcpNg), gw = g0 + i - y * ng;
+        const int perReg = rh * ngMax;
+        const uint32_t rcpPer = 0xffffffffu / (uint32_t)perReg + 1u, rcpNgMax = 0xffffffffu / (uint32_t)ngMax + 1u;   // exact below 65536
+        for (int i = threadIdx.x; i < nReg * perReg; i += kFastThreads) {
+            const int reg = (int)__umulhi((uint32_t)i, rcpPer), rem = i - reg * perReg;
+            const int y = (int)__umulhi((uint32_t)rem, rcpNgMax), k = rem - y * ngMax;
+            if (k >= sRegNg[reg]) continue;
+            const int gw = sRegG0[reg] + k;
             const uint32_t vm = colValid[gw];
             if (!vm) continue;
             const uint32_t* c = W + (y + 3) * wp + gw;
@@ -258,6 +276,7 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
         const int nG = sGroupN;
 
         // ---- pass 1: full test of the surviving groups in batches; corners go to the list and the corner bitmap ----
+        int flushes = 0, lastN = 0;
         for (int gb = 0; gb < nG; gb += kGroupBatch) {
             const int gEnd = min(nG, gb + kGroupBatch);
             for (int ib = gb; ib < gEnd; ib += kFastThreads) {
@@ -321,6 +340,7 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
             __syncthreads();
             if (sCornerN > kCornerCap - 4 * kGroupBatch || gEnd == nG) {   // uniform: score in bulk before the list could overflow
                 const int n = sCornerN;
+                lastN = n; ++flushes;
                 scorePass(n);
                 __syncthreads();
                 if (threadIdx.x == 0) sCornerN = 0;
@@ -328,24 +348,31 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
             }
         }
 
-        // ---- nms: 8 bitmap columns per step (strict >, 8 neighbours, zero outside the pixel's own cell) ----
-        for (int it = threadIdx.x; it < rh * BP * 4; it += kFastThreads) {
-            uint32_t bits = cornerBytes[it];
-            if (!bits) continue;
-            const int ly = (int)__umulhi((uint32_t)it, rcpBP4), lxb = (it - ly * BP * 4) << 3;
-            while (bits) {
-                const int b = __ffs(bits) - 1;
-                bits &= bits - 1;
-                const int lx = lxb + b;
-                const uint8_t* r = score + (ly + 1) * SP + (lx + 1);
-                const int s = r[0];
-                const int cj = colCell[lx], cx = lx - cj * wCell;
-                bool keep = s > r[-SP] && s > r[SP];
-                if (cx > 0) keep = keep && s > r[-1] && s > r[-SP - 1] && s > r[SP - 1];
-                if (cx < wCell - 1) keep = keep && s > r[1] && s > r[-SP + 1] && s > r[SP + 1];
-                if (keep) {
-                    survList[atomicAdd(&sSurvN, 1)] = ((uint32_t)s << 16) | (uint32_t)(ly << 10) | (uint32_t)lx;
-                    if (!sweep) atomicAdd(&sCellCnt[cj], 1);
+        // ---- nms (strict >, 8 neighbours, zero outside the pixel's own cell): one list entry per thread step when the
+        //      list still holds every corner of the sweep, else 8 bitmap columns per step ----
+        auto nmsOne = [&](int ly, int lx) {
+            const uint8_t* r = score + (ly + 1) * SP + (lx + 1);
+            const int s = r[0];
+            const int cj = colCell[lx], cx = lx - cj * wCell;
+            bool keep = s > r[-SP] && s > r[SP];
+            if (cx > 0) keep = keep && s > r[-1] && s > r[-SP - 1] && s > r[SP - 1];
+            if (cx < wCell - 1) keep = keep && s > r[1] && s > r[-SP + 1] && s > r[SP + 1];
+            if (keep) {
+                survList[atomicAdd(&sSurvN, 1)] = ((uint32_t)s << 16) | (uint32_t)(ly << 10) | (uint32_t)lx;
+                if (!sweep) atomicAdd(&sCellCnt[cj], 1);
+            }
+        };
+        if (flushes == 1) {
+            for (int i = threadIdx.x; i < lastN; i += kFastThreads) { const int code = cornerList[i]; nmsOne(code >> 10, code & 1023); }
+        } else if (flushes > 1) {
+            for (int it = threadIdx.x; it < rh * BP * 4; it += kFastThreads) {
+                uint32_t bits = cornerBytes[it];
+                if (!bits) continue;
+                const int ly = (int)__umulhi((uint32_t)it, rcpBP4), lxb = (it - ly * BP * 4) << 3;
+                while (bits) {
+                    const int b = __ffs(bits) - 1;
+                    bits &= bits - 1;
+                    nmsOne(ly, lxb + b);
                 }
             }
         }
@@ -375,9 +402,9 @@ int launchFast(Ctx* c, int frame0, int batch)
     if (g.stripsPerFrame > 0) {
         const int TP = g.fastTilePitch, TR = g.fastTileRows, SP = g.fastScorePitch;
         const int maxRh = TR - 6, BP = (SP + 31) / 32;
-        // corner list + group list, reused as the survivor list (u32 records)
-        size_t listBytes = sizeof(uint16_t) * ((size_t)kCornerCap + (size_t)maxRh * ((SP >> 2) + 2));
-        listBytes = std::max(listBytes, sizeof(uint32_t) * (size_t)fastSurvivorCap(SP, maxRh));
+        // corner list, then the group list whose space is reused as the survivor list (u32 records)
+        size_t listBytes = sizeof(uint16_t) * (size_t)kCornerCap +
+                           std::max(sizeof(uint16_t) * (size_t)maxRh * ((SP >> 2) + 2), sizeof(uint32_t) * (size_t)fastSurvivorCap(SP, maxRh));
         listBytes = (listBytes + 3) & ~(size_t)3;
         size_t smem = (size_t)TP * TR + (size_t)SP * (maxRh + 2);
         smem += sizeof(uint32_t) * ((size_t)maxRh * BP + (size_t)(TP >> 2));
