@@ -27,6 +27,9 @@ def main():
         print(name + "," + ",".join(r[hdr.index(w)] if w in hdr else "" for w in WANT))
     for k in sys.argv[2:]:
         rows = list(csv.reader(io.StringIO(ncu(["-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + k]))))
+        if len(rows) < 3:
+            print(f"\n== {k}: no kernel matches in {rep}")
+            continue
         hdr = rows[1]
         iS, iE, iSm = hdr.index('Source'), hdr.index('Instructions Executed'), hdr.index('# Samples')
         data = [r for r in rows[2:] if len(r) > iE]
