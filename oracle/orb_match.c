@@ -89,6 +89,28 @@ void orc_bow_transform(const orc_vocab* V, const uint8_t* desc, int n, int level
     }
 }
 
+/* Best / second-best state of the inner loops at src/ORBmatcher.cc:325-345 (strict <, first train wins ties), for every
+ * query of every segment against the trains of the same segment; t_valid models the `continue`s at :323,:822-826.
+ * Rows are reported in q_idx list order; an empty candidate set leaves (-1, 256, 256). */
+void orc_hamming_best2(const uint8_t* q, const uint8_t* t, const int32_t* q_seg, const int32_t* q_idx, const int32_t* t_seg,
+                       const int32_t* t_idx, int nseg, const uint8_t* t_valid, int32_t* best_idx, int32_t* best_dist,
+                       int32_t* second_dist)
+{
+    for (int s = 0; s < nseg; ++s)
+        for (int a = q_seg[s]; a < q_seg[s + 1]; ++a) {
+            const int iq = q_idx ? q_idx[a] : a;
+            int best1 = 256, best2 = 256, bi = -1;
+            for (int b = t_seg[s]; b < t_seg[s + 1]; ++b) {
+                const int it = t_idx ? t_idx[b] : b;
+                if (t_valid && !t_valid[it]) continue;
+                const int dist = orc_descriptor_distance(q + 32 * (size_t)iq, t + 32 * (size_t)it);
+                if (dist < best1) { best2 = best1; best1 = dist; bi = it; }
+                else if (dist < best2) best2 = dist;
+            }
+            best_idx[a] = bi; best_dist[a] = best1; second_dist[a] = best2;
+        }
+}
+
 /* FeatureVector::addFeature (FeatureVector.cpp:37-54) for every feature with weight > 0
  * (TemplatedVocabulary.h:1184-1189): std::map order = ascending node id, features ascending.
  * Returns number of nodes; node_id[nn], node_off[nn+1], feat[n_kept]. */

@@ -70,6 +70,9 @@ int orc_extract(const orc_params* p, const uint8_t* img, int w, int h, size_t st
 
 /* ---- matcher side (orb_match.c) ---- */
 int orc_descriptor_distance(const uint8_t* a, const uint8_t* b); /* src/ORBmatcher.cc:2123-2143 */
+void orc_hamming_best2(const uint8_t* q, const uint8_t* t, const int32_t* q_seg, const int32_t* q_idx, const int32_t* t_seg,
+                       const int32_t* t_idx, int nseg, const uint8_t* t_valid, int32_t* best_idx, int32_t* best_dist,
+                       int32_t* second_dist); /* inner loops :325-345 */
 void orc_three_maxima(const int* count, int L, int* ind1, int* ind2, int* ind3); /* :2076-2118 */
 
 /* DBoW2 vocabulary tree flattened: node 0 = root; children of node i = child[child_off[i]..child_off[i+1])

@@ -186,8 +186,24 @@ def _mlib():
     L.orc_search_by_projection_points.argtypes = [vp, ci, vp, vp, ci, vp, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, cf, vp]
     L.orc_search_by_projection_frame.argtypes = [vp, ci, vp, vp, ci, vp, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, ci, ci, vp]
     L.orc_stereo_matches.argtypes = [vp, vp, ci, vp, vp, ci, vp, vp, vp, vp, vp, vp, vp, cf, cf, vp, vp]
+    L.orc_hamming_best2.argtypes = [vp, vp, vp, vp, vp, vp, ci, vp, vp, vp, vp]
     L._match_ready = True
     return L
+
+
+def hamming_best2(q, t, q_seg=None, q_idx=None, t_seg=None, t_idx=None, t_valid=None):
+    q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
+    t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)
+    if q_seg is None:
+        q_seg, t_seg = np.array([0, len(q)], np.int32), np.array([0, len(t)], np.int32)
+    q_seg, t_seg = np.ascontiguousarray(q_seg, np.int32), np.ascontiguousarray(t_seg, np.int32)
+    opt = lambda a, dt: None if a is None else np.ascontiguousarray(a, dt)
+    q_idx, t_idx, t_valid = opt(q_idx, np.int32), opt(t_idx, np.int32), opt(t_valid, np.uint8)
+    n = len(q) if q_idx is None else len(q_idx)
+    bi, bd, sd = np.empty(n, np.int32), np.empty(n, np.int32), np.empty(n, np.int32)
+    pp = lambda a: None if a is None else _p(a)
+    _mlib().orc_hamming_best2(_p(q), _p(t), _p(q_seg), pp(q_idx), _p(t_seg), pp(t_idx), len(q_seg) - 1, pp(t_valid), _p(bi), _p(bd), _p(sd))
+    return bi, bd, sd
 
 
 def three_maxima(counts):

@@ -128,3 +128,28 @@ def test_device_sincosf_and_atan2_exact(P):
     assert L.orbx_test_fast_atan2(yx.ctypes.data, len(yx), out.ctypes.data) == 0
     want = np.array([lib.orc_fast_atan2(float(a), float(b)) for a, b in yx[:50000]], np.float32)
     assert np.array_equal(out[:50000].view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("pad_x,pad_w", [(1, 3), (4, 8), (16, 32), (0, 0)])
+def test_device_input_any_alignment(P, pad_x, pad_w):
+    """Device-resident frames whose base pointer / row pitch are not 16- or even 4-byte aligned take the plain-load
+    staging paths of every kernel (no bulk copies, generic resize); results must not change."""
+    import torch
+    B, w, h = 3, 640, 480
+    imgs = np.stack([synth.frame(40 + i, w, h) for i in range(B)])
+    big = torch.zeros((B, h + 2, w + pad_w), dtype=torch.uint8, device="cuda:0")
+    view = big[:, 1:h + 1, pad_x:pad_x + w]
+    view.copy_(torch.from_numpy(imgs).to("cuda:0"))
+    ex = P.ORBextractor(1000, 1.2, 8, 20, 7, max_w=w, max_h=h, max_batch=B)
+    cap = ex.max_keypoints()
+    kps = torch.zeros((B, cap, 28), dtype=torch.uint8, device="cuda:0")
+    desc = torch.zeros((B, cap, 32), dtype=torch.uint8, device="cuda:0")
+    n = torch.zeros((B,), dtype=torch.int32, device="cuda:0")
+    ex.extract_batch_device(view, kps, desc, n)
+    ex.sync()
+    p = O.params(1000)
+    for b in range(B):
+        nb = int(n[b])
+        k = np.frombuffer(kps[b, :nb].cpu().numpy().tobytes(), dtype=P.KP_DTYPE)
+        okps, odesc = O.extract(p, imgs[b])
+        assert_kps_equal(k, okps, desc[b, :nb].cpu().numpy(), odesc, (pad_x, pad_w, b))

@@ -84,7 +84,8 @@ def test_vocab_text_loader_and_transform(P, ctx, vocs, tmp_path):
 
 
 CASES = [(1, 1500, 1400, 0.08, 0.0, 1), (2, 2000, 2000, 0.12, 0.0, 2), (3, 1200, 900, 0.05, 0.6, 1), (4, 700, 1800, 0.10, 0.3, 3),
-         (5, 3000, 3000, 0.10, 0.0, 4), (6, 40, 35, 0.05, 0.0, 2), (7, 2500, 2500, 0.02, 0.9, 3)]
+         (5, 3000, 3000, 0.10, 0.0, 4), (6, 40, 35, 0.05, 0.0, 2), (7, 2500, 2500, 0.02, 0.9, 3),
+         (8, 10000, 10000, 0.10, 0.0, 4), (9, 10000, 10000, 0.10, 0.0, 1)]   # config 4: 10 k x 10 k, brute force (one node) and BoW
 
 
 @pytest.mark.parametrize("seed,n1,n2,flip,dup,levelsup", CASES)
