@@ -122,7 +122,6 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
 
     if (threadIdx.x == 0) {
         sGroupN = 0; sCornerN = 0; sSurvN = 0;
-        sRegG0[0] = off0 >> 2; sRegNg[0] = ((off0 + rw + 3) >> 2) - (off0 >> 2);
     }
     if (threadIdx.x < kMaxCellsPerStrip) sCellCnt[threadIdx.x] = 0;
     if (aligned) {
@@ -173,6 +172,7 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     __syncthreads();
 
     const int tmin = G.minTh, tini = G.iniTh;
+    const int lane = threadIdx.x & 31;
     const int g0 = off0 >> 2, g1 = (off0 + rw + 3) >> 2;            // word columns holding candidate pixels
     const int ng = g1 - g0;
     const int wCell = g.wCell;
@@ -254,22 +254,32 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
 
         // ---- pass 0: quick rejection, 4 pixels per step.  A 9-arc contains two adjacent compass pixels, i.e. one of
         //      {0, 8} and one of {4, 12}, both differing from the centre by more than the threshold. ----
-        const int perReg = rh * ngMax;
-        const uint32_t rcpPer = 0xffffffffu / (uint32_t)perReg + 1u, rcpNgMax = 0xffffffffu / (uint32_t)ngMax + 1u;   // exact below 65536
-        for (int i = threadIdx.x; i < nReg * perReg; i += kFastThreads) {
-            const int reg = (int)__umulhi((uint32_t)i, rcpPer), rem = i - reg * perReg;
-            const int y = (int)__umulhi((uint32_t)rem, rcpNgMax), k = rem - y * ngMax;
-            if (k >= sRegNg[reg]) continue;
-            const int gw = sRegG0[reg] + k;
-            const uint32_t vm = colValid[gw];
-            if (!vm) continue;
-            const uint32_t* c = W + (y + 3) * wp + gw;
+        auto quick = [&](const uint32_t* c, uint32_t vm, int y, int gw) {
             const uint32_t v = c[0], up = c[-3 * wp], dn = c[3 * wp];
             const uint32_t p4 = __funnelshift_r(v, c[1], 24), p12 = __funnelshift_r(c[-1], v, 8);
             // |p - v| per byte (VABSDIFF4); OR-ing two difference words can only over-estimate their maximum, and the
             // sign is ignored: a superset of the exact quick test at 13 instructions (pass 1 is exact)
             const uint32_t dv = __vabsdiffu4(dn, v) | __vabsdiffu4(up, v), dh = __vabsdiffu4(p4, v) | __vabsdiffu4(p12, v);
             if (gtu4(dv, T4, nT7) & gtu4(dh, T4, nT7) & vm) groupList[atomicAdd(&sGroupN, 1)] = (uint16_t)((y << 10) | gw);   // aggregated per warp by the compiler
+        };
+        if (!sweep) {
+            // whole strip: a warp per row, a lane per group column (no index arithmetic)
+            for (int y = threadIdx.x >> 5; y < rh; y += kFastThreads / 32) {
+                const uint32_t* crow = W + (y + 3) * wp;
+                for (int gw = g0 + lane; gw < g1; gw += 32) quick(crow + gw, colValid[gw], y, gw);
+            }
+        } else {
+            // retry cells only: flat enumeration of (region, row, group column)
+            const int perReg = rh * ngMax;
+            const uint32_t rcpPer = 0xffffffffu / (uint32_t)perReg + 1u, rcpNgMax = 0xffffffffu / (uint32_t)ngMax + 1u;   // exact below 65536
+            for (int i = threadIdx.x; i < nReg * perReg; i += kFastThreads) {
+                const int reg = (int)__umulhi((uint32_t)i, rcpPer), rem = i - reg * perReg;
+                const int y = (int)__umulhi((uint32_t)rem, rcpNgMax), k = rem - y * ngMax;
+                if (k >= sRegNg[reg]) continue;
+                const int gw = sRegG0[reg] + k;
+                const uint32_t vm = colValid[gw];
+                if (vm) quick(W + (y + 3) * wp + gw, vm, y, gw);
+            }
         }
         __syncthreads();
         const int nG = sGroupN;
