@@ -32,7 +32,7 @@ def main():
             continue
         hdr = rows[1]
         iS, iE, iSm = hdr.index('Source'), hdr.index('Instructions Executed'), hdr.index('# Samples')
-        data = [r for r in rows[2:] if len(r) > iE]
+        data = [r for r in rows[2:] if len(r) > iE and r[iE].isdigit()]   # several instances repeat the header
         tot = sum(int(r[iE]) for r in data); ts = max(1, sum(int(r[iSm]) for r in data))
         print(f"\n== {k}: {tot} warp instructions, {len(data)} SASS lines, {ts} samples")
         stall = [i for i, h in enumerate(hdr) if h.startswith('stall_') and 'Not Issued' not in h]
