@@ -98,7 +98,7 @@ __global__ void atan2ProbeKernel(const float* yx, int n, float* out)
 }
 
 constexpr int kDescWarps = 8;
-constexpr int kKpPerWarp = 4;                                                  // consecutive keypoints per warp, patches double-buffered
+constexpr int kKpPerWarp = 8;                                                  // consecutive keypoints per warp, patches double-buffered
 constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitchW = 11;   // blurred patch: 37 rows x 44 bytes
 constexpr int kRawRows = 2 * kHalfPatch + 1, kRawPitchW = 9;                   // raw patch: 31 rows x 36 bytes
 constexpr int kPatchWords = kPatchRows * kPatchPitchW, kRawWords = kRawRows * kRawPitchW;
@@ -109,7 +109,7 @@ __device__ __forceinline__ void cpAsync4(uint32_t dst, const void* src)
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
 }
 
-__global__ void __launch_bounds__(kDescWarps * 32)
+__global__ void __launch_bounds__(kDescWarps * 32, 3)
 describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
                const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                const orbx_keypoint* __restrict__ selAll, const int* __restrict__ selCount,
@@ -201,6 +201,10 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
             icMask[j] = m;
         }
     }
+    // this lane's 8 test pairs of the pattern stay in registers for all keypoints of the warp
+    float4 pat[8];
+    #pragma unroll
+    for (int j = 0; j < 8; ++j) pat[j] = __ldg(reinterpret_cast<const float4*>(kBriefPatternF) + lane * 8 + j);
     issue(0);
     if (nkp > 1) issue(1);
     for (int k = 0; k < nkp; ++k) {
@@ -242,11 +246,10 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
         glibcSinCosf(__fmul_rn(angle, factorPI), b, a); // a = cos, b = sin  (:158)
         const int offc = (cx - kPatchR) - ((cx - kPatchR) & ~3) + kPatchR;                 // byte column of the patch centre
         const uint8_t* pc = reinterpret_cast<const uint8_t*>(buf) + kPatchR * (kPatchPitchW * 4) + offc;
-        const float4* pat = reinterpret_cast<const float4*>(kBriefPatternF) + lane * 8;
         int val = 0;
         #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const float4 q = __ldg(pat + j);
+            const float4 q = pat[j];
             const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(q.x, b), __fmul_rn(q.y, a)));
             const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(q.x, a), __fmul_rn(q.y, b)));
             const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(q.z, b), __fmul_rn(q.w, a)));
