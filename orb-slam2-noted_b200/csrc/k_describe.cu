@@ -98,7 +98,7 @@ __global__ void atan2ProbeKernel(const float* yx, int n, float* out)
 }
 
 constexpr int kDescWarps = 8;
-constexpr int kKpPerWarp = 8;                                                  // consecutive keypoints per warp, patches double-buffered
+constexpr int kKpPerWarp = 16;                                                  // consecutive keypoints per warp, patches double-buffered
 constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitchW = 11;   // blurred patch: 37 rows x 44 bytes
 constexpr int kRawRows = 2 * kHalfPatch + 1, kRawPitchW = 9;                   // raw patch: 31 rows x 36 bytes
 constexpr int kPatchWords = kPatchRows * kPatchPitchW, kRawWords = kRawRows * kRawPitchW;
@@ -109,7 +109,7 @@ __device__ __forceinline__ void cpAsync4(uint32_t dst, const void* src)
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
 }
 
-__global__ void __launch_bounds__(kDescWarps * 32, 3)
+__global__ void __launch_bounds__(kDescWarps * 32, 2)
 describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
                const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                const orbx_keypoint* __restrict__ selAll, const int* __restrict__ selCount,
