@@ -125,7 +125,7 @@ gauss9Kernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0
                     const uint32_t b = q ? __funnelshift_r(w1, w2, 8 * q) : w1;
                     h[q] = __dp4a(w2, 7u << (8 * q), __dp4a(b, c1, __dp4a(a, c0, 0u)));
                 }
-                const uint32_t h01 = h[0] | (h[1] << 16), h23 = h[2] | (h[3] << 16);
+                const uint32_t h01 = h[1] * 65536u + h[0], h23 = h[3] * 65536u + h[2];   // one IMAD each (sums < 65536)
                 // pair (r-1, r) completes slot (r-1) & 7
                 const int sNew = (j + 7) & 7;
                 P[sNew][0] = __byte_perm(hp01, h01, 0x5410); P[sNew][1] = __byte_perm(hp01, h01, 0x7632);
@@ -146,7 +146,8 @@ gauss9Kernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0
                     }
                     // byte 2 of each accumulator
                     const uint32_t lo = __byte_perm(v[0], v[1], 0x0062), hi = __byte_perm(v[2], v[3], 0x0062);
-                    *reinterpret_cast<uint32_t*>(out + (size_t)(r - 2 * kBlurR) * opitch) = __byte_perm(lo, hi, 0x5410);
+                    *reinterpret_cast<uint32_t*>(out) = __byte_perm(lo, hi, 0x5410);
+                    out += opitch;
                 }
             }
         }
