@@ -242,6 +242,8 @@ int orbx_create(orbx_ctx** out, int device, int nfeatures, float scale_factor, i
         if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (cudaStreamCreateWithFlags(&c->sIn, cudaStreamNonBlocking) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (cudaStreamCreateWithFlags(&c->sOut, cudaStreamNonBlocking) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
+        if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
+        if (cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (const char* e = getenv("ORBX_CHUNK")) c->chunk = atoi(e);
         if (cudaMalloc(&c->dGeom, sizeof(GeomSet)) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (cudaMalloc(&c->dCandCount, sizeof(int) * (size_t)max_batch * kMaxLevels) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
@@ -273,6 +275,8 @@ void orbx_destroy(orbx_ctx* h)
     for (cudaEvent_t e : c->evDone) cudaEventDestroy(e);
     if (c->sIn) cudaStreamDestroy(c->sIn);
     if (c->sOut) cudaStreamDestroy(c->sOut);
+    if (c->stream2) cudaStreamDestroy(c->stream2);
+    if (c->evJoin) cudaEventDestroy(c->evJoin);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete h;
 }
@@ -430,9 +434,14 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
         if (!c->evFence) ORBX_CUDA(c, cudaEventCreateWithFlags(&c->evFence, cudaEventDisableTiming));
         ORBX_CUDA(c, cudaEventRecord(c->evFence, c->stream));
         ORBX_CUDA(c, cudaStreamWaitEvent(c->sIn, c->evFence, 0));
+        ORBX_CUDA(c, cudaStreamWaitEvent(c->stream2, c->evFence, 0));
     }
+    cudaStream_t const mainStream = c->stream;
+    struct StreamRestore { Ctx* c; cudaStream_t s; ~StreamRestore() { c->stream = s; } } restoreStream{c, mainStream};   // also on error returns
+    const bool twoStreams = !inDev && nChunks > 1;
     for (int i = 0; i < nChunks; ++i) {
         const int f0 = i * chunk, n = std::min(chunk, batch - f0);
+        c->stream = (twoStreams && (i & 1)) ? c->stream2 : mainStream;   // launchers enqueue on c->stream
         if (!inDev) {
             if (frame_stride == stride * (size_t)hgt || n == 1) {
                 ORBX_CUDA(c, cudaMemcpy2DAsync(d0 + (size_t)f0 * dp * hgt, dp, imgs + (size_t)f0 * frame_stride, stride, (size_t)w,
@@ -445,11 +454,12 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
             ORBX_CUDA(c, cudaEventRecord(c->evIn[i], c->sIn));
             ORBX_CUDA(c, cudaStreamWaitEvent(c->stream, c->evIn[i], 0));
         }
-        if ((rc = launchPyramid(c, f0, n))) return rc;
-        if ((rc = launchFast(c, f0, n))) return rc;
-        if ((rc = launchOctree(c, f0, n))) return rc;
-        if ((rc = launchBlur(c, f0, n))) return rc;
-        if ((rc = launchDescribe(c, f0, n, dK, dD, sc, dN))) return rc;
+        rc = launchPyramid(c, f0, n);
+        if (!rc) rc = launchFast(c, f0, n);
+        if (!rc) rc = launchOctree(c, f0, n);
+        if (!rc) rc = launchBlur(c, f0, n);
+        if (!rc) rc = launchDescribe(c, f0, n, dK, dD, sc, dN);
+        if (rc) { c->stream = mainStream; return rc; }
         if (!outDev) {
             ORBX_CUDA(c, cudaEventRecord(c->evDone[i], c->stream));
             ORBX_CUDA(c, cudaStreamWaitEvent(c->sOut, c->evDone[i], 0));
@@ -467,6 +477,11 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
                                                (size_t)32 * cap, (size_t)n, cudaMemcpyDeviceToHost, c->sOut));
             }
         }
+    }
+    c->stream = mainStream;
+    if (twoStreams) {   // later work on the context's stream sees both halves
+        ORBX_CUDA(c, cudaEventRecord(c->evJoin, c->stream2));
+        ORBX_CUDA(c, cudaStreamWaitEvent(c->stream, c->evJoin, 0));
     }
     if (outDev) return ORBX_OK; // asynchronous; orbx_sync() reports device-side errors
     ORBX_CUDA(c, cudaStreamSynchronize(c->sOut));

@@ -59,9 +59,11 @@ struct Ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t sIn = nullptr, sOut = nullptr;   // copy streams of the chunked pipeline (H2D / D2H overlap compute)
+    cudaStream_t stream2 = nullptr;               // odd chunks of the pipeline run here, so kernels of neighbouring chunks fill each other's tails
+    cudaEvent_t evJoin = nullptr;
     std::vector<cudaEvent_t> evIn, evDone;
     cudaEvent_t evFence = nullptr;                // orders a new call's H2D after the previous call's kernels
-    int chunk = 128;                               // frames per pipeline chunk (stages of a chunk stay L2-resident)
+    int chunk = 64;                                // frames per pipeline chunk (stages of a chunk stay L2-resident)
     int nfeatures = 0, nlevels = 0, iniTh = 0, minTh = 0;
     float scaleFactor = 0;
     float scale[kMaxLevels], invScale[kMaxLevels], sigma2[kMaxLevels], invSigma2[kMaxLevels];
