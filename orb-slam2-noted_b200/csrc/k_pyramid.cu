@@ -71,8 +71,12 @@ resizeLinearWordKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sF
                        uint8_t* __restrict__ dst, size_t dPitch, size_t dFrame, int dw, int dh,
                        const ResizeTap* __restrict__ tapX, const ResizeTap* __restrict__ tapY, int frame0)
 {
-    const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-    if (x0 >= dw) return;
+    // work items = (row band, 4-pixel group) flattened, so warps stay full whatever the level width
+    const int groups = (dw + 3) >> 2;
+    const int item = blockIdx.x * blockDim.x + threadIdx.x;
+    const int band = item / groups;
+    const int x0 = (item - band * groups) * 4;
+    if (band * kResizeRowsFast >= dh) return;
     uint32_t cpair[4], shift[4], pick[4];       // pick = all ones when the pixel's byte pair starts in the second word
     int base = 0;
     #pragma unroll
@@ -85,7 +89,7 @@ resizeLinearWordKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sF
     }
     const int pw = (int)(sPitch >> 2);
     const bool has1 = base + 1 < pw, has2 = base + 2 < pw;   // words past the row end only ever meet zero weights
-    const int yb = blockIdx.y * kResizeRowsFast, ye = min(yb + kResizeRowsFast, dh);
+    const int yb = band * kResizeRowsFast, ye = min(yb + kResizeRowsFast, dh);
     int y = yb;
     ResizeTap ty = tapY[y];
     int r = ty.s;                                             // source row the pointer is on
@@ -154,7 +158,8 @@ int launchPyramid(Ctx* c, int frame0, int batch)
         else { src = c->dPyr + s.planeOff; sp = (size_t)s.pitch; sf = (size_t)s.pitch * s.h; }
         const bool wordOk = c->resizeWordOk[l] && ((((size_t)src) | sp | sf) & 3) == 0;
         if (wordOk) {
-            dim3 grid((d.w + 511) / 512, (d.h + kResizeRowsFast - 1) / kResizeRowsFast, batch), block(128);
+            const int items = ((d.w + 3) / 4) * ((d.h + kResizeRowsFast - 1) / kResizeRowsFast);
+            dim3 grid((items + 127) / 128, 1, batch), block(128);
             resizeLinearWordKernel<<<grid, block, 0, c->stream>>>(src, sp, sf, s.w, s.h, c->dPyr + d.planeOff, (size_t)d.pitch,
                                                                  (size_t)d.pitch * d.h, d.w, d.h, c->dTapX[l], c->dTapY[l], frame0);
         } else {
