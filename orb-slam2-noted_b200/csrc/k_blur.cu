@@ -110,48 +110,56 @@ gauss9Kernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0
     uint32_t hp01 = 0, hp23 = 0;
     #pragma unroll
     for (int s = 0; s < 8; ++s) { P[s][0] = P[s][1] = P[s][2] = P[s][3] = 0; }
-    for (int rb = 0; rb < nH; rb += 8) {
+
+    // one row: horizontal sums, the (r-1, r) pairs, and -- once 9 rows are in -- one output row.  j = r mod 8.
+    auto step = [&](const int j, const bool emit) {
+        // horizontal: H(x) = sum_i k_i * src(x - 4 + i), 9 consecutive bytes
+        const uint32_t w0 = rp[0], w1 = rp[1], w2 = rp[2];
+        rp += kRawW / 4;
+        uint32_t h[4];
         #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int r = rb + j;
-            if (r < nH) {                                          // warp-uniform
-                // horizontal: H(x) = sum_i k_i * src(x - 4 + i), 9 consecutive bytes
-                const uint32_t w0 = rp[0], w1 = rp[1], w2 = rp[2];
-                rp += kRawW / 4;
-                uint32_t h[4];
-                #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const uint32_t a = q ? __funnelshift_r(w0, w1, 8 * q) : w0;
-                    const uint32_t b = q ? __funnelshift_r(w1, w2, 8 * q) : w1;
-                    h[q] = __dp4a(w2, 7u << (8 * q), __dp4a(b, c1, __dp4a(a, c0, 0u)));
-                }
-                const uint32_t h01 = h[1] * 65536u + h[0], h23 = h[3] * 65536u + h[2];   // one IMAD each (sums < 65536)
-                // pair (r-1, r) completes slot (r-1) & 7
-                const int sNew = (j + 7) & 7;
-                P[sNew][0] = __byte_perm(hp01, h01, 0x5410); P[sNew][1] = __byte_perm(hp01, h01, 0x7632);
-                P[sNew][2] = __byte_perm(hp23, h23, 0x5410); P[sNew][3] = __byte_perm(hp23, h23, 0x7632);
-                hp01 = h01; hp23 = h23;
-                if (r >= 2 * kBlurR) {
-                    // vertical for output row r-8: pairs (r-8,r-7) (r-6,r-5) (r-4,r-3) (r-2,r-1) and row r
-                    uint32_t v[4];
-                    #pragma unroll
-                    for (int p = 0; p < 4; ++p) {
-                        uint32_t acc = 32768u;
-                        acc = __dp2a_lo(P[j & 7][p], k01, acc);
-                        acc = __dp2a_lo(P[(j + 2) & 7][p], k23, acc);
-                        acc = __dp2a_lo(P[(j + 4) & 7][p], k45, acc);
-                        acc = __dp2a_lo(P[(j + 6) & 7][p], k67, acc);
-                        acc = __dp2a_lo((p & 2) ? h23 : h01, (p & 1) ? (7u << 8) : 7u, acc);
-                        v[p] = acc;
-                    }
-                    // byte 2 of each accumulator
-                    const uint32_t lo = __byte_perm(v[0], v[1], 0x0062), hi = __byte_perm(v[2], v[3], 0x0062);
-                    *reinterpret_cast<uint32_t*>(out) = __byte_perm(lo, hi, 0x5410);
-                    out += opitch;
-                }
-            }
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t a = q ? __funnelshift_r(w0, w1, 8 * q) : w0;
+            const uint32_t b = q ? __funnelshift_r(w1, w2, 8 * q) : w1;
+            h[q] = __dp4a(w2, 7u << (8 * q), __dp4a(b, c1, __dp4a(a, c0, 0u)));
         }
+        const uint32_t h01 = h[1] * 65536u + h[0], h23 = h[3] * 65536u + h[2];   // one IMAD each (sums < 65536)
+        // pair (r-1, r) completes slot (r-1) & 7
+        const int sNew = (j + 7) & 7;
+        P[sNew][0] = __byte_perm(hp01, h01, 0x5410); P[sNew][1] = __byte_perm(hp01, h01, 0x7632);
+        P[sNew][2] = __byte_perm(hp23, h23, 0x5410); P[sNew][3] = __byte_perm(hp23, h23, 0x7632);
+        hp01 = h01; hp23 = h23;
+        if (emit) {
+            // vertical for output row r-8: pairs (r-8,r-7) (r-6,r-5) (r-4,r-3) (r-2,r-1) and row r
+            uint32_t v[4];
+            #pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                uint32_t acc = 32768u;
+                acc = __dp2a_lo(P[j & 7][p], k01, acc);
+                acc = __dp2a_lo(P[(j + 2) & 7][p], k23, acc);
+                acc = __dp2a_lo(P[(j + 4) & 7][p], k45, acc);
+                acc = __dp2a_lo(P[(j + 6) & 7][p], k67, acc);
+                acc = __dp2a_lo((p & 2) ? h23 : h01, (p & 1) ? (7u << 8) : 7u, acc);
+                v[p] = acc;
+            }
+            // byte 2 of each accumulator
+            const uint32_t lo = __byte_perm(v[0], v[1], 0x0062), hi = __byte_perm(v[2], v[3], 0x0062);
+            *reinterpret_cast<uint32_t*>(out) = __byte_perm(lo, hi, 0x5410);
+            out += opitch;
+        }
+    };
+    // warm-up: the 8 rows above the band's first output row
+    #pragma unroll
+    for (int j = 0; j < 8; ++j) step(j, false);
+    // steady state, 8 rows per trip without any per-row test, then the remainder
+    int r = 2 * kBlurR;
+    for (; r + 8 <= nH; r += 8) {
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) step(j, true);
     }
+    #pragma unroll
+    for (int j = 0; j < 7; ++j)
+        if (r + j < nH) step(j, true);                             // warp-uniform
 }
 
 int launchBlur(Ctx* c, int frame0, int batch)
