@@ -40,8 +40,7 @@ bowTransformKernel(const int32_t* __restrict__ childOff, const int32_t* __restri
             if (base + lane < c1) {
                 const int id = child[base + lane];
                 const uint4 b0 = nodeDesc[2 * id], b1 = nodeDesc[2 * id + 1];
-                const int d = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-                              __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+                const int d = hamming256(a0, a1, b0, b1);
                 key = ((uint32_t)d << 20) | (uint32_t)(base + lane - c0); // first child wins ties
             }
             #pragma unroll

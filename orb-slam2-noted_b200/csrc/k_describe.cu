@@ -98,7 +98,7 @@ __global__ void atan2ProbeKernel(const float* yx, int n, float* out)
 }
 
 constexpr int kDescWarps = 8;
-constexpr int kKpPerWarp = 16;                                                  // consecutive keypoints per warp, patches double-buffered
+constexpr int kKpPerWarpMax = 32;                                               // consecutive keypoints per warp (lane k owns keypoint k), patches double-buffered
 constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitchW = 11;   // blurred patch: 37 rows x 44 bytes
 constexpr int kRawRows = 2 * kHalfPatch + 1, kRawPitchW = 9;                   // raw patch: 31 rows x 36 bytes
 constexpr int kPatchWords = kPatchRows * kPatchPitchW, kRawWords = kRawRows * kRawPitchW;
@@ -114,7 +114,7 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
                const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                const orbx_keypoint* __restrict__ selAll, const int* __restrict__ selCount,
                orbx_keypoint* __restrict__ outKp, uint8_t* __restrict__ outDesc, int cap, int* __restrict__ outN,
-               int* __restrict__ err)
+               int* __restrict__ err, int kpPerWarp)
 {
     __shared__ __align__(16) uint32_t sBuf[kDescWarps][2][kBufWords];
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
@@ -127,10 +127,10 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
     for (int o = 1; o < kMaxLevels; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
     const int total = __shfl_sync(0xffffffffu, incl, G.nlevels - 1);
     if (blockIdx.x == 0 && threadIdx.x == 0) outN[frame] = min(total, cap);
-    const int i0 = (blockIdx.x * kDescWarps + wrp) * kKpPerWarp;
+    const int i0 = (blockIdx.x * kDescWarps + wrp) * kpPerWarp;
     if (i0 >= total) return;
     if (total > cap) { if (lane == 0) atomicExch(err, 5); if (i0 >= cap) return; }
-    const int nkp = min(kKpPerWarp, min(total, cap) - i0);
+    const int nkp = min(kpPerWarp, min(total, cap) - i0);
 
     // lane k < nkp owns keypoint i0 + k: its level, its record
     int myLevel = 0; orbx_keypoint kp = {};
@@ -274,10 +274,16 @@ int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* 
     GeomSet g = c->geom;
     g.frame0 = frame0;
     stageBegin(c, ST_DESCRIBE);
-    const int perBlock = kDescWarps * kKpPerWarp;
-    dim3 grid((std::min(g.selPerFrame, capPerFrame) + perBlock - 1) / perBlock, batch), block(kDescWarps * 32);
+    // keypoints per warp: as many as keeps every SM busy (the pattern registers and the count prefix are per warp)
+    const int slots = std::min(g.selPerFrame, capPerFrame);
+    int kpw = kKpPerWarpMax;
+    int smCount = 148;
+    cudaDeviceGetAttribute(&smCount, cudaDevAttrMultiProcessorCount, c->device);
+    while (kpw > 2 && (long long)batch * ((slots + kpw - 1) / kpw) < (long long)smCount * 2 * kDescWarps) kpw >>= 1;
+    const int perBlock = kDescWarps * kpw;
+    dim3 grid((slots + perBlock - 1) / perBlock, batch), block(kDescWarps * 32);
     describeKernel<<<grid, block, 0, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur,
-                                                 c->dSel, c->dSelCount, dKps, dDesc, capPerFrame, dN, c->dErr);
+                                                 c->dSel, c->dSelCount, dKps, dDesc, capPerFrame, dN, c->dErr, kpw);
     stageEnd(c, ST_DESCRIBE, 1);
     ORBX_CUDA(c, cudaGetLastError());
     return ORBX_OK;

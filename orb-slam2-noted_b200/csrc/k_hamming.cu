@@ -10,12 +10,11 @@
 
 namespace orbx {
 
-constexpr int kHamThreads = 128, kHamQPT = 2, kHamChunk = 128;
+constexpr int kHamThreads = 256, kHamQPT = 1, kHamChunk = 256;   // kHamChunk == kHamThreads: one staged train row per thread
 
 __device__ __forceinline__ int dist256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
 {
-    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+    return hamming256(a0, a1, b0, b1);
 }
 
 __global__ void pairDistanceKernel(const uint4* __restrict__ a, const uint4* __restrict__ b, int n, int32_t* __restrict__ out)
@@ -23,6 +22,11 @@ __global__ void pairDistanceKernel(const uint4* __restrict__ a, const uint4* __r
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = dist256(a[2 * i], a[2 * i + 1], b[2 * i], b[2 * i + 1]);
 }
+
+// key of a candidate: distance << 20 | scan position inside the segment; the smallest key is the reference's best
+// (lowest distance, first in list order on ties), so best / second-best updates are three integer min/max.
+constexpr int kHamPosBits = 20;
+static_assert(kHamChunk == kHamThreads, "one staged train row per thread");
 
 __global__ void __launch_bounds__(kHamThreads)
 hammingBest2Kernel(const uint4* __restrict__ qDesc, const uint4* __restrict__ tDesc,
@@ -32,50 +36,67 @@ hammingBest2Kernel(const uint4* __restrict__ qDesc, const uint4* __restrict__ tD
                    int32_t* __restrict__ bestIdx, int32_t* __restrict__ bestDist, int32_t* __restrict__ secondDist)
 {
     __shared__ uint4 sT[kHamChunk * 2];
-    __shared__ int sTi[kHamChunk]; // train descriptor index, or -1 when masked out
+    __shared__ int sPos[kHamChunk];      // scan position of the staged (valid) train descriptors
+    __shared__ int sCnt[kHamThreads / 32];
     // segment of this CTA: largest s with blockPrefix[s] <= blockIdx.x
     int lo = 0, hi = nseg;
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (blockPrefix[mid] <= (int)blockIdx.x) lo = mid; else hi = mid; }
     const int seg = lo;
     const int qb = (blockIdx.x - blockPrefix[seg]) * (kHamThreads * kHamQPT);
     const int q0 = qSeg[seg], q1 = qSeg[seg + 1], t0 = tSeg[seg], t1 = tSeg[seg + 1];
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
 
     uint4 qa[kHamQPT], qbv[kHamQPT];
-    int row[kHamQPT], b1[kHamQPT], b2[kHamQPT], bi[kHamQPT];
+    int row[kHamQPT];
+    uint32_t k1[kHamQPT], k2[kHamQPT];                      // best and second-best keys
+    const uint32_t kNone = 256u << kHamPosBits;             // distance 256, position 0: the reference's initial state
     #pragma unroll
     for (int k = 0; k < kHamQPT; ++k) {
         row[k] = q0 + qb + k * kHamThreads + threadIdx.x;
-        b1[k] = 256; b2[k] = 256; bi[k] = -1;
+        k1[k] = kNone; k2[k] = kNone;
         if (row[k] < q1) {
             const int qi = qIdx ? qIdx[row[k]] : row[k];
             qa[k] = qDesc[2 * qi]; qbv[k] = qDesc[2 * qi + 1];
         } else { qa[k] = make_uint4(0, 0, 0, 0); qbv[k] = qa[k]; }
     }
     for (int c = t0; c < t1; c += kHamChunk) {
-        const int m = min(kHamChunk, t1 - c);
+        // stage the valid train descriptors of this chunk, compacted, in list order
+        const int i = c + (int)threadIdx.x;
+        int ti = -1;
+        if (i < t1) { ti = tIdx ? tIdx[i] : i; if (tValid && !tValid[ti]) ti = -1; }
+        const uint32_t mask = __ballot_sync(0xffffffffu, ti >= 0);
+        __syncthreads();                                    // previous chunk fully consumed
+        if (lane == 0) sCnt[wrp] = __popc(mask);
         __syncthreads();
-        for (int i = threadIdx.x; i < m; i += kHamThreads) {
-            const int ti = tIdx ? tIdx[c + i] : c + i;
-            const bool ok = !tValid || tValid[ti];
-            sTi[i] = ok ? ti : -1;
-            sT[2 * i] = tDesc[2 * ti]; sT[2 * i + 1] = tDesc[2 * ti + 1];
+        int base = 0, m = 0;
+        #pragma unroll
+        for (int w = 0; w < kHamThreads / 32; ++w) { const int n = sCnt[w]; if (w < wrp) base += n; m += n; }
+        if (ti >= 0) {
+            const int p = base + __popc(mask & ((1u << lane) - 1u));
+            sPos[p] = i - t0;
+            sT[2 * p] = tDesc[2 * ti]; sT[2 * p + 1] = tDesc[2 * ti + 1];
         }
         __syncthreads();
-        for (int i = 0; i < m; ++i) {
-            const int ti = sTi[i];
-            if (ti < 0) continue; // uniform across the CTA
-            const uint4 ta = sT[2 * i], tb = sT[2 * i + 1];
+        #pragma unroll 4
+        for (int j = 0; j < m; ++j) {
+            const uint4 ta = sT[2 * j], tb = sT[2 * j + 1];
+            const uint32_t pos = (uint32_t)sPos[j];
             #pragma unroll
             for (int k = 0; k < kHamQPT; ++k) {
-                const int d = dist256(qa[k], qbv[k], ta, tb);
-                if (d < b1[k]) { b2[k] = b1[k]; b1[k] = d; bi[k] = ti; }
-                else if (d < b2[k]) b2[k] = d;
+                const uint32_t key = ((uint32_t)hamming256(qa[k], qbv[k], ta, tb) << kHamPosBits) + pos;
+                k2[k] = min(k2[k], max(k1[k], key));
+                k1[k] = min(k1[k], key);
             }
         }
     }
     #pragma unroll
     for (int k = 0; k < kHamQPT; ++k)
-        if (row[k] < q1) { bestIdx[row[k]] = bi[k]; bestDist[row[k]] = b1[k]; secondDist[row[k]] = b2[k]; }
+        if (row[k] < q1) {
+            const int d1 = (int)(k1[k] >> kHamPosBits), d2 = (int)(k2[k] >> kHamPosBits);
+            int bi = -1;
+            if (k1[k] != kNone) { const int p = t0 + (int)(k1[k] & ((1u << kHamPosBits) - 1u)); bi = tIdx ? tIdx[p] : p; }
+            bestIdx[row[k]] = bi; bestDist[row[k]] = d1; secondDist[row[k]] = d2;
+        }
 }
 
 } // namespace orbx
@@ -128,6 +149,7 @@ extern "C" int orbx_hamming_best2(orbx_ctx* h, const uint8_t* q_desc, int nq, co
     prefix[0] = 0;
     for (int s = 0; s < nseg; ++s) {
         if (q_seg[s + 1] < q_seg[s] || t_seg[s + 1] < t_seg[s]) return ORBX_E_INVALID;
+        if (t_seg[s + 1] - t_seg[s] > (1 << kHamPosBits)) return ORBX_E_CAPACITY;   // scan position field of the candidate key
         prefix[s + 1] = prefix[s] + (q_seg[s + 1] - q_seg[s] + per - 1) / per;
     }
     const int nblocks = prefix[nseg];

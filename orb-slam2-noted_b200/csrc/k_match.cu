@@ -45,8 +45,7 @@ struct BowJob {
 
 __device__ __forceinline__ int dist256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
 {
-    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-           __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+    return hamming256(a0, a1, b0, b1);
 }
 
 __device__ __forceinline__ bool queryEligible(const BowJob& J, int i1)

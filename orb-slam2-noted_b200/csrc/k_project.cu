@@ -148,8 +148,7 @@ __global__ void projDistKernel(const orbx_proj_query* __restrict__ q, int nq, co
     }
     const uint4* qd = reinterpret_cast<const uint4*>(q[lo].desc);
     const uint4 a0 = qd[0], a1 = qd[1], b0 = desc[2 * f], b1 = desc[2 * f + 1];
-    const int d = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-                  __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+    const int d = hamming256(a0, a1, b0, b1);
     rec[e] = d | ((keys[f].octave & 63) << 9) | (skip << 15);
 }
 

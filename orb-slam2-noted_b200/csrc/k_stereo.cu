@@ -43,8 +43,7 @@ stereoMatchKernel(const orbx_keypoint* __restrict__ kL, const uint4* __restrict_
         if (r.octave < levelL - 1 || r.octave > levelL + 1) continue;
         if (!(r.x >= minU && r.x <= maxU)) continue;
         const uint4 b0 = dR[2 * iR], b1 = dR[2 * iR + 1];
-        const int d = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-                      __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+        const int d = hamming256(a0, a1, b0, b1);
         best = min(best, ((uint32_t)d << 20) | (uint32_t)iR);
     }
     #pragma unroll

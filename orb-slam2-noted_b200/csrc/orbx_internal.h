@@ -104,6 +104,23 @@ struct Ctx {
     void* dScratch = nullptr; size_t scratchBytes = 0;
 };
 
+#ifdef __CUDACC__
+// 256-bit Hamming distance (DescriptorDistance, src/ORBmatcher.cc:2123-2143).  POPC is a quarter-rate pipe, LOP3 a
+// half-rate one: the eight XOR words go through a carry-save adder tree (each CSA = 2 LOP3) down to one word of weight 1,
+// two of weight 2 and one of weight 4, so 4 POPCs are issued per pair instead of 8, and the weighted sum is IMADs (third pipe).
+__device__ __forceinline__ int hamming256(const uint4& a0, const uint4& a1, const uint4& b0, const uint4& b1)
+{
+    const uint32_t x0 = a0.x ^ b0.x, x1 = a0.y ^ b0.y, x2 = a0.z ^ b0.z, x3 = a0.w ^ b0.w;
+    const uint32_t x4 = a1.x ^ b1.x, x5 = a1.y ^ b1.y, x6 = a1.z ^ b1.z, x7 = a1.w ^ b1.w;
+    const uint32_t s1 = x0 ^ x1 ^ x2, c1 = (x0 & x1) | (x2 & (x0 | x1));
+    const uint32_t s2 = x3 ^ x4 ^ x5, c2 = (x3 & x4) | (x5 & (x3 | x4));
+    const uint32_t s3 = s1 ^ s2 ^ x6, c3 = (s1 & s2) | (x6 & (s1 | s2));
+    const uint32_t ones = s3 ^ x7, c4 = s3 & x7;
+    const uint32_t t1 = c1 ^ c2 ^ c3, d1 = (c1 & c2) | (c3 & (c1 | c2));
+    return __popc(ones) + 2 * (__popc(t1) + __popc(c4)) + 4 * __popc(d1);
+}
+#endif
+
 // RAII-free helpers -----------------------------------------------------------------------------
 int cudaFail(Ctx* c, cudaError_t e, const char* what);
 #define ORBX_CUDA(c, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return orbx::cudaFail((c), e_, #call); } while (0)
