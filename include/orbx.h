@@ -150,6 +150,12 @@ typedef struct {          /* SearchForTriangulation geometry, computed by the ca
 int orbx_match_bow(orbx_ctx* ctx, int mode, const orbx_bow_side* s1, const orbx_bow_side* s2,
                    const orbx_triangulation* tri, float nnratio, int check_orientation, int flags,
                    int32_t* match, int* nmatches);
+/* The same for npairs independent keyframe pairs in one set of launches (the keyframe-pair jobs of LocalMapping /
+ * LoopClosing): pair j uses s1[j], s2[j], tri[j] (tri may be NULL unless mode == TRIANGULATE) and writes
+ * match[j] and nmatches[j].  Results are identical to npairs separate orbx_match_bow calls. */
+int orbx_match_bow_batch(orbx_ctx* ctx, int mode, int npairs, const orbx_bow_side* const* s1, const orbx_bow_side* const* s2,
+                         const orbx_triangulation* const* tri, float nnratio, int check_orientation, int flags,
+                         int32_t* const* match, int* nmatches);
 
 /* ---- window (projection) matchers.  Replace the four ORBmatcher::SearchByProjection overloads
  *      (src/ORBmatcher.cc:78-191, :431-560, :1741-1910, :1922-2065) after the caller's projection step,

@@ -22,7 +22,7 @@ namespace orbx {
 
 constexpr int kTopK = 4;
 constexpr int kThLow = 50, kHisto = 30;      // TH_LOW, HISTO_LENGTH  src/ORBmatcher.cc:57-58
-constexpr int kATh = 128, kAQpt = 2, kAChunk = 128, kARows = kATh * kAQpt;
+constexpr int kATh = 128, kAQpt = 1, kAChunk = 128, kARows = kATh * kAQpt;   // one query row per thread: more CTAs per node, more warps per SM
 constexpr uint32_t kNoKey = 0xffffffffu;
 constexpr int kPosBits = 20;
 constexpr uint32_t kPosMask = (1u << kPosBits) - 1;
@@ -165,7 +165,8 @@ bowTopKKernel(const BowJob* __restrict__ jobs)
             for (int k = 0; k < kAQpt; ++k) {
                 const int d = dist256(qa[k], qb[k], ta, tb);
                 if (!tri) {
-                    insertKey(top[k], ((uint32_t)d << kPosBits) | pos);
+                    const uint32_t key = ((uint32_t)d << kPosBits) | pos;
+                    if (key < top[k][kTopK - 1]) insertKey(top[k], key);   // rare once the list has warmed up
                 } else if (d <= kThLow) {
                     const uint32_t key = ((uint32_t)d << kPosBits) | (kPosMask - pos); // last wins ties
                     if (act[k] && key < top[k][kTopK - 1] && triGeometryOk(J, epi[k], sX[i], sY[i], sOct[i] & 255, (sOct[i] & 256) != 0))
@@ -198,6 +199,11 @@ __device__ __forceinline__ void merge2(uint32_t& a1, uint32_t& a2, uint32_t b1, 
 
 constexpr int kBWarps = 4;
 
+// Greedy replay of one vocabulary node by one warp, in the reference's row order.  Rows are taken 32 at a time: lane l
+// loads everything row r0+l needs (global memory, all lanes in parallel), then the lanes take their turns in order, each
+// turn touching only its own registers and the node's claim mask in shared memory; accepted matches are written back
+// in parallel after the batch.  A row whose top-K list cannot decide (all listed rows claimed, or the second-best
+// unknown) is rescanned exactly by the whole warp.
 __global__ void __launch_bounds__(kBWarps * 32)
 bowResolveKernel(const BowJob* __restrict__ jobs, int maskWords)
 {
@@ -213,73 +219,103 @@ bowResolveKernel(const BowJob* __restrict__ jobs, int maskWords)
     __syncwarp();
     const bool tri = J.mode == ORBX_BOW_TRIANGULATE;
     const int thAccept = J.mode == ORBX_BOW_KF_KF ? kThLow - 1 : kThLow; // '<' vs '<=' (:845 vs :348)
+    const float nnratio = J.nnratio;
 
-    for (int r = sg.x; r < sg.y; ++r) {
-        const int i1 = J.idx1[r];
-        if (!queryEligible(J, i1)) continue;
-        const uint4 e4 = *reinterpret_cast<const uint4*>(J.topk + (size_t)r * kTopK);
-        const uint32_t e[kTopK] = {e4.x, e4.y, e4.z, e4.w};
-        uint32_t u0 = kNoKey, u1 = kNoKey;
-        const bool full = e[kTopK - 1] != kNoKey;
-        #pragma unroll
-        for (int j = 0; j < kTopK; ++j) {
-            if (e[j] == kNoKey) continue;
-            const uint32_t p = tri ? kPosMask - (e[j] & kPosMask) : (e[j] & kPosMask);
-            const bool taken = (mask[p >> 5] >> (p & 31)) & 1u;
-            if (!taken) { if (u0 == kNoKey) u0 = e[j]; else if (u1 == kNoKey) u1 = e[j]; }
-        }
-        bool need = false;
-        if (u0 == kNoKey) need = full;
-        else if (!tri && (int)(u0 >> kPosBits) <= thAccept && u1 == kNoKey && full) {
-            // second-best unknown: every unlisted row is >= the last listed distance
-            const float lb = (float)(e[kTopK - 1] >> kPosBits);
-            if (!((float)(u0 >> kPosBits) < __fmul_rn(J.nnratio, lb))) need = true;
-            else u1 = e[kTopK - 1]; // accepted whatever the true second is
-        }
-        if (need) { // exact rescan of the node for this row under the current claims
-            const uint4 qa = J.desc1[2 * i1], qb = J.desc1[2 * i1 + 1];
-            Epi epi; if (tri) epi = makeEpi(J, i1);
-            uint32_t k1 = kNoKey, k2 = kNoKey;
-            for (int p = lane; p < nt; p += 32) {
-                if ((mask[p >> 5] >> (p & 31)) & 1u) continue;
-                const int i2 = J.idx2[sg.z + p];
-                if (!trainEligible(J, i2)) continue;
-                const int d = dist256(qa, qb, J.desc2[2 * i2], J.desc2[2 * i2 + 1]);
-                uint32_t key;
-                if (!tri) key = ((uint32_t)d << kPosBits) | (uint32_t)p;
-                else {
-                    if (d > kThLow) continue;
-                    const orbx_keypoint kp = J.keys2[i2];
-                    if (!triGeometryOk(J, epi, kp.x, kp.y, kp.octave, J.ur2 && J.ur2[i2] >= 0)) continue;
-                    key = ((uint32_t)d << kPosBits) | (kPosMask - (uint32_t)p);
-                }
-                if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
-            }
-            #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                const uint32_t b1 = __shfl_xor_sync(0xffffffffu, k1, o), b2 = __shfl_xor_sync(0xffffffffu, k2, o);
-                merge2(k1, k2, b1, b2);
-            }
-            u0 = k1; u1 = k2;
-        }
-        if (u0 == kNoKey) continue;
+    // accept test on (best, second) keys; returns the claimed scan position or -1
+    auto settle = [&](uint32_t u0, uint32_t u1) -> int {
+        if (u0 == kNoKey) return -1;
         const int best = (int)(u0 >> kPosBits);
         bool accept;
         if (tri) accept = true; // d <= TH_LOW and geometry were applied when the key was built
         else {
             const int second = u1 == kNoKey ? 256 : (int)(u1 >> kPosBits);
-            accept = best <= thAccept && (float)best < __fmul_rn(J.nnratio, (float)second);
+            accept = best <= thAccept && (float)best < __fmul_rn(nnratio, (float)second);
         }
-        if (!accept) continue;
+        if (!accept) return -1;
         const uint32_t p = tri ? kPosMask - (u0 & kPosMask) : (u0 & kPosMask);
-        const int i2 = J.idx2[sg.z + (int)p];
-        __syncwarp();
-        if (lane == 0) {
-            mask[p >> 5] |= 1u << (p & 31);
+        mask[p >> 5] |= 1u << (p & 31);
+        return (int)p;
+    };
+
+    for (int r0 = sg.x; r0 < sg.y; r0 += 32) {
+        const int r = r0 + lane;
+        int i1 = -1; bool elig = false;
+        uint32_t e[kTopK] = {kNoKey, kNoKey, kNoKey, kNoKey};
+        if (r < sg.y) {
+            i1 = J.idx1[r];
+            elig = queryEligible(J, i1);
+            if (elig) {
+                const uint4 e4 = *reinterpret_cast<const uint4*>(J.topk + (size_t)r * kTopK);
+                e[0] = e4.x; e[1] = e4.y; e[2] = e4.z; e[3] = e4.w;
+            }
+        }
+        int accP = -1;
+        // a row whose best listed distance is already beyond the acceptance threshold can never claim anything
+        // (claims only remove candidates): it needs no turn
+        const bool canAccept = elig && e[0] != kNoKey && (tri || (int)(e[0] >> kPosBits) <= thAccept);
+        uint32_t turns = __ballot_sync(0xffffffffu, canAccept);
+        while (turns) {
+            const int t = __ffs(turns) - 1;
+            turns &= turns - 1;
+            bool need = false;
+            if (lane == t) {
+                uint32_t u0 = kNoKey, u1 = kNoKey;
+                const bool full = e[kTopK - 1] != kNoKey;
+                #pragma unroll
+                for (int j = 0; j < kTopK; ++j) {
+                    if (e[j] == kNoKey) continue;
+                    const uint32_t p = tri ? kPosMask - (e[j] & kPosMask) : (e[j] & kPosMask);
+                    const bool taken = (mask[p >> 5] >> (p & 31)) & 1u;
+                    if (!taken) { if (u0 == kNoKey) u0 = e[j]; else if (u1 == kNoKey) u1 = e[j]; }
+                }
+                // every unlisted row is at least as far as the last listed one: when that is already beyond the acceptance
+                // threshold nothing can be accepted and the rescan is pointless (SearchForTriangulation lists only hold
+                // acceptable candidates, so there it must be done)
+                if (u0 == kNoKey) need = full && (tri || (int)(e[kTopK - 1] >> kPosBits) <= thAccept);
+                else if (!tri && (int)(u0 >> kPosBits) <= thAccept && u1 == kNoKey && full) {
+                    // second-best unknown: every unlisted row is >= the last listed distance
+                    const float lb = (float)(e[kTopK - 1] >> kPosBits);
+                    if (!((float)(u0 >> kPosBits) < __fmul_rn(nnratio, lb))) need = true;
+                    else u1 = e[kTopK - 1]; // accepted whatever the true second is
+                }
+                if (!need) accP = settle(u0, u1);
+            }
+            __syncwarp();
+            if (__shfl_sync(0xffffffffu, (int)need, t)) { // exact rescan of the node for this row under the current claims
+                const int i1t = __shfl_sync(0xffffffffu, i1, t);
+                const uint4 qa = J.desc1[2 * i1t], qb = J.desc1[2 * i1t + 1];
+                Epi epi; if (tri) epi = makeEpi(J, i1t);
+                uint32_t k1 = kNoKey, k2 = kNoKey;
+                for (int p = lane; p < nt; p += 32) {
+                    if ((mask[p >> 5] >> (p & 31)) & 1u) continue;
+                    const int i2 = J.idx2[sg.z + p];
+                    if (!trainEligible(J, i2)) continue;
+                    const int d = dist256(qa, qb, J.desc2[2 * i2], J.desc2[2 * i2 + 1]);
+                    uint32_t key;
+                    if (!tri) key = ((uint32_t)d << kPosBits) | (uint32_t)p;
+                    else {
+                        if (d > kThLow) continue;
+                        const orbx_keypoint kp = J.keys2[i2];
+                        if (!triGeometryOk(J, epi, kp.x, kp.y, kp.octave, J.ur2 && J.ur2[i2] >= 0)) continue;
+                        key = ((uint32_t)d << kPosBits) | (kPosMask - (uint32_t)p);
+                    }
+                    if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
+                }
+                #pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const uint32_t b1 = __shfl_xor_sync(0xffffffffu, k1, o), b2 = __shfl_xor_sync(0xffffffffu, k2, o);
+                    merge2(k1, k2, b1, b2);
+                }
+                __syncwarp();
+                if (lane == t) accP = settle(k1, k2);
+                __syncwarp();
+            }
+        }
+        if (accP >= 0) {                                   // results of the batch, all lanes in parallel
+            const int i2 = J.idx2[sg.z + accP];
             if (J.mode == ORBX_BOW_KF_FRAME) J.match[i2] = i1; else J.match[i1] = i2;
             if (J.checkOri) atomicAdd(&J.hist[rotBin(J.keys1[i1].angle, J.keys2[i2].angle)], 1);
         }
-        __syncwarp();
     }
 }
 
@@ -357,98 +393,137 @@ int launchBowJobs(Ctx* c, const BowJob* dJobs, int njobs, int maxTiles, int maxS
 } // namespace orbx
 using namespace orbx;
 
-extern "C" int orbx_match_bow(orbx_ctx* h, int mode, const orbx_bow_side* s1, const orbx_bow_side* s2,
-                              const orbx_triangulation* tri, float nnratio, int check_ori, int flags,
-                              int32_t* match, int* nmatches)
+// One or many keyframe-pair jobs in ONE set of launches (grid.y = job): the top-K kernels of all pairs fill the GPU while
+// the per-node greedy replays (one warp per node) of different pairs run side by side.
+static int matchBowPairs(Ctx* c, int mode, int npairs, const orbx_bow_side* const* s1v, const orbx_bow_side* const* s2v,
+                         const orbx_triangulation* const* triv, float nnratio, int check_ori, int flags,
+                         int32_t* const* matchv, int* nmatches)
 {
-    if (!h || !s1 || !s2 || !match || mode < 0 || mode > 2 || (mode == ORBX_BOW_TRIANGULATE && !tri)) return ORBX_E_INVALID;
-    if (s1->n < 0 || s2->n < 0 || s1->nnodes < 0 || s2->nnodes < 0) return ORBX_E_INVALID;
-    if ((s1->n > 0 && (!s1->desc || !s1->keys)) || (s2->n > 0 && (!s2->desc || !s2->keys))) return ORBX_E_INVALID;
-    Ctx* c = &h->c;
-    ORBX_CUDA(c, cudaSetDevice(c->device));
     const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
-    const int nOut = mode == ORBX_BOW_KF_FRAME ? s2->n : s1->n;
-    // merge-join of the two FeatureVectors (the while/lower_bound loops, e.g. :285-390)
-    std::vector<int4> segs;
-    std::vector<int32_t> tilePrefix(1, 0);
-    int maxT = 0;
-    for (int a = 0, b = 0; a < s1->nnodes && b < s2->nnodes;) {
-        if (s1->node_id[a] < s2->node_id[b]) ++a;
-        else if (s1->node_id[a] > s2->node_id[b]) ++b;
-        else {
-            const int4 sg = make_int4(s1->node_off[a], s1->node_off[a + 1], s2->node_off[b], s2->node_off[b + 1]);
-            if (sg.y < sg.x || sg.w < sg.z || sg.w - sg.z > (int)kPosMask) return ORBX_E_INVALID;
-            if (sg.y > sg.x && sg.w > sg.z) {
-                segs.push_back(sg);
-                tilePrefix.push_back(tilePrefix.back() + (sg.y - sg.x + kARows - 1) / kARows);
-                maxT = std::max(maxT, sg.w - sg.z);
-            }
-            ++a; ++b;
-        }
-    }
-    const int nseg = (int)segs.size();
-    const int len1 = s1->nnodes ? s1->node_off[s1->nnodes] : 0, len2 = s2->nnodes ? s2->node_off[s2->nnodes] : 0;
-
+    struct Plan {
+        std::vector<int4> segs; std::vector<int32_t> tilePrefix;
+        int nseg = 0, len1 = 0, len2 = 0, nOut = 0, maxT = 0;
+        size_t oSeg = 0, oTp = 0, oTop = 0, oHist = 0, oIdx1 = 0, oIdx2 = 0, oD1 = 0, oD2 = 0, oK1 = 0, oK2 = 0, oF1 = 0, oF2 = 0, oU1 = 0, oU2 = 0, oMatch = 0;
+    };
+    std::vector<Plan> plans((size_t)npairs);
     Bump B;
-    const size_t oJob = B.take(sizeof(BowJob)), oSeg = B.take(sizeof(int4) * (size_t)std::max(nseg, 1)),
-                 oTp = B.take(sizeof(int32_t) * (size_t)(nseg + 1)), oTop = B.take(sizeof(uint32_t) * kTopK * (size_t)std::max(len1, 1)),
-                 oHist = B.take(sizeof(int) * (kHisto + 1)), oIdx1 = B.take(sizeof(int32_t) * (size_t)std::max(len1, 1)),
-                 oIdx2 = B.take(sizeof(int32_t) * (size_t)std::max(len2, 1));
-    size_t oD1 = 0, oD2 = 0, oK1 = 0, oK2 = 0, oF1 = 0, oF2 = 0, oU1 = 0, oU2 = 0, oMatch = 0;
-    if (!inDev) {
-        oD1 = B.take((size_t)32 * std::max(s1->n, 1)); oD2 = B.take((size_t)32 * std::max(s2->n, 1));
-        oK1 = B.take(sizeof(orbx_keypoint) * (size_t)std::max(s1->n, 1)); oK2 = B.take(sizeof(orbx_keypoint) * (size_t)std::max(s2->n, 1));
-        oF1 = B.take((size_t)std::max(s1->n, 1)); oF2 = B.take((size_t)std::max(s2->n, 1));
-        oU1 = B.take(sizeof(float) * (size_t)std::max(s1->n, 1)); oU2 = B.take(sizeof(float) * (size_t)std::max(s2->n, 1));
+    const size_t oJobs = B.take(sizeof(BowJob) * (size_t)npairs);
+    int maxTiles = 0, maxSeg = 0, maxN2 = 0;
+    for (int j = 0; j < npairs; ++j) {
+        const orbx_bow_side *s1 = s1v[j], *s2 = s2v[j];
+        if (!s1 || !s2 || !matchv[j] || (mode == ORBX_BOW_TRIANGULATE && !(triv && triv[j]))) return ORBX_E_INVALID;
+        if (s1->n < 0 || s2->n < 0 || s1->nnodes < 0 || s2->nnodes < 0) return ORBX_E_INVALID;
+        if ((s1->n > 0 && (!s1->desc || !s1->keys)) || (s2->n > 0 && (!s2->desc || !s2->keys))) return ORBX_E_INVALID;
+        Plan& P = plans[j];
+        P.nOut = mode == ORBX_BOW_KF_FRAME ? s2->n : s1->n;
+        P.tilePrefix.assign(1, 0);
+        // merge-join of the two FeatureVectors (the while/lower_bound loops, e.g. :285-390)
+        for (int a = 0, b = 0; a < s1->nnodes && b < s2->nnodes;) {
+            if (s1->node_id[a] < s2->node_id[b]) ++a;
+            else if (s1->node_id[a] > s2->node_id[b]) ++b;
+            else {
+                const int4 sg = make_int4(s1->node_off[a], s1->node_off[a + 1], s2->node_off[b], s2->node_off[b + 1]);
+                if (sg.y < sg.x || sg.w < sg.z || sg.w - sg.z > (int)kPosMask) return ORBX_E_INVALID;
+                if (sg.y > sg.x && sg.w > sg.z) {
+                    P.segs.push_back(sg);
+                    P.tilePrefix.push_back(P.tilePrefix.back() + (sg.y - sg.x + kARows - 1) / kARows);
+                    P.maxT = std::max(P.maxT, sg.w - sg.z);
+                }
+                ++a; ++b;
+            }
+        }
+        P.nseg = (int)P.segs.size();
+        P.len1 = s1->nnodes ? s1->node_off[s1->nnodes] : 0; P.len2 = s2->nnodes ? s2->node_off[s2->nnodes] : 0;
+        P.oSeg = B.take(sizeof(int4) * (size_t)std::max(P.nseg, 1)); P.oTp = B.take(sizeof(int32_t) * (size_t)(P.nseg + 1));
+        P.oTop = B.take(sizeof(uint32_t) * kTopK * (size_t)std::max(P.len1, 1)); P.oHist = B.take(sizeof(int) * (kHisto + 1));
+        P.oIdx1 = B.take(sizeof(int32_t) * (size_t)std::max(P.len1, 1)); P.oIdx2 = B.take(sizeof(int32_t) * (size_t)std::max(P.len2, 1));
+        if (!inDev) {
+            P.oD1 = B.take((size_t)32 * std::max(s1->n, 1)); P.oD2 = B.take((size_t)32 * std::max(s2->n, 1));
+            P.oK1 = B.take(sizeof(orbx_keypoint) * (size_t)std::max(s1->n, 1)); P.oK2 = B.take(sizeof(orbx_keypoint) * (size_t)std::max(s2->n, 1));
+            P.oF1 = B.take((size_t)std::max(s1->n, 1)); P.oF2 = B.take((size_t)std::max(s2->n, 1));
+            P.oU1 = B.take(sizeof(float) * (size_t)std::max(s1->n, 1)); P.oU2 = B.take(sizeof(float) * (size_t)std::max(s2->n, 1));
+        }
+        if (!outDev) P.oMatch = B.take(sizeof(int32_t) * (size_t)std::max(P.nOut, 1));
+        maxTiles = std::max(maxTiles, P.tilePrefix.back()); maxSeg = std::max(maxSeg, P.nseg); maxN2 = std::max(maxN2, P.maxT);
     }
-    if (!outDev) oMatch = B.take(sizeof(int32_t) * (size_t)std::max(nOut, 1));
     int rc = ensureScratch(c, B.off);
     if (rc) return rc;
     uint8_t* S = (uint8_t*)c->dScratch;
     auto h2d = [&](size_t off, const void* src, size_t bytes) -> cudaError_t {
         return bytes ? cudaMemcpyAsync(S + off, src, bytes, cudaMemcpyHostToDevice, c->stream) : cudaSuccess;
     };
-    BowJob J;
-    memset(&J, 0, sizeof(J));
+    std::vector<BowJob> jobs((size_t)npairs);
     stageBegin(c, ST_H2D);
-    if (!inDev) {
-        ORBX_CUDA(c, h2d(oD1, s1->desc, (size_t)32 * s1->n)); ORBX_CUDA(c, h2d(oD2, s2->desc, (size_t)32 * s2->n));
-        ORBX_CUDA(c, h2d(oK1, s1->keys, sizeof(orbx_keypoint) * (size_t)s1->n)); ORBX_CUDA(c, h2d(oK2, s2->keys, sizeof(orbx_keypoint) * (size_t)s2->n));
-        J.desc1 = (const uint4*)(S + oD1); J.desc2 = (const uint4*)(S + oD2);
-        J.keys1 = (const orbx_keypoint*)(S + oK1); J.keys2 = (const orbx_keypoint*)(S + oK2);
-        if (s1->has_point) { ORBX_CUDA(c, h2d(oF1, s1->has_point, (size_t)s1->n)); J.flag1 = S + oF1; }
-        if (s2->has_point) { ORBX_CUDA(c, h2d(oF2, s2->has_point, (size_t)s2->n)); J.flag2 = S + oF2; }
-        if (s1->uright) { ORBX_CUDA(c, h2d(oU1, s1->uright, sizeof(float) * (size_t)s1->n)); J.ur1 = (const float*)(S + oU1); }
-        if (s2->uright) { ORBX_CUDA(c, h2d(oU2, s2->uright, sizeof(float) * (size_t)s2->n)); J.ur2 = (const float*)(S + oU2); }
-    } else {
-        J.desc1 = (const uint4*)s1->desc; J.desc2 = (const uint4*)s2->desc; J.keys1 = s1->keys; J.keys2 = s2->keys;
-        J.flag1 = s1->has_point; J.flag2 = s2->has_point; J.ur1 = s1->uright; J.ur2 = s2->uright;
+    for (int j = 0; j < npairs; ++j) {
+        const orbx_bow_side *s1 = s1v[j], *s2 = s2v[j];
+        const Plan& P = plans[j];
+        BowJob& J = jobs[j];
+        memset(&J, 0, sizeof(J));
+        if (!inDev) {
+            ORBX_CUDA(c, h2d(P.oD1, s1->desc, (size_t)32 * s1->n)); ORBX_CUDA(c, h2d(P.oD2, s2->desc, (size_t)32 * s2->n));
+            ORBX_CUDA(c, h2d(P.oK1, s1->keys, sizeof(orbx_keypoint) * (size_t)s1->n)); ORBX_CUDA(c, h2d(P.oK2, s2->keys, sizeof(orbx_keypoint) * (size_t)s2->n));
+            J.desc1 = (const uint4*)(S + P.oD1); J.desc2 = (const uint4*)(S + P.oD2);
+            J.keys1 = (const orbx_keypoint*)(S + P.oK1); J.keys2 = (const orbx_keypoint*)(S + P.oK2);
+            if (s1->has_point) { ORBX_CUDA(c, h2d(P.oF1, s1->has_point, (size_t)s1->n)); J.flag1 = S + P.oF1; }
+            if (s2->has_point) { ORBX_CUDA(c, h2d(P.oF2, s2->has_point, (size_t)s2->n)); J.flag2 = S + P.oF2; }
+            if (s1->uright) { ORBX_CUDA(c, h2d(P.oU1, s1->uright, sizeof(float) * (size_t)s1->n)); J.ur1 = (const float*)(S + P.oU1); }
+            if (s2->uright) { ORBX_CUDA(c, h2d(P.oU2, s2->uright, sizeof(float) * (size_t)s2->n)); J.ur2 = (const float*)(S + P.oU2); }
+        } else {
+            J.desc1 = (const uint4*)s1->desc; J.desc2 = (const uint4*)s2->desc; J.keys1 = s1->keys; J.keys2 = s2->keys;
+            J.flag1 = s1->has_point; J.flag2 = s2->has_point; J.ur1 = s1->uright; J.ur2 = s2->uright;
+        }
+        ORBX_CUDA(c, h2d(P.oIdx1, s1->feat, sizeof(int32_t) * (size_t)P.len1));
+        ORBX_CUDA(c, h2d(P.oIdx2, s2->feat, sizeof(int32_t) * (size_t)P.len2));
+        ORBX_CUDA(c, h2d(P.oSeg, P.segs.data(), sizeof(int4) * (size_t)P.nseg));
+        ORBX_CUDA(c, h2d(P.oTp, P.tilePrefix.data(), sizeof(int32_t) * (size_t)(P.nseg + 1)));
+        J.idx1 = (const int32_t*)(S + P.oIdx1); J.idx2 = (const int32_t*)(S + P.oIdx2);
+        J.seg = (const int4*)(S + P.oSeg); J.tilePrefix = (const int32_t*)(S + P.oTp);
+        J.topk = (uint32_t*)(S + P.oTop); J.hist = (int*)(S + P.oHist);
+        J.match = outDev ? matchv[j] : (int32_t*)(S + P.oMatch);
+        J.nseg = P.nseg; J.n1 = s1->n; J.n2 = s2->n; J.mode = mode; J.checkOri = check_ori ? 1 : 0; J.nnratio = nnratio;
+        if (mode == ORBX_BOW_TRIANGULATE) {
+            const orbx_triangulation* tri = triv[j];
+            memcpy(J.F, tri->F12, sizeof(J.F)); J.ex = tri->ex; J.ey = tri->ey; J.onlyStereo = tri->only_stereo;
+            memcpy(J.scale2, tri->scale2, sizeof(J.scale2)); memcpy(J.sigma2, tri->sigma2_2, sizeof(J.sigma2));
+        }
+        ORBX_CUDA(c, cudaMemsetAsync(J.hist, 0, sizeof(int) * (kHisto + 1), c->stream));
+        if (P.nOut > 0) ORBX_CUDA(c, cudaMemsetAsync(J.match, 0xff, sizeof(int32_t) * (size_t)P.nOut, c->stream));
     }
-    ORBX_CUDA(c, h2d(oIdx1, s1->feat, sizeof(int32_t) * (size_t)len1));
-    ORBX_CUDA(c, h2d(oIdx2, s2->feat, sizeof(int32_t) * (size_t)len2));
-    ORBX_CUDA(c, h2d(oSeg, segs.data(), sizeof(int4) * (size_t)nseg));
-    ORBX_CUDA(c, h2d(oTp, tilePrefix.data(), sizeof(int32_t) * (size_t)(nseg + 1)));
-    J.idx1 = (const int32_t*)(S + oIdx1); J.idx2 = (const int32_t*)(S + oIdx2);
-    J.seg = (const int4*)(S + oSeg); J.tilePrefix = (const int32_t*)(S + oTp);
-    J.topk = (uint32_t*)(S + oTop); J.hist = (int*)(S + oHist);
-    J.match = outDev ? match : (int32_t*)(S + oMatch);
-    J.nseg = nseg; J.n1 = s1->n; J.n2 = s2->n; J.mode = mode; J.checkOri = check_ori ? 1 : 0; J.nnratio = nnratio;
-    if (tri) {
-        memcpy(J.F, tri->F12, sizeof(J.F)); J.ex = tri->ex; J.ey = tri->ey; J.onlyStereo = tri->only_stereo;
-        memcpy(J.scale2, tri->scale2, sizeof(J.scale2)); memcpy(J.sigma2, tri->sigma2_2, sizeof(J.sigma2));
-    }
-    ORBX_CUDA(c, h2d(oJob, &J, sizeof(J)));
-    ORBX_CUDA(c, cudaMemsetAsync(J.hist, 0, sizeof(int) * (kHisto + 1), c->stream));
-    if (nOut > 0) ORBX_CUDA(c, cudaMemsetAsync(J.match, 0xff, sizeof(int32_t) * (size_t)nOut, c->stream));
+    ORBX_CUDA(c, h2d(oJobs, jobs.data(), sizeof(BowJob) * (size_t)npairs));
     stageEnd(c, ST_H2D, 0);
-    rc = launchBowJobs(c, (const BowJob*)(S + oJob), 1, tilePrefix.back(), nseg, maxT);
+    rc = launchBowJobs(c, (const BowJob*)(S + oJobs), npairs, maxTiles, maxSeg, maxN2);
     if (rc) return rc;
-    int nm = 0;
+    std::vector<int> nm((size_t)npairs, 0);
     stageBegin(c, ST_D2H);
-    if (!outDev && nOut > 0) ORBX_CUDA(c, cudaMemcpyAsync(match, J.match, sizeof(int32_t) * (size_t)nOut, cudaMemcpyDeviceToHost, c->stream));
-    ORBX_CUDA(c, cudaMemcpyAsync(&nm, J.hist + kHisto, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    for (int j = 0; j < npairs; ++j) {
+        if (!outDev && plans[j].nOut > 0)
+            ORBX_CUDA(c, cudaMemcpyAsync(matchv[j], jobs[j].match, sizeof(int32_t) * (size_t)plans[j].nOut, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaMemcpyAsync(&nm[j], jobs[j].hist + kHisto, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    }
     stageEnd(c, ST_D2H, 0);
     ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
-    if (nmatches) *nmatches = nm;
+    if (nmatches) for (int j = 0; j < npairs; ++j) nmatches[j] = nm[j];
     return ORBX_OK;
+}
+
+extern "C" int orbx_match_bow(orbx_ctx* h, int mode, const orbx_bow_side* s1, const orbx_bow_side* s2,
+                              const orbx_triangulation* tri, float nnratio, int check_ori, int flags,
+                              int32_t* match, int* nmatches)
+{
+    if (!h || !s1 || !s2 || !match || mode < 0 || mode > 2 || (mode == ORBX_BOW_TRIANGULATE && !tri)) return ORBX_E_INVALID;
+    Ctx* c = &h->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    return matchBowPairs(c, mode, 1, &s1, &s2, &tri, nnratio, check_ori, flags, &match, nmatches);
+}
+
+extern "C" int orbx_match_bow_batch(orbx_ctx* h, int mode, int npairs, const orbx_bow_side* const* s1, const orbx_bow_side* const* s2,
+                                    const orbx_triangulation* const* tri, float nnratio, int check_ori, int flags,
+                                    int32_t* const* match, int* nmatches)
+{
+    if (!h || npairs < 0 || mode < 0 || mode > 2 || (npairs > 0 && (!s1 || !s2 || !match))) return ORBX_E_INVALID;
+    if (npairs == 0) return ORBX_OK;
+    if (npairs > 65535) return ORBX_E_CAPACITY;   // grid.y
+    Ctx* c = &h->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    return matchBowPairs(c, mode, npairs, s1, s2, tri, nnratio, check_ori, flags, match, nmatches);
 }

@@ -55,6 +55,7 @@ def _mlib():
     L.orbx_feature_vector.argtypes = [vp, vp, ci, vp, vp, vp, ip]
     L.orbx_match_bow.argtypes = [vp, ci, ctypes.POINTER(_BowSide), ctypes.POINTER(_BowSide), ctypes.POINTER(_Triangulation), cf, ci,
                                  ci, vp, ip]
+    L.orbx_match_bow_batch.argtypes = [vp, ci, ci, ctypes.POINTER(ctypes.POINTER(_BowSide)), ctypes.POINTER(ctypes.POINTER(_BowSide)), vp, cf, ci, ci, vp, vp]
     L.orbx_assign_grid.argtypes = [vp, vp, ci, ctypes.POINTER(_Grid), ci, vp, vp]
     L.orbx_search_by_projection.argtypes = [vp, vp, ci, vp, vp, vp, ci, ctypes.POINTER(_Grid), vp, ci, ci, cf, ci, ci, vp, ip]
     L.orbx_stereo_match.argtypes = [vp, vp, ci, vp, vp, ci, vp, vp, ci, cf, cf, ci, vp, vp, ip]
@@ -155,6 +156,26 @@ class ORBmatcher:
                                     self.mfNNratio, int(self.mbCheckOrientation), 0, _np(out), ctypes.byref(n))
         _chk(self._ex, rc, "orbx_match_bow")
         return out, n.value
+
+    def SearchByBoWBatch(self, pairs, other_is_keyframe=False):
+        """Many independent (KeyFrame, Frame/KeyFrame) pairs in one call (orbx_match_bow_batch): the keyframe-pair jobs of
+        LocalMapping / LoopClosing.  pairs: list of (FrameView, FrameView).  Returns a list of (matches, n) identical to
+        calling SearchByBoW on each pair."""
+        mode = BOW_KF_KF if other_is_keyframe else BOW_KF_FRAME
+        n = len(pairs)
+        if n == 0:
+            return []
+        a = [p[0]._c() for p in pairs]
+        b = [p[1]._c() for p in pairs]
+        PS = ctypes.POINTER(_BowSide)
+        pa = (PS * n)(*[ctypes.pointer(x) for x in a])
+        pb = (PS * n)(*[ctypes.pointer(x) for x in b])
+        outs = [np.empty(p[1].N if mode == BOW_KF_FRAME else p[0].N, np.int32) for p in pairs]
+        pm = (ctypes.c_void_p * n)(*[o.ctypes.data for o in outs])
+        nm = (ctypes.c_int * n)()
+        rc = _mlib().orbx_match_bow_batch(self._ex._h, mode, n, pa, pb, None, self.mfNNratio, int(self.mbCheckOrientation), 0, pm, nm)
+        _chk(self._ex, rc, "orbx_match_bow_batch")
+        return [(outs[i], int(nm[i])) for i in range(n)]
 
     def SearchByBoW(self, kf, other, other_is_keyframe=False):
         """SearchByBoW(KeyFrame*, Frame&, ..) src/ORBmatcher.cc:255 -> (vpMapPointMatches as KF feature index per F feature, n);

@@ -207,3 +207,21 @@ def test_stereo_matches_oracle(P, w, h, nf, seed):
     assert np.array_equal(want_u.view(np.uint32), got_u.view(np.uint32)), int((want_u != got_u).sum())
     assert np.array_equal(want_z.view(np.uint32), got_z.view(np.uint32))
     assert (got_u >= 0).sum() > 100, (int((got_u >= 0).sum()), nv)
+
+
+def test_search_by_bow_batch_equals_single_calls(P, ctx, vocs):
+    """orbx_match_bow_batch: several keyframe pairs of different sizes / modes in one set of launches."""
+    _, vo, vg = vocs
+    cases = [(21, 900, 800, 0.08, 0.0, 1), (22, 1500, 1700, 0.1, 0.5, 2), (23, 30, 25, 0.05, 0.0, 2), (24, 2000, 2000, 0.1, 0.0, 4),
+             (25, 600, 1200, 0.12, 0.8, 3)]
+    for kf_kf in (False, True):
+        pairs_g, want = [], []
+        for seed, n1, n2, flip, dup, levelsup in cases:
+            d1, k1, d2, k2 = make_pair(seed, n1, n2, flip, dup, KP=P.KP_DTYPE)
+            so, sg = sides(P, vo, vg, d1, k1, d2, k2, levelsup, seed)
+            pairs_g.append((sg[0], sg[1]))
+            want.append(O.search_by_bow(so[0], so[1], 0.75, True, kf_kf))
+        got = P.ORBmatcher(ctx, 0.75, True).SearchByBoWBatch(pairs_g, kf_kf)
+        assert len(got) == len(want)
+        for (wm, wn), (gm, gn) in zip(want, got):
+            assert np.array_equal(wm, gm) and wn == gn
