@@ -4,15 +4,19 @@
 //   ORBmatcher::SearchByProjection x4 inner loops  src/ORBmatcher.cc:78-191, 431-560, 1741-1910, 1922-2065
 //
 // The reference handles projected points one after another and lets every accepted match hide its keypoint
-// from the following points.  On the GPU the parallel part (window enumeration in the reference's cell order,
-// Hamming distances) runs first; one warp then replays the greedy decisions over the precomputed candidate
-// lists, so results are identical whatever the order of distances.
-//   P1 projCountKernel   thread per query: number of window candidates
-//   P2 (scan)            exclusive prefix over queries (single CTA)
-//   P3 projFillKernel    thread per query: candidate indices in visit order (ix outer, iy inner, cell order)
-//   P4 projDistKernel    thread per candidate: uright gate + 256-bit distance
-//   P5 projResolveKernel one warp: greedy best / second-best, thresholds, claims, rotation votes
-//   P6 projRotationKernel ComputeThreeMaxima + removal (only with check_orientation)
+// from the following points.  GetFeaturesInArea visits cells with ix outer / iy inner, i.e. in ascending cell id
+// c = ix * rows + iy, and each cell's list in ascending feature index -- which is exactly the order of the grid's
+// flat index array.  So the position j of a feature in that array is its visit rank for EVERY query, a query's
+// candidates are one contiguous j-range per window column, and "first visited wins a tie" is "smaller j wins".
+//   P1 gridBuildKernel    one CTA: cell of every keypoint, counts, prefix, stable fill; for the matcher also the
+//                         keypoints / descriptors gathered into cell order (so P2 reads them with unit stride)
+//   P2 projScanKernel     thread per query: window columns -> j-ranges -> filters + 256-bit distance; keeps the four
+//                         smallest keys (dist << 22 | j) and the number of candidates; nothing else is materialised
+//   P3 projResolveKernel  one CTA.  Warp 0 replays the greedy order 32 queries at a time: every lane decides for
+//                         its query from its four keys and the claim bitmask, lanes whose lists do not contain an
+//                         earlier lane's claim commit together, an exact warp-wide rescan runs only when the four keys
+//                         cannot decide.  All warps then write assign[], vote the rotation histogram and apply
+//                         ComputeThreeMaxima (check_orientation).
 #include "orbx_internal.h"
 #include <string.h>
 #include <algorithm>
@@ -20,40 +24,50 @@
 namespace orbx {
 
 constexpr int kHistoP = 30;
+constexpr int kJBits = 22;                       // position bits of a key: n < 2^22
+constexpr uint32_t kJMask = (1u << kJBits) - 1;
+constexpr uint32_t kNoKeyP = 0xffffffffu;
+constexpr int kGridThreads = 1024;
+constexpr int kResolveThreads = 256;
 
 struct GridDev { float minX, minY, invW, invH; int cols, rows; };
 
 // ---------------- grid ----------------
-__global__ void gridCellKernel(const orbx_keypoint* __restrict__ keys, int n, GridDev g, int* __restrict__ cell)
-{
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const int px = (int)roundf(__fmul_rn(__fsub_rn(keys[i].x, g.minX), g.invW));
-    const int py = (int)roundf(__fmul_rn(__fsub_rn(keys[i].y, g.minY), g.invH));
-    cell[i] = (px < 0 || px >= g.cols || py < 0 || py >= g.rows) ? -1 : px * g.rows + py;
+__device__ __forceinline__ int cellOfKey(float x, float y, const GridDev& g)
+{   // Frame::PosInGrid, src/Frame.cc:682-698
+    const int px = (int)roundf(__fmul_rn(__fsub_rn(x, g.minX), g.invW));
+    const int py = (int)roundf(__fmul_rn(__fsub_rn(y, g.minY), g.invH));
+    return (px < 0 || px >= g.cols || py < 0 || py >= g.rows) ? -1 : px * g.rows + py;
 }
 
-// one thread per cell: stable gather (ascending feature index = push_back order)
-__global__ void gridCountKernel(const int* __restrict__ cell, int n, int ncell, int* __restrict__ cnt)
+// cinfo[j] = (x, y, uright or -1, octave | occupied << 8) of the feature at position j of the flat grid array.
+__global__ void __launch_bounds__(kGridThreads)
+gridBuildKernel(const orbx_keypoint* __restrict__ keys, int n, GridDev g, int* __restrict__ cellTmp, int* __restrict__ tmpIdx,
+                int* __restrict__ off, int* __restrict__ idx, const uint4* __restrict__ desc, const float* __restrict__ uright,
+                const uint8_t* __restrict__ occupied, float4* __restrict__ cinfo, uint4* __restrict__ dsort,
+                int* __restrict__ assign, int nAssign)
 {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncell) return;
-    int k = 0;
-    for (int i = 0; i < n; ++i) k += cell[i] == c;
-    cnt[c] = k;
-}
-
-__global__ void __launch_bounds__(1024) exclusiveScanKernel(const int* __restrict__ in, int n, int* __restrict__ out)
-{   // out[0..n] (n+1 entries); single CTA, chunked
+    extern __shared__ int sGrid[];
     __shared__ int warpSum[32];
     __shared__ int carry;
-    if (threadIdx.x == 0) carry = 0;
+    const int ncell = g.cols * g.rows;
+    int* cnt = sGrid;                 // [ncell]    counts, later the fill cursors
+    int* start = sGrid + ncell;       // [ncell+1]  exclusive prefix
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    for (int c = tid; c < ncell; c += kGridThreads) cnt[c] = 0;
+    if (tid == 0) carry = 0;
     __syncthreads();
-    for (int base = 0; base < n; base += 1024) {
-        const int i = base + threadIdx.x;
-        const int v = i < n ? in[i] : 0;
+    for (int i = tid; i < n; i += kGridThreads) {
+        const int cell = cellOfKey(keys[i].x, keys[i].y, g);
+        cellTmp[i] = cell;
+        if (cell >= 0) atomicAdd(&cnt[cell], 1);
+    }
+    if (assign) for (int i = tid; i < nAssign; i += kGridThreads) assign[i] = -1;
+    __syncthreads();
+    for (int base = 0; base < ncell; base += kGridThreads) {
+        const int i = base + tid;
+        const int v = i < ncell ? cnt[i] : 0;
         int x = v;
-        const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
         #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += t; }
         if (lane == 31) warpSum[w] = x;
@@ -66,20 +80,35 @@ __global__ void __launch_bounds__(1024) exclusiveScanKernel(const int* __restric
         }
         __syncthreads();
         const int excl = carry + (w ? warpSum[w - 1] : 0) + x - v;
-        if (i < n) out[i] = excl;
+        if (i < ncell) start[i] = excl;
         __syncthreads();
-        if (threadIdx.x == 1023) carry = excl + v;
+        if (tid == kGridThreads - 1) carry = excl + v;
         __syncthreads();
     }
-    if (threadIdx.x == 0) out[n] = carry;
-}
-
-__global__ void gridFillKernel(const int* __restrict__ cell, int n, int ncell, const int* __restrict__ off, int* __restrict__ idx)
-{
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncell) return;
-    int o = off[c];
-    for (int i = 0; i < n; ++i) if (cell[i] == c) idx[o++] = i;
+    if (tid == 0) start[ncell] = carry;
+    __syncthreads();
+    for (int c = tid; c <= ncell; c += kGridThreads) { off[c] = start[c]; if (c < ncell) cnt[c] = start[c]; }
+    __syncthreads();
+    for (int i = tid; i < n; i += kGridThreads) {     // unordered fill ...
+        const int cell = cellTmp[i];
+        if (cell >= 0) tmpIdx[atomicAdd(&cnt[cell], 1)] = i;
+    }
+    __syncthreads();
+    const int placed = start[ncell];
+    for (int p = tid; p < placed; p += kGridThreads) { // ... then every entry finds its rank inside its cell (push_back order)
+        const int i = tmpIdx[p], cell = cellTmp[i];
+        const int b = start[cell], e = start[cell + 1];
+        int rank = 0;
+        for (int k = b; k < e; ++k) rank += tmpIdx[k] < i;
+        const int j = b + rank;
+        idx[j] = i;
+        if (cinfo) {
+            const orbx_keypoint kp = keys[i];
+            const int fl = (kp.octave & 0xff) | ((occupied && occupied[i]) ? 0x100 : 0);
+            cinfo[j] = make_float4(kp.x, kp.y, uright ? uright[i] : -1.0f, __int_as_float(fl));
+            dsort[2 * j] = desc[2 * i]; dsort[2 * j + 1] = desc[2 * i + 1];
+        }
+    }
 }
 
 // ---------------- window enumeration ----------------
@@ -99,57 +128,102 @@ __device__ __forceinline__ Window windowOf(const GridDev& g, float x, float y, f
     return w;
 }
 
-template <bool FILL>
-__global__ void projEnumKernel(const orbx_proj_query* __restrict__ q, int nq, const orbx_keypoint* __restrict__ keys, GridDev g,
-                               const int* __restrict__ cellOff, const int* __restrict__ cellIdx, int* __restrict__ count,
-                               const int* __restrict__ off, int* __restrict__ cand)
+struct QueryGeom { float x, y, r, ur; int minL, maxL; bool checkLevel; };
+__device__ __forceinline__ QueryGeom geomOf(const orbx_proj_query& q)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nq) return;
-    const float x = q[i].u, y = q[i].v, r = q[i].radius;
-    const int minL = q[i].min_level, maxL = q[i].max_level;
-    const Window w = windowOf(g, x, y, r);
-    int k = 0;
-    int o = FILL ? off[i] : 0;
-    if (!w.empty) {
-        const bool check = (minL > 0) || (maxL >= 0);
-        for (int ix = w.c0; ix <= w.c1; ++ix)
-            for (int iy = w.r0; iy <= w.r1; ++iy) {
-                const int c = ix * g.rows + iy;
-                for (int j = cellOff[c]; j < cellOff[c + 1]; ++j) {
-                    const int f = cellIdx[j];
-                    const orbx_keypoint kp = keys[f];
-                    if (check) {
-                        if (kp.octave < minL) continue;
-                        if (maxL >= 0 && kp.octave > maxL) continue;
-                    }
-                    const float dx = __fsub_rn(kp.x, x), dy = __fsub_rn(kp.y, y);
-                    if (fabsf(dx) < r && fabsf(dy) < r) { if (FILL) cand[o + k] = f; ++k; }
-                }
-            }
-    }
-    if (!FILL) count[i] = k;
+    QueryGeom s;
+    s.x = q.u; s.y = q.v; s.r = q.radius; s.ur = q.ur; s.minL = q.min_level; s.maxL = q.max_level;
+    s.checkLevel = (s.minL > 0) || (s.maxL >= 0);
+    return s;
 }
 
-// candidate record: distance (9 bits) | octave << 9 | skip << 15 ; feature index kept in cand[]
-__global__ void projDistKernel(const orbx_proj_query* __restrict__ q, int nq, const int* __restrict__ off, const int* __restrict__ cand,
-                               const orbx_keypoint* __restrict__ keys, const uint4* __restrict__ desc, const float* __restrict__ uright,
-                               int checkUr, int* __restrict__ rec)
+// GetFeaturesInArea's level / distance filter (src/Frame.cc:640-665), the caller's "already matched" skip and the
+// uright gate (src/ORBmatcher.cc:141-151, :1846-1852).  Pure filters: their order does not matter.
+__device__ __forceinline__ bool candPass(const float4& ci, const QueryGeom& s, int checkUr, int& octave)
 {
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= off[nq]) return;
-    int lo = 0, hi = nq; // query of this entry
-    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (off[mid] <= e) lo = mid; else hi = mid; }
-    const int f = cand[e];
-    int skip = 0;
-    if (checkUr && uright && uright[f] > 0) {
-        const float er = fabsf(__fsub_rn(q[lo].ur, uright[f]));
-        if (er > q[lo].radius) skip = 1;
+    const int fl = __float_as_int(ci.w);
+    octave = fl & 0xff;
+    if (fl & 0x100) return false;
+    if (s.checkLevel) {
+        if (octave < s.minL) return false;
+        if (s.maxL >= 0 && octave > s.maxL) return false;
     }
-    const uint4* qd = reinterpret_cast<const uint4*>(q[lo].desc);
-    const uint4 a0 = qd[0], a1 = qd[1], b0 = desc[2 * f], b1 = desc[2 * f + 1];
-    const int d = hamming256(a0, a1, b0, b1);
-    rec[e] = d | ((keys[f].octave & 63) << 9) | (skip << 15);
+    const float dx = __fsub_rn(ci.x, s.x), dy = __fsub_rn(ci.y, s.y);
+    if (!(fabsf(dx) < s.r && fabsf(dy) < s.r)) return false;
+    if (checkUr && ci.z > 0) {
+        const float er = fabsf(__fsub_rn(s.ur, ci.z));
+        if (er > s.r) return false;
+    }
+    return true;
+}
+
+// P2: four smallest keys of every query, the octaves that go with them, and the number of candidates.
+// One warp per query: the window's columns (one contiguous j-range each) are flattened over the lanes.
+constexpr int kScanWarps = 4;
+__global__ void __launch_bounds__(32 * kScanWarps)
+projScanKernel(const orbx_proj_query* __restrict__ q, int nq, GridDev g, const int* __restrict__ off,
+               const float4* __restrict__ cinfo, const uint4* __restrict__ dsort, int checkUr, uint4* __restrict__ topKey,
+               int2* __restrict__ meta)
+{
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * kScanWarps + (threadIdx.x >> 5);
+    if (i >= nq) return;
+    const QueryGeom s = geomOf(q[i]);
+    const Window w = windowOf(g, s.x, s.y, s.r);
+    uint32_t e0 = kNoKeyP, e1 = kNoKeyP, e2 = kNoKeyP, e3 = kNoKeyP;
+    int cnt = 0;
+    if (!w.empty) {
+        const uint4* qd = reinterpret_cast<const uint4*>(q[i].desc);
+        const uint4 a0 = qd[0], a1 = qd[1];
+        const int ncol = w.c1 - w.c0 + 1;
+        for (int cb = 0; cb < ncol; cb += 32) {
+            int jb = 0, len = 0;
+            if (cb + lane < ncol) {
+                const int c = (w.c0 + cb + lane) * g.rows;
+                jb = off[c + w.r0]; len = off[c + w.r1 + 1] - jb;
+            }
+            int incl = len;
+            #pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+            const int excl = incl - len;
+            const int T = __shfl_sync(0xffffffffu, incl, 31);
+            for (int tb = 0; tb < T; tb += 32) {
+                const int t = tb + lane;
+                int k = 0;                      // column of entry t: the last one whose first entry is <= t
+                #pragma unroll
+                for (int b = 16; b > 0; b >>= 1) { const int ex = __shfl_sync(0xffffffffu, excl, k + b); if (ex <= t) k += b; }
+                const int jbk = __shfl_sync(0xffffffffu, jb, k), exk = __shfl_sync(0xffffffffu, excl, k);
+                if (t >= T) continue;
+                const int j = jbk + (t - exk);
+                int oct;
+                if (!candPass(cinfo[j], s, checkUr, oct)) continue;
+                const uint32_t key = ((uint32_t)hamming256(a0, a1, dsort[2 * j], dsort[2 * j + 1]) << kJBits) | (uint32_t)j;
+                ++cnt;
+                if (key < e3) {
+                    e3 = key;
+                    if (e3 < e2) { const uint32_t u = e2; e2 = e3; e3 = u; }
+                    if (e2 < e1) { const uint32_t u = e1; e1 = e2; e2 = u; }
+                    if (e1 < e0) { const uint32_t u = e0; e0 = e1; e1 = u; }
+                }
+            }
+        }
+    }
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    uint32_t mine = kNoKeyP;                    // lane k < 4 ends up with the k-th smallest key of the warp
+    #pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t m = __reduce_min_sync(0xffffffffu, e0);
+        if (lane == k) mine = m;
+        if (e0 == m && m != kNoKeyP) { e0 = e1; e1 = e2; e2 = e3; e3 = kNoKeyP; }   // keys are unique: one owner pops
+    }
+    int lev = 0;
+    if (lane < 4 && mine != kNoKeyP) lev = (__float_as_int(cinfo[mine & kJMask].w) & 0xff) << (8 * lane);
+    lev = __reduce_or_sync(0xffffffffu, lev);
+    const uint32_t k1 = __shfl_sync(0xffffffffu, mine, 1), k2 = __shfl_sync(0xffffffffu, mine, 2), k3 = __shfl_sync(0xffffffffu, mine, 3);
+    if (lane == 0) {
+        topKey[i] = make_uint4(mine, k1, k2, k3);
+        meta[i] = make_int2(cnt, lev);
+    }
 }
 
 __device__ __forceinline__ int rotBinP(float a1, float a2)
@@ -161,105 +235,200 @@ __device__ __forceinline__ int rotBinP(float a1, float a2)
     return bin;
 }
 
-// One warp, queries in order.  key = dist << 22 | position-in-list: min = best with first-wins ties.
-__global__ void __launch_bounds__(32)
-projResolveKernel(const orbx_proj_query* __restrict__ q, int nq, const int* __restrict__ off, const int* __restrict__ cand,
-                  const int* __restrict__ rec, const orbx_keypoint* __restrict__ keys, const uint8_t* __restrict__ occupied, int n,
-                  int modeFlags, int thDist, float nnratio, int checkOri, int* __restrict__ assign, int* __restrict__ hist)
+// exact best / second-best key of query i among the candidates nobody has claimed yet (all lanes get the result)
+__device__ void rescanQuery(const orbx_proj_query* __restrict__ q, int i, const GridDev& g, const int* __restrict__ off,
+                            const float4* __restrict__ cinfo, const uint4* __restrict__ dsort, const uint32_t* occ,
+                            int checkUr, int lane, uint32_t& k1, uint32_t& k2)
 {
-    extern __shared__ uint32_t occ[];
-    const int lane = threadIdx.x;
-    for (int i = lane; i < (n + 31) / 32; i += 32) {
-        uint32_t m = 0;
-        if (occupied) for (int b = 0; b < 32; ++b) { const int j = i * 32 + b; if (j < n && occupied[j]) m |= 1u << b; }
-        occ[i] = m;
+    const QueryGeom s = geomOf(q[i]);
+    const Window w = windowOf(g, s.x, s.y, s.r);
+    k1 = kNoKeyP; k2 = kNoKeyP;
+    if (!w.empty) {
+        const uint4* qd = reinterpret_cast<const uint4*>(q[i].desc);
+        const uint4 a0 = qd[0], a1 = qd[1];
+        for (int ix = w.c0; ix <= w.c1; ++ix) {
+            const int jb = off[ix * g.rows + w.r0], je = off[ix * g.rows + w.r1 + 1];
+            for (int j = jb + lane; j < je; j += 32) {
+                int oct;
+                if (!candPass(cinfo[j], s, checkUr, oct)) continue;
+                if ((occ[j >> 5] >> (j & 31)) & 1u) continue;
+                const uint32_t key = ((uint32_t)hamming256(a0, a1, dsort[2 * j], dsort[2 * j + 1]) << kJBits) | (uint32_t)j;
+                k2 = min(k2, max(k1, key)); k1 = min(k1, key);
+            }
+        }
     }
-    __syncwarp();
-    int nm = 0;
-    for (int i = 0; i < nq; ++i) {
-        const int b = off[i], e = off[i + 1];
-        if (e == b) continue;
-        uint32_t k1 = 0xffffffffu, k2 = 0xffffffffu;
-        for (int p = b + lane; p < e; p += 32) {
-            const int f = cand[p], r = rec[p];
-            if ((r >> 15) & 1) continue;
-            if ((occ[f >> 5] >> (f & 31)) & 1u) continue;
-            const uint32_t key = ((uint32_t)(r & 511) << 22) | (uint32_t)(p - b);
-            if (key < k1) { k2 = k1; k1 = key; } else if (key < k2) k2 = key;
-        }
-        #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const uint32_t b1 = __shfl_xor_sync(0xffffffffu, k1, o), b2 = __shfl_xor_sync(0xffffffffu, k2, o);
-            const uint32_t lo = min(k1, b1), hi = max(k1, b1);
-            k2 = min(hi, min(k2, b2)); k1 = lo;
-        }
-        if (k1 == 0xffffffffu) continue;
-        const int best = (int)(k1 >> 22);
-        if (best > thDist) continue;
-        const int p1 = b + (int)(k1 & 0x3fffffu);
-        if (modeFlags & ORBX_PROJ_RATIO_SAME_LEVEL) {            // src/ORBmatcher.cc:177-186
-            if (k2 != 0xffffffffu) {
-                const int p2 = b + (int)(k2 & 0x3fffffu);
-                const int l1 = (rec[p1] >> 9) & 63, l2 = (rec[p2] >> 9) & 63;
-                if (l1 == l2 && (float)best > __fmul_rn(nnratio, (float)(int)(k2 >> 22))) continue;
-            }   // bestLevel2 == -1 never equals a real level
-        }
-        const int f = cand[p1];
-        __syncwarp();
-        if (lane == 0) {
-            occ[f >> 5] |= 1u << (f & 31);
-            assign[f] = i;
-            if (checkOri) hist[rotBinP(q[i].angle, keys[f].angle)]++;
-        }
-        ++nm;
-        __syncwarp();
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const uint32_t b1 = __shfl_xor_sync(0xffffffffu, k1, o), b2 = __shfl_xor_sync(0xffffffffu, k2, o);
+        const uint32_t lo = min(k1, b1), hi = max(k1, b1);
+        k2 = min(hi, min(k2, b2)); k1 = lo;
     }
-    if (lane == 0) hist[kHistoP] = nm;
 }
 
-__global__ void __launch_bounds__(256)
-projRotationKernel(const orbx_proj_query* __restrict__ q, const orbx_keypoint* __restrict__ keys, int n, int* __restrict__ assign,
-                   int* __restrict__ hist)
+// P3.  claims are bits over j (position in the flat grid array); matchJ[i] = claimed j of query i or -1.
+__global__ void __launch_bounds__(kResolveThreads)
+projResolveKernel(const orbx_proj_query* __restrict__ q, int nq, GridDev g, const int* __restrict__ off, const int* __restrict__ idx,
+                  const float4* __restrict__ cinfo, const uint4* __restrict__ dsort, const uint4* __restrict__ topKey,
+                  const int2* __restrict__ meta, const orbx_keypoint* __restrict__ keys, int n, int modeFlags, int thDist,
+                  float nnratio, int checkOri, int* __restrict__ matchJ, int* __restrict__ assign, int* __restrict__ nmOut)
 {
+    extern __shared__ uint32_t occ[];
+    __shared__ int sHist[kHistoP];
     __shared__ int keep[3];
     __shared__ int total;
-    if (threadIdx.x == 0) {
-        total = 0;
-        int max1 = 0, max2 = 0, max3 = 0, i1 = -1, i2 = -1, i3 = -1;
-        for (int i = 0; i < kHistoP; ++i) {
-            const int s = hist[i];
-            if (s > max1) { max3 = max2; max2 = max1; max1 = s; i3 = i2; i2 = i1; i1 = i; }
-            else if (s > max2) { max3 = max2; max2 = s; i3 = i2; i2 = i; }
-            else if (s > max3) { max3 = s; i3 = i; }
+    const int tid = threadIdx.x, lane = tid & 31;
+    for (int i = tid; i < (n + 31) / 32; i += kResolveThreads) occ[i] = 0;
+    if (tid < kHistoP) sHist[tid] = 0;
+    if (tid == 0) total = 0;
+    __syncthreads();
+    if (tid < 32) {
+        const bool ratio = modeFlags & ORBX_PROJ_RATIO_SAME_LEVEL;
+        const int checkUr = (modeFlags & ORBX_PROJ_CHECK_URIGHT) ? 1 : 0;
+        const uint4 none = make_uint4(kNoKeyP, kNoKeyP, kNoKeyP, kNoKeyP);
+        uint4 eN = none; int2 mN = make_int2(0, 0);
+        if (lane < nq) { eN = topKey[lane]; mN = meta[lane]; }
+        for (int i0 = 0; i0 < nq; i0 += 32) {
+            const int i = i0 + lane;
+            const uint4 e = eN; const int2 m = mN;
+            if (i + 32 < nq) { eN = topKey[i + 32]; mN = meta[i + 32]; } else eN = none;
+            const uint32_t j0 = e.x & kJMask, j1 = e.y & kJMask, j2 = e.z & kJMask, j3 = e.w & kJMask;
+            const bool complete = m.x <= 4;
+            // a query whose overall best is beyond the threshold can never be accepted
+            uint32_t pending = __ballot_sync(0xffffffffu, i < nq && e.x != kNoKeyP && (int)(e.x >> kJBits) <= thDist);
+            int myJ = -1;
+            while (pending) {
+                const int t0 = __ffs(pending) - 1;
+                int claim = -1; bool need = false;
+                uint32_t dep0 = kJMask, dep1 = kJMask;   // unclaimed entries (besides the claim) the decision rests on
+                if ((pending >> lane) & 1u) {
+                    // first and second unclaimed entry of the list
+                    uint32_t u0 = kNoKeyP, u1 = kNoKeyP; int lv0 = 0, lv1 = 0;
+                    const uint32_t ks[4] = {e.x, e.y, e.z, e.w}, js[4] = {j0, j1, j2, j3};
+                    #pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const bool free_ = ks[k] != kNoKeyP && !((occ[js[k] >> 5] >> (js[k] & 31)) & 1u);
+                        if (free_) {
+                            if (u0 == kNoKeyP) { u0 = ks[k]; lv0 = (m.y >> (8 * k)) & 255; }
+                            else if (u1 == kNoKeyP) { u1 = ks[k]; lv1 = (m.y >> (8 * k)) & 255; }
+                        }
+                    }
+                    if (u0 == kNoKeyP) {
+                        // everything listed is taken: unlisted candidates are no closer than the last listed one
+                        need = !complete && (int)(e.w >> kJBits) <= thDist;
+                    } else {
+                        const int best = (int)(u0 >> kJBits);
+                        if (best <= thDist) {          // else: later claims can only push the best further away
+                            bool ok = true;
+                            if (ratio) {                             // src/ORBmatcher.cc:177-186
+                                if (u1 != kNoKeyP) {
+                                    dep1 = u1 & kJMask;
+                                    if (lv0 == lv1 && (float)best > __fmul_rn(nnratio, (float)(int)(u1 >> kJBits))) { ok = false; dep0 = u0 & kJMask; }
+                                } else if (!complete) {
+                                    // the runner-up is unlisted, its distance >= the last listed one: if the ratio rule
+                                    // passes against that bound it passes against the real one, else look it up
+                                    if ((float)best > __fmul_rn(nnratio, (float)(int)(e.w >> kJBits))) { ok = false; need = true; }
+                                }   // no runner-up at all: bestLevel2 == -1 never equals a real level
+                            }
+                            if (ok) claim = (int)(u0 & kJMask);
+                        }
+                    }
+                }
+                const uint32_t needMask = __ballot_sync(0xffffffffu, need);
+                if ((needMask >> t0) & 1u) {
+                    uint32_t k1, k2;
+                    rescanQuery(q, i0 + t0, g, off, cinfo, dsort, occ, checkUr, lane, k1, k2);
+                    if (lane == t0 && k1 != kNoKeyP && (int)(k1 >> kJBits) <= thDist) {
+                        bool ok = true;
+                        if (ratio && k2 != kNoKeyP) {
+                            const int lv1 = __float_as_int(cinfo[k1 & kJMask].w) & 0xff, lv2 = __float_as_int(cinfo[k2 & kJMask].w) & 0xff;
+                            if (lv1 == lv2 && (float)(int)(k1 >> kJBits) > __fmul_rn(nnratio, (float)(int)(k2 >> kJBits))) ok = false;
+                        }
+                        if (ok) { myJ = (int)(k1 & kJMask); occ[myJ >> 5] |= 1u << (myJ & 31); }
+                    }
+                    pending &= ~(1u << t0);
+                    __syncwarp();
+                    continue;
+                }
+                // Speculative commit.  Lanes claiming the same entry: the lowest one (the leader) owns it.  Leaders mark
+                // their claim; a lane whose decision rests on an entry that somebody marked in this round (whoever it
+                // is: conservative) waits for the next round, as does everything behind it.  The lowest pending lane
+                // has nobody before it and always commits.
+                // (match.any costs a pass per distinct value, so it only runs when an atomicOr has seen a duplicate)
+                bool leader = claim >= 0;
+                uint32_t seen = 0;
+                if (leader) seen = atomicOr(&occ[claim >> 5], 1u << (claim & 31)) & (1u << (claim & 31));
+                if (__ballot_sync(0xffffffffu, seen != 0)) {
+                    const uint32_t peers = __match_any_sync(0xffffffffu, claim >= 0 ? (uint32_t)claim : (0x80000000u | (uint32_t)lane));
+                    leader = claim >= 0 && (peers & ((1u << lane) - 1u)) == 0;
+                }
+                bool unsafe = need || (claim >= 0 && !leader);
+                __syncwarp();
+                if (lane != t0) {
+                    if (dep0 != kJMask && ((occ[dep0 >> 5] >> (dep0 & 31)) & 1u)) unsafe = true;
+                    if (dep1 != kJMask && ((occ[dep1 >> 5] >> (dep1 & 31)) & 1u)) unsafe = true;
+                }
+                const uint32_t unsafeMask = __ballot_sync(0xffffffffu, unsafe) & pending;
+                const uint32_t commit = unsafeMask ? (pending & ((1u << (__ffs(unsafeMask) - 1)) - 1u)) : pending;
+                if (leader) {
+                    if ((commit >> lane) & 1u) myJ = claim;
+                    else atomicAnd(&occ[claim >> 5], ~(1u << (claim & 31)));
+                }
+                pending &= ~commit;
+                __syncwarp();
+            }
+            if (i < nq) matchJ[i] = myJ;
         }
-        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { i2 = -1; i3 = -1; }
-        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) i3 = -1;
-        keep[0] = i1; keep[1] = i2; keep[2] = i3;
     }
     __syncthreads();
     int cnt = 0;
-    for (int f = threadIdx.x; f < n; f += blockDim.x) {
-        const int i = assign[f];
-        if (i < 0) continue;
-        const int bin = rotBinP(q[i].angle, keys[f].angle);
-        if (bin != keep[0] && bin != keep[1] && bin != keep[2]) { assign[f] = -1; continue; }
-        ++cnt;
+    for (int i = tid; i < nq; i += kResolveThreads) {
+        const int j = matchJ[i];
+        if (j < 0) continue;
+        const int f = idx[j];
+        assign[f] = i; ++cnt;
+        if (checkOri) atomicAdd(&sHist[rotBinP(q[i].angle, keys[f].angle)], 1);
+    }
+    if (checkOri) {     // ComputeThreeMaxima + removal, src/ORBmatcher.cc:1884-1903, :2076-2120
+        __syncthreads();
+        if (tid == 0) {
+            int max1 = 0, max2 = 0, max3 = 0, i1 = -1, i2 = -1, i3 = -1;
+            for (int i = 0; i < kHistoP; ++i) {
+                const int s = sHist[i];
+                if (s > max1) { max3 = max2; max2 = max1; max1 = s; i3 = i2; i2 = i1; i1 = i; }
+                else if (s > max2) { max3 = max2; max2 = s; i3 = i2; i2 = i; }
+                else if (s > max3) { max3 = s; i3 = i; }
+            }
+            if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { i2 = -1; i3 = -1; }
+            else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) i3 = -1;
+            keep[0] = i1; keep[1] = i2; keep[2] = i3;
+        }
+        __syncthreads();
+        cnt = 0;
+        for (int i = tid; i < nq; i += kResolveThreads) {
+            const int j = matchJ[i];
+            if (j < 0) continue;
+            const int f = idx[j];
+            const int bin = rotBinP(q[i].angle, keys[f].angle);
+            if (bin != keep[0] && bin != keep[1] && bin != keep[2]) assign[f] = -1; else ++cnt;
+        }
     }
     atomicAdd(&total, cnt);
     __syncthreads();
-    if (threadIdx.x == 0) hist[kHistoP] = total;
+    if (tid == 0) *nmOut = total;
 }
 
 struct BumpP { size_t off = 0; size_t take(size_t b) { const size_t o = off; off += (b + 255) & ~(size_t)255; return o; } };
 
-static int buildGrid(Ctx* c, const orbx_keypoint* dKeys, int n, const GridDev& g, int* dCell, int* dCnt, int* dOff, int* dIdx)
+static int launchGridBuild(Ctx* c, const orbx_keypoint* dKeys, int n, const GridDev& g, int* dCellTmp, int* dTmpIdx, int* dOff, int* dIdx,
+                           const uint4* dDesc, const float* dUright, const uint8_t* dOcc, float4* dCinfo, uint4* dDsort,
+                           int* dAssign, int nAssign)
 {
-    const int ncell = g.cols * g.rows;
-    if (n > 0) gridCellKernel<<<(n + 255) / 256, 256, 0, c->stream>>>(dKeys, n, g, dCell);
-    gridCountKernel<<<(ncell + 127) / 128, 128, 0, c->stream>>>(dCell, n, ncell, dCnt);
-    exclusiveScanKernel<<<1, 1024, 0, c->stream>>>(dCnt, ncell, dOff);
-    gridFillKernel<<<(ncell + 127) / 128, 128, 0, c->stream>>>(dCell, n, ncell, dOff, dIdx);
-    c->kernelLaunches += 4; c->stageLaunches[ST_MATCH] += 4;
+    const size_t smem = sizeof(int) * (size_t)(2 * g.cols * g.rows + 1);
+    if (smem > 200 * 1024) return ORBX_E_CAPACITY;
+    if (smem > 48 * 1024) ORBX_CUDA(c, cudaFuncSetAttribute(gridBuildKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gridBuildKernel<<<1, kGridThreads, smem, c->stream>>>(dKeys, n, g, dCellTmp, dTmpIdx, dOff, dIdx, dDesc, dUright, dOcc, dCinfo,
+                                                          dDsort, dAssign, nAssign);
+    c->kernelLaunches += 1; c->stageLaunches[ST_MATCH] += 1;
     ORBX_CUDA(c, cudaGetLastError());
     return ORBX_OK;
 }
@@ -275,10 +444,10 @@ extern "C" int orbx_assign_grid(orbx_ctx* h, const orbx_keypoint* keys, int n, c
     ORBX_CUDA(c, cudaSetDevice(c->device));
     const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
     const int ncell = g->cols * g->rows;
+    const size_t n1 = (size_t)std::max(n, 1);
     BumpP B;
-    const size_t oK = B.take(sizeof(orbx_keypoint) * (size_t)std::max(n, 1)), oCell = B.take(sizeof(int) * (size_t)std::max(n, 1)),
-                 oCnt = B.take(sizeof(int) * (size_t)ncell), oOff = B.take(sizeof(int) * (size_t)(ncell + 1)),
-                 oIdx = B.take(sizeof(int) * (size_t)std::max(n, 1));
+    const size_t oK = B.take(sizeof(orbx_keypoint) * n1), oCell = B.take(sizeof(int) * n1), oTmp = B.take(sizeof(int) * n1),
+                 oOff = B.take(sizeof(int) * (size_t)(ncell + 1)), oIdx = B.take(sizeof(int) * n1);
     int rc = ensureScratch(c, B.off);
     if (rc) return rc;
     uint8_t* S = (uint8_t*)c->dScratch;
@@ -288,7 +457,7 @@ extern "C" int orbx_assign_grid(orbx_ctx* h, const orbx_keypoint* keys, int n, c
     int* dOff = outDev ? cell_off : (int*)(S + oOff);
     int* dIdx = outDev ? cell_idx : (int*)(S + oIdx);
     stageBegin(c, ST_MATCH);
-    rc = buildGrid(c, dK, n, gd, (int*)(S + oCell), (int*)(S + oCnt), dOff, dIdx);
+    rc = launchGridBuild(c, dK, n, gd, (int*)(S + oCell), (int*)(S + oTmp), dOff, dIdx, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0);
     stageEnd(c, ST_MATCH, 0);
     if (rc) return rc;
     if (!outDev) {
@@ -313,73 +482,77 @@ extern "C" int orbx_search_by_projection(orbx_ctx* h, const orbx_proj_query* q, 
     const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
     const int ncell = g->cols * g->rows;
     const size_t occBytes = (size_t)((n + 31) / 32 + 1) * 4;
-    if (occBytes > 200 * 1024) return ORBX_E_CAPACITY;
-    // pass 1 layout (fixed part)
+    if (occBytes > 200 * 1024 || n >= (1 << kJBits)) return ORBX_E_CAPACITY;
+    const size_t nq1 = (size_t)std::max(nq, 1);
+    // scratch: [inputs, one block so that host inputs arrive with a single copy][work][results]
     BumpP B;
-    const size_t oQ = B.take(sizeof(orbx_proj_query) * (size_t)std::max(nq, 1)), oK = B.take(sizeof(orbx_keypoint) * (size_t)n),
-                 oD = B.take((size_t)32 * n), oU = B.take(sizeof(float) * (size_t)n), oOcc = B.take((size_t)n),
-                 oCell = B.take(sizeof(int) * (size_t)n), oCnt = B.take(sizeof(int) * (size_t)ncell),
+    const size_t oQ = B.take(sizeof(orbx_proj_query) * nq1), oK = B.take(sizeof(orbx_keypoint) * (size_t)n),
+                 oD = B.take((size_t)32 * n), oU = B.take(sizeof(float) * (size_t)n), oOcc = B.take((size_t)n);
+    const size_t inBytes = B.off;
+    const size_t oCell = B.take(sizeof(int) * (size_t)n), oTmp = B.take(sizeof(int) * (size_t)n),
                  oOff = B.take(sizeof(int) * (size_t)(ncell + 1)), oIdx = B.take(sizeof(int) * (size_t)n),
-                 oQCnt = B.take(sizeof(int) * (size_t)std::max(nq, 1)), oQOff = B.take(sizeof(int) * (size_t)(nq + 1)),
-                 oHist = B.take(sizeof(int) * (kHistoP + 1)), oAssign = B.take(sizeof(int) * (size_t)n);
-    const size_t fixedBytes = B.off;
-    // worst case candidate volume is nq * n; allocate on demand after the count pass
-    int rc = ensureScratch(c, fixedBytes);
+                 oInfo = B.take(sizeof(float4) * (size_t)n), oSort = B.take((size_t)32 * n),
+                 oTop = B.take(sizeof(uint4) * nq1), oMeta = B.take(sizeof(int2) * nq1), oMJ = B.take(sizeof(int) * nq1),
+                 oOut = B.take(sizeof(int) * (size_t)(n + 1));
+    int rc = ensureScratch(c, B.off);
+    if (rc) return rc;
+    const size_t outBytes = sizeof(int) * (size_t)(n + 1);
+    rc = ensureMatchPinned(c, inBytes + outBytes);
     if (rc) return rc;
     uint8_t* S = (uint8_t*)c->dScratch;
     const orbx_proj_query* dQ = q; const orbx_keypoint* dK = keys; const uint4* dD = (const uint4*)desc;
     const float* dU = uright; const uint8_t* dOcc = occupied;
     stageBegin(c, ST_H2D);
     if (!inDev) {
-        if (nq) ORBX_CUDA(c, cudaMemcpyAsync(S + oQ, q, sizeof(orbx_proj_query) * (size_t)nq, cudaMemcpyHostToDevice, c->stream));
-        ORBX_CUDA(c, cudaMemcpyAsync(S + oK, keys, sizeof(orbx_keypoint) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
-        ORBX_CUDA(c, cudaMemcpyAsync(S + oD, desc, (size_t)32 * n, cudaMemcpyHostToDevice, c->stream));
+        uint8_t* H = c->hMatch;
+        if (nq) memcpy(H + oQ, q, sizeof(orbx_proj_query) * (size_t)nq);
+        memcpy(H + oK, keys, sizeof(orbx_keypoint) * (size_t)n);
+        memcpy(H + oD, desc, (size_t)32 * n);
+        if (uright) memcpy(H + oU, uright, sizeof(float) * (size_t)n);
+        if (occupied) memcpy(H + oOcc, occupied, (size_t)n);
+        ORBX_CUDA(c, cudaMemcpyAsync(S, H, inBytes, cudaMemcpyHostToDevice, c->stream));
         dQ = (const orbx_proj_query*)(S + oQ); dK = (const orbx_keypoint*)(S + oK); dD = (const uint4*)(S + oD);
-        if (uright) { ORBX_CUDA(c, cudaMemcpyAsync(S + oU, uright, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, c->stream)); dU = (const float*)(S + oU); }
-        if (occupied) { ORBX_CUDA(c, cudaMemcpyAsync(S + oOcc, occupied, (size_t)n, cudaMemcpyHostToDevice, c->stream)); dOcc = S + oOcc; }
+        if (uright) dU = (const float*)(S + oU);
+        if (occupied) dOcc = S + oOcc;
     }
     stageEnd(c, ST_H2D, 0);
     const GridDev gd = {g->min_x, g->min_y, g->inv_w, g->inv_h, g->cols, g->rows};
-    int* dAssign = outDev ? assign : (int*)(S + oAssign);
-    int* dHist = (int*)(S + oHist);
+    int* dOut = (int*)(S + oOut);                    // assign[n] then the match count
+    int* dAssign = outDev ? assign : dOut;
     stageBegin(c, ST_MATCH);
-    rc = buildGrid(c, dK, n, gd, (int*)(S + oCell), (int*)(S + oCnt), (int*)(S + oOff), (int*)(S + oIdx));
+    rc = launchGridBuild(c, dK, n, gd, (int*)(S + oCell), (int*)(S + oTmp), (int*)(S + oOff), (int*)(S + oIdx), dD, dU, dOcc,
+                         (float4*)(S + oInfo), (uint4*)(S + oSort), dAssign, n);
     if (rc) return rc;
-    ORBX_CUDA(c, cudaMemsetAsync(dHist, 0, sizeof(int) * (kHistoP + 1), c->stream));
-    ORBX_CUDA(c, cudaMemsetAsync(dAssign, 0xff, sizeof(int) * (size_t)n, c->stream));
-    int total = 0, launches = 0;
+    int launches = 0;
     if (nq > 0) {
-        projEnumKernel<false><<<(nq + 127) / 128, 128, 0, c->stream>>>(dQ, nq, dK, gd, (int*)(S + oOff), (int*)(S + oIdx),
-                                                                    (int*)(S + oQCnt), nullptr, nullptr);
-        exclusiveScanKernel<<<1, 1024, 0, c->stream>>>((int*)(S + oQCnt), nq, (int*)(S + oQOff));
+        projScanKernel<<<(nq + kScanWarps - 1) / kScanWarps, 32 * kScanWarps, 0, c->stream>>>(dQ, nq, gd, (int*)(S + oOff), (float4*)(S + oInfo), (uint4*)(S + oSort),
+                                                           (mode_flags & ORBX_PROJ_CHECK_URIGHT) ? 1 : 0, (uint4*)(S + oTop),
+                                                           (int2*)(S + oMeta));
+        if (occBytes > 40 * 1024)
+            ORBX_CUDA(c, cudaFuncSetAttribute(projResolveKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)occBytes));
+        projResolveKernel<<<1, kResolveThreads, occBytes, c->stream>>>(dQ, nq, gd, (int*)(S + oOff), (int*)(S + oIdx),
+                                                                       (float4*)(S + oInfo), (uint4*)(S + oSort), (uint4*)(S + oTop),
+                                                                       (int2*)(S + oMeta), dK, n, mode_flags, th_dist, nnratio,
+                                                                       check_ori ? 1 : 0, (int*)(S + oMJ), dAssign, dOut + n);
         launches += 2;
-        ORBX_CUDA(c, cudaMemcpyAsync(&total, (int*)(S + oQOff) + nq, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
-    }
-    // candidate arrays live after the fixed part; growing the scratch would move it, so use a second buffer
-    int *dCand = nullptr, *dRec = nullptr;
-    if (total > 0) {
-        ORBX_CUDA(c, cudaMallocAsync((void**)&dCand, sizeof(int) * (size_t)total * 2, c->stream));
-        dRec = dCand + total;
-        projEnumKernel<true><<<(nq + 127) / 128, 128, 0, c->stream>>>(dQ, nq, dK, gd, (int*)(S + oOff), (int*)(S + oIdx), nullptr,
-                                                                   (int*)(S + oQOff), dCand);
-        projDistKernel<<<(total + 255) / 256, 256, 0, c->stream>>>(dQ, nq, (int*)(S + oQOff), dCand, dK, dD, dU,
-                                                                  (mode_flags & ORBX_PROJ_CHECK_URIGHT) ? 1 : 0, dRec);
-        launches += 2;
-    }
-    if (nq > 0) {
-        projResolveKernel<<<1, 32, occBytes, c->stream>>>(dQ, nq, (int*)(S + oQOff), dCand, dRec, dK, dOcc, n, mode_flags, th_dist,
-                                                        nnratio, check_ori ? 1 : 0, dAssign, dHist);
-        ++launches;
-        if (check_ori) { projRotationKernel<<<1, 256, 0, c->stream>>>(dQ, dK, n, dAssign, dHist); ++launches; }
+    } else {
+        ORBX_CUDA(c, cudaMemsetAsync(dOut + n, 0, sizeof(int), c->stream));
     }
     stageEnd(c, ST_MATCH, launches);
     ORBX_CUDA(c, cudaGetLastError());
-    if (dCand) ORBX_CUDA(c, cudaFreeAsync(dCand, c->stream));
     int nm = 0;
-    if (!outDev) ORBX_CUDA(c, cudaMemcpyAsync(assign, dAssign, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
-    ORBX_CUDA(c, cudaMemcpyAsync(&nm, dHist + kHistoP, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (!outDev) {
+        int* HO = (int*)(c->hMatch + inBytes);
+        ORBX_CUDA(c, cudaMemcpyAsync(HO, dOut, outBytes, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+        memcpy(assign, HO, sizeof(int) * (size_t)n);
+        nm = HO[n];
+    } else {
+        int* HO = (int*)(c->hMatch + inBytes);
+        ORBX_CUDA(c, cudaMemcpyAsync(HO, dOut + n, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+        nm = HO[0];
+    }
     if (nmatches) *nmatches = nm;
     return ORBX_OK;
 }

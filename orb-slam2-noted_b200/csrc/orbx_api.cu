@@ -63,6 +63,16 @@ int ensureScratch(Ctx* c, size_t bytes)
     return ORBX_OK;
 }
 
+int ensureMatchPinned(Ctx* c, size_t bytes)
+{
+    if (bytes <= c->hMatchBytes) return ORBX_OK;
+    if (c->hMatch) { cudaStreamSynchronize(c->stream); cudaFreeHost(c->hMatch); c->hMatch = nullptr; c->hMatchBytes = 0; }
+    bytes = (bytes + (1u << 18)) & ~(size_t)((1u << 18) - 1);
+    ORBX_CUDA(c, cudaMallocHost((void**)&c->hMatch, bytes));
+    c->hMatchBytes = bytes;
+    return ORBX_OK;
+}
+
 // cvRound(float): round half to even under the default rounding mode
 static inline int cvRoundF(float v) { return (int)lrintf(v); }
 static inline int cvRoundD(double v) { return (int)lrint(v); }
@@ -270,6 +280,7 @@ void orbx_destroy(orbx_ctx* h)
                     c->dOutKp, c->dOutDesc, c->dOutN, c->dIn, c->dScratch, c->dTensorMaps};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->hPinned) cudaFreeHost(c->hPinned);
+    if (c->hMatch) cudaFreeHost(c->hMatch);
     if (c->evFence) cudaEventDestroy(c->evFence);
     for (cudaEvent_t e : c->evIn) cudaEventDestroy(e);
     for (cudaEvent_t e : c->evDone) cudaEventDestroy(e);

@@ -102,6 +102,7 @@ struct Ctx {
     std::string lastCudaError;
     // matcher scratch
     void* dScratch = nullptr; size_t scratchBytes = 0;
+    uint8_t* hMatch = nullptr; size_t hMatchBytes = 0; // pinned staging for the small matcher inputs / results (one copy each way)
 };
 
 #ifdef __CUDACC__
@@ -127,6 +128,7 @@ int cudaFail(Ctx* c, cudaError_t e, const char* what);
 void stageBegin(Ctx* c, int stage);
 void stageEnd(Ctx* c, int stage, int launches);
 int ensureScratch(Ctx* c, size_t bytes);
+int ensureMatchPinned(Ctx* c, size_t bytes);
 
 // kernels (one launcher per stage; all asynchronous on c->stream) -------------------------------
 // frames [frame0, frame0 + batch) of the current batch
