@@ -23,7 +23,6 @@
 
 namespace orbx {
 
-constexpr int kFastThreads = 256;
 constexpr int kCornerCap = 4096;                 // corner list capacity (scored in bulk whenever the next batch could overflow it)
 constexpr int kGroupBatch = 512;                 // 4-pixel groups per full-test batch (<= 2048 new corners)
 constexpr int kMaxCellsPerStrip = 32;
@@ -74,7 +73,8 @@ __device__ __forceinline__ int warpAppend(int* counter, int cnt)
 // upper bound of NMS survivors in a strip: no two 8-neighbours inside one cell both survive
 __host__ __device__ inline int fastSurvivorCap(int maxRw, int maxRh) { return ((maxRw + kMaxCellsPerStrip) / 2 + 1) * ((maxRh + 1) / 2); }
 
-__global__ void __launch_bounds__(kFastThreads, 4)
+template <int kFastThreads, int kMinCtas>
+__global__ void __launch_bounds__(kFastThreads, kMinCtas)
 fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
                 const uint8_t* __restrict__ pyr, unsigned long long* __restrict__ cand, int* __restrict__ candCount,
                 int tilePitchMax, int tileRowsMax, int scorePitchMax, int listBytes, uint32_t rcpBP4)
@@ -419,15 +419,20 @@ int launchFast(Ctx* c, int frame0, int batch)
         smem += sizeof(uint32_t) * ((size_t)maxRh * BP + (size_t)(TP >> 2));
         smem += listBytes + (size_t)SP;
         smem = (smem + 127) & ~(size_t)127;
-        static size_t configured = 0;
-        if (smem > 48 * 1024 && smem > configured) {
-            ORBX_CUDA(c, cudaFuncSetAttribute(fastStripKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            configured = smem;
-        }
         const uint32_t rcpBP4 = 0xffffffffu / (uint32_t)(BP * 4) + 1u;
-        dim3 grid(g.stripsPerFrame, batch), block(kFastThreads);
-        fastStripKernel<<<grid, block, smem, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr,
-                                                         c->dCand, c->dCandCount, TP, TR, SP, (int)listBytes, rcpBP4);
+        dim3 grid(g.stripsPerFrame, batch);
+        auto go = [&](auto kern, int threads, size_t* configured) -> int {
+            if (smem > 48 * 1024 && smem > *configured) {
+                ORBX_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                *configured = smem;
+            }
+            kern<<<grid, dim3(threads), smem, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr,
+                                                           c->dCand, c->dCandCount, TP, TR, SP, (int)listBytes, rcpBP4);
+            return ORBX_OK;
+        };
+        static size_t cfg256 = 0, cfg128 = 0;
+        const int rc = c->fastThreads == 128 ? go(fastStripKernel<128, 8>, 128, &cfg128) : go(fastStripKernel<256, 4>, 256, &cfg256);
+        if (rc != ORBX_OK) return rc;
         launches = 1;
     }
     stageEnd(c, ST_FAST, launches);

@@ -169,7 +169,7 @@ static int configure(Ctx* c, int w, int h)
         // FAST strips: segments of whole cells, at most 320 candidate columns and 32 cells each (k_fast.cu)
         q.stripBase = stripBase; q.segsPerRow = 0; q.cellsPerSeg = 1;
         if (q.nCols > 0) {
-            const int maxCells = std::max(1, std::min(32, 320 / q.wCell));
+            const int maxCells = std::max(1, std::min(32, c->fastSegW / q.wCell));
             q.segsPerRow = (q.nCols + maxCells - 1) / maxCells;
             q.cellsPerSeg = (q.nCols + q.segsPerRow - 1) / q.segsPerRow;
             stripBase += q.segsPerRow * q.nRows;
@@ -255,6 +255,8 @@ int orbx_create(orbx_ctx** out, int device, int nfeatures, float scale_factor, i
         if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (const char* e = getenv("ORBX_CHUNK")) c->chunk = atoi(e);
+        if (const char* e = getenv("ORBX_FAST_THREADS")) c->fastThreads = atoi(e) == 128 ? 128 : 256;
+        if (const char* e = getenv("ORBX_FAST_SEGW")) c->fastSegW = std::max(64, std::min(640, atoi(e)));
         if (cudaMalloc(&c->dGeom, sizeof(GeomSet)) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (cudaMalloc(&c->dCandCount, sizeof(int) * (size_t)max_batch * kMaxLevels) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (cudaMalloc(&c->dSelCount, sizeof(int) * (size_t)max_batch * kMaxLevels) != cudaSuccess) { rc = ORBX_E_CUDA; break; }

@@ -63,6 +63,7 @@ struct Ctx {
     cudaEvent_t evJoin = nullptr;
     std::vector<cudaEvent_t> evIn, evDone;
     cudaEvent_t evFence = nullptr;                // orders a new call's H2D after the previous call's kernels
+    int fastThreads = 256, fastSegW = 320;         // FAST strip shape: threads per CTA, max candidate columns per strip
     int chunk = 64;                                // frames per pipeline chunk (stages of a chunk stay L2-resident)
     int nfeatures = 0, nlevels = 0, iniTh = 0, minTh = 0;
     float scaleFactor = 0;
