@@ -2,29 +2,31 @@
 // (ComputeKeyPointsOctTree cell loop, src/ORBextractor.cc:1058-1153; cv::FAST(roi, th, nms=true)).
 //
 // One CTA per STRIP = one cell-row of one level of one frame, split into segments of whole cells so the tile fits in
-// shared memory; all levels and frames in ONE launch.  The candidate regions of the reference's cells tile the
-// detection window without overlap, so a strip is detected as one image with per-cell NMS boundaries.
+// shared memory; all levels and frames in ONE launch; the strip table is built on the host (StripDesc, 16 bytes).
+// The candidate regions of the reference's cells tile the detection window without overlap, so a strip is detected as
+// one image with per-cell NMS boundaries.
 //   stage   rows of the strip (+3 px apron) are brought into shared memory with 1-D bulk async copies
 //           (cp.async.bulk -> UBLKCP, completion on an mbarrier); plain loads when the source is not 16-byte aligned
 //   sweep 0 detects the whole strip at iniTh; sweep 1 (only if some cell kept nothing, :1128) detects those cells again
-//           at minTh.  Each sweep:
-//     pass 0  quick rejection, 4 pixels per thread step, byte-parallel in 32-bit registers; surviving groups -> list
-//     pass 1  full test of the listed groups: brighter/darker flags of the 16 ring pixels by SWAR unsigned-byte compares
-//             (3 LOP3/IADD per flag word), 9-contiguity as bit-sliced AND/OR trees (no per-pixel branches); corners go
-//             to a list and a bitmap
-//     score   list entries: exact OpenCV cornerScore (max over the 16 arcs of the arc's min margin, -1) -> u8 score map
+//           at minTh.  Inside a sweep every WARP owns the rows y = warp, warp + nWarps, ... and runs the detection
+//           phases on them without CTA barriers (lists and their counters are private to the warp):
+//     pass 0  quick rejection, 4 pixels per lane step, byte-parallel in 32-bit registers; surviving groups -> warp list
+//     pass 1  full test of the listed groups: brighter/darker flags of the 16 ring pixels by SWAR unsigned-byte compares,
+//             9-contiguity as bit-sliced AND/OR trees (no per-pixel branches); corners -> warp list
+//     score   listed corners: exact OpenCV cornerScore (max over the 16 arcs of the arc's min margin, -1) -> u8 score map
+//   one CTA barrier (the score map is complete), then
 //     nms     3x3 strict-> NMS inside the pixel's own cell (neighbours outside the cell count 0, exactly like the per-ROI
-//             cv::FAST calls); survivors -> compact list, per-cell survivor counts (the retry decision)
-//     emit    survivors -> global candidate records
+//             cv::FAST calls) over the warp's own corners; survivors go straight to the global candidate records
+//             (one global atomic per warp step); a cell that kept something is flagged for the retry decision
 // Output records are order-independent: key = (cell, ly, lx) reproduces the reference's push_back order
 // (cell-row-major, then pixel-row-major :1084-1149) whenever an ordered view is needed.
 #include "orbx_internal.h"
 #include <algorithm>
+#include <vector>
 
 namespace orbx {
 
-constexpr int kCornerCap = 4096;                 // corner list capacity (scored in bulk whenever the next batch could overflow it)
-constexpr int kGroupBatch = 512;                 // 4-pixel groups per full-test batch (<= 2048 new corners)
+constexpr int kCornerCapW = 384;                 // per-warp corner list (scored and dropped when the next step could overflow it)
 constexpr int kMaxCellsPerStrip = 32;
 
 __device__ __forceinline__ uint32_t smemAddr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -34,12 +36,6 @@ __device__ __forceinline__ uint32_t gtu4(uint32_t a, uint32_t b, uint32_t nb7)
 {
     const uint32_t x = (a & 0x7f7f7f7fu) + nb7;
     return (a & ~b) | (~(a ^ b) & x);
-}
-// per-byte unsigned a < b; b7 = b & 0x7f7f7f7f
-__device__ __forceinline__ uint32_t ltu4(uint32_t a, uint32_t b, uint32_t b7)
-{
-    const uint32_t x = b7 + (~a & 0x7f7f7f7fu);
-    return (b & ~a) | (~(a ^ b) & x);
 }
 
 __device__ __forceinline__ uint32_t nineOfSixteen(const uint32_t (&f)[16])
@@ -56,74 +52,50 @@ __device__ __forceinline__ uint32_t nineOfSixteen(const uint32_t (&f)[16])
     return (t0 | t1 | t2) | (t3 | t4 | a9[15]);
 }
 
-// warp-aggregated append of `cnt` items per lane; returns the lane's first slot
-__device__ __forceinline__ int warpAppend(int* counter, int cnt)
-{
-    const int lane = threadIdx.x & 31;
-    int incl = cnt;
-    #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
-    const int total = __shfl_sync(0xffffffffu, incl, 31);
-    int base = 0;
-    if (lane == 31) base = atomicAdd(counter, total);
-    base = __shfl_sync(0xffffffffu, base, 31);
-    return base + incl - cnt;
-}
-
-// upper bound of NMS survivors in a strip: no two 8-neighbours inside one cell both survive
-__host__ __device__ inline int fastSurvivorCap(int maxRw, int maxRh) { return ((maxRw + kMaxCellsPerStrip) / 2 + 1) * ((maxRh + 1) / 2); }
-
 template <int kFastThreads, int kMinCtas>
 __global__ void __launch_bounds__(kFastThreads, kMinCtas)
 fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
-                const uint8_t* __restrict__ pyr, unsigned long long* __restrict__ cand, int* __restrict__ candCount,
-                int tilePitchMax, int tileRowsMax, int scorePitchMax, int listBytes, uint32_t rcpBP4)
+                const uint8_t* __restrict__ pyr, const StripDesc* __restrict__ strips, unsigned long long* __restrict__ cand,
+                int* __restrict__ candCount, int tilePitchMax, int tileRowsMax, int scorePitchMax, int groupCapW)
 {
+    constexpr int nW = kFastThreads / 32;
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) unsigned long long sBar;
-    __shared__ int sGroupN, sCornerN, sSurvN, sBase;
-    __shared__ uint32_t sRetry;
-    __shared__ int sRegG0[kMaxCellsPerStrip], sRegNg[kMaxCellsPerStrip], sNgMax;   // pass-0 regions: first group column, group columns
-    __shared__ int sCellCnt[kMaxCellsPerStrip];
+    __shared__ int sCellKept[kMaxCellsPerStrip];
 
+    const uint4 sdw = __ldg(reinterpret_cast<const uint4*>(strips) + blockIdx.x);
+    const int level = sdw.x & 0xff, nc = (sdw.x >> 8) & 0xff, ci = sdw.x >> 16;
+    const int j0 = sdw.y & 0xffff, cx0 = sdw.y >> 16;
+    const int cy0 = sdw.z & 0xffff, rw = sdw.z >> 16;
+    const int rh = sdw.w & 0xffff;
+    const uint32_t rcpW = sdw.w >> 16;                               // (lx * rcpW) >> 16 == lx / wCell for lx < 1024
     const int frame = blockIdx.y + G.frame0;
-    int level = 0;
-    while (level + 1 < G.nlevels && (int)blockIdx.x >= G.lv[level + 1].stripBase) ++level;
     const LevelGeom& g = G.lv[level];
-    const int sIdx = blockIdx.x - g.stripBase;
-    const int ci = sIdx / g.segsPerRow, seg = sIdx - ci * g.segsPerRow;
-    const int j0 = seg * g.cellsPerSeg, j1 = min(j0 + g.cellsPerSeg, g.nCols);
-    const int cx0 = kEdge + j0 * g.wCell, cy0 = kEdge + ci * g.hCell;
-    const int cx1 = min(kEdge + j1 * g.wCell, g.w - kEdge), cy1 = min(cy0 + g.hCell, g.h - kEdge);
-    const int rw = cx1 - cx0, rh = cy1 - cy0;
-    if (rw <= 0 || rh <= 0) return; // skipped cells (:1094,:1112) have an empty candidate region
 
     const uint8_t* img; size_t pitch;
     if (level == 0) { img = lvl0 + (size_t)frame * lvl0Frame; pitch = lvl0Pitch; }
     else { img = pyr + g.planeOff + (size_t)frame * g.pitch * g.h; pitch = (size_t)g.pitch; }
 
     const int TP = tilePitchMax, SP = scorePitchMax;               // bytes per tile / score row
-    const int BP = (SP + 31) >> 5;                                  // bitmap words per row
     const int maxRh = tileRowsMax - 6;
     const int wp = TP >> 2;
     uint8_t* tile = smem;                                           // (rh + 6) rows
     uint8_t* score = smem + (size_t)TP * tileRowsMax;               // (rh + 2) x SP, zero apron
-    uint32_t* cornerBits = reinterpret_cast<uint32_t*>(score + (size_t)SP * (maxRh + 2)); // rh x BP
-    uint32_t* colValid = cornerBits + maxRh * BP;                   // per tile word column: bit 7 of the bytes to detect
-    uint16_t* cornerList = reinterpret_cast<uint16_t*>(colValid + wp);                    // kCornerCap
-    uint16_t* groupList = cornerList + kCornerCap;                  // up to maxRh * (SP/4 + 2) groups
-    uint32_t* survList = reinterpret_cast<uint32_t*>(groupList);    // reuses the group list once pass 1 is over
-    uint8_t* colCell = reinterpret_cast<uint8_t*>(cornerList) + listBytes;                // cell column of candidate column lx
+    uint32_t* colValid = reinterpret_cast<uint32_t*>(score + (size_t)SP * (maxRh + 2)); // per tile word column: bit 7 of the bytes to detect
+    uint16_t* cornerLists = reinterpret_cast<uint16_t*>(colValid + wp);                 // nW x kCornerCapW
+    uint16_t* groupLists = cornerLists + nW * kCornerCapW;          // nW x groupCapW
+    uint8_t* colCell = reinterpret_cast<uint8_t*>(groupLists + nW * groupCapW);          // cell column of candidate column lx
     const int TH = rh + 6;
     const bool aligned = ((((size_t)img) | pitch) & 15) == 0;
     const int xa = aligned ? ((cx0 - 4) & ~15) : (cx0 - 4) & ~3;    // image column of tile column 0 (>= 4 px left of cx0)
     const int off0 = cx0 - xa;                                      // tile column of the first candidate pixel (>= 4)
-    const int nc = j1 - j0;
+    const int cx1 = cx0 + rw;
+    const int wCell = g.wCell;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t ltMask = (1u << lane) - 1u;
+    asm volatile("" : "+r"(ltMask));                          // keep it in a register (ptxas would recompute it per use)
 
-    if (threadIdx.x == 0) {
-        sGroupN = 0; sCornerN = 0; sSurvN = 0;
-    }
-    if (threadIdx.x < kMaxCellsPerStrip) sCellCnt[threadIdx.x] = 0;
+    if (threadIdx.x < kMaxCellsPerStrip) sCellKept[threadIdx.x] = 0;
     if (aligned) {
         const int xb = min((cx1 + 3 + 15) & ~15, (int)pitch);
         const uint32_t rowBytes = (uint32_t)(xb - xa);
@@ -147,13 +119,13 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
             tile[y * TP + x] = img[(size_t)(cy0 - 3 + y) * pitch + xa + x];
         }
     }
-    // zero the score map and the bitmap, build the column tables while the copies are in flight
+    // zero the score map, build the column tables while the copies are in flight
     {
-        uint32_t* z = reinterpret_cast<uint32_t*>(score);
-        const int nz = (SP * (rh + 2) + 3) / 4;
-        for (int i = threadIdx.x; i < nz; i += kFastThreads) z[i] = 0;
-        for (int i = threadIdx.x; i < maxRh * BP; i += kFastThreads) cornerBits[i] = 0;
-        for (int i = threadIdx.x; i < rw; i += kFastThreads) colCell[i] = (uint8_t)(i / g.wCell);
+        const int nbytes = SP * (rh + 2);                           // SP is a multiple of 4, the map starts 16-byte aligned
+        uint4* z = reinterpret_cast<uint4*>(score);
+        for (int i = threadIdx.x; i < (nbytes >> 4); i += kFastThreads) z[i] = make_uint4(0, 0, 0, 0);
+        if ((int)threadIdx.x < ((nbytes & 15) >> 2)) reinterpret_cast<uint32_t*>(score)[(nbytes >> 4) * 4 + threadIdx.x] = 0;
+        for (int i = threadIdx.x; i < rw; i += kFastThreads) colCell[i] = (uint8_t)(((uint32_t)i * rcpW) >> 16);
         for (int i = threadIdx.x; i < wp; i += kFastThreads) {
             const int lx0 = i * 4 - off0;
             uint32_t m = 0;
@@ -172,18 +144,19 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     __syncthreads();
 
     const int tmin = G.minTh, tini = G.iniTh;
-    const int lane = threadIdx.x & 31;
     const int g0 = off0 >> 2, g1 = (off0 + rw + 3) >> 2;            // word columns holding candidate pixels
-    const int ng = g1 - g0;
-    const int wCell = g.wCell;
     const uint32_t* W = reinterpret_cast<const uint32_t*>(tile);
     const int o[16] = {3 * TP, 3 * TP + 1, 2 * TP + 2, TP + 3, 3, -TP + 3, -2 * TP + 2, -3 * TP + 1,
                        -3 * TP, -3 * TP - 1, -2 * TP - 2, -TP - 3, -3, TP - 3, 2 * TP - 2, 3 * TP - 1};
+    uint32_t myGoff = (uint32_t)(warp * groupCapW), myCoff = (uint32_t)(warp * kCornerCapW);
+    asm volatile("" : "+r"(myGoff), "+r"(myCoff));
+    uint16_t* myG = groupLists + myGoff;
+    uint16_t* myC = cornerLists + myCoff;
 
-    // exact score of the listed corners
-    auto scorePass = [&](int n) {
-        for (int i = threadIdx.x; i < n; i += kFastThreads) {
-            const int code = cornerList[i], ly = code >> 10, lx = code & 1023;
+    // exact score of the warp's listed corners
+    auto scoreWarp = [&](int n) {
+        for (int i = lane; i < n; i += 32) {
+            const int code = myC[i], ly = code >> 10, lx = code & 1023;
             const uint8_t* c = tile + (ly + 3) * TP + (lx + off0);
             const int v = c[0];
             int d[16];
@@ -208,30 +181,17 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     };
 
     unsigned long long* out = cand + (size_t)frame * G.candPerFrame + g.candBase;
-    const uint8_t* cornerBytes = reinterpret_cast<const uint8_t*>(cornerBits);
+    int* outCount = candCount + frame * G.nlevels + level;
+    const uint32_t cellKey0 = (uint32_t)(ci * g.nCols + j0);
 
     for (int sweep = 0; sweep < 2; ++sweep) {
         const int th = sweep ? tmin : tini;
-        int nReg = 1, ngMax = ng;                                   // sweep 0: one region, the whole strip
+        uint32_t retry = 0xffffffffu;
         if (sweep) {
-            // the retry set (:1128): cells of this strip that kept nothing at iniTh; each becomes a pass-0 region
-            if (threadIdx.x < 32) {
-                const int j = threadIdx.x;
-                const bool mine = j < nc && sCellCnt[j] == 0;
-                const uint32_t m = __ballot_sync(0xffffffffu, mine);
-                int gFirst = (off0 + j * wCell) >> 2;
-                const int gLast = (off0 + min((j + 1) * wCell, rw) - 1) >> 2;
-                // a group column shared with a retry cell on the left is enumerated by that cell
-                if (j > 0 && ((m >> (j - 1)) & 1u) && ((off0 + j * wCell - 1) >> 2) == gFirst) ++gFirst;
-                const int n = mine ? gLast - gFirst + 1 : 0;
-                const int mx = __reduce_max_sync(0xffffffffu, n);
-                if (mine) { const int slot = __popc(m & ((1u << j) - 1u)); sRegG0[slot] = gFirst; sRegNg[slot] = n; }
-                if (j == 0) { sRetry = m; sNgMax = mx; sGroupN = 0; sCornerN = 0; sSurvN = 0; }
-            }
-            __syncthreads();
-            const uint32_t retry = sRetry;
+            // the retry set (:1128): cells of this strip that kept nothing at iniTh
+            __syncthreads();                                        // every warp's survivors of sweep 0 are flagged
+            retry = __ballot_sync(0xffffffffu, lane < nc && sCellKept[lane] == 0);
             if (!retry || tmin == tini) break;
-            nReg = __popc(retry); ngMax = max(sNgMax, 1);
             for (int i = threadIdx.x; i < wp; i += kFastThreads) {
                 const int lx0 = i * 4 - off0;
                 uint32_t m = 0;
@@ -242,7 +202,6 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
                 }
                 colValid[i] = m;
             }
-            for (int i = threadIdx.x; i < rh * BP; i += kFastThreads) cornerBits[i] = 0;
             if (tmin > tini) {   // scores in [iniTh, minTh) are not corners of this sweep
                 uint32_t* z = reinterpret_cast<uint32_t*>(score);
                 const int nz = (SP * (rh + 2) + 3) / 4;
@@ -252,152 +211,168 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
         }
         const uint32_t T4 = (uint32_t)th * 0x01010101u, nT7 = ~T4 & 0x7f7f7f7fu;
 
-        // ---- pass 0: quick rejection, 4 pixels per step.  A 9-arc contains two adjacent compass pixels, i.e. one of
-        //      {0, 8} and one of {4, 12}, both differing from the centre by more than the threshold. ----
-        auto quick = [&](const uint32_t* c, uint32_t vm, int y, int gw) {
-            const uint32_t v = c[0], up = c[-3 * wp], dn = c[3 * wp];
-            const uint32_t p4 = __funnelshift_r(v, c[1], 24), p12 = __funnelshift_r(c[-1], v, 8);
-            // |p - v| per byte (VABSDIFF4); OR-ing two difference words can only over-estimate their maximum, and the
-            // sign is ignored: a superset of the exact quick test at 13 instructions (pass 1 is exact)
-            const uint32_t dv = __vabsdiffu4(dn, v) | __vabsdiffu4(up, v), dh = __vabsdiffu4(p4, v) | __vabsdiffu4(p12, v);
-            if (gtu4(dv, T4, nT7) & gtu4(dh, T4, nT7) & vm) groupList[atomicAdd(&sGroupN, 1)] = (uint16_t)((y << 10) | gw);   // aggregated per warp by the compiler
-        };
-        if (!sweep) {
-            // whole strip: a warp per row, a lane per group column (no index arithmetic)
-            for (int y = threadIdx.x >> 5; y < rh; y += kFastThreads / 32) {
-                const uint32_t* crow = W + (y + 3) * wp;
-                for (int gw = g0 + lane; gw < g1; gw += 32) quick(crow + gw, colValid[gw], y, gw);
-            }
-        } else {
-            // retry cells only: flat enumeration of (region, row, group column)
-            const int perReg = rh * ngMax;
-            const uint32_t rcpPer = 0xffffffffu / (uint32_t)perReg + 1u, rcpNgMax = 0xffffffffu / (uint32_t)ngMax + 1u;   // exact below 65536
-            for (int i = threadIdx.x; i < nReg * perReg; i += kFastThreads) {
-                const int reg = (int)__umulhi((uint32_t)i, rcpPer), rem = i - reg * perReg;
-                const int y = (int)__umulhi((uint32_t)rem, rcpNgMax), k = rem - y * ngMax;
-                if (k >= sRegNg[reg]) continue;
-                const int gw = sRegG0[reg] + k;
-                const uint32_t vm = colValid[gw];
-                if (vm) quick(W + (y + 3) * wp + gw, vm, y, gw);
+        // ---- pass 0: quick rejection, 4 pixels per lane step.  A 9-arc contains two adjacent compass pixels, i.e. one
+        //      of {0, 8} and one of {4, 12}, both differing from the centre by more than the threshold. ----
+        int gcnt = 0;
+        const int nSteps = (g1 - g0 + 31) >> 5;
+        for (int y = warp; y < rh; y += nW) {
+            const uint32_t* c = W + (y + 3) * wp + g0 + lane;      // branch-free steps: lanes past g1 read inside the
+            const uint32_t* cv = colValid + g0 + lane;              // shared-memory block and are masked by vm = 0
+            const uint32_t code0 = (uint32_t)(y << 10) | (uint32_t)(g0 + lane);
+            #pragma unroll 1
+            for (int k = 0; k < nSteps; ++k, c += 32, cv += 32) {
+                const uint32_t vm = (g0 + lane + 32 * k < g1) ? *cv : 0u;
+                const uint32_t v = c[0], up = c[-3 * wp], dn = c[3 * wp];
+                const uint32_t p4 = __funnelshift_r(v, c[1], 24), p12 = __funnelshift_r(c[-1], v, 8);
+                // |p - v| per byte (VABSDIFF4); OR-ing two difference words can only over-estimate their maximum, and
+                // the sign is ignored: a superset of the exact quick test (pass 1 is exact)
+                const uint32_t dv = __vabsdiffu4(dn, v) | __vabsdiffu4(up, v), dh = __vabsdiffu4(p4, v) | __vabsdiffu4(p12, v);
+                const bool pass = (gtu4(dv, T4, nT7) & gtu4(dh, T4, nT7) & vm) != 0;
+                const uint32_t m = __ballot_sync(0xffffffffu, pass);
+                if (pass) myG[gcnt + __popc(m & ltMask)] = (uint16_t)(code0 + 32 * k);
+                gcnt += __popc(m);
             }
         }
-        __syncthreads();
-        const int nG = sGroupN;
+        __syncwarp();
 
-        // ---- pass 1: full test of the surviving groups in batches; corners go to the list and the corner bitmap ----
-        int flushes = 0, lastN = 0;
-        for (int gb = 0; gb < nG; gb += kGroupBatch) {
-            const int gEnd = min(nG, gb + kGroupBatch);
-            for (int ib = gb; ib < gEnd; ib += kFastThreads) {
-                const int i = ib + threadIdx.x;
-                uint32_t nib = 0; int y = 0, lx0 = 0;
-                if (i < gEnd) {
-                    const int code = groupList[i], gw = code & 1023;
-                    y = code >> 10; lx0 = gw * 4 - off0;
-                    const uint32_t* c = W + (y + 3) * wp + gw;
-                    uint32_t a[7][3];
-                    #pragma unroll
-                    for (int r = 0; r < 7; ++r) { a[r][0] = c[(r - 3) * wp - 1]; a[r][1] = c[(r - 3) * wp]; a[r][2] = c[(r - 3) * wp + 1]; }
-                    const uint32_t v = a[3][1];
-                    const uint32_t hi = __vaddus4(v, T4), lo = __vsubus4(v, T4);    // min(v + t, 255), max(v - t, 0) per byte
-                    const uint32_t nh7 = ~hi & 0x7f7f7f7fu, lo7 = lo & 0x7f7f7f7fu;
-                    uint32_t p[16];
-                    p[0] = a[6][1];                                   // ( 0, 3)
-                    p[1] = __funnelshift_r(a[6][1], a[6][2], 8);      // ( 1, 3)
-                    p[2] = __funnelshift_r(a[5][1], a[5][2], 16);     // ( 2, 2)
-                    p[3] = __funnelshift_r(a[4][1], a[4][2], 24);     // ( 3, 1)
-                    p[4] = __funnelshift_r(a[3][1], a[3][2], 24);     // ( 3, 0)
-                    p[5] = __funnelshift_r(a[2][1], a[2][2], 24);     // ( 3,-1)
-                    p[6] = __funnelshift_r(a[1][1], a[1][2], 16);     // ( 2,-2)
-                    p[7] = __funnelshift_r(a[0][1], a[0][2], 8);      // ( 1,-3)
-                    p[8] = a[0][1];                                   // ( 0,-3)
-                    p[9] = __funnelshift_r(a[0][0], a[0][1], 24);     // (-1,-3)
-                    p[10] = __funnelshift_r(a[1][0], a[1][1], 16);    // (-2,-2)
-                    p[11] = __funnelshift_r(a[2][0], a[2][1], 8);     // (-3,-1)
-                    p[12] = __funnelshift_r(a[3][0], a[3][1], 8);     // (-3, 0)
-                    p[13] = __funnelshift_r(a[4][0], a[4][1], 8);     // (-3, 1)
-                    p[14] = __funnelshift_r(a[5][0], a[5][1], 16);    // (-2, 2)
-                    p[15] = __funnelshift_r(a[6][0], a[6][1], 24);    // (-1, 3)
-                    uint32_t f[16];
-                    #pragma unroll
-                    for (int k = 0; k < 16; ++k) f[k] = gtu4(p[k], hi, nh7);
-                    uint32_t corner = nineOfSixteen(f);
-                    #pragma unroll
-                    for (int k = 0; k < 16; ++k) f[k] = ltu4(p[k], lo, lo7);
-                    corner = (corner | nineOfSixteen(f)) & colValid[gw];
-                    nib = ((corner >> 7) & 1u) | ((corner >> 14) & 2u) | ((corner >> 21) & 4u) | ((corner >> 28) & 8u);
+        // ---- pass 1: full test of the warp's groups; corners go to the warp's list, scored in bulk ----
+        int ccnt = 0, flushes = 0;
+        for (int ib = 0; ib < gcnt; ib += 32) {
+            const int i = ib + lane;
+            uint32_t nib = 0; int y = 0, lx0 = 0;
+            if (i < gcnt) {
+                const int code = myG[i], gw = code & 1023;
+                y = code >> 10; lx0 = gw * 4 - off0;
+                const uint32_t* c = W + (y + 3) * wp + gw;
+                uint32_t a[7][3];
+                #pragma unroll
+                for (int r = 0; r < 7; ++r) { a[r][0] = c[(r - 3) * wp - 1]; a[r][1] = c[(r - 3) * wp]; a[r][2] = c[(r - 3) * wp + 1]; }
+                const uint32_t v = a[3][1];
+                const uint32_t hi = __vaddus4(v, T4), lo = __vsubus4(v, T4);    // min(v + t, 255), max(v - t, 0) per byte
+                const uint32_t nh7 = ~hi & 0x7f7f7f7fu, cl = (lo & 0x7f7f7f7fu) + 0x7f7f7f7fu;
+                uint32_t p[16];
+                p[0] = a[6][1];                                   // ( 0, 3)
+                p[1] = __funnelshift_r(a[6][1], a[6][2], 8);      // ( 1, 3)
+                p[2] = __funnelshift_r(a[5][1], a[5][2], 16);     // ( 2, 2)
+                p[3] = __funnelshift_r(a[4][1], a[4][2], 24);     // ( 3, 1)
+                p[4] = __funnelshift_r(a[3][1], a[3][2], 24);     // ( 3, 0)
+                p[5] = __funnelshift_r(a[2][1], a[2][2], 24);     // ( 3,-1)
+                p[6] = __funnelshift_r(a[1][1], a[1][2], 16);     // ( 2,-2)
+                p[7] = __funnelshift_r(a[0][1], a[0][2], 8);      // ( 1,-3)
+                p[8] = a[0][1];                                   // ( 0,-3)
+                p[9] = __funnelshift_r(a[0][0], a[0][1], 24);     // (-1,-3)
+                p[10] = __funnelshift_r(a[1][0], a[1][1], 16);    // (-2,-2)
+                p[11] = __funnelshift_r(a[2][0], a[2][1], 8);     // (-3,-1)
+                p[12] = __funnelshift_r(a[3][0], a[3][1], 8);     // (-3, 0)
+                p[13] = __funnelshift_r(a[4][0], a[4][1], 8);     // (-3, 1)
+                p[14] = __funnelshift_r(a[5][0], a[5][1], 16);    // (-2, 2)
+                p[15] = __funnelshift_r(a[6][0], a[6][1], 24);    // (-1, 3)
+                // brighter: p > hi, darker: p < lo, per byte in bit 7; the two compares share p & 0x7f7f7f7f:
+                //   p > hi : carry of (p & 7f) + (~hi & 7f) decides when the top bits agree
+                //   p < lo : carry of (lo & 7f) + 7f - (p & 7f) likewise (no borrow between bytes)
+                uint32_t fb[16], fd[16];
+                #pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    const uint32_t p7 = p[k] & 0x7f7f7f7fu;
+                    const uint32_t xb = p7 + nh7, xd = cl - p7;
+                    fb[k] = (p[k] & ~hi) | (~(p[k] ^ hi) & xb);
+                    fd[k] = (lo & ~p[k]) | (~(p[k] ^ lo) & xd);
                 }
-                const uint32_t m = __ballot_sync(0xffffffffu, nib != 0);
-                if (m) {
-                    // few lanes hold corners in scene-like frames: direct shared atomics; dense warps use the scan
-                    int slot = 0;
-                    if (__popc(m) <= 6) { if (nib) slot = atomicAdd(&sCornerN, __popc(nib)); }
-                    else slot = warpAppend(&sCornerN, __popc(nib));
-                    if (nib) {
-                        #pragma unroll
-                        for (int b = 0; b < 4; ++b)
-                            if ((nib >> b) & 1u) cornerList[slot++] = (uint16_t)((y << 10) | (lx0 + b));
-                        // the 4 pixels may straddle two bitmap words
-                        const int lxa = max(lx0, 0);
-                        const uint32_t bitsA = (lx0 >= 0 ? nib : nib >> (-lx0));
-                        const int wA = y * BP + (lxa >> 5), sh = lxa & 31;
-                        atomicOr(&cornerBits[wA], bitsA << sh);
-                        if (sh > 28 && (bitsA >> (32 - sh))) atomicOr(&cornerBits[wA + 1], bitsA >> (32 - sh));
+                const uint32_t corner = (nineOfSixteen(fb) | nineOfSixteen(fd)) & colValid[gw];
+                nib = ((corner >> 7) & 1u) | ((corner >> 14) & 2u) | ((corner >> 21) & 4u) | ((corner >> 28) & 8u);
+            }
+            if (__any_sync(0xffffffffu, nib != 0)) {
+                #pragma unroll
+                for (int b = 0; b < 4; ++b) {                       // list order is free: bit plane by bit plane
+                    const bool on = (nib >> b) & 1u;
+                    const uint32_t m = __ballot_sync(0xffffffffu, on);
+                    if (on) myC[ccnt + __popc(m & ltMask)] = (uint16_t)((y << 10) | (lx0 + b));
+                    ccnt += __popc(m);
+                }
+                if (ccnt > kCornerCapW - 128) {                     // the next step could overflow the list
+                    __syncwarp();
+                    scoreWarp(ccnt);
+                    __syncwarp();
+                    ccnt = 0; ++flushes;
+                }
+            }
+        }
+        __syncwarp();
+        scoreWarp(ccnt);
+        __syncthreads();                                            // the score map of this sweep is complete
+
+        // ---- nms (strict >, 8 neighbours, zero outside the pixel's own cell) + emit ----
+        auto nmsEmit = [&](bool have, int ly, int lx) {
+            bool keep = false; int s = 0, cj = 0, cx = 0;
+            if (have) {
+                const uint8_t* r = score + (ly + 1) * SP + (lx + 1);
+                s = r[0];
+                cj = colCell[lx]; cx = lx - cj * wCell;
+                keep = s > r[-SP] && s > r[SP];
+                if (cx > 0) keep = keep && s > r[-1] && s > r[-SP - 1] && s > r[SP - 1];
+                if (cx < wCell - 1) keep = keep && s > r[1] && s > r[-SP + 1] && s > r[SP + 1];
+            }
+            const uint32_t m = __ballot_sync(0xffffffffu, keep);
+            if (!m) return;
+            int base = 0;
+            if (lane == 0) base = atomicAdd(outCount, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (keep) {
+                if (!sweep) sCellKept[cj] = 1;
+                const uint32_t key = ((cellKey0 + (uint32_t)cj) << 12) | (uint32_t)(ly << 6) | (uint32_t)cx;
+                out[base + __popc(m & ltMask)] = ((unsigned long long)((uint32_t)s << 24) << 32) | key; // hi = score<<24 | node(0), lo = key
+            }
+        };
+        if (!flushes) {
+            for (int ib = 0; ib < ccnt; ib += 32) {
+                const int i = ib + lane;
+                const int code = i < ccnt ? myC[i] : 0;
+                nmsEmit(i < ccnt, code >> 10, code & 1023);
+            }
+        } else {
+            // the list was dropped on the way: walk the score map of the warp's rows (dense frames only)
+            const int nWords = (rw + 1 + 3) >> 2;
+            for (int y = warp; y < rh; y += nW) {
+                const uint32_t* srow = reinterpret_cast<const uint32_t*>(score + (y + 1) * SP);
+                for (int wb = 0; wb < nWords; wb += 32) {
+                    const int wi = wb + lane;
+                    const uint32_t word = wi < nWords ? srow[wi] : 0;
+                    if (!__any_sync(0xffffffffu, word != 0)) continue;
+                    #pragma unroll
+                    for (int b = 0; b < 4; ++b) {
+                        const int lx = wi * 4 + b - 1;
+                        bool have = ((word >> (8 * b)) & 0xffu) >= (uint32_t)th && lx >= 0 && lx < rw;
+                        if (have && sweep) have = (retry >> colCell[lx]) & 1u;
+                        nmsEmit(have, y, lx);
                     }
                 }
             }
-            __syncthreads();
-            if (sCornerN > kCornerCap - 4 * kGroupBatch || gEnd == nG) {   // uniform: score in bulk before the list could overflow
-                const int n = sCornerN;
-                lastN = n; ++flushes;
-                scorePass(n);
-                __syncthreads();
-                if (threadIdx.x == 0) sCornerN = 0;
-                __syncthreads();
-            }
         }
+    }
+}
 
-        // ---- nms (strict >, 8 neighbours, zero outside the pixel's own cell): one list entry per thread step when the
-        //      list still holds every corner of the sweep, else 8 bitmap columns per step ----
-        auto nmsOne = [&](int ly, int lx) {
-            const uint8_t* r = score + (ly + 1) * SP + (lx + 1);
-            const int s = r[0];
-            const int cj = colCell[lx], cx = lx - cj * wCell;
-            bool keep = s > r[-SP] && s > r[SP];
-            if (cx > 0) keep = keep && s > r[-1] && s > r[-SP - 1] && s > r[SP - 1];
-            if (cx < wCell - 1) keep = keep && s > r[1] && s > r[-SP + 1] && s > r[SP + 1];
-            if (keep) {
-                survList[atomicAdd(&sSurvN, 1)] = ((uint32_t)s << 16) | (uint32_t)(ly << 10) | (uint32_t)lx;
-                if (!sweep) atomicAdd(&sCellCnt[cj], 1);
+// Host side of the strip table: one entry per non-empty strip of a frame (skipped cells :1094,:1112 have an empty
+// candidate region and get no CTA).
+void buildFastStrips(const GeomSet& g, std::vector<StripDesc>& out)
+{
+    out.clear();
+    for (int l = 0; l < g.nlevels; ++l) {
+        const LevelGeom& q = g.lv[l];
+        for (int ci = 0; ci < q.nRows; ++ci)
+            for (int seg = 0; seg < q.segsPerRow; ++seg) {
+                const int j0 = seg * q.cellsPerSeg, j1 = std::min(j0 + q.cellsPerSeg, q.nCols);
+                const int cx0 = kEdge + j0 * q.wCell, cy0 = kEdge + ci * q.hCell;
+                const int cx1 = std::min(kEdge + j1 * q.wCell, q.w - kEdge), cy1 = std::min(cy0 + q.hCell, q.h - kEdge);
+                const int rw = cx1 - cx0, rh = cy1 - cy0;
+                if (rw <= 0 || rh <= 0 || j1 <= j0) continue;
+                const int nc = (rw + q.wCell - 1) / q.wCell;         // cells that own at least one candidate column
+                StripDesc d;
+                d.a = (uint32_t)l | ((uint32_t)nc << 8) | ((uint32_t)ci << 16);
+                d.b = (uint32_t)j0 | ((uint32_t)cx0 << 16);
+                d.c = (uint32_t)cy0 | ((uint32_t)rw << 16);
+                d.d = (uint32_t)rh | ((65536u / (uint32_t)q.wCell + 1u) << 16);
+                out.push_back(d);
             }
-        };
-        if (flushes == 1) {
-            for (int i = threadIdx.x; i < lastN; i += kFastThreads) { const int code = cornerList[i]; nmsOne(code >> 10, code & 1023); }
-        } else if (flushes > 1) {
-            for (int it = threadIdx.x; it < rh * BP * 4; it += kFastThreads) {
-                uint32_t bits = cornerBytes[it];
-                if (!bits) continue;
-                const int ly = (int)__umulhi((uint32_t)it, rcpBP4), lxb = (it - ly * BP * 4) << 3;
-                while (bits) {
-                    const int b = __ffs(bits) - 1;
-                    bits &= bits - 1;
-                    nmsOne(ly, lxb + b);
-                }
-            }
-        }
-        __syncthreads();
-        // ---- emit ----
-        const int nS = sSurvN;
-        if (threadIdx.x == 0) sBase = nS ? atomicAdd(&candCount[frame * G.nlevels + level], nS) : 0;
-        __syncthreads();
-        for (int i = threadIdx.x; i < nS; i += kFastThreads) {
-            const uint32_t r = survList[i];
-            const int s = r >> 16, ly = (r >> 10) & 63, lx = r & 1023;
-            const int cj = colCell[lx], cx = lx - cj * wCell;
-            const uint32_t key = ((uint32_t)(ci * g.nCols + j0 + cj) << 12) | (uint32_t)(ly << 6) | (uint32_t)cx;
-            out[sBase + i] = ((unsigned long long)((uint32_t)s << 24) << 32) | key; // hi = score<<24 | node(0), lo = key
-        }
-        __syncthreads();
     }
 }
 
@@ -408,26 +383,22 @@ int launchFast(Ctx* c, int frame0, int batch)
     stageBegin(c, ST_FAST);
     ORBX_CUDA(c, cudaMemsetAsync(c->dCandCount + (size_t)frame0 * g.nlevels, 0, sizeof(int) * (size_t)batch * g.nlevels, c->stream));
     int launches = 0;
-    if (g.stripsPerFrame > 0) {
+    if (c->nStrips > 0) {
         const int TP = g.fastTilePitch, TR = g.fastTileRows, SP = g.fastScorePitch;
-        const int maxRh = TR - 6, BP = (SP + 31) / 32;
-        // corner list, then the group list whose space is reused as the survivor list (u32 records)
-        size_t listBytes = sizeof(uint16_t) * (size_t)kCornerCap +
-                           std::max(sizeof(uint16_t) * (size_t)maxRh * ((SP >> 2) + 2), sizeof(uint32_t) * (size_t)fastSurvivorCap(SP, maxRh));
-        listBytes = (listBytes + 3) & ~(size_t)3;
-        size_t smem = (size_t)TP * TR + (size_t)SP * (maxRh + 2);
-        smem += sizeof(uint32_t) * ((size_t)maxRh * BP + (size_t)(TP >> 2));
-        smem += listBytes + (size_t)SP;
+        const int maxRh = TR - 6;
+        const int nW = c->fastThreads / 32;
+        const int groupCapW = (((maxRh + nW - 1) / nW) * ((SP >> 2) + 2) + 1) & ~1;   // rows of a warp x group columns of a row
+        size_t smem = (size_t)TP * TR + (size_t)SP * (maxRh + 2) + sizeof(uint32_t) * (size_t)(TP >> 2);
+        smem += sizeof(uint16_t) * (size_t)nW * (kCornerCapW + groupCapW) + (size_t)SP;
         smem = (smem + 127) & ~(size_t)127;
-        const uint32_t rcpBP4 = 0xffffffffu / (uint32_t)(BP * 4) + 1u;
-        dim3 grid(g.stripsPerFrame, batch);
+        dim3 grid(c->nStrips, batch);
         auto go = [&](auto kern, int threads, size_t* configured) -> int {
             if (smem > 48 * 1024 && smem > *configured) {
                 ORBX_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
                 *configured = smem;
             }
-            kern<<<grid, dim3(threads), smem, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr,
-                                                           c->dCand, c->dCandCount, TP, TR, SP, (int)listBytes, rcpBP4);
+            kern<<<grid, dim3(threads), smem, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dStrips,
+                                                           c->dCand, c->dCandCount, TP, TR, SP, groupCapW);
             return ORBX_OK;
         };
         static size_t cfg256 = 0, cfg128 = 0;

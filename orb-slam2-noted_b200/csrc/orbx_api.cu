@@ -206,6 +206,19 @@ static int configure(Ctx* c, int w, int h)
         ORBX_CUDA(c, cudaMemcpy(c->dTapY[l], ty.data(), sizeof(ResizeTap) * ty.size(), cudaMemcpyHostToDevice));
     }
     ORBX_CUDA(c, cudaMemcpy(c->dGeom, &g, sizeof(g), cudaMemcpyHostToDevice));
+    {
+        std::vector<StripDesc> strips;
+        buildFastStrips(g, strips);
+        if ((int)strips.size() > c->stripCap) {
+            if (c->dStrips) cudaFree(c->dStrips);
+            c->dStrips = nullptr; c->stripCap = 0;
+            ORBX_CUDA(c, cudaMalloc(&c->dStrips, sizeof(StripDesc) * strips.size()));
+            c->stripCap = (int)strips.size();
+        }
+        if (!strips.empty())
+            ORBX_CUDA(c, cudaMemcpy(c->dStrips, strips.data(), sizeof(StripDesc) * strips.size(), cudaMemcpyHostToDevice));
+        c->nStrips = (int)strips.size();
+    }
     c->curW = w; c->curH = h; c->geomStamp++;
     return ORBX_OK;
 }
@@ -279,7 +292,7 @@ void orbx_destroy(orbx_ctx* h)
     for (cudaEvent_t e : c->eventPool) cudaEventDestroy(e);
     freeGeometry(c);
     void* ptrs[] = {c->dGeom, c->dPyr, c->dBlur, c->dCand, c->dCandCount, c->dSel, c->dSelCount, c->dErr,
-                    c->dOutKp, c->dOutDesc, c->dOutN, c->dIn, c->dScratch, c->dTensorMaps};
+                    c->dOutKp, c->dOutDesc, c->dOutN, c->dIn, c->dScratch, c->dTensorMaps, c->dStrips};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->hPinned) cudaFreeHost(c->hPinned);
     if (c->hMatch) cudaFreeHost(c->hMatch);

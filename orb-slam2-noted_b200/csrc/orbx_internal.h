@@ -40,6 +40,10 @@ struct LevelGeom {
     int stripBase, segsPerRow, cellsPerSeg; // FAST strips: one cell-row, split into segments of whole cells
 };
 
+// One FAST strip (k_fast.cu): a = level | cells<<8 | cellRow<<16, b = firstCell | x0<<16, c = y0 | width<<16,
+// d = height | (65536 / wCell + 1)<<16; x0/y0 = first candidate pixel in level coordinates.
+struct StripDesc { uint32_t a, b, c, d; };
+
 struct ResizeTap { uint16_t s; int16_t c0, c1; uint16_t pad; }; // source index + 11-bit fixed-point weights
 
 struct GeomSet {            // what kernels need, uploaded to constant memory on (re)configuration
@@ -63,7 +67,7 @@ struct Ctx {
     cudaEvent_t evJoin = nullptr;
     std::vector<cudaEvent_t> evIn, evDone;
     cudaEvent_t evFence = nullptr;                // orders a new call's H2D after the previous call's kernels
-    int fastThreads = 256, fastSegW = 320;         // FAST strip shape: threads per CTA, max candidate columns per strip
+    int fastThreads = 128, fastSegW = 320;         // FAST strip shape: threads per CTA, max candidate columns per strip
     int chunk = 64;                                // frames per pipeline chunk (stages of a chunk stay L2-resident)
     int nfeatures = 0, nlevels = 0, iniTh = 0, minTh = 0;
     float scaleFactor = 0;
@@ -77,6 +81,7 @@ struct Ctx {
     GeomSet* dGeom = nullptr;            // device copy (global memory; kernels read via __ldg / constant cache)
     ResizeTap* dTapX[kMaxLevels] = {};   // per-level tables (level l = taps from level l-1)
     ResizeTap* dTapY[kMaxLevels] = {};
+    StripDesc* dStrips = nullptr; int nStrips = 0, stripCap = 0;   // FAST strip table of the current geometry
     int geomStamp = 0;                   // bumped whenever the geometry / arenas change
     void* dTensorMaps = nullptr; int mapsStamp = -1;   // CUtensorMap[2][kMaxLevels] of the blurred / pyramid planes (k_describe.cu)
     bool resizeWordOk[kMaxLevels] = {};  // level l: every 4-pixel group reads <= 8 source bytes from an aligned word (k_pyramid.cu fast path)
@@ -135,6 +140,7 @@ int ensureMatchPinned(Ctx* c, size_t bytes);
 // frames [frame0, frame0 + batch) of the current batch
 int launchPyramid(Ctx* c, int frame0, int batch);
 int launchFast(Ctx* c, int frame0, int batch);
+void buildFastStrips(const GeomSet& g, std::vector<StripDesc>& out);
 int launchOctree(Ctx* c, int frame0, int batch);
 int launchBlur(Ctx* c, int frame0, int batch);
 int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN);
