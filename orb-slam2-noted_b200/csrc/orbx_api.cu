@@ -430,8 +430,20 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
     const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
     uint8_t* d0 = c->dPyr + g.lv[0].planeOff;
     const size_t dp = (size_t)g.lv[0].pitch;
-    if (inDev) { c->lvl0 = imgs; c->lvl0Pitch = stride; c->lvl0FrameStride = frame_stride; }
+    // a device image whose rows are not 16-byte aligned (e.g. a dense 1241-wide frame) is repacked into the arena once:
+    // the bulk-copy staging of every stage needs aligned rows, and one extra pass over level 0 is cheaper than byte loads
+    const bool repack = inDev && ((((size_t)imgs) | stride | (batch > 1 ? frame_stride : 0)) & 15) != 0;
+    if (inDev && !repack) { c->lvl0 = imgs; c->lvl0Pitch = stride; c->lvl0FrameStride = frame_stride; }
     else { c->lvl0 = d0; c->lvl0Pitch = dp; c->lvl0FrameStride = dp * hgt; }
+    if (repack) {
+        if (frame_stride == stride * (size_t)hgt || batch == 1) {
+            ORBX_CUDA(c, cudaMemcpy2DAsync(d0, dp, imgs, stride, (size_t)w, (size_t)hgt * batch, cudaMemcpyDeviceToDevice, c->stream));
+        } else {
+            for (int b = 0; b < batch; ++b)
+                ORBX_CUDA(c, cudaMemcpy2DAsync(d0 + (size_t)b * dp * hgt, dp, imgs + (size_t)b * frame_stride, stride, (size_t)w,
+                                               (size_t)hgt, cudaMemcpyDeviceToDevice, c->stream));
+        }
+    }
     c->lastBatch = batch;
 
     orbx_keypoint* dK = kps; uint8_t* dD = desc; int* dN = n_out;
