@@ -183,6 +183,16 @@ int orbx_search_by_projection(orbx_ctx* ctx, const orbx_proj_query* q, int nq, c
                               const uint8_t* occupied, int mode_flags, int th_dist, float nnratio,
                               int check_orientation, int flags, int32_t* assign, int* nmatches);
 
+/* ---- monocular initialisation.  Replaces ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:580-748 (window search of
+ *      F1's level-0 keypoints around vbPrevMatched in F2's grid, best/second-best ratio test, distance-masked candidates,
+ *      stolen matches, rotation histogram).  prev_xy = vbPrevMatched as n1 (x, y) pairs, updated in place for the matched
+ *      keypoints (:741-744); matches12[i1] = F2 index or -1 (vnMatches12).  With ORBX_IN_DEVICE every input pointer
+ *      (prev_xy included) is a device pointer; ORBX_OUT_DEVICE leaves matches12 on the device. ---- */
+int orbx_search_for_initialization(orbx_ctx* ctx, const orbx_keypoint* keys1, const uint8_t* desc1, int n1, float* prev_xy,
+                                   const orbx_keypoint* keys2, const uint8_t* desc2, int n2, const orbx_grid* g,
+                                   int window, float nnratio, int check_orientation, int flags, int32_t* matches12,
+                                   int* nmatches);
+
 /* ---- stereo.  Replaces Frame::ComputeStereoMatches, src/Frame.cc:831-1128.  left/right are the two extractor
  *      contexts whose LAST orbx_extract call produced the keypoints (their pyramids are read on the device). ---- */
 int orbx_stereo_match(orbx_ctx* left, orbx_ctx* right, int frame, const orbx_keypoint* kps_l, const uint8_t* desc_l,

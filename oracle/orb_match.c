@@ -447,6 +447,146 @@ int orc_search_by_projection_frame(const orc_projpoint* pts, int npts, const orc
     return nmatches;
 }
 
+/* SearchByProjection(Frame& Cur, KeyFrame*, set& sAlreadyFound, th, ORBdist): src/ORBmatcher.cc:1922-2065 (relocalisation),
+ * after the caller's projection and PredictScale (:1949-1978): pts[i] = (u, v, level = nPredictedLevel,
+ * angle = pKF->mvKeysUn[i].angle, desc).  Window levels [level-1, level+1] (:1985), keypoints already holding a
+ * MapPoint skipped (:2000), best only, accept <= orb_dist (:2015), rotation histogram on the frame index (:2033). */
+int orc_search_by_projection_reloc(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
+                                   const float* scale, const orc_grid* g, const int32_t* cell_off, const int32_t* cell_idx,
+                                   const uint8_t* occupied_in, float th, int orb_dist, int check_ori, int32_t* assign)
+{
+    ivec hist[HISTO_LENGTH]; memset(hist, 0, sizeof(hist));
+    uint8_t* occ = (uint8_t*)malloc((size_t)(n > 0 ? n : 1));
+    int32_t* cand = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    for (int j = 0; j < n; ++j) { occ[j] = occupied_in ? occupied_in[j] : 0; assign[j] = -1; }
+    int nmatches = 0;
+    for (int i = 0; i < npts; ++i) {
+        const orc_projpoint* p = &pts[i];
+        const int lvl = p->level;
+        const float radius = th * scale[lvl];
+        const int nc = orc_features_in_area(keys, g, cell_off, cell_idx, p->u, p->v, radius, lvl - 1, lvl + 1, cand);
+        if (nc == 0) continue;
+        int best = 256, bestIdx2 = -1;
+        for (int k = 0; k < nc; ++k) {
+            const int i2 = cand[k];
+            if (occ[i2]) continue;
+            const int dist = orc_descriptor_distance(p->desc, desc + 32 * (size_t)i2);
+            if (dist < best) { best = dist; bestIdx2 = i2; }
+        }
+        if (best <= orb_dist) {
+            assign[bestIdx2] = i; occ[bestIdx2] = 1;
+            ++nmatches;
+            if (check_ori) ipush(&hist[rot_bin(p->angle, keys[bestIdx2].angle)], bestIdx2);
+        }
+    }
+    if (check_ori) {
+        int cnt[HISTO_LENGTH], i1, i2, i3;
+        for (int i = 0; i < HISTO_LENGTH; ++i) cnt[i] = hist[i].n;
+        orc_three_maxima(cnt, HISTO_LENGTH, &i1, &i2, &i3);
+        for (int i = 0; i < HISTO_LENGTH; ++i) {
+            if (i == i1 || i == i2 || i == i3) continue;
+            for (int j = 0; j < hist[i].n; ++j) { assign[hist[i].v[j]] = -1; --nmatches; }
+        }
+    }
+    for (int i = 0; i < HISTO_LENGTH; ++i) free(hist[i].v);
+    free(occ); free(cand);
+    return nmatches;
+}
+
+/* SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th): src/ORBmatcher.cc:431-560 (loop closing), after the
+ * caller's Sim3 projection, depth / viewing-angle gates and PredictScale (:470-512): pts[i] = (u, v, level, desc).
+ * KeyFrame::GetFeaturesInArea has no level filter (src/KeyFrame.cc:794-838); keypoints with vpMatched set are skipped
+ * (:531), levels outside [level-1, level] are skipped (:536), best only, accept <= TH_LOW (:552), no histogram. */
+int orc_search_by_projection_sim3(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
+                                  const float* scale, const orc_grid* g, const int32_t* cell_off, const int32_t* cell_idx,
+                                  const uint8_t* occupied_in, int th, int32_t* assign)
+{
+    uint8_t* occ = (uint8_t*)malloc((size_t)(n > 0 ? n : 1));
+    int32_t* cand = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    for (int j = 0; j < n; ++j) { occ[j] = occupied_in ? occupied_in[j] : 0; assign[j] = -1; }
+    int nmatches = 0;
+    for (int i = 0; i < npts; ++i) {
+        const orc_projpoint* p = &pts[i];
+        const int lvl = p->level;
+        const float radius = th * scale[lvl];
+        const int nc = orc_features_in_area(keys, g, cell_off, cell_idx, p->u, p->v, radius, -1, -1, cand);
+        if (nc == 0) continue;
+        int best = 256, bestIdx = -1;
+        for (int k = 0; k < nc; ++k) {
+            const int idx = cand[k];
+            if (occ[idx]) continue;
+            const int kpLevel = keys[idx].octave;
+            if (kpLevel < lvl - 1 || kpLevel > lvl) continue;
+            const int dist = orc_descriptor_distance(p->desc, desc + 32 * (size_t)idx);
+            if (dist < best) { best = dist; bestIdx = idx; }
+        }
+        if (best <= TH_LOW) { assign[bestIdx] = i; occ[bestIdx] = 1; ++nmatches; }
+    }
+    free(occ); free(cand);
+    return nmatches;
+}
+
+/* SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize): src/ORBmatcher.cc:580-748.
+ * keys1/desc1: F1.mvKeysUn / mDescriptors; prev_xy[2*i1..]: vbPrevMatched[i1]; the grid is F2's.  Only level-0 keypoints
+ * of F1 search (:609), F2 candidates are level 0 inside the window (:615); a candidate whose current match is at least as
+ * close is skipped (:643); best/second-best, accept best <= TH_LOW (:660) and best < second * nnratio (:664); a candidate
+ * taken before is stolen (:667-671).  The histogram keeps the i1 of every accepted match, stolen or not (:692), exactly
+ * like the reference, so the three maxima are computed on those counts.  matches12[i1] = i2 or -1; prev_xy is updated
+ * for the matched i1 (:741-744). */
+int orc_search_for_initialization(const orc_keypoint* keys1, const uint8_t* desc1, int n1, float* prev_xy,
+                                  const orc_keypoint* keys2, const uint8_t* desc2, int n2, const orc_grid* g,
+                                  const int32_t* cell_off, const int32_t* cell_idx, int window, float nnratio, int check_ori,
+                                  int32_t* matches12)
+{
+    ivec hist[HISTO_LENGTH]; memset(hist, 0, sizeof(hist));
+    int* matched_dist = (int*)malloc(sizeof(int) * (size_t)(n2 > 0 ? n2 : 1));
+    int32_t* matches21 = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n2 > 0 ? n2 : 1));
+    int32_t* cand = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n2 > 0 ? n2 : 1));
+    for (int j = 0; j < n2; ++j) { matched_dist[j] = INT_MAX; matches21[j] = -1; }
+    for (int i = 0; i < n1; ++i) matches12[i] = -1;
+    int nmatches = 0;
+    for (int i1 = 0; i1 < n1; ++i1) {
+        const int level1 = keys1[i1].octave;
+        if (level1 > 0) continue;
+        const int nc = orc_features_in_area(keys2, g, cell_off, cell_idx, prev_xy[2 * i1], prev_xy[2 * i1 + 1], (float)window,
+                                            level1, level1, cand);
+        if (nc == 0) continue;
+        int best = INT_MAX, best2 = INT_MAX, bestIdx2 = -1;
+        for (int k = 0; k < nc; ++k) {
+            const int i2 = cand[k];
+            const int dist = orc_descriptor_distance(desc1 + 32 * (size_t)i1, desc2 + 32 * (size_t)i2);
+            if (matched_dist[i2] <= dist) continue;
+            if (dist < best) { best2 = best; best = dist; bestIdx2 = i2; }
+            else if (dist < best2) best2 = dist;
+        }
+        if (best <= TH_LOW) {
+            if ((float)best < (float)best2 * nnratio) {
+                if (matches21[bestIdx2] >= 0) { matches12[matches21[bestIdx2]] = -1; --nmatches; }
+                matches12[i1] = bestIdx2; matches21[bestIdx2] = i1; matched_dist[bestIdx2] = best;
+                ++nmatches;
+                if (check_ori) ipush(&hist[rot_bin(keys1[i1].angle, keys2[bestIdx2].angle)], i1);
+            }
+        }
+    }
+    if (check_ori) {
+        int cnt[HISTO_LENGTH], a, b, c;
+        for (int i = 0; i < HISTO_LENGTH; ++i) cnt[i] = hist[i].n;
+        orc_three_maxima(cnt, HISTO_LENGTH, &a, &b, &c);
+        for (int i = 0; i < HISTO_LENGTH; ++i) {
+            if (i == a || i == b || i == c) continue;
+            for (int j = 0; j < hist[i].n; ++j) {
+                const int idx1 = hist[i].v[j];
+                if (matches12[idx1] >= 0) { matches12[idx1] = -1; --nmatches; }
+            }
+        }
+    }
+    for (int i1 = 0; i1 < n1; ++i1)
+        if (matches12[i1] >= 0) { prev_xy[2 * i1] = keys2[matches12[i1]].x; prev_xy[2 * i1 + 1] = keys2[matches12[i1]].y; }
+    for (int i = 0; i < HISTO_LENGTH; ++i) free(hist[i].v);
+    free(matched_dist); free(matches21); free(cand);
+    return nmatches;
+}
+
 /* ---------------- Frame::ComputeStereoMatches: src/Frame.cc:831-1128 ----------------
  * pyrL/pyrR: un-bordered level images packed back to back (level l at lvl_off[l], size lvl_w[l] x lvl_h[l]). */
 typedef struct { int d, i; } distidx;

@@ -117,6 +117,16 @@ int orc_search_by_projection_frame(const orc_projpoint* pts, int npts, const orc
                                    const float* uright, const float* scale, const orc_grid* g, const int32_t* cell_off,
                                    const int32_t* cell_idx, const uint8_t* occupied_in, float th, int motion, int check_ori,
                                    int32_t* assign);
+int orc_search_by_projection_reloc(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
+                                   const float* scale, const orc_grid* g, const int32_t* cell_off, const int32_t* cell_idx,
+                                   const uint8_t* occupied_in, float th, int orb_dist, int check_ori, int32_t* assign); /* :1922-2065 */
+int orc_search_by_projection_sim3(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
+                                  const float* scale, const orc_grid* g, const int32_t* cell_off, const int32_t* cell_idx,
+                                  const uint8_t* occupied_in, int th, int32_t* assign); /* :431-560 */
+int orc_search_for_initialization(const orc_keypoint* keys1, const uint8_t* desc1, int n1, float* prev_xy,
+                                  const orc_keypoint* keys2, const uint8_t* desc2, int n2, const orc_grid* g,
+                                  const int32_t* cell_off, const int32_t* cell_idx, int window, float nnratio, int check_ori,
+                                  int32_t* matches12); /* :580-748 */
 int orc_stereo_matches(const orc_keypoint* kL, const uint8_t* dL, int N, const orc_keypoint* kR, const uint8_t* dR, int Nr,
                        const uint8_t* pyrL, const uint8_t* pyrR, const int* lvl_w, const int* lvl_h, const size_t* lvl_off,
                        const float* scale, const float* inv_scale, float mbf, float mb, float* uRight, float* depth);

@@ -417,6 +417,140 @@ projResolveKernel(const orbx_proj_query* __restrict__ q, int nq, GridDev g, cons
     if (tid == 0) *nmOut = total;
 }
 
+// ---------------- SearchForInitialization (src/ORBmatcher.cc:580-748) ----------------
+// F1 keypoint i1 (level 0 only, :609) searches the square window of half-size windowSize around vbPrevMatched[i1] among
+// the level-0 keypoints of F2 (:615).  The reference's loop is sequential with a DISTANCE-dependent mask (a candidate
+// whose current match is at least as close is skipped, :643) and later queries steal matches (:667-671):
+//   I1 initQueryKernel     every F1 keypoint becomes a window query (radius -1 = no candidates for levels > 0)
+//   P2 projScanKernel      (shared with SearchByProjection) the four smallest (distance, visit rank) keys per query
+//   I2 initResolveKernel   one warp replays the queries in order: a query is decided from its four keys when two of
+//                          them survive the mask (or the list is complete), otherwise the warp rescans its window with
+//                          the mask applied; then the rotation histogram (every accepted i1 votes, stolen or not, :692)
+__global__ void initQueryKernel(const orbx_keypoint* __restrict__ keys1, const uint4* __restrict__ desc1,
+                                const float2* __restrict__ prev, int n1, float window, orbx_proj_query* __restrict__ q)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n1) return;
+    const orbx_keypoint k = keys1[i];
+    const float2 p = prev[i];
+    uint4* o = reinterpret_cast<uint4*>(q + i);
+    o[0] = make_uint4(__float_as_uint(p.x), __float_as_uint(p.y), __float_as_uint(k.octave > 0 ? -1.0f : window), 0u);
+    o[1] = make_uint4(__float_as_uint(k.angle), 0u, 0u, 0u);     // min_level = max_level = 0: level-0 candidates only
+    o[2] = desc1[2 * i]; o[3] = desc1[2 * i + 1];
+}
+
+__global__ void __launch_bounds__(32)
+initResolveKernel(const orbx_proj_query* __restrict__ q, int n1, GridDev g, const int* __restrict__ off, const int* __restrict__ idx,
+                  const float4* __restrict__ cinfo, const uint4* __restrict__ dsort, const uint4* __restrict__ topKey,
+                  const int2* __restrict__ meta, const orbx_keypoint* __restrict__ keys2, int n2, float nnratio, int checkOri,
+                  int* __restrict__ binOf, int* __restrict__ matches12, float2* __restrict__ prev, int* __restrict__ nmOut)
+{
+    extern __shared__ uint32_t smemI[];
+    int* m21 = reinterpret_cast<int*>(smemI);                      // vnMatches21 over visit ranks j
+    uint16_t* md = reinterpret_cast<uint16_t*>(m21 + n2);           // vMatchedDistance (0xffff = INT_MAX)
+    __shared__ int sHist[kHistoP];
+    __shared__ int keep[3];
+    const int lane = threadIdx.x;
+    for (int j = lane; j < n2; j += 32) { m21[j] = -1; md[j] = 0xffffu; }
+    for (int i = lane; i < n1; i += 32) { matches12[i] = -1; binOf[i] = -1; }
+    if (lane < kHistoP) sHist[lane] = 0;
+    __syncwarp();
+    const uint4 none = make_uint4(kNoKeyP, kNoKeyP, kNoKeyP, kNoKeyP);
+    for (int i0 = 0; i0 < n1; i0 += 32) {
+        uint4 eL = none; int cntL = 0;
+        if (i0 + lane < n1) { eL = topKey[i0 + lane]; cntL = meta[i0 + lane].x; }
+        const int kEnd = min(32, n1 - i0);
+        for (int k = 0; k < kEnd; ++k) {
+            const int i = i0 + k;
+            uint32_t e[4];
+            e[0] = __shfl_sync(0xffffffffu, eL.x, k); e[1] = __shfl_sync(0xffffffffu, eL.y, k);
+            e[2] = __shfl_sync(0xffffffffu, eL.z, k); e[3] = __shfl_sync(0xffffffffu, eL.w, k);
+            const int cnt = __shfl_sync(0xffffffffu, cntL, k);
+            // the unmasked best of the whole window is a lower bound of the masked best (:660)
+            if (e[0] == kNoKeyP || (int)(e[0] >> kJBits) > 50) continue;
+            uint32_t b1 = kNoKeyP, b2 = kNoKeyP;
+            #pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                if (e[t] == kNoKeyP) continue;
+                const uint32_t d = e[t] >> kJBits, j = e[t] & kJMask;
+                if ((uint32_t)md[j] <= d) continue;
+                if (b1 == kNoKeyP) b1 = e[t]; else if (b2 == kNoKeyP) b2 = e[t];
+            }
+            if (b2 == kNoKeyP && cnt > 4) {
+                // fewer than two listed keys survive the mask and the window holds more candidates: exact rescan
+                const QueryGeom s = geomOf(q[i]);
+                const Window w = windowOf(g, s.x, s.y, s.r);
+                uint32_t k1 = kNoKeyP, k2 = kNoKeyP;
+                if (!w.empty) {
+                    const uint4* qd = reinterpret_cast<const uint4*>(q[i].desc);
+                    const uint4 a0 = qd[0], a1 = qd[1];
+                    for (int ix = w.c0; ix <= w.c1; ++ix) {
+                        const int jb = off[ix * g.rows + w.r0], je = off[ix * g.rows + w.r1 + 1];
+                        for (int j = jb + lane; j < je; j += 32) {
+                            int oct;
+                            if (!candPass(cinfo[j], s, 0, oct)) continue;
+                            const uint32_t d = (uint32_t)hamming256(a0, a1, dsort[2 * j], dsort[2 * j + 1]);
+                            if ((uint32_t)md[j] <= d) continue;
+                            const uint32_t key = (d << kJBits) | (uint32_t)j;
+                            k2 = min(k2, max(k1, key)); k1 = min(k1, key);
+                        }
+                    }
+                }
+                #pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const uint32_t c1 = __shfl_xor_sync(0xffffffffu, k1, o), c2 = __shfl_xor_sync(0xffffffffu, k2, o);
+                    const uint32_t lo = min(k1, c1), hi = max(k1, c1);
+                    k2 = min(hi, min(k2, c2)); k1 = lo;
+                }
+                b1 = k1; b2 = k2;
+            }
+            if (b1 == kNoKeyP) continue;
+            const int best = (int)(b1 >> kJBits);
+            const float best2 = b2 == kNoKeyP ? 2147483648.0f : (float)(int)(b2 >> kJBits);   // (float)INT_MAX
+            if (best <= 50 && (float)best < __fmul_rn(best2, nnratio)) {            // :660, :664
+                const int j = (int)(b1 & kJMask);
+                if (lane == 0) {
+                    const int old = m21[j];
+                    if (old >= 0) matches12[old] = -1;                              // :667-671
+                    matches12[i] = j; m21[j] = i; md[j] = (uint16_t)best;
+                    if (checkOri) {
+                        const int bin = rotBinP(q[i].angle, keys2[idx[j]].angle);   // :683-692
+                        binOf[i] = bin; sHist[bin] += 1;
+                    }
+                }
+                __syncwarp();
+            }
+        }
+    }
+    __syncwarp();
+    if (checkOri && lane == 0) {    // ComputeThreeMaxima :2076-2118
+        int max1 = 0, max2 = 0, max3 = 0, i1 = -1, i2 = -1, i3 = -1;
+        for (int i = 0; i < kHistoP; ++i) {
+            const int s = sHist[i];
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; i3 = i2; i2 = i1; i1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; i3 = i2; i2 = i; }
+            else if (s > max3) { max3 = s; i3 = i; }
+        }
+        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { i2 = -1; i3 = -1; }
+        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) i3 = -1;
+        keep[0] = i1; keep[1] = i2; keep[2] = i3;
+    }
+    __syncwarp();
+    int cnt = 0;
+    for (int i = lane; i < n1; i += 32) {
+        int j = matches12[i];
+        if (j >= 0 && checkOri) {
+            const int bin = binOf[i];
+            if (bin != keep[0] && bin != keep[1] && bin != keep[2]) j = -1;         // :706-722
+        }
+        int f = -1;
+        if (j >= 0) { f = idx[j]; prev[i] = make_float2(keys2[f].x, keys2[f].y); ++cnt; }   // :741-744
+        matches12[i] = f;
+    }
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    if (lane == 0) *nmOut = cnt;
+}
+
 struct BumpP { size_t off = 0; size_t take(size_t b) { const size_t o = off; off += (b + 255) & ~(size_t)255; return o; } };
 
 static int launchGridBuild(Ctx* c, const orbx_keypoint* dKeys, int n, const GridDev& g, int* dCellTmp, int* dTmpIdx, int* dOff, int* dIdx,
@@ -554,5 +688,89 @@ extern "C" int orbx_search_by_projection(orbx_ctx* h, const orbx_proj_query* q, 
         nm = HO[0];
     }
     if (nmatches) *nmatches = nm;
+    return ORBX_OK;
+}
+
+extern "C" int orbx_search_for_initialization(orbx_ctx* h, const orbx_keypoint* keys1, const uint8_t* desc1, int n1, float* prev_xy,
+                                              const orbx_keypoint* keys2, const uint8_t* desc2, int n2, const orbx_grid* g,
+                                              int window, float nnratio, int check_ori, int flags, int32_t* matches12,
+                                              int* nmatches)
+{
+    if (!h || !g || n1 < 0 || n2 < 0 || g->cols < 1 || g->rows < 1 || (n1 > 0 && (!keys1 || !desc1 || !prev_xy || !matches12)) ||
+        (n2 > 0 && (!keys2 || !desc2)))
+        return ORBX_E_INVALID;
+    Ctx* c = &h->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    if (nmatches) *nmatches = 0;
+    if (n1 == 0) return ORBX_OK;
+    const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
+    if (n2 == 0) {
+        if (outDev) ORBX_CUDA(c, cudaMemsetAsync(matches12, 0xff, sizeof(int) * (size_t)n1, c->stream));
+        else for (int i = 0; i < n1; ++i) matches12[i] = -1;
+        return ORBX_OK;
+    }
+    const int ncell = g->cols * g->rows;
+    const size_t resolveSmem = (size_t)n2 * 6 + 16;
+    if (resolveSmem > 200 * 1024 || n2 >= (1 << kJBits)) return ORBX_E_CAPACITY;
+    BumpP B;
+    const size_t oK1 = B.take(sizeof(orbx_keypoint) * (size_t)n1), oD1 = B.take((size_t)32 * n1), oP = B.take(sizeof(float2) * (size_t)n1),
+                 oK2 = B.take(sizeof(orbx_keypoint) * (size_t)n2), oD2 = B.take((size_t)32 * n2);
+    const size_t inBytes = B.off;
+    const size_t oQ = B.take(sizeof(orbx_proj_query) * (size_t)n1), oCell = B.take(sizeof(int) * (size_t)n2),
+                 oTmp = B.take(sizeof(int) * (size_t)n2), oOff = B.take(sizeof(int) * (size_t)(ncell + 1)),
+                 oIdx = B.take(sizeof(int) * (size_t)n2), oInfo = B.take(sizeof(float4) * (size_t)n2), oSort = B.take((size_t)32 * n2),
+                 oTop = B.take(sizeof(uint4) * (size_t)n1), oMeta = B.take(sizeof(int2) * (size_t)n1), oBin = B.take(sizeof(int) * (size_t)n1),
+                 oOut = B.take(sizeof(int) * (size_t)(n1 + 1));
+    int rc = ensureScratch(c, B.off);
+    if (rc) return rc;
+    const size_t outBytes = sizeof(int) * (size_t)(n1 + 1);
+    rc = ensureMatchPinned(c, inBytes + outBytes + sizeof(float2) * (size_t)n1);
+    if (rc) return rc;
+    uint8_t* S = (uint8_t*)c->dScratch;
+    const orbx_keypoint *dK1 = keys1, *dK2 = keys2;
+    const uint4 *dD1 = (const uint4*)desc1, *dD2 = (const uint4*)desc2;
+    float2* dPrev = (float2*)prev_xy;
+    stageBegin(c, ST_H2D);
+    if (!inDev) {
+        uint8_t* H = c->hMatch;
+        memcpy(H + oK1, keys1, sizeof(orbx_keypoint) * (size_t)n1); memcpy(H + oD1, desc1, (size_t)32 * n1);
+        memcpy(H + oP, prev_xy, sizeof(float2) * (size_t)n1);
+        memcpy(H + oK2, keys2, sizeof(orbx_keypoint) * (size_t)n2); memcpy(H + oD2, desc2, (size_t)32 * n2);
+        ORBX_CUDA(c, cudaMemcpyAsync(S, H, inBytes, cudaMemcpyHostToDevice, c->stream));
+        dK1 = (const orbx_keypoint*)(S + oK1); dD1 = (const uint4*)(S + oD1); dPrev = (float2*)(S + oP);
+        dK2 = (const orbx_keypoint*)(S + oK2); dD2 = (const uint4*)(S + oD2);
+    }
+    stageEnd(c, ST_H2D, 0);
+    const GridDev gd = {g->min_x, g->min_y, g->inv_w, g->inv_h, g->cols, g->rows};
+    int* dOut = (int*)(S + oOut);
+    int* dM12 = outDev ? matches12 : dOut;
+    stageBegin(c, ST_MATCH);
+    rc = launchGridBuild(c, dK2, n2, gd, (int*)(S + oCell), (int*)(S + oTmp), (int*)(S + oOff), (int*)(S + oIdx), dD2, nullptr, nullptr,
+                         (float4*)(S + oInfo), (uint4*)(S + oSort), nullptr, 0);
+    if (rc) return rc;
+    initQueryKernel<<<(n1 + 255) / 256, 256, 0, c->stream>>>(dK1, dD1, dPrev, n1, (float)window, (orbx_proj_query*)(S + oQ));
+    projScanKernel<<<(n1 + kScanWarps - 1) / kScanWarps, 32 * kScanWarps, 0, c->stream>>>((orbx_proj_query*)(S + oQ), n1, gd, (int*)(S + oOff),
+                                                       (float4*)(S + oInfo), (uint4*)(S + oSort), 0, (uint4*)(S + oTop), (int2*)(S + oMeta));
+    if (resolveSmem > 40 * 1024)
+        ORBX_CUDA(c, cudaFuncSetAttribute(initResolveKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)resolveSmem));
+    initResolveKernel<<<1, 32, resolveSmem, c->stream>>>((orbx_proj_query*)(S + oQ), n1, gd, (int*)(S + oOff), (int*)(S + oIdx),
+                                                         (float4*)(S + oInfo), (uint4*)(S + oSort), (uint4*)(S + oTop), (int2*)(S + oMeta),
+                                                         dK2, n2, nnratio, check_ori ? 1 : 0, (int*)(S + oBin), dM12, dPrev, dOut + n1);
+    stageEnd(c, ST_MATCH, 3);
+    ORBX_CUDA(c, cudaGetLastError());
+    int* HO = (int*)(c->hMatch + inBytes);
+    if (!outDev) {
+        ORBX_CUDA(c, cudaMemcpyAsync(HO, dOut, outBytes, cudaMemcpyDeviceToHost, c->stream));
+        float2* HP = (float2*)(c->hMatch + inBytes + outBytes);
+        if (!inDev) ORBX_CUDA(c, cudaMemcpyAsync(HP, dPrev, sizeof(float2) * (size_t)n1, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+        memcpy(matches12, HO, sizeof(int) * (size_t)n1);
+        if (!inDev) memcpy(prev_xy, HP, sizeof(float2) * (size_t)n1);
+        if (nmatches) *nmatches = HO[n1];
+    } else {
+        ORBX_CUDA(c, cudaMemcpyAsync(HO, dOut + n1, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (nmatches) *nmatches = HO[0];
+    }
     return ORBX_OK;
 }

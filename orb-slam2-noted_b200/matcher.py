@@ -58,6 +58,7 @@ def _mlib():
     L.orbx_match_bow_batch.argtypes = [vp, ci, ci, ctypes.POINTER(ctypes.POINTER(_BowSide)), ctypes.POINTER(ctypes.POINTER(_BowSide)), vp, cf, ci, ci, vp, vp]
     L.orbx_assign_grid.argtypes = [vp, vp, ci, ctypes.POINTER(_Grid), ci, vp, vp]
     L.orbx_search_by_projection.argtypes = [vp, vp, ci, vp, vp, vp, ci, ctypes.POINTER(_Grid), vp, ci, ci, cf, ci, ci, vp, ip]
+    L.orbx_search_for_initialization.argtypes = [vp, vp, vp, ci, vp, vp, vp, ci, ctypes.POINTER(_Grid), ci, cf, ci, ci, vp, ip]
     L.orbx_stereo_match.argtypes = [vp, vp, ci, vp, vp, ci, vp, vp, ci, cf, cf, ci, vp, vp, ip]
     _ready = True
     return L
@@ -211,6 +212,22 @@ class ORBmatcher:
                                                ctypes.byref(n))
         _chk(self._ex, rc, "orbx_search_by_projection")
         return out, n.value
+
+
+    def SearchForInitialization(self, f1, f2, prev_matched, grid, window_size=100, grid_dims=(FRAME_GRID_COLS, FRAME_GRID_ROWS)):
+        """ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:580-748).  f1, f2: FrameView (mvKeysUn, mDescriptors);
+        prev_matched: (N1, 2) float32 vbPrevMatched; grid: F2's (mnMinX, mnMinY, widthInv, heightInv).
+        Returns (vnMatches12, nmatches, updated vbPrevMatched)."""
+        prev = np.ascontiguousarray(prev_matched, np.float32).copy()
+        assert prev.shape == (f1.N, 2)
+        g = _Grid(float(grid[0]), float(grid[1]), float(grid[2]), float(grid[3]), grid_dims[0], grid_dims[1])
+        out = np.empty(max(f1.N, 1), np.int32)
+        n = ctypes.c_int()
+        rc = _mlib().orbx_search_for_initialization(self._ex._h, _np(f1.keys), _np(f1.desc), f1.N, _np(prev), _np(f2.keys), _np(f2.desc),
+                                                    f2.N, ctypes.byref(g), int(window_size), self.mfNNratio, int(self.mbCheckOrientation),
+                                                    0, _np(out), ctypes.byref(n))
+        _chk(self._ex, rc, "orbx_search_for_initialization")
+        return out[:f1.N], n.value, prev
 
 
 def assign_features_to_grid(ex, keys, grid, grid_dims=(FRAME_GRID_COLS, FRAME_GRID_ROWS)):

@@ -185,6 +185,9 @@ def _mlib():
     L.orc_features_in_area.argtypes = [vp, ctypes.POINTER(Grid), vp, vp, cf, cf, cf, ci, ci, vp]
     L.orc_search_by_projection_points.argtypes = [vp, ci, vp, vp, ci, vp, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, cf, vp]
     L.orc_search_by_projection_frame.argtypes = [vp, ci, vp, vp, ci, vp, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, ci, ci, vp]
+    L.orc_search_by_projection_reloc.argtypes = [vp, ci, vp, vp, ci, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, ci, ci, vp]
+    L.orc_search_by_projection_sim3.argtypes = [vp, ci, vp, vp, ci, vp, ctypes.POINTER(Grid), vp, vp, vp, ci, vp]
+    L.orc_search_for_initialization.argtypes = [vp, vp, ci, vp, vp, vp, ci, ctypes.POINTER(Grid), vp, vp, ci, cf, ci, vp]
     L.orc_stereo_matches.argtypes = [vp, vp, ci, vp, vp, ci, vp, vp, vp, vp, vp, vp, vp, cf, cf, vp, vp]
     L.orc_hamming_best2.argtypes = [vp, vp, vp, vp, vp, vp, ci, vp, vp, vp, vp]
     L._match_ready = True
@@ -315,6 +318,47 @@ def search_by_projection(pts, keys, desc, uright, scale, grid, occupied, th, nnr
                                                    _p(scale), ctypes.byref(g), _p(off), _p(idx), None if occ is None else _p(occ),
                                                    th, motion, int(check_ori), _p(out))
     return out, n
+
+
+def _proj_common(pts, keys, desc, scale, grid, occupied):
+    pts = np.ascontiguousarray(pts)
+    keys = np.ascontiguousarray(keys)
+    desc = np.ascontiguousarray(desc, np.uint8)
+    scale = np.ascontiguousarray(scale, np.float32)
+    off, idx = assign_grid(keys, grid)
+    idx = np.ascontiguousarray(np.concatenate([idx, np.zeros(1, np.int32)]))
+    occ = None if occupied is None else np.ascontiguousarray(occupied, np.uint8)
+    return pts, keys, desc, scale, off, idx, Grid(*grid), occ, np.empty(len(keys), np.int32)
+
+
+def search_by_projection_reloc(pts, keys, desc, scale, grid, occupied, th, orb_dist, check_ori=True):
+    """SearchByProjection(Frame, KeyFrame, sAlreadyFound, th, ORBdist) (a17), after the caller's projection."""
+    pts, keys, desc, scale, off, idx, g, occ, out = _proj_common(pts, keys, desc, scale, grid, occupied)
+    n = _mlib().orc_search_by_projection_reloc(_p(pts), len(pts), _p(keys), _p(desc), len(keys), _p(scale), ctypes.byref(g), _p(off),
+                                               _p(idx), None if occ is None else _p(occ), th, int(orb_dist), int(check_ori), _p(out))
+    return out, n
+
+
+def search_by_projection_sim3(pts, keys, desc, scale, grid, occupied, th):
+    """SearchByProjection(KeyFrame, Scw, vpPoints, vpMatched, th) (a18), after the caller's Sim3 projection."""
+    pts, keys, desc, scale, off, idx, g, occ, out = _proj_common(pts, keys, desc, scale, grid, occupied)
+    n = _mlib().orc_search_by_projection_sim3(_p(pts), len(pts), _p(keys), _p(desc), len(keys), _p(scale), ctypes.byref(g), _p(off),
+                                              _p(idx), None if occ is None else _p(occ), int(th), _p(out))
+    return out, n
+
+
+def search_for_initialization(keys1, desc1, prev_xy, keys2, desc2, grid, window, nnratio, check_ori=True):
+    """SearchForInitialization (src/ORBmatcher.cc:580-748).  Returns (matches12, nmatches, updated prev_xy)."""
+    keys1 = np.ascontiguousarray(keys1); keys2 = np.ascontiguousarray(keys2)
+    desc1 = np.ascontiguousarray(desc1, np.uint8); desc2 = np.ascontiguousarray(desc2, np.uint8)
+    prev = np.ascontiguousarray(prev_xy, np.float32).copy()
+    off, idx = assign_grid(keys2, grid)
+    idx = np.ascontiguousarray(np.concatenate([idx, np.zeros(1, np.int32)]))
+    g = Grid(*grid)
+    out = np.empty(max(len(keys1), 1), np.int32)
+    n = _mlib().orc_search_for_initialization(_p(keys1), _p(desc1), len(keys1), _p(prev), _p(keys2), _p(desc2), len(keys2),
+                                              ctypes.byref(g), _p(off), _p(idx), int(window), nnratio, int(check_ori), _p(out))
+    return out[:len(keys1)], n, prev
 
 
 def stereo_matches(kL, dL, kR, dR, pyrL, pyrR, sizes, scale, inv_scale, mbf, mb):

@@ -188,6 +188,53 @@ def test_search_by_projection_matches_oracle(P, ctx, seed, n, nq):
         assert nw == ng and nw > 0
 
 
+@pytest.mark.parametrize("seed,n,nq", [(11, 1000, 600), (12, 3000, 3500), (13, 200, 40)])
+def test_search_by_projection_reloc_and_sim3_match_oracle(P, ctx, seed, n, nq):
+    """(a17) SearchByProjection(Frame, KeyFrame, sAlreadyFound, th, ORBdist) src/ORBmatcher.cc:1922-2065 and
+    (a18) SearchByProjection(KeyFrame, Scw, vpPoints, vpMatched, th) :431-560 through the shared window matcher."""
+    keys, desc, uright, occupied, pts = proj_scene(P, seed, n, nq)
+    p = O.params(1000)
+    scale = np.array(p.scale[:8], np.float32)
+    grid = (0.0, 0.0, np.float32(64) / np.float32(640), np.float32(48) / np.float32(480))
+    fv = P.FrameView(desc, keys, None, uright)
+
+    def queries(th):
+        q = np.zeros(nq, P.PROJ_QUERY_DTYPE)
+        q["u"], q["v"], q["angle"], q["desc"] = pts["u"], pts["v"], pts["angle"], pts["desc"]
+        q["radius"] = (np.float32(th) * scale[pts["level"]]).astype(np.float32)
+        return q
+    for th, orb_dist, ori in ((10.0, 100, True), (3.0, 64, True), (10.0, 100, False)):
+        want, nw = O.search_by_projection_reloc(pts, keys, desc, scale, grid, occupied, th, orb_dist, ori)
+        q = queries(th)
+        q["min_level"], q["max_level"] = pts["level"] - 1, pts["level"] + 1
+        got, ng = P.ORBmatcher(ctx, 0.9, ori).SearchByProjection(fv, q, grid, orb_dist, occupied, check_uright=False)
+        assert np.array_equal(want, got), (th, orb_dist, int((want != got).sum()), nw, ng)
+        assert nw == ng and nw > 0
+    for th in (10, 4):
+        want, nw = O.search_by_projection_sim3(pts, keys, desc, scale, grid, occupied, th)
+        q = queries(th)
+        q["min_level"], q["max_level"] = pts["level"] - 1, pts["level"]
+        got, ng = P.ORBmatcher(ctx, 0.9, False).SearchByProjection(fv, q, grid, 50, occupied, check_uright=False)
+        assert np.array_equal(want, got), (th, int((want != got).sum()), nw, ng)
+        assert nw == ng and nw > 0
+
+
+@pytest.mark.parametrize("seed,n1,n2,window,nnratio,ori,dup", [(1, 400, 380, 100, 0.9, True, 0.3), (2, 1000, 1100, 100, 0.9, True, 0.3),
+                                                              (3, 300, 300, 30, 0.8, False, 0.6), (4, 3000, 3000, 100, 0.9, True, 0.8),
+                                                              (5, 50, 0, 100, 0.9, True, 0.0), (6, 2000, 2100, 200, 0.95, True, 0.9)])
+def test_search_for_initialization_matches_oracle(P, ctx, seed, n1, n2, window, nnratio, ori, dup):
+    """SearchForInitialization src/ORBmatcher.cc:580-748 (distance-masked candidates, stolen matches, histogram quirk)."""
+    from test_oracle_match import init_scene
+    grid = (0.0, 0.0, np.float32(64) / np.float32(640), np.float32(48) / np.float32(480))
+    k1, d1, prev, k2, d2 = init_scene(seed, n1, max(n2, 1), dup=dup)
+    k2, d2 = k2[:n2], d2[:n2]
+    want, nw, wprev = O.search_for_initialization(k1, d1, prev, k2, d2, grid, window, nnratio, ori)
+    got, ng, gprev = P.ORBmatcher(ctx, nnratio, ori).SearchForInitialization(P.FrameView(d1, k1), P.FrameView(d2, k2), prev, grid, window)
+    assert np.array_equal(want, got), (int((want != got).sum()), nw, ng)
+    assert nw == ng and (n2 == 0 or nw > 10)
+    assert np.array_equal(wprev.view(np.uint32), gprev.view(np.uint32))
+
+
 @pytest.mark.parametrize("w,h,nf,seed", [(752, 480, 1200, 3), (1241, 376, 2000, 4)])
 def test_stereo_matches_oracle(P, w, h, nf, seed):
     left, right = synth.stereo_pair(seed, w, h)

@@ -174,3 +174,195 @@ def test_features_in_area_vs_bruteforce():
                 sel &= keys["octave"] <= hi
         # the grid window (floor/ceil of the cell span) always covers the square, so the sets must agree
         assert sorted(out[:n]) == list(np.flatnonzero(sel))
+
+
+# ---- independent (naive) restatements of the window matchers: brute-force candidate sets in grid iteration order ----
+def py_features_in_area(keys, grid, x, y, r, lo, hi):
+    """Frame::GetFeaturesInArea (src/Frame.cc:590-671): candidates in column-major cell order, insertion order inside a cell."""
+    min_x, min_y, inv_w, inv_h = (np.float32(v) for v in grid)
+    x, y, r = np.float32(x), np.float32(y), np.float32(r)
+    c0 = max(0, int(np.floor(np.float32(np.float32(x - min_x) - r) * inv_w)))
+    if c0 >= 64:
+        return []
+    c1 = min(63, int(np.ceil(np.float32(np.float32(x - min_x) + r) * inv_w)))
+    if c1 < 0:
+        return []
+    r0 = max(0, int(np.floor(np.float32(np.float32(y - min_y) - r) * inv_h)))
+    if r0 >= 48:
+        return []
+    r1 = min(47, int(np.ceil(np.float32(np.float32(y - min_y) + r) * inv_h)))
+    if r1 < 0:
+        return []
+    # cell of every keypoint (AssignFeaturesToGrid, src/Frame.cc:398-422 / PosInGrid :682-698)
+    px = np.round(np.float32(keys["x"] - min_x) * inv_w).astype(np.int64)
+    py = np.round(np.float32(keys["y"] - min_y) * inv_h).astype(np.int64)
+    out = []
+    for ix in range(c0, c1 + 1):
+        for iy in range(r0, r1 + 1):
+            for j in np.flatnonzero((px == ix) & (py == iy)):
+                o = int(keys["octave"][j])
+                if lo > 0 or hi >= 0:
+                    if o < lo or (hi >= 0 and o > hi):
+                        continue
+                if abs(np.float32(keys["x"][j] - x)) < r and abs(np.float32(keys["y"][j] - y)) < r:
+                    out.append(int(j))
+    return out
+
+
+def py_rot_bin(a1, a2):
+    rot = np.float32(a1) - np.float32(a2)
+    if rot < 0:
+        rot = np.float32(rot + np.float32(360.0))
+    b = int(round_half_away(np.float32(rot * np.float32(30 / 360.0))))
+    return 0 if b == 30 else b
+
+
+def round_half_away(x):
+    return np.floor(x + 0.5) if x >= 0 else np.ceil(x - 0.5)
+
+
+def py_prune_hist(hist, assign_clear):
+    i1, i2, i3 = py_three_maxima([len(h) for h in hist])
+    removed = 0
+    for i, h in enumerate(hist):
+        if i in (i1, i2, i3):
+            continue
+        for j in h:
+            removed += assign_clear(j)
+    return removed
+
+
+def py_window_search(pts, keys, desc, scale, grid, occupied, th, levels, accept, check_ori, level_in_area=True):
+    occ = list(occupied) if occupied is not None else [0] * len(keys)
+    assign = [-1] * len(keys)
+    hist = [[] for _ in range(30)]
+    n = 0
+    for i, p in enumerate(pts):
+        lvl = int(p["level"])
+        lo, hi = levels(lvl)
+        r = np.float32(np.float32(th) * scale[lvl])
+        cand = py_features_in_area(keys, grid, p["u"], p["v"], r, lo, hi) if level_in_area else \
+            [j for j in py_features_in_area(keys, grid, p["u"], p["v"], r, -1, -1)]
+        best, bi = 256, -1
+        for j in cand:
+            if occ[j]:
+                continue
+            if not level_in_area and not (lo <= keys["octave"][j] <= hi):
+                continue
+            d = hamming(p["desc"], desc[j])
+            if d < best:
+                best, bi = d, j
+        if best <= accept:
+            assign[bi] = i; occ[bi] = 1; n += 1
+            if check_ori:
+                hist[py_rot_bin(p["angle"], keys["angle"][bi])].append(bi)
+    if check_ori:
+        def clear(j):
+            assign[j] = -1
+            return 1
+        n -= py_prune_hist(hist, clear)
+    return assign, n
+
+
+def _window_scene(seed, n, nq):
+    rng = np.random.default_rng(seed)
+    keys = synth.keypoints(seed, n, 640, 480, dtype=O.KP_DTYPE)
+    desc = synth.descriptors(seed + 1, n)
+    src = rng.integers(0, n, nq)
+    pts = np.zeros(nq, O.PROJ_DTYPE)
+    pts["u"] = keys["x"][src] + rng.normal(0, 3, nq).astype(np.float32)
+    pts["v"] = keys["y"][src] + rng.normal(0, 3, nq).astype(np.float32)
+    pts["u"][:4] = [-30, 900, 100, 320]; pts["v"][:4] = [100, 100, -50, 700]
+    pts["level"] = np.clip(keys["octave"][src] + rng.integers(-1, 2, nq), 0, 7)
+    pts["angle"] = np.mod(keys["angle"][src] + 20 + rng.normal(0, 4, nq), 360).astype(np.float32)
+    pts["desc"] = synth.descriptors(seed + 2, nq, 0.12, desc[src])
+    occupied = (rng.random(n) < 0.1).astype(np.uint8)
+    return keys, desc, pts, occupied
+
+
+def test_search_by_projection_reloc_and_sim3_vs_python():
+    p = O.params(1000)
+    scale = np.array(p.scale[:8], np.float32)
+    grid = (0.0, 0.0, np.float32(64) / np.float32(640), np.float32(48) / np.float32(480))
+    for seed, n, nq in ((5, 500, 300), (6, 900, 700)):
+        keys, desc, pts, occupied = _window_scene(seed, n, nq)
+        for th, orb_dist, ori in ((10.0, 100, True), (3.0, 64, True), (10.0, 100, False)):
+            got, ng = O.search_by_projection_reloc(pts, keys, desc, scale, grid, occupied, th, orb_dist, ori)
+            want, nw = py_window_search(pts, keys, desc, scale, grid, occupied, th, lambda l: (l - 1, l + 1), orb_dist, ori)
+            assert list(got) == want and ng == nw
+        for th in (10, 4):
+            got, ng = O.search_by_projection_sim3(pts, keys, desc, scale, grid, occupied, th)
+            want, nw = py_window_search(pts, keys, desc, scale, grid, occupied, th, lambda l: (l - 1, l), 50, False, level_in_area=False)
+            assert list(got) == want and ng == nw and nw > 0
+
+
+def py_search_for_initialization(keys1, desc1, prev, keys2, desc2, grid, window, nnratio, check_ori):
+    n1, n2 = len(keys1), len(keys2)
+    m12, m21, md = [-1] * n1, [-1] * n2, [2 ** 31 - 1] * n2
+    hist = [[] for _ in range(30)]
+    prev = np.array(prev, np.float32).copy()
+    n = 0
+    for i1 in range(n1):
+        if keys1["octave"][i1] > 0:
+            continue
+        cand = py_features_in_area(keys2, grid, prev[i1, 0], prev[i1, 1], window, 0, 0)
+        best, best2, bi = 2 ** 31 - 1, 2 ** 31 - 1, -1
+        for i2 in cand:
+            d = hamming(desc1[i1], desc2[i2])
+            if md[i2] <= d:
+                continue
+            if d < best:
+                best2, best, bi = best, d, i2
+            elif d < best2:
+                best2 = d
+        if best <= 50 and np.float32(best) < np.float32(np.float32(best2) * np.float32(nnratio)):
+            if m21[bi] >= 0:
+                m12[m21[bi]] = -1; n -= 1
+            m12[i1] = bi; m21[bi] = i1; md[bi] = best; n += 1
+            if check_ori:
+                hist[py_rot_bin(keys1["angle"][i1], keys2["angle"][bi])].append(i1)
+    if check_ori:
+        def clear(i1):
+            if m12[i1] >= 0:
+                m12[i1] = -1
+                return 1
+            return 0
+        n -= py_prune_hist(hist, clear)
+    for i1 in range(n1):
+        if m12[i1] >= 0:
+            prev[i1] = (keys2["x"][m12[i1]], keys2["y"][m12[i1]])
+    return m12, n, prev
+
+
+def init_scene(seed, n1, n2, shift=6.0, dup=0.3):
+    """Two frames of level-0-heavy keypoints: frame 2 = frame 1 moved by a few pixels, descriptors perturbed; a share of
+    duplicated descriptors makes several F1 keypoints compete for (and steal) the same F2 keypoint."""
+    rng = np.random.default_rng(seed)
+    k1 = synth.keypoints(seed, n1, 640, 480, dtype=O.KP_DTYPE)
+    k1["octave"] = np.where(rng.random(n1) < 0.7, 0, k1["octave"])
+    d1 = synth.descriptors(seed + 1, n1)
+    ndup = int(dup * n1)
+    srcd = rng.integers(0, n1, ndup); dstd = rng.integers(0, n1, ndup)
+    d1[dstd] = synth.descriptors(seed + 5, ndup, 0.03, d1[srcd])
+    k1["x"][dstd] = np.clip(k1["x"][srcd] + rng.normal(0, 20, ndup), 0, 639).astype(np.float32)
+    k1["y"][dstd] = np.clip(k1["y"][srcd] + rng.normal(0, 20, ndup), 0, 479).astype(np.float32)
+    src = rng.integers(0, n1, n2)
+    k2 = k1[src].copy()
+    k2["x"] = np.clip(k2["x"] + shift + rng.normal(0, 2, n2), 0, 639).astype(np.float32)
+    k2["y"] = np.clip(k2["y"] + rng.normal(0, 2, n2), 0, 479).astype(np.float32)
+    k2["angle"] = np.mod(k2["angle"] + 10 + rng.normal(0, 5, n2), 360).astype(np.float32)
+    d2 = synth.descriptors(seed + 2, n2, 0.06, d1[src])
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    return k1, d1, prev, k2, d2
+
+
+def test_search_for_initialization_vs_python():
+    grid = (0.0, 0.0, np.float32(64) / np.float32(640), np.float32(48) / np.float32(480))
+    stolen = 0
+    for seed, n1, n2, window, nnratio, ori in ((1, 400, 380, 100, 0.9, True), (2, 600, 700, 100, 0.9, True), (3, 300, 300, 30, 0.8, False)):
+        k1, d1, prev, k2, d2 = init_scene(seed, n1, n2)
+        got, ng, gprev = O.search_for_initialization(k1, d1, prev, k2, d2, grid, window, nnratio, ori)
+        want, nw, wprev = py_search_for_initialization(k1, d1, prev, k2, d2, grid, window, nnratio, ori)
+        assert list(got) == want and ng == nw and nw > 20
+        assert np.array_equal(gprev, wprev)
+        assert ng == sum(1 for x in want if x >= 0)
