@@ -4,6 +4,7 @@
 // tree the real headers are used and this directory is not on the include path.
 #ifndef ORBX_COMPAT_SLAM_FRAME_H
 #define ORBX_COMPAT_SLAM_FRAME_H
+#include <cmath>
 #include <map>
 #include <set>
 #include <vector>
@@ -16,10 +17,19 @@ namespace ORB_SLAM2
 #define FRAME_GRID_ROWS 48
 #define FRAME_GRID_COLS 64
 
+class Frame;
+class KeyFrame;
+
 class MapPoint
 {
 public:
-    MapPoint() : mTrackProjX(0), mTrackProjY(0), mTrackProjXR(0), mbTrackInView(false), mnTrackScaleLevel(0), mTrackViewCos(1), mbBad(false), nObs(1) {}
+    MapPoint() : mTrackProjX(0), mTrackProjY(0), mTrackProjXR(0), mbTrackInView(false), mnTrackScaleLevel(0), mTrackViewCos(1), mbBad(false), nObs(1),
+                 mfMaxDistance(0), mfMinDistance(0) {}
+    float GetMinDistanceInvariance() { return 0.8f * mfMinDistance; }   // src/MapPoint.cc:549-559
+    float GetMaxDistanceInvariance() { return 1.2f * mfMaxDistance; }
+    cv::Mat GetNormal() { return mNormalVector; }
+    int PredictScale(const float& currentDist, KeyFrame* pKF);          // src/MapPoint.cc:584-604
+    int PredictScale(const float& currentDist, Frame* pF);              // :613-631
     bool isBad() { return mbBad; }
     int Observations() { return nObs; }
     cv::Mat GetDescriptor() { return mDescriptor; }
@@ -29,7 +39,7 @@ public:
     int mnTrackScaleLevel;
     float mTrackViewCos;
     // test-side state
-    bool mbBad; int nObs; cv::Mat mDescriptor, mWorldPos;
+    bool mbBad; int nObs; cv::Mat mDescriptor, mWorldPos, mNormalVector; float mfMaxDistance, mfMinDistance;
 };
 
 class Frame
@@ -43,6 +53,7 @@ public:
     std::vector<bool> mvbOutlier;
     DBoW2::FeatureVector mFeatVec;
     std::vector<float> mvScaleFactors;
+    int mnScaleLevels; float mfLogScaleFactor;
     cv::Mat mTcw;
     float mb, mbf;
     static float fx, fy, cx, cy;
@@ -60,6 +71,10 @@ public:
     DBoW2::FeatureVector mFeatVec;
     std::vector<float> mvScaleFactors, mvLevelSigma2;
     float fx, fy, cx, cy;
+    int mnScaleLevels; float mfLogScaleFactor;
+    int mnGridCols, mnGridRows; float mfGridElementWidthInv, mfGridElementHeightInv;
+    int mnMinX, mnMinY, mnMaxX, mnMaxY;
+    bool IsInImage(const float& x, const float& y) const { return (x >= mnMinX && x < mnMaxX && y >= mnMinY && y < mnMaxY); } // src/KeyFrame.cc:841
     std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
     MapPoint* GetMapPoint(const size_t& idx) { return mvpMapPoints[idx]; }
     cv::Mat GetCameraCenter() { return Ow; }
@@ -69,6 +84,16 @@ public:
     std::vector<MapPoint*> mvpMapPoints;
     cv::Mat Ow, Rcw, tcw;
 };
+
+inline int predictScaleImpl(float maxDistance, float currentDist, float logScaleFactor, int nLevels)
+{
+    const float ratio = maxDistance / currentDist;
+    int nScale = (int)ceil(log(ratio) / logScaleFactor);
+    if (nScale < 0) nScale = 0; else if (nScale >= nLevels) nScale = nLevels - 1;
+    return nScale;
+}
+inline int MapPoint::PredictScale(const float& d, KeyFrame* pKF) { return predictScaleImpl(mfMaxDistance, d, pKF->mfLogScaleFactor, pKF->mnScaleLevels); }
+inline int MapPoint::PredictScale(const float& d, Frame* pF) { return predictScaleImpl(mfMaxDistance, d, pF->mfLogScaleFactor, pF->mnScaleLevels); }
 
 } // namespace ORB_SLAM2
 #endif

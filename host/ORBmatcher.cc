@@ -156,14 +156,15 @@ int ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F
 
 namespace {
 int projectionSearch(orbx_ctx* ctx, Frame& F, const std::vector<orbx_proj_query>& q, const std::vector<MapPoint*>& src, int modeFlags,
-                     int thDist, float nnratio, bool checkOri)
+                     int thDist, float nnratio, bool checkOri, bool anyPointOccupies = false)
 {
     std::vector<uint8_t> occupied(F.N, 0), tmp;
-    for (int i = 0; i < F.N; ++i) occupied[i] = F.mvpMapPoints[i] && F.mvpMapPoints[i]->Observations() > 0;   // :136-138
+    for (int i = 0; i < F.N; ++i)                                                                              // :136-138, :2000
+        occupied[i] = F.mvpMapPoints[i] && (anyPointOccupies || F.mvpMapPoints[i]->Observations() > 0);
     const orbx_grid g = {Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, FRAME_GRID_COLS, FRAME_GRID_ROWS};
     std::vector<int32_t> assign(F.N > 0 ? F.N : 1);
     int n = 0;
-    const bool stereo = !F.mvuRight.empty();
+    const bool stereo = !F.mvuRight.empty() && !anyPointOccupies;   // the relocalisation overload has no uright gate
     check(orbx_search_by_projection(ctx, q.data(), (int)q.size(), reinterpret_cast<const orbx_keypoint*>(F.mvKeysUn.data()),
                                     contiguous(F.mDescriptors, tmp), stereo ? F.mvuRight.data() : nullptr, F.N, &g, occupied.data(),
                                     modeFlags | (stereo ? ORBX_PROJ_CHECK_URIGHT : 0), thDist, nnratio, checkOri ? 1 : 0, 0,
@@ -240,6 +241,130 @@ int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, 
         q.push_back(e); src.push_back(pMP);
     }
     return projectionSearch(Context(), CurrentFrame, q, src, 0, TH_HIGH, mfNNratio, mbCheckOrientation);
+}
+
+namespace {
+// 3x3 (row-major) and 3x1 float blocks of a pose matrix, and the camera centre -R^T t
+void poseOf(const cv::Mat& T, float R[9], float t[3], float Ow[3], float invScale = 1.0f)
+{
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) R[3 * r + c] = T.at<float>(r, c) * invScale;
+        t[r] = T.at<float>(r, 3) * invScale;
+    }
+    for (int r = 0; r < 3; ++r) Ow[r] = -(R[r] * t[0] + R[3 + r] * t[1] + R[6 + r] * t[2]);
+}
+float norm3(float x, float y, float z) { return (float)std::sqrt((double)x * x + (double)y * y + (double)z * z); }   // cv::norm(NORM_L2)
+} // namespace
+
+// Relocalisation: project the KeyFrame's MapPoints into the current frame (:1949-1978) and search around them.
+int ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound, const float th,
+                                   const int ORBdist)
+{
+    float Rcw[9], tcw[3], Ow[3];
+    poseOf(CurrentFrame.mTcw, Rcw, tcw, Ow);
+    const std::vector<MapPoint*> vpMPs = pKF->GetMapPointMatches();
+    std::vector<orbx_proj_query> q;
+    std::vector<MapPoint*> src;
+    for (size_t i = 0, iend = vpMPs.size(); i < iend; i++) {
+        MapPoint* pMP = vpMPs[i];
+        if (!pMP || pMP->isBad() || sAlreadyFound.count(pMP)) continue;
+        cv::Mat X = pMP->GetWorldPos();
+        const float x = X.at<float>(0), y = X.at<float>(1), z = X.at<float>(2);
+        const float xc = Rcw[0] * x + Rcw[1] * y + Rcw[2] * z + tcw[0];
+        const float yc = Rcw[3] * x + Rcw[4] * y + Rcw[5] * z + tcw[1];
+        const float invzc = 1.0 / (Rcw[6] * x + Rcw[7] * y + Rcw[8] * z + tcw[2]);
+        const float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+        const float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+        if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+        if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+        const float dist3D = norm3(x - Ow[0], y - Ow[1], z - Ow[2]);
+        const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        const int nPredictedLevel = pMP->PredictScale(dist3D, &CurrentFrame);
+        orbx_proj_query e;
+        memset(&e, 0, sizeof(e));
+        e.u = u; e.v = v; e.radius = th * CurrentFrame.mvScaleFactors[nPredictedLevel];
+        e.angle = pKF->mvKeysUn[i].angle;
+        e.min_level = nPredictedLevel - 1; e.max_level = nPredictedLevel + 1;
+        const cv::Mat d = pMP->GetDescriptor();
+        memcpy(e.desc, d.ptr<uint8_t>(), 32);
+        q.push_back(e); src.push_back(pMP);
+    }
+    return projectionSearch(Context(), CurrentFrame, q, src, 0, ORBdist, mfNNratio, mbCheckOrientation, true);
+}
+
+// Loop closing: project candidate MapPoints with the Sim3 Scw into the KeyFrame (:437-512) and search around them.
+int ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, std::vector<MapPoint*>& vpMatched, int th)
+{
+    const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy;
+    const float r00 = Scw.at<float>(0, 0), r01 = Scw.at<float>(0, 1), r02 = Scw.at<float>(0, 2);
+    const float scw = std::sqrt(r00 * r00 + r01 * r01 + r02 * r02);
+    float Rcw[9], tcw[3], Ow[3];
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) Rcw[3 * r + c] = Scw.at<float>(r, c) / scw;
+        tcw[r] = Scw.at<float>(r, 3) / scw;
+    }
+    for (int r = 0; r < 3; ++r) Ow[r] = -(Rcw[r] * tcw[0] + Rcw[3 + r] * tcw[1] + Rcw[6 + r] * tcw[2]);
+    std::set<MapPoint*> spAlreadyFound(vpMatched.begin(), vpMatched.end());
+    spAlreadyFound.erase(static_cast<MapPoint*>(NULL));
+    std::vector<orbx_proj_query> q;
+    std::vector<MapPoint*> src;
+    for (int iMP = 0, iendMP = (int)vpPoints.size(); iMP < iendMP; iMP++) {
+        MapPoint* pMP = vpPoints[iMP];
+        if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+        cv::Mat X = pMP->GetWorldPos();
+        const float x = X.at<float>(0), y = X.at<float>(1), z = X.at<float>(2);
+        const float xc = Rcw[0] * x + Rcw[1] * y + Rcw[2] * z + tcw[0];
+        const float yc = Rcw[3] * x + Rcw[4] * y + Rcw[5] * z + tcw[1];
+        const float zc = Rcw[6] * x + Rcw[7] * y + Rcw[8] * z + tcw[2];
+        if (zc < 0.0) continue;
+        const float invz = 1 / zc;
+        const float u = fx * (xc * invz) + cx, v = fy * (yc * invz) + cy;
+        if (!pKF->IsInImage(u, v)) continue;
+        const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+        const float POx = x - Ow[0], POy = y - Ow[1], POz = z - Ow[2];
+        const float dist = norm3(POx, POy, POz);
+        if (dist < minDistance || dist > maxDistance) continue;
+        cv::Mat Pn = pMP->GetNormal();
+        if (POx * Pn.at<float>(0) + POy * Pn.at<float>(1) + POz * Pn.at<float>(2) < 0.5 * dist) continue;
+        const int nPredictedLevel = pMP->PredictScale(dist, pKF);
+        orbx_proj_query e;
+        memset(&e, 0, sizeof(e));
+        e.u = u; e.v = v; e.radius = th * pKF->mvScaleFactors[nPredictedLevel];
+        e.min_level = nPredictedLevel - 1; e.max_level = nPredictedLevel;      // :536 (KeyFrame::GetFeaturesInArea has no level filter)
+        const cv::Mat d = pMP->GetDescriptor();
+        memcpy(e.desc, d.ptr<uint8_t>(), 32);
+        q.push_back(e); src.push_back(pMP);
+    }
+    std::vector<uint8_t> occupied(pKF->N, 0), tmp;
+    for (int i = 0; i < pKF->N; ++i) occupied[i] = vpMatched[i] != NULL;                                     // :531
+    const orbx_grid g = {(float)pKF->mnMinX, (float)pKF->mnMinY, pKF->mfGridElementWidthInv, pKF->mfGridElementHeightInv,
+                         pKF->mnGridCols, pKF->mnGridRows};
+    std::vector<int32_t> assign(pKF->N > 0 ? pKF->N : 1);
+    int n = 0;
+    check(orbx_search_by_projection(Context(), q.data(), (int)q.size(), reinterpret_cast<const orbx_keypoint*>(pKF->mvKeysUn.data()),
+                                    contiguous(pKF->mDescriptors, tmp), nullptr, pKF->N, &g, occupied.data(), 0, TH_LOW, mfNNratio, 0, 0,
+                                    assign.data(), &n), "orbx_search_by_projection");
+    for (int i = 0; i < pKF->N; ++i) if (assign[i] >= 0) vpMatched[i] = src[assign[i]];                      // :554
+    return n;
+}
+
+int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
+                                        int windowSize)
+{
+    static_assert(sizeof(cv::Point2f) == 2 * sizeof(float), "vbPrevMatched is read as (x, y) float pairs");
+    const int n1 = (int)F1.mvKeysUn.size(), n2 = (int)F2.mvKeysUn.size();
+    vnMatches12 = std::vector<int>(n1, -1);                                                                  // :590
+    if (n1 == 0) return 0;
+    std::vector<uint8_t> t1, t2;
+    const orbx_grid g = {Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, FRAME_GRID_COLS, FRAME_GRID_ROWS};
+    int n = 0;
+    check(orbx_search_for_initialization(Context(), reinterpret_cast<const orbx_keypoint*>(F1.mvKeysUn.data()), contiguous(F1.mDescriptors, t1),
+                                         n1, reinterpret_cast<float*>(vbPrevMatched.data()),
+                                         reinterpret_cast<const orbx_keypoint*>(F2.mvKeysUn.data()), contiguous(F2.mDescriptors, t2), n2, &g,
+                                         windowSize, mfNNratio, mbCheckOrientation ? 1 : 0, 0, vnMatches12.data(), &n),
+          "orbx_search_for_initialization");
+    return n;
 }
 
 // static members of the compat Frame stand-in (the reference defines them in src/Frame.cc:38-42)

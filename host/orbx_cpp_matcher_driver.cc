@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <set>
 #include <vector>
 using namespace ORB_SLAM2;
 
@@ -103,6 +104,54 @@ int main(int argc, char** argv)
         put(o, &n, 4); put(o, res.data(), 4 * F.N);
         int dd = ORBmatcher::DescriptorDistance(k1.mDescriptors.row(0), k2.mDescriptors.row(0));
         put(o, &dd, 4);
+        if (in.size() > 20) {
+            // 18: per KF1 feature 8 floats (world x, y, z, mfMaxDistance, mfMinDistance, normal x, y, z)
+            // 19: float[8]: th_reloc, ORBdist, th_sim3, window, logScaleFactor, sim3 scale
+            const float* Wd = as<float>(in[18]);
+            const float* Q = as<float>(in[19]);
+            for (int i = 0; i < k1.N; ++i) {
+                MapPoint& mp = pool1[i];
+                mp.mWorldPos = cv::Mat(3, 1, CV_32F); memcpy(mp.mWorldPos.data, Wd + 8 * i, 12);
+                mp.mfMaxDistance = Wd[8 * i + 3]; mp.mfMinDistance = Wd[8 * i + 4];
+                mp.mNormalVector = cv::Mat(3, 1, CV_32F); memcpy(mp.mNormalVector.data, Wd + 8 * i + 5, 12);
+                mp.mDescriptor = cv::Mat(1, 32, CV_8U); memcpy(mp.mDescriptor.data, in[20].data() + 32 * i, 32);   // 20: MapPoint descriptors
+            }
+            // (e) SearchByProjection(Frame, KeyFrame, sAlreadyFound, th, ORBdist): relocalisation
+            F.mTcw = cv::Mat::zeros(4, 4, CV_32F); for (int i = 0; i < 4; ++i) F.mTcw.at<float>(i, i) = 1.f;
+            Frame::fx = P[3]; Frame::fy = P[4]; Frame::cx = P[5]; Frame::cy = P[6];
+            F.mnScaleLevels = 8; F.mfLogScaleFactor = Q[4];
+            F.mvpMapPoints.assign(F.N, (MapPoint*)NULL);
+            for (int i = 0; i < F.N; ++i) if (in[17][i]) F.mvpMapPoints[i] = &occupiedMP;
+            std::set<MapPoint*> found;
+            for (int i = 0; i < k1.N; i += 17) if (k1.mvpMapPoints[i]) found.insert(k1.mvpMapPoints[i]);
+            n = ORBmatcher(P[0], true).SearchByProjection(F, &k1, found, Q[0], (int)Q[1]);
+            res.assign(F.N, -1);
+            for (int i = 0; i < F.N; ++i) if (F.mvpMapPoints[i] && F.mvpMapPoints[i] != &occupiedMP) res[i] = (int)(F.mvpMapPoints[i] - pool1.data());
+            put(o, &n, 4); put(o, res.data(), 4 * F.N);
+            // (f) SearchByProjection(KeyFrame, Scw, vpPoints, vpMatched, th): loop closing, KF = side 2
+            k2.mnScaleLevels = 8; k2.mfLogScaleFactor = Q[4];
+            k2.mnGridCols = FRAME_GRID_COLS; k2.mnGridRows = FRAME_GRID_ROWS;
+            k2.mfGridElementWidthInv = P[8]; k2.mfGridElementHeightInv = P[9];
+            k2.mnMinX = (int)P[10]; k2.mnMinY = (int)P[11]; k2.mnMaxX = (int)P[12]; k2.mnMaxY = (int)P[13];
+            cv::Mat Scw = cv::Mat::zeros(4, 4, CV_32F);
+            for (int i = 0; i < 3; ++i) Scw.at<float>(i, i) = Q[5];
+            Scw.at<float>(3, 3) = 1.f;
+            std::vector<MapPoint*> vpPoints, vpMatched(k2.N, (MapPoint*)NULL);
+            for (int i = 0; i < k1.N; ++i) if (k1.mvpMapPoints[i]) vpPoints.push_back(k1.mvpMapPoints[i]);
+            for (int i = 0; i < k2.N; ++i) if (in[17][i]) vpMatched[i] = &occupiedMP;
+            n = ORBmatcher(P[0], true).SearchByProjection(&k2, Scw, vpPoints, vpMatched, (int)Q[2]);
+            res.assign(k2.N, -1);
+            for (int i = 0; i < k2.N; ++i) if (vpMatched[i] && vpMatched[i] != &occupiedMP) res[i] = (int)(vpMatched[i] - pool1.data());
+            put(o, &n, 4); put(o, res.data(), 4 * k2.N);
+            // (g) SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)
+            Frame F1;
+            F1.N = k1.N; F1.mDescriptors = k1.mDescriptors; F1.mvKeys = k1.mvKeysUn; F1.mvKeysUn = k1.mvKeysUn;
+            std::vector<cv::Point2f> prev(F1.N);
+            for (int i = 0; i < F1.N; ++i) prev[i] = F1.mvKeysUn[i].pt;
+            std::vector<int> m12;
+            n = ORBmatcher(P[0], true).SearchForInitialization(F1, F, prev, m12, (int)Q[3]);
+            put(o, &n, 4); put(o, m12.data(), 4 * F1.N); put(o, prev.data(), 8 * F1.N);
+        }
     } catch (const std::exception& e) { fprintf(stderr, "error: %s\n", e.what()); return 1; }
     fclose(o);
     return 0;

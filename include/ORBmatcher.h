@@ -2,12 +2,12 @@
 // class, constructor, static members and method signatures, so Tracking / LocalMapping / LoopClosing call it unchanged.
 // The Hamming work runs in hand-written sm_100a CUDA kernels behind the C ABI (include/orbx.h); the bodies in
 // host/ORBmatcher.cc only flatten the SLAM objects.  Implemented here: DescriptorDistance, both SearchByBoW overloads,
-// SearchForTriangulation, SearchByProjection(Frame&, vector<MapPoint*>&, th) and SearchByProjection(Frame&, const
-// Frame&, th, bMono).  The remaining overloads (SearchByProjection with KeyFrame / Sim3, SearchForInitialization,
-// SearchBySim3, Fuse x2) are the "next" rows of SURVEY.md 8(f): they keep the reference's own bodies until then.
+// SearchForTriangulation, all four SearchByProjection overloads and SearchForInitialization.  SearchBySim3 and Fuse x2
+//  keep the reference's own bodies for now (they call the static DescriptorDistance below).
 #ifndef ORBMATCHER_H
 #define ORBMATCHER_H
 
+#include <set>
 #include <vector>
 #include <opencv2/core/core.hpp>
 #include <opencv2/features2d/features2d.hpp>
@@ -31,6 +31,12 @@ public:
 
     int SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th = 3);                // :78-191
     int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);          // :1741-1910
+    int SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound, const float th,
+                           const int ORBdist);                                                                      // :1922-2065
+    int SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints,
+                           std::vector<MapPoint*>& vpMatched, int th);                                              // :431-560
+    int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
+                                int windowSize = 10);                                                               // :580-748
     int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);                            // :255-419
     int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);                           // :760-903
     int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12,

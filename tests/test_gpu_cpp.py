@@ -89,6 +89,27 @@ def test_cpp_dropin_matcher(tmp_path):
     pts["v"] = keys["y"][src] + rng.normal(0, 3, len(pts)).astype(np.float32)
     pts["level"] = np.clip(keys["octave"][src] + rng.integers(-1, 2, len(pts)), 0, 7)
     uright = sides[1][3]
+    # map points of KF1 placed so that they project (identity pose) next to keypoints of side 2; float32 steps mirror
+    # host/ORBmatcher.cc (which mirrors src/ORBmatcher.cc:1949-1978 and :470-512)
+    f32 = np.float32
+    has1 = sides[0][2]
+    tgt = rng.integers(0, n2, n1)
+    zw = (2 + 4 * rng.random(n1)).astype(f32)
+    xw = ((k2["x"][tgt] + rng.normal(0, 3, n1).astype(f32) - cx) * zw / fx).astype(f32)
+    yw = ((k2["y"][tgt] + rng.normal(0, 3, n1).astype(f32) - cy) * zw / fy).astype(f32)
+    xw[:6] = [9, -9, 0, 0, 0.1, 0.2]; yw[:6] = [0, 0, 9, -9, 0.1, 0.2]; zw[4] = -1.0   # out of the image / behind the camera
+    lvl_w = np.clip(k2["octave"][tgt] + rng.integers(-1, 2, n1), 0, 7)
+    dist = np.sqrt(xw.astype(np.float64) ** 2 + yw.astype(np.float64) ** 2 + zw.astype(np.float64) ** 2).astype(f32)
+    logsf = f32(np.log(1.2))
+    maxd = (dist * f32(1.2) ** (lvl_w.astype(f32) - f32(0.5))).astype(f32)
+    mind = (maxd / scale[7]).astype(f32)
+    maxd[6] = dist[6] / f32(1.3); mind[7] = dist[7] * f32(1.5)                            # outside the distance range
+    nrm = np.stack([xw, yw, zw], 1).astype(np.float64)
+    nrm = (nrm / np.linalg.norm(nrm, axis=1, keepdims=True)).astype(f32)
+    nrm[8::9] *= -1                                                                       # seen from behind (Sim3 variant only)
+    world = np.concatenate([np.stack([xw, yw, zw, maxd, mind], 1), nrm], 1).astype(f32)
+    th_reloc, orb_dist, th_sim3, window = 10.0, 100, 10, 100
+    mpdesc = synth.descriptors(seed + 21, n1, 0.1, d2[tgt])
     inp, outp = tmp_path / "m_in.bin", tmp_path / "m_out.bin"
     with open(inp, "wb") as f:
         _arr(f, np.array([nnratio, 1, 0, fx, fy, cx, cy, th, grid[2], grid[3], 0, 0, 640, 480, 0, 0], np.float32))
@@ -97,6 +118,7 @@ def test_cpp_dropin_matcher(tmp_path):
         _arr(f, scale); _arr(f, sigma2); _arr(f, F12); _arr(f, Ow)
         _arr(f, np.stack([pts["u"], pts["v"], pts["ur"], pts["view_cos"], pts["level"].astype(np.float32)], 1).astype(np.float32))
         _arr(f, pts["desc"]); _arr(f, occupied)
+        _arr(f, world); _arr(f, np.array([th_reloc, orb_dist, th_sim3, window, logsf, 2.0, 0, 0], np.float32)); _arr(f, mpdesc)
     r = subprocess.run([os.path.join(ROOT, "host", "orbx_cpp_matcher_driver"), str(inp), str(outp)], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     out = _read_all(outp)
@@ -114,6 +136,35 @@ def test_cpp_dropin_matcher(tmp_path):
     assert int(np.frombuffer(out[6], np.int32)[0]) == nw and np.array_equal(np.frombuffer(out[7], np.int32), want)
     assert nw > 0
     assert int(np.frombuffer(out[8], np.int32)[0]) == int(np.unpackbits(d1[0] ^ d2[0]).sum())
+
+    # the host-side projection of both overloads, restated step by step in float32
+    invz = (1.0 / zw.astype(np.float64)).astype(f32)
+    u_r = ((fx * xw) * invz + cx).astype(f32); v_r = ((fy * yw) * invz + cy).astype(f32)       # :1962-1963
+    lvl_pred = np.clip(np.ceil(np.log((maxd / dist).astype(f32).astype(np.float64)) / np.float64(logsf)), 0, 7).astype(np.int32)
+    in_range = ~((dist < f32(0.8) * mind) | (dist > f32(1.2) * maxd))
+    found = np.zeros(n1, bool); found[::17] = True
+    sel = (has1 != 0) & ~found & ~((u_r < 0) | (u_r > 640)) & ~((v_r < 0) | (v_r > 480)) & in_range
+    idx_r = np.flatnonzero(sel)
+    pr = np.zeros(len(idx_r), O.PROJ_DTYPE)
+    pr["u"], pr["v"], pr["level"], pr["angle"], pr["desc"] = u_r[idx_r], v_r[idx_r], lvl_pred[idx_r], k1["angle"][idx_r], mpdesc[idx_r]
+    want, nw = O.search_by_projection_reloc(pr, keys, desc, scale, grid, occupied, th_reloc, orb_dist, True)
+    want = np.where(want >= 0, idx_r[np.maximum(want, 0)], -1)
+    assert int(np.frombuffer(out[9], np.int32)[0]) == nw and np.array_equal(np.frombuffer(out[10], np.int32), want)
+    assert nw > 50
+    u_s = (fx * (xw * invz) + cx).astype(f32); v_s = (fy * (yw * invz) + cy).astype(f32)         # :487-491
+    dots = (xw * nrm[:, 0] + yw * nrm[:, 1] + zw * nrm[:, 2]).astype(f32)
+    sel = (has1 != 0) & ~(zw < 0) & (u_s >= 0) & (u_s < 640) & (v_s >= 0) & (v_s < 480) & in_range & ~(dots.astype(np.float64) < 0.5 * dist.astype(np.float64))
+    idx_s = np.flatnonzero(sel)
+    ps = np.zeros(len(idx_s), O.PROJ_DTYPE)
+    ps["u"], ps["v"], ps["level"], ps["desc"] = u_s[idx_s], v_s[idx_s], lvl_pred[idx_s], mpdesc[idx_s]
+    want, nw = O.search_by_projection_sim3(ps, keys, desc, scale, grid, occupied, th_sim3)
+    want = np.where(want >= 0, idx_s[np.maximum(want, 0)], -1)
+    assert int(np.frombuffer(out[11], np.int32)[0]) == nw and np.array_equal(np.frombuffer(out[12], np.int32), want)
+    assert nw > 50
+    prev0 = np.stack([k1["x"], k1["y"]], 1).astype(f32)
+    want, nw, wprev = O.search_for_initialization(k1, d1, prev0, keys, desc, grid, window, float(nnratio), True)
+    assert int(np.frombuffer(out[13], np.int32)[0]) == nw and np.array_equal(np.frombuffer(out[14], np.int32), want)
+    assert np.array_equal(np.frombuffer(out[15], f32).reshape(-1, 2).view(np.uint32), wprev.view(np.uint32))
 
 
 def pkg_mod():
