@@ -99,14 +99,13 @@ __global__ void atan2ProbeKernel(const float* yx, int n, float* out)
 
 constexpr int kDescWarps = 8;
 constexpr int kKpPerWarpMax = 32;                                               // consecutive keypoints per warp (lane k owns keypoint k), patches double-buffered
-constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitchW = 11;   // blurred patch: 37 rows x 44 bytes
-constexpr int kRawRows = 2 * kHalfPatch + 1, kRawPitchW = 9;                   // raw patch: 31 rows x 36 bytes
+constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitchW = 16;   // blurred patch: 37 rows x 64 bytes (four 16-byte chunks)
+constexpr int kRawRows = 2 * kHalfPatch + 1, kRawPitchW = 12;                  // raw patch: 31 rows x 48 bytes (three 16-byte chunks)
 constexpr int kPatchWords = kPatchRows * kPatchPitchW, kRawWords = kRawRows * kRawPitchW;
-constexpr int kBufWords = kPatchWords + kRawWords;
 
-__device__ __forceinline__ void cpAsync4(uint32_t dst, const void* src)
+__device__ __forceinline__ void cpAsync16(uint32_t dst, const void* src)
 {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
 
 __global__ void __launch_bounds__(kDescWarps * 32, 2)
@@ -116,7 +115,7 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
                orbx_keypoint* __restrict__ outKp, uint8_t* __restrict__ outDesc, int cap, int* __restrict__ outN,
                int* __restrict__ err, int kpPerWarp)
 {
-    __shared__ __align__(16) uint32_t sBuf[kDescWarps][2][kBufWords];
+    extern __shared__ __align__(16) uint32_t sBufAll[];                      // [kDescWarps][2][kPatchWords]; pass A uses it as [2][kRawWords]
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
     const int frame = blockIdx.y + G.frame0;
 
@@ -142,43 +141,34 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
         if (lane < nkp) kp = selAll[(size_t)frame * G.selPerFrame + G.lv[myLevel].outBase + (i - before)];
     }
 
-    // ---- patches come into shared memory as 4-byte async copies, one commit group per keypoint, two keypoints in
-    //      flight: the 37 x 37 blurred patch for BRIEF (rotated pattern points stay within +-18; 10 words per row) and
-    //      the 31 x 31 raw patch for IC_Angle (9 words per row).  All later accesses are shared-memory loads. ----
-    auto issue = [&](int k) {
+    // ---- two passes over the warp's keypoints, each streaming its patches through a double buffer of 16-byte async
+    //      copies (rows of every plane are 16-byte aligned; a patch is fetched as the chunks that cover it):
+    //      pass A  31 x 31 raw patch (3 chunks per row) -> IC_Angle moments, lane k keeps the moments of keypoint k;
+    //              then fastAtan2 + sinf/cosf run ONCE, lane-parallel over the warp's keypoints
+    //      pass B  37 x 37 blurred patch (rotated pattern points stay within +-18; 4 chunks per row) -> steered BRIEF ----
+    uint32_t* const bufBase = sBufAll + wrp * (2 * kPatchWords);
+    auto issueRaw = [&](int k) {
         const int level = __shfl_sync(0xffffffffu, myLevel, k);
         const int cx = __float2int_rn(__shfl_sync(0xffffffffu, kp.x, k)), cy = __float2int_rn(__shfl_sync(0xffffffffu, kp.y, k));
         const LevelGeom& g = G.lv[level];
-        uint32_t* buf = sBuf[wrp][k & 1];
-        const int bp = g.pitch;
-        {
-            const int a0 = (cx - kPatchR) & ~3;                     // aligned first column of the blurred patch
-            const int lr = lane / 10, lk = lane - lr * 10;          // 3 rows x 10 words per step
-            const bool ok = lane < 30 && a0 + 4 * lk + 3 < bp;      // a word starting beyond the padded row is never used
-            const uint8_t* src = blur + g.blurOff + ((size_t)frame * g.h + (cy - kPatchR + lr)) * bp + a0 + 4 * lk;
-            uint32_t dst = (uint32_t)__cvta_generic_to_shared(buf + lr * kPatchPitchW + lk);
-            #pragma unroll
-            for (int t = 0; t < (kPatchRows + 2) / 3; ++t) {
-                if (ok && 3 * t + lr < kPatchRows) cpAsync4(dst, src);
-                src += 3 * bp; dst += 3 * kPatchPitchW * 4;
-            }
-        }
+        uint32_t* buf = bufBase + (k & 1) * kRawWords;
         const uint8_t* img; int pitch;
         if (level == 0) { img = lvl0 + (size_t)frame * lvl0Frame; pitch = (int)lvl0Pitch; }
         else { img = pyr + g.planeOff + (size_t)frame * g.pitch * g.h; pitch = g.pitch; }
-        const int ra0 = (cx - kHalfPatch) & ~3;
-        if (((((size_t)img) | (size_t)pitch) & 3) == 0) {
-            const int lr = lane / 9, lk = lane - lr * 9;            // 3 rows x 9 words per step
-            const bool ok = lane < 27 && ra0 + 4 * lk + 3 < pitch;
-            const uint8_t* src = img + (size_t)(cy - kHalfPatch + lr) * pitch + ra0 + 4 * lk;
-            uint32_t dst = (uint32_t)__cvta_generic_to_shared(buf + kPatchWords + lr * kRawPitchW + lk);
+        const int ra0 = (cx - kHalfPatch) & ~15;
+        if (((((size_t)img) | (size_t)pitch) & 15) == 0) {
+            const int lr = lane / 3, lk = lane - lr * 3;            // 10 rows x 3 chunks per step
+            const bool ok = lane < 30 && ra0 + 16 * lk < pitch;     // a chunk beyond the padded row is never used
+            const uint8_t* src = img + (size_t)(cy - kHalfPatch + lr) * pitch + ra0 + 16 * lk;
+            uint32_t dst = (uint32_t)__cvta_generic_to_shared(buf + lr * kRawPitchW + 4 * lk);
+            const int step = 10 * pitch;
             #pragma unroll
-            for (int t = 0; t < (kRawRows + 2) / 3; ++t) {
-                if (ok && 3 * t + lr < kRawRows) cpAsync4(dst, src);
-                src += 3 * pitch; dst += 3 * kRawPitchW * 4;
+            for (int t = 0; t < (kRawRows + 9) / 10; ++t) {
+                if (ok && 10 * t + lr < kRawRows) cpAsync16(dst, src);
+                src += step; dst += 10 * kRawPitchW * 4;
             }
-        } else {                                                     // unaligned caller image (level 0 only): byte loads
-            uint8_t* rb = reinterpret_cast<uint8_t*>(buf + kPatchWords);
+        } else {                                                     // caller image without 16-byte rows (level 0 only): byte loads
+            uint8_t* rb = reinterpret_cast<uint8_t*>(buf);
             const int offr = (cx - kHalfPatch) - ra0;
             for (int i = lane; i < kRawRows * 31; i += 32) {
                 const int r = i / 31, c = i - r * 31;
@@ -187,10 +177,31 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
+    auto issueBlur = [&](int k) {
+        const int level = __shfl_sync(0xffffffffu, myLevel, k);
+        const int cx = __float2int_rn(__shfl_sync(0xffffffffu, kp.x, k)), cy = __float2int_rn(__shfl_sync(0xffffffffu, kp.y, k));
+        const LevelGeom& g = G.lv[level];
+        uint32_t* buf = bufBase + (k & 1) * kPatchWords;
+        const int bp = g.pitch;
+        const int a0 = (cx - kPatchR) & ~15;                        // aligned first column of the blurred patch
+        const int lr = lane >> 2, lk = lane & 3;                    // 8 rows x 4 chunks per step
+        const bool ok = a0 + 16 * lk < bp;
+        const uint8_t* src = blur + g.blurOff + ((size_t)frame * g.h + (cy - kPatchR + lr)) * bp + a0 + 16 * lk;
+        uint32_t dst = (uint32_t)__cvta_generic_to_shared(buf + lr * kPatchPitchW + 4 * lk);
+        const int step = 8 * bp;
+        #pragma unroll
+        for (int t = 0; t < (kPatchRows + 7) / 8; ++t) {
+            if (ok && 8 * t + lr < kPatchRows) cpAsync16(dst, src);
+            src += step; dst += 8 * kPatchPitchW * 4;
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
 
-    // IC_Angle row mask of this lane (row v = lane - 15): bytes t = u + 15 with |u| <= umax[|v|]
-    uint32_t icMask[8];
+    // ---- pass A: IC_Angle.  lane = row v of the disc: the row's 31 bytes are aligned into 8 words, bytes outside
+    //      |u| <= umax[|v|] are masked off, and IDP.4A gives the row sum (m01 = v * sum) and the sum of u * p. ----
+    int myM10 = 0, myM01 = 0;
     {
+        uint32_t icMask[8];
         const int v = lane - kHalfPatch, d = lane < 2 * kHalfPatch + 1 ? G.umax[v < 0 ? -v : v] : -1;
         const int lo = kHalfPatch - d, hi = kHalfPatch + d;            // inclusive byte range (empty when d < 0)
         #pragma unroll
@@ -200,51 +211,63 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
             for (int b2 = 0; b2 < 4; ++b2) if (4 * j + b2 >= lo && 4 * j + b2 <= hi) m |= 0xffu << (8 * b2);
             icMask[j] = m;
         }
+        issueRaw(0);
+        if (nkp > 1) issueRaw(1);
+        for (int k = 0; k < nkp; ++k) {
+            if (k + 1 < nkp) asm volatile("cp.async.wait_group 1;" ::: "memory");
+            else asm volatile("cp.async.wait_group 0;" ::: "memory");
+            __syncwarp();
+            const int cx = __float2int_rn(__shfl_sync(0xffffffffu, kp.x, k));
+            const uint32_t* buf = bufBase + (k & 1) * kRawWords;
+            int m10 = 0, m01 = 0;
+            if (lane < 2 * kHalfPatch + 1) {
+                const uint32_t* row = buf + lane * kRawPitchW + (((cx - kHalfPatch) & 15) >> 2);   // word holding u = -15
+                const uint32_t sh = 8u * (uint32_t)((cx - kHalfPatch) & 3);                         // its byte inside that word
+                uint32_t w[9];
+                #pragma unroll
+                for (int j = 0; j < 9; ++j) w[j] = row[j];
+                int cs = 0;
+                #pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t x = __funnelshift_r(w[j], w[j + 1], sh) & icMask[j];
+                    // signed weights u = 4j-15 .. 4j-12 of the word's four bytes
+                    const int uw = (int)(((uint32_t)(uint8_t)(4 * j - 15)) | ((uint32_t)(uint8_t)(4 * j - 14) << 8) |
+                                         ((uint32_t)(uint8_t)(4 * j - 13) << 16) | ((uint32_t)(uint8_t)(4 * j - 12) << 24));
+                    cs = (int)__dp4a(x, 0x01010101u, (uint32_t)cs);
+                    asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(x), "r"(uw));
+                }
+                m01 = (lane - kHalfPatch) * cs;
+            }
+            m10 = __reduce_add_sync(0xffffffffu, m10);      // REDUX: exact integer sums, any order
+            m01 = __reduce_add_sync(0xffffffffu, m01);
+            if (lane == k) { myM10 = m10; myM01 = m01; }
+            __syncwarp();                                    // everyone is done with this buffer
+            if (k + 2 < nkp) issueRaw(k + 2);
+        }
     }
-    // this lane's 8 test pairs of the pattern stay in registers for all keypoints of the warp
+    // orientation and its sine / cosine, one keypoint per lane (:140, :158)
+    const float myAngle = fastAtan2Dev((float)myM01, (float)myM10);
+    float myCos, mySin;
+    {
+        const float factorPI = (float)(3.14159265358979323846 / 180.f);
+        glibcSinCosf(__fmul_rn(myAngle, factorPI), mySin, myCos);
+    }
+
+    // ---- pass B: steered BRIEF on the blurred patch: lane = descriptor byte; the lane's 8 test pairs of the pattern
+    //      stay in registers for all keypoints of the warp ----
     float4 pat[8];
     #pragma unroll
     for (int j = 0; j < 8; ++j) pat[j] = __ldg(reinterpret_cast<const float4*>(kBriefPatternF) + lane * 8 + j);
-    issue(0);
-    if (nkp > 1) issue(1);
+    issueBlur(0);
+    if (nkp > 1) issueBlur(1);
     for (int k = 0; k < nkp; ++k) {
         if (k + 1 < nkp) asm volatile("cp.async.wait_group 1;" ::: "memory");
         else asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncwarp();
-        const int level = __shfl_sync(0xffffffffu, myLevel, k);
         const int cx = __float2int_rn(__shfl_sync(0xffffffffu, kp.x, k));
-        const uint32_t* buf = sBuf[wrp][k & 1];
-
-        // ---- IC_Angle: lane = row v of the disc.  The row's 31 bytes are aligned into 8 words, bytes outside
-        //      |u| <= umax[|v|] are masked off, and IDP.4A gives the row sum (m01 = v * sum) and sum of u * p. ----
-        int m10 = 0, m01 = 0;
-        if (lane < 2 * kHalfPatch + 1) {
-            const uint32_t* row = buf + kPatchWords + lane * kRawPitchW;
-            const uint32_t sh = 8u * (uint32_t)((cx - kHalfPatch) & 3);         // byte column of u = -15 inside the staged row
-            uint32_t w[kRawPitchW];
-            #pragma unroll
-            for (int j = 0; j < kRawPitchW; ++j) w[j] = row[j];
-            int cs = 0;
-            #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const uint32_t x = __funnelshift_r(w[j], w[j + 1], sh) & icMask[j];
-                // signed weights u = 4j-15 .. 4j-12 of the word's four bytes
-                const int uw = (int)(((uint32_t)(uint8_t)(4 * j - 15)) | ((uint32_t)(uint8_t)(4 * j - 14) << 8) |
-                                     ((uint32_t)(uint8_t)(4 * j - 13) << 16) | ((uint32_t)(uint8_t)(4 * j - 12) << 24));
-                cs = (int)__dp4a(x, 0x01010101u, (uint32_t)cs);
-                asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(x), "r"(uw));
-            }
-            m01 = (lane - kHalfPatch) * cs;
-        }
-        m10 = __reduce_add_sync(0xffffffffu, m10);      // REDUX: exact integer sums, any order
-        m01 = __reduce_add_sync(0xffffffffu, m01);
-        const float angle = fastAtan2Dev((float)m01, (float)m10);
-
-        // ---- steered BRIEF on the blurred patch: lane = descriptor byte ----
-        const float factorPI = (float)(3.14159265358979323846 / 180.f);
-        float a, b;
-        glibcSinCosf(__fmul_rn(angle, factorPI), b, a); // a = cos, b = sin  (:158)
-        const int offc = (cx - kPatchR) - ((cx - kPatchR) & ~3) + kPatchR;                 // byte column of the patch centre
+        const float a = __shfl_sync(0xffffffffu, myCos, k), b = __shfl_sync(0xffffffffu, mySin, k);
+        const uint32_t* buf = bufBase + (k & 1) * kPatchWords;
+        const int offc = (cx - kPatchR) - ((cx - kPatchR) & ~15) + kPatchR;                // byte column of the patch centre
         const uint8_t* pc = reinterpret_cast<const uint8_t*>(buf) + kPatchR * (kPatchPitchW * 4) + offc;
         int val = 0;
         #pragma unroll
@@ -257,15 +280,14 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
             const int t0 = pc[r0 * (kPatchPitchW * 4) + c0], t1 = pc[r1 * (kPatchPitchW * 4) + c1];
             val |= (t0 < t1) << j;
         }
-        const int idx = i0 + k;
-        outDesc[((size_t)frame * cap + idx) * 32 + lane] = (uint8_t)val;
-        if (lane == k) {
-            kp.angle = angle;
-            if (level != 0) { const float sc = G.lv[level].scale; kp.x = __fmul_rn(kp.x, sc); kp.y = __fmul_rn(kp.y, sc); }
-            outKp[(size_t)frame * cap + idx] = kp;
-        }
+        outDesc[((size_t)frame * cap + (i0 + k)) * 32 + lane] = (uint8_t)val;
         __syncwarp();                                              // everyone is done with this buffer
-        if (k + 2 < nkp) issue(k + 2);
+        if (k + 2 < nkp) issueBlur(k + 2);
+    }
+    if (lane < nkp) {
+        kp.angle = myAngle;
+        if (myLevel != 0) { const float sc = G.lv[myLevel].scale; kp.x = __fmul_rn(kp.x, sc); kp.y = __fmul_rn(kp.y, sc); }
+        outKp[(size_t)frame * cap + i0 + lane] = kp;
     }
 }
 
@@ -282,7 +304,13 @@ int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* 
     while (kpw > 2 && (long long)batch * ((slots + kpw - 1) / kpw) < (long long)smCount * 2 * kDescWarps) kpw >>= 1;
     const int perBlock = kDescWarps * kpw;
     dim3 grid((slots + perBlock - 1) / perBlock, batch), block(kDescWarps * 32);
-    describeKernel<<<grid, block, 0, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur,
+    const size_t smem = sizeof(uint32_t) * (size_t)kDescWarps * 2 * kPatchWords;
+    static bool configured = false;
+    if (!configured) {
+        ORBX_CUDA(c, cudaFuncSetAttribute(describeKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    describeKernel<<<grid, block, smem, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur,
                                                  c->dSel, c->dSelCount, dKps, dDesc, capPerFrame, dN, c->dErr, kpw);
     stageEnd(c, ST_DESCRIBE, 1);
     ORBX_CUDA(c, cudaGetLastError());
