@@ -108,7 +108,7 @@ __device__ __forceinline__ void cpAsync16(uint32_t dst, const void* src)
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
 
-__global__ void __launch_bounds__(kDescWarps * 32, 2)
+__global__ void __launch_bounds__(kDescWarps * 32, 3)
 describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0, size_t lvl0Pitch, size_t lvl0Frame,
                const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                const orbx_keypoint* __restrict__ selAll, const int* __restrict__ selCount,

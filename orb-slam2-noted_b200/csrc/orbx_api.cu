@@ -465,7 +465,10 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
         c->hPinnedBytes = sizeof(int) * (size_t)c->maxBatch;
     }
     int* hN = reinterpret_cast<int*>(c->hPinned);
-    const int nChunks = (batch + chunk - 1) / chunk;
+    std::vector<int> cuts(1, 0);                                   // chunk boundaries
+    for (int f = chunk; f < batch; f += chunk) cuts.push_back(f);
+    cuts.push_back(batch);
+    const int nChunks = (int)cuts.size() - 1;
     while ((int)c->evIn.size() < nChunks) { cudaEvent_t e; ORBX_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); c->evIn.push_back(e); }
     while ((int)c->evDone.size() < nChunks) { cudaEvent_t e; ORBX_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); c->evDone.push_back(e); }
     if (!inDev) {
@@ -477,8 +480,12 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
     cudaStream_t const mainStream = c->stream;
     struct StreamRestore { Ctx* c; cudaStream_t s; ~StreamRestore() { c->stream = s; } } restoreStream{c, mainStream};   // also on error returns
     const bool twoStreams = !inDev && nChunks > 1;
+    static const bool dbgTl = getenv("ORBX_DBG_TIMELINE") != nullptr;
+    std::vector<cudaEvent_t> tl;
+    auto mark = [&](cudaStream_t st) { if (!dbgTl) return; cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st); tl.push_back(e); };
+    mark(c->sIn);
     for (int i = 0; i < nChunks; ++i) {
-        const int f0 = i * chunk, n = std::min(chunk, batch - f0);
+        const int f0 = cuts[i], n = cuts[i + 1] - f0;
         c->stream = (twoStreams && (i & 1)) ? c->stream2 : mainStream;   // launchers enqueue on c->stream
         if (!inDev) {
             if (frame_stride == stride * (size_t)hgt || n == 1) {
@@ -490,6 +497,7 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
                                                    (size_t)hgt, cudaMemcpyHostToDevice, c->sIn));
             }
             ORBX_CUDA(c, cudaEventRecord(c->evIn[i], c->sIn));
+            mark(c->sIn);
             ORBX_CUDA(c, cudaStreamWaitEvent(c->stream, c->evIn[i], 0));
         }
         rc = launchPyramid(c, f0, n);
@@ -500,6 +508,7 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
         if (rc) { c->stream = mainStream; return rc; }
         if (!outDev) {
             ORBX_CUDA(c, cudaEventRecord(c->evDone[i], c->stream));
+            mark(c->stream);
             ORBX_CUDA(c, cudaStreamWaitEvent(c->sOut, c->evDone[i], 0));
             ORBX_CUDA(c, cudaMemcpyAsync(hN + f0, dN + f0, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, c->sOut));
             if (sc == cap) {
@@ -514,6 +523,7 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
                 ORBX_CUDA(c, cudaMemcpy2DAsync(desc + (size_t)32 * f0 * cap, (size_t)32 * cap, dD + (size_t)32 * f0 * sc, (size_t)32 * sc,
                                                (size_t)32 * cap, (size_t)n, cudaMemcpyDeviceToHost, c->sOut));
             }
+            mark(c->sOut);
         }
     }
     c->stream = mainStream;
@@ -523,6 +533,12 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
     }
     if (outDev) return ORBX_OK; // asynchronous; orbx_sync() reports device-side errors
     ORBX_CUDA(c, cudaStreamSynchronize(c->sOut));
+    if (dbgTl && !tl.empty()) {
+        fprintf(stderr, "timeline (ms since start; per chunk: h2d done, kernels done, d2h done)\n");
+        for (size_t k = 1; k < tl.size(); ++k) { float ms = 0; cudaEventElapsedTime(&ms, tl[0], tl[k]); fprintf(stderr, "%s%.3f", (k - 1) % 3 ? " " : "\n  ", ms); }
+        fprintf(stderr, "\n");
+        for (cudaEvent_t e : tl) cudaEventDestroy(e);
+    }
     memcpy(n_out, hN, sizeof(int) * (size_t)batch);
     rc = checkDeviceError(c);
     if (rc) return rc;
