@@ -14,7 +14,7 @@
 
 namespace orbx {
 
-constexpr int kBlurR = 4, kBlurThreads = 256, kBlurWarps = kBlurThreads / 32;
+constexpr int kBlurR = 4, kBlurThreads = 128, kBlurWarps = kBlurThreads / 32;
 constexpr int kRawPad = 16;                              // columns staged left of the tile (keeps bulk copies 16-byte aligned)
 constexpr int kRawW = kBlurTW + 2 * kRawPad;             // bytes per staged row (160: 40 words)
 constexpr int kRawH = kBlurTH + 2 * kBlurR;

@@ -14,7 +14,7 @@ constexpr int kHalfPatch = 15;   // HALF_PATCH_SIZE :80
 constexpr int kPatch = 31;       // PATCH_SIZE :79
 constexpr int kWinOff = 16;      // minBorderX = EDGE_THRESHOLD-3 :1061
 constexpr int kMaxLevels = ORBX_MAX_LEVELS;
-constexpr int kBlurTW = 128, kBlurTH = 256;   // blur tile: columns per CTA, max rows per CTA (k_blur.cu)
+constexpr int kBlurTW = 128, kBlurTH = 160;   // blur tile: columns per CTA, max rows per CTA (k_blur.cu)
 
 enum Stage { ST_PYRAMID = 0, ST_FAST, ST_OCTREE, ST_BLUR, ST_DESCRIBE, ST_H2D, ST_D2H, ST_HAMMING, ST_MATCH, ST_STEREO, ST_BOW, ST_COUNT };
 
