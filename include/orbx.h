@@ -183,6 +183,23 @@ int orbx_search_by_projection(orbx_ctx* ctx, const orbx_proj_query* q, int nq, c
                               const uint8_t* occupied, int mode_flags, int th_dist, float nnratio,
                               int check_orientation, int flags, int32_t* assign, int* nmatches);
 
+/* ---- MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:366-448, for npoints map points per call: the observed
+ *      descriptors of point p are rows [seg[p], seg[p+1]) of desc (seg: HOST array of npoints+1 offsets, at most 1024 rows
+ *      per point); best[p] = row (relative to seg[p]) with the smallest median distance to the point's descriptors, first
+ *      one on ties; -1 for a point without descriptors. ---- */
+int orbx_distinctive_descriptors(orbx_ctx* ctx, const uint8_t* desc, const int32_t* seg, int npoints, int flags, int32_t* best);
+
+/* ---- independent window searches: every query finds its best keypoint on its own (no claims between queries).  Replaces
+ *      the candidate loops of ORBmatcher::Fuse(KeyFrame*, vector<MapPoint*>&, th) src/ORBmatcher.cc:1139-1300 (with the
+ *      reprojection gate :1254-1285: inv_sigma2 = pKF->mvInvLevelSigma2, a HOST array of ORBX_MAX_LEVELS floats; a keypoint
+ *      with uright >= 0 uses the stereo form and 7.8, otherwise 5.99), Fuse(KeyFrame*, Scw, ..) :1310-1458 and both
+ *      directions of SearchBySim3 :1472-1723 (inv_sigma2 = NULL: no gate).  The caller projects (u, v, ur, radius,
+ *      min_level = L-1, max_level = L).  best_dist[i] = smallest distance in the window or -1 when it is empty;
+ *      best_idx[i] = its keypoint (first visited wins a tie) when best_dist[i] <= th_dist, else -1. ---- */
+int orbx_window_best(orbx_ctx* ctx, const orbx_proj_query* q, int nq, const orbx_keypoint* keys, const uint8_t* desc,
+                     const float* uright, int n, const orbx_grid* g, const float* inv_sigma2, int th_dist, int flags,
+                     int32_t* best_idx, int32_t* best_dist);
+
 /* ---- monocular initialisation.  Replaces ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:580-748 (window search of
  *      F1's level-0 keypoints around vbPrevMatched in F2's grid, best/second-best ratio test, distance-masked candidates,
  *      stolen matches, rotation histogram).  prev_xy = vbPrevMatched as n1 (x, y) pairs, updated in place for the matched

@@ -587,6 +587,70 @@ int orc_search_for_initialization(const orc_keypoint* keys1, const uint8_t* desc
     return nmatches;
 }
 
+/* Candidate loops of Fuse(KeyFrame*, vector<MapPoint*>&, th) src/ORBmatcher.cc:1139-1300 (inv_sigma2 != NULL: reprojection gate
+ * :1254-1285), Fuse(KeyFrame*, Scw, ...) :1310-1458 and SearchBySim3 :1472-1723 (inv_sigma2 == NULL), after the caller's
+ * projection: pts[i] = (u, v, ur, level = nPredictedLevel, desc); radius = th * scale[level].  Queries are independent.
+ * best_dist[i] = smallest distance among the candidates (-1: none), best_idx[i] = its keypoint if <= th_dist else -1. */
+void orc_window_best(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, const float* uright, int n,
+                     const float* scale, const orc_grid* g, const int32_t* cell_off, const int32_t* cell_idx, float th,
+                     const float* inv_sigma2, int th_dist, int32_t* best_idx, int32_t* best_dist)
+{
+    int32_t* cand = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < npts; ++i) {
+        const orc_projpoint* p = &pts[i];
+        const int lvl = p->level;
+        const float radius = th * scale[lvl];
+        const float u = p->u, v = p->v, ur = p->ur;
+        const int nc = orc_features_in_area(keys, g, cell_off, cell_idx, u, v, radius, -1, -1, cand);
+        int best = INT_MAX, bestIdx = -1;
+        for (int k = 0; k < nc; ++k) {
+            const int idx = cand[k];
+            const int kpLevel = keys[idx].octave;
+            if (kpLevel < lvl - 1 || kpLevel > lvl) continue;
+            if (inv_sigma2) {
+                if (uright && uright[idx] >= 0) {
+                    const float ex = u - keys[idx].x, ey = v - keys[idx].y, er = ur - uright[idx];
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * inv_sigma2[kpLevel] > 7.8) continue;
+                } else {
+                    const float ex = u - keys[idx].x, ey = v - keys[idx].y;
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * inv_sigma2[kpLevel] > 5.99) continue;
+                }
+            }
+            const int dist = orc_descriptor_distance(p->desc, desc + 32 * (size_t)idx);
+            if (dist < best) { best = dist; bestIdx = idx; }
+        }
+        best_dist[i] = bestIdx >= 0 ? best : -1;
+        best_idx[i] = (bestIdx >= 0 && best <= th_dist) ? bestIdx : -1;
+    }
+    free(cand);
+}
+
+/* MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:366-448: among the N observed descriptors of a map point, the
+ * one whose median distance to all of them (itself included, index (int)(0.5 * (N - 1)) of the sorted row) is smallest;
+ * the first such row wins.  desc: the points' descriptors back to back, point p owns rows [seg[p], seg[p+1]). */
+static int cmp_int(const void* a, const void* b) { return *(const int*)a - *(const int*)b; }
+void orc_distinctive_descriptors(const uint8_t* desc, const int32_t* seg, int npoints, int32_t* best)
+{
+    for (int p = 0; p < npoints; ++p) {
+        const int N = seg[p + 1] - seg[p];
+        best[p] = -1;
+        if (N <= 0) continue;
+        const uint8_t* D = desc + 32 * (size_t)seg[p];
+        int* row = (int*)malloc(sizeof(int) * (size_t)N);
+        int bestMedian = INT_MAX, bestIdx = 0;
+        for (int i = 0; i < N; ++i) {
+            for (int j = 0; j < N; ++j) row[j] = i == j ? 0 : orc_descriptor_distance(D + 32 * (size_t)i, D + 32 * (size_t)j);
+            qsort(row, (size_t)N, sizeof(int), cmp_int);
+            const int median = row[(int)(0.5 * (N - 1))];
+            if (median < bestMedian) { bestMedian = median; bestIdx = i; }
+        }
+        best[p] = bestIdx;
+        free(row);
+    }
+}
+
 /* ---------------- Frame::ComputeStereoMatches: src/Frame.cc:831-1128 ----------------
  * pyrL/pyrR: un-bordered level images packed back to back (level l at lvl_off[l], size lvl_w[l] x lvl_h[l]). */
 typedef struct { int d, i; } distidx;

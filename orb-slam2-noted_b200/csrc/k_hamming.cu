@@ -7,6 +7,7 @@
 // train descriptors stream through shared memory in 128-descriptor chunks and are read as
 // warp-broadcast 128-bit loads, so each LDS feeds 2 x 4 POPCs per thread.
 #include "orbx_internal.h"
+#include <algorithm>
 
 namespace orbx {
 
@@ -99,6 +100,42 @@ hammingBest2Kernel(const uint4* __restrict__ qDesc, const uint4* __restrict__ tD
         }
 }
 
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:366-448) for many map points in one launch: one warp per map
+// point.  Row i of the point's N x N distance matrix is written to shared memory as it is computed; its median
+// (element (N-1)/2 of the sorted row, self-distance 0 included) is found by bisection on the value (distances are 0..256)
+// with warp-wide counts, so nothing is sorted.  The first row with the smallest median wins (strict <, :437).
+constexpr int kDistinctWarps = 4, kDistinctMaxObs = 1024;
+__global__ void __launch_bounds__(32 * kDistinctWarps)
+distinctiveKernel(const uint4* __restrict__ desc, const int* __restrict__ seg, int npoints, int* __restrict__ best)
+{
+    __shared__ uint16_t sd[kDistinctWarps][kDistinctMaxObs];
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    const int p = blockIdx.x * kDistinctWarps + wrp;
+    if (p >= npoints) return;
+    const int s0 = seg[p], N = seg[p + 1] - s0;
+    if (N <= 0 || N > kDistinctMaxObs) { if (lane == 0) best[p] = N <= 0 ? -1 : -2; return; }
+    const uint4* D = desc + 2 * (size_t)s0;
+    uint16_t* row = sd[wrp];
+    const int k1 = ((N - 1) >> 1) + 1;                               // rank of the median, 1-based
+    int bestMedian = 0x7fffffff, bestIdx = 0;
+    for (int i = 0; i < N; ++i) {
+        const uint4 a0 = D[2 * i], a1 = D[2 * i + 1];
+        for (int j = lane; j < N; j += 32) row[j] = (uint16_t)(i == j ? 0 : hamming256(a0, a1, D[2 * j], D[2 * j + 1]));
+        __syncwarp();
+        int lo = 0, hi = 256;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            int cnt = 0;
+            for (int j = lane; j < N; j += 32) cnt += row[j] <= mid;
+            cnt = __reduce_add_sync(0xffffffffu, cnt);
+            if (cnt >= k1) hi = mid; else lo = mid + 1;
+        }
+        if (lo < bestMedian) { bestMedian = lo; bestIdx = i; }
+        __syncwarp();
+    }
+    if (lane == 0) best[p] = bestIdx;
+}
+
 } // namespace orbx
 using namespace orbx;
 
@@ -129,6 +166,37 @@ extern "C" int orbx_descriptor_distance(orbx_ctx* h, const uint8_t* a, const uin
         ORBX_CUDA(c, cudaMemcpyAsync(dist, dd, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
         ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
     }
+    return ORBX_OK;
+}
+
+// seg is a HOST array of npoints + 1 offsets (rows of desc); desc / best follow `flags`.
+extern "C" int orbx_distinctive_descriptors(orbx_ctx* h, const uint8_t* desc, const int32_t* seg, int npoints, int flags, int32_t* best)
+{
+    if (!h || npoints < 0 || (npoints > 0 && (!seg || !best))) return ORBX_E_INVALID;
+    if (npoints == 0) return ORBX_OK;
+    const int total = seg[npoints];
+    if (total < 0 || (total > 0 && !desc)) return ORBX_E_INVALID;
+    for (int p = 0; p < npoints; ++p) {
+        if (seg[p + 1] < seg[p]) return ORBX_E_INVALID;
+        if (seg[p + 1] - seg[p] > kDistinctMaxObs) return ORBX_E_CAPACITY;
+    }
+    Ctx* c = &h->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
+    const size_t dBytes = ((size_t)std::max(total, 1) * 32 + 255) & ~(size_t)255, sBytes = (sizeof(int) * (size_t)(npoints + 1) + 255) & ~(size_t)255;
+    int rc = ensureScratch(c, dBytes + sBytes + sizeof(int) * (size_t)npoints);
+    if (rc) return rc;
+    uint8_t* S = (uint8_t*)c->dScratch;
+    const uint4* dD = (const uint4*)desc;
+    if (!inDev && total > 0) { ORBX_CUDA(c, cudaMemcpyAsync(S, desc, (size_t)total * 32, cudaMemcpyHostToDevice, c->stream)); dD = (const uint4*)S; }
+    ORBX_CUDA(c, cudaMemcpyAsync(S + dBytes, seg, sizeof(int) * (size_t)(npoints + 1), cudaMemcpyHostToDevice, c->stream));
+    int* dBest = outDev ? best : (int*)(S + dBytes + sBytes);
+    stageBegin(c, ST_HAMMING);
+    distinctiveKernel<<<(npoints + kDistinctWarps - 1) / kDistinctWarps, 32 * kDistinctWarps, 0, c->stream>>>(dD, (const int*)(S + dBytes), npoints, dBest);
+    stageEnd(c, ST_HAMMING, 1);
+    ORBX_CUDA(c, cudaGetLastError());
+    if (!outDev) ORBX_CUDA(c, cudaMemcpyAsync(best, dBest, sizeof(int) * (size_t)npoints, cudaMemcpyDeviceToHost, c->stream));
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));   // seg is read from pageable host memory
     return ORBX_OK;
 }
 

@@ -160,10 +160,14 @@ __device__ __forceinline__ bool candPass(const float4& ci, const QueryGeom& s, i
 // P2: four smallest keys of every query, the octaves that go with them, and the number of candidates.
 // One warp per query: the window's columns (one contiguous j-range each) are flattened over the lanes.
 constexpr int kScanWarps = 4;
+// kGate: the reprojection chi-square gate of Fuse (src/ORBmatcher.cc:1254-1285): e2 * invSigma2[level] > 5.99 (7.8 with a
+// right coordinate) rejects the candidate; plain float arithmetic in the reference's order, compared as double.
+struct ReprojGate { float invSigma2[ORBX_MAX_LEVELS]; };
+template <bool kGate>
 __global__ void __launch_bounds__(32 * kScanWarps)
 projScanKernel(const orbx_proj_query* __restrict__ q, int nq, GridDev g, const int* __restrict__ off,
                const float4* __restrict__ cinfo, const uint4* __restrict__ dsort, int checkUr, uint4* __restrict__ topKey,
-               int2* __restrict__ meta)
+               int2* __restrict__ meta, const ReprojGate gate)
 {
     const int lane = threadIdx.x & 31;
     const int i = blockIdx.x * kScanWarps + (threadIdx.x >> 5);
@@ -196,7 +200,15 @@ projScanKernel(const orbx_proj_query* __restrict__ q, int nq, GridDev g, const i
                 if (t >= T) continue;
                 const int j = jbk + (t - exk);
                 int oct;
-                if (!candPass(cinfo[j], s, checkUr, oct)) continue;
+                const float4 ci = cinfo[j];
+                if (!candPass(ci, s, checkUr, oct)) continue;
+                if (kGate) {
+                    const float ex = __fsub_rn(s.x, ci.x), ey = __fsub_rn(s.y, ci.y);
+                    float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                    double lim = 5.99;
+                    if (ci.z >= 0.0f) { const float er = __fsub_rn(s.ur, ci.z); e2 = __fadd_rn(e2, __fmul_rn(er, er)); lim = 7.8; }
+                    if ((double)__fmul_rn(e2, gate.invSigma2[min(oct, ORBX_MAX_LEVELS - 1)]) > lim) continue;
+                }
                 const uint32_t key = ((uint32_t)hamming256(a0, a1, dsort[2 * j], dsort[2 * j + 1]) << kJBits) | (uint32_t)j;
                 ++cnt;
                 if (key < e3) {
@@ -551,6 +563,19 @@ initResolveKernel(const orbx_proj_query* __restrict__ q, int n1, GridDev g, cons
     if (lane == 0) *nmOut = cnt;
 }
 
+// ---------------- independent window searches (Fuse x2, SearchBySim3) ----------------
+// No claims between queries: the smallest key of the scan IS the reference's answer (strict <, first visited wins).
+__global__ void windowBestKernel(const uint4* __restrict__ topKey, const int* __restrict__ idx, int nq, int thDist,
+                                 int* __restrict__ bestIdx, int* __restrict__ bestDist)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nq) return;
+    const uint32_t k = topKey[i].x;
+    const int d = k == kNoKeyP ? -1 : (int)(k >> kJBits);
+    bestDist[i] = d;
+    bestIdx[i] = (d >= 0 && d <= thDist) ? idx[k & kJMask] : -1;
+}
+
 struct BumpP { size_t off = 0; size_t take(size_t b) { const size_t o = off; off += (b + 255) & ~(size_t)255; return o; } };
 
 static int launchGridBuild(Ctx* c, const orbx_keypoint* dKeys, int n, const GridDev& g, int* dCellTmp, int* dTmpIdx, int* dOff, int* dIdx,
@@ -659,9 +684,9 @@ extern "C" int orbx_search_by_projection(orbx_ctx* h, const orbx_proj_query* q, 
     if (rc) return rc;
     int launches = 0;
     if (nq > 0) {
-        projScanKernel<<<(nq + kScanWarps - 1) / kScanWarps, 32 * kScanWarps, 0, c->stream>>>(dQ, nq, gd, (int*)(S + oOff), (float4*)(S + oInfo), (uint4*)(S + oSort),
+        projScanKernel<false><<<(nq + kScanWarps - 1) / kScanWarps, 32 * kScanWarps, 0, c->stream>>>(dQ, nq, gd, (int*)(S + oOff), (float4*)(S + oInfo), (uint4*)(S + oSort),
                                                            (mode_flags & ORBX_PROJ_CHECK_URIGHT) ? 1 : 0, (uint4*)(S + oTop),
-                                                           (int2*)(S + oMeta));
+                                                           (int2*)(S + oMeta), ReprojGate());
         if (occBytes > 40 * 1024)
             ORBX_CUDA(c, cudaFuncSetAttribute(projResolveKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)occBytes));
         projResolveKernel<<<1, kResolveThreads, occBytes, c->stream>>>(dQ, nq, gd, (int*)(S + oOff), (int*)(S + oIdx),
@@ -749,8 +774,8 @@ extern "C" int orbx_search_for_initialization(orbx_ctx* h, const orbx_keypoint* 
                          (float4*)(S + oInfo), (uint4*)(S + oSort), nullptr, 0);
     if (rc) return rc;
     initQueryKernel<<<(n1 + 255) / 256, 256, 0, c->stream>>>(dK1, dD1, dPrev, n1, (float)window, (orbx_proj_query*)(S + oQ));
-    projScanKernel<<<(n1 + kScanWarps - 1) / kScanWarps, 32 * kScanWarps, 0, c->stream>>>((orbx_proj_query*)(S + oQ), n1, gd, (int*)(S + oOff),
-                                                       (float4*)(S + oInfo), (uint4*)(S + oSort), 0, (uint4*)(S + oTop), (int2*)(S + oMeta));
+    projScanKernel<false><<<(n1 + kScanWarps - 1) / kScanWarps, 32 * kScanWarps, 0, c->stream>>>((orbx_proj_query*)(S + oQ), n1, gd, (int*)(S + oOff),
+                                                       (float4*)(S + oInfo), (uint4*)(S + oSort), 0, (uint4*)(S + oTop), (int2*)(S + oMeta), ReprojGate());
     if (resolveSmem > 40 * 1024)
         ORBX_CUDA(c, cudaFuncSetAttribute(initResolveKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)resolveSmem));
     initResolveKernel<<<1, 32, resolveSmem, c->stream>>>((orbx_proj_query*)(S + oQ), n1, gd, (int*)(S + oOff), (int*)(S + oIdx),
@@ -771,6 +796,81 @@ extern "C" int orbx_search_for_initialization(orbx_ctx* h, const orbx_keypoint* 
         ORBX_CUDA(c, cudaMemcpyAsync(HO, dOut + n1, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
         ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
         if (nmatches) *nmatches = HO[0];
+    }
+    return ORBX_OK;
+}
+
+extern "C" int orbx_window_best(orbx_ctx* h, const orbx_proj_query* q, int nq, const orbx_keypoint* keys, const uint8_t* desc,
+                                const float* uright, int n, const orbx_grid* g, const float* inv_sigma2, int th_dist, int flags,
+                                int32_t* best_idx, int32_t* best_dist)
+{
+    if (!h || !g || nq < 0 || n < 0 || g->cols < 1 || g->rows < 1 || (n > 0 && (!keys || !desc)) || (nq > 0 && (!q || !best_idx || !best_dist)))
+        return ORBX_E_INVALID;
+    Ctx* c = &h->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    if (nq == 0) return ORBX_OK;
+    const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
+    if (n == 0) {
+        if (outDev) { ORBX_CUDA(c, cudaMemsetAsync(best_idx, 0xff, sizeof(int) * (size_t)nq, c->stream)); ORBX_CUDA(c, cudaMemsetAsync(best_dist, 0xff, sizeof(int) * (size_t)nq, c->stream)); }
+        else for (int i = 0; i < nq; ++i) { best_idx[i] = -1; best_dist[i] = -1; }
+        return ORBX_OK;
+    }
+    if (n >= (1 << kJBits)) return ORBX_E_CAPACITY;
+    const int ncell = g->cols * g->rows;
+    BumpP B;
+    const size_t oQ = B.take(sizeof(orbx_proj_query) * (size_t)nq), oK = B.take(sizeof(orbx_keypoint) * (size_t)n),
+                 oD = B.take((size_t)32 * n), oU = B.take(sizeof(float) * (size_t)n);
+    const size_t inBytes = B.off;
+    const size_t oCell = B.take(sizeof(int) * (size_t)n), oTmp = B.take(sizeof(int) * (size_t)n),
+                 oOff = B.take(sizeof(int) * (size_t)(ncell + 1)), oIdx = B.take(sizeof(int) * (size_t)n),
+                 oInfo = B.take(sizeof(float4) * (size_t)n), oSort = B.take((size_t)32 * n),
+                 oTop = B.take(sizeof(uint4) * (size_t)nq), oMeta = B.take(sizeof(int2) * (size_t)nq),
+                 oOut = B.take(sizeof(int) * 2 * (size_t)nq);
+    int rc = ensureScratch(c, B.off);
+    if (rc) return rc;
+    const size_t outBytes = sizeof(int) * 2 * (size_t)nq;
+    rc = ensureMatchPinned(c, inBytes + outBytes);
+    if (rc) return rc;
+    uint8_t* S = (uint8_t*)c->dScratch;
+    const orbx_proj_query* dQ = q; const orbx_keypoint* dK = keys; const uint4* dD = (const uint4*)desc; const float* dU = uright;
+    stageBegin(c, ST_H2D);
+    if (!inDev) {
+        uint8_t* H = c->hMatch;
+        memcpy(H + oQ, q, sizeof(orbx_proj_query) * (size_t)nq);
+        memcpy(H + oK, keys, sizeof(orbx_keypoint) * (size_t)n);
+        memcpy(H + oD, desc, (size_t)32 * n);
+        if (uright) memcpy(H + oU, uright, sizeof(float) * (size_t)n);
+        ORBX_CUDA(c, cudaMemcpyAsync(S, H, inBytes, cudaMemcpyHostToDevice, c->stream));
+        dQ = (const orbx_proj_query*)(S + oQ); dK = (const orbx_keypoint*)(S + oK); dD = (const uint4*)(S + oD);
+        if (uright) dU = (const float*)(S + oU);
+    }
+    stageEnd(c, ST_H2D, 0);
+    const GridDev gd = {g->min_x, g->min_y, g->inv_w, g->inv_h, g->cols, g->rows};
+    ReprojGate gate;
+    for (int l = 0; l < ORBX_MAX_LEVELS; ++l) gate.invSigma2[l] = inv_sigma2 ? inv_sigma2[l] : 0.0f;   // inv_sigma2 is a HOST array
+    int* dOut = (int*)(S + oOut);
+    int* dBI = outDev ? best_idx : dOut;
+    int* dBD = outDev ? best_dist : dOut + nq;
+    stageBegin(c, ST_MATCH);
+    rc = launchGridBuild(c, dK, n, gd, (int*)(S + oCell), (int*)(S + oTmp), (int*)(S + oOff), (int*)(S + oIdx), dD, dU, nullptr,
+                         (float4*)(S + oInfo), (uint4*)(S + oSort), nullptr, 0);
+    if (rc) return rc;
+    const int blocks = (nq + kScanWarps - 1) / kScanWarps;
+    if (inv_sigma2)
+        projScanKernel<true><<<blocks, 32 * kScanWarps, 0, c->stream>>>(dQ, nq, gd, (int*)(S + oOff), (float4*)(S + oInfo), (uint4*)(S + oSort), 0,
+                                                                        (uint4*)(S + oTop), (int2*)(S + oMeta), gate);
+    else
+        projScanKernel<false><<<blocks, 32 * kScanWarps, 0, c->stream>>>(dQ, nq, gd, (int*)(S + oOff), (float4*)(S + oInfo), (uint4*)(S + oSort), 0,
+                                                                         (uint4*)(S + oTop), (int2*)(S + oMeta), gate);
+    windowBestKernel<<<(nq + 255) / 256, 256, 0, c->stream>>>((uint4*)(S + oTop), (int*)(S + oIdx), nq, th_dist, dBI, dBD);
+    stageEnd(c, ST_MATCH, 2);
+    ORBX_CUDA(c, cudaGetLastError());
+    if (!outDev) {
+        int* HO = (int*)(c->hMatch + inBytes);
+        ORBX_CUDA(c, cudaMemcpyAsync(HO, dOut, outBytes, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+        memcpy(best_idx, HO, sizeof(int) * (size_t)nq);
+        memcpy(best_dist, HO + nq, sizeof(int) * (size_t)nq);
     }
     return ORBX_OK;
 }

@@ -59,6 +59,8 @@ def _mlib():
     L.orbx_assign_grid.argtypes = [vp, vp, ci, ctypes.POINTER(_Grid), ci, vp, vp]
     L.orbx_search_by_projection.argtypes = [vp, vp, ci, vp, vp, vp, ci, ctypes.POINTER(_Grid), vp, ci, ci, cf, ci, ci, vp, ip]
     L.orbx_search_for_initialization.argtypes = [vp, vp, vp, ci, vp, vp, vp, ci, ctypes.POINTER(_Grid), ci, cf, ci, ci, vp, ip]
+    L.orbx_window_best.argtypes = [vp, vp, ci, vp, vp, vp, ci, ctypes.POINTER(_Grid), vp, ci, ci, vp, vp]
+    L.orbx_distinctive_descriptors.argtypes = [vp, vp, vp, ci, ci, vp]
     L.orbx_stereo_match.argtypes = [vp, vp, ci, vp, vp, ci, vp, vp, ci, cf, cf, ci, vp, vp, ip]
     _ready = True
     return L
@@ -228,6 +230,31 @@ class ORBmatcher:
                                                     0, _np(out), ctypes.byref(n))
         _chk(self._ex, rc, "orbx_search_for_initialization")
         return out[:f1.N], n.value, prev
+
+
+def window_best(ex, frame, queries, grid, th_dist, inv_sigma2=None, grid_dims=(FRAME_GRID_COLS, FRAME_GRID_ROWS)):
+    """Candidate loops of ORBmatcher::Fuse x2 (src/ORBmatcher.cc:1139-1300 with inv_sigma2 = mvInvLevelSigma2, :1310-1458) and
+    SearchBySim3 (:1472-1723): every query independently.  Returns (best_idx, best_dist)."""
+    q = np.ascontiguousarray(queries, PROJ_QUERY_DTYPE)
+    g = _Grid(float(grid[0]), float(grid[1]), float(grid[2]), float(grid[3]), grid_dims[0], grid_dims[1])
+    bi, bd = np.empty(max(len(q), 1), np.int32), np.empty(max(len(q), 1), np.int32)
+    is2 = None
+    if inv_sigma2 is not None:
+        is2 = np.zeros(16, np.float32); is2[:len(inv_sigma2)] = inv_sigma2
+    rc = _mlib().orbx_window_best(ex._h, _np(q), len(q), _np(frame.keys), _np(frame.desc), _np(frame.uright), frame.N, ctypes.byref(g),
+                                  _np(is2), int(th_dist), 0, _np(bi), _np(bd))
+    _chk(ex, rc, "orbx_window_best")
+    return bi[:len(q)], bd[:len(q)]
+
+
+def distinctive_descriptors(ex, desc, seg):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:366-448) for many map points per call."""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    seg = np.ascontiguousarray(seg, np.int32)
+    out = np.empty(max(len(seg) - 1, 1), np.int32)
+    rc = _mlib().orbx_distinctive_descriptors(ex._h, _np(desc), _np(seg), len(seg) - 1, 0, _np(out))
+    _chk(ex, rc, "orbx_distinctive_descriptors")
+    return out[:len(seg) - 1]
 
 
 def assign_features_to_grid(ex, keys, grid, grid_dims=(FRAME_GRID_COLS, FRAME_GRID_ROWS)):

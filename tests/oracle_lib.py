@@ -188,6 +188,10 @@ def _mlib():
     L.orc_search_by_projection_reloc.argtypes = [vp, ci, vp, vp, ci, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, ci, ci, vp]
     L.orc_search_by_projection_sim3.argtypes = [vp, ci, vp, vp, ci, vp, ctypes.POINTER(Grid), vp, vp, vp, ci, vp]
     L.orc_search_for_initialization.argtypes = [vp, vp, ci, vp, vp, vp, ci, ctypes.POINTER(Grid), vp, vp, ci, cf, ci, vp]
+    L.orc_window_best.argtypes = [vp, ci, vp, vp, vp, ci, vp, ctypes.POINTER(Grid), vp, vp, cf, vp, ci, vp, vp]
+    L.orc_window_best.restype = None
+    L.orc_distinctive_descriptors.argtypes = [vp, vp, ci, vp]
+    L.orc_distinctive_descriptors.restype = None
     L.orc_stereo_matches.argtypes = [vp, vp, ci, vp, vp, ci, vp, vp, vp, vp, vp, vp, vp, cf, cf, vp, vp]
     L.orc_hamming_best2.argtypes = [vp, vp, vp, vp, vp, vp, ci, vp, vp, vp, vp]
     L._match_ready = True
@@ -345,6 +349,25 @@ def search_by_projection_sim3(pts, keys, desc, scale, grid, occupied, th):
     n = _mlib().orc_search_by_projection_sim3(_p(pts), len(pts), _p(keys), _p(desc), len(keys), _p(scale), ctypes.byref(g), _p(off),
                                               _p(idx), None if occ is None else _p(occ), int(th), _p(out))
     return out, n
+
+
+def window_best(pts, keys, desc, uright, scale, grid, th, inv_sigma2, th_dist):
+    """Candidate loops of Fuse x2 / SearchBySim3 (independent queries).  Returns (best_idx, best_dist)."""
+    pts, keys, desc, scale, off, idx, g, _, _ = _proj_common(pts, keys, desc, scale, grid, None)
+    ur = None if uright is None else np.ascontiguousarray(uright, np.float32)
+    is2 = None if inv_sigma2 is None else np.ascontiguousarray(inv_sigma2, np.float32)
+    bi, bd = np.empty(max(len(pts), 1), np.int32), np.empty(max(len(pts), 1), np.int32)
+    _mlib().orc_window_best(_p(pts), len(pts), _p(keys), _p(desc), None if ur is None else _p(ur), len(keys), _p(scale), ctypes.byref(g),
+                            _p(off), _p(idx), th, None if is2 is None else _p(is2), int(th_dist), _p(bi), _p(bd))
+    return bi[:len(pts)], bd[:len(pts)]
+
+
+def distinctive_descriptors(desc, seg):
+    """MapPoint::ComputeDistinctiveDescriptors for many map points: desc rows [seg[p], seg[p+1]) belong to point p."""
+    desc = np.ascontiguousarray(desc, np.uint8); seg = np.ascontiguousarray(seg, np.int32)
+    out = np.empty(max(len(seg) - 1, 1), np.int32)
+    _mlib().orc_distinctive_descriptors(_p(desc), _p(seg), len(seg) - 1, _p(out))
+    return out[:len(seg) - 1]
 
 
 def search_for_initialization(keys1, desc1, prev_xy, keys2, desc2, grid, window, nnratio, check_ori=True):

@@ -235,6 +235,43 @@ def test_search_for_initialization_matches_oracle(P, ctx, seed, n1, n2, window, 
     assert np.array_equal(wprev.view(np.uint32), gprev.view(np.uint32))
 
 
+@pytest.mark.parametrize("seed,n,nq", [(21, 1000, 800), (22, 4000, 5000), (23, 100, 30)])
+def test_window_best_matches_oracle(P, ctx, seed, n, nq):
+    """Candidate loops of Fuse x2 (src/ORBmatcher.cc:1139-1300 with the reprojection gate, :1310-1458) and SearchBySim3
+    (:1472-1723): independent best-only window searches."""
+    keys, desc, uright, occupied, pts = proj_scene(P, seed, n, nq)
+    p = O.params(1000)
+    scale = np.array(p.scale[:8], np.float32)
+    inv_sigma2 = np.array(p.inv_sigma2[:8], np.float32)
+    grid = (0.0, 0.0, np.float32(64) / np.float32(640), np.float32(48) / np.float32(480))
+    uright = np.where(uright > 0, keys["x"] - 6, -1).astype(np.float32)
+    pts["ur"] = pts["u"] - 6 + np.random.default_rng(seed).normal(0, 2, nq).astype(np.float32)
+    for th, is2, ur, thd in ((3.0, inv_sigma2, uright, 50), (4.0, inv_sigma2, None, 50), (7.5, None, None, 100), (3.0, None, uright, 50)):
+        wi, wd = O.window_best(pts, keys, desc, ur, scale, grid, th, is2, thd)
+        q = np.zeros(nq, P.PROJ_QUERY_DTYPE)
+        q["u"], q["v"], q["ur"], q["desc"] = pts["u"], pts["v"], pts["ur"], pts["desc"]
+        q["radius"] = (np.float32(th) * scale[pts["level"]]).astype(np.float32)
+        q["min_level"], q["max_level"] = pts["level"] - 1, pts["level"]
+        gi, gd = P.window_best(ctx, P.FrameView(desc, keys, None, ur), q, grid, thd, is2)
+        assert np.array_equal(wd, gd), (th, int((wd != gd).sum()))
+        assert np.array_equal(wi, gi), (th, int((wi != gi).sum()))
+        assert (wi >= 0).sum() > 5
+
+
+def test_distinctive_descriptors_match_oracle(P, ctx):
+    """MapPoint::ComputeDistinctiveDescriptors src/MapPoint.cc:366-448, many map points per call."""
+    rng = np.random.default_rng(5)
+    sizes = [1, 2, 3, 7, 16, 33, 64, 100, 0, 5, 31, 32, 257, 1024] + list(rng.integers(1, 60, 300))
+    seg = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    base = synth.descriptors(1, len(sizes))
+    desc = np.concatenate([synth.descriptors(10 + k, s, 0.15, np.repeat(base[k:k + 1], max(s, 1), 0)) for k, s in enumerate(sizes)])
+    want = O.distinctive_descriptors(desc, seg)
+    got = P.distinctive_descriptors(ctx, desc, seg)
+    assert np.array_equal(want, got), int((want != got).sum())
+    with pytest.raises(P.OrbxError):
+        P.distinctive_descriptors(ctx, synth.descriptors(2, 1025), np.array([0, 1025], np.int32))
+
+
 @pytest.mark.parametrize("w,h,nf,seed", [(752, 480, 1200, 3), (1241, 376, 2000, 4)])
 def test_stereo_matches_oracle(P, w, h, nf, seed):
     left, right = synth.stereo_pair(seed, w, h)

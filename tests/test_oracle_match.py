@@ -366,3 +366,64 @@ def test_search_for_initialization_vs_python():
         assert list(got) == want and ng == nw and nw > 20
         assert np.array_equal(gprev, wprev)
         assert ng == sum(1 for x in want if x >= 0)
+
+
+def py_window_best(pts, keys, desc, uright, scale, grid, th, inv_sigma2, th_dist):
+    bi, bd = [], []
+    for p in pts:
+        lvl = int(p["level"])
+        r = np.float32(np.float32(th) * scale[lvl])
+        best, idx = 2 ** 31 - 1, -1
+        for j in py_features_in_area(keys, grid, p["u"], p["v"], r, -1, -1):
+            o = int(keys["octave"][j])
+            if o < lvl - 1 or o > lvl:
+                continue
+            if inv_sigma2 is not None:
+                ex, ey = np.float32(p["u"] - keys["x"][j]), np.float32(p["v"] - keys["y"][j])
+                e2 = np.float32(np.float32(ex * ex) + np.float32(ey * ey))
+                lim = 5.99
+                if uright is not None and uright[j] >= 0:
+                    er = np.float32(p["ur"] - uright[j])
+                    e2 = np.float32(e2 + np.float32(er * er)); lim = 7.8
+                if float(np.float32(e2 * inv_sigma2[o])) > lim:
+                    continue
+            d = hamming(p["desc"], desc[j])
+            if d < best:
+                best, idx = d, j
+        bd.append(best if idx >= 0 else -1)
+        bi.append(idx if idx >= 0 and best <= th_dist else -1)
+    return bi, bd
+
+
+def test_window_best_vs_python():
+    p = O.params(1000)
+    scale = np.array(p.scale[:8], np.float32)
+    inv_sigma2 = np.array(p.inv_sigma2[:8], np.float32)
+    grid = (0.0, 0.0, np.float32(64) / np.float32(640), np.float32(48) / np.float32(480))
+    for seed, n, nq in ((7, 500, 300), (8, 900, 500)):
+        keys, desc, pts, _ = _window_scene(seed, n, nq)
+        rng = np.random.default_rng(seed)
+        uright = np.where(rng.random(n) < 0.5, keys["x"] - 6, -1).astype(np.float32)
+        pts["ur"] = pts["u"] - 6 + rng.normal(0, 2, nq).astype(np.float32)
+        for th, is2, ur, thd in ((3.0, inv_sigma2, uright, 50), (4.0, inv_sigma2, None, 50), (7.5, None, None, 100)):
+            bi, bd = O.window_best(pts, keys, desc, ur, scale, grid, th, is2, thd)
+            wi, wd = py_window_best(pts, keys, desc, ur, scale, grid, th, is2, thd)
+            assert list(bi) == wi and list(bd) == wd
+            assert sum(1 for x in wi if x >= 0) > 20
+
+
+def test_distinctive_descriptors_vs_numpy():
+    rng = np.random.default_rng(3)
+    sizes = [1, 2, 3, 7, 16, 33, 64, 100, 0, 5]
+    seg = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    base = synth.descriptors(1, len(sizes))
+    desc = np.concatenate([synth.descriptors(10 + k, s, 0.15, np.repeat(base[k:k + 1], max(s, 1), 0)) for k, s in enumerate(sizes)])
+    got = O.distinctive_descriptors(desc, seg)
+    for k, s in enumerate(sizes):
+        if s == 0:
+            assert got[k] == -1
+            continue
+        D = desc[seg[k]:seg[k + 1]]
+        dist = np.unpackbits(D[:, None, :] ^ D[None, :, :], axis=2).sum(2)
+        med = np.sort(dist, axis=1)[:, int(0.5 * (s - 1))]
+        assert got[k] == int(np.argmin(med))
