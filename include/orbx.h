@@ -74,6 +74,14 @@ int orbx_pyramid_level(orbx_ctx* ctx, int frame, int level, int border, int flag
                        size_t dst_stride, int* w, int* h);
 int orbx_level_size(const orbx_ctx* ctx, int level, int w0, int h0, int* w, int* h);
 
+/* Colour to gray in front of the extractor.  Replaces the cvtColor calls of Tracking::GrabImageStereo / RGBD / Monocular
+ * (src/Tracking.cc:252-278, 313-326, 377-390) with OpenCV's 8-bit fixed point (R*9798 + G*19235 + B*3735 + 16384) >> 15.
+ * src: interleaved 3- or 4-channel 8-bit image; dst: w x h gray (a device dst can be passed to orbx_extract with
+ * ORBX_IN_DEVICE). */
+enum { ORBX_FMT_RGB = 0, ORBX_FMT_BGR = 1, ORBX_FMT_RGBA = 2, ORBX_FMT_BGRA = 3 };
+int orbx_cvt_gray(orbx_ctx* ctx, const uint8_t* src, int w, int h, size_t stride, int format, int flags, uint8_t* dst,
+                  size_t dst_stride);
+
 /* Frames per pipeline chunk of orbx_extract_batch when the images are HOST buffers (default 64, env ORBX_CHUNK; 0 = whole
  * batch in one pass): the H2D of chunk i+1 and the D2H of chunk i-1 overlap the kernels of chunk i.  Device-resident
  * batches always run in one pass. */

@@ -537,3 +537,15 @@ int orc_extract(const orc_params* p, const uint8_t* img, int w, int h, size_t st
     free(blur); free(sel); free(cand); free(pyr);
     return status ? status : ntot;
 }
+
+/* cv::cvtColor(src, dst, RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY), 8-bit (call sites src/Tracking.cc:252-278, 313-326,
+ * 377-390; third-party OpenCV imgproc, pinned to cv2 4.13: 15-bit fixed point).  channels = 3 or 4, bgr = 1: B first. */
+void orc_cvt_gray(const uint8_t* src, int w, int h, size_t sstride, int channels, int bgr, uint8_t* dst, size_t dstride)
+{
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            const uint8_t* p = src + (size_t)y * sstride + (size_t)x * channels;
+            const int r = bgr ? p[2] : p[0], g = p[1], b = bgr ? p[0] : p[2];
+            dst[(size_t)y * dstride + x] = (uint8_t)((r * 9798 + g * 19235 + b * 3735 + 16384) >> 15);
+        }
+}

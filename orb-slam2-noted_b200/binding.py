@@ -57,6 +57,7 @@ def lib():
     L.orbx_kernel_launches.argtypes = [vp]
     L.orbx_kernel_launches.restype = ctypes.c_longlong
     L.orbx_descriptor_distance.argtypes = [vp, vp, vp, ci, ci, vp]
+    L.orbx_cvt_gray.argtypes = [vp, vp, ci, ci, sz, ci, ci, vp, sz]
     L.orbx_hamming_best2.argtypes = [vp, vp, ci, vp, ci, vp, vp, vp, vp, ci, vp, ci, vp, vp, vp]
     L.orbx_test_sincosf.argtypes = [ctypes.c_uint32, ctypes.c_uint32, vp, vp]
     L.orbx_test_fast_atan2.argtypes = [vp, ci, vp]
@@ -243,6 +244,20 @@ class _PyramidView:
 
     def __getitem__(self, level):
         return self._ex.pyramid_level(level)
+
+
+FMT_RGB, FMT_BGR, FMT_RGBA, FMT_BGRA = 0, 1, 2, 3
+
+
+def cvt_gray(ex, img, fmt=FMT_RGB):
+    """cv::cvtColor(img, gray, {RGB,BGR,RGBA,BGRA}2GRAY) as called by Tracking::GrabImage* (src/Tracking.cc:252-278) on the GPU.
+    img: (h, w, 3|4) uint8 (any row stride); returns (h, w) uint8."""
+    img = np.asarray(img, np.uint8)
+    h, w, ch = img.shape
+    assert ch == (4 if fmt & 2 else 3) and img.strides[2] == 1 and img.strides[1] == ch
+    out = np.empty((h, w), np.uint8)
+    ex._check(ex._lib.orbx_cvt_gray(ex._h, img.ctypes.data, w, h, img.strides[0], fmt, 0, _np(out), w), "orbx_cvt_gray")
+    return out
 
 
 def descriptor_distance(ex, a, b):

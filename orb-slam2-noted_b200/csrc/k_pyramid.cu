@@ -145,6 +145,56 @@ resizeLinearWordKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sF
     }
 }
 
+// cvtColor(RGB / BGR / RGBA / BGRA -> GRAY), the step in front of the extractor (src/Tracking.cc:252-278, 313-326, 377-390),
+// with OpenCV's 8-bit fixed point: (R * 9798 + G * 19235 + B * 3735 + 16384) >> 15 (cv2 4.13, the pinned dependency).
+// 4 pixels per thread: 12 or 16 source bytes in, one 32-bit store out.
+template <int kCh>
+__global__ void __launch_bounds__(256)
+cvtGrayKernel(const uint8_t* __restrict__ src, size_t sPitch, int w, int h, int bgr, uint8_t* __restrict__ dst, size_t dPitch)
+{
+    const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4, y = blockIdx.y;
+    if (x0 >= w) return;
+    const uint8_t* s = src + (size_t)y * sPitch + (size_t)x0 * kCh;
+    const uint32_t cr = bgr ? 3735u : 9798u, cb = bgr ? 9798u : 3735u;   // weights of channel 0 and channel 2
+    uint32_t px[4];
+    if (x0 + 4 <= w && ((((size_t)s) & 3) == 0)) {
+        const uint32_t* sw = reinterpret_cast<const uint32_t*>(s);
+        if (kCh == 4) {
+            #pragma unroll
+            for (int i = 0; i < 4; ++i) px[i] = __ldg(sw + i);
+        } else {
+            const uint32_t a = __ldg(sw), b = __ldg(sw + 1), c = __ldg(sw + 2);
+            px[0] = a; px[1] = __funnelshift_r(a, b, 24); px[2] = __funnelshift_r(b, c, 16); px[3] = c >> 8;
+        }
+    } else {
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint8_t* q = s + (size_t)min(i, w - 1 - x0) * kCh;
+            px[i] = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16);
+        }
+    }
+    uint32_t out = 0;
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t c0 = px[i] & 0xffu, c1 = (px[i] >> 8) & 0xffu, c2 = (px[i] >> 16) & 0xffu;
+        out |= ((c0 * cr + c1 * 19235u + c2 * cb + 16384u) >> 15) << (8 * i);
+    }
+    uint8_t* d = dst + (size_t)y * dPitch + x0;
+    if (x0 + 4 <= w && ((((size_t)d) & 3) == 0)) *reinterpret_cast<uint32_t*>(d) = out;
+    else for (int i = 0; i < min(4, w - x0); ++i) d[i] = (uint8_t)(out >> (8 * i));
+}
+
+int launchCvtGray(Ctx* c, const uint8_t* src, size_t sPitch, int w, int h, int format, uint8_t* dst, size_t dPitch)
+{
+    dim3 grid((w + 1023) / 1024, h), block(256);
+    const int bgr = format & 1;
+    if (format & 2) cvtGrayKernel<4><<<grid, block, 0, c->stream>>>(src, sPitch, w, h, bgr, dst, dPitch);
+    else cvtGrayKernel<3><<<grid, block, 0, c->stream>>>(src, sPitch, w, h, bgr, dst, dPitch);
+    c->kernelLaunches += 1;
+    ORBX_CUDA(c, cudaGetLastError());
+    return ORBX_OK;
+}
+
 int launchPyramid(Ctx* c, int frame0, int batch)
 {
     const GeomSet& g = c->geom;

@@ -546,6 +546,34 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
     return ORBX_OK;
 }
 
+int orbx_cvt_gray(orbx_ctx* h, const uint8_t* src, int w, int hgt, size_t stride, int format, int flags, uint8_t* dst, size_t dst_stride)
+{
+    if (!h || !src || !dst || w < 1 || hgt < 1 || format < 0 || format > 3) return ORBX_E_INVALID;
+    const int ch = (format & 2) ? 4 : 3;
+    if (stride < (size_t)w * ch || dst_stride < (size_t)w) return ORBX_E_INVALID;
+    Ctx* c = &h->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
+    const size_t inPitch = ((size_t)w * ch + 15) & ~(size_t)15, outPitch = ((size_t)w + 15) & ~(size_t)15;
+    const size_t inBytes = inDev ? 0 : inPitch * hgt, outBytes = outDev ? 0 : outPitch * hgt;
+    int rc = ensureScratch(c, inBytes + outBytes + 256);
+    if (rc) return rc;
+    uint8_t* S = (uint8_t*)c->dScratch;
+    const uint8_t* dS = src; size_t sP = stride;
+    if (!inDev) {
+        ORBX_CUDA(c, cudaMemcpy2DAsync(S, inPitch, src, stride, (size_t)w * ch, (size_t)hgt, cudaMemcpyHostToDevice, c->stream));
+        dS = S; sP = inPitch;
+    }
+    uint8_t* dD = outDev ? dst : S + inBytes; const size_t dP = outDev ? dst_stride : outPitch;
+    rc = launchCvtGray(c, dS, sP, w, hgt, format, dD, dP);
+    if (rc) return rc;
+    if (!outDev) {
+        ORBX_CUDA(c, cudaMemcpy2DAsync(dst, dst_stride, dD, dP, (size_t)w, (size_t)hgt, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return ORBX_OK;
+}
+
 int orbx_set_chunk(orbx_ctx* h, int frames)
 {
     if (!h || frames < 0) return ORBX_E_INVALID;

@@ -139,6 +139,7 @@ int ensureMatchPinned(Ctx* c, size_t bytes);
 // kernels (one launcher per stage; all asynchronous on c->stream) -------------------------------
 // frames [frame0, frame0 + batch) of the current batch
 int launchPyramid(Ctx* c, int frame0, int batch);
+int launchCvtGray(Ctx* c, const uint8_t* src, size_t sPitch, int w, int h, int format, uint8_t* dst, size_t dPitch);
 int launchFast(Ctx* c, int frame0, int batch);
 void buildFastStrips(const GeomSet& g, std::vector<StripDesc>& out);
 int launchOctree(Ctx* c, int frame0, int batch);

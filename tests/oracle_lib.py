@@ -108,6 +108,18 @@ def blur(src, ksize=9):
     return dst
 
 
+def cvt_gray(img, bgr=False):
+    """cv::cvtColor(..2GRAY) restatement; img: (h, w, 3|4) uint8."""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w, ch = img.shape
+    out = np.empty((h, w), np.uint8)
+    L = lib()
+    L.orc_cvt_gray.restype = None
+    L.orc_cvt_gray.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_size_t, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t]
+    L.orc_cvt_gray(_p(img), w, h, w * ch, ch, int(bgr), _p(out), w)
+    return out
+
+
 def fast_roi(roi, th):
     roi = np.ascontiguousarray(roi)
     cap = roi.size

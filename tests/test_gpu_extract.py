@@ -153,3 +153,23 @@ def test_device_input_any_alignment(P, pad_x, pad_w):
         k = np.frombuffer(kps[b, :nb].cpu().numpy().tobytes(), dtype=P.KP_DTYPE)
         okps, odesc = O.extract(p, imgs[b])
         assert_kps_equal(k, okps, desc[b, :nb].cpu().numpy(), odesc, (pad_x, pad_w, b))
+
+
+def test_cvt_gray_matches_golden_and_oracle(P):
+    """cvtColor -> gray in front of the extractor (src/Tracking.cc:252-278): cv2 golden, oracle on odd sizes / strides."""
+    import os
+    ex = P.ORBextractor(100, 1.2, 8, 20, 7, max_w=64, max_h=64)
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "cvt_gray.npz"))
+    rng = np.random.default_rng(77)
+    inputs = {"rgb": rng.integers(0, 256, (37, 61, 3), dtype=np.uint8), "bgr": rng.integers(0, 256, (40, 64, 3), dtype=np.uint8),
+              "rgba": rng.integers(0, 256, (33, 50, 4), dtype=np.uint8), "bgra": rng.integers(0, 256, (16, 31, 4), dtype=np.uint8)}
+    fm = {"rgb": P.FMT_RGB, "bgr": P.FMT_BGR, "rgba": P.FMT_RGBA, "bgra": P.FMT_BGRA}
+    for k, im in inputs.items():
+        assert np.array_equal(P.cvt_gray(ex, im, fm[k]), g[k]), k
+    for (h, w, ch, pad) in ((480, 640, 3, 0), (376, 1241, 3, 5), (1, 1, 3, 0), (7, 3, 4, 2), (1080, 1920, 4, 0), (33, 1023, 3, 1)):
+        buf = rng.integers(0, 256, (h, w + pad, ch), dtype=np.uint8)
+        im = buf[:, :w]                                   # rows with a stride the kernel has to honour
+        for bgr in (False, True):
+            want = O.cvt_gray(np.ascontiguousarray(im), bgr)
+            got = P.cvt_gray(ex, im, (2 if ch == 4 else 0) | int(bgr))
+            assert np.array_equal(want, got), (h, w, ch, pad, bgr)

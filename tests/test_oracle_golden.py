@@ -73,3 +73,16 @@ def test_ctor_tables():
     assert list(p.umax) == [15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3]
     assert O.level_sizes(p, 640, 480) == [(640, 480), (533, 400), (444, 333), (370, 278), (309, 231), (257, 193), (214, 161), (179, 134)]
     assert list(O.params(4000).nfeat_level)[:8] == [869, 724, 603, 503, 419, 349, 291, 242]
+
+
+def test_cvt_gray_matches_cv2():
+    """cvtColor RGB/BGR/RGBA/BGRA -> GRAY (src/Tracking.cc:252-278): the oracle against cv2 4.13 outputs (tests/golden/cvt_gray.npz)."""
+    g = np.load(os.path.join(G, "cvt_gray.npz"))
+    rng = np.random.default_rng(77)
+    inputs = {"rgb": rng.integers(0, 256, (37, 61, 3), dtype=np.uint8), "bgr": rng.integers(0, 256, (40, 64, 3), dtype=np.uint8),
+              "rgba": rng.integers(0, 256, (33, 50, 4), dtype=np.uint8), "bgra": rng.integers(0, 256, (16, 31, 4), dtype=np.uint8)}
+    for k, im in inputs.items():
+        assert np.array_equal(O.cvt_gray(im, bgr=k.startswith("bgr")), g[k]), k
+    r_, g_, b_ = np.meshgrid(np.arange(256), np.arange(256), np.arange(0, 256, 3), indexing="ij")
+    sweep = np.stack([r_, g_, b_], -1).astype(np.uint8).reshape(256, -1, 3)
+    assert sha(O.cvt_gray(sweep)) == str(g["sweep_sha"])

@@ -17,6 +17,20 @@ os.makedirs(G, exist_ok=True)
 
 def sha(a): return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 
+# --- cvtColor -> gray (separate small fixture; `gen_golden.py --only-cvt` regenerates just this one) ---
+def cvt_inputs():
+    rng = np.random.default_rng(77)
+    return {"rgb": rng.integers(0, 256, (37, 61, 3), dtype=np.uint8), "bgr": rng.integers(0, 256, (40, 64, 3), dtype=np.uint8),
+            "rgba": rng.integers(0, 256, (33, 50, 4), dtype=np.uint8), "bgra": rng.integers(0, 256, (16, 31, 4), dtype=np.uint8)}
+codes = {"rgb": cv2.COLOR_RGB2GRAY, "bgr": cv2.COLOR_BGR2GRAY, "rgba": cv2.COLOR_RGBA2GRAY, "bgra": cv2.COLOR_BGRA2GRAY}
+cvt = {k: cv2.cvtColor(v, codes[k]) for k, v in cvt_inputs().items()}
+r_, g_, b_ = np.meshgrid(np.arange(256), np.arange(256), np.arange(0, 256, 3), indexing="ij")
+sweep = np.stack([r_, g_, b_], -1).astype(np.uint8).reshape(256, -1, 3)      # every (R, G) with every third B
+cvt["sweep_sha"] = np.array(sha(cv2.cvtColor(sweep, cv2.COLOR_RGB2GRAY)))
+np.savez_compressed(os.path.join(G, "cvt_gray.npz"), **cvt)
+if "--only-cvt" in sys.argv:
+    sys.exit(0)
+
 # --- primitives ---
 prim = {}
 img = synth.frame(11, 213, 160, "blocks")
