@@ -268,6 +268,7 @@ int orbx_create(orbx_ctx** out, int device, int nfeatures, float scale_factor, i
         if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (const char* e = getenv("ORBX_CHUNK")) c->chunk = atoi(e);
+        if (const char* e = getenv("ORBX_OVERLAP_BLUR")) c->overlapBlur = atoi(e) != 0;
         if (const char* e = getenv("ORBX_FAST_THREADS")) c->fastThreads = atoi(e) == 128 ? 128 : 256;
         if (const char* e = getenv("ORBX_FAST_SEGW")) c->fastSegW = std::max(64, std::min(640, atoi(e)));
         if (cudaMalloc(&c->dGeom, sizeof(GeomSet)) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
@@ -303,6 +304,9 @@ void orbx_destroy(orbx_ctx* h)
     if (c->sOut) cudaStreamDestroy(c->sOut);
     if (c->stream2) cudaStreamDestroy(c->stream2);
     if (c->evJoin) cudaEventDestroy(c->evJoin);
+    if (c->evFork) cudaEventDestroy(c->evFork);
+    if (c->evBlur) cudaEventDestroy(c->evBlur);
+    if (c->sBlur) cudaStreamDestroy(c->sBlur);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete h;
 }
@@ -501,9 +505,29 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
             ORBX_CUDA(c, cudaStreamWaitEvent(c->stream, c->evIn[i], 0));
         }
         rc = launchPyramid(c, f0, n);
-        if (!rc) rc = launchFast(c, f0, n);
-        if (!rc) rc = launchOctree(c, f0, n);
-        if (!rc) rc = launchBlur(c, f0, n);
+        if (!rc && c->overlapBlur && !twoStreams) {
+            // the blur only needs the pyramid: it runs on a side stream next to FAST + quadtree (FAST is limited to 5 CTAs per
+            // SM by shared memory and leaves registers, shared memory and issue slots for a blur CTA) and joins before describe
+            cudaStream_t const s0 = c->stream;
+            if (!c->sBlur) {
+                ORBX_CUDA(c, cudaStreamCreateWithFlags(&c->sBlur, cudaStreamNonBlocking));
+                ORBX_CUDA(c, cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
+                ORBX_CUDA(c, cudaEventCreateWithFlags(&c->evBlur, cudaEventDisableTiming));
+            }
+            ORBX_CUDA(c, cudaEventRecord(c->evFork, s0));
+            ORBX_CUDA(c, cudaStreamWaitEvent(c->sBlur, c->evFork, 0));
+            rc = launchFast(c, f0, n);
+            c->stream = c->sBlur;
+            if (!rc) rc = launchBlur(c, f0, n);
+            c->stream = s0;
+            if (!rc) rc = launchOctree(c, f0, n);
+            ORBX_CUDA(c, cudaEventRecord(c->evBlur, c->sBlur));
+            ORBX_CUDA(c, cudaStreamWaitEvent(s0, c->evBlur, 0));
+        } else {
+            if (!rc) rc = launchFast(c, f0, n);
+            if (!rc) rc = launchOctree(c, f0, n);
+            if (!rc) rc = launchBlur(c, f0, n);
+        }
         if (!rc) rc = launchDescribe(c, f0, n, dK, dD, sc, dN);
         if (rc) { c->stream = mainStream; return rc; }
         if (!outDev) {

@@ -65,6 +65,8 @@ struct Ctx {
     cudaStream_t sIn = nullptr, sOut = nullptr;   // copy streams of the chunked pipeline (H2D / D2H overlap compute)
     cudaStream_t stream2 = nullptr;               // odd chunks of the pipeline run here, so kernels of neighbouring chunks fill each other's tails
     cudaEvent_t evJoin = nullptr;
+    cudaStream_t sBlur = nullptr; cudaEvent_t evFork = nullptr, evBlur = nullptr;   // blur next to FAST + quadtree (device-resident batches)
+    bool overlapBlur = false;                      // env ORBX_OVERLAP_BLUR=1: no gain at 640x480 (the kernels are throughput-bound), ~4 % at 1241x376
     std::vector<cudaEvent_t> evIn, evDone;
     cudaEvent_t evFence = nullptr;                // orders a new call's H2D after the previous call's kernels
     int fastThreads = 128, fastSegW = 320;         // FAST strip shape: threads per CTA, max candidate columns per strip
