@@ -130,6 +130,19 @@ int orbx_bow_transform(orbx_ctx* ctx, const orbx_vocab* v, const uint8_t* desc, 
 /* FeatureVector (FeatureVector.cpp:37-54) as CSR from the per-feature node ids (features with weight <= 0 dropped,
  * TemplatedVocabulary.h:1184): ascending node id, ascending feature index inside a node.  Host index glue.
  * node_id[nn], node_off[nn+1], feat[<= n]; returns nn through *nnodes. */
+/* The BowVector half of transform (TemplatedVocabulary.h:1166-1221: addWeight per feature, BowVector.cpp:37-49; then
+ * BowVector::normalize(L1), BowVector.cpp:59-82) for TF-IDF / L1 vocabularies such as ORBvoc, and L1Scoring::score
+ * (ScoringObject.cpp:28-61) of a query vector against many database vectors (KeyFrameDatabase::DetectLoopCandidates /
+ * DetectRelocalizationCandidates, src/KeyFrameDatabase.cc).  WordValue is a double; sums run in the reference's order, so
+ * results are bit-equal.  word = the word id of every feature (orbx_bow_transform, n <= 16384); ids / values (capacity n) receive the
+ * vector in ascending word id, *nwords its size.  orbx_vocab_set_word_weights replaces the per-word weights by exact
+ * doubles (orbx_vocab_create takes floats; the text loader calls it with the parsed values). */
+int orbx_vocab_set_word_weights(orbx_vocab* v, const double* weights, int nwords);
+int orbx_bow_vector(orbx_ctx* ctx, const orbx_vocab* v, const int32_t* word, int n, int flags, int32_t* ids, double* values,
+                    int* nwords);
+/* seg: HOST array of nvec + 1 offsets into ids / vals; score[j] = L1 score of the query against vector j. */
+int orbx_bow_score_l1(orbx_ctx* ctx, const int32_t* q_ids, const double* q_vals, int nq, const int32_t* ids, const double* vals,
+                      const int32_t* seg, int nvec, int flags, double* score);
 int orbx_feature_vector(const int32_t* node, const float* weight, int n, int32_t* node_id, int32_t* node_off,
                         int32_t* feat, int* nnodes);
 

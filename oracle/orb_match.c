@@ -651,6 +651,42 @@ void orc_distinctive_descriptors(const uint8_t* desc, const int32_t* seg, int np
     }
 }
 
+/* BowVector of TemplatedVocabulary::transform for a TF-IDF / L1 vocabulary (TemplatedVocabulary.h:1166-1221): every feature
+ * whose word weight is > 0 does v.addWeight(id, w) in feature order (BowVector.cpp:37-49: insert, then +=), then
+ * BowVector::normalize(L1) (BowVector.cpp:59-82: norm summed in ascending id, every value divided).  word_weight is indexed by
+ * word id (WordValue = double).  Returns the number of words; ids ascending. */
+int orc_bow_vector(const int32_t* word, int n, const double* word_weight, int nword_ids, int32_t* ids, double* values)
+{
+    double* acc = (double*)calloc((size_t)(nword_ids > 0 ? nword_ids : 1), sizeof(double));
+    uint8_t* seen = (uint8_t*)calloc((size_t)(nword_ids > 0 ? nword_ids : 1), 1);
+    for (int f = 0; f < n; ++f) {
+        const int id = word[f];
+        if (id < 0 || id >= nword_ids) continue;
+        const double w = word_weight[id];
+        if (!(w > 0)) continue;
+        if (seen[id]) acc[id] += w; else { acc[id] = w; seen[id] = 1; }
+    }
+    int nw = 0;
+    double norm = 0.0;
+    for (int id = 0; id < nword_ids; ++id) if (seen[id]) { ids[nw] = id; values[nw] = acc[id]; norm += fabs(acc[id]); ++nw; }
+    if (norm > 0.0) for (int i = 0; i < nw; ++i) values[i] /= norm;
+    free(acc); free(seen);
+    return nw;
+}
+
+/* L1Scoring::score, ScoringObject.cpp:28-61 */
+double orc_bow_score_l1(const int32_t* ids1, const double* v1, int n1, const int32_t* ids2, const double* v2, int n2)
+{
+    int a = 0, b = 0;
+    double score = 0;
+    while (a < n1 && b < n2) {
+        if (ids1[a] == ids2[b]) { const double vi = v1[a], wi = v2[b]; score += fabs(vi - wi) - fabs(vi) - fabs(wi); ++a; ++b; }
+        else if (ids1[a] < ids2[b]) { while (a < n1 && ids1[a] < ids2[b]) ++a; }      /* lower_bound */
+        else { while (b < n2 && ids2[b] < ids1[a]) ++b; }
+    }
+    return -score / 2.0;
+}
+
 /* ---------------- Frame::ComputeStereoMatches: src/Frame.cc:831-1128 ----------------
  * pyrL/pyrR: un-bordered level images packed back to back (level l at lvl_off[l], size lvl_w[l] x lvl_h[l]). */
 typedef struct { int d, i; } distidx;

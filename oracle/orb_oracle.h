@@ -132,6 +132,8 @@ void orc_window_best(const orc_projpoint* pts, int npts, const orc_keypoint* key
                      const float* scale, const orc_grid* g, const int32_t* cell_off, const int32_t* cell_idx, float th,
                      const float* inv_sigma2, int th_dist, int32_t* best_idx, int32_t* best_dist); /* Fuse x2, SearchBySim3 */
 void orc_distinctive_descriptors(const uint8_t* desc, const int32_t* seg, int npoints, int32_t* best); /* src/MapPoint.cc:366-448 */
+int orc_bow_vector(const int32_t* word, int n, const double* word_weight, int nword_ids, int32_t* ids, double* values); /* transform's BowVector */
+double orc_bow_score_l1(const int32_t* ids1, const double* v1, int n1, const int32_t* ids2, const double* v2, int n2); /* ScoringObject.cpp:28-61 */
 int orc_stereo_matches(const orc_keypoint* kL, const uint8_t* dL, int N, const orc_keypoint* kR, const uint8_t* dR, int Nr,
                        const uint8_t* pyrL, const uint8_t* pyrR, const int* lvl_w, const int* lvl_h, const size_t* lvl_off,
                        const float* scale, const float* inv_scale, float mbf, float mb, float* uRight, float* depth);

@@ -12,10 +12,13 @@
 #include <fstream>
 #include <sstream>
 #include <new>
+#include <vector>
 
 struct orbx_vocab {
     int device = 0, k = 0, L = 0, nnodes = 0, nwords = 0;
     int32_t* dChildOff = nullptr; int32_t* dChild = nullptr; uint4* dDesc = nullptr; int32_t* dWord = nullptr; float* dWeight = nullptr;
+    double* dWordWeight = nullptr;      // weight of word id w as a double (WordValue), for the BowVector
+    int wordCap = 0;                    // 1 + largest word id
 };
 
 namespace orbx {
@@ -53,6 +56,113 @@ bowTransformKernel(const int32_t* __restrict__ childOff, const int32_t* __restri
     if (lane == 0) { outWord[f] = wordId[node]; outWeight[f] = weight[node]; outNode[f] = nid; }
 }
 
+// ---------------- BowVector + L1 score (the step after transform) ----------------
+// TemplatedVocabulary::transform's BowVector half (TemplatedVocabulary.h:1166-1221: addWeight per feature in feature
+// order, then BowVector::normalize(L1), BowVector.cpp:37-49,59-82) and L1Scoring::score (ScoringObject.cpp:28-61).
+// WordValue is a double and the reference adds in a fixed order (features of a word in feature order; the norm and the
+// score in ascending word id), so the sums here are sequential in exactly that order; everything around them is parallel.
+constexpr int kBowThreads = 1024;
+
+__global__ void __launch_bounds__(kBowThreads)
+bowVectorKernel(const int32_t* __restrict__ word, int n, int npow2, const double* __restrict__ wordWeight, int wordCap,
+                int32_t* __restrict__ ids, double* __restrict__ values, int* __restrict__ nOut)
+{
+    extern __shared__ unsigned long long keys[];        // (word << 32 | feature), sorted; later reused for the sums
+    __shared__ int sWarpTot[32];
+    __shared__ int sTotal;
+    __shared__ double sNorm;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < npow2; i += kBowThreads) {
+        unsigned long long k = ~0ull;
+        if (i < n) {
+            const int w = word[i];
+            if (w >= 0 && w < wordCap && wordWeight[w] > 0.0) k = ((unsigned long long)(uint32_t)w << 32) | (uint32_t)i;   // w > 0: not stopped (:1181)
+        }
+        keys[i] = k;
+    }
+    __syncthreads();
+    for (int size = 2; size <= npow2; size <<= 1)
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            for (int t = tid; t < (npow2 >> 1); t += kBowThreads) {
+                const int lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+                const bool up = (lo & size) == 0;
+                const unsigned long long a = keys[lo], b = keys[hi];
+                if ((a > b) == up) { keys[lo] = b; keys[hi] = a; }
+            }
+            __syncthreads();
+        }
+    // heads of the runs of equal word id, compacted in order
+    const int per = npow2 / kBowThreads > 0 ? npow2 / kBowThreads : 1;
+    const int i0 = tid * per;
+    int cnt = 0;
+    for (int i = i0; i < i0 + per && i < npow2; ++i) {
+        const unsigned long long k = keys[i];
+        if (k != ~0ull && (i == 0 || (uint32_t)(keys[i - 1] >> 32) != (uint32_t)(k >> 32))) ++cnt;
+    }
+    int incl = cnt;
+    #pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if ((tid & 31) >= o) incl += t; }
+    if ((tid & 31) == 31) sWarpTot[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+        int v = sWarpTot[tid], iv = v;
+        #pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, iv, o); if (tid >= o) iv += t; }
+        sWarpTot[tid] = iv - v;
+        if (tid == 31) sTotal = iv;
+    }
+    __syncthreads();
+    int pos = sWarpTot[tid >> 5] + incl - cnt;
+    for (int i = i0; i < i0 + per && i < npow2; ++i) {
+        const unsigned long long k = keys[i];
+        if (k == ~0ull) break;
+        const uint32_t w = (uint32_t)(k >> 32);
+        if (i == 0 || (uint32_t)(keys[i - 1] >> 32) != w) {
+            const double ww = wordWeight[w];
+            double sum = ww;                                 // first addWeight inserts, the others add (feature order)
+            for (int j = i + 1; j < npow2 && (uint32_t)(keys[j] >> 32) == w && keys[j] != ~0ull; ++j) sum += ww;
+            ids[pos] = (int32_t)w; values[pos] = sum;
+            ++pos;
+        }
+    }
+    __syncthreads();
+    const int nw = sTotal;
+    double* sums = reinterpret_cast<double*>(keys);          // the sort buffer is free now
+    for (int p = tid; p < nw; p += kBowThreads) sums[p] = values[p];
+    __syncthreads();
+    if (tid == 0) {
+        double norm = 0.0;
+        for (int p = 0; p < nw; ++p) norm += fabs(sums[p]);  // BowVector::normalize(L1): ascending word id
+        sNorm = norm;
+        *nOut = nw;
+    }
+    __syncthreads();
+    const double norm = sNorm;
+    if (norm > 0.0) for (int p = tid; p < nw; p += kBowThreads) values[p] = sums[p] / norm;
+}
+
+// One thread per database vector: L1Scoring::score(query, vector).  The reference's lower_bound jumps visit the common
+// word ids in ascending order, which is what the linear merge does.
+__global__ void __launch_bounds__(128)
+bowScoreL1Kernel(const int32_t* __restrict__ qIds, const double* __restrict__ qVal, int nq, const int32_t* __restrict__ ids,
+                 const double* __restrict__ vals, const int32_t* __restrict__ seg, int nvec, double* __restrict__ score)
+{
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nvec) return;
+    int a = 0, b = seg[v];
+    const int bEnd = seg[v + 1];
+    double s = 0.0;
+    while (a < nq && b < bEnd) {
+        const int ia = qIds[a], ib = ids[b];
+        if (ia == ib) {
+            const double vi = qVal[a], wi = vals[b];
+            s += fabs(vi - wi) - fabs(vi) - fabs(wi);
+            ++a; ++b;
+        } else if (ia < ib) ++a; else ++b;
+    }
+    score[v] = -s / 2.0;
+}
+
 } // namespace orbx
 using namespace orbx;
 
@@ -81,6 +191,14 @@ extern "C" int orbx_vocab_create(orbx_ctx* h, int k, int L, int nnodes, const in
     up((void**)&v->dDesc, node_desc, (size_t)32 * nnodes);
     up((void**)&v->dWord, word_id, sizeof(int32_t) * (size_t)nnodes);
     up((void**)&v->dWeight, weight, sizeof(float) * (size_t)nnodes);
+    {
+        int cap = 0;
+        for (int i = 0; i < nnodes; ++i) if (child_off[i + 1] == child_off[i] && word_id[i] >= cap) cap = word_id[i] + 1;
+        std::vector<double> ww((size_t)std::max(cap, 1), 0.0);
+        for (int i = 0; i < nnodes; ++i) if (child_off[i + 1] == child_off[i] && word_id[i] >= 0) ww[word_id[i]] = (double)weight[i];
+        v->wordCap = cap;
+        up((void**)&v->dWordWeight, ww.data(), sizeof(double) * ww.size());
+    }
     if (e != cudaSuccess) { orbx_vocab_destroy(v); return cudaFail(c, e, "orbx_vocab_create"); }
     *out = v;
     return ORBX_OK;
@@ -90,7 +208,7 @@ extern "C" void orbx_vocab_destroy(orbx_vocab* v)
 {
     if (!v) return;
     cudaSetDevice(v->device);
-    void* p[] = {v->dChildOff, v->dChild, v->dDesc, v->dWord, v->dWeight};
+    void* p[] = {v->dChildOff, v->dChild, v->dDesc, v->dWord, v->dWeight, v->dWordWeight};
     for (void* q : p) if (q) cudaFree(q);
     delete v;
 }
@@ -120,6 +238,7 @@ extern "C" int orbx_vocab_load_text(orbx_ctx* h, const char* path, orbx_vocab** 
     std::vector<int32_t> parent(1, -1), leaf(1, 0);
     std::vector<uint8_t> desc(32, 0);
     std::vector<float> weight(1, 0.f);
+    std::vector<double> weight64(1, 0.0);          // WordValue is a double in DBoW2: the BowVector uses the parsed value
     while (std::getline(f, line)) {
         if (line.find_first_not_of(" \t\r\n") == std::string::npos) continue; // the reference's trailing phantom node is never visited
         std::stringstream ss(line);
@@ -128,7 +247,7 @@ extern "C" int orbx_vocab_load_text(orbx_ctx* h, const char* path, orbx_vocab** 
         if (pid < 0 || pid >= (int)parent.size()) return ORBX_E_INVALID;
         parent.push_back(pid); leaf.push_back(isLeaf);
         for (int i = 0; i < 32; ++i) { int b = 0; ss >> b; desc.push_back((uint8_t)b); }
-        double w = 0; ss >> w; weight.push_back((float)w);
+        double w = 0; ss >> w; weight.push_back((float)w); weight64.push_back(w);
     }
     const int nn = (int)parent.size();
     std::vector<int32_t> off((size_t)nn + 1, 0), child((size_t)(nn > 1 ? nn - 1 : 0)), word((size_t)nn, 0);
@@ -138,7 +257,103 @@ extern "C" int orbx_vocab_load_text(orbx_ctx* h, const char* path, orbx_vocab** 
     for (int i = 1; i < nn; ++i) child[fill[parent[i]]++] = i; // ascending id = push_back order (:1448)
     int wid = 0;
     for (int i = 1; i < nn; ++i) if (leaf[i] > 0) word[i] = wid++; // :1467-1473
-    return orbx_vocab_create(h, k, L, nn, off.data(), child.data(), desc.data(), word.data(), weight.data(), out);
+    int rc = orbx_vocab_create(h, k, L, nn, off.data(), child.data(), desc.data(), word.data(), weight.data(), out);
+    if (rc) return rc;
+    std::vector<double> ww((size_t)std::max(wid, 1), 0.0);
+    for (int i = 1; i < nn; ++i) if (leaf[i] > 0) ww[word[i]] = weight64[i];
+    return orbx_vocab_set_word_weights(*out, ww.data(), wid);
+}
+
+extern "C" int orbx_vocab_set_word_weights(orbx_vocab* v, const double* weights, int nwords)
+{
+    if (!v || !weights || nwords != v->wordCap) return ORBX_E_INVALID;
+    if (cudaSetDevice(v->device) != cudaSuccess) return ORBX_E_CUDA;
+    if (nwords > 0 && cudaMemcpy(v->dWordWeight, weights, sizeof(double) * (size_t)nwords, cudaMemcpyHostToDevice) != cudaSuccess) return ORBX_E_CUDA;
+    return ORBX_OK;
+}
+
+// word: the word id of every feature (orbx_bow_transform); ids / values receive the BowVector (ascending word id).
+extern "C" int orbx_bow_vector(orbx_ctx* h, const orbx_vocab* v, const int32_t* word, int n, int flags, int32_t* ids, double* values,
+                               int* nwords)
+{
+    if (!h || !v || n < 0 || !nwords || (n > 0 && (!word || !ids || !values))) return ORBX_E_INVALID;
+    *nwords = 0;
+    if (n == 0) return ORBX_OK;
+    Ctx* c = &h->c;
+    if (c->device != v->device) return ORBX_E_INVALID;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    int npow2 = 32;
+    while (npow2 < n) npow2 <<= 1;
+    const size_t smem = sizeof(unsigned long long) * (size_t)npow2;
+    if (smem > 200 * 1024) return ORBX_E_CAPACITY;              // at most 16 384 features per call (power-of-two sort buffer)
+    const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
+    const size_t oW = 0, oI = (sizeof(int32_t) * (size_t)n + 255) & ~(size_t)255, oV = oI + ((sizeof(int32_t) * (size_t)n + 255) & ~(size_t)255),
+                 oN = oV + sizeof(double) * (size_t)n;
+    int rc = ensureScratch(c, oN + 256);
+    if (rc) return rc;
+    rc = ensureMatchPinned(c, sizeof(int));
+    if (rc) return rc;
+    uint8_t* S = (uint8_t*)c->dScratch;
+    const int32_t* dW = word;
+    if (!inDev) { ORBX_CUDA(c, cudaMemcpyAsync(S + oW, word, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, c->stream)); dW = (const int32_t*)(S + oW); }
+    int32_t* dI = outDev ? ids : (int32_t*)(S + oI);
+    double* dV = outDev ? values : (double*)(S + oV);
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        ORBX_CUDA(c, cudaFuncSetAttribute(bowVectorKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    stageBegin(c, ST_BOW);
+    bowVectorKernel<<<1, kBowThreads, smem, c->stream>>>(dW, n, npow2, v->dWordWeight, v->wordCap, dI, dV, (int*)(S + oN));
+    stageEnd(c, ST_BOW, 1);
+    ORBX_CUDA(c, cudaGetLastError());
+    int* HN = (int*)c->hMatch;
+    ORBX_CUDA(c, cudaMemcpyAsync(HN, S + oN, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    *nwords = *HN;
+    if (!outDev && *nwords > 0) {
+        ORBX_CUDA(c, cudaMemcpyAsync(ids, dI, sizeof(int32_t) * (size_t)*nwords, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaMemcpyAsync(values, dV, sizeof(double) * (size_t)*nwords, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return ORBX_OK;
+}
+
+// L1Scoring::score of one query BowVector against nvec database vectors (ids / vals back to back, seg = HOST offsets).
+extern "C" int orbx_bow_score_l1(orbx_ctx* h, const int32_t* q_ids, const double* q_vals, int nq, const int32_t* ids, const double* vals,
+                                 const int32_t* seg, int nvec, int flags, double* score)
+{
+    if (!h || nq < 0 || nvec < 0 || (nq > 0 && (!q_ids || !q_vals)) || (nvec > 0 && (!seg || !score))) return ORBX_E_INVALID;
+    if (nvec == 0) return ORBX_OK;
+    const int total = seg[nvec];
+    if (total < 0 || (total > 0 && (!ids || !vals))) return ORBX_E_INVALID;
+    Ctx* c = &h->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
+    auto al = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t oQV = 0, oV = oQV + al(sizeof(double) * (size_t)std::max(nq, 1)), oS = oV + al(sizeof(double) * (size_t)std::max(total, 1)),
+                 oQI = oS + al(sizeof(double) * (size_t)nvec), oI = oQI + al(sizeof(int32_t) * (size_t)std::max(nq, 1)),
+                 oSeg = oI + al(sizeof(int32_t) * (size_t)std::max(total, 1)), end = oSeg + al(sizeof(int32_t) * (size_t)(nvec + 1));
+    int rc = ensureScratch(c, end);
+    if (rc) return rc;
+    uint8_t* S = (uint8_t*)c->dScratch;
+    const int32_t *dQI = q_ids, *dI = ids; const double *dQV = q_vals, *dV = vals;
+    if (!inDev) {
+        if (nq) { ORBX_CUDA(c, cudaMemcpyAsync(S + oQI, q_ids, sizeof(int32_t) * (size_t)nq, cudaMemcpyHostToDevice, c->stream));
+                  ORBX_CUDA(c, cudaMemcpyAsync(S + oQV, q_vals, sizeof(double) * (size_t)nq, cudaMemcpyHostToDevice, c->stream)); }
+        if (total) { ORBX_CUDA(c, cudaMemcpyAsync(S + oI, ids, sizeof(int32_t) * (size_t)total, cudaMemcpyHostToDevice, c->stream));
+                     ORBX_CUDA(c, cudaMemcpyAsync(S + oV, vals, sizeof(double) * (size_t)total, cudaMemcpyHostToDevice, c->stream)); }
+        dQI = (const int32_t*)(S + oQI); dQV = (const double*)(S + oQV); dI = (const int32_t*)(S + oI); dV = (const double*)(S + oV);
+    }
+    ORBX_CUDA(c, cudaMemcpyAsync(S + oSeg, seg, sizeof(int32_t) * (size_t)(nvec + 1), cudaMemcpyHostToDevice, c->stream));
+    double* dS = outDev ? score : (double*)(S + oS);
+    stageBegin(c, ST_BOW);
+    bowScoreL1Kernel<<<(nvec + 127) / 128, 128, 0, c->stream>>>(dQI, dQV, nq, dI, dV, (const int32_t*)(S + oSeg), nvec, dS);
+    stageEnd(c, ST_BOW, 1);
+    ORBX_CUDA(c, cudaGetLastError());
+    if (!outDev) ORBX_CUDA(c, cudaMemcpyAsync(score, dS, sizeof(double) * (size_t)nvec, cudaMemcpyDeviceToHost, c->stream));
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return ORBX_OK;
 }
 
 extern "C" int orbx_bow_transform(orbx_ctx* h, const orbx_vocab* v, const uint8_t* desc, int n, int levelsup, int flags,

@@ -61,6 +61,9 @@ def _mlib():
     L.orbx_search_for_initialization.argtypes = [vp, vp, vp, ci, vp, vp, vp, ci, ctypes.POINTER(_Grid), ci, cf, ci, ci, vp, ip]
     L.orbx_window_best.argtypes = [vp, vp, ci, vp, vp, vp, ci, ctypes.POINTER(_Grid), vp, ci, ci, vp, vp]
     L.orbx_distinctive_descriptors.argtypes = [vp, vp, vp, ci, ci, vp]
+    L.orbx_vocab_set_word_weights.argtypes = [vp, vp, ci]
+    L.orbx_bow_vector.argtypes = [vp, vp, vp, ci, ci, vp, vp, ip]
+    L.orbx_bow_score_l1.argtypes = [vp, vp, vp, ci, vp, vp, vp, ci, ci, vp]
     L.orbx_stereo_match.argtypes = [vp, vp, ci, vp, vp, ci, vp, vp, ci, cf, cf, ci, vp, vp, ip]
     _ready = True
     return L
@@ -98,6 +101,20 @@ class Vocabulary:
         _chk(self._ex, _mlib().orbx_bow_transform(self._ex._h, self._v, _np(desc), n, levelsup, 0, _np(word), _np(weight), _np(node)),
              "orbx_bow_transform")
         return word, weight, node
+
+    def set_word_weights(self, weights):
+        """Exact double weights per word id (WordValue); orbx_vocab_create takes floats, the text loader sets these itself."""
+        w = np.ascontiguousarray(weights, np.float64)
+        _chk(self._ex, _mlib().orbx_vocab_set_word_weights(self._v, _np(w), len(w)), "orbx_vocab_set_word_weights")
+
+    def bow_vector(self, word):
+        """BowVector of transform (TF-IDF weights, L1 norm) from the features' word ids -> (ids ascending, double values)."""
+        word = np.ascontiguousarray(word, np.int32)
+        ids, vals = np.empty(max(len(word), 1), np.int32), np.empty(max(len(word), 1), np.float64)
+        n = ctypes.c_int()
+        _chk(self._ex, _mlib().orbx_bow_vector(self._ex._h, self._v, _np(word), len(word), 0, _np(ids), _np(vals), ctypes.byref(n)),
+             "orbx_bow_vector")
+        return ids[:n.value].copy(), vals[:n.value].copy()
 
     def close(self):
         if self._v:
@@ -245,6 +262,18 @@ def window_best(ex, frame, queries, grid, th_dist, inv_sigma2=None, grid_dims=(F
                                   _np(is2), int(th_dist), 0, _np(bi), _np(bd))
     _chk(ex, rc, "orbx_window_best")
     return bi[:len(q)], bd[:len(q)]
+
+
+def bow_score_l1(ex, q_ids, q_vals, vectors):
+    """L1Scoring::score (ScoringObject.cpp:28-61) of one BowVector against many: vectors = list of (ids, values)."""
+    q_ids = np.ascontiguousarray(q_ids, np.int32); q_vals = np.ascontiguousarray(q_vals, np.float64)
+    seg = np.concatenate([[0], np.cumsum([len(v[0]) for v in vectors])]).astype(np.int32)
+    ids = np.ascontiguousarray(np.concatenate([np.asarray(v[0], np.int32) for v in vectors] + [np.zeros(0, np.int32)]), np.int32)
+    vals = np.ascontiguousarray(np.concatenate([np.asarray(v[1], np.float64) for v in vectors] + [np.zeros(0, np.float64)]), np.float64)
+    out = np.empty(max(len(vectors), 1), np.float64)
+    _chk(ex, _mlib().orbx_bow_score_l1(ex._h, _np(q_ids), _np(q_vals), len(q_ids), _np(ids), _np(vals), _np(seg), len(vectors), 0, _np(out)),
+         "orbx_bow_score_l1")
+    return out[:len(vectors)]
 
 
 def distinctive_descriptors(ex, desc, seg):

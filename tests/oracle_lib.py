@@ -204,6 +204,9 @@ def _mlib():
     L.orc_window_best.restype = None
     L.orc_distinctive_descriptors.argtypes = [vp, vp, ci, vp]
     L.orc_distinctive_descriptors.restype = None
+    L.orc_bow_vector.argtypes = [vp, ci, vp, ci, vp, vp]
+    L.orc_bow_score_l1.argtypes = [vp, vp, ci, vp, vp, ci]
+    L.orc_bow_score_l1.restype = ctypes.c_double
     L.orc_stereo_matches.argtypes = [vp, vp, ci, vp, vp, ci, vp, vp, vp, vp, vp, vp, vp, cf, cf, vp, vp]
     L.orc_hamming_best2.argtypes = [vp, vp, vp, vp, vp, vp, ci, vp, vp, vp, vp]
     L._match_ready = True
@@ -372,6 +375,20 @@ def window_best(pts, keys, desc, uright, scale, grid, th, inv_sigma2, th_dist):
     _mlib().orc_window_best(_p(pts), len(pts), _p(keys), _p(desc), None if ur is None else _p(ur), len(keys), _p(scale), ctypes.byref(g),
                             _p(off), _p(idx), th, None if is2 is None else _p(is2), int(th_dist), _p(bi), _p(bd))
     return bi[:len(pts)], bd[:len(pts)]
+
+
+def bow_vector(word, word_weight):
+    """BowVector (ids ascending, L1-normalised double values) of the features' word ids; word_weight[id] = WordValue."""
+    word = np.ascontiguousarray(word, np.int32); ww = np.ascontiguousarray(word_weight, np.float64)
+    ids = np.empty(max(len(word), 1), np.int32); vals = np.empty(max(len(word), 1), np.float64)
+    n = _mlib().orc_bow_vector(_p(word), len(word), _p(ww), len(ww), _p(ids), _p(vals))
+    return ids[:n].copy(), vals[:n].copy()
+
+
+def bow_score_l1(ids1, v1, ids2, v2):
+    ids1 = np.ascontiguousarray(ids1, np.int32); ids2 = np.ascontiguousarray(ids2, np.int32)
+    v1 = np.ascontiguousarray(v1, np.float64); v2 = np.ascontiguousarray(v2, np.float64)
+    return _mlib().orc_bow_score_l1(_p(ids1), _p(v1), len(ids1), _p(ids2), _p(v2), len(ids2))
 
 
 def distinctive_descriptors(desc, seg):

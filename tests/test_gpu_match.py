@@ -258,6 +258,46 @@ def test_window_best_matches_oracle(P, ctx, seed, n, nq):
         assert (wi >= 0).sum() > 5
 
 
+def test_bow_vector_and_l1_score_match_oracle(P, ctx, vocs, tmp_path):
+    """BowVector of transform (addWeight in feature order + L1 normalisation, doubles) and L1Scoring::score against many
+    database vectors: bit-equal doubles.  Also the text loader's exact double weights."""
+    from test_oracle_match import bow_scene
+    v, vo, vg = vocs
+    nwords = vg.info()[3]
+    rng = np.random.default_rng(9)
+    ww = rng.random(nwords) * 3 + 0.01
+    ww[rng.random(nwords) < 0.05] = 0.0
+    vg.set_word_weights(ww)
+    vecs_o, vecs_g = [], []
+    for seed, nfeat in ((1, 1500), (2, 4000), (3, 1), (4, 10000), (5, 300), (6, 16384)):
+        word = np.random.default_rng(seed).integers(0, nwords, nfeat).astype(np.int32)
+        word[: nfeat // 3] = word[0]
+        io, vo_ = O.bow_vector(word, ww)
+        ig, vg_ = vg.bow_vector(word)
+        assert np.array_equal(io, ig) and np.array_equal(vo_.view(np.uint64), vg_.view(np.uint64)), (seed, nfeat)
+        vecs_o.append((io, vo_)); vecs_g.append((ig, vg_))
+    with pytest.raises(P.OrbxError):
+        vg.bow_vector(np.zeros(20000, np.int32))                      # more than 16384 features per call
+    want = np.array([O.bow_score_l1(vecs_o[0][0], vecs_o[0][1], i, x) for i, x in vecs_o])
+    got = P.bow_score_l1(ctx, vecs_g[0][0], vecs_g[0][1], vecs_g)
+    assert np.array_equal(want.view(np.uint64), got.view(np.uint64))
+    assert got[0] > 0.999
+    vg.set_word_weights(v["weight"][v["leaf"] > 0].astype(np.float64))       # back to the fixture's weights
+    # descriptors -> words -> vector through the whole chain, with a text vocabulary whose weights need all 17 digits
+    v2 = dict(v)
+    w64 = v["weight"].astype(np.float64)
+    w64[v["leaf"] > 0] = ww
+    v2["weight"] = w64
+    path = tmp_path / "voc64.txt"
+    path.write_text(synth.vocabulary_text(v2))
+    vt = P.Vocabulary(ctx, path=str(path))
+    d = synth.descriptors(77, 2000)
+    w, _, _ = vt.transform(d, 4)
+    ig, vg_ = vt.bow_vector(w)
+    io, vo_ = O.bow_vector(w, ww)
+    assert len(io) > 100 and np.array_equal(io, ig) and np.array_equal(vo_.view(np.uint64), vg_.view(np.uint64))
+
+
 def test_distinctive_descriptors_match_oracle(P, ctx):
     """MapPoint::ComputeDistinctiveDescriptors src/MapPoint.cc:366-448, many map points per call."""
     rng = np.random.default_rng(5)

@@ -427,3 +427,51 @@ def test_distinctive_descriptors_vs_numpy():
         dist = np.unpackbits(D[:, None, :] ^ D[None, :, :], axis=2).sum(2)
         med = np.sort(dist, axis=1)[:, int(0.5 * (s - 1))]
         assert got[k] == int(np.argmin(med))
+
+
+def py_bow_vector(word, ww):
+    v = {}
+    for w in word:
+        w = int(w)
+        if ww[w] > 0:
+            v[w] = v[w] + ww[w] if w in v else ww[w]        # python floats are IEEE doubles, added in feature order
+    ids = sorted(v)
+    norm = 0.0
+    for i in ids:
+        norm += abs(v[i])
+    return ids, [v[i] / norm if norm > 0 else v[i] for i in ids]
+
+
+def py_score_l1(i1, v1, i2, v2):
+    d2 = dict(zip(i2, v2))
+    s = 0.0
+    for i, a in zip(i1, v1):
+        if i in d2:
+            s += abs(a - d2[i]) - abs(a) - abs(d2[i])
+    return -s / 2.0
+
+
+def bow_scene(seed, nwords, nfeat):
+    rng = np.random.default_rng(seed)
+    ww = (rng.random(nwords) * 3 + 0.01)
+    ww[rng.random(nwords) < 0.05] = 0.0                      # stopped words
+    hot = rng.integers(0, nwords, max(nwords // 8, 1))
+    word = np.where(rng.random(nfeat) < 0.6, hot[rng.integers(0, len(hot), nfeat)], rng.integers(0, nwords, nfeat)).astype(np.int32)
+    return ww, word
+
+
+def test_bow_vector_and_score_vs_python():
+    for seed, nwords, nfeat in ((1, 1000, 1500), (2, 100000, 4000), (3, 10, 300), (4, 50, 1)):
+        ww, word = bow_scene(seed, nwords, nfeat)
+        ids, vals = O.bow_vector(word, ww)
+        wi, wv = py_bow_vector(word, ww)
+        assert list(ids) == wi and np.array_equal(vals.view(np.uint64), np.array(wv, np.float64).view(np.uint64))
+        if len(wv):
+            assert abs(sum(wv) - 1.0) < 1e-9
+        _, word2 = bow_scene(seed + 100, nwords, nfeat)
+        word2[: nfeat // 2] = word[: nfeat // 2]
+        ids2, vals2 = O.bow_vector(word2, ww)
+        got = O.bow_score_l1(ids, vals, ids2, vals2)
+        want = py_score_l1(list(ids), list(vals), list(ids2), list(vals2))
+        assert np.float64(got).view(np.uint64) == np.float64(want).view(np.uint64)
+        assert O.bow_score_l1(ids, vals, ids, vals) > 0.999 or len(ids) == 0

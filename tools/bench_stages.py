@@ -16,6 +16,8 @@ def main():
     ap.add_argument("--nfeat", type=int, default=1000)
     ap.add_argument("--distinct", type=int, default=32)
     ap.add_argument("--e2e", action="store_true")
+    ap.add_argument("--ini", type=int, default=20)
+    ap.add_argument("--min", type=int, default=7)
     a = ap.parse_args()
     import torch, synth
     P = importlib.import_module("orb-slam2-noted_b200")
@@ -23,7 +25,7 @@ def main():
     frames = np.stack([synth.frame(s, a.w, a.h) for s in range(a.distinct)])
     reps = (a.batch + a.distinct - 1) // a.distinct
     host = torch.from_numpy(np.concatenate([frames] * reps)[:a.batch]).contiguous().pin_memory()
-    ex = P.ORBextractor(a.nfeat, 1.2, 8, 20, 7, device=0, max_w=a.w, max_h=a.h, max_batch=a.batch)
+    ex = P.ORBextractor(a.nfeat, 1.2, 8, a.ini, a.min, device=0, max_w=a.w, max_h=a.h, max_batch=a.batch)
     cap = ex.max_keypoints()
     d_img = host.to(dev)
     d_kps = torch.empty((a.batch, cap, 28), dtype=torch.uint8, device=dev)
