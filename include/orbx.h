@@ -82,6 +82,12 @@ enum { ORBX_FMT_RGB = 0, ORBX_FMT_BGR = 1, ORBX_FMT_RGBA = 2, ORBX_FMT_BGRA = 3 
 int orbx_cvt_gray(orbx_ctx* ctx, const uint8_t* src, int w, int h, size_t stride, int format, int flags, uint8_t* dst,
                   size_t dst_stride);
 
+/* Frame::UndistortKeyPoints, src/Frame.cc:725-781 (cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK): 5 iterations
+ * in double precision, results rounded to float).  dist = mDistCoef (k1, k2, p1, p2[, k3]), ndist = 4 or 5; every other
+ * field of a keypoint is copied.  dist[0] == 0 copies the keypoints unchanged, like :727-731. */
+int orbx_undistort_keypoints(orbx_ctx* ctx, const orbx_keypoint* keys, int n, float fx, float fy, float cx, float cy,
+                             const float* dist, int ndist, int flags, orbx_keypoint* out);
+
 /* Frames per pipeline chunk of orbx_extract_batch when the images are HOST buffers (default 64, env ORBX_CHUNK; 0 = whole
  * batch in one pass): the H2D of chunk i+1 and the D2H of chunk i-1 overlap the kernels of chunk i.  Device-resident
  * batches always run in one pass. */

@@ -549,3 +549,33 @@ void orc_cvt_gray(const uint8_t* src, int w, int h, size_t sstride, int channels
             dst[(size_t)y * dstride + x] = (uint8_t)((r * 9798 + g * 19235 + b * 3735 + 16384) >> 15);
         }
 }
+
+/* Frame::UndistortKeyPoints, src/Frame.cc:725-781: cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK) (third-party
+ * OpenCV calib3d, pinned to cv2 4.13: cvUndistortPointsInternal with the default 5 iterations, everything in double, the
+ * result stored as float).  K = (fx, fy, cx, cy) and dist (k1, k2, p1, p2[, k3]) are the float entries of mK / mDistCoef. */
+void orc_undistort_keypoints(const orc_keypoint* in, int n, float fx_, float fy_, float cx_, float cy_, const float* dist, int ndist,
+                             orc_keypoint* out)
+{
+    if (dist[0] == 0.0f) { for (int i = 0; i < n; ++i) out[i] = in[i]; return; }           /* :727-731 */
+    double k[12] = {0};
+    for (int i = 0; i < ndist && i < 5; ++i) k[i] = dist[i];
+    const double fx = fx_, fy = fy_, cx = cx_, cy = cy_, ifx = 1. / fx, ify = 1. / fy;
+    for (int i = 0; i < n; ++i) {
+        out[i] = in[i];
+        const double u = in[i].x, v = in[i].y;
+        double x = (u - cx) * ifx, y = (v - cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; ++j) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        const double xx = fx * x + 0.0 * y + cx, yy = 0.0 * x + fy * y + cy, ww = 1. / (0.0 * x + 0.0 * y + 1.0);
+        out[i].x = (float)(xx * ww);
+        out[i].y = (float)(yy * ww);
+    }
+}

@@ -70,6 +70,8 @@ int orc_extract(const orc_params* p, const uint8_t* img, int w, int h, size_t st
 
 /* ---- matcher side (orb_match.c) ---- */
 void orc_cvt_gray(const uint8_t* src, int w, int h, size_t sstride, int channels, int bgr, uint8_t* dst, size_t dstride); /* cvtColor */
+void orc_undistort_keypoints(const orc_keypoint* in, int n, float fx, float fy, float cx, float cy, const float* dist, int ndist,
+                             orc_keypoint* out); /* src/Frame.cc:725-781 */
 int orc_descriptor_distance(const uint8_t* a, const uint8_t* b); /* src/ORBmatcher.cc:2123-2143 */
 void orc_hamming_best2(const uint8_t* q, const uint8_t* t, const int32_t* q_seg, const int32_t* q_idx, const int32_t* t_seg,
                        const int32_t* t_idx, int nseg, const uint8_t* t_valid, int32_t* best_idx, int32_t* best_dist,

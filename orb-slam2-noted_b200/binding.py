@@ -58,6 +58,7 @@ def lib():
     L.orbx_kernel_launches.restype = ctypes.c_longlong
     L.orbx_descriptor_distance.argtypes = [vp, vp, vp, ci, ci, vp]
     L.orbx_cvt_gray.argtypes = [vp, vp, ci, ci, sz, ci, ci, vp, sz]
+    L.orbx_undistort_keypoints.argtypes = [vp, vp, ci, cf, cf, cf, cf, vp, ci, ci, vp]
     L.orbx_hamming_best2.argtypes = [vp, vp, ci, vp, ci, vp, vp, vp, vp, ci, vp, ci, vp, vp, vp]
     L.orbx_test_sincosf.argtypes = [ctypes.c_uint32, ctypes.c_uint32, vp, vp]
     L.orbx_test_fast_atan2.argtypes = [vp, ci, vp]
@@ -258,6 +259,16 @@ def cvt_gray(ex, img, fmt=FMT_RGB):
     out = np.empty((h, w), np.uint8)
     ex._check(ex._lib.orbx_cvt_gray(ex._h, img.ctypes.data, w, h, img.strides[0], fmt, 0, _np(out), w), "orbx_cvt_gray")
     return out
+
+
+def undistort_keypoints(ex, kps, K, dist):
+    """Frame::UndistortKeyPoints (src/Frame.cc:725-781) on the GPU; K = (fx, fy, cx, cy), dist = (k1, k2, p1, p2[, k3])."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    d = np.ascontiguousarray(dist, np.float32)
+    out = np.empty(max(len(kps), 1), KP_DTYPE)
+    ex._check(ex._lib.orbx_undistort_keypoints(ex._h, _np(kps), len(kps), *[float(np.float32(x)) for x in K], _np(d), len(d), 0, _np(out)),
+              "orbx_undistort_keypoints")
+    return out[:len(kps)]
 
 
 def descriptor_distance(ex, a, b):

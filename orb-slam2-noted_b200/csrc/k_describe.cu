@@ -291,6 +291,47 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
     }
 }
 
+// Frame::UndistortKeyPoints (src/Frame.cc:725-781) = cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK) on the
+// keypoint coordinates (third-party OpenCV calib3d; pinned to cv2 4.13): normalise with K, 5 fixed-point iterations of the
+// radial / tangential model in double precision, re-project with K, round to float.  Every double operation is an explicit
+// round-to-nearest intrinsic in OpenCV's order (the x86-64 baseline build has no FMA).
+struct UndistortP { double fx, fy, cx, cy, k[5]; };
+__global__ void undistortKernel(const orbx_keypoint* __restrict__ in, int n, const UndistortP P, orbx_keypoint* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    orbx_keypoint kp = in[i];
+    const double ifx = __ddiv_rn(1.0, P.fx), ify = __ddiv_rn(1.0, P.fy);
+    double x = __dmul_rn(__dsub_rn((double)kp.x, P.cx), ifx), y = __dmul_rn(__dsub_rn((double)kp.y, P.cy), ify);
+    const double x0 = x, y0 = y;
+    const double k1 = P.k[0], k2 = P.k[1], p1 = P.k[2], p2 = P.k[3], k3 = P.k[4];
+    bool bad = false;
+    for (int j = 0; j < 5 && !bad; ++j) {
+        const double r2 = __dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y));
+        // (1 + ((k[7]*r2 + k[6])*r2 + k[5])*r2) / (1 + ((k[4]*r2 + k[1])*r2 + k[0])*r2) with k[5..7] = 0
+        const double num = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(0.0, r2), 0.0), r2), 0.0), r2));
+        const double den = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(k3, r2), k2), r2), k1), r2));
+        const double icdist = __ddiv_rn(num, den);
+        if (icdist < 0) { x = x0; y = y0; bad = true; break; }
+        // deltaX = 2*p1*x*y + p2*(r2 + 2*x*x) (+ 0*r2 + 0*r2*r2), deltaY = p1*(r2 + 2*y*y) + 2*p2*x*y (+ ...)
+        const double dX = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(__dmul_rn(__dmul_rn(2.0, p1), x), y),
+                                                        __dmul_rn(p2, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, x), x)))),
+                                              __dmul_rn(0.0, r2)), __dmul_rn(__dmul_rn(0.0, r2), r2));
+        const double dY = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(p1, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, y), y))),
+                                                        __dmul_rn(__dmul_rn(__dmul_rn(2.0, p2), x), y)),
+                                              __dmul_rn(0.0, r2)), __dmul_rn(__dmul_rn(0.0, r2), r2));
+        x = __dmul_rn(__dsub_rn(x0, dX), icdist);
+        y = __dmul_rn(__dsub_rn(y0, dY), icdist);
+    }
+    // RR = K: xx = fx*x + 0*y + cx, yy = 0*x + fy*y + cy, ww = 1/(0*x + 0*y + 1)
+    const double xx = __dadd_rn(__dadd_rn(__dmul_rn(P.fx, x), __dmul_rn(0.0, y)), P.cx);
+    const double yy = __dadd_rn(__dadd_rn(__dmul_rn(0.0, x), __dmul_rn(P.fy, y)), P.cy);
+    const double ww = __ddiv_rn(1.0, __dadd_rn(__dadd_rn(__dmul_rn(0.0, x), __dmul_rn(0.0, y)), 1.0));
+    kp.x = __double2float_rn(__dmul_rn(xx, ww));
+    kp.y = __double2float_rn(__dmul_rn(yy, ww));
+    out[i] = kp;
+}
+
 int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN)
 {
     GeomSet g = c->geom;
@@ -318,6 +359,40 @@ int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* 
 }
 
 } // namespace orbx
+
+// dist: mDistCoef (k1, k2, p1, p2[, k3]) as floats, ndist = 4 or 5; dist[0] == 0 copies the keypoints (src/Frame.cc:727-731).
+extern "C" int orbx_undistort_keypoints(orbx_ctx* h, const orbx_keypoint* keys, int n, float fx, float fy, float cx, float cy,
+                                        const float* dist, int ndist, int flags, orbx_keypoint* out)
+{
+    if (!h || n < 0 || !dist || ndist < 4 || ndist > 5 || (n > 0 && (!keys || !out))) return ORBX_E_INVALID;
+    if (n == 0) return ORBX_OK;
+    orbx::Ctx* c = &h->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
+    const size_t bytes = sizeof(orbx_keypoint) * (size_t)n;
+    if (dist[0] == 0.0f) {
+        const cudaMemcpyKind kind = inDev ? (outDev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost)
+                                          : (outDev ? cudaMemcpyHostToDevice : cudaMemcpyHostToHost);
+        if (keys != out) ORBX_CUDA(c, cudaMemcpyAsync(out, keys, bytes, kind, c->stream));
+        ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+        return ORBX_OK;
+    }
+    int rc = orbx::ensureScratch(c, 2 * ((bytes + 255) & ~(size_t)255));
+    if (rc) return rc;
+    uint8_t* S = (uint8_t*)c->dScratch;
+    const orbx_keypoint* dIn = keys; orbx_keypoint* dOut = out;
+    if (!inDev) { ORBX_CUDA(c, cudaMemcpyAsync(S, keys, bytes, cudaMemcpyHostToDevice, c->stream)); dIn = (const orbx_keypoint*)S; }
+    if (!outDev) dOut = (orbx_keypoint*)(S + ((bytes + 255) & ~(size_t)255));
+    orbx::UndistortP P;
+    P.fx = fx; P.fy = fy; P.cx = cx; P.cy = cy;
+    for (int i = 0; i < 5; ++i) P.k[i] = i < ndist ? (double)dist[i] : 0.0;
+    orbx::undistortKernel<<<(n + 255) / 256, 256, 0, c->stream>>>(dIn, n, P, dOut);
+    c->kernelLaunches += 1;
+    ORBX_CUDA(c, cudaGetLastError());
+    if (!outDev) ORBX_CUDA(c, cudaMemcpyAsync(out, dOut, bytes, cudaMemcpyDeviceToHost, c->stream));
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return ORBX_OK;
+}
 
 // ---- test probes (C ABI, declared in include/orbx_test.h) ----
 extern "C" int orbx_test_sincosf(uint32_t first_bits, uint32_t count, float* h_sin, float* h_cos)

@@ -120,6 +120,18 @@ def cvt_gray(img, bgr=False):
     return out
 
 
+def undistort_keypoints(kps, K, dist):
+    """Frame::UndistortKeyPoints; K = (fx, fy, cx, cy), dist = (k1, k2, p1, p2[, k3])."""
+    kps = np.ascontiguousarray(kps, KP_DTYPE)
+    d = np.ascontiguousarray(dist, np.float32)
+    out = np.empty(max(len(kps), 1), KP_DTYPE)
+    L = lib()
+    L.orc_undistort_keypoints.restype = None
+    L.orc_undistort_keypoints.argtypes = [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_float] * 4 + [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+    L.orc_undistort_keypoints(_p(kps), len(kps), *[float(np.float32(x)) for x in K], _p(d), len(d), _p(out))
+    return out[:len(kps)]
+
+
 def fast_roi(roi, th):
     roi = np.ascontiguousarray(roi)
     cap = roi.size

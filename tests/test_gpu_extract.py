@@ -173,3 +173,21 @@ def test_cvt_gray_matches_golden_and_oracle(P):
             want = O.cvt_gray(np.ascontiguousarray(im), bgr)
             got = P.cvt_gray(ex, im, (2 if ch == 4 else 0) | int(bgr))
             assert np.array_equal(want, got), (h, w, ch, pad, bgr)
+
+
+def test_undistort_keypoints_matches_golden_and_oracle(P):
+    """Frame::UndistortKeyPoints (src/Frame.cc:725-781): cv2 golden + oracle on real extractor output."""
+    import os
+    from test_oracle_golden import UNDISTORT, undistort_points
+    ex = P.ORBextractor(1000, 1.2, 8, 20, 7, max_w=640, max_h=480)
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "undistort.npz"))
+    k = undistort_points()
+    for name, (K, D) in UNDISTORT.items():
+        out = P.undistort_keypoints(ex, k, K, D)
+        assert np.array_equal(out["x"].view(np.uint32), g[name][:, 0].view(np.uint32)), name
+        assert np.array_equal(out["y"].view(np.uint32), g[name][:, 1].view(np.uint32)), name
+        assert np.array_equal(out["octave"], k["octave"]) and np.array_equal(out["angle"], k["angle"])
+    kps, _ = ex(synth.frame(0, 640, 480))
+    K, D = UNDISTORT["tum1"]
+    assert np.array_equal(P.undistort_keypoints(ex, kps, K, D), O.undistort_keypoints(kps, K, D))
+    assert np.array_equal(P.undistort_keypoints(ex, kps, K, (0.0, 0.1, 0.0, 0.0)), kps)

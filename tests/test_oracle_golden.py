@@ -86,3 +86,30 @@ def test_cvt_gray_matches_cv2():
     r_, g_, b_ = np.meshgrid(np.arange(256), np.arange(256), np.arange(0, 256, 3), indexing="ij")
     sweep = np.stack([r_, g_, b_], -1).astype(np.uint8).reshape(256, -1, 3)
     assert sha(O.cvt_gray(sweep)) == str(g["sweep_sha"])
+
+
+UNDISTORT = {"tum1": ((517.306408, 516.469215, 318.643040, 255.313989), (0.262383, -0.953104, -0.005358, 0.002628, 1.163314)),
+             "tum2": ((520.908620, 521.007327, 325.141442, 249.701764), (0.231222, -0.784899, -0.003257, -0.000105, 0.917205)),
+             "four": ((458.654, 457.296, 367.215, 248.375), (-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05))}
+
+
+def undistort_points():
+    rng = np.random.default_rng(78)
+    pts = np.stack([rng.random(3000) * 640, rng.random(3000) * 480], 1).astype(np.float32)
+    pts[:4] = [[0, 0], [639, 479], [318.64304, 255.313989], [-20, 500]]
+    k = np.zeros(len(pts), O.KP_DTYPE)
+    k["x"], k["y"], k["octave"], k["angle"] = pts[:, 0], pts[:, 1], np.arange(len(pts)) % 8, 12.5
+    return k
+
+
+def test_undistort_keypoints_matches_cv2():
+    """Frame::UndistortKeyPoints (src/Frame.cc:725-781): the oracle against cv2.undistortPoints outputs (tests/golden/undistort.npz)."""
+    g = np.load(os.path.join(G, "undistort.npz"))
+    k = undistort_points()
+    for name, (K, D) in UNDISTORT.items():
+        out = O.undistort_keypoints(k, K, D)
+        assert np.array_equal(out["x"].view(np.uint32), g[name][:, 0].view(np.uint32)), name
+        assert np.array_equal(out["y"].view(np.uint32), g[name][:, 1].view(np.uint32)), name
+        assert np.array_equal(out["octave"], k["octave"]) and np.array_equal(out["angle"], k["angle"])
+    same = O.undistort_keypoints(k, UNDISTORT["tum1"][0], (0.0, 0.1, 0, 0))
+    assert np.array_equal(same, k)

@@ -28,7 +28,22 @@ r_, g_, b_ = np.meshgrid(np.arange(256), np.arange(256), np.arange(0, 256, 3), i
 sweep = np.stack([r_, g_, b_], -1).astype(np.uint8).reshape(256, -1, 3)      # every (R, G) with every third B
 cvt["sweep_sha"] = np.array(sha(cv2.cvtColor(sweep, cv2.COLOR_RGB2GRAY)))
 np.savez_compressed(os.path.join(G, "cvt_gray.npz"), **cvt)
-if "--only-cvt" in sys.argv:
+# --- Frame::UndistortKeyPoints = cv2.undistortPoints(pts, K, D, None, K) (outputs only; inputs are seeded) ---
+def undistort_cases():
+    rng = np.random.default_rng(78)
+    pts = np.stack([rng.random(3000) * 640, rng.random(3000) * 480], 1).astype(np.float32)
+    pts[:4] = [[0, 0], [639, 479], [318.64304, 255.313989], [-20, 500]]
+    return pts, {"tum1": ((517.306408, 516.469215, 318.643040, 255.313989), (0.262383, -0.953104, -0.005358, 0.002628, 1.163314)),
+                 "tum2": ((520.908620, 521.007327, 325.141442, 249.701764), (0.231222, -0.784899, -0.003257, -0.000105, 0.917205)),
+                 "four": ((458.654, 457.296, 367.215, 248.375), (-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05))}
+und = {}
+upts, ucases = undistort_cases()
+for name, (Kp, Dp) in ucases.items():
+    Km = np.array([[Kp[0], 0, Kp[2]], [0, Kp[1], Kp[3]], [0, 0, 1]], np.float32)
+    Dm = np.array(Dp, np.float32).reshape(-1, 1)
+    und[name] = cv2.undistortPoints(upts.reshape(-1, 1, 2).copy(), Km, Dm, None, Km).reshape(-1, 2)
+np.savez_compressed(os.path.join(G, "undistort.npz"), **und)
+if "--only-cvt" in sys.argv or "--only-small" in sys.argv:
     sys.exit(0)
 
 # --- primitives ---
