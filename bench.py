@@ -132,7 +132,7 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
-def hamming_gmatch(P, ex, dev, n=10000, pairs=16, reps=3):
+def hamming_gmatch(P, ex, dev, n=10000, pairs=32, reps=3):
     """K6 many-vs-many (segments = keyframe pairs of n x n descriptors, device resident): GMatch/s on this rank."""
     import torch
     L = P.lib()
@@ -316,7 +316,7 @@ def run_orbx(args, rank, world):
                              "pipeline_frac": total_alg * value / world / 1e9 / hbm, "stage_ms_per_step": stage_ms},
                 "cpu_baseline": cpu,
                 "hamming": {"metric": "hamming_gmatch_per_s", "value": gm_total, "unit": "GMatch/s", "per_gpu": gm,
-                            "workload": "brute force 10000 x 10000 descriptors per keyframe pair, 16 pairs per GPU per call, device resident",
+                            "workload": "brute force 10000 x 10000 descriptors per keyframe pair, 32 pairs per GPU per call, device resident",
                             "ms_per_call": gm_ms, "calls": gm_reps,
                             "roofline": {"bound": "popc", "achieved": gm * 8.0, "peak": popc_peak / 1e9, "unit": "GPOPC32/s",
                                          "frac": gm * 8e9 / popc_peak, "peak_source": "measured in this run (orbx_test_popc_peak)",
