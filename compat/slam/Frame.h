@@ -28,6 +28,11 @@ public:
     float GetMinDistanceInvariance() { return 0.8f * mfMinDistance; }   // src/MapPoint.cc:549-559
     float GetMaxDistanceInvariance() { return 1.2f * mfMaxDistance; }
     cv::Mat GetNormal() { return mNormalVector; }
+    // observation bookkeeping, reduced to what ORBmatcher::Fuse / SearchBySim3 touch (src/MapPoint.cc:139-330)
+    bool IsInKeyFrame(KeyFrame* pKF) { return mObs.count(pKF) != 0; }
+    int GetIndexInKeyFrame(KeyFrame* pKF) { return mObs.count(pKF) ? (int)mObs[pKF] : -1; }
+    void AddObservation(KeyFrame* pKF, size_t idx) { if (!mObs.count(pKF)) { mObs[pKF] = idx; ++nObs; } }
+    void Replace(MapPoint* pMP);
     int PredictScale(const float& currentDist, KeyFrame* pKF);          // src/MapPoint.cc:584-604
     int PredictScale(const float& currentDist, Frame* pF);              // :613-631
     bool isBad() { return mbBad; }
@@ -40,6 +45,7 @@ public:
     float mTrackViewCos;
     // test-side state
     bool mbBad; int nObs; cv::Mat mDescriptor, mWorldPos, mNormalVector; float mfMaxDistance, mfMinDistance;
+    std::map<KeyFrame*, size_t> mObs; MapPoint* mpReplaced = 0;
 };
 
 class Frame
@@ -71,6 +77,9 @@ public:
     DBoW2::FeatureVector mFeatVec;
     std::vector<float> mvScaleFactors, mvLevelSigma2;
     float fx, fy, cx, cy;
+    float mbf; std::vector<float> mvInvLevelSigma2;
+    void AddMapPoint(MapPoint* pMP, const size_t& idx) { mvpMapPoints[idx] = pMP; }
+    std::set<MapPoint*> GetMapPoints() { std::set<MapPoint*> s; for (size_t i = 0; i < mvpMapPoints.size(); ++i) if (mvpMapPoints[i] && !mvpMapPoints[i]->isBad()) s.insert(mvpMapPoints[i]); return s; }
     int mnScaleLevels; float mfLogScaleFactor;
     int mnGridCols, mnGridRows; float mfGridElementWidthInv, mfGridElementHeightInv;
     int mnMinX, mnMinY, mnMaxX, mnMaxY;
@@ -84,6 +93,20 @@ public:
     std::vector<MapPoint*> mvpMapPoints;
     cv::Mat Ow, Rcw, tcw;
 };
+
+// MapPoint::Replace, src/MapPoint.cc:257-311, reduced: this point goes bad, its observations move to pMP
+inline void MapPoint::Replace(MapPoint* pMP)
+{
+    if (pMP == this) return;
+    mbBad = true; mpReplaced = pMP;
+    std::map<KeyFrame*, size_t> obs = mObs;
+    mObs.clear();
+    for (std::map<KeyFrame*, size_t>::iterator it = obs.begin(); it != obs.end(); ++it) {
+        KeyFrame* kf = it->first;
+        if (!pMP->IsInKeyFrame(kf)) { kf->mvpMapPoints[it->second] = pMP; pMP->AddObservation(kf, it->second); }
+        else kf->mvpMapPoints[it->second] = 0;
+    }
+}
 
 inline int predictScaleImpl(float maxDistance, float currentDist, float logScaleFactor, int nLevels)
 {

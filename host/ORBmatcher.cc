@@ -367,6 +367,201 @@ int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Po
     return n;
 }
 
+namespace {
+// the independent window search of Fuse x2 / SearchBySim3 on a KeyFrame's keypoints (orbx_window_best)
+void keyFrameWindowBest(orbx_ctx* ctx, KeyFrame* pKF, const std::vector<orbx_proj_query>& q, bool reprojGate, int thDist,
+                        std::vector<int32_t>& bestIdx)
+{
+    bestIdx.assign(q.size() > 0 ? q.size() : 1, -1);
+    if (q.empty() || pKF->N == 0) return;
+    std::vector<int32_t> bestDist(q.size());
+    std::vector<uint8_t> tmp;
+    float invSigma2[ORBX_MAX_LEVELS] = {0};
+    for (size_t l = 0; l < pKF->mvInvLevelSigma2.size() && l < (size_t)ORBX_MAX_LEVELS; ++l) invSigma2[l] = pKF->mvInvLevelSigma2[l];
+    const orbx_grid g = {(float)pKF->mnMinX, (float)pKF->mnMinY, pKF->mfGridElementWidthInv, pKF->mfGridElementHeightInv,
+                         pKF->mnGridCols, pKF->mnGridRows};
+    check(orbx_window_best(ctx, q.data(), (int)q.size(), reinterpret_cast<const orbx_keypoint*>(pKF->mvKeysUn.data()),
+                           contiguous(pKF->mDescriptors, tmp), pKF->mvuRight.empty() ? nullptr : pKF->mvuRight.data(), pKF->N, &g,
+                           reprojGate ? invSigma2 : nullptr, thDist, 0, bestIdx.data(), bestDist.data()), "orbx_window_best");
+}
+
+// project a world point with (R, t) and the KeyFrame's intrinsics; the gates shared by Fuse x2 (:1166-1222, :1345-1395)
+bool projectForFuse(KeyFrame* pKF, MapPoint* pMP, const float R[9], const float t[3], const float Ow[3], float th, float bf,
+                    orbx_proj_query& e)
+{
+    cv::Mat X = pMP->GetWorldPos();
+    const float x = X.at<float>(0), y = X.at<float>(1), z = X.at<float>(2);
+    const float xc = R[0] * x + R[1] * y + R[2] * z + t[0];
+    const float yc = R[3] * x + R[4] * y + R[5] * z + t[1];
+    const float zc = R[6] * x + R[7] * y + R[8] * z + t[2];
+    if (zc < 0.0f) return false;
+    const float invz = 1 / zc;
+    const float u = pKF->fx * (xc * invz) + pKF->cx, v = pKF->fy * (yc * invz) + pKF->cy;
+    if (!pKF->IsInImage(u, v)) return false;
+    const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+    const float POx = x - Ow[0], POy = y - Ow[1], POz = z - Ow[2];
+    const float dist3D = norm3(POx, POy, POz);
+    if (dist3D < minDistance || dist3D > maxDistance) return false;
+    cv::Mat Pn = pMP->GetNormal();
+    if (POx * Pn.at<float>(0) + POy * Pn.at<float>(1) + POz * Pn.at<float>(2) < 0.5 * dist3D) return false;
+    const int nPredictedLevel = pMP->PredictScale(dist3D, pKF);
+    memset(&e, 0, sizeof(e));
+    e.u = u; e.v = v; e.ur = u - bf * invz;
+    e.radius = th * pKF->mvScaleFactors[nPredictedLevel];
+    e.min_level = nPredictedLevel - 1; e.max_level = nPredictedLevel;
+    const cv::Mat d = pMP->GetDescriptor();
+    memcpy(e.desc, d.ptr<uint8_t>(), 32);
+    return true;
+}
+} // namespace
+
+// LocalMapping: fuse the neighbours' MapPoints into pKF.  The candidate search of every point is independent (GPU); the map
+// is then updated point by point in the reference's order, re-checking the skip conditions the earlier updates can change.
+int ORBmatcher::Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th)
+{
+    float Rcw[9], tcw[3], Ow[3];
+    const cv::Mat R = pKF->GetRotation(), t = pKF->GetTranslation(), O = pKF->GetCameraCenter();
+    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) Rcw[3 * r + c] = R.at<float>(r, c); tcw[r] = t.at<float>(r); Ow[r] = O.at<float>(r); }
+    std::vector<orbx_proj_query> q;
+    std::vector<int> src;
+    for (int i = 0, n = (int)vpMapPoints.size(); i < n; i++) {
+        MapPoint* pMP = vpMapPoints[i];
+        if (!pMP) continue;
+        if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+        orbx_proj_query e;
+        if (!projectForFuse(pKF, pMP, Rcw, tcw, Ow, th, pKF->mbf, e)) continue;
+        q.push_back(e); src.push_back(i);
+    }
+    std::vector<int32_t> bestIdx;
+    keyFrameWindowBest(Context(), pKF, q, true, TH_LOW, bestIdx);
+    int nFused = 0;
+    for (size_t k = 0; k < q.size(); ++k) {
+        MapPoint* pMP = vpMapPoints[src[k]];
+        if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;          // changed by an earlier Replace / AddObservation (:1157)
+        if (bestIdx[k] < 0) continue;
+        MapPoint* pMPinKF = pKF->GetMapPoint(bestIdx[k]);               // :1288-1300
+        if (pMPinKF) {
+            if (!pMPinKF->isBad()) {
+                if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+                else pMPinKF->Replace(pMP);
+            }
+        } else {
+            pMP->AddObservation(pKF, bestIdx[k]);
+            pKF->AddMapPoint(pMP, bestIdx[k]);
+        }
+        nFused++;
+    }
+    return nFused;
+}
+
+// LoopClosing: fuse the loop's MapPoints into pKF with the corrected Sim3 pose (:1310-1458).
+int ORBmatcher::Fuse(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, float th, std::vector<MapPoint*>& vpReplacePoint)
+{
+    const float r00 = Scw.at<float>(0, 0), r01 = Scw.at<float>(0, 1), r02 = Scw.at<float>(0, 2);
+    const float scw = std::sqrt(r00 * r00 + r01 * r01 + r02 * r02);
+    float Rcw[9], tcw[3], Ow[3];
+    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) Rcw[3 * r + c] = Scw.at<float>(r, c) / scw; tcw[r] = Scw.at<float>(r, 3) / scw; }
+    for (int r = 0; r < 3; ++r) Ow[r] = -(Rcw[r] * tcw[0] + Rcw[3 + r] * tcw[1] + Rcw[6 + r] * tcw[2]);
+    const std::set<MapPoint*> spAlreadyFound = pKF->GetMapPoints();
+    std::vector<orbx_proj_query> q;
+    std::vector<int> src;
+    for (int iMP = 0, n = (int)vpPoints.size(); iMP < n; iMP++) {
+        MapPoint* pMP = vpPoints[iMP];
+        if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+        orbx_proj_query e;
+        if (!projectForFuse(pKF, pMP, Rcw, tcw, Ow, th, 0.0f, e)) continue;
+        q.push_back(e); src.push_back(iMP);
+    }
+    std::vector<int32_t> bestIdx;
+    keyFrameWindowBest(Context(), pKF, q, false, TH_LOW, bestIdx);
+    int nFused = 0;
+    for (size_t k = 0; k < q.size(); ++k) {
+        if (bestIdx[k] < 0) continue;
+        MapPoint* pMP = vpPoints[src[k]];
+        MapPoint* pMPinKF = pKF->GetMapPoint(bestIdx[k]);               // :1442-1456
+        if (pMPinKF) {
+            if (!pMPinKF->isBad()) vpReplacePoint[src[k]] = pMPinKF;
+        } else {
+            pMP->AddObservation(pKF, bestIdx[k]);
+            pKF->AddMapPoint(pMP, bestIdx[k]);
+        }
+        nFused++;
+    }
+    return nFused;
+}
+
+// LoopClosing: more matches between two keyframes once a Sim3 is known; both directions must agree (:1472-1723).
+int ORBmatcher::SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12, const float& s12, const cv::Mat& R12,
+                             const cv::Mat& t12, const float th)
+{
+    float R1w[9], t1w[3], R2w[9], t2w[3], sR12[9], sR21[9], t21[3], T12[3];
+    const cv::Mat r1 = pKF1->GetRotation(), tt1 = pKF1->GetTranslation(), r2 = pKF2->GetRotation(), tt2 = pKF2->GetTranslation();
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) {
+            R1w[3 * r + c] = r1.at<float>(r, c); R2w[3 * r + c] = r2.at<float>(r, c);
+            sR12[3 * r + c] = s12 * R12.at<float>(r, c);
+            sR21[3 * r + c] = (float)(1.0 / s12) * R12.at<float>(c, r);     // cv::Mat scaling of CV_32F works in float
+        }
+        t1w[r] = tt1.at<float>(r); t2w[r] = tt2.at<float>(r); T12[r] = t12.at<float>(r);
+    }
+    for (int r = 0; r < 3; ++r) t21[r] = -(sR21[3 * r] * T12[0] + sR21[3 * r + 1] * T12[1] + sR21[3 * r + 2] * T12[2]);
+    const std::vector<MapPoint*> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+    const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
+    std::vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+    for (int i = 0; i < N1; i++) {
+        MapPoint* pMP = vpMatches12[i];
+        if (pMP) {
+            vbAlreadyMatched1[i] = true;
+            const int idx2 = pMP->GetIndexInKeyFrame(pKF2);
+            if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+        }
+    }
+    // one direction: points of `from` (pose Raw, taw) into `to` through (sRba, tba)
+    auto direction = [&](const std::vector<MapPoint*>& pts, const std::vector<bool>& done, const float* Raw, const float* taw,
+                         const float* sRba, const float* tba, KeyFrame* to, std::vector<int>& match) {
+        std::vector<orbx_proj_query> q;
+        std::vector<int> src;
+        for (int i = 0; i < (int)pts.size(); i++) {
+            MapPoint* pMP = pts[i];
+            if (!pMP || done[i]) continue;
+            if (pMP->isBad()) continue;
+            cv::Mat X = pMP->GetWorldPos();
+            const float x = X.at<float>(0), y = X.at<float>(1), z = X.at<float>(2);
+            const float ax = Raw[0] * x + Raw[1] * y + Raw[2] * z + taw[0], ay = Raw[3] * x + Raw[4] * y + Raw[5] * z + taw[1],
+                        az = Raw[6] * x + Raw[7] * y + Raw[8] * z + taw[2];
+            const float bx = sRba[0] * ax + sRba[1] * ay + sRba[2] * az + tba[0], by = sRba[3] * ax + sRba[4] * ay + sRba[5] * az + tba[1],
+                        bz = sRba[6] * ax + sRba[7] * ay + sRba[8] * az + tba[2];
+            if (bz < 0.0) continue;
+            const float invz = 1.0 / bz;
+            const float u = to->fx * (bx * invz) + to->cx, v = to->fy * (by * invz) + to->cy;
+            if (!to->IsInImage(u, v)) continue;
+            const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+            const float dist3D = norm3(bx, by, bz);
+            if (dist3D < minDistance || dist3D > maxDistance) continue;
+            const int nPredictedLevel = pMP->PredictScale(dist3D, to);
+            orbx_proj_query e;
+            memset(&e, 0, sizeof(e));
+            e.u = u; e.v = v; e.radius = th * to->mvScaleFactors[nPredictedLevel];
+            e.min_level = nPredictedLevel - 1; e.max_level = nPredictedLevel;
+            const cv::Mat d = pMP->GetDescriptor();
+            memcpy(e.desc, d.ptr<uint8_t>(), 32);
+            q.push_back(e); src.push_back(i);
+        }
+        std::vector<int32_t> bestIdx;
+        keyFrameWindowBest(Context(), to, q, false, TH_HIGH, bestIdx);
+        for (size_t k = 0; k < q.size(); ++k) if (bestIdx[k] >= 0) match[src[k]] = bestIdx[k];
+    };
+    std::vector<int> vnMatch1(N1, -1), vnMatch2(N2, -1);
+    direction(vpMapPoints1, vbAlreadyMatched1, R1w, t1w, sR21, t21, pKF2, vnMatch1);
+    direction(vpMapPoints2, vbAlreadyMatched2, R2w, t2w, sR12, T12, pKF1, vnMatch2);
+    int nFound = 0;
+    for (int i1 = 0; i1 < N1; i1++) {                                                                        // :1700-1720
+        const int idx2 = vnMatch1[i1];
+        if (idx2 >= 0 && vnMatch2[idx2] == i1) { vpMatches12[i1] = vpMapPoints2[idx2]; nFound++; }
+    }
+    return nFound;
+}
+
 // static members of the compat Frame stand-in (the reference defines them in src/Frame.cc:38-42)
 #ifdef ORBX_COMPAT_SLAM_FRAME_H
 float Frame::fx, Frame::fy, Frame::cx, Frame::cy;

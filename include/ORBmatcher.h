@@ -2,8 +2,8 @@
 // class, constructor, static members and method signatures, so Tracking / LocalMapping / LoopClosing call it unchanged.
 // The Hamming work runs in hand-written sm_100a CUDA kernels behind the C ABI (include/orbx.h); the bodies in
 // host/ORBmatcher.cc only flatten the SLAM objects.  Implemented here: DescriptorDistance, both SearchByBoW overloads,
-// SearchForTriangulation, all four SearchByProjection overloads and SearchForInitialization.  SearchBySim3 and Fuse x2
-//  keep the reference's own bodies for now (they call the static DescriptorDistance below).
+// SearchForTriangulation, all four SearchByProjection overloads, SearchForInitialization, SearchBySim3 and Fuse x2: the
+// complete public surface of the reference class.
 #ifndef ORBMATCHER_H
 #define ORBMATCHER_H
 
@@ -37,6 +37,11 @@ public:
                            std::vector<MapPoint*>& vpMatched, int th);                                              // :431-560
     int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
                                 int windowSize = 10);                                                               // :580-748
+    int SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12, const float& s12, const cv::Mat& R12,
+                     const cv::Mat& t12, const float th);                                                           // :1472-1723
+    int Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th = 3.0);                       // :1139-1300
+    int Fuse(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, float th,
+             std::vector<MapPoint*>& vpReplacePoint);                                                               // :1310-1458
     int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);                            // :255-419
     int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);                           // :760-903
     int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12,

@@ -98,6 +98,7 @@ __global__ void atan2ProbeKernel(const float* yx, int n, float* out)
 }
 
 constexpr int kDescWarps = 8;
+constexpr int kDepth = 2;                                                       // patches in flight per warp (3 measured no faster)
 constexpr int kKpPerWarpMax = 32;                                               // consecutive keypoints per warp (lane k owns keypoint k), patches double-buffered
 constexpr int kPatchR = 18, kPatchRows = 2 * kPatchR + 1, kPatchPitchW = 16;   // blurred patch: 37 rows x 64 bytes (four 16-byte chunks)
 constexpr int kRawRows = 2 * kHalfPatch + 1, kRawPitchW = 12;                  // raw patch: 31 rows x 48 bytes (three 16-byte chunks)
@@ -146,12 +147,12 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
     //      pass A  31 x 31 raw patch (3 chunks per row) -> IC_Angle moments, lane k keeps the moments of keypoint k;
     //              then fastAtan2 + sinf/cosf run ONCE, lane-parallel over the warp's keypoints
     //      pass B  37 x 37 blurred patch (rotated pattern points stay within +-18; 4 chunks per row) -> steered BRIEF ----
-    uint32_t* const bufBase = sBufAll + wrp * (2 * kPatchWords);
+    uint32_t* const bufBase = sBufAll + wrp * (kDepth * kPatchWords);
     auto issueRaw = [&](int k) {
         const int level = __shfl_sync(0xffffffffu, myLevel, k);
         const int cx = __float2int_rn(__shfl_sync(0xffffffffu, kp.x, k)), cy = __float2int_rn(__shfl_sync(0xffffffffu, kp.y, k));
         const LevelGeom& g = G.lv[level];
-        uint32_t* buf = bufBase + (k & 1) * kRawWords;
+        uint32_t* buf = bufBase + (k % kDepth) * kRawWords;
         const uint8_t* img; int pitch;
         if (level == 0) { img = lvl0 + (size_t)frame * lvl0Frame; pitch = (int)lvl0Pitch; }
         else { img = pyr + g.planeOff + (size_t)frame * g.pitch * g.h; pitch = g.pitch; }
@@ -181,7 +182,7 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
         const int level = __shfl_sync(0xffffffffu, myLevel, k);
         const int cx = __float2int_rn(__shfl_sync(0xffffffffu, kp.x, k)), cy = __float2int_rn(__shfl_sync(0xffffffffu, kp.y, k));
         const LevelGeom& g = G.lv[level];
-        uint32_t* buf = bufBase + (k & 1) * kPatchWords;
+        uint32_t* buf = bufBase + (k % kDepth) * kPatchWords;
         const int bp = g.pitch;
         const int a0 = (cx - kPatchR) & ~15;                        // aligned first column of the blurred patch
         const int lr = lane >> 2, lk = lane & 3;                    // 8 rows x 4 chunks per step
@@ -211,14 +212,13 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
             for (int b2 = 0; b2 < 4; ++b2) if (4 * j + b2 >= lo && 4 * j + b2 <= hi) m |= 0xffu << (8 * b2);
             icMask[j] = m;
         }
-        issueRaw(0);
-        if (nkp > 1) issueRaw(1);
+        #pragma unroll
+        for (int d = 0; d < kDepth; ++d) { if (d < nkp) issueRaw(d); else asm volatile("cp.async.commit_group;" ::: "memory"); }
         for (int k = 0; k < nkp; ++k) {
-            if (k + 1 < nkp) asm volatile("cp.async.wait_group 1;" ::: "memory");
-            else asm volatile("cp.async.wait_group 0;" ::: "memory");
+            asm volatile("cp.async.wait_group %0;" ::"n"(kDepth - 1) : "memory");   // one group per keypoint, kDepth in flight
             __syncwarp();
             const int cx = __float2int_rn(__shfl_sync(0xffffffffu, kp.x, k));
-            const uint32_t* buf = bufBase + (k & 1) * kRawWords;
+            const uint32_t* buf = bufBase + (k % kDepth) * kRawWords;
             int m10 = 0, m01 = 0;
             if (lane < 2 * kHalfPatch + 1) {
                 const uint32_t* row = buf + lane * kRawPitchW + (((cx - kHalfPatch) & 15) >> 2);   // word holding u = -15
@@ -242,7 +242,7 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
             m01 = __reduce_add_sync(0xffffffffu, m01);
             if (lane == k) { myM10 = m10; myM01 = m01; }
             __syncwarp();                                    // everyone is done with this buffer
-            if (k + 2 < nkp) issueRaw(k + 2);
+            if (k + kDepth < nkp) issueRaw(k + kDepth); else asm volatile("cp.async.commit_group;" ::: "memory");
         }
     }
     // orientation and its sine / cosine, one keypoint per lane (:140, :158)
@@ -258,15 +258,14 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
     float4 pat[8];
     #pragma unroll
     for (int j = 0; j < 8; ++j) pat[j] = __ldg(reinterpret_cast<const float4*>(kBriefPatternF) + lane * 8 + j);
-    issueBlur(0);
-    if (nkp > 1) issueBlur(1);
+    #pragma unroll
+    for (int d = 0; d < kDepth; ++d) { if (d < nkp) issueBlur(d); else asm volatile("cp.async.commit_group;" ::: "memory"); }
     for (int k = 0; k < nkp; ++k) {
-        if (k + 1 < nkp) asm volatile("cp.async.wait_group 1;" ::: "memory");
-        else asm volatile("cp.async.wait_group 0;" ::: "memory");
+        asm volatile("cp.async.wait_group %0;" ::"n"(kDepth - 1) : "memory");
         __syncwarp();
         const int cx = __float2int_rn(__shfl_sync(0xffffffffu, kp.x, k));
         const float a = __shfl_sync(0xffffffffu, myCos, k), b = __shfl_sync(0xffffffffu, mySin, k);
-        const uint32_t* buf = bufBase + (k & 1) * kPatchWords;
+        const uint32_t* buf = bufBase + (k % kDepth) * kPatchWords;
         const int offc = (cx - kPatchR) - ((cx - kPatchR) & ~15) + kPatchR;                // byte column of the patch centre
         const uint8_t* pc = reinterpret_cast<const uint8_t*>(buf) + kPatchR * (kPatchPitchW * 4) + offc;
         int val = 0;
@@ -282,7 +281,7 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
         }
         outDesc[((size_t)frame * cap + (i0 + k)) * 32 + lane] = (uint8_t)val;
         __syncwarp();                                              // everyone is done with this buffer
-        if (k + 2 < nkp) issueBlur(k + 2);
+        if (k + kDepth < nkp) issueBlur(k + kDepth); else asm volatile("cp.async.commit_group;" ::: "memory");
     }
     if (lane < nkp) {
         kp.angle = myAngle;
@@ -345,7 +344,7 @@ int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* 
     while (kpw > 2 && (long long)batch * ((slots + kpw - 1) / kpw) < (long long)smCount * 2 * kDescWarps) kpw >>= 1;
     const int perBlock = kDescWarps * kpw;
     dim3 grid((slots + perBlock - 1) / perBlock, batch), block(kDescWarps * 32);
-    const size_t smem = sizeof(uint32_t) * (size_t)kDescWarps * 2 * kPatchWords;
+    const size_t smem = sizeof(uint32_t) * (size_t)kDescWarps * kDepth * kPatchWords;
     static bool configured = false;
     if (!configured) {
         ORBX_CUDA(c, cudaFuncSetAttribute(describeKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
