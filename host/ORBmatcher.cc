@@ -326,7 +326,7 @@ int ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector
         const float dist = norm3(POx, POy, POz);
         if (dist < minDistance || dist > maxDistance) continue;
         cv::Mat Pn = pMP->GetNormal();
-        if (POx * Pn.at<float>(0) + POy * Pn.at<float>(1) + POz * Pn.at<float>(2) < 0.5 * dist) continue;
+        if ((double)POx * Pn.at<float>(0) + (double)POy * Pn.at<float>(1) + (double)POz * Pn.at<float>(2) < 0.5 * dist) continue;   // cv::Mat::dot sums in double
         const int nPredictedLevel = pMP->PredictScale(dist, pKF);
         orbx_proj_query e;
         memset(&e, 0, sizeof(e));
@@ -403,7 +403,7 @@ bool projectForFuse(KeyFrame* pKF, MapPoint* pMP, const float R[9], const float 
     const float dist3D = norm3(POx, POy, POz);
     if (dist3D < minDistance || dist3D > maxDistance) return false;
     cv::Mat Pn = pMP->GetNormal();
-    if (POx * Pn.at<float>(0) + POy * Pn.at<float>(1) + POz * Pn.at<float>(2) < 0.5 * dist3D) return false;
+    if ((double)POx * Pn.at<float>(0) + (double)POy * Pn.at<float>(1) + (double)POz * Pn.at<float>(2) < 0.5 * dist3D) return false;   // cv::Mat::dot sums in double
     const int nPredictedLevel = pMP->PredictScale(dist3D, pKF);
     memset(&e, 0, sizeof(e));
     e.u = u; e.v = v; e.ur = u - bf * invz;

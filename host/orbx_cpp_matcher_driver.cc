@@ -152,6 +152,78 @@ int main(int argc, char** argv)
             n = ORBmatcher(P[0], true).SearchForInitialization(F1, F, prev, m12, (int)Q[3]);
             put(o, &n, 4); put(o, m12.data(), 4 * F1.N); put(o, prev.data(), 8 * F1.N);
         }
+        if (in.size() > 24) {
+            // 21: world2 (per KF2 feature: x, y, z, maxDist, minDist, normal), 22: KF2 MapPoint descriptors,
+            // 23: int32 observation counts of pool1 then pool2, 24: float[8]: th_fuse, bf, th_fuse_sim3, th_sim3
+            const float* W1 = as<float>(in[18]); const float* W2 = as<float>(in[21]);
+            const int* obsN = as<int>(in[23]);
+            const float* Q2 = as<float>(in[24]);
+            const std::vector<MapPoint*> has1 = k1.mvpMapPoints, has2 = k2.mvpMapPoints;
+            auto setPoint = [&](MapPoint& mp, const float* w, const char* d) {
+                mp = MapPoint();
+                mp.mWorldPos = cv::Mat(3, 1, CV_32F); memcpy(mp.mWorldPos.data, w, 12);
+                mp.mfMaxDistance = w[3]; mp.mfMinDistance = w[4];
+                mp.mNormalVector = cv::Mat(3, 1, CV_32F); memcpy(mp.mNormalVector.data, w + 5, 12);
+                mp.mDescriptor = cv::Mat(1, 32, CV_8U); memcpy(mp.mDescriptor.data, d, 32);
+            };
+            auto reset = [&]() {
+                for (int i = 0; i < k1.N; ++i) { setPoint(pool1[i], W1 + 8 * i, in[20].data() + 32 * i); k1.mvpMapPoints[i] = has1[i]; }
+                for (int i = 0; i < k2.N; ++i) { setPoint(pool2[i], W2 + 8 * i, in[22].data() + 32 * i); k2.mvpMapPoints[i] = has2[i]; }
+                for (int i = 0; i < k1.N; ++i) if (has1[i]) { pool1[i].mObs[&k1] = i; pool1[i].nObs = obsN[i]; }
+                for (int i = 0; i < k2.N; ++i) if (has2[i]) { pool2[i].mObs[&k2] = i; pool2[i].nObs = obsN[k1.N + i]; }
+            };
+            auto code = [&](MapPoint* p) { return !p ? -1 : (p >= pool1.data() && p < pool1.data() + k1.N) ? (int)(p - pool1.data()) : 100000 + (int)(p - pool2.data()); };
+            for (int s = 0; s < 2; ++s) {
+                KeyFrame& K = *ks[s];
+                K.Rcw = cv::Mat::zeros(3, 3, CV_32F); for (int i = 0; i < 3; ++i) K.Rcw.at<float>(i, i) = 1.f;
+                K.tcw = cv::Mat::zeros(3, 1, CV_32F); K.Ow = cv::Mat::zeros(3, 1, CV_32F);
+                K.mbf = Q2[1];
+                K.mvInvLevelSigma2.resize(8); for (int l = 0; l < 8; ++l) K.mvInvLevelSigma2[l] = 1.0f / K.mvLevelSigma2[l];
+                K.mnScaleLevels = 8; K.mfLogScaleFactor = as<float>(in[19])[4];
+                K.mnGridCols = FRAME_GRID_COLS; K.mnGridRows = FRAME_GRID_ROWS;
+                K.mfGridElementWidthInv = P[8]; K.mfGridElementHeightInv = P[9];
+                K.mnMinX = (int)P[10]; K.mnMinY = (int)P[11]; K.mnMaxX = (int)P[12]; K.mnMaxY = (int)P[13];
+            }
+            // (h) Fuse(KeyFrame, vpMapPoints, th): KF1's points (with NULL gaps and a few duplicates) into KF2
+            reset();
+            std::vector<MapPoint*> vp = k1.mvpMapPoints;
+            for (int i = 0; i + 50 < k1.N; i += 50) vp.push_back(vp[i]);
+            n = ORBmatcher(P[0], true).Fuse(&k2, vp, Q2[0]);
+            res.assign(k2.N, -1);
+            for (int i = 0; i < k2.N; ++i) res[i] = code(k2.mvpMapPoints[i]);
+            put(o, &n, 4); put(o, res.data(), 4 * k2.N);
+            std::vector<int> st(k1.N + k2.N);
+            for (int i = 0; i < k1.N; ++i) st[i] = (pool1[i].mbBad ? 1 : 0) | (pool1[i].nObs << 1);
+            for (int i = 0; i < k2.N; ++i) st[k1.N + i] = (pool2[i].mbBad ? 1 : 0) | (pool2[i].nObs << 1);
+            put(o, st.data(), 4 * (int)st.size());
+            // (i) Fuse(KeyFrame, Scw, vpPoints, th, vpReplacePoint)
+            reset();
+            cv::Mat Scw = cv::Mat::zeros(4, 4, CV_32F);
+            for (int i = 0; i < 3; ++i) Scw.at<float>(i, i) = 2.f;
+            Scw.at<float>(3, 3) = 1.f;
+            std::vector<MapPoint*> vpts;
+            for (int i = 0; i < k1.N; ++i) if (k1.mvpMapPoints[i]) vpts.push_back(k1.mvpMapPoints[i]);
+            for (size_t i = 0, nv = vpts.size(); i + 40 < nv; i += 40) vpts.push_back(vpts[i]);
+            std::vector<MapPoint*> repl(vpts.size(), (MapPoint*)NULL);
+            n = ORBmatcher(P[0], true).Fuse(&k2, Scw, vpts, Q2[2], repl);
+            res.assign(k2.N, -1);
+            for (int i = 0; i < k2.N; ++i) res[i] = code(k2.mvpMapPoints[i]);
+            put(o, &n, 4); put(o, res.data(), 4 * k2.N);
+            std::vector<int> rc(repl.size());
+            for (size_t i = 0; i < repl.size(); ++i) rc[i] = code(repl[i]);
+            put(o, rc.data(), 4 * (int)rc.size());
+            // (j) SearchBySim3(KF1, KF2, vpMatches12, s12 = 1, R12 = I, t12 = 0, th)
+            reset();
+            std::vector<MapPoint*> m12(k1.N, (MapPoint*)NULL);
+            for (int i = 0; i < k1.N; i += 23) if (k1.mvpMapPoints[i] && i < k2.N && k2.mvpMapPoints[i]) m12[i] = k2.mvpMapPoints[i];
+            cv::Mat R12 = cv::Mat::zeros(3, 3, CV_32F); for (int i = 0; i < 3; ++i) R12.at<float>(i, i) = 1.f;
+            cv::Mat t12 = cv::Mat::zeros(3, 1, CV_32F);
+            const float s12 = 1.0f;
+            n = ORBmatcher(P[0], true).SearchBySim3(&k1, &k2, m12, s12, R12, t12, Q2[3]);
+            res.assign(k1.N, -1);
+            for (int i = 0; i < k1.N; ++i) res[i] = code(m12[i]);
+            put(o, &n, 4); put(o, res.data(), 4 * k1.N);
+        }
     } catch (const std::exception& e) { fprintf(stderr, "error: %s\n", e.what()); return 1; }
     fclose(o);
     return 0;
