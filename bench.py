@@ -81,6 +81,32 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.samples)}
 
 
+def bind_near_gpu(index):
+    """Run this rank on the CPUs of its GPU's NUMA node, so that the pinned host buffers it allocates (first touch) sit
+    behind the same PCIe root as the GPU.  Returns the number of CPUs bound to, or None when the box does not tell."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(index)
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByUUID("GPU-" + str(pr.uuid))
+            pynvml.nvmlDeviceSetCpuAffinity(h)
+        except Exception:
+            bus = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+            node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+            if node < 0:
+                return None
+            cpus = set()
+            for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+            os.sched_setaffinity(0, cpus & os.sched_getaffinity(0) or cpus)
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return None
+
+
 def cpu_oracle_fps(frames, threads, min_seconds=8.0):
     """Time the CPU restatement (oracle/) on `threads` host threads over a bounded sample."""
     import oracle_lib as O
@@ -169,6 +195,8 @@ def run_orbx(args, rank, world):
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    all_cpus = os.sched_getaffinity(0)
+    near = bind_near_gpu(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     B = args.batch
@@ -178,22 +206,43 @@ def run_orbx(args, rank, world):
     ex = P.ORBextractor(NFEAT, SCALE, NLEVELS, INI, MINTH, device=local, max_w=W, max_h=H, max_batch=B)
     cap = ex.max_keypoints()
     d_img = host.to(dev)
-    d_kps = torch.empty((B, cap, 28), dtype=torch.uint8, device=dev)
-    d_desc = torch.empty((B, cap, 32), dtype=torch.uint8, device=dev)
-    d_n = torch.zeros(B, dtype=torch.int32, device=dev)
+    # results are double-buffered when there are several ranks: the gather of step i runs on its own stream under the
+    # extraction of step i + 1 (every gather is still inside the timed region; the last one is waited for before it ends)
+    nbuf = 2 if world > 1 else 1
+    bufs = [(torch.empty((B, cap, 28), dtype=torch.uint8, device=dev), torch.empty((B, cap, 32), dtype=torch.uint8, device=dev),
+             torch.zeros(B, dtype=torch.int32, device=dev)) for _ in range(nbuf)]
+    d_kps, d_desc, d_n = bufs[0]
     stream = torch.cuda.ExternalStream(ex.stream(), device=dev)
     sh = importlib.import_module("orb-slam2-noted_b200.sharding")
     gather = None
-    if world > 1:  # final gather of keypoint/descriptor records over NVLink (fixed padded records)
+    if world > 1:  # gather of keypoint/descriptor records over NVLink (fixed padded records)
         gather = [torch.empty((world * B, cap, 28), dtype=torch.uint8, device=dev),
                   torch.empty((world * B, cap, 32), dtype=torch.uint8, device=dev),
                   torch.empty(world * B, dtype=torch.int32, device=dev)]
+        comm_stream = torch.cuda.Stream(device=dev)
+        extracted = [torch.cuda.Event() for _ in range(nbuf)]
+        gathered = [torch.cuda.Event() for _ in range(nbuf)]
+        for e in gathered:
+            e.record(comm_stream)
+    step_no = [0]
 
     def step():
-        ex.extract_batch_device(d_img, d_kps, d_desc, d_n)
+        k = step_no[0] % nbuf
+        step_no[0] += 1
         if gather is not None:
-            with torch.cuda.stream(stream):
-                sh.gather_frames(d_kps, d_desc, d_n, world, out=gather)
+            stream.wait_event(gathered[k])            # the gather that last read this buffer pair has finished
+        ex.extract_batch_device(d_img, *bufs[k])
+        if gather is not None:
+            extracted[k].record(stream)
+            comm_stream.wait_event(extracted[k])
+            with torch.cuda.stream(comm_stream):
+                sh.gather_frames(*bufs[k], world, out=gather)
+            gathered[k].record(comm_stream)
+
+    def drain():                                      # the extraction stream waits for every gather issued so far
+        if gather is not None:
+            for e in gathered:
+                stream.wait_event(e)
 
     def barrier():
         torch.cuda.synchronize()
@@ -204,6 +253,7 @@ def run_orbx(args, rank, world):
     # ---- device-resident throughput (`value`) ----
     for _ in range(max(args.warmup, 3)):
         step()
+    drain()
     ex.sync()
     ex.set_profiling(True)
     ex.reset_stats()
@@ -215,6 +265,7 @@ def run_orbx(args, rank, world):
     e0.record(stream)
     for _ in range(args.steps):
         step()
+    drain()
     e1.record(stream)
     barrier()
     ms = e0.elapsed_time(e1)
@@ -298,6 +349,7 @@ def run_orbx(args, rank, world):
         cores = os.cpu_count() or 1
         cpu = None
         if world == 1 or True:
+            os.sched_setaffinity(0, all_cpus)              # the CPU baseline gets every host core again
             fps_all, n_all, dt_all = cpu_oracle_fps(frames[:8], cores, min_seconds=8.0)
             cpu = {"value": fps_all, "unit": "frames/s", "cores": cores, "kind": "port",
                    "sample": f"{n_all} frames of the same workload in {dt_all:.1f}s on {cores} host threads (oracle/ restatement)"}
@@ -309,7 +361,9 @@ def run_orbx(args, rank, world):
                                      "~3% of pixels are FAST corners at threshold 7)",
                            "batch_per_gpu": B, "distinct_frames": DISTINCT, "keypoints_per_frame": nkp / B,
                            "l2": f"per-step working set {B * (total_alg + W * H) / 1e6:.0f} MB > 126 MB L2 (no flush needed)",
-                           "parallelism": f"frames sharded, {world} rank(s)" + (", NCCL all_gather of results" if world > 1 else "")},
+                           "host": (f"rank bound to the {near} CPUs of its GPU's NUMA node while pinned buffers are allocated" if near
+                                    else "no NUMA binding"),
+                           "parallelism": f"frames sharded, {world} rank(s)" + (", NCCL all_gather of every step's results on a side stream, overlapped with the next step" if world > 1 else "")},
                 "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
                              "traffic": traffic, "peak_source": "measured" if peaks else "fallback",
                              "algorithmic_bytes_per_frame": alg[dom], "ms_per_launch": per_launch_ms,
