@@ -58,9 +58,28 @@ class ClockSampler(threading.Thread):
         self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
 
     def run(self):
+        # NVML in-process (what nvidia-smi itself reads); one nvidia-smi process per sample only when pynvml is missing
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByUUID("GPU-" + str(torch.cuda.get_device_properties(self.index).uuid))
+            bits = [pynvml.nvmlClocksEventReasonHwSlowdown, pynvml.nvmlClocksEventReasonHwThermalSlowdown,
+                    pynvml.nvmlClocksEventReasonSwThermalSlowdown, pynvml.nvmlClocksEventReasonSwPowerCap]
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            while not self.stop_flag:
+                self.samples.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                for nm, b in zip(names, bits):
+                    if r & b:
+                        self.reasons.add(nm)
+                time.sleep(0.02)
+            return
+        except Exception:
+            pass
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
@@ -290,7 +309,7 @@ def run_orbx(args, rank, world):
                                   ctypes.c_void_p(h_kps.data_ptr()), ctypes.c_void_p(h_desc.data_ptr()), cap,
                                   h_n.ctypes.data_as(ctypes.c_void_p))
         assert rc == 0, rc
-    e2e_steps = max(2, args.steps // 2)
+    e2e_steps = max(2, args.steps)
     for _ in range(2):
         e2e_step()
     barrier()
