@@ -6,7 +6,7 @@
 //           async copies (cp.async.bulk, completion on an mbarrier); the <= 4 reflected columns outside the image are
 //           then filled in shared memory.  Plain loads when the source is not 16-byte aligned.
 //   filter  each warp owns a band of rows, each lane 4 columns.  Walking down its band a lane computes the horizontal
-//           sums of a row with 3 x IDP.4A per pixel (byte windows funnel-shifted from three aligned words) and keeps
+//           sums of a row with 3 x IDP.4A per pixel (three aligned words against byte-shifted weight constants) and keeps
 //           the last 8 rows as (row, row+1) pairs of 16-bit sums in registers, so the vertical pass is 5 x IDP.2A per
 //           pixel with no second trip through shared memory; one 32-bit store per lane per row.
 // HBM traffic = one read + one write of every level.
@@ -100,7 +100,6 @@ gauss9Kernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0
     const int nOut = min(rowsW, vh - yb);
     if (nOut <= 0 || lane >= ng) return;
     const int nH = nOut + 2 * kBlurR;                             // horizontal rows the band needs
-    const uint32_t c0 = 7u | (17u << 8) | (32u << 16) | (46u << 24), c1 = 52u | (46u << 8) | (32u << 16) | (17u << 24);
     const uint32_t k01 = 7u | (17u << 8), k23 = 32u | (46u << 8), k45 = 52u | (46u << 8), k67 = 32u | (17u << 8);
     const uint32_t* rp = &raw[yb][(kRawPad - kBlurR) / 4 + lane];  // words holding columns x0-4+4*lane .. +11 of the band's row 0
     uint8_t* out = blur + g.blurOff + (size_t)frame * g.pitch * g.h + (size_t)(y0 + yb) * g.pitch + x0 + 4 * lane;
@@ -116,12 +115,16 @@ gauss9Kernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lvl0
         // horizontal: H(x) = sum_i k_i * src(x - 4 + i), 9 consecutive bytes
         const uint32_t w0 = rp[0], w1 = rp[1], w2 = rp[2];
         rp += kRawW / 4;
+        // pixel q needs bytes q .. q+8 of (w0, w1, w2): the nine weights are laid over the three aligned words, shifted by q
+        // bytes (compile-time constants), so no byte window has to be cut out of the data
         uint32_t h[4];
         #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const uint32_t a = q ? __funnelshift_r(w0, w1, 8 * q) : w0;
-            const uint32_t b = q ? __funnelshift_r(w1, w2, 8 * q) : w1;
-            h[q] = __dp4a(w2, 7u << (8 * q), __dp4a(b, c1, __dp4a(a, c0, 0u)));
+            constexpr unsigned long long kLo = 7ull | (17ull << 8) | (32ull << 16) | (46ull << 24) | (52ull << 32) | (46ull << 40) | (32ull << 48) | (17ull << 56);
+            const uint32_t k0 = (uint32_t)(kLo << (8 * q));                                  // weights on w0
+            const uint32_t k1 = (uint32_t)(q ? (kLo >> (32 - 8 * q)) : (kLo >> 32));          // weights on w1
+            const uint32_t k2 = (uint32_t)((q ? (kLo >> (64 - 8 * q)) : 0ull) | (7ull << (8 * q)));   // weights on w2 (tap 8 = 7)
+            h[q] = __dp4a(w2, k2, __dp4a(w1, k1, __dp4a(w0, k0, 0u)));
         }
         const uint32_t h01 = h[1] * 65536u + h[0], h23 = h[3] * 65536u + h[2];   // one IMAD each (sums < 65536)
         // pair (r-1, r) completes slot (r-1) & 7

@@ -62,6 +62,7 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) unsigned long long sBar;
     __shared__ int sCellKept[kMaxCellsPerStrip];
+    __shared__ int sRetryN;
 
     const uint4 sdw = __ldg(reinterpret_cast<const uint4*>(strips) + blockIdx.x);
     const int level = sdw.x & 0xff, nc = (sdw.x >> 8) & 0xff, ci = sdw.x >> 16;
@@ -85,6 +86,7 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
     uint16_t* cornerLists = reinterpret_cast<uint16_t*>(colValid + wp);                 // nW x kCornerCapW
     uint16_t* groupLists = cornerLists + nW * kCornerCapW;          // nW x groupCapW
     uint8_t* colCell = reinterpret_cast<uint8_t*>(groupLists + nW * groupCapW);          // cell column of candidate column lx
+    uint16_t* retryCols = reinterpret_cast<uint16_t*>(colCell + SP);                    // sweep 1: word columns with pixels to detect
     const int TH = rh + 6;
     const bool aligned = ((((size_t)img) | pitch) & 15) == 0;
     const int xa = aligned ? ((cx0 - 4) & ~15) : (cx0 - 4) & ~3;    // image column of tile column 0 (>= 4 px left of cx0)
@@ -202,6 +204,18 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
                 }
                 colValid[i] = m;
             }
+            __syncthreads();
+            if (warp == 0) {                                        // ordered list of the word columns left to detect
+                int n = 0;
+                for (int w0 = g0; w0 < g1; w0 += 32) {
+                    const int w = w0 + lane;
+                    const bool on = w < g1 && colValid[w] != 0;
+                    const uint32_t m = __ballot_sync(0xffffffffu, on);
+                    if (on) retryCols[n + __popc(m & ltMask)] = (uint16_t)w;
+                    n += __popc(m);
+                }
+                if (lane == 0) sRetryN = n;
+            }
             if (tmin > tini) {   // scores in [iniTh, minTh) are not corners of this sweep
                 uint32_t* z = reinterpret_cast<uint32_t*>(score);
                 const int nz = (SP * (rh + 2) + 3) / 4;
@@ -214,23 +228,38 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
         // ---- pass 0: quick rejection, 4 pixels per lane step.  A 9-arc contains two adjacent compass pixels, i.e. one
         //      of {0, 8} and one of {4, 12}, both differing from the centre by more than the threshold. ----
         int gcnt = 0;
-        const int nSteps = (g1 - g0 + 31) >> 5;
-        for (int y = warp; y < rh; y += nW) {
-            const uint32_t* c = W + (y + 3) * wp + g0 + lane;      // branch-free steps: lanes past g1 read inside the
-            const uint32_t* cv = colValid + g0 + lane;              // shared-memory block and are masked by vm = 0
-            const uint32_t code0 = (uint32_t)(y << 10) | (uint32_t)(g0 + lane);
-            #pragma unroll 1
-            for (int k = 0; k < nSteps; ++k, c += 32, cv += 32) {
-                const uint32_t vm = (g0 + lane + 32 * k < g1) ? *cv : 0u;
-                const uint32_t v = c[0], up = c[-3 * wp], dn = c[3 * wp];
-                const uint32_t p4 = __funnelshift_r(v, c[1], 24), p12 = __funnelshift_r(c[-1], v, 8);
-                // |p - v| per byte (VABSDIFF4); OR-ing two difference words can only over-estimate their maximum, and
-                // the sign is ignored: a superset of the exact quick test (pass 1 is exact)
-                const uint32_t dv = __vabsdiffu4(dn, v) | __vabsdiffu4(up, v), dh = __vabsdiffu4(p4, v) | __vabsdiffu4(p12, v);
-                const bool pass = (gtu4(dv, T4, nT7) & gtu4(dh, T4, nT7) & vm) != 0;
-                const uint32_t m = __ballot_sync(0xffffffffu, pass);
-                if (pass) myG[gcnt + __popc(m & ltMask)] = (uint16_t)(code0 + 32 * k);
-                gcnt += __popc(m);
+        // one lane step: the 4 pixels of tile word *c (row y, word column in the low bits of code)
+        auto quick = [&](const uint32_t* c, const uint32_t vm, const uint32_t code) {
+            const uint32_t v = c[0], up = c[-3 * wp], dn = c[3 * wp];
+            const uint32_t p4 = __funnelshift_r(v, c[1], 24), p12 = __funnelshift_r(c[-1], v, 8);
+            // |p - v| per byte (VABSDIFF4); OR-ing two difference words can only over-estimate their maximum, and
+            // the sign is ignored: a superset of the exact quick test (pass 1 is exact)
+            const uint32_t dv = __vabsdiffu4(dn, v) | __vabsdiffu4(up, v), dh = __vabsdiffu4(p4, v) | __vabsdiffu4(p12, v);
+            const bool pass = (gtu4(dv, T4, nT7) & gtu4(dh, T4, nT7) & vm) != 0;
+            const uint32_t m = __ballot_sync(0xffffffffu, pass);
+            if (pass) myG[gcnt + __popc(m & ltMask)] = (uint16_t)code;
+            gcnt += __popc(m);
+        };
+        if (!sweep) {
+            const int nSteps = (g1 - g0 + 31) >> 5;
+            for (int y = warp; y < rh; y += nW) {
+                const uint32_t* c = W + (y + 3) * wp + g0 + lane;  // branch-free steps: lanes past g1 read inside the
+                const uint32_t* cv = colValid + g0 + lane;          // shared-memory block and are masked by vm = 0
+                const uint32_t code0 = (uint32_t)(y << 10) | (uint32_t)(g0 + lane);
+                #pragma unroll 1
+                for (int k = 0; k < nSteps; ++k, c += 32, cv += 32)
+                    quick(c, (g0 + lane + 32 * k < g1) ? *cv : 0u, code0 + 32 * k);
+            }
+        } else {
+            // retry sweep: only the word columns of the cells that kept nothing (about a third of a strip's columns)
+            const int nR = sRetryN;
+            for (int k0 = 0; k0 < nR; k0 += 32) {
+                const bool on = k0 + lane < nR;
+                const uint32_t col = on ? retryCols[k0 + lane] : (uint32_t)g0;
+                const uint32_t vm = on ? colValid[col] : 0u;
+                const uint32_t* c = W + 3 * wp + col;
+                #pragma unroll 1
+                for (int y = warp; y < rh; y += nW) quick(c + y * wp, vm, (uint32_t)(y << 10) | col);
             }
         }
         __syncwarp();
@@ -389,7 +418,7 @@ int launchFast(Ctx* c, int frame0, int batch)
         const int nW = c->fastThreads / 32;
         const int groupCapW = (((maxRh + nW - 1) / nW) * ((SP >> 2) + 2) + 1) & ~1;   // rows of a warp x group columns of a row
         size_t smem = (size_t)TP * TR + (size_t)SP * (maxRh + 2) + sizeof(uint32_t) * (size_t)(TP >> 2);
-        smem += sizeof(uint16_t) * (size_t)nW * (kCornerCapW + groupCapW) + (size_t)SP;
+        smem += sizeof(uint16_t) * (size_t)nW * (kCornerCapW + groupCapW) + (size_t)SP + sizeof(uint16_t) * (size_t)(TP >> 2);
         smem = (smem + 127) & ~(size_t)127;
         dim3 grid(c->nStrips, batch);
         auto go = [&](auto kern, int threads, size_t* configured) -> int {
