@@ -241,14 +241,21 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
             gcnt += __popc(m);
         };
         if (!sweep) {
-            const int nSteps = (g1 - g0 + 31) >> 5;
-            for (int y = warp; y < rh; y += nW) {
-                const uint32_t* c = W + (y + 3) * wp + g0 + lane;  // branch-free steps: lanes past g1 read inside the
-                const uint32_t* cv = colValid + g0 + lane;          // shared-memory block and are masked by vm = 0
-                const uint32_t code0 = (uint32_t)(y << 10) | (uint32_t)(g0 + lane);
+            // column chunks of 32 words, rows inside: a lane keeps its column (and that column's mask) for the whole chunk.
+            // A last chunk of <= 16 columns is laid over the warp q = 32 / width times, each copy taking every q-th row.
+            for (int k0 = g0; k0 < g1; k0 += 32) {
+                const int wk = min(32, g1 - k0);
+                const int q = min(32 / wk, 8), sub = lane / wk;    // q >= 1; lanes with sub >= q idle
+                const uint32_t col = (uint32_t)(k0 + lane - sub * wk);
+                const uint32_t vm = sub < q ? colValid[col] : 0u;
+                const int yStep = nW * q;
+                int y = warp + nW * sub;
+                const uint32_t* const cSafe = W + 3 * wp + col;     // lanes past the last row read row 0 (masked by vm = 0)
+                const uint32_t* c = W + (y + 3) * wp + col;
+                uint32_t code = (uint32_t)(y << 10) | col;
                 #pragma unroll 1
-                for (int k = 0; k < nSteps; ++k, c += 32, cv += 32)
-                    quick(c, (g0 + lane + 32 * k < g1) ? *cv : 0u, code0 + 32 * k);
+                for (int yl = warp; yl < rh; yl += yStep, y += yStep, c += yStep * wp, code += (uint32_t)(yStep << 10))
+                    quick(y < rh ? c : cSafe, y < rh ? vm : 0u, code);
             }
         } else {
             // retry sweep: only the word columns of the cells that kept nothing (about a third of a strip's columns)
