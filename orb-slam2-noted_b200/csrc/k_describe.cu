@@ -268,15 +268,23 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
         const uint32_t* buf = bufBase + (k % kDepth) * kPatchWords;
         const int offc = (cx - kPatchR) - ((cx - kPatchR) & ~15) + kPatchR;                // byte column of the patch centre
         const uint8_t* pc = reinterpret_cast<const uint8_t*>(buf) + kPatchR * (kPatchPitchW * 4) + offc;
+        // cvRound without the conversion unit: x + 1.5 * 2^23 rounds x (|x| < 2^22) to the nearest integer, ties to even,
+        // and leaves it in the low mantissa bits; the constant part of (row * pitch + col) is folded into the base address
+        constexpr float kMagic = 12582912.0f;
+        constexpr uint32_t kMagicBits = 0x4B400000u, kPitchB = kPatchPitchW * 4;
+        const uint32_t pcm = (uint32_t)__cvta_generic_to_shared(pc) - kMagicBits * (kPitchB + 1u);
+        auto sample = [&](float fx, float fy) -> uint32_t {          // pattern point (fx, fy) rotated by the keypoint angle
+            const float r = __fadd_rn(__fadd_rn(__fmul_rn(fx, b), __fmul_rn(fy, a)), kMagic);
+            const float c = __fadd_rn(__fsub_rn(__fmul_rn(fx, a), __fmul_rn(fy, b)), kMagic);
+            uint32_t v;
+            asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(pcm + __float_as_uint(r) * kPitchB + __float_as_uint(c)));
+            return v;
+        };
         int val = 0;
         #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const float4 q = pat[j];
-            const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(q.x, b), __fmul_rn(q.y, a)));
-            const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(q.x, a), __fmul_rn(q.y, b)));
-            const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(q.z, b), __fmul_rn(q.w, a)));
-            const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(q.z, a), __fmul_rn(q.w, b)));
-            const int t0 = pc[r0 * (kPatchPitchW * 4) + c0], t1 = pc[r1 * (kPatchPitchW * 4) + c1];
+            const uint32_t t0 = sample(q.x, q.y), t1 = sample(q.z, q.w);
             val |= (t0 < t1) << j;
         }
         outDesc[((size_t)frame * cap + (i0 + k)) * 32 + lane] = (uint8_t)val;
