@@ -298,10 +298,9 @@ extern "C" int orbx_bow_vector(orbx_ctx* h, const orbx_vocab* v, const int32_t* 
     if (!inDev) { ORBX_CUDA(c, cudaMemcpyAsync(S + oW, word, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, c->stream)); dW = (const int32_t*)(S + oW); }
     int32_t* dI = outDev ? ids : (int32_t*)(S + oI);
     double* dV = outDev ? values : (double*)(S + oV);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
+    if (smem > 48 * 1024 && smem > c->smemCfg[SMEM_BOW_VECTOR]) {
         ORBX_CUDA(c, cudaFuncSetAttribute(bowVectorKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+        c->smemCfg[SMEM_BOW_VECTOR] = smem;
     }
     stageBegin(c, ST_BOW);
     bowVectorKernel<<<1, kBowThreads, smem, c->stream>>>(dW, n, npow2, v->dWordWeight, v->wordCap, dI, dV, (int*)(S + oN));

@@ -353,10 +353,9 @@ int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* 
     const int perBlock = kDescWarps * kpw;
     dim3 grid((slots + perBlock - 1) / perBlock, batch), block(kDescWarps * 32);
     const size_t smem = sizeof(uint32_t) * (size_t)kDescWarps * kDepth * kPatchWords;
-    static bool configured = false;
-    if (!configured) {
+    if (smem > c->smemCfg[SMEM_DESCRIBE]) {
         ORBX_CUDA(c, cudaFuncSetAttribute(describeKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
+        c->smemCfg[SMEM_DESCRIBE] = smem;
     }
     describeKernel<<<grid, block, smem, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur,
                                                  c->dSel, c->dSelCount, dKps, dDesc, capPerFrame, dN, c->dErr, kpw);

@@ -437,8 +437,8 @@ int launchFast(Ctx* c, int frame0, int batch)
                                                            c->dCand, c->dCandCount, TP, TR, SP, groupCapW);
             return ORBX_OK;
         };
-        static size_t cfg256 = 0, cfg128 = 0;
-        const int rc = c->fastThreads == 128 ? go(fastStripKernel<128, 8>, 128, &cfg128) : go(fastStripKernel<256, 4>, 256, &cfg256);
+        const int rc = c->fastThreads == 128 ? go(fastStripKernel<128, 8>, 128, &c->smemCfg[SMEM_FAST128])
+                                             : go(fastStripKernel<256, 4>, 256, &c->smemCfg[SMEM_FAST256]);
         if (rc != ORBX_OK) return rc;
         launches = 1;
     }

@@ -375,10 +375,9 @@ int launchBowJobs(Ctx* c, const BowJob* dJobs, int njobs, int maxTiles, int maxS
         const int maskWords = (maxN2 + 31) / 32 + 1;
         const size_t smem = (size_t)kBWarps * maskWords * sizeof(uint32_t);
         if (smem > 200 * 1024) return ORBX_E_CAPACITY;
-        static size_t configured = 0;
-        if (smem > 48 * 1024 && smem > configured) {
+        if (smem > 48 * 1024 && smem > c->smemCfg[SMEM_BOW_RESOLVE]) {
             ORBX_CUDA(c, cudaFuncSetAttribute(bowResolveKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            configured = smem;
+            c->smemCfg[SMEM_BOW_RESOLVE] = smem;
         }
         bowResolveKernel<<<dim3((maxSeg + kBWarps - 1) / kBWarps, njobs), kBWarps * 32, smem, c->stream>>>(dJobs, maskWords);
         ++launches;

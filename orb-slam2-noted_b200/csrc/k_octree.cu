@@ -276,10 +276,9 @@ int launchOctree(Ctx* c, int frame0, int batch)
     M = (M + 7) & ~7;
     const size_t smem = octreeSmem(M);
     if (smem > 200 * 1024) return ORBX_E_UNSUPPORTED;
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
+    if (smem > 48 * 1024 && smem > c->smemCfg[SMEM_OCTREE]) {
         ORBX_CUDA(c, cudaFuncSetAttribute(octreeKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
+        c->smemCfg[SMEM_OCTREE] = smem;
     }
     stageBegin(c, ST_OCTREE);
     dim3 grid(g.nlevels, batch), block(kOctThreads);

@@ -59,8 +59,13 @@ struct GeomSet {            // what kernels need, uploaded to constant memory on
     int umax[16];
 };
 
+// kernels with more than 48 KB of dynamic shared memory: cudaFuncSetAttribute is per device, so what has been configured is
+// remembered per context (a context belongs to one device and one caller), not in a process-wide static
+enum { SMEM_FAST128, SMEM_FAST256, SMEM_DESCRIBE, SMEM_OCTREE, SMEM_BOW_RESOLVE, SMEM_BOW_VECTOR, SMEM_SLOTS };
+
 struct Ctx {
     int device = 0;
+    size_t smemCfg[SMEM_SLOTS] = {};
     cudaStream_t stream = nullptr;
     cudaStream_t sIn = nullptr, sOut = nullptr;   // copy streams of the chunked pipeline (H2D / D2H overlap compute)
     cudaStream_t stream2 = nullptr;               // odd chunks of the pipeline run here, so kernels of neighbouring chunks fill each other's tails

@@ -89,6 +89,29 @@ def test_batch_equals_single(P):
         assert_kps_equal(res[b][0], okps, res[b][1], odesc, b)
 
 
+def test_two_callers_two_handles(P):
+    """The end-to-end pattern of bench.py: two host threads, one extractor handle each, batches in flight at the same time
+    (the handles share the device, nothing else); every result equals the single-caller result."""
+    import threading
+    imgs = [np.stack([synth.frame(100 * t + s, 320, 240) for s in range(6)]) for t in range(2)]
+    exs = [P.ORBextractor(500, 1.2, 8, 20, 7, max_w=320, max_h=240, max_batch=6) for _ in range(2)]
+    want = [exs[0].extract_batch(im) for im in imgs]
+    got = [[None] * 4 for _ in range(2)]
+
+    def work(t):
+        for r in range(4):
+            got[t][r] = exs[t].extract_batch(imgs[t])
+    th = [threading.Thread(target=work, args=(t,)) for t in range(2)]
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    for t in range(2):
+        for r in range(4):
+            for (k0, d0), (k1, d1) in zip(want[t], got[t][r]):
+                assert_kps_equal(k1, k0, d1, d0, (t, r))
+
+
 def test_configs_geometry_1080p(P):
     img = synth.frame(5, 1920, 1080)
     ex = P.ORBextractor(4000, 1.2, 8, 20, 7, max_w=1920, max_h=1080)
