@@ -128,7 +128,8 @@ resizeLinearWordKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sF
         for (int k = 0; k < 4; ++k) {
             uint32_t tc[4];
             hcompute(w[k], tc);                               // row rb + 1
-            while (y < ye && ty.s == rb) {                    // rows (rb, rb+1) are this destination row's pair
+            if (y < ye && ty.s == rb) {                       // rows (rb, rb+1) are this destination row's pair: at most one
+                                                              // destination row per source row (the host checks that the taps rise)
                 // (b * t) >> 16 as the high word of (b << 16) * t: weights and sums are non-negative
                 const uint32_t b0 = (uint32_t)ty.c0 << 16, b1 = (uint32_t)ty.c1 << 16;
                 uint32_t v[4];

@@ -199,6 +199,7 @@ static int configure(Ctx* c, int w, int h)
         }
         for (const ResizeTap& t : tx) if (t.c0 < 0 || t.c1 < 0) wordOk = false;
         for (const ResizeTap& t : ty) if (t.c0 < 0 || t.c1 < 0) wordOk = false;
+        for (size_t y = 1; y < ty.size(); ++y) if (ty[y].s <= ty[y - 1].s) wordOk = false;   // one destination row per source row at most
         c->resizeWordOk[l] = wordOk;
         ORBX_CUDA(c, cudaMalloc(&c->dTapX[l], sizeof(ResizeTap) * tx.size()));
         ORBX_CUDA(c, cudaMalloc(&c->dTapY[l], sizeof(ResizeTap) * ty.size()));
