@@ -19,7 +19,7 @@
 
 namespace orbx {
 
-constexpr int kOctThreads = 256;
+constexpr int kOctThreads = 128;
 
 // inclusive block scan of data[0..n) in place; returns the total. All threads must call.
 __device__ int blockInclusiveScan(int* data, int n, int* warpSums)
