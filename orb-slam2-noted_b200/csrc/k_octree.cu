@@ -19,12 +19,12 @@
 
 namespace orbx {
 
-constexpr int kOctThreads = 128;
+constexpr int kOctThreadsMax = 512;   // CTA size is chosen per launch (128 for VGA-class frames, more when a level holds many candidates)
 
 // inclusive block scan of data[0..n) in place; returns the total. All threads must call.
 __device__ int blockInclusiveScan(int* data, int n, int* warpSums)
 {
-    const int T = kOctThreads;
+    const int T = blockDim.x;
     const int per = (n + T - 1) / T;
     const int b = threadIdx.x * per, e = min(b + per, n);
     int sum = 0;
@@ -67,12 +67,12 @@ __device__ __forceinline__ int quadrant(const Box& b, int x, int y)
     return (x < mx ? 0 : 1) + (y < my ? 0 : 2);        // 0..3 = n1,n2,n3,n4  :659-669
 }
 
-__global__ void __launch_bounds__(kOctThreads)
+__global__ void __launch_bounds__(kOctThreadsMax)
 octreeKernel(const __grid_constant__ GeomSet G, unsigned long long* __restrict__ candAll, const int* __restrict__ candCount,
              orbx_keypoint* __restrict__ selAll, int* __restrict__ selCount, int M, int* __restrict__ err)
 {
     extern __shared__ __align__(16) uint8_t smemRaw[];
-    __shared__ int warpSums[kOctThreads / 32];
+    __shared__ int warpSums[kOctThreadsMax / 32];
     __shared__ int sL, sNSplit, sC, sFinish, sMode;
 
     const int level = blockIdx.x, frame = blockIdx.y + G.frame0;
@@ -96,7 +96,7 @@ octreeKernel(const __grid_constant__ GeomSet G, unsigned long long* __restrict__
     unsigned short* childPos = reinterpret_cast<unsigned short*>(newPos + M); // 4*M
     unsigned long long* best = reinterpret_cast<unsigned long long*>(childCnt); // aliases childCnt (final phase)
 
-    const int T = kOctThreads, tid = threadIdx.x;
+    const int T = blockDim.x, tid = threadIdx.x;
     const int winH = (g.h - kEdge + 3) - kWinOff; // maxY - minY
 
     // ---- roots (:719-749) ----
@@ -154,14 +154,16 @@ octreeKernel(const __grid_constant__ GeomSet G, unsigned long long* __restrict__
         if (mode == 0) {
             for (int p = tid; p < L; p += T) if (cnt[p] > 1) ord[scanA[p] - 1] = p;
         } else {
-            // rank among expandable: size desc, then list position asc (canonical tie-break)
-            for (int p = tid; p < L; p += T) {
-                const int c = cnt[p];
-                if (c > 1) {
-                    int r = 0;
-                    for (int q = 0; q < L; ++q) { const int cq = cnt[q]; r += (cq > 1) && (cq > c || (cq == c && q < p)); }
-                    ord[r] = p;
-                }
+            // rank among expandable: size desc, then list position asc (canonical tie-break).  The E expandable nodes are
+            // packed in list order with key = count : (4095 - position) (M <= 3400, counts < 2^20), rank = larger keys.
+            uint32_t* key = reinterpret_cast<uint32_t*>(newPos);                 // free until step (d)
+            for (int p = tid; p < L; p += T) if (cnt[p] > 1) key[scanA[p] - 1] = ((uint32_t)cnt[p] << 12) | (uint32_t)(4095 - p);
+            __syncthreads();
+            for (int e = tid; e < E; e += T) {
+                const uint32_t k = key[e];
+                int r = 0;
+                for (int q = 0; q < E; ++q) r += key[q] > k;
+                ord[r] = 4095 - (int)(k & 4095u);
             }
         }
         __syncthreads();
@@ -281,7 +283,12 @@ int launchOctree(Ctx* c, int frame0, int batch)
         c->smemCfg[SMEM_OCTREE] = smem;
     }
     stageBegin(c, ST_OCTREE);
-    dim3 grid(g.nlevels, batch), block(kOctThreads);
+    // the rounds are barrier-bound: small CTAs for VGA-class levels, larger ones when level 0 can hold tens of thousands of candidates
+    static const int envThreads = getenv("ORBX_OCT_THREADS") ? atoi(getenv("ORBX_OCT_THREADS")) : 0;
+    const int area = g.lv[0].w * g.lv[0].h;
+    int threads = area > 1000 * 1000 ? 512 : area > 400 * 1000 ? 256 : 128;   // measured: VGA 128, KITTI 1241x376 256, 1080p 512
+    if (envThreads >= 32 && envThreads <= kOctThreadsMax && envThreads % 32 == 0) threads = envThreads;
+    dim3 grid(g.nlevels, batch), block(threads);
     octreeKernel<<<grid, block, smem, c->stream>>>(g, c->dCand, c->dCandCount, c->dSel, c->dSelCount, M, c->dErr);
     stageEnd(c, ST_OCTREE, 1);
     ORBX_CUDA(c, cudaGetLastError());
