@@ -422,7 +422,8 @@ int launchFast(Ctx* c, int frame0, int batch)
     if (c->nStrips > 0) {
         const int TP = g.fastTilePitch, TR = g.fastTileRows, SP = g.fastScorePitch;
         const int maxRh = TR - 6;
-        const int nW = c->fastThreads / 32;
+        const int fastThreads = (long long)batch * c->nStrips < 148 * 8 ? 256 : c->fastThreads;   // few CTAs: more warps per strip
+        const int nW = fastThreads / 32;
         const int groupCapW = (((maxRh + nW - 1) / nW) * ((SP >> 2) + 2) + 1) & ~1;   // rows of a warp x group columns of a row
         size_t smem = (size_t)TP * TR + (size_t)SP * (maxRh + 2) + sizeof(uint32_t) * (size_t)(TP >> 2);
         smem += sizeof(uint16_t) * (size_t)nW * (kCornerCapW + groupCapW) + (size_t)SP + sizeof(uint16_t) * (size_t)(TP >> 2);
@@ -437,7 +438,7 @@ int launchFast(Ctx* c, int frame0, int batch)
                                                            c->dCand, c->dCandCount, TP, TR, SP, groupCapW);
             return ORBX_OK;
         };
-        const int rc = c->fastThreads == 128 ? go(fastStripKernel<128, 8>, 128, &c->smemCfg[SMEM_FAST128])
+        const int rc = fastThreads == 128 ? go(fastStripKernel<128, 8>, 128, &c->smemCfg[SMEM_FAST128])
                                              : go(fastStripKernel<256, 4>, 256, &c->smemCfg[SMEM_FAST256]);
         if (rc != ORBX_OK) return rc;
         launches = 1;

@@ -287,6 +287,7 @@ int launchOctree(Ctx* c, int frame0, int batch)
     static const int envThreads = getenv("ORBX_OCT_THREADS") ? atoi(getenv("ORBX_OCT_THREADS")) : 0;
     const int area = g.lv[0].w * g.lv[0].h;
     int threads = area > 1000 * 1000 ? 512 : area > 400 * 1000 ? 256 : 128;   // measured: VGA 128, KITTI 1241x376 256, 1080p 512
+    if (batch * g.nlevels < 2 * 148) threads = 512;                        // a frame or two: latency of the rounds, not throughput
     if (envThreads >= 32 && envThreads <= kOctThreadsMax && envThreads % 32 == 0) threads = envThreads;
     dim3 grid(g.nlevels, batch), block(threads);
     octreeKernel<<<grid, block, smem, c->stream>>>(g, c->dCand, c->dCandCount, c->dSel, c->dSelCount, M, c->dErr);

@@ -64,8 +64,9 @@ resizeLinearKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sFrame
 // Fast path (scale <= ~1.33, word-aligned source): the 4 destination pixels of a thread read at most 8 consecutive
 // source bytes counted from an aligned word, so one horizontal pass is 3 aligned 32-bit loads, and per pixel one
 // funnel shift (bytes s, s+1 into the low half) and one IDP.2A against the (c0, c1) weight pair.
-constexpr int kResizeRowsFast = 16;
-
+// kRows destination rows per thread: 16 for batches that fill the GPU (a source row is reduced once for ~1.2 destination rows,
+// taps and pointers amortised), 2 for a single frame or a stereo pair, where the chain of dependent loads per thread is the latency
+template <int kRows>
 __global__ void __launch_bounds__(128)
 resizeLinearWordKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sFrame, int sw, int sh,
                        uint8_t* __restrict__ dst, size_t dPitch, size_t dFrame, int dw, int dh,
@@ -76,7 +77,7 @@ resizeLinearWordKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sF
     const int item = blockIdx.x * blockDim.x + threadIdx.x;
     const int band = item / groups;
     const int x0 = (item - band * groups) * 4;
-    if (band * kResizeRowsFast >= dh) return;
+    if (band * kRows >= dh) return;
     uint32_t cpair[4], shift[4], pick[4];       // pick = all ones when the pixel's byte pair starts in the second word
     int base = 0;
     #pragma unroll
@@ -89,7 +90,7 @@ resizeLinearWordKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sF
     }
     const int pw = (int)(sPitch >> 2);
     const bool has1 = base + 1 < pw, has2 = base + 2 < pw;   // words past the row end only ever meet zero weights
-    const int yb = band * kResizeRowsFast, ye = min(yb + kResizeRowsFast, dh);
+    const int yb = band * kRows, ye = min(yb + kRows, dh);
     int y = yb;
     ResizeTap ty = tapY[y];
     int r = ty.s;                                             // source row the pointer is on
@@ -209,10 +210,17 @@ int launchPyramid(Ctx* c, int frame0, int batch)
         else { src = c->dPyr + s.planeOff; sp = (size_t)s.pitch; sf = (size_t)s.pitch * s.h; }
         const bool wordOk = c->resizeWordOk[l] && ((((size_t)src) | sp | sf) & 3) == 0;
         if (wordOk) {
-            const int items = ((d.w + 3) / 4) * ((d.h + kResizeRowsFast - 1) / kResizeRowsFast);
+            const int groups = (d.w + 3) / 4;
+            const bool small = (long long)batch * groups * ((d.h + 15) / 16) < 148LL * 640;     // too few threads to fill the GPU
+            const int rows = small ? 2 : 16;
+            const int items = groups * ((d.h + rows - 1) / rows);
             dim3 grid((items + 127) / 128, 1, batch), block(128);
-            resizeLinearWordKernel<<<grid, block, 0, c->stream>>>(src, sp, sf, s.w, s.h, c->dPyr + d.planeOff, (size_t)d.pitch,
-                                                                 (size_t)d.pitch * d.h, d.w, d.h, c->dTapX[l], c->dTapY[l], frame0);
+            if (small)
+                resizeLinearWordKernel<2><<<grid, block, 0, c->stream>>>(src, sp, sf, s.w, s.h, c->dPyr + d.planeOff, (size_t)d.pitch,
+                                                                        (size_t)d.pitch * d.h, d.w, d.h, c->dTapX[l], c->dTapY[l], frame0);
+            else
+                resizeLinearWordKernel<16><<<grid, block, 0, c->stream>>>(src, sp, sf, s.w, s.h, c->dPyr + d.planeOff, (size_t)d.pitch,
+                                                                         (size_t)d.pitch * d.h, d.w, d.h, c->dTapX[l], c->dTapY[l], frame0);
         } else {
             dim3 grid((d.w + 511) / 512, (d.h + kResizeRows - 1) / kResizeRows, batch), block(128);
             resizeLinearKernel<<<grid, block, 0, c->stream>>>(src, sp, sf, s.w, s.h, c->dPyr + d.planeOff, (size_t)d.pitch,
