@@ -506,7 +506,8 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
             ORBX_CUDA(c, cudaStreamWaitEvent(c->stream, c->evIn[i], 0));
         }
         rc = launchPyramid(c, f0, n);
-        if (!rc && c->overlapBlur && !twoStreams) {
+        const bool fewCtas = (long long)n * c->nStrips < 148 * 8;   // a frame or two: kernels leave most SMs idle, so the blur runs beside FAST
+        if (!rc && (c->overlapBlur || fewCtas) && !twoStreams) {
             // the blur only needs the pyramid: it runs on a side stream next to FAST + quadtree (FAST is limited to 5 CTAs per
             // SM by shared memory and leaves registers, shared memory and issue slots for a blur CTA) and joins before describe
             cudaStream_t const s0 = c->stream;
