@@ -89,6 +89,21 @@ def test_batch_equals_single(P):
         assert_kps_equal(res[b][0], okps, res[b][1], odesc, b)
 
 
+def test_throughput_launch_shapes_equal_latency_shapes(P):
+    """A batch that fills the GPU takes other launch shapes than a single frame (16-row resize threads, 128-thread FAST and
+    quadtree CTAs, blur in line); both must give the oracle's result."""
+    distinct = [synth.frame(300 + i, 640, 480, "texture" if i % 4 else "noise") for i in range(8)]
+    imgs = np.stack([distinct[i % 8] for i in range(96)])
+    ex = P.ORBextractor(1000, 1.2, 8, 20, 7, max_w=640, max_h=480, max_batch=96)
+    res = ex.extract_batch(imgs)
+    p = O.params(1000)
+    want = [O.extract(p, im) for im in distinct]
+    for b in range(96):
+        assert_kps_equal(res[b][0], want[b % 8][0], res[b][1], want[b % 8][1], b)
+    one = ex.extract_batch(imgs[:1])
+    assert_kps_equal(one[0][0], want[0][0], one[0][1], want[0][1], "single")
+
+
 def test_two_callers_two_handles(P):
     """The end-to-end pattern of bench.py: two host threads, one extractor handle each, batches in flight at the same time
     (the handles share the device, nothing else); every result equals the single-caller result."""
