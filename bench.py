@@ -8,6 +8,11 @@ A step = one pass of ORBextractor::operator() over a batch of B synthetic frames
 `value`  : frames/s with frames already resident in HBM, results left in HBM (CUDA events, max over ranks).
 `e2e`    : the same metric through the host-buffer C-ABI call (pinned host images in, host keypoints and
            descriptors out; H2D and D2H inside the timed region).
+           Two host threads, one extractor handle and one set of pinned buffers each, take alternate
+           batches through the synchronous orbx_extract_batch, so the PCIe link stays busy between calls;
+           every step's input copy and result read-back is inside the timed region.
+           With N > 1 every step's results are also all-gathered over NCCL (side stream, inside the
+           timed region of `value`).
 `--impl reference`: the CPU restatement of the reference path (oracle/, the only executable copy of the
            reference here - it needs OpenCV C++ to compile) on all host cores, bounded sample per step.
 """
