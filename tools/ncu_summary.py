@@ -24,7 +24,7 @@ def main():
     print("kernel," + ",".join(WANT))
     for r in rows[2:]:
         name = r[hdr.index('Kernel Name')].split('(')[0]
-        print(name + "," + ",".join(r[hdr.index(w)] if w in hdr else "" for w in WANT))
+        print('"' + name + '",' + ",".join(r[hdr.index(w)] if w in hdr else "" for w in WANT))   # template names hold commas
     for k in sys.argv[2:]:
         rows = list(csv.reader(io.StringIO(ncu(["-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + k]))))
         if len(rows) < 3:
