@@ -10,6 +10,7 @@
 //    reduction + polynomial with exactly the FMA contraction pattern of that build;
 //  * sample coordinates use cvRound = round-half-even = __float2int_rn.
 #include "orbx_internal.h"
+#include <type_traits>
 #include <algorithm>
 
 namespace orbx {
@@ -221,20 +222,30 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
             const uint32_t* buf = bufBase + (k % kDepth) * kRawWords;
             int m10 = 0, m01 = 0;
             if (lane < 2 * kHalfPatch + 1) {
-                const uint32_t* row = buf + lane * kRawPitchW + (((cx - kHalfPatch) & 15) >> 2);   // word holding u = -15
-                const uint32_t sh = 8u * (uint32_t)((cx - kHalfPatch) & 3);                         // its byte inside that word
-                uint32_t w[9];
-                #pragma unroll
-                for (int j = 0; j < 9; ++j) w[j] = row[j];
+                // the row's 12 words as three 128-bit loads: with a pitch of 12 words the 8 lanes of a quarter warp cover all 32
+                // banks (32-bit loads of one word column would hit only 8 banks: 4-way conflicts)
+                const uint4* row4 = reinterpret_cast<const uint4*>(buf + lane * kRawPitchW);
+                const uint4 q0 = row4[0], q1 = row4[1], q2 = row4[2];
+                const uint32_t w[12] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w};
+                const uint32_t sh = 8u * (uint32_t)((cx - kHalfPatch) & 3);                         // byte of u = -15 inside its word
                 int cs = 0;
-                #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const uint32_t x = __funnelshift_r(w[j], w[j + 1], sh) & icMask[j];
-                    // signed weights u = 4j-15 .. 4j-12 of the word's four bytes
-                    const int uw = (int)(((uint32_t)(uint8_t)(4 * j - 15)) | ((uint32_t)(uint8_t)(4 * j - 14) << 8) |
-                                         ((uint32_t)(uint8_t)(4 * j - 13) << 16) | ((uint32_t)(uint8_t)(4 * j - 12) << 24));
-                    cs = (int)__dp4a(x, 0x01010101u, (uint32_t)cs);
-                    asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(x), "r"(uw));
+                auto rowSums = [&](auto oc) {                                                       // oc = word holding u = -15
+                    constexpr int o = decltype(oc)::value;
+                    #pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const uint32_t x = __funnelshift_r(w[o + j], w[o + j + 1], sh) & icMask[j];
+                        // signed weights u = 4j-15 .. 4j-12 of the word's four bytes
+                        const int uw = (int)(((uint32_t)(uint8_t)(4 * j - 15)) | ((uint32_t)(uint8_t)(4 * j - 14) << 8) |
+                                             ((uint32_t)(uint8_t)(4 * j - 13) << 16) | ((uint32_t)(uint8_t)(4 * j - 12) << 24));
+                        cs = (int)__dp4a(x, 0x01010101u, (uint32_t)cs);
+                        asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(x), "r"(uw));
+                    }
+                };
+                switch (((cx - kHalfPatch) & 15) >> 2) {                                            // warp-uniform
+                    case 0: rowSums(std::integral_constant<int, 0>()); break;
+                    case 1: rowSums(std::integral_constant<int, 1>()); break;
+                    case 2: rowSums(std::integral_constant<int, 2>()); break;
+                    default: rowSums(std::integral_constant<int, 3>()); break;
                 }
                 m01 = (lane - kHalfPatch) * cs;
             }
