@@ -31,7 +31,7 @@ public:
     // observation bookkeeping, reduced to what ORBmatcher::Fuse / SearchBySim3 touch (src/MapPoint.cc:139-330)
     bool IsInKeyFrame(KeyFrame* pKF) { return mObs.count(pKF) != 0; }
     int GetIndexInKeyFrame(KeyFrame* pKF) { return mObs.count(pKF) ? (int)mObs[pKF] : -1; }
-    void AddObservation(KeyFrame* pKF, size_t idx) { if (!mObs.count(pKF)) { mObs[pKF] = idx; ++nObs; } }
+    void AddObservation(KeyFrame* pKF, size_t idx);                      // :139-150 (+2 for a stereo keypoint)
     void Replace(MapPoint* pMP);
     int PredictScale(const float& currentDist, KeyFrame* pKF);          // src/MapPoint.cc:584-604
     int PredictScale(const float& currentDist, Frame* pF);              // :613-631
@@ -93,6 +93,13 @@ public:
     std::vector<MapPoint*> mvpMapPoints;
     cv::Mat Ow, Rcw, tcw;
 };
+
+inline void MapPoint::AddObservation(KeyFrame* pKF, size_t idx)
+{
+    if (mObs.count(pKF)) return;
+    mObs[pKF] = idx;
+    nObs += (idx < pKF->mvuRight.size() && pKF->mvuRight[idx] >= 0) ? 2 : 1;
+}
 
 // MapPoint::Replace, src/MapPoint.cc:257-311, reduced: this point goes bad, its observations move to pMP
 inline void MapPoint::Replace(MapPoint* pMP)

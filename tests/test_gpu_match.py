@@ -20,25 +20,7 @@ def ctx(P):
     return P.ORBextractor(1000, 1.2, 8, 20, 7, max_w=64, max_h=64)
 
 
-def make_pair(seed, n1, n2, flip=0.08, dup=0.0, nlevels=8, KP=None):
-    """Two feature sets with true correspondences: set 2 = perturbed, shuffled subset of set 1 + random rest."""
-    rng = np.random.default_rng(seed)
-    d1 = synth.descriptors(seed, n1)
-    if dup > 0:  # many identical descriptors: forces claimed-entry handling and node rescans
-        src = rng.integers(0, max(1, int(n1 * (1 - dup))), n1)
-        d1 = d1[src]
-    m = min(n1, n2) * 3 // 4
-    pick = rng.permutation(n1)[:m]
-    d2 = np.concatenate([synth.descriptors(seed + 1, m, flip, d1[pick]), synth.descriptors(seed + 2, n2 - m)])
-    k1 = synth.keypoints(seed + 3, n1, dtype=KP)
-    k2 = synth.keypoints(seed + 4, n2, dtype=KP)
-    rot = np.float32(37.5)
-    k2["angle"][:m] = np.mod(k1["angle"][pick] - rot + rng.normal(0, 3, m).astype(np.float32), np.float32(360)).astype(np.float32)
-    k2["x"][:m] = k1["x"][pick] + rng.normal(0, 2, m).astype(np.float32)
-    k2["y"][:m] = k1["y"][pick] + rng.normal(0, 2, m).astype(np.float32)
-    k2["octave"][:m] = k1["octave"][pick]
-    perm = rng.permutation(n2)
-    return d1, k1, d2[perm], k2[perm]
+from matcher_scene import make_pair
 
 
 def sides(P, voc_o, voc_g, d1, k1, d2, k2, levelsup, seed, p_has=0.7, stereo=False):
@@ -133,22 +115,8 @@ def test_assign_grid_matches_oracle(P, ctx):
 
 
 def proj_scene(P, seed, n, nq):
-    rng = np.random.default_rng(seed)
-    keys = synth.keypoints(seed, n, 640, 480, dtype=P.KP_DTYPE)
-    desc = synth.descriptors(seed + 1, n)
-    src = rng.integers(0, n, nq)
-    pts = np.zeros(nq, O.PROJ_DTYPE)
-    pts["u"] = keys["x"][src] + rng.normal(0, 3, nq).astype(np.float32)
-    pts["v"] = keys["y"][src] + rng.normal(0, 3, nq).astype(np.float32)
-    pts["u"][:4] = [-30, 900, 100, 320]; pts["v"][:4] = [100, 100, -50, 700]
-    pts["level"] = np.clip(keys["octave"][src] + rng.integers(-1, 2, nq), 0, 7)
-    pts["view_cos"] = np.where(rng.random(nq) < 0.5, 0.9995, 0.9).astype(np.float32)
-    pts["angle"] = np.mod(keys["angle"][src] + 20 + rng.normal(0, 4, nq), 360).astype(np.float32)
-    pts["desc"] = synth.descriptors(seed + 2, nq, 0.12, desc[src])
-    uright = np.where(rng.random(n) < 0.6, keys["x"] - 8, -1).astype(np.float32)
-    pts["ur"] = pts["u"] - 8 + rng.normal(0, 6, nq).astype(np.float32)
-    occupied = (rng.random(n) < 0.1).astype(np.uint8)
-    return keys, desc, uright, occupied, pts
+    import matcher_scene
+    return matcher_scene.proj_scene(seed, n, nq)
 
 
 @pytest.mark.parametrize("seed,n,nq", [(1, 1000, 600), (2, 2000, 2500), (3, 300, 50), (4, 4000, 4000)])
