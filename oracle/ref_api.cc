@@ -57,7 +57,8 @@ namespace {
 const size_t kArenaBytes = (size_t)4 << 30;    // address space only (MAP_NORESERVE); reset between calls
 char* g_arena = NULL;
 std::atomic<size_t> g_arena_off(0);
-std::atomic<int> g_alloc_mode(0);
+std::atomic<int> g_alloc_mode(0);     // what operator new does right now
+std::atomic<int> g_alloc_model(0);    // the model selected for extraction calls
 inline bool inArena(const void* p) { return g_arena && (const char*)p >= g_arena && (const char*)p < g_arena + kArenaBytes; }
 inline void* refAlloc(size_t n)
 {
@@ -88,8 +89,17 @@ extern "C" int ref_set_allocator(int mode)
     }
     if (g_arena_off.load() > ((size_t)1 << 30)) madvise(g_arena, kArenaBytes, MADV_DONTNEED);   // give the pages back
     g_arena_off.store(0);
-    g_alloc_mode.store(mode);
+    g_alloc_model.store(mode);
     return 0;
+}
+namespace {
+// The model is in force only inside the extraction entry points: there every small block is allocated and freed by code
+// instantiated in this library.  Elsewhere (vocabulary loading, matcher scenes) libstdc++.so itself frees blocks that
+// this library allocated (std::getline growing a string), so those calls always use the real heap.
+struct ExtractionScope {
+    ExtractionScope() { g_alloc_mode.store(g_alloc_model.load()); }
+    ~ExtractionScope() { g_alloc_mode.store(0); }
+};
 }
 
 extern "C" {
@@ -100,6 +110,7 @@ extern "C" {
 int ref_extract(int nfeatures, float scale, int nlevels, int ini_th, int min_th, const uint8_t* img, int w, int h, size_t stride,
                 orc_keypoint* kps, uint8_t* desc, int cap, uint8_t* pyr, uint8_t* pyr_bordered)
 {
+    ExtractionScope scope;
     ORBextractor ex(nfeatures, scale, nlevels, ini_th, min_th);
     cv::Mat image(h, w, CV_8UC1, (void*)img, stride);
     std::vector<cv::KeyPoint> keys;
@@ -140,6 +151,7 @@ void ref_extractor_tables(int nfeatures, float scale, int nlevels, int ini_th, i
 // equal-size nodes by the ADDRESS of their std::list node.
 int ref_distribute_octree(const orc_keypoint* in, int n, int minX, int maxX, int minY, int maxY, int N, int level, orc_keypoint* out, int cap)
 {
+    ExtractionScope scope;
     ORBextractor ex(1000, 1.2f, 8, 20, 7);
     std::vector<cv::KeyPoint> v((const cv::KeyPoint*)in, (const cv::KeyPoint*)in + n);
     std::vector<cv::KeyPoint> r = ex.DistributeOctTree(v, minX, maxX, minY, maxY, N, level);
@@ -153,6 +165,7 @@ int ref_distribute_octree(const orc_keypoint* in, int n, int minX, int maxX, int
 double ref_extract_throughput(int nfeatures, float scale, int nlevels, int ini_th, int min_th, const uint8_t* imgs, int nimg, int w, int h,
                               int frames, int threads, long long* total_keypoints)
 {
+    ExtractionScope scope;
     std::vector<std::thread> pool;
     std::vector<long long> cnt(threads, 0);
     const auto t0 = std::chrono::steady_clock::now();
@@ -181,6 +194,7 @@ int ref_stereo_frame(int nfeatures, float scale, int nlevels, int ini_th, int mi
                      orc_keypoint* keysL, uint8_t* descL, int* nL, orc_keypoint* keysR, uint8_t* descR, int* nR, int cap,
                      float* uRight, float* depth, orc_keypoint* keysUn)
 {
+    ExtractionScope scope;
     ORBextractor exL(nfeatures, scale, nlevels, ini_th, min_th), exR(nfeatures, scale, nlevels, ini_th, min_th);
     cv::Mat L(h, w, CV_8UC1, (void*)imL, (size_t)w), R(h, w, CV_8UC1, (void*)imR, (size_t)w);
     cv::Mat K = cv::Mat::eye(3, 3, CV_32F);

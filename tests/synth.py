@@ -177,3 +177,60 @@ def stereo_pair(seed, w, h, max_disp=40):
     noise = rng.integers(-2, 3, size=right.shape)
     right = np.clip(right.astype(np.int32) + noise, 0, 255).astype(np.uint8)
     return left, np.ascontiguousarray(right)
+
+
+def vocabulary_bfs(seed, k=10, L=6):
+    """A full k-ary DBoW2 tree of depth L in breadth-first node order (node i's children are k*i+1 .. k*i+k), built with
+    vectorised numpy so that the ORBvoc-sized k=10, L=6 tree (1 111 111 nodes, 10^6 words) takes a second.  Children are
+    perturbed copies of their parent (half the bits at level 1, one bit in eight below); leaf weights are multiples of
+    1/1024 (exact in float32, double and a 10-digit decimal text), 2 % of them 0 (stop words).  Same dict as vocabulary()."""
+    rng = np.random.default_rng(seed)
+    levels = [rng.integers(0, 256, (1, 32), dtype=np.uint8)]
+    for l in range(1, L + 1):
+        par = np.repeat(levels[-1], k, axis=0)
+        n = len(par)
+        flips = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+        if l > 1:
+            flips &= rng.integers(0, 256, (n, 32), dtype=np.uint8)
+            flips &= rng.integers(0, 256, (n, 32), dtype=np.uint8)
+        levels.append(par ^ flips)
+    levels[0] = np.zeros((1, 32), np.uint8)            # the root carries no descriptor
+    desc = np.concatenate(levels)
+    n = len(desc)
+    first_leaf = n - len(levels[-1])
+    idx = np.arange(n, dtype=np.int64)
+    parent = np.where(idx > 0, (idx - 1) // k, -1)
+    leaf = (idx >= first_leaf).astype(np.int64)
+    child_off = np.minimum(idx * k, n - 1)             # BFS: children of i start at k*i+1, i.e. position k*i in child[]
+    child_off = np.concatenate([child_off, [n - 1]]).astype(np.int32)
+    child = np.arange(1, n, dtype=np.int32)
+    word = np.where(leaf > 0, idx - first_leaf, 0).astype(np.int32)
+    wq = rng.integers(10, 3083, n)
+    wq[rng.random(n) < 0.02] = 0
+    weight = np.where(leaf > 0, wq / 1024.0, 0.0).astype(np.float32)
+    return dict(k=k, L=L, child_off=child_off, child=child, desc=desc, word_id=word, weight=weight, parent=parent, leaf=leaf,
+                weight_q=np.where(leaf > 0, wq, 0))
+
+
+def vocabulary_text_fixed(v):
+    """ORBvoc text format (TemplatedVocabulary.h:1385-1487) as bytes, written with fixed-width fields from numpy arrays
+    (the loader reads whitespace-separated numbers, so padding is free).  Needs v["weight_q"] (weights in 1/1024)."""
+    n = len(v["parent"]) - 1
+    par = v["parent"][1:].astype(np.int64)
+    W = 8 + 2 + 32 * 4 + 1 + 13 + 1
+    buf = np.full((n, W), ord(" "), np.uint8)
+    for j in range(8):
+        buf[:, 7 - j] = ord("0") + (par // 10 ** j) % 10
+    buf[:, 9] = ord("0") + v["leaf"][1:]
+    d = v["desc"][1:].astype(np.int64)
+    for j in range(3):
+        buf[:, 10 + 3 - j:10 + 128:4] = ord("0") + (d // 10 ** j) % 10
+    q = v["weight_q"][1:].astype(np.int64)             # q / 1024 = q * 9765625 / 10^10
+    ip, fr = q // 1024, (q % 1024) * 9765625
+    o = 10 + 128 + 1
+    buf[:, o] = ord("0") + ip
+    buf[:, o + 1] = ord(".")
+    for j in range(10):
+        buf[:, o + 11 - j] = ord("0") + (fr // 10 ** j) % 10
+    buf[:, W - 1] = ord("\n")
+    return f"{v['k']} {v['L']} 0 0\n".encode() + buf.tobytes()

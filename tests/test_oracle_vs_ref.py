@@ -146,3 +146,76 @@ def test_real_heap_tie_break_is_measured():
     assert abs(len(rk) - len(ok)) <= 24 and common >= 0.95 * len(ok), (len(ok), len(rk), common)
     both = {bytes(k): bytes(d) for k, d in zip(ok, od)}
     assert all(both[bytes(k)] == bytes(d) for k, d in zip(rk, rd) if bytes(k) in both)   # same keypoint -> same descriptor
+
+
+def _ref_vocab(tmp_path, v, text):
+    path = tmp_path / "voc.txt"
+    # no trailing newline: the reference's `while(!f.eof()) getline` loop (TemplatedVocabulary.h:1425) would otherwise parse
+    # one more, empty line with an uninitialised parent id (undefined behaviour; the product's loader skips empty lines)
+    path.write_bytes((text if isinstance(text, bytes) else text.encode()).rstrip(b"\n"))
+    h = R.lib().ref_vocab_load_text(str(path).encode())
+    assert h
+    os.unlink(path)
+    return h
+
+
+def _check_vocab(h, v, desc, levelsups):
+    """DBoW2's own loadFromTextFile + transform (TemplatedVocabulary.h:1385-1487, :1145-1306) against orc_bow_transform,
+    orc_feature_vector and orc_bow_vector on the flattened tree."""
+    L = R.lib()
+    vo = O.VocabArrays(v["k"], v["L"], v["child_off"], v["child"], v["desc"], v["word_id"], v["weight"])
+    info = [ctypes.c_int() for _ in range(6)]
+    L.ref_vocab_info(h, *[ctypes.byref(x) for x in info])
+    assert [x.value for x in info] == [v["k"], v["L"], int(v["leaf"].sum()), len(v["desc"]), 0, 0]
+    n = len(desc)
+    ww = np.zeros(int(v["leaf"].sum()), np.float64)
+    ww[v["word_id"][v["leaf"] > 0]] = v["weight"][v["leaf"] > 0].astype(np.float64)
+    for levelsup in levelsups:
+        word, wt, node = O.bow_transform(vo, desc, levelsup)
+        rw, rwt, rn = np.empty(n, np.int32), np.empty(n, np.float64), np.empty(n, np.int32)
+        L.ref_vocab_transform_each(h, desc.ctypes.data, n, levelsup, rw.ctypes.data, rwt.ctypes.data, rn.ctypes.data)
+        assert np.array_equal(word, rw) and np.array_equal(node, rn) and np.array_equal(wt.astype(np.float64), rwt)
+        nid, noff, feat = O.feature_vector(node, wt)
+        ids, vals = O.bow_vector(word, ww)
+        bi, bv = np.empty(n, np.int32), np.empty(n, np.float64)
+        fn, fo, ff = np.empty(n + 1, np.int32), np.empty(n + 2, np.int32), np.empty(n + 1, np.int32)
+        nn = ctypes.c_int()
+        nb = L.ref_vocab_transform(h, desc.ctypes.data, n, levelsup, bi.ctypes.data, bv.ctypes.data, fn.ctypes.data, fo.ctypes.data,
+                                   ff.ctypes.data, ctypes.byref(nn))
+        assert nb == len(ids) and np.array_equal(bi[:nb], ids) and np.array_equal(bv[:nb].view(np.uint64), vals.view(np.uint64))
+        assert nn.value == len(nid) and np.array_equal(fn[:nn.value], nid) and np.array_equal(fo[:nn.value + 1], noff)
+        assert np.array_equal(ff[:noff[-1]], feat)
+    # L1Scoring::score (ScoringObject.cpp:28-61) between two halves
+    w1, _, _ = O.bow_transform(vo, desc[:n // 2], 4); w2, _, _ = O.bow_transform(vo, desc[n // 2:], 4)
+    i1, v1 = O.bow_vector(w1, ww); i2, v2 = O.bow_vector(w2, ww)
+    s = L.ref_vocab_score(h, i1.ctypes.data, v1.ctypes.data, len(i1), i2.ctypes.data, v2.ctypes.data, len(i2))
+    assert np.float64(s).view(np.uint64) == np.float64(O.bow_score_l1(i1, v1, i2, v2)).view(np.uint64)
+
+
+def _voc_queries(v, seed, n):
+    """Descriptors near random leaves (so that descents are meaningful) plus pure noise."""
+    rng = np.random.default_rng(seed)
+    leaves = np.flatnonzero(v["leaf"] > 0)
+    near = synth.descriptors(seed, n * 3 // 4, 0.06, v["desc"][rng.choice(leaves, n * 3 // 4)])
+    return np.ascontiguousarray(np.concatenate([near, synth.descriptors(seed + 1, n - len(near))]))
+
+
+def test_vocabulary_small_equals_reference(tmp_path):
+    v = synth.vocabulary(0, 10, 3)                          # depth-first node order, arbitrary float weights, stop words
+    h = _ref_vocab(tmp_path, v, synth.vocabulary_text(v))
+    _check_vocab(h, v, _voc_queries(v, 5, 3000), (0, 1, 2, 3, 4))
+    R.lib().ref_vocab_free(h)
+    v = synth.vocabulary_bfs(3, 9, 4)                       # breadth-first order, fixed-width text
+    h = _ref_vocab(tmp_path, v, synth.vocabulary_text_fixed(v))
+    _check_vocab(h, v, _voc_queries(v, 6, 2000), (0, 2, 4, 5))
+    R.lib().ref_vocab_free(h)
+
+
+def test_vocabulary_orbvoc_size_equals_reference(tmp_path):
+    """configs[3]: k = 10, L = 6 (1 111 111 nodes, 10^6 words, a 170 MB text file) through DBoW2's own loader and descent:
+    10 k descriptors at levelsup 4 (BoW mode, <= 100 nodes) and 6 (one node: brute force)."""
+    v = synth.vocabulary_bfs(0, 10, 6)
+    R.set_allocator(0)
+    h = _ref_vocab(tmp_path, v, synth.vocabulary_text_fixed(v))
+    _check_vocab(h, v, _voc_queries(v, 7, 10000), (4, 6, 0))
+    R.lib().ref_vocab_free(h)
