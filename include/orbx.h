@@ -118,6 +118,23 @@ int orbx_hamming_best2(orbx_ctx* ctx, const uint8_t* q_desc, int nq, const uint8
                        const int32_t* q_seg, const int32_t* q_idx, const int32_t* t_seg, const int32_t* t_idx,
                        int nseg, const uint8_t* t_valid, int flags,
                        int32_t* best_idx, int32_t* best_dist, int32_t* second_dist);
+/* orbx_hamming_best2 for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.  Same
+ * arguments, same kernel, same results; it calls no cudaMalloc / cudaFree / allocating library routine on any path.
+ * Its scratch (the CSR arrays, and the staging of host buffers when the flags say host) lives in one file-scope device
+ * array of ORBX_HAMMING_STATIC_BYTES that every GPU loading the library holds until the process exits.
+ * Limits: nseg <= ORBX_HAMMING_STATIC_MAX_SEG and a scratch need <= ORBX_HAMMING_STATIC_BYTES (3 x 256-byte-rounded
+ * (nseg+1) x 4 B always; plus 32 B per descriptor, 4 B per index, 1 B per t_valid entry without ORBX_IN_DEVICE; plus 12 B
+ * per query row without ORBX_OUT_DEVICE -- e.g. 8192 x 8192 host descriptors fit, any size fits with device buffers).
+ * Beyond either limit it returns ORBX_E_CAPACITY and orbx_last_cuda_error() says which.  All calls on a GPU SHARE the
+ * array: calls that overlap on the GPU (two contexts, streams or threads) race; serialise them.  The call returns after
+ * its stream work has finished. */
+#define ORBX_HAMMING_STATIC_BYTES (1 << 20)
+#define ORBX_HAMMING_STATIC_MAX_SEG 1024
+int orbx_hamming_best2_static(orbx_ctx* ctx, const uint8_t* q_desc, int nq, const uint8_t* t_desc, int nt,
+                              const int32_t* q_seg, const int32_t* q_idx, const int32_t* t_seg, const int32_t* t_idx,
+                              int nseg, const uint8_t* t_valid, int flags,
+                              int32_t* best_idx, int32_t* best_dist, int32_t* second_dist);
 
 /* ---- DBoW2 vocabulary + transform (feeds SearchByBoW).  Replaces TemplatedVocabulary::transform,
  *      Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1145-1221,1255-1306 (FORB::distance, FORB.cpp:81-101). ----

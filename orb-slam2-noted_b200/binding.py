@@ -60,6 +60,7 @@ def lib():
     L.orbx_cvt_gray.argtypes = [vp, vp, ci, ci, sz, ci, ci, vp, sz]
     L.orbx_undistort_keypoints.argtypes = [vp, vp, ci, cf, cf, cf, cf, vp, ci, ci, vp]
     L.orbx_hamming_best2.argtypes = [vp, vp, ci, vp, ci, vp, vp, vp, vp, ci, vp, ci, vp, vp, vp]
+    L.orbx_hamming_best2_static.argtypes = L.orbx_hamming_best2.argtypes      # the no-allocation variant (include/orbx.h)
     L.orbx_test_sincosf.argtypes = [ctypes.c_uint32, ctypes.c_uint32, vp, vp]
     L.orbx_test_fast_atan2.argtypes = [vp, ci, vp]
     L.orbx_test_popc_peak.argtypes = [ci, ci, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]

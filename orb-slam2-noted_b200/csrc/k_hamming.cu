@@ -310,3 +310,113 @@ extern "C" int orbx_test_popc_peak(int device, int iters, double* popc_per_s, do
     if (ms_out) *ms_out = best;
     return ORBX_OK;
 }
+
+// ---- orbx_hamming_best2_static: the same kernel with NO allocation on any path ---------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  orbx_hamming_best2 keeps its CSR
+// arrays and host staging in the context's scratch buffer, which ensureScratch() grows with cudaFree + cudaMalloc; here
+// the scratch is a file-scope device array of ORBX_HAMMING_STATIC_BYTES that every GPU loading this library holds until
+// the process exits.
+//
+// gHamStaticScratch is, in HOST code, only a stand-in for the symbol: it is NOT a device address and must never be handed
+// to a kernel or a memcpy.  The device address is fetched per device with cudaGetSymbolAddress (staticScratch below).
+// All calls on a device share the array and it keeps the previous call's contents: every byte the kernel reads is
+// rewritten by this call's copies first (nothing has to start at zero), and two calls that overlap on the GPU -- two
+// contexts, two streams, two host threads -- race on it.  Serialise them.
+#include <mutex>
+namespace orbx {
+static __device__ __align__(256) unsigned char gHamStaticScratch[ORBX_HAMMING_STATIC_BYTES];
+
+constexpr int kStaticMaxDevices = 64;
+static unsigned char* gHamStaticPtr[kStaticMaxDevices] = {};   // device address of the array on each GPU (0 = not asked yet)
+static std::mutex gHamStaticMutex;
+
+// Set-up, once per device, with that device current (the caller has just done cudaSetDevice(c->device)).
+static int staticScratch(Ctx* c, unsigned char** out)
+{
+    if (c->device < 0 || c->device >= kStaticMaxDevices) return ORBX_E_INVALID;
+    std::lock_guard<std::mutex> lock(gHamStaticMutex);
+    if (!gHamStaticPtr[c->device]) {
+        unsigned char* p = nullptr;
+        ORBX_CUDA(c, cudaGetSymbolAddress((void**)&p, gHamStaticScratch));
+        if (!p) return ORBX_E_CUDA;
+        gHamStaticPtr[c->device] = p;
+    }
+    *out = gHamStaticPtr[c->device];
+    return ORBX_OK;
+}
+} // namespace orbx
+
+extern "C" int orbx_hamming_best2_static(orbx_ctx* h, const uint8_t* q_desc, int nq, const uint8_t* t_desc, int nt,
+                                         const int32_t* q_seg, const int32_t* q_idx, const int32_t* t_seg, const int32_t* t_idx,
+                                         int nseg, const uint8_t* t_valid, int flags,
+                                         int32_t* best_idx, int32_t* best_dist, int32_t* second_dist)
+{
+    if (!h || nq < 0 || nt < 0 || nseg < 1 || !q_seg || !t_seg || !best_idx || !best_dist || !second_dist) return ORBX_E_INVALID;
+    if ((nq > 0 && !q_desc) || (nt > 0 && !t_desc)) return ORBX_E_INVALID;
+    Ctx* c = &h->c;
+    if (nseg > ORBX_HAMMING_STATIC_MAX_SEG) {
+        c->lastCudaError = "orbx_hamming_best2_static: nseg exceeds ORBX_HAMMING_STATIC_MAX_SEG";
+        return ORBX_E_CAPACITY;
+    }
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    const int nrowQ = q_seg[nseg], nrowT = t_seg[nseg];
+    if (nrowQ == 0) return ORBX_OK;
+    int32_t prefix[ORBX_HAMMING_STATIC_MAX_SEG + 1];          // on the stack: no host allocation either
+    const int per = kHamThreads * kHamQPT;
+    prefix[0] = 0;
+    for (int s = 0; s < nseg; ++s) {
+        if (q_seg[s + 1] < q_seg[s] || t_seg[s + 1] < t_seg[s]) return ORBX_E_INVALID;
+        if (t_seg[s + 1] - t_seg[s] > (1 << kHamPosBits)) return ORBX_E_CAPACITY;
+        prefix[s + 1] = prefix[s] + (q_seg[s + 1] - q_seg[s] + per - 1) / per;
+    }
+    const int nblocks = prefix[nseg];
+    const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
+    // layout inside the static array: [prefix | qSeg | tSeg | (host inputs) | (host outputs)], as in orbx_hamming_best2
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t oPrefix = take(sizeof(int32_t) * (nseg + 1)), oQs = take(sizeof(int32_t) * (nseg + 1)), oTs = take(sizeof(int32_t) * (nseg + 1));
+    size_t oQ = 0, oT = 0, oQi = 0, oTi = 0, oTv = 0, oOut = 0;
+    if (!inDev) {
+        oQ = take((size_t)nq * 32); oT = take((size_t)nt * 32);
+        if (q_idx) oQi = take(sizeof(int32_t) * (size_t)nrowQ);
+        if (t_idx) oTi = take(sizeof(int32_t) * (size_t)nrowT);
+        if (t_valid) oTv = take((size_t)nt);
+    }
+    if (!outDev) oOut = take(sizeof(int32_t) * 3 * (size_t)nrowQ);
+    if (off > (size_t)ORBX_HAMMING_STATIC_BYTES) {
+        c->lastCudaError = "orbx_hamming_best2_static: this call needs more scratch than ORBX_HAMMING_STATIC_BYTES "
+                           "(pass device buffers, or use orbx_hamming_best2)";
+        return ORBX_E_CAPACITY;
+    }
+    unsigned char* S = nullptr;                               // the array's DEVICE address on this GPU
+    int rc = staticScratch(c, &S);
+    if (rc) return rc;
+    ORBX_CUDA(c, cudaMemcpyAsync(S + oPrefix, prefix, sizeof(int32_t) * (nseg + 1), cudaMemcpyHostToDevice, c->stream));
+    ORBX_CUDA(c, cudaMemcpyAsync(S + oQs, q_seg, sizeof(int32_t) * (nseg + 1), cudaMemcpyHostToDevice, c->stream));
+    ORBX_CUDA(c, cudaMemcpyAsync(S + oTs, t_seg, sizeof(int32_t) * (nseg + 1), cudaMemcpyHostToDevice, c->stream));
+    const uint4 *dq = (const uint4*)q_desc, *dt = (const uint4*)t_desc;
+    const int32_t *dqi = q_idx, *dti = t_idx; const uint8_t* dtv = t_valid;
+    if (!inDev) {
+        ORBX_CUDA(c, cudaMemcpyAsync(S + oQ, q_desc, (size_t)nq * 32, cudaMemcpyHostToDevice, c->stream)); dq = (const uint4*)(S + oQ);
+        ORBX_CUDA(c, cudaMemcpyAsync(S + oT, t_desc, (size_t)nt * 32, cudaMemcpyHostToDevice, c->stream)); dt = (const uint4*)(S + oT);
+        if (q_idx) { ORBX_CUDA(c, cudaMemcpyAsync(S + oQi, q_idx, sizeof(int32_t) * (size_t)nrowQ, cudaMemcpyHostToDevice, c->stream)); dqi = (const int32_t*)(S + oQi); }
+        if (t_idx) { ORBX_CUDA(c, cudaMemcpyAsync(S + oTi, t_idx, sizeof(int32_t) * (size_t)nrowT, cudaMemcpyHostToDevice, c->stream)); dti = (const int32_t*)(S + oTi); }
+        if (t_valid) { ORBX_CUDA(c, cudaMemcpyAsync(S + oTv, t_valid, (size_t)nt, cudaMemcpyHostToDevice, c->stream)); dtv = S + oTv; }
+    }
+    int32_t *dbi = best_idx, *dbd = best_dist, *dsd = second_dist;
+    if (!outDev) { dbi = (int32_t*)(S + oOut); dbd = dbi + nrowQ; dsd = dbd + nrowQ; }
+    // launch counters only: stageBegin() would take events from a pool that can grow while profiling is on
+    hammingBest2Kernel<<<nblocks, kHamThreads, 0, c->stream>>>(dq, dt, (const int32_t*)(S + oQs), dqi, (const int32_t*)(S + oTs), dti,
+                                                               (const int32_t*)(S + oPrefix), nseg, dtv, dbi, dbd, dsd);
+    c->kernelLaunches += 1; c->stageLaunches[ST_HAMMING] += 1;
+    ORBX_CUDA(c, cudaGetLastError());
+    if (!outDev) {
+        ORBX_CUDA(c, cudaMemcpyAsync(best_idx, dbi, sizeof(int32_t) * (size_t)nrowQ, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaMemcpyAsync(best_dist, dbd, sizeof(int32_t) * (size_t)nrowQ, cudaMemcpyDeviceToHost, c->stream));
+        ORBX_CUDA(c, cudaMemcpyAsync(second_dist, dsd, sizeof(int32_t) * (size_t)nrowQ, cudaMemcpyDeviceToHost, c->stream));
+    }
+    // the CSR arrays (and `prefix` on this stack frame) are read by the copies above: wait before returning
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return ORBX_OK;
+}
