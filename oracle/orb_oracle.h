@@ -5,14 +5,15 @@
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
  * legs may load this library.  The product (liborbx.so) never links or calls it.
  *
- * PARITY PINNING: the reference has no tests/golden vectors for this path and cannot be
- * compiled here (needs OpenCV C++ headers).  The third-party arithmetic it calls
- * (cv::resize, cv::GaussianBlur, cv::FAST, cv::fastAtan2, cv::copyMakeBorder, libm
- * cosf/sinf) is pinned against the executable copies in this image (cv2 4.13.0,
- * glibc 2.39) by tests/golden fixtures generated with tools/gen_golden.py; the glue
- * (cells, quadtree, ordering) is pinned against an independent Python restatement that
- * calls cv2 for every primitive.  The quadtree tie-break is canonicalised (see
- * orc_distribute_octree) because the reference's is heap-address dependent.
+ * PARITY PINNING: pinned.  (1) Control flow: tests/test_oracle_vs_ref.py compares this library byte for byte with the
+ * reference's own sources compiled unmodified (oracle/_ref/liborb_ref.so, recipe in oracle/Makefile, cv:: shim in
+ * oracle/cvshim/): whole frames, pyramids, the quadtree, stereo frames, all twelve ORBmatcher methods, DBoW2 transform.
+ * (2) The third-party arithmetic the reference calls (cv::resize, cv::GaussianBlur, cv::FAST, cv::fastAtan2,
+ * cv::copyMakeBorder, cv::undistortPoints, cv::cvtColor, libm cosf/sinf) against the executable copies in this image
+ * (cv2 4.13.0, glibc 2.39): tests/golden fixtures generated with tools/gen_golden.py.  The reference has no tests of its
+ * own for this path.  The quadtree tie-break is canonicalised (see orc_distribute_octree): the reference's depends on heap
+ * addresses; it equals this library when address order == creation order, and DESIGN.md section 2 holds the measured
+ * difference under glibc's real heap.
  */
 #ifndef ORB_ORACLE_H
 #define ORB_ORACLE_H
