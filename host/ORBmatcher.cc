@@ -155,6 +155,15 @@ int ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F
 }
 
 namespace {
+// -R^T t the way OpenCV evaluates `-Rcw.t() * tcw` (src/ORBmatcher.cc:446, :1335, :1760, :1932): a product with a transposed
+// operand leaves gemm's small-matrix float path and accumulates in DOUBLE, one rounding to float at the end (alpha = -1).
+// oracle/cvshim states the same rule; tests/test_shim_algebra.py pins it to cv2 4.13 (a float sum differs in 4 of 5 cases).
+void centreOf(const float R[9], const float t[3], float Ow[3])
+{
+    for (int r = 0; r < 3; ++r)
+        Ow[r] = (float)(-((double)R[r] * (double)t[0] + (double)R[3 + r] * (double)t[1] + (double)R[6 + r] * (double)t[2]));
+}
+
 int projectionSearch(orbx_ctx* ctx, Frame& F, const std::vector<orbx_proj_query>& q, const std::vector<MapPoint*>& src, int modeFlags,
                      int thDist, float nnratio, bool checkOri, bool anyPointOccupies = false)
 {
@@ -192,6 +201,7 @@ int ORBmatcher::SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMap
         e.u = pMP->mTrackProjX; e.v = pMP->mTrackProjY; e.ur = pMP->mTrackProjXR;
         e.radius = r * F.mvScaleFactors[nPredictedLevel];
         e.min_level = nPredictedLevel - 1; e.max_level = nPredictedLevel;
+        e.flags = pMP->Observations() > 0 ? 0 : ORBX_PROJ_QUERY_TRANSIENT;        // :136-138: only an observed holder hides a keypoint
         const cv::Mat d = pMP->GetDescriptor();
         memcpy(e.desc, d.ptr<uint8_t>(), 32);
         q.push_back(e); src.push_back(pMP);
@@ -208,7 +218,7 @@ int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, 
         for (int c = 0; c < 3; ++c) { Rcw[3 * r + c] = Tc.at<float>(r, c); Rlw[3 * r + c] = Tl.at<float>(r, c); }
         tcw[r] = Tc.at<float>(r, 3); tlw[r] = Tl.at<float>(r, 3);
     }
-    for (int r = 0; r < 3; ++r) twc[r] = -(Rcw[r] * tcw[0] + Rcw[3 + r] * tcw[1] + Rcw[6 + r] * tcw[2]);        // -Rcw^T tcw
+    centreOf(Rcw, tcw, twc);                                                                                     // -Rcw^T tcw, :1760
     for (int r = 0; r < 3; ++r) tlc[r] = Rlw[3 * r] * twc[0] + Rlw[3 * r + 1] * twc[1] + Rlw[3 * r + 2] * twc[2] + tlw[r];
     const bool bForward = tlc[2] > CurrentFrame.mb && !bMono;
     const bool bBackward = -tlc[2] > CurrentFrame.mb && !bMono;
@@ -236,6 +246,7 @@ int ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, 
         if (bForward) { e.min_level = nLastOctave; e.max_level = -1; }
         else if (bBackward) { e.min_level = 0; e.max_level = nLastOctave; }
         else { e.min_level = nLastOctave - 1; e.max_level = nLastOctave + 1; }
+        e.flags = pMP->Observations() > 0 ? 0 : ORBX_PROJ_QUERY_TRANSIENT;        // :1840-1842 (UpdateLastFrame's temporal points)
         const cv::Mat d = pMP->GetDescriptor();
         memcpy(e.desc, d.ptr<uint8_t>(), 32);
         q.push_back(e); src.push_back(pMP);
@@ -251,7 +262,15 @@ void poseOf(const cv::Mat& T, float R[9], float t[3], float Ow[3], float invScal
         for (int c = 0; c < 3; ++c) R[3 * r + c] = T.at<float>(r, c) * invScale;
         t[r] = T.at<float>(r, 3) * invScale;
     }
-    for (int r = 0; r < 3; ++r) Ow[r] = -(R[r] * t[0] + R[3 + r] * t[1] + R[6 + r] * t[2]);
+    centreOf(R, t, Ow);
+}
+// Sim3 pose Scw -> (Rcw, tcw, Ow) as src/ORBmatcher.cc:441-446 / :1330-1335 evaluate it: scw = sqrt(row0 . row0) with
+// cv::Mat::dot and sqrt in double, rounded to float; Mat / scw = Mat * (float)(1.0 / scw) element by element.
+void sim3PoseOf(const cv::Mat& Scw, float R[9], float t[3], float Ow[3])
+{
+    const double r00 = Scw.at<float>(0, 0), r01 = Scw.at<float>(0, 1), r02 = Scw.at<float>(0, 2);
+    const float scw = (float)std::sqrt(r00 * r00 + r01 * r01 + r02 * r02);
+    poseOf(Scw, R, t, Ow, (float)(1.0 / scw));
 }
 float norm3(float x, float y, float z) { return (float)std::sqrt((double)x * x + (double)y * y + (double)z * z); }   // cv::norm(NORM_L2)
 } // namespace
@@ -297,14 +316,8 @@ int ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std
 int ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, std::vector<MapPoint*>& vpMatched, int th)
 {
     const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy;
-    const float r00 = Scw.at<float>(0, 0), r01 = Scw.at<float>(0, 1), r02 = Scw.at<float>(0, 2);
-    const float scw = std::sqrt(r00 * r00 + r01 * r01 + r02 * r02);
     float Rcw[9], tcw[3], Ow[3];
-    for (int r = 0; r < 3; ++r) {
-        for (int c = 0; c < 3; ++c) Rcw[3 * r + c] = Scw.at<float>(r, c) / scw;
-        tcw[r] = Scw.at<float>(r, 3) / scw;
-    }
-    for (int r = 0; r < 3; ++r) Ow[r] = -(Rcw[r] * tcw[0] + Rcw[3 + r] * tcw[1] + Rcw[6 + r] * tcw[2]);
+    sim3PoseOf(Scw, Rcw, tcw, Ow);
     std::set<MapPoint*> spAlreadyFound(vpMatched.begin(), vpMatched.end());
     spAlreadyFound.erase(static_cast<MapPoint*>(NULL));
     std::vector<orbx_proj_query> q;
@@ -457,11 +470,8 @@ int ORBmatcher::Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, c
 // LoopClosing: fuse the loop's MapPoints into pKF with the corrected Sim3 pose (:1310-1458).
 int ORBmatcher::Fuse(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, float th, std::vector<MapPoint*>& vpReplacePoint)
 {
-    const float r00 = Scw.at<float>(0, 0), r01 = Scw.at<float>(0, 1), r02 = Scw.at<float>(0, 2);
-    const float scw = std::sqrt(r00 * r00 + r01 * r01 + r02 * r02);
     float Rcw[9], tcw[3], Ow[3];
-    for (int r = 0; r < 3; ++r) { for (int c = 0; c < 3; ++c) Rcw[3 * r + c] = Scw.at<float>(r, c) / scw; tcw[r] = Scw.at<float>(r, 3) / scw; }
-    for (int r = 0; r < 3; ++r) Ow[r] = -(Rcw[r] * tcw[0] + Rcw[3 + r] * tcw[1] + Rcw[6 + r] * tcw[2]);
+    sim3PoseOf(Scw, Rcw, tcw, Ow);
     const std::set<MapPoint*> spAlreadyFound = pKF->GetMapPoints();
     std::vector<orbx_proj_query> q;
     std::vector<int> src;

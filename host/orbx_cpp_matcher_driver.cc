@@ -22,6 +22,14 @@ static std::vector<std::vector<char> > readAll(const char* path)
 template <typename T> static const T* as(const std::vector<char>& b) { return reinterpret_cast<const T*>(b.data()); }
 static void put(FILE* f, const void* p, int nbytes) { fwrite(&nbytes, 4, 1, f); fwrite(p, 1, nbytes, f); }
 
+// optional 4x4 row-major pose at in[k]; absent or empty -> the given default
+static cv::Mat pose4(const std::vector<std::vector<char> >& in, size_t k, const cv::Mat& dflt)
+{
+    if (in.size() <= k || in[k].size() < 64) return dflt;
+    cv::Mat m(4, 4, CV_32F); memcpy(m.data, in[k].data(), 64); return m;
+}
+static cv::Mat eye4() { cv::Mat m = cv::Mat::zeros(4, 4, CV_32F); for (int i = 0; i < 4; ++i) m.at<float>(i, i) = 1.f; return m; }
+
 static void fillFeatVec(DBoW2::FeatureVector& fv, const int* node, int n)
 {
     for (int i = 0; i < n; ++i) if (node[i] >= 0) fv[(unsigned)node[i]].push_back((unsigned)i);
@@ -87,6 +95,7 @@ int main(int argc, char** argv)
         std::vector<MapPoint*> vp(np);
         for (int i = 0; i < np; ++i) {
             const float* q = as<float>(in[15]) + 5 * i;
+            pts[i].nObs = in.size() > 25 ? as<int>(in[25])[i] : 1;       // 0: a temporal point (Tracking::UpdateLastFrame)
             pts[i].mbTrackInView = true; pts[i].mTrackProjX = q[0]; pts[i].mTrackProjY = q[1]; pts[i].mTrackProjXR = q[2];
             pts[i].mTrackViewCos = q[3]; pts[i].mnTrackScaleLevel = (int)q[4];
             pts[i].mDescriptor = cv::Mat(1, 32, CV_8U); memcpy(pts[i].mDescriptor.data, in[16].data() + 32 * i, 32);
@@ -117,7 +126,7 @@ int main(int argc, char** argv)
                 mp.mDescriptor = cv::Mat(1, 32, CV_8U); memcpy(mp.mDescriptor.data, in[20].data() + 32 * i, 32);   // 20: MapPoint descriptors
             }
             // (e) SearchByProjection(Frame, KeyFrame, sAlreadyFound, th, ORBdist): relocalisation
-            F.mTcw = cv::Mat::zeros(4, 4, CV_32F); for (int i = 0; i < 4; ++i) F.mTcw.at<float>(i, i) = 1.f;
+            F.mTcw = pose4(in, 31, eye4());
             Frame::fx = P[3]; Frame::fy = P[4]; Frame::cx = P[5]; Frame::cy = P[6];
             F.mnScaleLevels = 8; F.mfLogScaleFactor = Q[4];
             F.mvpMapPoints.assign(F.N, (MapPoint*)NULL);
@@ -136,6 +145,7 @@ int main(int argc, char** argv)
             cv::Mat Scw = cv::Mat::zeros(4, 4, CV_32F);
             for (int i = 0; i < 3; ++i) Scw.at<float>(i, i) = Q[5];
             Scw.at<float>(3, 3) = 1.f;
+            Scw = pose4(in, 29, Scw);
             std::vector<MapPoint*> vpPoints, vpMatched(k2.N, (MapPoint*)NULL);
             for (int i = 0; i < k1.N; ++i) if (k1.mvpMapPoints[i]) vpPoints.push_back(k1.mvpMapPoints[i]);
             for (int i = 0; i < k2.N; ++i) if (in[17][i]) vpMatched[i] = &occupiedMP;
@@ -201,6 +211,7 @@ int main(int argc, char** argv)
             cv::Mat Scw = cv::Mat::zeros(4, 4, CV_32F);
             for (int i = 0; i < 3; ++i) Scw.at<float>(i, i) = 2.f;
             Scw.at<float>(3, 3) = 1.f;
+            Scw = pose4(in, 30, Scw);
             std::vector<MapPoint*> vpts;
             for (int i = 0; i < k1.N; ++i) if (k1.mvpMapPoints[i]) vpts.push_back(k1.mvpMapPoints[i]);
             for (size_t i = 0, nv = vpts.size(); i + 40 < nv; i += 40) vpts.push_back(vpts[i]);
@@ -223,6 +234,37 @@ int main(int argc, char** argv)
             res.assign(k1.N, -1);
             for (int i = 0; i < k1.N; ++i) res[i] = code(m12[i]);
             put(o, &n, 4); put(o, res.data(), 4 * k1.N);
+            if (in.size() > 28) {
+                // (k) SearchByProjection(CurrentFrame, LastFrame, th, bMono): see oracle/ref_api.cc for the scene
+                reset();
+                const int* lastObs = as<int>(in[26]);
+                const float thK = as<float>(in[28])[0];
+                MapPoint transientMP; transientMP.nObs = 0;
+                MapPoint occMP;
+                Frame Fl;
+                Fl.N = k1.N; Fl.mDescriptors = k1.mDescriptors; Fl.mvKeys = k1.mvKeysUn; Fl.mvKeysUn = k1.mvKeysUn;
+                Fl.mTcw = eye4();
+                Fl.mvpMapPoints.assign(Fl.N, (MapPoint*)NULL); Fl.mvbOutlier.assign(Fl.N, false);
+                for (int i = 0; i < Fl.N; ++i) {
+                    Fl.mvpMapPoints[i] = has1[i] ? &pool1[i] : (MapPoint*)NULL;
+                    Fl.mvbOutlier[i] = (i % 13) == 5;
+                    pool1[i].nObs = lastObs[i];
+                }
+                for (int mono = 0; mono < 2; ++mono) {
+                    Frame Fc;
+                    Fc.N = k2.N; Fc.mDescriptors = k2.mDescriptors; Fc.mvKeys = k2.mvKeysUn; Fc.mvKeysUn = k2.mvKeysUn;
+                    Fc.mvuRight = k2.mvuRight; Fc.mvScaleFactors = k2.mvScaleFactors;
+                    Fc.mbf = Q2[1]; Fc.mb = Q2[1] / P[3];
+                    Fc.mTcw = pose4(in, 27, eye4());
+                    Fc.mvpMapPoints.assign(Fc.N, (MapPoint*)NULL);
+                    for (int i = 0; i < Fc.N; ++i) Fc.mvpMapPoints[i] = in[17][i] ? &occMP : ((i % 7) == 3 ? &transientMP : (MapPoint*)NULL);
+                    n = ORBmatcher(P[0], true).SearchByProjection(Fc, Fl, thK, mono != 0);
+                    res.assign(Fc.N, -1);
+                    for (int i = 0; i < Fc.N; ++i)
+                        if (Fc.mvpMapPoints[i] && Fc.mvpMapPoints[i] != &occMP && Fc.mvpMapPoints[i] != &transientMP) res[i] = code(Fc.mvpMapPoints[i]);
+                    put(o, &n, 4); put(o, res.data(), 4 * Fc.N);
+                }
+            }
         }
     } catch (const std::exception& e) { fprintf(stderr, "error: %s\n", e.what()); return 1; }
     fclose(o);

@@ -211,16 +211,22 @@ typedef struct {
     float ur;              /* projected right coordinate (used when the frame has uright > 0) */
     float angle;           /* keypoint angle of the source observation (rotation histogram) */
     int32_t min_level, max_level; /* octave filter, max_level < 0 = unbounded (GetFeaturesInArea semantics) */
-    int32_t reserved;
+    int32_t flags;         /* ORBX_PROJ_QUERY_*; 0 = the match hides its keypoint from the following queries */
     uint8_t desc[32];
 } orbx_proj_query;
+/* The query's map point has Observations() == 0 (the temporal points Tracking::UpdateLastFrame creates for stereo / RGB-D):
+ * the reference skips a keypoint only while its CURRENT holder is observed (src/ORBmatcher.cc:136-138, :1840-1842), so the
+ * match is recorded but later queries may take the same keypoint again: assign[] then holds the last one, nmatches counts
+ * every accept, and with check_orientation every accept votes and un-counts itself when its bin is dropped (:1893-1903).
+ * Only the map-point and motion-model overloads use it; relocalisation / Sim3 skip any held keypoint (:2000, :531). */
+enum { ORBX_PROJ_QUERY_TRANSIENT = 1 };
 typedef struct { float min_x, min_y, inv_w, inv_h; int cols, rows; } orbx_grid; /* mnMinX.. FRAME_GRID_COLS/ROWS */
 enum { ORBX_PROJ_RATIO_SAME_LEVEL = 1,  /* keep best/second-best + the bestLevel==bestLevel2 ratio rule (:177-186) */
        ORBX_PROJ_CHECK_URIGHT = 2 };    /* |ur - uright[i]| > radius rejects (:141-151, :1846-1852) */
 int orbx_assign_grid(orbx_ctx* ctx, const orbx_keypoint* keys, int n, const orbx_grid* g, int flags,
                      int32_t* cell_off /* cols*rows+1 */, int32_t* cell_idx /* n */);
-/* Queries are processed in order; a keypoint taken by an earlier query (or with occupied[i] != 0 on entry) is
- * skipped by later ones, exactly like the reference's writes to mvpMapPoints / vpMatched.
+/* Queries are processed in order; a keypoint taken by an earlier query (unless that query is ORBX_PROJ_QUERY_TRANSIENT)
+ * or with occupied[i] != 0 on entry is skipped by later ones, exactly like the reference's writes to mvpMapPoints / vpMatched.
  * assign[i] = query index matched to keypoint i, or -1. */
 int orbx_search_by_projection(orbx_ctx* ctx, const orbx_proj_query* q, int nq, const orbx_keypoint* keys,
                               const uint8_t* desc, const float* uright, int n, const orbx_grid* g,

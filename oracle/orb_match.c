@@ -353,12 +353,15 @@ int orc_features_in_area(const orc_keypoint* keys, const orc_grid* g, const int3
 
 /* SearchByProjection(Frame&, vector<MapPoint*>&, th): src/ORBmatcher.cc:78-191 + RadiusByViewingCos :194-201.
  * pts: the visible, good map points in caller order (mbTrackInView && !isBad).  occupied[j] != 0: frame
- * keypoint j already holds a MapPoint with Observations() > 0 (:136-138); it is updated as matches are made
- * (the reference writes F.mvpMapPoints[bestIdx] = pMP and the candidate points are observed map points).
- * assign[j] = index of the point matched to keypoint j, or -1. */
+ * keypoint j already holds a MapPoint with Observations() > 0 (:136-138); it is updated as matches are made: the
+ * reference writes F.mvpMapPoints[bestIdx] = pMP, which hides keypoint bestIdx from the following points iff pMP is
+ * observed.  transient (optional): transient[i] != 0 = point i has Observations() == 0 (the temporal points of
+ * Tracking::UpdateLastFrame); its match is recorded and counted but a later point may take the keypoint again.
+ * assign[j] = index of the LAST point matched to keypoint j, or -1. */
 int orc_search_by_projection_points(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
                                     const float* uright, const float* scale, const orc_grid* g, const int32_t* cell_off,
-                                    const int32_t* cell_idx, const uint8_t* occupied_in, float th, float nnratio, int32_t* assign)
+                                    const int32_t* cell_idx, const uint8_t* occupied_in, float th, float nnratio, int32_t* assign,
+                                    const uint8_t* transient)
 {
     uint8_t* occ = (uint8_t*)malloc((size_t)(n > 0 ? n : 1));
     int32_t* cand = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n > 0 ? n : 1));
@@ -386,7 +389,8 @@ int orc_search_by_projection_points(const orc_projpoint* pts, int npts, const or
         }
         if (best <= TH_HIGH) {
             if (bestLevel == bestLevel2 && (float)best > nnratio * (float)best2) continue;
-            assign[bestIdx] = i; occ[bestIdx] = 1;
+            assign[bestIdx] = i;                                   /* F.mvpMapPoints[bestIdx] = pMP, :185 */
+            if (!transient || !transient[i]) occ[bestIdx] = 1;     /* hidden from later points only if pMP is observed, :136-138 */
             ++nmatches;
         }
     }
@@ -400,7 +404,7 @@ int orc_search_by_projection_points(const orc_projpoint* pts, int npts, const or
 int orc_search_by_projection_frame(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
                                    const float* uright, const float* scale, const orc_grid* g, const int32_t* cell_off,
                                    const int32_t* cell_idx, const uint8_t* occupied_in, float th, int motion, int check_ori,
-                                   int32_t* assign)
+                                   int32_t* assign, const uint8_t* transient)
 {
     ivec hist[HISTO_LENGTH]; memset(hist, 0, sizeof(hist));
     uint8_t* occ = (uint8_t*)malloc((size_t)(n > 0 ? n : 1));
@@ -428,9 +432,10 @@ int orc_search_by_projection_frame(const orc_projpoint* pts, int npts, const orc
             if (dist < best) { best = dist; bestIdx2 = i2; }
         }
         if (best <= TH_HIGH) {
-            assign[bestIdx2] = i; occ[bestIdx2] = 1;
+            assign[bestIdx2] = i;                                  /* CurrentFrame.mvpMapPoints[bestIdx2] = pMP, :1858 */
+            if (!transient || !transient[i]) occ[bestIdx2] = 1;    /* :1840-1842: skipped later only if pMP is observed */
             ++nmatches;
-            if (check_ori) ipush(&hist[rot_bin(p->angle, keys[bestIdx2].angle)], bestIdx2);
+            if (check_ori) ipush(&hist[rot_bin(p->angle, keys[bestIdx2].angle)], bestIdx2);   /* one entry per accept */
         }
     }
     if (check_ori) {
@@ -439,6 +444,7 @@ int orc_search_by_projection_frame(const orc_projpoint* pts, int npts, const orc
         orc_three_maxima(cnt, HISTO_LENGTH, &i1, &i2, &i3);
         for (int i = 0; i < HISTO_LENGTH; ++i) {
             if (i == i1 || i == i2 || i == i3) continue;
+            /* :1893-1903: every entry clears its keypoint (whoever holds it by now) and un-counts itself */
             for (int j = 0; j < hist[i].n; ++j) { assign[hist[i].v[j]] = -1; --nmatches; }
         }
     }

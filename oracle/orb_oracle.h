@@ -116,11 +116,12 @@ int orc_features_in_area(const orc_keypoint* keys, const orc_grid* g, const int3
 typedef struct { float u, v, ur, view_cos, angle; int32_t level; uint8_t desc[32]; } orc_projpoint;
 int orc_search_by_projection_points(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
                                     const float* uright, const float* scale, const orc_grid* g, const int32_t* cell_off,
-                                    const int32_t* cell_idx, const uint8_t* occupied_in, float th, float nnratio, int32_t* assign);
+                                    const int32_t* cell_idx, const uint8_t* occupied_in, float th, float nnratio, int32_t* assign,
+                                    const uint8_t* transient /* optional: point i has Observations() == 0 */);
 int orc_search_by_projection_frame(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
                                    const float* uright, const float* scale, const orc_grid* g, const int32_t* cell_off,
                                    const int32_t* cell_idx, const uint8_t* occupied_in, float th, int motion, int check_ori,
-                                   int32_t* assign);
+                                   int32_t* assign, const uint8_t* transient);
 int orc_search_by_projection_reloc(const orc_projpoint* pts, int npts, const orc_keypoint* keys, const uint8_t* desc, int n,
                                    const float* scale, const orc_grid* g, const int32_t* cell_off, const int32_t* cell_idx,
                                    const uint8_t* occupied_in, float th, int orb_dist, int check_ori, int32_t* assign); /* :1922-2065 */

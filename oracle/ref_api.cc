@@ -271,6 +271,28 @@ double ref_vocab_score(void* vv, const int32_t* ids1, const double* v1, int n1, 
     return v->score(a, b);
 }
 
+// The shim's float matrix algebra, exposed so that tests/test_shim_algebra.py can pin it to the executable OpenCV of this
+// image (cv2.gemm / cv2.norm, 4.13).  op: 0 = A*B, 1 = A*B + C, 2 = A.t()*B, 3 = -A.t()*B, 4 = A / s (s = C[0]),
+// 5 = -A*B (unary minus on a materialised Mat, KeyFrame::SetPose's Ow).  Returns the element count written to out.
+int ref_shim_algebra(int op, const float* A, int ar, int ac, const float* B, int br, int bc, const float* C, float* out)
+{
+    cv::Mat a(ar, ac, CV_32F, (void*)A), b, c, r;
+    if (B) b = cv::Mat(br, bc, CV_32F, (void*)B);
+    switch (op) {
+    case 0: r = a * b; break;
+    case 1: c = cv::Mat(ar, bc, CV_32F, (void*)C); r = a * b + c; break;
+    case 2: r = a.t() * b; break;
+    case 3: r = -a.t() * b; break;
+    case 4: r = a / C[0]; break;
+    case 5: r = -a * b; break;
+    default: return -1;
+    }
+    for (int y = 0; y < r.rows; ++y) for (int x = 0; x < r.cols; ++x) out[y * r.cols + x] = r.at<float>(y, x);
+    return r.rows * r.cols;
+}
+double ref_shim_norm(const float* a, int n) { return cv::norm(cv::Mat(n, 1, CV_32F, (void*)a)); }
+double ref_shim_dot(const float* a, const float* b, int n) { return cv::Mat(n, 1, CV_32F, (void*)a).dot(cv::Mat(n, 1, CV_32F, (void*)b)); }
+
 int ref_descriptor_distance(const uint8_t* a, const uint8_t* b)
 {
     cv::Mat A(1, 32, CV_8U, (void*)a), B(1, 32, CV_8U, (void*)b);
@@ -298,6 +320,12 @@ Arrays readAll(const char* path)
 template <typename T> const T* as(const std::vector<char>& b) { return reinterpret_cast<const T*>(b.data()); }
 void put(FILE* f, const void* p, int nbytes) { fwrite(&nbytes, 4, 1, f); fwrite(p, 1, nbytes, f); }
 cv::Mat vec3(const float* p) { cv::Mat m(3, 1, CV_32F); std::memcpy(m.data, p, 12); return m; }
+// optional 4x4 row-major pose at in[k]; absent or empty -> the given default
+cv::Mat pose4(const Arrays& in, size_t k, const cv::Mat& dflt)
+{
+    if (in.size() <= k || in[k].size() < 64) return dflt;
+    cv::Mat m(4, 4, CV_32F); std::memcpy(m.data, in[k].data(), 64); return m;
+}
 cv::Mat rowDesc(const char* p) { cv::Mat m(1, 32, CV_8U); std::memcpy(m.data, p, 32); return m; }
 
 struct Scene {
@@ -435,7 +463,7 @@ extern "C" int ref_run_matcher_scene(const char* in_path, const char* out_path)
         const float* q = as<float>(in[15]) + 5 * i;
         static const float w0[3] = {0, 0, 1};
         MapPoint* mp = new MapPoint(vec3(w0), &k1, &map);
-        mp->nObs = 1;
+        mp->nObs = in.size() > 25 ? as<int>(in[25])[i] : 1;      // 0: a temporal point (Tracking::UpdateLastFrame)
         mp->mbTrackInView = true; mp->mTrackProjX = q[0]; mp->mTrackProjY = q[1]; mp->mTrackProjXR = q[2];
         mp->mTrackViewCos = q[3]; mp->mnTrackScaleLevel = (int)q[4];
         mp->mDescriptor = rowDesc(in[16].data() + 32 * i);
@@ -456,7 +484,7 @@ extern "C" int ref_run_matcher_scene(const char* in_path, const char* out_path)
     if (full) {
         const float* Q = as<float>(in[19]);
         // (e) SearchByProjection(Frame, KeyFrame, sAlreadyFound, th, ORBdist): relocalisation
-        F.SetPose(cv::Mat::eye(4, 4, CV_32F));
+        F.SetPose(pose4(in, 31, cv::Mat::eye(4, 4, CV_32F)));
         F.mvpMapPoints.assign(F.N, (MapPoint*)NULL);
         for (int i = 0; i < F.N; ++i) if (in[17][i]) F.mvpMapPoints[i] = occupiedMP;
         std::set<MapPoint*> found;
@@ -469,6 +497,7 @@ extern "C" int ref_run_matcher_scene(const char* in_path, const char* out_path)
         cv::Mat Scw = cv::Mat::zeros(4, 4, CV_32F);
         for (int i = 0; i < 3; ++i) Scw.at<float>(i, i) = Q[5];
         Scw.at<float>(3, 3) = 1.f;
+        Scw = pose4(in, 29, Scw);
         std::vector<MapPoint*> vpPoints, vpMatched(k2.N, (MapPoint*)NULL);
         for (int i = 0; i < k1.N; ++i) if (k1.mvpMapPoints[i]) vpPoints.push_back(k1.mvpMapPoints[i]);
         for (int i = 0; i < k2.N; ++i) if (in[17][i]) vpMatched[i] = occupiedMP;
@@ -503,6 +532,7 @@ extern "C" int ref_run_matcher_scene(const char* in_path, const char* out_path)
         cv::Mat Scw = cv::Mat::zeros(4, 4, CV_32F);
         for (int i = 0; i < 3; ++i) Scw.at<float>(i, i) = 2.f;
         Scw.at<float>(3, 3) = 1.f;
+        Scw = pose4(in, 30, Scw);
         std::vector<MapPoint*> vpts;
         { std::vector<MapPoint*> cur = k1.GetMapPointMatches(); for (int i = 0; i < k1.N; ++i) if (cur[i]) vpts.push_back(cur[i]); }
         for (size_t i = 0, nv = vpts.size(); i + 40 < nv; i += 40) vpts.push_back(vpts[i]);
@@ -524,6 +554,33 @@ extern "C" int ref_run_matcher_scene(const char* in_path, const char* out_path)
         res.assign(k1.N, -1);
         for (int i = 0; i < k1.N; ++i) res[i] = code(m12[i]);
         put(o, &n, 4); put(o, res.data(), 4 * k1.N);
+    }
+    if (in.size() > 28) {
+        // (k) SearchByProjection(CurrentFrame, LastFrame, th, bMono) (:1741-1910): the last frame is side 1 with its map points
+        //     (observation counts in[26]: 0 = temporal point; every 13th keypoint an outlier), the current frame is side 2
+        //     at pose in[27], holding the occupied pattern plus temporal points (nObs 0) that must not hide their keypoint
+        reset(); rebuildCodes();
+        const int* lastObs = as<int>(in[26]);
+        const float thK = as<float>(in[28])[0];
+        MapPoint* transientMP = new MapPoint(vec3(w0), &k1, &map);
+        transientMP->nObs = 0;
+        Frame Fl(base[0]);
+        Fl.SetPose(cv::Mat::eye(4, 4, CV_32F));
+        for (int i = 0; i < Fl.N; ++i) {
+            Fl.mvpMapPoints[i] = in[3][i] ? pool[0][i] : (MapPoint*)NULL;
+            Fl.mvbOutlier[i] = (i % 13) == 5;
+            pool[0][i]->nObs = lastObs[i];
+        }
+        for (int mono = 0; mono < 2; ++mono) {
+            Frame Fc(base[1]);
+            Fc.SetPose(pose4(in, 27, cv::Mat::eye(4, 4, CV_32F)));
+            for (int i = 0; i < Fc.N; ++i) Fc.mvpMapPoints[i] = in[17][i] ? occupiedMP : ((i % 7) == 3 ? transientMP : (MapPoint*)NULL);
+            n = ORBmatcher(P[0], true).SearchByProjection(Fc, Fl, thK, mono != 0);
+            res.assign(Fc.N, -1);
+            for (int i = 0; i < Fc.N; ++i)
+                if (Fc.mvpMapPoints[i] && Fc.mvpMapPoints[i] != occupiedMP && Fc.mvpMapPoints[i] != transientMP) res[i] = code(Fc.mvpMapPoints[i]);
+            put(o, &n, 4); put(o, res.data(), 4 * Fc.N);
+        }
     }
     fclose(o);
     return 0;   // the scene's objects are left to the process (the Map owns raw pointers exactly as in the reference)

@@ -305,6 +305,10 @@ projResolveKernel(const orbx_proj_query* __restrict__ q, int nq, GridDev g, cons
             if (i + 32 < nq) { eN = topKey[i + 32]; mN = meta[i + 32]; } else eN = none;
             const uint32_t j0 = e.x & kJMask, j1 = e.y & kJMask, j2 = e.z & kJMask, j3 = e.w & kJMask;
             const bool complete = m.x <= 4;
+            // A transient query (ORBX_PROJ_QUERY_TRANSIENT: its map point has Observations() == 0) takes a keypoint without
+            // hiding it: the reference skips a keypoint only if its CURRENT holder is observed (src/ORBmatcher.cc:136-138,
+            // :1840-1842), so a later query may take the same keypoint again (assign[] keeps the last one, every accept counts).
+            const bool occupies = !(i < nq && (q[i].flags & ORBX_PROJ_QUERY_TRANSIENT));
             // a query whose overall best is beyond the threshold can never be accepted
             uint32_t pending = __ballot_sync(0xffffffffu, i < nq && e.x != kNoKeyP && (int)(e.x >> kJBits) <= thDist);
             int myJ = -1;
@@ -355,7 +359,7 @@ projResolveKernel(const orbx_proj_query* __restrict__ q, int nq, GridDev g, cons
                             const int lv1 = __float_as_int(cinfo[k1 & kJMask].w) & 0xff, lv2 = __float_as_int(cinfo[k2 & kJMask].w) & 0xff;
                             if (lv1 == lv2 && (float)(int)(k1 >> kJBits) > __fmul_rn(nnratio, (float)(int)(k2 >> kJBits))) ok = false;
                         }
-                        if (ok) { myJ = (int)(k1 & kJMask); occ[myJ >> 5] |= 1u << (myJ & 31); }
+                        if (ok) { myJ = (int)(k1 & kJMask); if (occupies) occ[myJ >> 5] |= 1u << (myJ & 31); }
                     }
                     pending &= ~(1u << t0);
                     __syncwarp();
@@ -366,25 +370,29 @@ projResolveKernel(const orbx_proj_query* __restrict__ q, int nq, GridDev g, cons
                 // is: conservative) waits for the next round, as does everything behind it.  The lowest pending lane
                 // has nobody before it and always commits.
                 // (match.any costs a pass per distinct value, so it only runs when an atomicOr has seen a duplicate)
-                bool leader = claim >= 0;
+                // A transient lane marks nothing and contends with nobody; its own claim is one more entry its decision
+                // rests on (an earlier occupying lane of this round may take it first).
+                const bool marks = claim >= 0 && occupies;
+                bool leader = marks;
                 uint32_t seen = 0;
                 if (leader) seen = atomicOr(&occ[claim >> 5], 1u << (claim & 31)) & (1u << (claim & 31));
                 if (__ballot_sync(0xffffffffu, seen != 0)) {
-                    const uint32_t peers = __match_any_sync(0xffffffffu, claim >= 0 ? (uint32_t)claim : (0x80000000u | (uint32_t)lane));
-                    leader = claim >= 0 && (peers & ((1u << lane) - 1u)) == 0;
+                    const uint32_t peers = __match_any_sync(0xffffffffu, marks ? (uint32_t)claim : (0x80000000u | (uint32_t)lane));
+                    leader = marks && (peers & ((1u << lane) - 1u)) == 0;
                 }
-                bool unsafe = need || (claim >= 0 && !leader);
+                bool unsafe = need || (marks && !leader);
                 __syncwarp();
                 if (lane != t0) {
                     if (dep0 != kJMask && ((occ[dep0 >> 5] >> (dep0 & 31)) & 1u)) unsafe = true;
                     if (dep1 != kJMask && ((occ[dep1 >> 5] >> (dep1 & 31)) & 1u)) unsafe = true;
+                    if (claim >= 0 && !occupies && ((occ[claim >> 5] >> (claim & 31)) & 1u)) unsafe = true;
                 }
                 const uint32_t unsafeMask = __ballot_sync(0xffffffffu, unsafe) & pending;
                 const uint32_t commit = unsafeMask ? (pending & ((1u << (__ffs(unsafeMask) - 1)) - 1u)) : pending;
                 if (leader) {
                     if ((commit >> lane) & 1u) myJ = claim;
                     else atomicAnd(&occ[claim >> 5], ~(1u << (claim & 31)));
-                }
+                } else if (claim >= 0 && !occupies && ((commit >> lane) & 1u)) myJ = claim;
                 pending &= ~commit;
                 __syncwarp();
             }
@@ -397,7 +405,7 @@ projResolveKernel(const orbx_proj_query* __restrict__ q, int nq, GridDev g, cons
         const int j = matchJ[i];
         if (j < 0) continue;
         const int f = idx[j];
-        assign[f] = i; ++cnt;
+        atomicMax(&assign[f], i); ++cnt;        // assign[] starts at -1; with transient queries the last accept stays (:185, :1858)
         if (checkOri) atomicAdd(&sHist[rotBinP(q[i].angle, keys[f].angle)], 1);
     }
     if (checkOri) {     // ComputeThreeMaxima + removal, src/ORBmatcher.cc:1884-1903, :2076-2120
@@ -421,6 +429,7 @@ projResolveKernel(const orbx_proj_query* __restrict__ q, int nq, GridDev g, cons
             if (j < 0) continue;
             const int f = idx[j];
             const int bin = rotBinP(q[i].angle, keys[f].angle);
+            // every accept of a dropped bin clears its keypoint, whoever holds it by now, and un-counts itself (:1893-1903)
             if (bin != keep[0] && bin != keep[1] && bin != keep[2]) assign[f] = -1; else ++cnt;
         }
     }

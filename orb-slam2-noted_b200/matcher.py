@@ -16,7 +16,7 @@ PROJ_RATIO_SAME_LEVEL, PROJ_CHECK_URIGHT = 1, 2
 FRAME_GRID_COLS, FRAME_GRID_ROWS = 64, 48  # include/Frame.h:55,60
 
 PROJ_QUERY_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("radius", "<f4"), ("ur", "<f4"), ("angle", "<f4"),
-                             ("min_level", "<i4"), ("max_level", "<i4"), ("reserved", "<i4"), ("desc", "u1", (32,))])
+                             ("min_level", "<i4"), ("max_level", "<i4"), ("flags", "<i4"), ("desc", "u1", (32,))])
 assert PROJ_QUERY_DTYPE.itemsize == 64
 
 

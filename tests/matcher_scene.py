@@ -59,9 +59,22 @@ def proj_scene(seed, n, nq):
     return keys, desc, uright, occupied, pts
 
 
-def check_scene(run_driver, tmp_path, seed=11, n1=1500, n2=1300):
+def _similarity(rng, scale, angle_deg, t):
+    """4x4 float32 [s R | t; 0 0 0 1] with a rotation of angle_deg about a random axis."""
+    ax = rng.normal(size=3); ax /= np.linalg.norm(ax)
+    a = np.deg2rad(angle_deg)
+    K = np.array([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]])
+    Rm = np.eye(3) + np.sin(a) * K + (1 - np.cos(a)) * (K @ K)
+    T = np.eye(4)
+    T[:3, :3] = scale * Rm; T[:3, 3] = t
+    return T.astype(np.float32)
+
+
+def check_scene(run_driver, tmp_path, seed=11, n1=1500, n2=1300, general_poses=False):
     """Builds one two-keyframe scene file, runs it through run_driver(in_path, out_path) and checks every output record
-    against the oracle (candidate loops) plus a Python replay of the map updates.  Returns the raw output bytes."""
+    against the oracle (candidate loops) plus a Python replay of the map updates.  Returns the raw output bytes.
+    general_poses=True: the projection sections get poses with real rotations, scales and translations; the expectations
+    below assume axis-aligned poses, so that scene is only run and returned (the caller compares two drivers' bytes)."""
     d1, k1, d2, k2 = make_pair(seed, n1, n2, 0.08, 0.2, KP=O.KP_DTYPE)
     v = synth.vocabulary(0, 10, 3)
     vo = O.VocabArrays(v["k"], v["L"], v["child_off"], v["child"], v["desc"], v["word_id"], v["weight"])
@@ -131,6 +144,19 @@ def check_scene(run_driver, tmp_path, seed=11, n1=1500, n2=1300):
     mpdesc2 = synth.descriptors(seed + 22, n2, 0.1, d1[tgt2])
     obs_n = rng.integers(1, 6, n1 + n2).astype(np.int32)
     th_fuse, bf_fuse, th_fuse_s, th_s3 = 3.0, 40.0, 4.0, 7.5
+    # (d) a third of the projected points and (k) a third of the last frame's points are temporal ones (Observations() == 0,
+    # Tracking::UpdateLastFrame): their matches do not hide the keypoint from the following points (:136-138, :1840-1842)
+    proj_obs = np.where(rng.random(len(pts)) < 0.35, 0, rng.integers(1, 5, len(pts))).astype(np.int32)
+    last_obs = np.where(rng.random(n1) < 0.35, 0, rng.integers(1, 5, n1)).astype(np.int32)
+    th_motion = 15.0
+    if general_poses:
+        Tck = _similarity(rng, 1.0, 2.0, [0.03, -0.02, -0.12])               # (k) current frame: small rotation, forward motion
+        Scw_f = _similarity(rng, 1.7, 1.5, [0.05, 0.02, 0.04])               # (f) Sim3 projection
+        Scw_i = _similarity(rng, 0.6, 1.0, [-0.03, 0.02, 0.05])              # (i) Sim3 fuse
+        Tcr = _similarity(rng, 1.0, 1.5, [0.04, 0.01, -0.03])                # (e) relocalisation frame
+    else:
+        Tck = np.eye(4, dtype=np.float32); Tck[:3, 3] = [0.01, -0.005, -0.1]
+        Scw_f = Scw_i = Tcr = np.zeros(0, np.float32)                        # empty = the drivers' axis-aligned defaults
     inp, outp = tmp_path / "m_in.bin", tmp_path / "m_out.bin"
     with open(inp, "wb") as f:
         _arr(f, np.array([nnratio, 1, 0, fx, fy, cx, cy, th, grid[2], grid[3], 0, 0, 640, 480, 0, 0], np.float32))
@@ -141,7 +167,11 @@ def check_scene(run_driver, tmp_path, seed=11, n1=1500, n2=1300):
         _arr(f, pts["desc"]); _arr(f, occupied)
         _arr(f, world); _arr(f, np.array([th_reloc, orb_dist, th_sim3, window, logsf, 2.0, 0, 0], np.float32)); _arr(f, mpdesc)
         _arr(f, world2); _arr(f, mpdesc2); _arr(f, obs_n); _arr(f, np.array([th_fuse, bf_fuse, th_fuse_s, th_s3, 0, 0, 0, 0], np.float32))
+        _arr(f, proj_obs); _arr(f, last_obs); _arr(f, Tck); _arr(f, np.array([th_motion, 0, 0, 0], np.float32))      # 25..28
+        _arr(f, Scw_f); _arr(f, Scw_i); _arr(f, Tcr)                                                                 # 29..31
     run_driver(str(inp), str(outp))
+    if general_poses:
+        return open(outp, "rb").read()
     out = _read_all(outp)
     so = [O.Side(*s) for s in sides]
     want, nw = O.search_by_bow(so[0], so[1], float(nnratio), True, False)
@@ -153,9 +183,13 @@ def check_scene(run_driver, tmp_path, seed=11, n1=1500, n2=1300):
     want, nw = O.search_for_triangulation(so[0], so[1], F12, float(ex), float(ey), sc16, sg16, False, True)
     assert int(np.frombuffer(out[4], np.int32)[0]) == nw and np.array_equal(np.frombuffer(out[5], np.int32), want)
     assert nw > 0
-    want, nw = O.search_by_projection(pts, keys, desc, uright, scale, grid, occupied, float(th), nnratio=float(nnratio))
+    want, nw = O.search_by_projection(pts, keys, desc, uright, scale, grid, occupied, float(th), nnratio=float(nnratio),
+                                      transient=(proj_obs == 0))
     assert int(np.frombuffer(out[6], np.int32)[0]) == nw and np.array_equal(np.frombuffer(out[7], np.int32), want)
     assert nw > 0
+    blocking, _ = O.search_by_projection(pts, keys, desc, uright, scale, grid, occupied, float(th), nnratio=float(nnratio))
+    if n1 >= 1500:
+        assert not np.array_equal(blocking, want) and nw > int((want >= 0).sum())   # the rule matters here: keypoints were re-taken
     assert int(np.frombuffer(out[8], np.int32)[0]) == int(np.unpackbits(d1[0] ^ d2[0]).sum())
 
     # the host-side projection of both overloads, restated step by step in float32
@@ -307,4 +341,26 @@ def check_scene(run_driver, tmp_path, seed=11, n1=1500, n2=1300):
             m12[i1] = 100000 + int(vn1[i1]); nfound += 1
     assert int(np.frombuffer(out[22], np.int32)[0]) == nfound and nfound > min(20, n1 // 75)
     assert list(np.frombuffer(out[23], np.int32)) == [-1 if m is None else m for m in m12]
+    # (k) SearchByProjection(CurrentFrame, LastFrame, th, bMono): the projection of src/ORBmatcher.cc:1762-1808 restated in
+    #     float32 for the axis-aligned pose of this scene (Rcw = I: x3Dc = x3Dw + tcw), then the oracle's loop
+    tck = Tck[:3, 3]
+    outl = (np.arange(n1) % 13) == 5
+    xc = (xw + tck[0]).astype(f32); yc = (yw + tck[1]).astype(f32); zc = (zw + tck[2]).astype(f32)
+    invzc = (1.0 / zc.astype(np.float64)).astype(f32)
+    u_k = ((fx * xc) * invzc + cx).astype(f32); v_k = ((fy * yc) * invzc + cy).astype(f32)
+    sel = (has1 != 0) & ~outl & ~(invzc < 0) & ~((u_k < 0) | (u_k > 640)) & ~((v_k < 0) | (v_k > 480))
+    idx_k = np.flatnonzero(sel)
+    pk = np.zeros(len(idx_k), O.PROJ_DTYPE)
+    pk["u"], pk["v"], pk["level"], pk["angle"], pk["desc"] = u_k[idx_k], v_k[idx_k], k1["octave"][idx_k], k1["angle"][idx_k], mpdesc[idx_k]
+    pk["ur"] = (u_k[idx_k] - (f32(bf_fuse) * invzc[idx_k]).astype(f32)).astype(f32)
+    assert -tck[2] > f32(bf_fuse) / fx                                 # tlc.z > mb: "forward" when not monocular (:1768)
+    for r, (mono, motion) in enumerate(((False, 1), (True, 0))):
+        want, nw = O.search_by_projection(pk, keys, desc, uright, scale, grid, occupied, th_motion, motion=motion, check_ori=True,
+                                          transient=(last_obs[idx_k] == 0))
+        want = np.where(want >= 0, idx_k[np.maximum(want, 0)], -1)
+        assert int(np.frombuffer(out[24 + 2 * r], np.int32)[0]) == nw and np.array_equal(np.frombuffer(out[25 + 2 * r], np.int32), want), (mono, nw)
+        assert nw > min(15, n1 // 60)
+        blocking, nb = O.search_by_projection(pk, keys, desc, uright, scale, grid, occupied, th_motion, motion=motion, check_ori=True)
+        if n1 >= 1500:                                                  # in the large scene keypoints do get re-taken
+            assert nb != nw or not np.array_equal(np.where(blocking >= 0, idx_k[np.maximum(blocking, 0)], -1), want)
     return open(outp, "rb").read()

@@ -207,8 +207,8 @@ def _mlib():
     L.orc_search_for_triangulation.argtypes = [ctypes.POINTER(BowFrame), ctypes.POINTER(BowFrame), vp, cf, cf, vp, vp, ci, ci, vp]
     L.orc_assign_grid.argtypes = [vp, ci, ctypes.POINTER(Grid), vp, vp]
     L.orc_features_in_area.argtypes = [vp, ctypes.POINTER(Grid), vp, vp, cf, cf, cf, ci, ci, vp]
-    L.orc_search_by_projection_points.argtypes = [vp, ci, vp, vp, ci, vp, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, cf, vp]
-    L.orc_search_by_projection_frame.argtypes = [vp, ci, vp, vp, ci, vp, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, ci, ci, vp]
+    L.orc_search_by_projection_points.argtypes = [vp, ci, vp, vp, ci, vp, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, cf, vp, vp]
+    L.orc_search_by_projection_frame.argtypes = [vp, ci, vp, vp, ci, vp, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, ci, ci, vp, vp]
     L.orc_search_by_projection_reloc.argtypes = [vp, ci, vp, vp, ci, vp, ctypes.POINTER(Grid), vp, vp, vp, cf, ci, ci, vp]
     L.orc_search_by_projection_sim3.argtypes = [vp, ci, vp, vp, ci, vp, ctypes.POINTER(Grid), vp, vp, vp, ci, vp]
     L.orc_search_for_initialization.argtypes = [vp, vp, ci, vp, vp, vp, ci, ctypes.POINTER(Grid), vp, vp, ci, cf, ci, vp]
@@ -328,8 +328,10 @@ def assign_grid(keys, grid):
     return off, idx[:off[-1]].copy()
 
 
-def search_by_projection(pts, keys, desc, uright, scale, grid, occupied, th, nnratio=None, motion=0, check_ori=True):
-    """nnratio given -> SearchByProjection(Frame, MapPoints) (a15); else the Frame/Frame variant (a16)."""
+def search_by_projection(pts, keys, desc, uright, scale, grid, occupied, th, nnratio=None, motion=0, check_ori=True, transient=None):
+    """nnratio given -> SearchByProjection(Frame, MapPoints) (a15); else the Frame/Frame variant (a16).
+    transient[i] != 0: point i has Observations() == 0, its match does not hide the keypoint from later points."""
+    tr = None if transient is None else np.ascontiguousarray(transient, np.uint8)
     pts = np.ascontiguousarray(pts)
     keys = np.ascontiguousarray(keys)
     desc = np.ascontiguousarray(desc, np.uint8)
@@ -343,11 +345,11 @@ def search_by_projection(pts, keys, desc, uright, scale, grid, occupied, th, nnr
     if nnratio is not None:
         n = _mlib().orc_search_by_projection_points(_p(pts), len(pts), _p(keys), _p(desc), len(keys), None if ur is None else _p(ur),
                                                     _p(scale), ctypes.byref(g), _p(off), _p(idx), None if occ is None else _p(occ),
-                                                    th, nnratio, _p(out))
+                                                    th, nnratio, _p(out), None if tr is None else _p(tr))
     else:
         n = _mlib().orc_search_by_projection_frame(_p(pts), len(pts), _p(keys), _p(desc), len(keys), None if ur is None else _p(ur),
                                                    _p(scale), ctypes.byref(g), _p(off), _p(idx), None if occ is None else _p(occ),
-                                                   th, motion, int(check_ori), _p(out))
+                                                   th, motion, int(check_ori), _p(out), None if tr is None else _p(tr))
     return out, n
 
 

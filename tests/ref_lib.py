@@ -45,6 +45,11 @@ def lib():
         L.ref_vocab_score.argtypes = [vp, vp, vp, ci, vp, vp, ci]
         L.ref_vocab_score.restype = cd
         L.ref_descriptor_distance.argtypes = [vp, vp]
+        L.ref_shim_algebra.argtypes = [ci, vp, ci, ci, vp, ci, ci, vp, vp]
+        L.ref_shim_norm.argtypes = [vp, ci]
+        L.ref_shim_norm.restype = cd
+        L.ref_shim_dot.argtypes = [vp, vp, ci]
+        L.ref_shim_dot.restype = cd
         L.ref_run_matcher_scene.argtypes = [ctypes.c_char_p, ctypes.c_char_p]
         L.ref_set_allocator.argtypes = [ci]
         assert L.ref_set_allocator(1) == 0      # canonical (monotonic) model by default; set_allocator(0) = the real heap

@@ -55,6 +55,19 @@ def test_cpp_dropin_matcher(tmp_path):
         rin, rout = str(tmp_path / "m_in.bin"), str(tmp_path / "ref_out.bin")
         assert ref_lib.lib().ref_run_matcher_scene(rin.encode(), rout.encode()) == 0
         assert open(rout, "rb").read() == got
+        # a second scene whose projection sections use poses with real rotations, scales and translations (Sim3 1.7 / 0.6,
+        # 1-2 degree rotations): no hand-made expectation, the drop-in's output file must equal the reference's
+        for k, (seed, n1, n2) in enumerate(((21, 1500, 1300), (22, 900, 1100))):
+            d = tmp_path / f"general{k}"
+            d.mkdir()
+            got = matcher_scene.check_scene(_dropin_driver, d, seed, n1, n2, general_poses=True)
+            assert ref_lib.lib().ref_run_matcher_scene(str(d / "m_in.bin").encode(), str(d / "ref_out.bin").encode()) == 0
+            want = (d / "ref_out.bin").read_bytes()
+            if got != want:
+                a, b = matcher_scene._read_all(d / "m_out.bin"), matcher_scene._read_all(d / "ref_out.bin")
+                diff = [(i, int((np.frombuffer(x, np.int32) != np.frombuffer(y, np.int32)).sum()) if len(x) == len(y) else -1)
+                        for i, (x, y) in enumerate(zip(a, b)) if x != y]
+                raise AssertionError(f"scene {seed}: records differing from the reference (index, entries): {diff}")
 
 
 def pkg_mod():
