@@ -145,6 +145,10 @@ int orbx_vocab_create(orbx_ctx* ctx, int k, int L, int nnodes, const int32_t* ch
                       const uint8_t* node_desc, const int32_t* word_id, const float* weight, orbx_vocab** out);
 /* ORBvoc text format (TemplatedVocabulary::loadFromTextFile, TemplatedVocabulary.h:1385-1487) */
 int orbx_vocab_load_text(orbx_ctx* ctx, const char* path, orbx_vocab** out);
+/* scoring / weighting of the text header (DBoW2 ScoringType / WeightingType; 0 / 0 = L1_NORM / TF_IDF, what ORBvoc uses and
+ * what orbx_vocab_create assumes).  orbx_bow_vector returns ORBX_E_UNSUPPORTED unless scoring is L1_NORM and weighting is
+ * TF_IDF or TF: the other modes accumulate and normalise differently (TemplatedVocabulary.h:1166-1221). */
+int orbx_vocab_modes(const orbx_vocab* v, int* scoring, int* weighting);
 void orbx_vocab_destroy(orbx_vocab* v);
 int orbx_vocab_info(const orbx_vocab* v, int* k, int* L, int* nnodes, int* nwords);
 /* Per feature: leaf word id, leaf weight, and the node id at level L - levelsup (0 = root when levelsup >= L). */

@@ -6,6 +6,8 @@
 // descends; L sequential steps.  The node table (k=10, L=6: 1.11 M nodes x 32 B = 35 MB) is L2-resident on
 // B200 (126 MB), so the 2 x 16-byte gathers per lane are L2 hits after the first frames.
 #include "orbx_internal.h"
+#include <cstdio>
+#include <cstdlib>
 #include <stdio.h>
 #include <string.h>
 #include <algorithm>
@@ -19,6 +21,7 @@ struct orbx_vocab {
     int32_t* dChildOff = nullptr; int32_t* dChild = nullptr; uint4* dDesc = nullptr; int32_t* dWord = nullptr; float* dWeight = nullptr;
     double* dWordWeight = nullptr;      // weight of word id w as a double (WordValue), for the BowVector
     int wordCap = 0;                    // 1 + largest word id
+    int scoring = 0, weighting = 0;     // DBoW2 ScoringType / WeightingType of the text header (0, 0 = L1_NORM, TF_IDF: ORBvoc)
 };
 
 namespace orbx {
@@ -225,29 +228,69 @@ extern "C" int orbx_vocab_info(const orbx_vocab* v, int* k, int* L, int* nnodes,
 
 // ORBvoc text format: header "k L scoring weighting", then one line per node (creation order, ids 1..):
 // "parent isLeaf b0 ... b31 weight" (TemplatedVocabulary.h:1385-1487; FORB::fromString FORB.cpp:120-135).
+// One pass over the file buffer (strtol-style scanning; a 170 MB ORBvoc-sized file parses in about a second, the reference's
+// per-line stringstreams take ten).  Format, TemplatedVocabulary.h:1385-1487: "k L scoring weighting", then one line per
+// node in id order: "parent isLeaf d0 ... d31 weight".
+namespace {
+inline const char* skipBlank(const char* p, const char* e) { while (p < e && (*p == ' ' || *p == '\t' || *p == '\r')) ++p; return p; }
+inline bool scanInt(const char*& p, const char* e, long& v)
+{
+    p = skipBlank(p, e);
+    if (p >= e) return false;
+    bool neg = false;
+    if (*p == '-' || *p == '+') { neg = *p == '-'; ++p; }
+    if (p >= e || *p < '0' || *p > '9') return false;
+    long r = 0;
+    while (p < e && *p >= '0' && *p <= '9') { r = r * 10 + (*p - '0'); ++p; }
+    v = neg ? -r : r;
+    return true;
+}
+}
+
 extern "C" int orbx_vocab_load_text(orbx_ctx* h, const char* path, orbx_vocab** out)
 {
     if (!h || !path || !out) return ORBX_E_INVALID;
-    std::ifstream f(path);
-    if (!f.good()) return ORBX_E_INVALID;
-    std::string line;
-    if (!std::getline(f, line)) return ORBX_E_INVALID;
-    int k = 0, L = 0, n1 = 0, n2 = 0;
-    { std::stringstream ss(line); ss >> k >> L >> n1 >> n2; }
+    std::string buf;
+    {
+        FILE* f = fopen(path, "rb");
+        if (!f) return ORBX_E_INVALID;
+        fseek(f, 0, SEEK_END);
+        const long sz = ftell(f);
+        fseek(f, 0, SEEK_SET);
+        if (sz <= 0) { fclose(f); return ORBX_E_INVALID; }
+        buf.resize((size_t)sz);
+        const size_t got = fread(&buf[0], 1, (size_t)sz, f);
+        fclose(f);
+        if (got != (size_t)sz) return ORBX_E_INVALID;
+    }
+    const char* p = buf.data(); const char* const e = p + buf.size();
+    long k = 0, L = 0, n1 = 0, n2 = 0;
+    if (!scanInt(p, e, k) || !scanInt(p, e, L) || !scanInt(p, e, n1) || !scanInt(p, e, n2)) return ORBX_E_INVALID;
     if (k < 1 || k > 20 || L < 1 || L > 10 || n1 < 0 || n1 > 5 || n2 < 0 || n2 > 3) return ORBX_E_INVALID; // same gate as :1409
+    while (p < e && *p != '\n') ++p;
+    size_t expect = 1, pw = 1;
+    for (long l = 0; l < L; ++l) { pw *= (size_t)k; expect += pw; }
     std::vector<int32_t> parent(1, -1), leaf(1, 0);
     std::vector<uint8_t> desc(32, 0);
     std::vector<float> weight(1, 0.f);
     std::vector<double> weight64(1, 0.0);          // WordValue is a double in DBoW2: the BowVector uses the parsed value
-    while (std::getline(f, line)) {
-        if (line.find_first_not_of(" \t\r\n") == std::string::npos) continue; // the reference's trailing phantom node is never visited
-        std::stringstream ss(line);
-        int pid = 0, isLeaf = 0;
-        ss >> pid >> isLeaf;
-        if (pid < 0 || pid >= (int)parent.size()) return ORBX_E_INVALID;
-        parent.push_back(pid); leaf.push_back(isLeaf);
-        for (int i = 0; i < 32; ++i) { int b = 0; ss >> b; desc.push_back((uint8_t)b); }
-        double w = 0; ss >> w; weight.push_back((float)w); weight64.push_back(w);
+    parent.reserve(expect); leaf.reserve(expect); desc.reserve(32 * expect); weight.reserve(expect); weight64.reserve(expect);
+    while (p < e) {
+        if (*p == '\n') { ++p; continue; }
+        p = skipBlank(p, e);
+        if (p >= e) break;
+        if (*p == '\n') continue;                  // an empty line: the reference's trailing phantom node is never visited
+        long pid = 0, isLeaf = 0;
+        if (!scanInt(p, e, pid) || !scanInt(p, e, isLeaf)) return ORBX_E_INVALID;
+        if (pid < 0 || pid >= (long)parent.size()) return ORBX_E_INVALID;
+        parent.push_back((int32_t)pid); leaf.push_back((int32_t)isLeaf);
+        for (int i = 0; i < 32; ++i) { long b = 0; if (!scanInt(p, e, b)) return ORBX_E_INVALID; desc.push_back((uint8_t)b); }
+        p = skipBlank(p, e);
+        char* endw = nullptr;
+        const double w = (p < e && *p != '\n') ? strtod(p, &endw) : 0.0;   // buf is NUL-terminated (std::string)
+        if (endw) p = endw;
+        weight.push_back((float)w); weight64.push_back(w);
+        while (p < e && *p != '\n') ++p;
     }
     const int nn = (int)parent.size();
     std::vector<int32_t> off((size_t)nn + 1, 0), child((size_t)(nn > 1 ? nn - 1 : 0)), word((size_t)nn, 0);
@@ -257,11 +300,20 @@ extern "C" int orbx_vocab_load_text(orbx_ctx* h, const char* path, orbx_vocab** 
     for (int i = 1; i < nn; ++i) child[fill[parent[i]]++] = i; // ascending id = push_back order (:1448)
     int wid = 0;
     for (int i = 1; i < nn; ++i) if (leaf[i] > 0) word[i] = wid++; // :1467-1473
-    int rc = orbx_vocab_create(h, k, L, nn, off.data(), child.data(), desc.data(), word.data(), weight.data(), out);
+    int rc = orbx_vocab_create(h, (int)k, (int)L, nn, off.data(), child.data(), desc.data(), word.data(), weight.data(), out);
     if (rc) return rc;
+    (*out)->scoring = (int)n1; (*out)->weighting = (int)n2;
     std::vector<double> ww((size_t)std::max(wid, 1), 0.0);
     for (int i = 1; i < nn; ++i) if (leaf[i] > 0) ww[word[i]] = weight64[i];
     return orbx_vocab_set_word_weights(*out, ww.data(), wid);
+}
+
+extern "C" int orbx_vocab_modes(const orbx_vocab* v, int* scoring, int* weighting)
+{
+    if (!v) return ORBX_E_INVALID;
+    if (scoring) *scoring = v->scoring;
+    if (weighting) *weighting = v->weighting;
+    return ORBX_OK;
 }
 
 extern "C" int orbx_vocab_set_word_weights(orbx_vocab* v, const double* weights, int nwords)
@@ -278,6 +330,10 @@ extern "C" int orbx_bow_vector(orbx_ctx* h, const orbx_vocab* v, const int32_t* 
 {
     if (!h || !v || n < 0 || !nwords || (n > 0 && (!word || !ids || !values))) return ORBX_E_INVALID;
     *nwords = 0;
+    // TemplatedVocabulary::transform accumulates with addWeight only for TF_IDF (0) / TF (1) weighting (IDF / BINARY use
+    // addIfNotExist, :1166-1221) and this entry point normalises with the L1 norm of L1_NORM scoring (0): anything else
+    // would be silently wrong, so it is refused.
+    if (v->scoring != 0 || v->weighting > 1) return ORBX_E_UNSUPPORTED;
     if (n == 0) return ORBX_OK;
     Ctx* c = &h->c;
     if (c->device != v->device) return ORBX_E_INVALID;

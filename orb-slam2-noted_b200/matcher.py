@@ -51,6 +51,7 @@ def _mlib():
     L.orbx_vocab_destroy.argtypes = [vp]
     L.orbx_vocab_destroy.restype = None
     L.orbx_vocab_info.argtypes = [vp, ip, ip, ip, ip]
+    L.orbx_vocab_modes.argtypes = [vp, ip, ip]
     L.orbx_bow_transform.argtypes = [vp, vp, vp, ci, ci, ci, vp, vp, vp]
     L.orbx_feature_vector.argtypes = [vp, vp, ci, vp, vp, vp, ip]
     L.orbx_match_bow.argtypes = [vp, ci, ctypes.POINTER(_BowSide), ctypes.POINTER(_BowSide), ctypes.POINTER(_Triangulation), cf, ci,
@@ -92,6 +93,12 @@ class Vocabulary:
         v = [ctypes.c_int() for _ in range(4)]
         _mlib().orbx_vocab_info(self._v, *[ctypes.byref(x) for x in v])
         return tuple(x.value for x in v)  # k, L, nnodes, nwords
+
+    def modes(self):
+        """(scoring, weighting) of the text header; (0, 0) = L1_NORM / TF_IDF."""
+        a, b = ctypes.c_int(), ctypes.c_int()
+        _mlib().orbx_vocab_modes(self._v, ctypes.byref(a), ctypes.byref(b))
+        return a.value, b.value
 
     def transform(self, desc, levelsup=4):
         """-> (word_id, weight, node_id) per feature; see feature_vector() for the FeatureVector."""

@@ -65,6 +65,105 @@ def test_vocab_text_loader_and_transform(P, ctx, vocs, tmp_path):
             assert np.array_equal(x.view(np.uint32), y.view(np.uint32)) and np.array_equal(y.view(np.uint32), z.view(np.uint32))
 
 
+@pytest.fixture(scope="module")
+def vocs6(P, ctx):
+    """configs[3]'s vocabulary shape: k = 10, L = 6 (1 111 111 nodes = 35 MB of node descriptors, 10^6 words)."""
+    v = synth.vocabulary_bfs(0, 10, 6)
+    vo = O.VocabArrays(v["k"], v["L"], v["child_off"], v["child"], v["desc"], v["word_id"], v["weight"])
+    vg = P.Vocabulary(ctx, v["k"], v["L"], v["child_off"], v["child"], v["desc"], v["word_id"], v["weight"])
+    return v, vo, vg
+
+
+def _near_leaves(v, seed, n):
+    rng = np.random.default_rng(seed)
+    leaves = np.flatnonzero(v["leaf"] > 0)
+    near = synth.descriptors(seed, n * 3 // 4, 0.06, v["desc"][rng.choice(leaves, n * 3 // 4)])
+    return np.ascontiguousarray(np.concatenate([near, synth.descriptors(seed + 1, n - len(near))]))
+
+
+def test_orbvoc_sized_vocabulary_transform_and_text_loader(P, ctx, vocs6, tmp_path):
+    """The 6-level descent over 1.1 M nodes: GPU == oracle at levelsup 0 / 4 / 6 (6 = one node = brute-force SearchByBoW),
+    from the flattened arrays and from the 170 MB ORBvoc-format text file (which DBoW2's own loader reads to the same tree:
+    tests/test_oracle_vs_ref.py); BowVector of the 10 k features bit-equal as doubles."""
+    v, vo, vg = vocs6
+    assert vg.info() == (10, 6, 1111111, 1000000)
+    d = _near_leaves(v, 7, 10000)
+    want = {ls: O.bow_transform(vo, d, ls) for ls in (0, 4, 6)}
+    for ls, w in want.items():
+        got = vg.transform(d, ls)
+        for x, y in zip(w, got):
+            assert np.array_equal(x.view(np.uint32), y.view(np.uint32)), ls
+    assert len(np.unique(want[4][2])) <= 100 and len(np.unique(want[4][2])) > 50 and np.all(want[6][2] == 0)
+    assert len(np.unique(want[0][0])) > 5000                                   # the descents really spread over the leaves
+    path = tmp_path / "voc6.txt"
+    path.write_bytes(synth.vocabulary_text_fixed(v))
+    vt = P.Vocabulary(ctx, path=str(path))
+    path.unlink()
+    assert vt.info() == vg.info() and vt.modes() == (0, 0)
+    for ls, w in want.items():
+        got = vt.transform(d, ls)
+        for x, y in zip(w, got):
+            assert np.array_equal(x.view(np.uint32), y.view(np.uint32)), ("text", ls)
+    ww = np.zeros(1000000, np.float64)
+    ww[v["word_id"][v["leaf"] > 0]] = v["weight"][v["leaf"] > 0].astype(np.float64)
+    ids, vals = O.bow_vector(want[4][0], ww)
+    gi, gv = vt.bow_vector(want[4][0])
+    assert np.array_equal(ids, gi) and np.array_equal(vals.view(np.uint64), gv.view(np.uint64))
+
+
+@pytest.mark.parametrize("levelsup", [4, 6])
+def test_config4_matchers_through_the_orbvoc_sized_vocabulary(P, ctx, vocs6, levelsup):
+    """configs[3]: 10 k x 10 k descriptors per keyframe pair, FeatureVectors from the k = 10, L = 6 tree at levelsup 4 (BoW
+    mode, <= 100 nodes) and 6 (one node: brute force): SearchByBoW x2 and SearchForTriangulation == oracle."""
+    v, vo, vg = vocs6
+    n = 10000
+    d1 = _near_leaves(v, 31, n)
+    rng = np.random.default_rng(32)
+    perm = rng.permutation(n)
+    d2 = np.concatenate([synth.descriptors(33, 7000, 0.05, d1[perm[:7000]]), _near_leaves(v, 34, 3000)])
+    k1, k2 = synth.keypoints(35, n, dtype=P.KP_DTYPE), synth.keypoints(36, n, dtype=P.KP_DTYPE)
+    k2["angle"][:7000] = np.mod(k1["angle"][perm[:7000]] - np.float32(30) + rng.normal(0, 3, 7000).astype(np.float32), np.float32(360))
+    k2["x"][:7000] = k1["x"][perm[:7000]] + rng.normal(0, 2, 7000).astype(np.float32)
+    k2["y"][:7000] = k1["y"][perm[:7000]] + rng.normal(0, 2, 7000).astype(np.float32)
+    k2["octave"][:7000] = k1["octave"][perm[:7000]]
+    so, sg = sides(P, vo, vg, d1, k1, d2, k2, levelsup, 37, p_has=0.6, stereo=True)
+    assert (len(so[0].node_id) == 1) == (levelsup == 6)
+    for kf_kf in (False, True):
+        want, nw = O.search_by_bow(so[0], so[1], 0.7, True, kf_kf)
+        got, ng = P.ORBmatcher(ctx, 0.7, True).SearchByBoW(sg[0], sg[1], kf_kf)
+        assert np.array_equal(want, got) and nw == ng and nw > 500, (kf_kf, nw, ng)
+    p = O.params(1000)
+    F12 = (np.array([[0, 0, 0], [0, 0, -1], [0, 1, 0]], np.float32) + np.float32(1e-4) * rng.normal(size=(3, 3)).astype(np.float32))
+    sc16 = np.zeros(16, np.float32); sc16[:8] = p.scale[:8]
+    sg16 = np.zeros(16, np.float32); sg16[:8] = np.array(p.sigma2[:8], np.float32) * 9
+    want, nw = O.search_for_triangulation(so[0], so[1], F12, 300.0, 200.0, sc16, sg16, False, True)
+    got, ng = P.ORBmatcher(ctx, 0.6, True).SearchForTriangulation(sg[0], sg[1], F12, (300.0, 200.0), sc16, sg16, False)
+    assert np.array_equal(want, got) and nw == ng and nw > 100, (nw, ng)
+
+
+def test_vocabulary_modes_other_than_l1_tfidf_are_refused(P, ctx, tmp_path):
+    """A text header with IDF / BINARY weighting or a non-L1 scoring: transform still works (the descent does not depend on
+    them), the BowVector entry point refuses instead of accumulating the wrong way (TemplatedVocabulary.h:1166-1221)."""
+    v = synth.vocabulary(0, 10, 3)
+    body = synth.vocabulary_text(v).split("\n", 1)[1]
+    d = synth.descriptors(5, 200)
+    for scoring, weighting, ok in ((0, 0, True), (0, 1, True), (0, 2, False), (0, 3, False), (1, 0, False), (5, 0, False)):
+        path = tmp_path / f"voc_{scoring}_{weighting}.txt"
+        path.write_text(f"10 3 {scoring} {weighting}\n" + body)
+        vt = P.Vocabulary(ctx, path=str(path))
+        assert vt.modes() == (scoring, weighting)
+        word, _, _ = vt.transform(d, 2)
+        if ok:
+            assert len(vt.bow_vector(word)[0]) > 0
+        else:
+            with pytest.raises(P.OrbxError, match="unsupported"):
+                vt.bow_vector(word)
+    bad = tmp_path / "bad.txt"
+    bad.write_text("10 3 9 0\n" + body)                                   # the reference's own header gate (:1409)
+    with pytest.raises(P.OrbxError):
+        P.Vocabulary(ctx, path=str(bad))
+
+
 CASES = [(1, 1500, 1400, 0.08, 0.0, 1), (2, 2000, 2000, 0.12, 0.0, 2), (3, 1200, 900, 0.05, 0.6, 1), (4, 700, 1800, 0.10, 0.3, 3),
          (5, 3000, 3000, 0.10, 0.0, 4), (6, 40, 35, 0.05, 0.0, 2), (7, 2500, 2500, 0.02, 0.9, 3),
          (8, 10000, 10000, 0.10, 0.0, 4), (9, 10000, 10000, 0.10, 0.0, 1)]   # config 4: 10 k x 10 k, brute force (one node) and BoW
