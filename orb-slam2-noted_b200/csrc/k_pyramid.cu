@@ -5,6 +5,7 @@
 // per-level table (L1/L2 resident).  Level l is produced from level l-1, so levels are separate
 // launches; the batch dimension provides the parallelism (grid.z = frames).
 #include "orbx_internal.h"
+#include <algorithm>
 
 namespace orbx {
 
@@ -147,6 +148,110 @@ resizeLinearWordKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sF
     }
 }
 
+// Staged path (batches that fill the GPU).  ncu on the register-only kernels shows the LSU data pipe, not DRAM, as the
+// limiter (l1tex data-pipe wavefronts 71 %, DRAM 31 %): a warp's lanes sit ~1.2 x their pixel count apart in the source,
+// so every warp-wide global load spans 3-4 cache lines (one wavefront each), twice that where a warp straddles two row
+// bands.  Here a CTA takes kBands bands of 16 destination rows; the source rows they need are CONTIGUOUS in memory (whole
+// rows incl. padding), so ONE bulk async copy (cp.async.bulk -> UBLKCP, completion on an mbarrier) brings them into shared
+// memory without touching the LSU, and the strided per-thread reads become 32-bit LDS with at most 2-way bank conflicts.
+// Thread = 8 destination pixels x 16 rows: three funnel shifts align the 12-byte window to the first pixel's source column
+// once per source row, then pixel i's byte pair (s_i, s_i + 1) is one PRMT with a per-thread selector (pixels 0-3 start 0..6
+// bytes into words v0:v1, pixels 4-7 start 4..10 bytes in = words v1:v2; checked per group on the host: resize8Ok), one
+// IDP.2A against the (c0, c1) pair and one shift; a destination row is 2 IMAD.HI + add + shift per pixel, 3 PRMT per packed
+// word and one 64-bit store.  Reads past a row's end stay inside the staged block (+16 bytes of slack) and meet zero weights.
+constexpr int kStageRows = 16;
+__global__ void __launch_bounds__(512)
+resizeLinearStagedKernel(const uint8_t* __restrict__ src, size_t sPitch, size_t sFrame, int sw, int sh,
+                         uint8_t* __restrict__ dst, size_t dPitch, size_t dFrame, int dw, int dh,
+                         const uint32_t* __restrict__ tapG, const ResizeTap* __restrict__ tapY, int frame0, int nBands)
+{
+    extern __shared__ __align__(128) uint8_t sRows[];
+    __shared__ __align__(8) unsigned long long sBar;
+    const int groups = (dw + 7) >> 3;
+    const int yCta = blockIdx.x * nBands * kStageRows;
+    const int yCtaEnd = min(yCta + nBands * kStageRows, dh);
+    const int rFirst = tapY[yCta].s, rLast = min((int)tapY[yCtaEnd - 1].s + 1, sh - 1);
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&sBar);
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        const uint32_t bytes = (uint32_t)((size_t)(rLast - rFirst + 1) * sPitch);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        const uint8_t* g = src + (size_t)(blockIdx.z + frame0) * sFrame + (size_t)rFirst * sPitch;
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"((uint32_t)__cvta_generic_to_shared(sRows)), "l"(g), "r"(bytes), "r"(bar) : "memory");
+    }
+    // per-thread constants while the copy is in flight
+    const int band = threadIdx.x / groups;
+    const int x0 = (threadIdx.x - band * groups) * 8;
+    (void)dw;
+    const int yb = yCta + band * kStageRows, ye = min(yb + kStageRows, yCtaEnd);
+    const bool active = band < nBands && yb < yCtaEnd;
+    // Per-group constants from the host-built table (buildResizeGroups), structure of arrays: a warp's 11 loads are 11
+    // lane-contiguous lines.  (Reading the eight 8-byte ResizeTap records per thread instead puts the lanes 64 bytes apart:
+    // 16 cache lines per request, as many LSU wavefronts as the whole band's row work -- measured with ncu.)
+    uint32_t cpair[8], sel[8];
+    const int gi = min(threadIdx.x - band * groups, groups - 1);
+    const int s0 = (int)__ldg(tapG + gi);
+    {
+        const uint32_t sa = __ldg(tapG + groups + gi), sb = __ldg(tapG + 2 * groups + gi);
+        // PRMT reads the low four nibbles of its selector; bytes 2-3 of the result are never used, so a shifted copy will do
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) { sel[i] = sa >> (8 * i); sel[4 + i] = sb >> (8 * i); }
+        #pragma unroll
+        for (int i = 0; i < 8; ++i) cpair[i] = __ldg(tapG + (3 + i) * groups + gi);
+    }
+    const uint32_t ash = 8u * (uint32_t)(s0 & 3);
+    const int pw = (int)(sPitch >> 2);
+    int y = active ? yb : 0;
+    ResizeTap ty = tapY[y];
+    __syncthreads();                                          // the mbarrier is initialised before anybody polls it
+    uint32_t done = 0;
+    while (!done)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(done) : "r"(bar) : "memory");
+    if (!active) return;
+    int r = ty.s;                                             // source row the pointer is on
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(sRows) + (size_t)(r - rFirst) * pw + (s0 >> 2);
+    uint8_t* D = dst + (size_t)(blockIdx.z + frame0) * dFrame + (size_t)y * dPitch + x0;
+
+    auto hrow = [&](uint32_t (&t)[8]) {                       // reduces the row under the pointer, then steps down
+        const uint32_t w0 = p[0], w1 = p[1], w2 = p[2], w3 = p[3];
+        if (r < rLast) p += pw;                               // rows are clipped, weights kept (OpenCV VResize)
+        ++r;
+        const uint32_t v0 = __funnelshift_r(w0, w1, ash), v1 = __funnelshift_r(w1, w2, ash), v2 = __funnelshift_r(w2, w3, ash);
+        #pragma unroll
+        for (int i = 0; i < 4; ++i) t[i] = __dp2a_lo(cpair[i], __byte_perm(v0, v1, sel[i]), 0u) >> 4;
+        #pragma unroll
+        for (int i = 4; i < 8; ++i) t[i] = __dp2a_lo(cpair[i], __byte_perm(v1, v2, sel[i]), 0u) >> 4;
+    };
+    uint32_t tp[8];
+    hrow(tp);
+    int rb = ty.s;                                            // tp holds row rb
+    while (y < ye) {
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint32_t tc[8];
+            hrow(tc);                                         // row rb + 1
+            if (y < ye && ty.s == rb) {                       // at most one destination row per source row (host-checked)
+                const uint32_t b0 = (uint32_t)ty.c0 << 16, b1 = (uint32_t)ty.c1 << 16;
+                uint32_t v[8];
+                #pragma unroll
+                for (int i = 0; i < 8; ++i) v[i] = (__umulhi(b0, tp[i]) + __umulhi(b1, tc[i]) + 2u) >> 2;   // <= 255
+                uint2 o;
+                o.x = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
+                o.y = __byte_perm(__byte_perm(v[4], v[5], 0x0040), __byte_perm(v[6], v[7], 0x0040), 0x5410);
+                *reinterpret_cast<uint2*>(D) = o;             // x0 is a multiple of 8 and rows are padded to 16 bytes
+                D += dPitch;
+                if (++y < ye) ty = tapY[y];
+            }
+            ++rb;
+            #pragma unroll
+            for (int i = 0; i < 8; ++i) tp[i] = tc[i];
+        }
+    }
+}
+
 // cvtColor(RGB / BGR / RGBA / BGRA -> GRAY), the step in front of the extractor (src/Tracking.cc:252-278, 313-326, 377-390),
 // with OpenCV's 8-bit fixed point: (R * 9798 + G * 19235 + B * 3735 + 16384) >> 15 (cv2 4.13, the pinned dependency).
 // 4 pixels per thread: 12 or 16 source bytes in, one 32-bit store out.
@@ -209,7 +314,28 @@ int launchPyramid(Ctx* c, int frame0, int batch)
         if (l == 1) { src = c->lvl0; sp = c->lvl0Pitch; sf = c->lvl0FrameStride; }
         else { src = c->dPyr + s.planeOff; sp = (size_t)s.pitch; sf = (size_t)s.pitch * s.h; }
         const bool wordOk = c->resizeWordOk[l] && ((((size_t)src) | sp | sf) & 3) == 0;
-        if (wordOk) {
+        // staged path: 16-byte aligned rows for the bulk copy, 8-byte aligned destination rows, enough CTAs to fill the GPU
+        const int groups8 = (d.w + 7) / 8;
+        int nBands = 0; size_t smem = 0;
+        if (wordOk && c->resize8Ok[l] && c->dTapG[l] && c->resizeWide && ((((size_t)src) | sp | sf) & 15) == 0 && (d.pitch & 7) == 0 &&
+            ((d.planeOff | (size_t)d.pitch * d.h) & 7) == 0 && groups8 <= 512) {
+            const int allBands = (d.h + kStageRows - 1) / kStageRows;
+            for (int nb = std::min(4, 512 / groups8); nb >= 1; --nb) {     // most bands per CTA (fewer idle lanes) that fit 64 KB
+                const size_t rows = (size_t)((long long)nb * kStageRows * s.h / d.h) + 4;
+                const size_t need = rows * sp + 16;
+                if (need <= 64 * 1024 && (long long)batch * ((allBands + nb - 1) / nb) >= 148LL * 3) { nBands = nb; smem = need; break; }
+            }
+        }
+        if (nBands > 0) {
+            if (smem > 48 * 1024 && smem > c->smemCfg[SMEM_RESIZE]) {
+                ORBX_CUDA(c, cudaFuncSetAttribute(resizeLinearStagedKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+                c->smemCfg[SMEM_RESIZE] = 64 * 1024;
+            }
+            const int allBands = (d.h + kStageRows - 1) / kStageRows;
+            dim3 grid((allBands + nBands - 1) / nBands, 1, batch), block(((groups8 * nBands + 31) / 32) * 32);
+            resizeLinearStagedKernel<<<grid, block, smem, c->stream>>>(src, sp, sf, s.w, s.h, c->dPyr + d.planeOff, (size_t)d.pitch,
+                                                                      (size_t)d.pitch * d.h, d.w, d.h, c->dTapG[l], c->dTapY[l], frame0, nBands);
+        } else if (wordOk) {
             const int groups = (d.w + 3) / 4;
             const bool small = (long long)batch * groups * ((d.h + 15) / 16) < 148LL * 640;     // too few threads to fill the GPU
             const int rows = small ? 2 : 16;

@@ -123,7 +123,8 @@ static void freeGeometry(Ctx* c)
     for (int l = 0; l < kMaxLevels; ++l) {
         if (c->dTapX[l]) cudaFree(c->dTapX[l]);
         if (c->dTapY[l]) cudaFree(c->dTapY[l]);
-        c->dTapX[l] = c->dTapY[l] = nullptr;
+        if (c->dTapG[l]) cudaFree(c->dTapG[l]);
+        c->dTapX[l] = c->dTapY[l] = nullptr; c->dTapG[l] = nullptr;
     }
 }
 
@@ -201,6 +202,31 @@ static int configure(Ctx* c, int w, int h)
         for (const ResizeTap& t : ty) if (t.c0 < 0 || t.c1 < 0) wordOk = false;
         for (size_t y = 1; y < ty.size(); ++y) if (ty[y].s <= ty[y - 1].s) wordOk = false;   // one destination row per source row at most
         c->resizeWordOk[l] = wordOk;
+        bool ok8 = wordOk;
+        for (size_t x = 0; x < tx.size(); x += 8)
+            for (size_t i = 1; i < 8 && x + i < tx.size(); ++i) {
+                const int d = tx[x + i].s - tx[x].s;
+                if (i < 4 ? (d < 0 || d > 6) : (d < 4 || d > 10)) ok8 = false;
+            }
+        c->resize8Ok[l] = ok8;
+        if (ok8) {   // constants of the staged kernel, one column per 8-pixel group (k_pyramid.cu: resizeLinearStagedKernel)
+            const int groups = ((int)tx.size() + 7) / 8;
+            std::vector<uint32_t> tg((size_t)11 * groups, 0u);
+            for (int gI = 0; gI < groups; ++gI) {
+                const int first = tx[(size_t)gI * 8].s;
+                tg[gI] = (uint32_t)first;
+                for (int i = 0; i < 8; ++i) {
+                    const ResizeTap& t = tx[std::min((size_t)gI * 8 + i, tx.size() - 1)];
+                    // pixels past the row end reuse the last tap (they land in the row's padding): keep the selector in range
+                    const int dlt = std::min(std::max(t.s - first - (i >= 4 ? 4 : 0), 0), 6);
+                    const uint32_t sel = (uint32_t)dlt | ((uint32_t)(dlt + 1) << 4);
+                    tg[(size_t)(1 + i / 4) * groups + gI] |= sel << (8 * (i & 3));
+                    tg[(size_t)(3 + i) * groups + gI] = (uint32_t)(uint16_t)t.c0 | ((uint32_t)(uint16_t)t.c1 << 16);
+                }
+            }
+            ORBX_CUDA(c, cudaMalloc(&c->dTapG[l], sizeof(uint32_t) * tg.size()));
+            ORBX_CUDA(c, cudaMemcpy(c->dTapG[l], tg.data(), sizeof(uint32_t) * tg.size(), cudaMemcpyHostToDevice));
+        }
         ORBX_CUDA(c, cudaMalloc(&c->dTapX[l], sizeof(ResizeTap) * tx.size()));
         ORBX_CUDA(c, cudaMalloc(&c->dTapY[l], sizeof(ResizeTap) * ty.size()));
         ORBX_CUDA(c, cudaMemcpy(c->dTapX[l], tx.data(), sizeof(ResizeTap) * tx.size(), cudaMemcpyHostToDevice));
@@ -270,6 +296,7 @@ int orbx_create(orbx_ctx** out, int device, int nfeatures, float scale_factor, i
         if (cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (const char* e = getenv("ORBX_CHUNK")) c->chunk = atoi(e);
         if (const char* e = getenv("ORBX_OVERLAP_BLUR")) c->overlapBlur = atoi(e) != 0;
+        if (const char* e = getenv("ORBX_RESIZE_WIDE")) c->resizeWide = atoi(e) != 0;
         if (const char* e = getenv("ORBX_FAST_THREADS")) c->fastThreads = atoi(e) == 128 ? 128 : 256;
         if (const char* e = getenv("ORBX_FAST_SEGW")) c->fastSegW = std::max(64, std::min(640, atoi(e)));
         if (cudaMalloc(&c->dGeom, sizeof(GeomSet)) != cudaSuccess) { rc = ORBX_E_CUDA; break; }

@@ -61,7 +61,7 @@ struct GeomSet {            // what kernels need, uploaded to constant memory on
 
 // kernels with more than 48 KB of dynamic shared memory: cudaFuncSetAttribute is per device, so what has been configured is
 // remembered per context (a context belongs to one device and one caller), not in a process-wide static
-enum { SMEM_FAST128, SMEM_FAST256, SMEM_DESCRIBE, SMEM_OCTREE, SMEM_BOW_RESOLVE, SMEM_BOW_VECTOR, SMEM_SLOTS };
+enum { SMEM_FAST128, SMEM_FAST256, SMEM_DESCRIBE, SMEM_OCTREE, SMEM_BOW_RESOLVE, SMEM_BOW_VECTOR, SMEM_RESIZE, SMEM_SLOTS };
 
 struct Ctx {
     int device = 0;
@@ -88,10 +88,13 @@ struct Ctx {
     GeomSet* dGeom = nullptr;            // device copy (global memory; kernels read via __ldg / constant cache)
     ResizeTap* dTapX[kMaxLevels] = {};   // per-level tables (level l = taps from level l-1)
     ResizeTap* dTapY[kMaxLevels] = {};
+    uint32_t* dTapG[kMaxLevels] = {};    // staged resize: per 8-pixel group [s0 | 4 selectors | 4 selectors | 8 x (c0, c1)], SoA over groups
     StripDesc* dStrips = nullptr; int nStrips = 0, stripCap = 0;   // FAST strip table of the current geometry
     int geomStamp = 0;                   // bumped whenever the geometry / arenas change
     void* dTensorMaps = nullptr; int mapsStamp = -1;   // CUtensorMap[2][kMaxLevels] of the blurred / pyramid planes (k_describe.cu)
     bool resizeWordOk[kMaxLevels] = {};  // level l: every 4-pixel group reads <= 8 source bytes from an aligned word (k_pyramid.cu fast path)
+    bool resize8Ok[kMaxLevels] = {};     // level l: in every 8-pixel group pixels 0-3 start 0..6 and pixels 4-7 start 4..10 bytes after pixel 0 (staged path)
+    bool resizeWide = true;              // env ORBX_RESIZE_WIDE=0 keeps the register-only 4-pixel kernel (A/B measurements)
     // arenas
     uint8_t* dPyr = nullptr; size_t pyrBytes = 0;      // levels (level 0 too unless used in place)
     uint8_t* dBlur = nullptr; size_t blurBytes = 0;
