@@ -36,6 +36,17 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 W, H, NFEAT, NLEVELS, SCALE, INI, MINTH = 640, 480, 1000, 8, 1.2, 20, 7
 DISTINCT = 32  # distinct synthetic frames; the batch tiles them (addresses differ, so caches see B frames)
+# BASELINE.json configs (the metric is quoted on "tum"; the others are the parity-test shapes, measurable with --config):
+#   name: (width, height, features, default frames per GPU per step, stereo pairs?)
+CONFIGS = {"tum": (640, 480, 1000, 1024, False), "kitti": (1241, 376, 2000, 512, True), "euroc": (752, 480, 1200, 1024, True),
+           "1080p": (1920, 1080, 4000, 128, False), "match": (640, 480, 1000, 64, False)}
+CONFIG = "tum"
+
+
+def set_config(name):
+    global W, H, NFEAT, CONFIG
+    CONFIG = name
+    W, H, NFEAT = CONFIGS[name][:3]
 
 
 def level_sizes():
@@ -56,7 +67,7 @@ def algorithmic_bytes():
 
 def workload_config():
     """`config` of BOTH arms: the driver compares the two dicts, so everything arm-specific lives in other keys."""
-    return {"workload": f"{W}x{H} gray, {NFEAT} features, {NLEVELS} levels, scale {SCALE}, FAST {INI}/{MINTH}",
+    return {"workload": f"{W}x{H} gray, {NFEAT} features, {NLEVELS} levels, scale {SCALE}, FAST {INI}/{MINTH}", "name": CONFIG,
             "frames": "tests/synth.py kind=texture (scene-like: multi-octave shading + rotated rectangles + noise; "
                       "~3% of pixels are FAST corners at threshold 7)"}
 
@@ -250,6 +261,117 @@ def hamming_gmatch(P, ex, dev, n=10000, pairs=32, reps=3):
     return pairs * n * n / (ms * 1e-3) / 1e9, ms, peak.value, reps
 
 
+def hamming_cpu_baseline(cores, n=10000, seconds=6.0):
+    """The reference's best / second-best loop (src/ORBmatcher.cc:325-345 with its own DescriptorDistance; oracle/_ref) on all
+    host cores, on a bounded slice of the 10 k x 10 k workload.  Falls back to the oracle port when the library is absent."""
+    import synth
+    q, t = synth.descriptors(1, n), synth.descriptors(2, n)
+    try:
+        import ref_lib as R
+        if not os.path.exists(R.SO):
+            raise OSError("no oracle/_ref")
+        L = R.lib()
+        nq = 64 * cores
+        rate = L.ref_hamming_throughput(q.ctypes.data, nq, t.ctypes.data, n, cores, None, None, None)      # probe
+        nq = int(min(n, max(64 * cores, rate * seconds / n)))
+        t0 = time.perf_counter()
+        rate = L.ref_hamming_throughput(q.ctypes.data, nq, t.ctypes.data, n, cores, None, None, None)
+        dt = time.perf_counter() - t0
+        kind, note = "reference", "oracle/_ref: the reference's DescriptorDistance in the loop of src/ORBmatcher.cc:325-345, one cv::Mat row per candidate"
+    except Exception:
+        import oracle_lib as O
+        nq = 500
+        t0 = time.perf_counter()
+        O.hamming_best2(q[:nq], t)
+        dt = time.perf_counter() - t0
+        rate, cores, kind, note = nq * n / dt, 1, "port", "oracle/ restatement, one thread"
+    return {"value": rate / 1e9, "unit": "GMatch/s", "cores": cores, "kind": kind,
+            "sample": f"{nq} x {n} descriptor pairs in {dt:.1f}s on {cores} host threads; {note}"}
+
+
+def match_e2e(P, ex, n=10000, pairs_bf=64, pairs_bow=256):
+    """Host descriptors in, match lists out, through orbx_match_bow_batch (SearchByBoW(KeyFrame, Frame) with its greedy
+    semantics, ratio test and rotation histogram): configs[3], brute force (levelsup = L: one node, 10^8 pairs per keyframe
+    pair) and BoW mode (levelsup = 4), FeatureVectors from the ORBvoc-sized k = 10, L = 6 vocabulary."""
+    import synth
+    v = synth.vocabulary_bfs(0, 10, 6)
+    voc = P.Vocabulary(ex, v["k"], v["L"], v["child_off"], v["child"], v["desc"], v["word_id"], v["weight"])
+    rng = np.random.default_rng(0)
+    leaves = np.flatnonzero(v["leaf"] > 0)
+    d1 = synth.descriptors(1, n, 0.06, v["desc"][rng.choice(leaves, n)])
+    d2 = np.concatenate([synth.descriptors(2, n * 3 // 4, 0.05, d1[: n * 3 // 4]), synth.descriptors(3, n - n * 3 // 4, 0.06, v["desc"][rng.choice(leaves, n - n * 3 // 4)])])[rng.permutation(n)]
+    k1, k2 = synth.keypoints(4, n, dtype=P.KP_DTYPE), synth.keypoints(5, n, dtype=P.KP_DTYPE)
+    out = {}
+    for name, levelsup, npairs in (("brute_force", 6, pairs_bf), ("bow", 4, pairs_bow)):
+        sides = []
+        for d, k in ((d1, k1), (d2, k2)):
+            w, wt, nd = voc.transform(d, levelsup)
+            nid, noff, feat = P.feature_vector(nd, wt)
+            sides.append(P.FrameView(d, k, np.ones(n, np.uint8), None, nid, noff, feat))
+        m = P.ORBmatcher(ex, 0.7, True)
+        batch = [(sides[0], sides[1])] * npairs
+        m.SearchByBoWBatch(batch[:2])
+        t0 = time.perf_counter()
+        res = m.SearchByBoWBatch(batch)
+        dt = time.perf_counter() - t0
+        off2 = {int(nid): int(sides[1].node_off[i + 1] - sides[1].node_off[i]) for i, nid in enumerate(sides[1].node_id)}
+        evals = sum(int(sides[0].node_off[i + 1] - sides[0].node_off[i]) * off2.get(int(nid), 0) for i, nid in enumerate(sides[0].node_id))
+        out[name] = {"pairs": npairs, "ms_per_pair": dt * 1e3 / npairs, "pairs_per_s": npairs / dt, "gmatch_per_s": npairs * evals / dt / 1e9,
+                     "nodes": int(len(sides[0].node_id)), "matches_per_pair": int(res[0][1]),
+                     "h2d_bytes_per_pair": int(2 * n * (32 + 28 + 1) + 8 * n), "d2h_bytes_per_pair": int(4 * n)}
+    out["note"] = ("host descriptors, keypoints and FeatureVectors in, match lists out, one orbx_match_bow_batch call per mode; "
+                   "gmatch_per_s counts the descriptor pairs the reference's loops would evaluate")
+    return out
+
+
+def stereo_pairs(P, device, npairs=48):
+    """configs[1] / configs[2]: a stereo frame the way Frame::Frame(imLeft, imRight) builds it (src/Frame.cc:119-217): left and right
+    extraction (two extractor handles, host images in, host keypoints out) and ComputeStereoMatches on the resident pyramids."""
+    import synth
+    exl = P.ORBextractor(NFEAT, SCALE, NLEVELS, INI, MINTH, device=device, max_w=W, max_h=H, max_batch=1)
+    exr = P.ORBextractor(NFEAT, SCALE, NLEVELS, INI, MINTH, device=device, max_w=W, max_h=H, max_batch=1)
+    imgs = [synth.stereo_pair(2000 + i, W, H) for i in range(4)]
+    bf, fx = 386.1448, 718.856                               # Examples/Stereo/KITTI00-02.yaml
+    nm = 0
+
+    def one(i):
+        left, right = imgs[i % len(imgs)]
+        kl, dl = exl(left)
+        kr, dr = exr(right)
+        ur, z = P.compute_stereo_matches(exl, exr, kl, dl, kr, dr, bf, bf / fx)
+        return int((z > 0).sum())
+    for i in range(4):
+        one(i)
+    t0 = time.perf_counter()
+    for i in range(npairs):
+        nm += one(i)
+    dt = time.perf_counter() - t0
+    return {"pairs_per_s": npairs / dt, "ms_per_pair": dt * 1e3 / npairs, "pairs": npairs, "stereo_matches_per_pair": nm / npairs,
+            "note": "one pair at a time: left + right orbx_extract (host in / host out) and orbx_stereo_match, one caller"}
+
+
+def cpp_latency():
+    """ORBextractor::operator() and ORBmatcher::SearchByProjection(Frame, Frame) through the compiled C++ drop-in classes
+    (host/orbx_cpp_latency.cc): what the reference's Tracking thread would wait for per frame."""
+    import synth
+    exe = os.path.join(ROOT, "host", "orbx_cpp_latency")
+    try:
+        if not os.path.exists(exe):
+            subprocess.run(["make", "-C", os.path.join(ROOT, "host"), "-s", "orbx_cpp_latency"], check=True, capture_output=True)
+        raw = f"/tmp/orbx_lat_{os.getpid()}.raw"
+        synth.frame(1000, W, H).tofile(raw)
+        r = subprocess.run([exe, raw, str(W), str(H), str(NFEAT), "200"], capture_output=True, text=True, timeout=120)
+        os.unlink(raw)
+        if r.returncode != 0:
+            return {"error": r.stderr.strip()[-200:]}
+        d = json.loads(r.stdout.strip().splitlines()[-1])
+        d["note"] = ("median wall time of the C++ classes (include/ORBextractor.h, include/ORBmatcher.h) on one host image / one frame pair: "
+                     "with_pyramid_mirror also downloads the eight bordered levels into mvImagePyramid, the reference's default surface")
+        return d
+    except Exception as e:  # the driver is a measurement aid, not part of the metric
+        return {"error": repr(e)[:200]}
+
+
 def run_orbx(args, rank, world):
     import torch
     import torch.distributed as dist
@@ -397,10 +519,17 @@ def run_orbx(args, rank, world):
     single_ms = float(np.median(lat[10:]))
 
     gm, gm_ms, popc_peak, gm_reps = hamming_gmatch(P, ex, dev)
+    me = match_e2e(P, ex)                                  # every rank matches its own keyframe pairs (jobs are independent)
+    stereo = stereo_pairs(P, local) if CONFIGS[CONFIG][4] else None
     if world > 1:
-        t = torch.tensor([gm], device=dev)
+        t = torch.tensor([gm, me["brute_force"]["pairs_per_s"], me["brute_force"]["gmatch_per_s"], me["bow"]["pairs_per_s"],
+                          me["bow"]["gmatch_per_s"], stereo["pairs_per_s"] if stereo else 0.0], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        gm_total = float(t.item())
+        gm_total = float(t[0].item())
+        for k, (a, b) in zip(("brute_force", "bow"), ((1, 2), (3, 4))):
+            me[k]["pairs_per_s_all_ranks"], me[k]["gmatch_per_s_all_ranks"] = float(t[a].item()), float(t[b].item())
+        if stereo:
+            stereo["pairs_per_s_all_ranks"] = float(t[5].item())
     else:
         gm_total = gm
 
@@ -418,15 +547,23 @@ def run_orbx(args, rank, world):
         launches_per_step = 7 if dom == "pyramid" else 1
         ach = alg[dom] * B / launches_per_step / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms > 0 else 0.0
         total_alg = sum(alg.values())
-        traffic = None
-        try:  # dram__bytes_read.sum + dram__bytes_write.sum per frame from the committed ncu --set full capture
-            tr = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
-            traffic = tr["bytes_per_frame"].get(dom) * B / launches_per_step
-        except Exception:
-            pass
+        traffic = alu_frac = None
+        traffic_src = None
+        for name in ("r2_traffic.json", "r1_traffic.json"):   # ncu cannot run inside a timed bench: the newest committed capture
+            try:  # dram__bytes_read.sum + dram__bytes_write.sum per frame of the dominant kernel (ncu --set full, tools/refresh_profiles.py)
+                tr = json.load(open(os.path.join(ROOT, "profiles", name)))
+                traffic = tr["bytes_per_frame"].get(dom) * B / launches_per_step
+                alu_frac = (tr.get("alu_pipe_pct") or {}).get(dom)
+                alu_frac = None if alu_frac is None else alu_frac / 100.0
+                traffic_src = "profiles/" + name
+                break
+            except Exception:
+                pass
         stage_ms = {k: round(v[0] / args.steps, 4) for k, v in stats.items() if v[0] > 0}
         os.sched_setaffinity(0, all_cpus)                  # the CPU baseline gets every host core again
         cores = len(all_cpus) or 1
+        lat = cpp_latency()
+        hcpu = hamming_cpu_baseline(cores)
         fps_all, n_all, dt_all, kind, note = cpu_baseline(frames[:8], cores, 8.0)
         cpu = {"value": fps_all, "unit": "frames/s", "cores": cores, "kind": kind,
                "sample": f"{n_all} frames of the same workload in {dt_all:.1f}s on {cores} host threads; {note}"}
@@ -440,11 +577,14 @@ def run_orbx(args, rank, world):
                                  else "no NUMA binding"),
                         "parallelism": f"frames sharded, {world} rank(s)" + (", NCCL all_gather of every step's results on a side stream, overlapped with the next step" if world > 1 else "")},
                 "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
-                             "traffic": traffic, "peak_source": "measured" if peaks else "fallback",
+                             "traffic": traffic, "traffic_source": traffic_src, "alu_frac": alu_frac,
+                             "peak_source": "measured" if peaks else "fallback",
                              "algorithmic_bytes_per_frame": alg[dom], "ms_per_launch": per_launch_ms,
                              "pipeline_frac": total_alg * value / world / 1e9 / hbm, "stage_ms_per_step": stage_ms},
                 "cpu_baseline": cpu,
+                "cpp_latency": lat,
                 "hamming": {"metric": "hamming_gmatch_per_s", "value": gm_total, "unit": "GMatch/s", "per_gpu": gm,
+                            "cpu_baseline": hcpu, "match_e2e": me,
                             "workload": "brute force 10000 x 10000 descriptors per keyframe pair, 32 pairs per GPU per call, device resident",
                             "ms_per_call": gm_ms, "calls": gm_reps,
                             "roofline": {"bound": "popc", "achieved": gm * 8.0, "peak": popc_peak / 1e9, "unit": "GPOPC32/s",
@@ -459,6 +599,16 @@ def run_orbx(args, rank, world):
                 "single_frame": {"latency_ms": single_ms, "note": "median of 50 orbx_extract calls, one 640x480 host image in, "
                                  "host keypoints + descriptors out (BASELINE.json configs[0])"},
                 "gpu_launches": int(launches), "clocks": sampler.summary()}
+        if stereo:
+            line["stereo"] = stereo
+        if CONFIG == "match":   # configs[3]: the Hamming core is the headline; the extraction numbers stay in the line as context
+            line["extraction"] = {k: line[k] for k in ("metric", "value", "unit", "ms_per_step", "roofline", "cpu_baseline", "e2e")}
+            bf = me["brute_force"]
+            line.update({"metric": "hamming_gmatch_per_s", "value": gm_total, "unit": "GMatch/s", "ms_per_step": gm_ms, "steps": gm_reps,
+                         "roofline": line["hamming"]["roofline"], "cpu_baseline": hcpu,
+                         "e2e": {"value": bf.get("gmatch_per_s_all_ranks", bf["gmatch_per_s"]), "unit": "GMatch/s",
+                                 "h2d_bytes_per_step": bf["h2d_bytes_per_pair"] * bf["pairs"], "d2h_bytes_per_step": bf["d2h_bytes_per_pair"] * bf["pairs"],
+                                 "note": "SearchByBoW(KeyFrame, Frame) with the full greedy semantics, host buffers in and out, brute-force mode"}})
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -470,9 +620,13 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--batch", type=int, default=1024)
+    ap.add_argument("--batch", type=int, default=0, help="frames per GPU per step (default: the config's)")
     ap.add_argument("--impl", default="orbx", choices=["orbx", "reference"])
+    ap.add_argument("--config", default="tum", choices=sorted(CONFIGS), help="BASELINE.json workload (the metric is quoted on tum)")
     args = ap.parse_args()
+    set_config(args.config)
+    if args.batch <= 0:
+        args.batch = CONFIGS[args.config][3]
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     if args.impl == "reference":

@@ -3,27 +3,32 @@
 #include "ORBextractor.h"
 #include "orbx.h"
 #include <cassert>
-#include <stdexcept>
-#include <string>
+#include <cstdio>
+#include <cstring>
 
 namespace ORB_SLAM2
 {
 
 static const int EDGE_THRESHOLD = 19; // src/ORBextractor.cc:81
 
-static void check(int rc, orbx_ctx* ctx, const char* what)
+// The reference's contract is "no exceptions, no return codes" (Tracking calls operator() from its own thread and checks
+// nothing): an error from the library is recorded, reported once on stderr and turned into "no keypoints".
+bool ORBextractor::Ok(int rc, const char* what)
 {
-    if (rc != ORBX_OK)
-        throw std::runtime_error(std::string(what) + ": " + orbx_strerror(rc) + " " + (ctx ? orbx_last_cuda_error(ctx) : ""));
+    if (rc == ORBX_OK) return true;
+    if (mnLastStatus == ORBX_OK)
+        fprintf(stderr, "ORBextractor: %s failed: %s %s\n", what, orbx_strerror(rc), mpCtx ? orbx_last_cuda_error(mpCtx) : "");
+    mnLastStatus = rc;
+    return false;
 }
 
 ORBextractor::ORBextractor(int _nfeatures, float _scaleFactor, int _nlevels, int _iniThFAST, int _minThFAST)
     : nfeatures(_nfeatures), scaleFactor(_scaleFactor), nlevels(_nlevels), iniThFAST(_iniThFAST), minThFAST(_minThFAST),
-      mpCtx(nullptr), mnDevice(0), mnMaxW(0), mnMaxH(0), mbMirrorPyramid(true)
+      mpCtx(nullptr), mnDevice(0), mnMaxW(0), mnMaxH(0), mbMirrorPyramid(true), mnLastStatus(0)
 {
     // The tables come from the library (same formulas as src/ORBextractor.cc:484-531) so that the getters,
     // which Frame's constructors copy (src/Frame.cc:128-140), agree bit for bit with what the kernels use.
-    EnsureContext(64, 64);
+    EnsureContext(64, 64);          // a failure (no CUDA device) is remembered in LastStatus(); operator() then returns nothing
 }
 
 ORBextractor::~ORBextractor() { if (mpCtx) orbx_destroy(mpCtx); }
@@ -36,18 +41,21 @@ void ORBextractor::SetDevice(int device)
     EnsureContext(64, 64);
 }
 
-void ORBextractor::EnsureContext(int w, int h)
+bool ORBextractor::EnsureContext(int w, int h)
 {
-    if (mpCtx && w <= mnMaxW && h <= mnMaxH) return;
+    if (mpCtx && w <= mnMaxW && h <= mnMaxH) return true;
     if (mpCtx) { orbx_destroy(mpCtx); mpCtx = nullptr; }
     mnMaxW = w > mnMaxW ? w : mnMaxW; mnMaxH = h > mnMaxH ? h : mnMaxH;
-    check(orbx_create(&mpCtx, mnDevice, nfeatures, (float)scaleFactor, nlevels, iniThFAST, minThFAST, mnMaxW, mnMaxH, 1), nullptr, "orbx_create");
-    mvScaleFactor.resize(nlevels); mvInvScaleFactor.resize(nlevels); mvLevelSigma2.resize(nlevels); mvInvLevelSigma2.resize(nlevels);
-    mnFeaturesPerLevel.resize(nlevels);
-    check(orbx_get_tables(mpCtx, mvScaleFactor.data(), mvInvScaleFactor.data(), mvLevelSigma2.data(), mvInvLevelSigma2.data(),
-                          mnFeaturesPerLevel.data()), mpCtx, "orbx_get_tables");
+    mvScaleFactor.assign(nlevels, 1.f); mvInvScaleFactor.assign(nlevels, 1.f); mvLevelSigma2.assign(nlevels, 1.f); mvInvLevelSigma2.assign(nlevels, 1.f);
+    mnFeaturesPerLevel.assign(nlevels, 0);
     mvImagePyramid.resize(nlevels);
     mvBordered.resize(nlevels);
+    if (!Ok(orbx_create(&mpCtx, mnDevice, nfeatures, (float)scaleFactor, nlevels, iniThFAST, minThFAST, mnMaxW, mnMaxH, 1), "orbx_create")) {
+        mpCtx = nullptr; mnMaxW = mnMaxH = 0;
+        return false;
+    }
+    return Ok(orbx_get_tables(mpCtx, mvScaleFactor.data(), mvInvScaleFactor.data(), mvLevelSigma2.data(), mvInvLevelSigma2.data(),
+                              mnFeaturesPerLevel.data()), "orbx_get_tables");
 }
 
 void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, std::vector<cv::KeyPoint>& _keypoints, cv::OutputArray _descriptors)
@@ -55,15 +63,16 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
     if (_image.empty()) return;                       // src/ORBextractor.cc:1547-1548
     cv::Mat image = _image.getMat();
     assert(image.type() == CV_8UC1);                  // :1553
-    EnsureContext(image.cols, image.rows);
+    if (!EnsureContext(image.cols, image.rows)) { _keypoints.clear(); _descriptors.release(); return; }
 
     const int cap = orbx_max_keypoints(mpCtx);
     _keypoints.resize(cap);
     cv::Mat desc(cap, 32, CV_8U);
     int n = 0;
     static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_keypoint), "cv::KeyPoint must be the 28-byte POD the kernels write");
-    check(orbx_extract(mpCtx, image.data, image.cols, image.rows, image.step, 0, reinterpret_cast<orbx_keypoint*>(_keypoints.data()),
-                       desc.data, cap, &n), mpCtx, "orbx_extract");
+    if (!Ok(orbx_extract(mpCtx, image.data, image.cols, image.rows, image.step, 0, reinterpret_cast<orbx_keypoint*>(_keypoints.data()),
+                         desc.data, cap, &n), "orbx_extract")) { _keypoints.clear(); _descriptors.release(); return; }
+    mnLastStatus = ORBX_OK;
     _keypoints.resize(n);
     if (n == 0) _descriptors.release();               // :1582
     else {
@@ -72,13 +81,18 @@ void ORBextractor::operator()(cv::InputArray _image, cv::InputArray /*_mask*/, s
         for (int i = 0; i < n; ++i) memcpy(out.ptr<unsigned char>(i), desc.ptr<unsigned char>(i), 32);
     }
     if (mbMirrorPyramid) {
+        // every level with its 19-px frame in one device pass and one copy; the Mats are views into one host block
+        std::vector<size_t> off(nlevels);
+        size_t total = 0;
+        if (!Ok(orbx_pyramid_bordered(mpCtx, 0, EDGE_THRESHOLD, 0, nullptr, 0, off.data(), &total), "orbx_pyramid_bordered")) return;
+        if (mvPyramidBlock.size() != total) mvPyramidBlock.resize(total);
+        if (!Ok(orbx_pyramid_bordered(mpCtx, 0, EDGE_THRESHOLD, 0, mvPyramidBlock.data(), total, off.data(), &total), "orbx_pyramid_bordered")) return;
         for (int level = 0; level < nlevels; ++level) {
             int w = 0, h = 0;
-            check(orbx_level_size(mpCtx, level, image.cols, image.rows, &w, &h), mpCtx, "orbx_level_size");
-            cv::Mat& temp = mvBordered[level];
-            temp.create(h + 2 * EDGE_THRESHOLD, w + 2 * EDGE_THRESHOLD, CV_8UC1);
-            check(orbx_pyramid_level(mpCtx, 0, level, EDGE_THRESHOLD, 0, temp.data, temp.step, nullptr, nullptr), mpCtx, "orbx_pyramid_level");
-            mvImagePyramid[level] = temp(cv::Rect(EDGE_THRESHOLD, EDGE_THRESHOLD, w, h)); // :1677,1704-1727
+            if (!Ok(orbx_level_size(mpCtx, level, image.cols, image.rows, &w, &h), "orbx_level_size")) return;
+            mvBordered[level] = cv::Mat(h + 2 * EDGE_THRESHOLD, w + 2 * EDGE_THRESHOLD, CV_8UC1, mvPyramidBlock.data() + off[level],
+                                        (size_t)(w + 2 * EDGE_THRESHOLD));
+            mvImagePyramid[level] = mvBordered[level](cv::Rect(EDGE_THRESHOLD, EDGE_THRESHOLD, w, h)); // :1677,1704-1727
         }
     }
 }

@@ -3,10 +3,11 @@
 // decision, claim, ratio test and rotation-histogram vote runs on the GPU (csrc/k_match.cu, csrc/k_project.cu).
 #include "ORBmatcher.h"
 #include "orbx.h"
+#include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
-#include <stdexcept>
-#include <string>
 
 namespace ORB_SLAM2
 {
@@ -20,10 +21,18 @@ struct CtxHolder {
     orbx_ctx* ctx = nullptr;
     ~CtxHolder() { if (ctx) orbx_destroy(ctx); }
 };
-void check(int rc, const char* what)
+// The reference's matchers neither throw nor return codes: a library error (no device, a CUDA failure) is recorded per
+// thread, reported once on stderr and turned into "no matches" (every result array is reset to its no-match state).
+thread_local int tlsLastStatus = ORBX_OK;
+thread_local int tlsDevice = -1;             // -1: env ORBX_DEVICE or 0
+bool ok(int rc, const char* what)
 {
-    if (rc != ORBX_OK) throw std::runtime_error(std::string(what) + ": " + orbx_strerror(rc));
+    if (rc == ORBX_OK) { tlsLastStatus = ORBX_OK; return true; }
+    if (tlsLastStatus == ORBX_OK) fprintf(stderr, "ORBmatcher: %s failed: %s\n", what, orbx_strerror(rc));
+    tlsLastStatus = rc;
+    return false;
 }
+template <typename V> void noMatch(V& v, int& n) { std::fill(v.begin(), v.end(), -1); n = 0; }
 static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_keypoint), "cv::KeyPoint must be the 28-byte POD the kernels read");
 
 // DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned>>) -> CSR in map order (ascending node id)
@@ -64,12 +73,24 @@ orbx_bow_side makeSide(const cv::Mat& desc, std::vector<uint8_t>& tmp, const std
 }
 } // namespace
 
+// One light context (a device and a stream, no extraction arenas: orbx_create_matcher) per calling thread: the reference
+// builds an ORBmatcher on the stack at every call site, from the tracking, mapping and loop-closing threads concurrently.
 orbx_ctx* ORBmatcher::Context()
 {
     static thread_local CtxHolder holder;
-    if (!holder.ctx) check(orbx_create(&holder.ctx, 0, 1000, 1.2f, 8, 20, 7, 64, 64, 1), "orbx_create (ORBmatcher)");
-    return holder.ctx;
+    static thread_local int holderDevice = -1;
+    int dev = tlsDevice;
+    if (dev < 0) { const char* e = getenv("ORBX_DEVICE"); dev = e ? atoi(e) : 0; }
+    if (holder.ctx && holderDevice != dev) { orbx_destroy(holder.ctx); holder.ctx = nullptr; }
+    if (!holder.ctx) {
+        if (!ok(orbx_create_matcher(&holder.ctx, dev), "orbx_create_matcher")) holder.ctx = nullptr;
+        holderDevice = dev;
+    }
+    return holder.ctx;                       // NULL after a failure: every orbx_* call then returns ORBX_E_INVALID
 }
+
+void ORBmatcher::SetDevice(int device) { tlsDevice = device; }
+int ORBmatcher::LastStatus() { return tlsLastStatus; }
 
 ORBmatcher::ORBmatcher(float nnratio, bool checkOri) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
 
@@ -95,8 +116,8 @@ int ORBmatcher::SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpM
     const orbx_bow_side s2 = makeSide(F.mDescriptors, t2, F.mvKeys, nullptr, nullptr, F.N, fvF);   // F.mvKeys[..].angle, :362
     std::vector<int32_t> match(F.N > 0 ? F.N : 1);
     int n = 0;
-    check(orbx_match_bow(Context(), ORBX_BOW_KF_FRAME, &s1, &s2, nullptr, mfNNratio, mbCheckOrientation, 0, match.data(), &n),
-          "orbx_match_bow");
+    if (!ok(orbx_match_bow(Context(), ORBX_BOW_KF_FRAME, &s1, &s2, nullptr, mfNNratio, mbCheckOrientation, 0, match.data(), &n),
+            "orbx_match_bow")) noMatch(match, n);
     for (int j = 0; j < F.N; ++j) if (match[j] >= 0) vpMapPointMatches[j] = vpMapPointsKF[match[j]];
     return n;
 }
@@ -114,8 +135,8 @@ int ORBmatcher::SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint
     const orbx_bow_side s2 = makeSide(pKF2->mDescriptors, t2, pKF2->mvKeysUn, &has2, nullptr, pKF2->N, fv2);
     std::vector<int32_t> match(pKF1->N > 0 ? pKF1->N : 1);
     int n = 0;
-    check(orbx_match_bow(Context(), ORBX_BOW_KF_KF, &s1, &s2, nullptr, mfNNratio, mbCheckOrientation, 0, match.data(), &n),
-          "orbx_match_bow");
+    if (!ok(orbx_match_bow(Context(), ORBX_BOW_KF_KF, &s1, &s2, nullptr, mfNNratio, mbCheckOrientation, 0, match.data(), &n),
+            "orbx_match_bow")) noMatch(match, n);
     for (int i = 0; i < pKF1->N; ++i) if (match[i] >= 0) vpMatches12[i] = vpMapPoints2[match[i]];
     return n;
 }
@@ -146,8 +167,8 @@ int ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F
     const orbx_bow_side s2 = makeSide(pKF2->mDescriptors, t2, pKF2->mvKeysUn, &has2, &pKF2->mvuRight, pKF2->N, fv2);
     std::vector<int32_t> match(pKF1->N > 0 ? pKF1->N : 1);
     int n = 0;
-    check(orbx_match_bow(Context(), ORBX_BOW_TRIANGULATE, &s1, &s2, &tri, mfNNratio, mbCheckOrientation, 0, match.data(), &n),
-          "orbx_match_bow");
+    if (!ok(orbx_match_bow(Context(), ORBX_BOW_TRIANGULATE, &s1, &s2, &tri, mfNNratio, mbCheckOrientation, 0, match.data(), &n),
+            "orbx_match_bow")) noMatch(match, n);
     vMatchedPairs.clear();
     vMatchedPairs.reserve(n);
     for (int i = 0; i < pKF1->N; ++i) if (match[i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)match[i])); // :1116-1124
@@ -174,10 +195,10 @@ int projectionSearch(orbx_ctx* ctx, Frame& F, const std::vector<orbx_proj_query>
     std::vector<int32_t> assign(F.N > 0 ? F.N : 1);
     int n = 0;
     const bool stereo = !F.mvuRight.empty() && !anyPointOccupies;   // the relocalisation overload has no uright gate
-    check(orbx_search_by_projection(ctx, q.data(), (int)q.size(), reinterpret_cast<const orbx_keypoint*>(F.mvKeysUn.data()),
-                                    contiguous(F.mDescriptors, tmp), stereo ? F.mvuRight.data() : nullptr, F.N, &g, occupied.data(),
-                                    modeFlags | (stereo ? ORBX_PROJ_CHECK_URIGHT : 0), thDist, nnratio, checkOri ? 1 : 0, 0,
-                                    assign.data(), &n), "orbx_search_by_projection");
+    if (!ok(orbx_search_by_projection(ctx, q.data(), (int)q.size(), reinterpret_cast<const orbx_keypoint*>(F.mvKeysUn.data()),
+                                      contiguous(F.mDescriptors, tmp), stereo ? F.mvuRight.data() : nullptr, F.N, &g, occupied.data(),
+                                      modeFlags | (stereo ? ORBX_PROJ_CHECK_URIGHT : 0), thDist, nnratio, checkOri ? 1 : 0, 0,
+                                      assign.data(), &n), "orbx_search_by_projection")) noMatch(assign, n);
     for (int i = 0; i < F.N; ++i) if (assign[i] >= 0) F.mvpMapPoints[i] = src[assign[i]];
     return n;
 }
@@ -355,9 +376,9 @@ int ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector
                          pKF->mnGridCols, pKF->mnGridRows};
     std::vector<int32_t> assign(pKF->N > 0 ? pKF->N : 1);
     int n = 0;
-    check(orbx_search_by_projection(Context(), q.data(), (int)q.size(), reinterpret_cast<const orbx_keypoint*>(pKF->mvKeysUn.data()),
-                                    contiguous(pKF->mDescriptors, tmp), nullptr, pKF->N, &g, occupied.data(), 0, TH_LOW, mfNNratio, 0, 0,
-                                    assign.data(), &n), "orbx_search_by_projection");
+    if (!ok(orbx_search_by_projection(Context(), q.data(), (int)q.size(), reinterpret_cast<const orbx_keypoint*>(pKF->mvKeysUn.data()),
+                                      contiguous(pKF->mDescriptors, tmp), nullptr, pKF->N, &g, occupied.data(), 0, TH_LOW, mfNNratio, 0, 0,
+                                      assign.data(), &n), "orbx_search_by_projection")) noMatch(assign, n);
     for (int i = 0; i < pKF->N; ++i) if (assign[i] >= 0) vpMatched[i] = src[assign[i]];                      // :554
     return n;
 }
@@ -372,11 +393,11 @@ int ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Po
     std::vector<uint8_t> t1, t2;
     const orbx_grid g = {Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv, Frame::mfGridElementHeightInv, FRAME_GRID_COLS, FRAME_GRID_ROWS};
     int n = 0;
-    check(orbx_search_for_initialization(Context(), reinterpret_cast<const orbx_keypoint*>(F1.mvKeysUn.data()), contiguous(F1.mDescriptors, t1),
-                                         n1, reinterpret_cast<float*>(vbPrevMatched.data()),
-                                         reinterpret_cast<const orbx_keypoint*>(F2.mvKeysUn.data()), contiguous(F2.mDescriptors, t2), n2, &g,
-                                         windowSize, mfNNratio, mbCheckOrientation ? 1 : 0, 0, vnMatches12.data(), &n),
-          "orbx_search_for_initialization");
+    if (!ok(orbx_search_for_initialization(Context(), reinterpret_cast<const orbx_keypoint*>(F1.mvKeysUn.data()), contiguous(F1.mDescriptors, t1),
+                                           n1, reinterpret_cast<float*>(vbPrevMatched.data()),
+                                           reinterpret_cast<const orbx_keypoint*>(F2.mvKeysUn.data()), contiguous(F2.mDescriptors, t2), n2, &g,
+                                           windowSize, mfNNratio, mbCheckOrientation ? 1 : 0, 0, vnMatches12.data(), &n),
+            "orbx_search_for_initialization")) noMatch(vnMatches12, n);
     return n;
 }
 
@@ -393,9 +414,10 @@ void keyFrameWindowBest(orbx_ctx* ctx, KeyFrame* pKF, const std::vector<orbx_pro
     for (size_t l = 0; l < pKF->mvInvLevelSigma2.size() && l < (size_t)ORBX_MAX_LEVELS; ++l) invSigma2[l] = pKF->mvInvLevelSigma2[l];
     const orbx_grid g = {(float)pKF->mnMinX, (float)pKF->mnMinY, pKF->mfGridElementWidthInv, pKF->mfGridElementHeightInv,
                          pKF->mnGridCols, pKF->mnGridRows};
-    check(orbx_window_best(ctx, q.data(), (int)q.size(), reinterpret_cast<const orbx_keypoint*>(pKF->mvKeysUn.data()),
-                           contiguous(pKF->mDescriptors, tmp), pKF->mvuRight.empty() ? nullptr : pKF->mvuRight.data(), pKF->N, &g,
-                           reprojGate ? invSigma2 : nullptr, thDist, 0, bestIdx.data(), bestDist.data()), "orbx_window_best");
+    if (!ok(orbx_window_best(ctx, q.data(), (int)q.size(), reinterpret_cast<const orbx_keypoint*>(pKF->mvKeysUn.data()),
+                             contiguous(pKF->mDescriptors, tmp), pKF->mvuRight.empty() ? nullptr : pKF->mvuRight.data(), pKF->N, &g,
+                             reprojGate ? invSigma2 : nullptr, thDist, 0, bestIdx.data(), bestDist.data()), "orbx_window_best"))
+        std::fill(bestIdx.begin(), bestIdx.end(), -1);          // nothing found: Fuse / SearchBySim3 then change nothing
 }
 
 // project a world point with (R, t) and the KeyFrame's intrinsics; the gates shared by Fuse x2 (:1166-1222, :1345-1395)

@@ -21,6 +21,10 @@ int main(int argc, char** argv)
         cv::Mat desc;
         ex(im, cv::Mat(), keys, desc);
         ex(im, cv::Mat(), keys, desc); // second call: context reuse
+        if (ex.LastStatus() != 0) {       // the class itself never throws; the driver reports what it recorded
+            fprintf(stderr, "ORBextractor::LastStatus() = %d, %d keypoints, descriptors %s\n", ex.LastStatus(), (int)keys.size(), desc.empty() ? "released" : "kept");
+            return 3;
+        }
         FILE* o = fopen(argv[5], "wb");
         int n = (int)keys.size(), L = ex.GetLevels();
         fwrite(&n, 4, 1, o);

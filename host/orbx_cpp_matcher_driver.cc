@@ -268,5 +268,9 @@ int main(int argc, char** argv)
         }
     } catch (const std::exception& e) { fprintf(stderr, "error: %s\n", e.what()); return 1; }
     fclose(o);
+    if (ORBmatcher::LastStatus() != 0) {  // the class itself never throws; the driver reports what it recorded
+        fprintf(stderr, "ORBmatcher::LastStatus() = %d\n", ORBmatcher::LastStatus());
+        return 3;
+    }
     return 0;
 }

@@ -2,8 +2,8 @@
 // same namespace, class name, constructor, operator(), getters and public mvImagePyramid
 // (reference include/ORBextractor.h:75-158), so src/Frame.cc:128-153,430-443 and src/Tracking.cc:166-190
 // compile and behave unchanged.  The work is done by hand-written sm_100a CUDA kernels behind the C ABI in
-// include/orbx.h (liborbx.so); this class is host glue only.  There is no CPU fallback: constructing an
-// extractor without a CUDA device throws std::runtime_error.
+// include/orbx.h (liborbx.so); this class is host glue only.  There is no CPU fallback and, like the reference, no
+// exception: without a CUDA device every operator() call returns no keypoints and LastStatus() says why.
 #ifndef ORBEXTRACTOR_H
 #define ORBEXTRACTOR_H
 
@@ -44,9 +44,14 @@ public:
     void SetHostPyramidMirror(bool on) { mbMirrorPyramid = on; }
     void SetDevice(int device);            // must be called before the first operator(); default device 0
     orbx_ctx* Context() { return mpCtx; }  // for orbx_stereo_match / orbx_match_* calls
+    // Like the reference, nothing here throws or returns a code (src/ORBextractor.cc:1547-1553 returns silently).  When the
+    // library reports an error (no device, a CUDA failure) the call leaves `keypoints` empty and `descriptors` released,
+    // prints one line to stderr the first time, and keeps the status here (0 = ORBX_OK) until the next successful call.
+    int LastStatus() const { return mnLastStatus; }
 
 protected:
-    void EnsureContext(int w, int h);
+    bool EnsureContext(int w, int h);
+    bool Ok(int rc, const char* what);
 
     int nfeatures;
     double scaleFactor;
@@ -62,7 +67,9 @@ protected:
     orbx_ctx* mpCtx;
     int mnDevice, mnMaxW, mnMaxH;
     bool mbMirrorPyramid;
-    std::vector<cv::Mat> mvBordered; // owners of the bordered level images
+    std::vector<cv::Mat> mvBordered; // the bordered level images: views into mvPyramidBlock
+    std::vector<unsigned char> mvPyramidBlock; // all bordered levels of the last frame, back to back (one copy per frame)
+    int mnLastStatus;
 };
 
 } // namespace ORB_SLAM2

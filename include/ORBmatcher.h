@@ -55,6 +55,11 @@ public:
     // the per-thread CUDA context the matcher calls run on (matchers are constructed on the stack at every call site and
     // used from the tracking, mapping and loop-closing threads concurrently)
     static orbx_ctx* Context();
+    // ---- additions (not in the reference) ----
+    static void SetDevice(int device);   // CUDA device of the calling thread's context (default: env ORBX_DEVICE, else 0)
+    // Like the reference, no method throws or returns a code.  A library error (no device, a CUDA failure) makes the call
+    // report no matches, prints one line to stderr, and is kept here per thread (0 = ORBX_OK) until a call succeeds.
+    static int LastStatus();
 
 protected:
     float RadiusByViewingCos(const float& viewCos);

@@ -40,6 +40,11 @@ enum { ORBX_IN_DEVICE = 1, ORBX_OUT_DEVICE = 2 }; /* flags: where image / result
 /* ---- lifetime.  Replaces ORBextractor::ORBextractor, src/ORBextractor.cc:471-579 ---- */
 int orbx_create(orbx_ctx** out, int device, int nfeatures, float scale_factor, int nlevels,
                 int ini_th_fast, int min_th_fast, int max_w, int max_h, int max_batch);
+/* A light context for the matcher entry points (orbx_hamming_*, orbx_match_bow*, orbx_search_*, orbx_window_best,
+ * orbx_assign_grid, orbx_distinctive_descriptors, orbx_bow_*, orbx_vocab_*): a device and a stream, no extraction arenas.
+ * The reference constructs an ORBmatcher on the stack at every call site (src/Tracking.cc:1356, src/LocalMapping.cc:...),
+ * so the drop-in keeps one of these per thread.  Extraction calls on it return ORBX_E_CAPACITY. */
+int orbx_create_matcher(orbx_ctx** out, int device);
 void orbx_destroy(orbx_ctx* ctx);
 const char* orbx_strerror(int status);
 const char* orbx_last_cuda_error(const orbx_ctx* ctx);
@@ -72,6 +77,12 @@ int orbx_extract_batch(orbx_ctx* ctx, const uint8_t* imgs, int batch, int w, int
  * dst is host memory unless flags has ORBX_OUT_DEVICE. */
 int orbx_pyramid_level(orbx_ctx* ctx, int frame, int level, int border, int flags, uint8_t* dst,
                        size_t dst_stride, int* w, int* h);
+/* All levels of frame `frame` of the LAST extract call at once, each with its reflect-101 frame of `border` pixels, packed
+ * back to back: level l starts at offsets[l] (nlevels entries, bytes) with rows of w_l + 2 * border bytes -- the memory
+ * behind ORBextractor::mvImagePyramid (src/ORBextractor.cc:1674-1727) in one kernel, one copy and one synchronisation
+ * (orbx_pyramid_level costs one of each per level).  dst == NULL: sizing call, fills offsets[] and *total_bytes only. */
+int orbx_pyramid_bordered(orbx_ctx* ctx, int frame, int border, int flags, uint8_t* dst, size_t dst_bytes, size_t* offsets,
+                          size_t* total_bytes);
 int orbx_level_size(const orbx_ctx* ctx, int level, int w0, int h0, int* w, int* h);
 
 /* Colour to gray in front of the extractor.  Replaces the cvtColor calls of Tracking::GrabImageStereo / RGBD / Monocular

@@ -293,6 +293,39 @@ int ref_shim_algebra(int op, const float* A, int ar, int ac, const float* B, int
 double ref_shim_norm(const float* a, int n) { return cv::norm(cv::Mat(n, 1, CV_32F, (void*)a)); }
 double ref_shim_dot(const float* a, const float* b, int n) { return cv::Mat(n, 1, CV_32F, (void*)a).dot(cv::Mat(n, 1, CV_32F, (void*)b)); }
 
+// CPU baseline of the Hamming core: the reference's inner matching loop (src/ORBmatcher.cc:325-345: best / second-best
+// ORBmatcher::DescriptorDistance over the candidates of one vocabulary node; with one node holding everything this is the
+// brute-force mode of configs[3]) on `threads` host threads, queries dealt round-robin.  The rows are taken the way the
+// reference takes them (`const cv::Mat& d = descriptors.row(idx)` per candidate) and the distance function is the
+// reference's own.  Returns descriptor-pair evaluations per second; best_idx / best_dist / second_dist as the loop leaves them.
+double ref_hamming_throughput(const uint8_t* q, int nq, const uint8_t* t, int nt, int threads, int32_t* best_idx, int32_t* best_dist,
+                              int32_t* second_dist)
+{
+    cv::Mat Q0(nq, 32, CV_8U, (void*)q), T0(nt, 32, CV_8U, (void*)t);
+    std::vector<std::thread> pool;
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int th = 0; th < threads; ++th)
+        pool.emplace_back([&, th]() {
+            // every thread owns its descriptor matrices, as every thread of the reference works on its own keyframe pair:
+            // row() bumps the matrix's reference count, which threads sharing one cv::Mat would fight over
+            const cv::Mat Q = Q0.clone(), T = T0.clone();
+            for (int i = th; i < nq; i += threads) {
+                const cv::Mat& dKF = Q.row(i);
+                int bestDist1 = 256, bestIdxF = -1, bestDist2 = 256;
+                for (int j = 0; j < nt; ++j) {
+                    const cv::Mat& dF = T.row(j);
+                    const int dist = ORBmatcher::DescriptorDistance(dKF, dF);
+                    if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdxF = j; }
+                    else if (dist < bestDist2) bestDist2 = dist;
+                }
+                if (best_idx) { best_idx[i] = bestIdxF; best_dist[i] = bestDist1; second_dist[i] = bestDist2; }
+            }
+        });
+    for (auto& th : pool) th.join();
+    const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return (double)nq * (double)nt / sec;
+}
+
 int ref_descriptor_distance(const uint8_t* a, const uint8_t* b)
 {
     cv::Mat A(1, 32, CV_8U, (void*)a), B(1, 32, CV_8U, (void*)b);

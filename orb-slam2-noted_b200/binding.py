@@ -60,6 +60,8 @@ def lib():
     L.orbx_cvt_gray.argtypes = [vp, vp, ci, ci, sz, ci, ci, vp, sz]
     L.orbx_undistort_keypoints.argtypes = [vp, vp, ci, cf, cf, cf, cf, vp, ci, ci, vp]
     L.orbx_hamming_best2.argtypes = [vp, vp, ci, vp, ci, vp, vp, vp, vp, ci, vp, ci, vp, vp, vp]
+    L.orbx_pyramid_bordered.argtypes = [vp, ci, ci, ci, vp, sz, vp, vp]
+    L.orbx_create_matcher.argtypes = [ctypes.POINTER(vp), ci]
     L.orbx_hamming_best2_static.argtypes = L.orbx_hamming_best2.argtypes      # the no-allocation variant (include/orbx.h)
     L.orbx_test_sincosf.argtypes = [ctypes.c_uint32, ctypes.c_uint32, vp, vp]
     L.orbx_test_fast_atan2.argtypes = [vp, ci, vp]
@@ -211,6 +213,24 @@ class ORBextractor:
         out = np.empty((h.value + 2 * border, w.value + 2 * border), np.uint8)
         self._check(self._lib.orbx_pyramid_level(self._h, frame, level, border, 0, _np(out), out.strides[0], ctypes.byref(w),
                                                  ctypes.byref(h)), "orbx_pyramid_level")
+        return out
+
+    def pyramid_bordered(self, frame=0, border=19):
+        """All levels of one frame of the last call with their reflect-101 frame (mvImagePyramid's memory), one device pass:
+        list of (h + 2 border, w + 2 border) uint8 views into one block."""
+        n = self.nlevels
+        off = (ctypes.c_size_t * n)()
+        total = ctypes.c_size_t()
+        self._check(self._lib.orbx_pyramid_bordered(self._h, frame, border, 0, None, 0, off, ctypes.byref(total)), "orbx_pyramid_bordered")
+        block = np.empty(total.value, np.uint8)
+        self._check(self._lib.orbx_pyramid_bordered(self._h, frame, border, 0, _np(block), block.size, off, ctypes.byref(total)),
+                    "orbx_pyramid_bordered")
+        out = []
+        for l in range(n):
+            w, h = ctypes.c_int(), ctypes.c_int()
+            self._check(self._lib.orbx_level_size(self._h, l, *self._last_wh, ctypes.byref(w), ctypes.byref(h)), "orbx_level_size")
+            ow, oh = w.value + 2 * border, h.value + 2 * border
+            out.append(block[off[l]:off[l] + ow * oh].reshape(oh, ow))
         return out
 
     # ---- instrumentation ----

@@ -372,6 +372,54 @@ __global__ void borderCopyKernel(const uint8_t* __restrict__ src, int w, int h, 
     dst[(size_t)y * dpitch + x] = src[(size_t)sy * pitch + sx];
 }
 
+// All levels of one frame with their reflect-101 frame in ONE launch, packed back to back (level l at off[l], row pitch
+// w_l + 2 * border): what ORBextractor::mvImagePyramid holds after operator() (src/ORBextractor.cc:1674-1727).  4 output bytes
+// per thread; grid.z = level.
+struct BorderedLevels { const uint8_t* src[kMaxLevels]; unsigned long long pitch[kMaxLevels]; int w[kMaxLevels], h[kMaxLevels];
+                        unsigned long long off[kMaxLevels]; };
+__global__ void __launch_bounds__(128)
+borderedPyramidKernel(const __grid_constant__ BorderedLevels L, uint8_t* __restrict__ dst, int border)
+{
+    const int l = blockIdx.z, w = L.w[l], h = L.h[l];
+    const int ow = w + 2 * border, oh = h + 2 * border;
+    const int y = blockIdx.y, x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (y >= oh || x0 >= ow) return;
+    int sy = y - border;
+    if (h == 1) sy = 0; else { while (sy < 0 || sy >= h) sy = sy < 0 ? -sy : 2 * (h - 1) - sy; }
+    const uint8_t* S = L.src[l] + (size_t)sy * L.pitch[l];
+    uint8_t* D = dst + L.off[l] + (size_t)y * ow + x0;
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (x0 + i >= ow) break;
+        int sx = x0 + i - border;
+        if (w == 1) sx = 0; else { while (sx < 0 || sx >= w) sx = sx < 0 ? -sx : 2 * (w - 1) - sx; }
+        D[i] = S[sx];
+    }
+}
+
+int launchBorderedPyramid(Ctx* c, int frame, int border, uint8_t* dst, size_t* offsets, size_t* total)
+{
+    const GeomSet& g = c->geom;
+    BorderedLevels L;
+    size_t off = 0; int maxW = 0, maxH = 0;
+    for (int l = 0; l < g.nlevels; ++l) {
+        const LevelGeom& q = g.lv[l];
+        if (l == 0) { L.src[l] = c->lvl0 + (size_t)frame * c->lvl0FrameStride; L.pitch[l] = c->lvl0Pitch; }
+        else { L.src[l] = c->dPyr + q.planeOff + (size_t)frame * q.pitch * q.h; L.pitch[l] = (unsigned long long)q.pitch; }
+        L.w[l] = q.w; L.h[l] = q.h; L.off[l] = off;
+        if (offsets) offsets[l] = off;
+        off += (size_t)(q.w + 2 * border) * (q.h + 2 * border);
+        maxW = std::max(maxW, q.w + 2 * border); maxH = std::max(maxH, q.h + 2 * border);
+    }
+    if (total) *total = off;
+    if (!dst) return ORBX_OK;
+    dim3 grid((maxW + 511) / 512, maxH, g.nlevels), block(128);
+    borderedPyramidKernel<<<grid, block, 0, c->stream>>>(L, dst, border);
+    c->kernelLaunches++;
+    ORBX_CUDA(c, cudaGetLastError());
+    return ORBX_OK;
+}
+
 int launchBorderCopy(Ctx* c, const uint8_t* src, int w, int h, size_t pitch, uint8_t* dst, size_t dpitch, int border)
 {
     dim3 grid((w + 2 * border + 127) / 128, h + 2 * border), block(128);

@@ -311,6 +311,26 @@ int orbx_create(orbx_ctx** out, int device, int nfeatures, float scale_factor, i
     return ORBX_OK;
 }
 
+// A context for the matcher entry points only: a device, a stream and (grown on demand) the matcher scratch; no pyramid,
+// candidate or keypoint arenas, no geometry.  Extraction calls on it fail with ORBX_E_CAPACITY (max_w = max_h = 0).
+int orbx_create_matcher(orbx_ctx** out, int device)
+{
+    if (!out) return ORBX_E_INVALID;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return ORBX_E_CUDA; // no CPU fallback
+    orbx_ctx* h = new (std::nothrow) orbx_ctx();
+    if (!h) return ORBX_E_NOMEM;
+    Ctx* c = &h->c;
+    c->device = device; c->nlevels = 1; c->scaleFactor = 1.2f; c->scale[0] = c->invScale[0] = c->sigma2[0] = c->invSigma2[0] = 1.0f;
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        orbx_destroy(h);
+        return ORBX_E_CUDA;
+    }
+    *out = h;
+    return ORBX_OK;
+}
+
 void orbx_destroy(orbx_ctx* h)
 {
     if (!h) return;
@@ -520,9 +540,26 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
         const int f0 = cuts[i], n = cuts[i + 1] - f0;
         c->stream = (twoStreams && (i & 1)) ? c->stream2 : mainStream;   // launchers enqueue on c->stream
         if (!inDev) {
-            if (frame_stride == stride * (size_t)hgt || n == 1) {
-                ORBX_CUDA(c, cudaMemcpy2DAsync(d0 + (size_t)f0 * dp * hgt, dp, imgs + (size_t)f0 * frame_stride, stride, (size_t)w,
-                                               (size_t)hgt * n, cudaMemcpyHostToDevice, c->sIn));
+            if ((frame_stride == stride * (size_t)hgt || n == 1) && stride == dp) {
+                // both sides are one contiguous block: a plain 1-D copy.  (cudaMemcpy2DAsync with equal pitches still runs as a
+                // strided DMA, one descriptor per row: 6 GB/s for 752-byte rows against 49 GB/s for the flat copy.)
+                ORBX_CUDA(c, cudaMemcpyAsync(d0 + (size_t)f0 * dp * hgt, imgs + (size_t)f0 * frame_stride, dp * (size_t)hgt * n,
+                                             cudaMemcpyHostToDevice, c->sIn));
+            } else if (frame_stride == stride * (size_t)hgt || n == 1) {
+                // rows of the caller's images and of the arena differ in pitch (e.g. 1241 -> 1248): the chunk crosses PCIe as one
+                // flat block into a staging buffer and is repacked on the device, on the same copy stream (so the buffer is free
+                // again before the next chunk's copy starts)
+                const size_t bytes = stride * (size_t)hgt * n;
+                if (bytes > c->dInBytes) {
+                    ORBX_CUDA(c, cudaStreamSynchronize(c->sIn));
+                    if (c->dIn) cudaFree(c->dIn);
+                    c->dIn = nullptr; c->dInBytes = 0;
+                    ORBX_CUDA(c, cudaMalloc(&c->dIn, bytes));
+                    c->dInBytes = bytes;
+                }
+                ORBX_CUDA(c, cudaMemcpyAsync(c->dIn, imgs + (size_t)f0 * frame_stride, bytes, cudaMemcpyHostToDevice, c->sIn));
+                ORBX_CUDA(c, cudaMemcpy2DAsync(d0 + (size_t)f0 * dp * hgt, dp, c->dIn, stride, (size_t)w, (size_t)hgt * n,
+                                               cudaMemcpyDeviceToDevice, c->sIn));
             } else {
                 for (int b = f0; b < f0 + n; ++b)
                     ORBX_CUDA(c, cudaMemcpy2DAsync(d0 + (size_t)b * dp * hgt, dp, imgs + (size_t)b * frame_stride, stride, (size_t)w,
@@ -638,6 +675,31 @@ int orbx_extract(orbx_ctx* h, const uint8_t* img, int w, int hgt, size_t stride,
                  uint8_t* desc, int cap, int* n_out)
 {
     return orbx_extract_batch(h, img, 1, w, hgt, stride, stride * (size_t)(hgt > 0 ? hgt : 0), flags, kps, desc, cap, n_out);
+}
+
+// Every level of `frame` with its border, packed: level l starts at offsets[l] (bytes), rows of w_l + 2 * border bytes.
+// dst == NULL: only offsets[] and *total_bytes are filled (sizing call).  One kernel, one copy, one synchronisation.
+int orbx_pyramid_bordered(orbx_ctx* h, int frame, int border, int flags, uint8_t* dst, size_t dst_bytes, size_t* offsets, size_t* total_bytes)
+{
+    if (!h) return ORBX_E_INVALID;
+    Ctx* c = &h->c;
+    if (c->curW <= 0 || border < 0 || border > 64) return ORBX_E_INVALID;
+    size_t total = 0;
+    int rc = launchBorderedPyramid(c, 0, border, nullptr, offsets, &total);
+    if (rc) return rc;
+    if (total_bytes) *total_bytes = total;
+    if (!dst) return ORBX_OK;
+    if (frame < 0 || frame >= c->lastBatch) return ORBX_E_INVALID;
+    if (dst_bytes < total) return ORBX_E_CAPACITY;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    if (flags & ORBX_OUT_DEVICE) return launchBorderedPyramid(c, frame, border, dst, nullptr, nullptr);
+    if ((rc = ensureScratch(c, total))) return rc;
+    if ((rc = ensureMatchPinned(c, total))) return rc;
+    if ((rc = launchBorderedPyramid(c, frame, border, (uint8_t*)c->dScratch, nullptr, nullptr))) return rc;
+    ORBX_CUDA(c, cudaMemcpyAsync(c->hMatch, c->dScratch, total, cudaMemcpyDeviceToHost, c->stream));   // pinned landing zone
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    memcpy(dst, c->hMatch, total);
+    return ORBX_OK;
 }
 
 int orbx_pyramid_level(orbx_ctx* h, int frame, int level, int border, int flags, uint8_t* dst, size_t dst_stride, int* w, int* hh)

@@ -155,6 +155,7 @@ void buildFastStrips(const GeomSet& g, std::vector<StripDesc>& out);
 int launchOctree(Ctx* c, int frame0, int batch);
 int launchBlur(Ctx* c, int frame0, int batch);
 int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN);
+int launchBorderedPyramid(Ctx* c, int frame, int border, uint8_t* dst, size_t* offsets, size_t* total);   // dst == NULL: sizes only
 int launchBorderCopy(Ctx* c, const uint8_t* src, int w, int h, size_t pitch, uint8_t* dst, size_t dpitch, int border);
 
 } // namespace orbx

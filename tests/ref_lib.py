@@ -45,6 +45,8 @@ def lib():
         L.ref_vocab_score.argtypes = [vp, vp, vp, ci, vp, vp, ci]
         L.ref_vocab_score.restype = cd
         L.ref_descriptor_distance.argtypes = [vp, vp]
+        L.ref_hamming_throughput.argtypes = [vp, ci, vp, ci, ci, vp, vp, vp]
+        L.ref_hamming_throughput.restype = cd
         L.ref_shim_algebra.argtypes = [ci, vp, ci, ci, vp, ci, ci, vp, vp]
         L.ref_shim_norm.argtypes = [vp, ci]
         L.ref_shim_norm.restype = cd

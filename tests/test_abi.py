@@ -49,3 +49,36 @@ def test_product_never_references_oracle():
                 txt = open(os.path.join(dp, f), errors="ignore").read()
                 for b in bad:
                     assert b not in txt, (f, b)
+
+
+def test_cpp_dropins_never_throw_without_a_device(tmp_path):
+    """Reference contract (SURVEY 8b): no exceptions, no return codes.  Without a CUDA device ORBextractor::operator() returns no
+    keypoints and releases the descriptors, every ORBmatcher method reports no matches; LastStatus() carries the reason and one
+    line goes to stderr.  The drivers exit 3 (their own convention for a recorded status), never through std::terminate."""
+    if has_gpu():
+        pytest.skip("GPU present")
+    import subprocess
+    import numpy as np
+    import matcher_scene
+    import __graft_entry__ as ge
+    ge.build()
+    subprocess.run(["make", "-C", os.path.join(ROOT, "host"), "-s"], check=True)
+    raw = tmp_path / "in.raw"
+    np.zeros((480, 640), np.uint8).tofile(raw)
+    r = subprocess.run([os.path.join(ROOT, "host", "orbx_cpp_driver"), str(raw), "640", "480", "1000", str(tmp_path / "o.bin")],
+                       capture_output=True, text=True)
+    assert r.returncode == 3, (r.returncode, r.stderr)
+    assert "ORBextractor: orbx_create failed" in r.stderr and "0 keypoints, descriptors released" in r.stderr
+    assert "terminate" not in r.stderr and r.stderr.count("ORBextractor: ") == 1            # reported once, not per call
+
+    def run(i, o):
+        r = subprocess.run([os.path.join(ROOT, "host", "orbx_cpp_matcher_driver"), i, o], capture_output=True, text=True)
+        assert r.returncode == 3 and "ORBmatcher: orbx_create_matcher failed" in r.stderr and "terminate" not in r.stderr, (r.returncode, r.stderr)
+    try:
+        matcher_scene.check_scene(run, tmp_path, 12, 300, 280)
+    except AssertionError:
+        pass                                                    # the expectations cannot hold without matches; the records must still be there
+    out = matcher_scene._read_all(tmp_path / "m_out.bin")
+    assert len(out) == 28
+    assert all(int(np.frombuffer(out[i], np.int32)[0]) == 0 for i in (0, 2, 4, 6, 9, 11, 13, 16, 19, 22, 24, 26))   # nmatches == 0 everywhere
+    assert all(np.all(np.frombuffer(out[i], np.int32) == -1) for i in (1, 3, 5, 7, 10, 12, 14, 25, 27))             # nothing assigned

@@ -43,6 +43,44 @@ def test_pyramid_levels_bit_exact(P):
         assert np.array_equal(ex.pyramid_level(l, border=19), O.border(want, 19)), ("border", l)
 
 
+def test_bordered_pyramid_in_one_pass_and_matcher_context(P):
+    """orbx_pyramid_bordered (what the C++ class mirrors into mvImagePyramid) == the per-level call, for a frame in the middle
+    of a batch and an unaligned width; and orbx_create_matcher gives a context on which matcher calls work and extraction
+    calls are refused."""
+    import ctypes
+    for w, h, nf in ((640, 480, 1000), (333, 251, 700)):
+        imgs = np.stack([synth.frame(40 + i, w, h) for i in range(3)])
+        ex = P.ORBextractor(nf, 1.2, 8, 20, 7, max_w=w, max_h=h, max_batch=3)
+        ex.extract_batch(imgs)
+        for frame in (0, 2):
+            got = ex.pyramid_bordered(frame, 19)
+            for l in range(8):
+                assert np.array_equal(got[l], ex.pyramid_level(l, frame=frame, border=19)), (w, frame, l)
+        p = O.params(nf)
+        _, _, pyr = O.extract(p, imgs[2], want_pyr=True)
+        lw, lh = O.level_sizes(p, w, h)[0]
+        assert np.array_equal(ex.pyramid_bordered(2, 19)[0], O.border(pyr[:lw * lh].reshape(lh, lw), 19))
+    L = P.lib()
+    hm = ctypes.c_void_p()
+    assert L.orbx_create_matcher(ctypes.byref(hm), 0) == 0
+
+    class M:                                            # just enough of the extractor wrapper for hamming_best2
+        _h, _lib = hm, L
+
+        def _check(self, rc, what):
+            assert rc == 0, (what, rc)
+    q, t = synth.descriptors(1, 300), synth.descriptors(2, 500)
+    want = O.hamming_best2(q, t)
+    got = P.hamming_best2(M(), q, t)
+    assert all(np.array_equal(a, b) for a, b in zip(want, got))
+    kps = np.empty(2000, P.KP_DTYPE); desc = np.empty((2000, 32), np.uint8); n = ctypes.c_int()
+    img = synth.frame(1, 64, 64)
+    rc = L.orbx_extract(hm, img.ctypes.data_as(ctypes.c_void_p), 64, 64, 64, 0, kps.ctypes.data_as(ctypes.c_void_p),
+                        desc.ctypes.data_as(ctypes.c_void_p), 2000, ctypes.byref(n))
+    assert rc == -4                                     # ORBX_E_CAPACITY: no extraction arenas on a matcher context
+    L.orbx_destroy(hm)
+
+
 CASES = ["tum", "euroc", "kitti", "grad", "noise", "black", "small", "blocks"]
 
 
