@@ -280,6 +280,17 @@ int orbx_search_for_initialization(orbx_ctx* ctx, const orbx_keypoint* keys1, co
 int orbx_stereo_match(orbx_ctx* left, orbx_ctx* right, int frame, const orbx_keypoint* kps_l, const uint8_t* desc_l,
                       int n_l, const orbx_keypoint* kps_r, const uint8_t* desc_r, int n_r, float bf, float b,
                       int flags, float* u_right, float* depth, int* n_matched);
+/* n_matched (optional) = the left keypoints that END with a depth, i.e. after the 1.5 * 1.4 * median SAD rejection (:1112-1127).
+ * Keypoints whose octave is outside [0, nlevels) or whose 11 x 11 SAD window leaves its level are left unmatched (the
+ * reference's rowRange would assert); at most 2^20 - 1 keypoints per image (ORBX_E_CAPACITY). */
+/* The same for `pairs` stereo pairs in one set of launches (configs[1] / configs[2] as throughput jobs): pair p uses frames
+ * frame0 + p of the two contexts' last extract calls and rows [p * cap, p * cap + n[p]) of the arrays, the layout
+ * orbx_extract_batch writes (cap = its cap_per_frame).  With ORBX_IN_DEVICE every input -- n_l and n_r included -- is a device
+ * pointer, so it chains behind two orbx_extract_batch(..., ORBX_OUT_DEVICE) calls without a host round trip.  u_right / depth:
+ * pairs x cap floats.  n_matched: host array of `pairs` counts or NULL (NULL keeps a device-to-device call asynchronous). */
+int orbx_stereo_match_batch(orbx_ctx* left, orbx_ctx* right, int frame0, int pairs, const orbx_keypoint* kps_l, const uint8_t* desc_l,
+                            const int32_t* n_l, const orbx_keypoint* kps_r, const uint8_t* desc_r, const int32_t* n_r, int cap,
+                            float bf, float b, int flags, float* u_right, float* depth, int32_t* n_matched);
 
 #ifdef __cplusplus
 }

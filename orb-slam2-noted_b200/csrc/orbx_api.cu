@@ -341,7 +341,7 @@ void orbx_destroy(orbx_ctx* h)
     for (cudaEvent_t e : c->eventPool) cudaEventDestroy(e);
     freeGeometry(c);
     void* ptrs[] = {c->dGeom, c->dPyr, c->dBlur, c->dCand, c->dCandCount, c->dSel, c->dSelCount, c->dErr,
-                    c->dOutKp, c->dOutDesc, c->dOutN, c->dIn, c->dScratch, c->dTensorMaps, c->dStrips};
+                    c->dOutKp, c->dOutDesc, c->dOutN, c->dIn, c->dScratch, c->dTensorMaps, c->dStrips, c->dStereoN};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->hPinned) cudaFreeHost(c->hPinned);
     if (c->hMatch) cudaFreeHost(c->hMatch);

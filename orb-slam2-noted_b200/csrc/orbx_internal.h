@@ -118,6 +118,7 @@ struct Ctx {
     std::string lastCudaError;
     // matcher scratch
     void* dScratch = nullptr; size_t scratchBytes = 0;
+    int* dStereoN = nullptr;                       // the two counts of a single-pair orbx_stereo_match with device arrays
     uint8_t* hMatch = nullptr; size_t hMatchBytes = 0; // pinned staging for the small matcher inputs / results (one copy each way)
 };
 

@@ -66,6 +66,7 @@ def _mlib():
     L.orbx_bow_vector.argtypes = [vp, vp, vp, ci, ci, vp, vp, ip]
     L.orbx_bow_score_l1.argtypes = [vp, vp, vp, ci, vp, vp, vp, ci, ci, vp]
     L.orbx_stereo_match.argtypes = [vp, vp, ci, vp, vp, ci, vp, vp, ci, cf, cf, ci, vp, vp, ip]
+    L.orbx_stereo_match_batch.argtypes = [vp, vp, ci, ci, vp, vp, vp, vp, vp, vp, ci, cf, cf, ci, vp, vp, vp]
     _ready = True
     return L
 
@@ -314,3 +315,29 @@ def compute_stereo_matches(left, right, kps_l, desc_l, kps_r, desc_r, bf, b, fra
                                    float(bf), float(b), 0, _np(ur), _np(z), ctypes.byref(n))
     _chk(left, rc, "orbx_stereo_match")
     return ur, z
+
+
+def compute_stereo_matches_batch(left, right, kps_l, desc_l, n_l, kps_r, desc_r, n_r, bf, b, frame0=0, device=False):
+    """Frame::ComputeStereoMatches for many stereo pairs in one call (orbx_stereo_match_batch).  kps / desc: (pairs, cap, ..)
+    blocks and per-pair counts exactly as extract_batch wrote them for the left and the right batch -- numpy arrays, or torch
+    CUDA tensors with device=True (the call then chains behind the two extractions without a host round trip).
+    Returns (mvuRight, mvDepth) as (pairs, cap) arrays / tensors and the per-pair number of keypoints that got a depth."""
+    pairs, cap = int(kps_l.shape[0]), int(kps_l.shape[1])
+    nm = (ctypes.c_int32 * max(pairs, 1))()
+    if device:
+        import torch
+        ur = torch.empty((pairs, cap), dtype=torch.float32, device=kps_l.device)
+        z = torch.empty((pairs, cap), dtype=torch.float32, device=kps_l.device)
+        P = lambda t: ctypes.c_void_p(t.data_ptr())
+        rc = _mlib().orbx_stereo_match_batch(left._h, right._h, frame0, pairs, P(kps_l), P(desc_l), P(n_l), P(kps_r), P(desc_r), P(n_r), cap,
+                                             float(bf), float(b), 3, P(ur), P(z), nm)
+    else:
+        kps_l, kps_r = np.ascontiguousarray(kps_l, KP_DTYPE), np.ascontiguousarray(kps_r, KP_DTYPE)
+        desc_l, desc_r = np.ascontiguousarray(desc_l, np.uint8), np.ascontiguousarray(desc_r, np.uint8)
+        n_l, n_r = np.ascontiguousarray(n_l, np.int32), np.ascontiguousarray(n_r, np.int32)
+        ur, z = np.full((pairs, cap), -1, np.float32), np.full((pairs, cap), -1, np.float32)
+        rc = _mlib().orbx_stereo_match_batch(left._h, right._h, frame0, pairs, _np(kps_l), _np(desc_l), _np(n_l), _np(kps_r), _np(desc_r),
+                                             _np(n_r), cap, float(bf), float(b), 0, _np(ur), _np(z), nm)
+    _chk(left, rc, "orbx_stereo_match_batch")
+    return ur, z, np.array(nm[:pairs], np.int32)
+

@@ -409,6 +409,59 @@ def test_stereo_matches_oracle(P, w, h, nf, seed):
     assert (got_u >= 0).sum() > 100, (int((got_u >= 0).sum()), nv)
 
 
+@pytest.mark.parametrize("w,h,nf,pairs", [(752, 480, 1200, 64), (1241, 376, 2000, 24)])
+def test_stereo_batch_matches_oracle_and_device_chain(P, w, h, nf, pairs):
+    """configs[2] / configs[1] as batches: left and right extract_batch, then ONE orbx_stereo_match_batch, against
+    orc_extract + orc_stereo_matches pair by pair (mvuRight / mvDepth as raw bits); then the same chain with everything left
+    on the device (counts included) must give the same bits."""
+    import torch
+    bf, b = 386.1448, 386.1448 / 718.856
+    prs = [synth.stereo_pair(100 + i, w, h) for i in range(min(pairs, 6))]            # six distinct pairs, tiled
+    left = np.stack([prs[i % len(prs)][0] for i in range(pairs)]); right = np.stack([prs[i % len(prs)][1] for i in range(pairs)])
+    exl = P.ORBextractor(nf, 1.2, 8, 20, 7, max_w=w, max_h=h, max_batch=pairs)
+    exr = P.ORBextractor(nf, 1.2, 8, 20, 7, max_w=w, max_h=h, max_batch=pairs)
+    cap = exl.max_keypoints()
+    dev = torch.device("cuda", 0)
+    dl, dr = torch.from_numpy(left).to(dev), torch.from_numpy(right).to(dev)
+    mk = lambda: (torch.empty((pairs, cap, 28), dtype=torch.uint8, device=dev), torch.empty((pairs, cap, 32), dtype=torch.uint8, device=dev),
+                  torch.zeros(pairs, dtype=torch.int32, device=dev))
+    kl, xl, nl = mk(); kr, xr, nr = mk()
+    exl.extract_batch_device(dl, kl, xl, nl); exr.extract_batch_device(dr, kr, xr, nr)
+    exl.sync(); exr.sync()
+    ur_d, z_d, nm_d = P.compute_stereo_matches_batch(exl, exr, kl, xl, nl, kr, xr, nr, bf, b, device=True)
+    exl.sync()
+    hk = lambda t: t.cpu().numpy().view(P.KP_DTYPE).reshape(pairs, cap)
+    ur_h, z_h, nm_h = P.compute_stereo_matches_batch(exl, exr, hk(kl), xl.cpu().numpy(), nl.cpu().numpy(), hk(kr), xr.cpu().numpy(),
+                                                     nr.cpu().numpy(), bf, b)
+    p = O.params(nf)
+    sizes = O.level_sizes(p, w, h)
+    want = {}
+    for i in range(len(prs)):
+        okl, odl, pyl = O.extract(p, prs[i][0], want_pyr=True)
+        okr, odr, pyr = O.extract(p, prs[i][1], want_pyr=True)
+        want[i] = O.stereo_matches(okl, odl, okr, odr, pyl, pyr, sizes, np.array(p.scale[:8], np.float32), np.array(p.inv_scale[:8], np.float32), bf, b)
+    nl_h = nl.cpu().numpy()
+    for q in range(pairs):
+        wu, wz, _ = want[q % len(prs)]
+        n = int(nl_h[q])
+        assert n == len(wu)
+        for got_u, got_z, nm in ((ur_h, z_h, nm_h), (ur_d.cpu().numpy(), z_d.cpu().numpy(), nm_d)):
+            assert np.array_equal(got_u[q, :n].view(np.uint32), wu.view(np.uint32)), q
+            assert np.array_equal(got_z[q, :n].view(np.uint32), wz.view(np.uint32)), q
+            assert nm[q] == int((wz > 0).sum()) and nm[q] > 100
+    # the single-pair call is the batch of one: same bits, and n_matched counts the keypoints that keep a depth
+    k0, d0 = hk(kl)[3, :nl_h[3]], xl.cpu().numpy()[3, :nl_h[3]]
+    k1, d1 = hk(kr)[3, :int(nr.cpu().numpy()[3])], xr.cpu().numpy()[3, :int(nr.cpu().numpy()[3])]
+    u1, z1 = P.compute_stereo_matches(exl, exr, k0, d0, k1, d1, bf, b, frame=3)
+    assert np.array_equal(u1.view(np.uint32), ur_h[3, :len(k0)].view(np.uint32)) and np.array_equal(z1.view(np.uint32), z_h[3, :len(k0)].view(np.uint32))
+    # guards: keypoints that did not come from this extractor (octave out of range, window outside the level) are left unmatched
+    bad = k0.copy()
+    bad["octave"][::3] = 9; bad["octave"][1::3] = -1
+    bad["x"][2::3] = 2.0; bad["y"][2::3] = 1.0
+    u2, z2 = P.compute_stereo_matches(exl, exr, bad, d0, k1, d1, bf, b, frame=3)
+    assert np.all(u2[::3] == -1) and np.all(u2[1::3] == -1) and np.all(z2[2::3] == -1)
+
+
 def test_search_by_bow_batch_equals_single_calls(P, ctx, vocs):
     """orbx_match_bow_batch: several keyframe pairs of different sizes / modes in one set of launches."""
     _, vo, vg = vocs
