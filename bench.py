@@ -316,6 +316,8 @@ def match_e2e(P, ex, n=10000, pairs_bf=64, pairs_bow=256):
         dt = time.perf_counter() - t0
         off2 = {int(nid): int(sides[1].node_off[i + 1] - sides[1].node_off[i]) for i, nid in enumerate(sides[1].node_id)}
         evals = sum(int(sides[0].node_off[i + 1] - sides[0].node_off[i]) * off2.get(int(nid), 0) for i, nid in enumerate(sides[0].node_id))
+        if name == "brute_force":
+            out["_bf_matches"] = np.stack([r[0] for r in res])
         out[name] = {"pairs": npairs, "ms_per_pair": dt * 1e3 / npairs, "pairs_per_s": npairs / dt, "gmatch_per_s": npairs * evals / dt / 1e9,
                      "nodes": int(len(sides[0].node_id)), "matches_per_pair": int(res[0][1]),
                      "h2d_bytes_per_pair": int(2 * n * (32 + 28 + 1) + 8 * n), "d2h_bytes_per_pair": int(4 * n)}
@@ -416,43 +418,47 @@ def run_orbx(args, rank, world):
     ex = P.ORBextractor(NFEAT, SCALE, NLEVELS, INI, MINTH, device=local, max_w=W, max_h=H, max_batch=B)
     cap = ex.max_keypoints()
     d_img = host.to(dev)
-    # results are double-buffered when there are several ranks: the gather of step i runs on its own stream under the
-    # extraction of step i + 1 (every gather is still inside the timed region; the last one is waited for before it ends)
+    # Results are double-buffered when there are several ranks: the gather of step i (compact records to rank 0 over NCCL, behind
+    # the C ABI: orbx_gather_frames on the communicator's own stream) is issued AFTER step i + 1's extraction has been enqueued,
+    # so the one host synchronisation it needs (the ranks' totals) never leaves the GPU idle.  Every gather is inside the timed
+    # region; the last one is waited for before it ends.
     nbuf = 2 if world > 1 else 1
     bufs = [(torch.empty((B, cap, 28), dtype=torch.uint8, device=dev), torch.empty((B, cap, 32), dtype=torch.uint8, device=dev),
              torch.zeros(B, dtype=torch.int32, device=dev)) for _ in range(nbuf)]
     d_kps, d_desc, d_n = bufs[0]
     stream = torch.cuda.ExternalStream(ex.stream(), device=dev)
     sh = importlib.import_module("orb-slam2-noted_b200.sharding")
-    gather = None
-    if world > 1:  # gather of keypoint/descriptor records over NVLink (fixed padded records)
-        gather = [torch.empty((world * B, cap, 28), dtype=torch.uint8, device=dev),
-                  torch.empty((world * B, cap, 32), dtype=torch.uint8, device=dev),
-                  torch.empty(world * B, dtype=torch.int32, device=dev)]
-        comm_stream = torch.cuda.Stream(device=dev)
-        extracted = [torch.cuda.Event() for _ in range(nbuf)]
-        gathered = [torch.cuda.Event() for _ in range(nbuf)]
-        for e in gathered:
-            e.record(comm_stream)
+    comm = gather = None
+    if world > 1:
+        comm = sh.Comm.from_torch(ex)
+        recs = world * B * (NFEAT + 64) if rank == 0 else 1         # dense: about NFEAT records per frame (cap is NFEAT + 3 per level, rounded)
+        gather = (torch.empty(world * B, dtype=torch.int32, device=dev), torch.empty((recs, 28), dtype=torch.uint8, device=dev),
+                  torch.empty((recs, 32), dtype=torch.uint8, device=dev))
     step_no = [0]
+    pending = [None]                                  # (buffer index, ticket) of the step whose gather has not been issued yet
+    gathered_records = [0]
+
+    def issue_gather():
+        if pending[0] is not None:
+            k, ticket = pending[0]
+            gathered_records[0] = comm.gather_frames(*bufs[k], gather, root=0, ticket=ticket)
+            pending[0] = None
 
     def step():
         k = step_no[0] % nbuf
         step_no[0] += 1
-        if gather is not None:
-            stream.wait_event(gathered[k])            # the gather that last read this buffer pair has finished
+        if comm is not None and step_no[0] > nbuf:
+            comm.wait()                               # the extraction stream waits (on the device) for the gather that read this buffer pair
         ex.extract_batch_device(d_img, *bufs[k])
-        if gather is not None:
-            extracted[k].record(stream)
-            comm_stream.wait_event(extracted[k])
-            with torch.cuda.stream(comm_stream):
-                sh.gather_frames(*bufs[k], world, out=gather)
-            gathered[k].record(comm_stream)
+        if comm is not None:
+            ticket = comm.mark()
+            issue_gather()                            # the previous step's, now that this step's kernels are queued behind it
+            pending[0] = (k, ticket)
 
-    def drain():                                      # the extraction stream waits for every gather issued so far
-        if gather is not None:
-            for e in gathered:
-                stream.wait_event(e)
+    def drain():                                      # the extraction stream waits for every gather
+        if comm is not None:
+            issue_gather()
+            comm.wait()
 
     def barrier():
         torch.cuda.synchronize()
@@ -546,6 +552,18 @@ def run_orbx(args, rank, world):
 
     gm, gm_ms, popc_peak, gm_reps = hamming_gmatch(P, ex, dev)
     me = match_e2e(P, ex)                                  # every rank matches its own keyframe pairs (jobs are independent)
+    bf_matches = me.pop("_bf_matches")
+    if comm is not None:   # keyframe-pair jobs are sharded like frames: the ranks' match lists go to rank 0 as (idx1, idx2) records
+        dm = torch.from_numpy(bf_matches).to(dev)
+        rows = torch.full((dm.shape[0],), dm.shape[1], dtype=torch.int32, device=dev)
+        mo = (torch.empty(world * dm.shape[0], dtype=torch.int32, device=dev),
+              torch.empty((world * dm.shape[0] * dm.shape[1] if rank == 0 else 1, 2), dtype=torch.int32, device=dev))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        nrec = comm.gather_matches(dm, rows, mo, root=0)
+        comm.sync()
+        me["gather"] = {"records_at_root": int(nrec), "ms": (time.perf_counter() - t0) * 1e3, "pairs_per_rank": int(dm.shape[0]),
+                        "note": "orbx_gather_matches: the ranks' brute-force match lists as dense (idx1, idx2) records to rank 0"}
     stereo = stereo_pairs(P, local) if CONFIGS[CONFIG][4] else None
     if world > 1:
         t = torch.tensor([gm, me["brute_force"]["pairs_per_s"], me["brute_force"]["gmatch_per_s"], me["bow"]["pairs_per_s"],
@@ -601,7 +619,7 @@ def run_orbx(args, rank, world):
                         "l2": f"per-step working set {B * (total_alg + W * H) / 1e6:.0f} MB > 126 MB L2 (no flush needed)",
                         "host": (f"rank bound to the {near} CPUs of its GPU's NUMA node while pinned buffers are allocated" if near
                                  else "no NUMA binding"),
-                        "parallelism": f"frames sharded, {world} rank(s)" + (", NCCL all_gather of every step's results on a side stream, overlapped with the next step" if world > 1 else "")},
+                        "parallelism": f"frames sharded, {world} rank(s)" + (f", every step's results gathered to rank 0 as compact records (orbx_gather_frames: device-side scan + compaction, grouped ncclSend/ncclRecv on its own stream; {gathered_records[0]} records in the last step)" if world > 1 else "")},
                 "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
                              "traffic": traffic, "traffic_source": traffic_src, "alu_frac": alu_frac,
                              "peak_source": "measured" if peaks else "fallback",
@@ -659,7 +677,15 @@ def main():
         import __graft_entry__  # noqa: F401  (sys.path)
         run_reference(args, rank)
         return
-    run_orbx(args, rank, world)
+    try:
+        run_orbx(args, rank, world)
+    except BaseException:
+        # a rank that fails must not linger in communicator teardown while its peers wait for it in a collective:
+        # report and leave at once, so that the launcher takes the other ranks down
+        import traceback
+        traceback.print_exc()
+        sys.stderr.flush()
+        os._exit(1)
 
 
 if __name__ == "__main__":

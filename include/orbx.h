@@ -248,6 +248,43 @@ int orbx_search_by_projection(orbx_ctx* ctx, const orbx_proj_query* q, int nq, c
                               const uint8_t* occupied, int mode_flags, int th_dist, float nnratio,
                               int check_orientation, int flags, int32_t* assign, int* nmatches);
 
+/* ---- multi-GPU collection (no counterpart in the reference, which is one CPU process).  Frames and keyframe-pair jobs
+ *      are sharded over one process per GPU with no exchange while they are computed; these calls are the FINAL GATHER of the
+ *      keypoint / descriptor / match lists to one root rank over NCCL (NVLink).  Only the records in use travel: the counts are
+ *      scanned and the padded blocks compacted on the device first.  NCCL is loaded at run time (libnccl.so.2): without it
+ *      orbx_comm_create(nranks > 1) returns ORBX_E_UNSUPPORTED and everything else in this header still works.
+ *      Set-up: rank 0 calls orbx_comm_unique_id and gets the 128 bytes to the other ranks by any means (MPI, a file,
+ *      torch.distributed); every rank then calls orbx_comm_create with its context (the communicator lives on that context's
+ *      device and has its own stream).  nranks == 1 needs no NCCL and no id. ---- */
+typedef struct orbx_comm orbx_comm;
+#define ORBX_COMM_ID_BYTES 128
+int orbx_comm_unique_id(uint8_t* id /* ORBX_COMM_ID_BYTES */);
+int orbx_comm_create(orbx_comm** out, orbx_ctx* ctx, int nranks, int rank, const uint8_t* id);
+void orbx_comm_destroy(orbx_comm* comm);
+const char* orbx_comm_last_error(const orbx_comm* comm);
+/* Ordering.  orbx_comm_mark records "the results enqueued on ctx so far are complete" and returns a ticket (>= 0; at most 7
+ * outstanding); a gather given that ticket starts after it, whatever the caller enqueues on ctx in between (the next step's
+ * extraction into other buffers).  ticket < 0 = after everything enqueued on ctx at the time of the gather call.
+ * orbx_comm_wait makes ctx's stream wait (on the device) for the gathers issued so far -- call it before overwriting buffers a
+ * gather reads; orbx_comm_sync blocks the host until they are done. */
+int orbx_comm_mark(orbx_comm* comm, orbx_ctx* ctx);
+int orbx_comm_wait(orbx_comm* comm, orbx_ctx* ctx);
+int orbx_comm_sync(orbx_comm* comm);
+/* Frames: every rank passes the DEVICE buffers orbx_extract_batch(..., ORBX_OUT_DEVICE) filled (kps / desc: frames x cap rows,
+ * n: frames counts).  At the root, all_n receives nranks x frames counts (rank-major) and all_kps / all_desc the records of rank 0's
+ * frame 0, 1, ..., then rank 1's, ... back to back (device buffers of all_records_cap rows; ignored on the other ranks);
+ * *total_records = rows written.  Every rank returns ORBX_E_CAPACITY when the ROOT's buffers are too small (nothing is sent;
+ * all_records_cap of the other ranks is ignored, their all_* pointers may be NULL).
+ * The call blocks the host once, for the ranks' totals; the transfer itself is asynchronous on the communicator's stream. */
+int orbx_gather_frames(orbx_comm* comm, orbx_ctx* ctx, int ticket, const orbx_keypoint* kps, const uint8_t* desc, const int32_t* n,
+                       int frames, int cap, int root, int32_t* all_n, orbx_keypoint* all_kps, uint8_t* all_desc,
+                       size_t all_records_cap, long long* total_records);
+/* Match lists: match = pairs x cap int32 (what orbx_match_bow_batch / orbx_search_by_projection write: row i matched to match[i],
+ * -1 = none), rows[p] = rows in use of pair p; both DEVICE pointers.  At the root: all_n = nranks x pairs match counts and
+ * all_pairs = the (row, match[row]) records (2 x int32 each, ascending row) of every pair in rank, then pair order. */
+int orbx_gather_matches(orbx_comm* comm, orbx_ctx* ctx, int ticket, const int32_t* match, const int32_t* rows, int pairs, int cap,
+                        int root, int32_t* all_n, int32_t* all_pairs, size_t all_records_cap, long long* total_records);
+
 /* ---- MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:366-448, for npoints map points per call: the observed
  *      descriptors of point p are rows [seg[p], seg[p+1]) of desc (seg: HOST array of npoints+1 offsets, at most 1024 rows
  *      per point); best[p] = row (relative to seg[p]) with the smallest median distance to the point's descriptors, first

@@ -38,3 +38,100 @@ def global_order(gathered, n_items, world):
     B = (n_items + world - 1) // world
     f = torch.arange(n_items)
     return (f % world) * B + (f // world)
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+# The product path: the final gather behind the C ABI (include/orbx.h: orbx_comm_*, orbx_gather_frames, orbx_gather_matches;
+# csrc/k_gather.cu).  Compact records only, to ONE root rank, on the communicator's own stream.  torch.distributed is used for
+# nothing but handing NCCL's 128-byte unique id to the other ranks; any other transport does as well.
+import ctypes
+import numpy as np
+
+
+class Comm:
+    """orbx_comm: one per rank, tied to an ORBextractor's context (device + stream)."""
+
+    def __init__(self, ex, world=1, rank=0, unique_id=None):
+        from .binding import lib
+        L = lib()
+        vp, ci = ctypes.c_void_p, ctypes.c_int
+        L.orbx_comm_unique_id.argtypes = [vp]
+        L.orbx_comm_create.argtypes = [ctypes.POINTER(vp), vp, ci, ci, vp]
+        L.orbx_comm_destroy.argtypes = [vp]
+        L.orbx_comm_destroy.restype = None
+        L.orbx_comm_last_error.argtypes = [vp]
+        L.orbx_comm_last_error.restype = ctypes.c_char_p
+        for f in (L.orbx_comm_mark, L.orbx_comm_wait):
+            f.argtypes = [vp, vp]
+        L.orbx_comm_sync.argtypes = [vp]
+        L.orbx_gather_frames.argtypes = [vp, vp, ci, vp, vp, vp, ci, ci, ci, vp, vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_longlong)]
+        L.orbx_gather_matches.argtypes = [vp, vp, ci, vp, vp, ci, ci, ci, vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_longlong)]
+        self._L, self._ex, self.world, self.rank = L, ex, world, rank
+        self._h = vp()
+        idp = None if unique_id is None else (ctypes.c_uint8 * 128).from_buffer_copy(bytes(unique_id))
+        rc = L.orbx_comm_create(ctypes.byref(self._h), ex._h, world, rank, idp)
+        if rc:
+            raise RuntimeError(f"orbx_comm_create: {L.orbx_strerror(rc).decode()} ({rc})")
+
+    @staticmethod
+    def unique_id():
+        from .binding import lib
+        L = lib()
+        L.orbx_comm_unique_id.argtypes = [ctypes.c_void_p]
+        buf = (ctypes.c_uint8 * 128)()
+        rc = L.orbx_comm_unique_id(buf)
+        if rc:
+            raise RuntimeError(f"orbx_comm_unique_id: {L.orbx_strerror(rc).decode()} ({rc})")
+        return bytes(buf)
+
+    @classmethod
+    def from_torch(cls, ex):
+        """Inside an initialised torch.distributed job: rank 0 makes the id, broadcast_object_list hands it round."""
+        world, rank = dist.get_world_size(), dist.get_rank()
+        box = [cls.unique_id() if rank == 0 else None]
+        if world > 1:
+            dist.broadcast_object_list(box, src=0)
+        return cls(ex, world, rank, box[0] if world > 1 else None)
+
+    def _chk(self, rc, what):
+        if rc < 0:
+            raise RuntimeError(f"{what}: {self._L.orbx_strerror(rc).decode()} ({rc}) {self._L.orbx_comm_last_error(self._h).decode()}")
+        return rc
+
+    def mark(self):
+        """'The results enqueued on the extractor so far are complete' -> ticket for a later gather."""
+        return self._chk(self._L.orbx_comm_mark(self._h, self._ex._h), "orbx_comm_mark")
+
+    def wait(self):
+        self._chk(self._L.orbx_comm_wait(self._h, self._ex._h), "orbx_comm_wait")
+
+    def sync(self):
+        self._chk(self._L.orbx_comm_sync(self._h), "orbx_comm_sync")
+
+    def gather_frames(self, kps, desc, n, out, root=0, ticket=-1):
+        """kps (B, cap, 28) u8, desc (B, cap, 32) u8, n (B,) i32: torch CUDA tensors of this rank.  out = (all_n (world * B,) i32,
+        all_kps (R, 28) u8, all_desc (R, 32) u8) CUDA tensors, used at the root.  Returns the total number of records."""
+        P = lambda t: ctypes.c_void_p(t.data_ptr())
+        total = ctypes.c_longlong()
+        self._chk(self._L.orbx_gather_frames(self._h, self._ex._h, ticket, P(kps), P(desc), P(n), kps.shape[0], kps.shape[1], root,
+                                             P(out[0]), P(out[1]), P(out[2]), out[1].shape[0], ctypes.byref(total)), "orbx_gather_frames")
+        return total.value
+
+    def gather_matches(self, match, rows, out, root=0, ticket=-1):
+        """match (pairs, cap) i32, rows (pairs,) i32 CUDA tensors; out = (all_n (world * pairs,) i32, all_pairs (R, 2) i32)."""
+        P = lambda t: ctypes.c_void_p(t.data_ptr())
+        total = ctypes.c_longlong()
+        self._chk(self._L.orbx_gather_matches(self._h, self._ex._h, ticket, P(match), P(rows), match.shape[0], match.shape[1], root,
+                                              P(out[0]), P(out[1]), out[1].shape[0], ctypes.byref(total)), "orbx_gather_matches")
+        return total.value
+
+    def close(self):
+        if self._h:
+            self._L.orbx_comm_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
