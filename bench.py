@@ -432,8 +432,12 @@ def run_orbx(args, rank, world):
     if world > 1:
         comm = sh.Comm.from_torch(ex)
         recs = world * B * (NFEAT + 64) if rank == 0 else 1         # dense: about NFEAT records per frame (cap is NFEAT + 3 per level, rounded)
-        gather = (torch.empty(world * B, dtype=torch.int32, device=dev), torch.empty((recs, 28), dtype=torch.uint8, device=dev),
-                  torch.empty((recs, 32), dtype=torch.uint8, device=dev))
+        # the root's record buffers live in its peer window (orbx_comm_window): the other ranks' compaction kernels store their
+        # records straight into rank 0's HBM over NVLink; without peer access the gather falls back to ncclSend/ncclRecv
+        shapes = (((recs, 28), torch.uint8), ((recs, 32), torch.uint8))
+        win = comm.window(sh.Comm.carve_bytes(*shapes) if rank == 0 else 0)
+        g_k, g_d = sh.Comm.carve(win, *shapes) if win is not None else [torch.empty(s_, dtype=t_, device=dev) for s_, t_ in shapes]
+        gather = (torch.empty(world * B, dtype=torch.int32, device=dev), g_k, g_d)
     step_no = [0]
     pending = [None]                                  # (buffer index, ticket) of the step whose gather has not been issued yet
     gathered_records = [0]
@@ -481,19 +485,40 @@ def run_orbx(args, rank, world):
     e0.record(stream)
     for _ in range(args.steps):
         step()
+    e_mid = torch.cuda.Event(enable_timing=True)
+    e_mid.record(stream)
     drain()
     e1.record(stream)
     barrier()
     ms = e0.elapsed_time(e1)
+    ms_before_drain = e0.elapsed_time(e_mid)
     launches = ex.kernel_launches() - l0
     stats = ex.stage_stats()
     ex.set_profiling(False)
     nkp = int(d_n.sum().item())
+    per_rank = None
     if world > 1:
+        # every rank's own clock: the whole timed region, the part before the last gather is waited for, and the sum of its
+        # extraction stages (profiling events) -- the step is the MAX over ranks; the rest says where a rank waited for others
+        mine = torch.tensor([ms, ms_before_drain, sum(v[0] for v in stats.values())], device=dev) / args.steps
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = {"ms_per_step": [round(float(x[0]), 4) for x in allr], "ms_per_step_before_last_gather": [round(float(x[1]), 4) for x in allr],
+                    "extraction_stage_ms_per_step": [round(float(x[2]), 4) for x in allr]}
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     value = world * B * args.steps / (ms * 1e-3)
+    if args.value_only:
+        sampler.stop_flag = True
+        clk = [None] * world
+        if world > 1:
+            dist.all_gather_object(clk, sampler.summary())
+        if rank == 0:
+            print(json.dumps({"value_only": True, "clocks_per_rank": [c and c.get("sm_mhz") for c in clk], "reasons_per_rank": [c and c.get("reasons") for c in clk], "value": value, "ms_per_step": ms / args.steps, "n_gpus": world, "ranks": per_rank,
+                              "gather": comm.stats() if comm else None}))
+        barrier()
+        return
 
     # ---- end-to-end through the host-buffer C ABI (`e2e`) ----
     # Two callers, one extractor handle and one set of pinned buffers each, take alternate batches through the synchronous
@@ -619,7 +644,10 @@ def run_orbx(args, rank, world):
                         "l2": f"per-step working set {B * (total_alg + W * H) / 1e6:.0f} MB > 126 MB L2 (no flush needed)",
                         "host": (f"rank bound to the {near} CPUs of its GPU's NUMA node while pinned buffers are allocated" if near
                                  else "no NUMA binding"),
-                        "parallelism": f"frames sharded, {world} rank(s)" + (f", every step's results gathered to rank 0 as compact records (orbx_gather_frames: device-side scan + compaction, grouped ncclSend/ncclRecv on its own stream; {gathered_records[0]} records in the last step)" if world > 1 else "")},
+                        **({"ranks": per_rank} if per_rank else {}),
+                        "parallelism": f"frames sharded, {world} rank(s)" + (f", every step's results gathered to rank 0 as compact records (orbx_gather_frames on its own stream: device-side scan, then "
+                                                                                  + ("each rank compacts and writes its records into rank 0's peer window over NVLink (CUDA IPC, DMA engines)" if comm.stats()[0] else "compaction + grouped ncclSend/ncclRecv")
+                                                                                  + f"; {gathered_records[0]} records in the last step; gathers direct/staged: {comm.stats()})" if world > 1 else "")},
                 "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
                              "traffic": traffic, "traffic_source": traffic_src, "alu_frac": alu_frac,
                              "peak_source": "measured" if peaks else "fallback",
@@ -666,6 +694,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=0, help="frames per GPU per step (default: the config's)")
     ap.add_argument("--impl", default="orbx", choices=["orbx", "reference"])
+    ap.add_argument("--value-only", action="store_true", help="diagnosis: stop after the device-resident measurement and print its timing only")
     ap.add_argument("--config", default="tum", choices=sorted(CONFIGS), help="BASELINE.json workload (the metric is quoted on tum)")
     args = ap.parse_args()
     set_config(args.config)

@@ -285,6 +285,21 @@ int orbx_gather_frames(orbx_comm* comm, orbx_ctx* ctx, int ticket, const orbx_ke
 int orbx_gather_matches(orbx_comm* comm, orbx_ctx* ctx, int ticket, const int32_t* match, const int32_t* rows, int pairs, int cap,
                         int root, int32_t* all_n, int32_t* all_pairs, size_t all_records_cap, long long* total_records);
 
+/* The peer window: device memory of this rank that the other ranks of the communicator map over NVLink / NVSwitch (CUDA IPC).
+ * COLLECTIVE, once per communicator: every rank passes the bytes it wants to be able to receive as a root (0 = never a root)
+ * and gets the base of its own window (*base, NULL for 0 bytes; owned by the communicator).  A gather whose root-side record
+ * buffers (all_kps and all_desc, or all_pairs; all_n may lie anywhere) are carved out of the ROOT's window needs no staging
+ * and no ncclSend/ncclRecv of records: each rank writes its dense records straight into the root's memory at their final place
+ * (peer copies on the DMA engines; env ORBX_GATHER_COPY=0: the compaction kernel's own stores, ORBX_GATHER_CTAS of them), and
+ * only the per-rank counts (the completion handshake) go through NCCL.  Results are the same either way.  All ranks return alike: ORBX_OK, or ORBX_E_UNSUPPORTED when some rank could not export or map a window (no peer
+ * access, IPC not permitted) -- nothing stays mapped then and the gathers travel by ncclSend/ncclRecv as before.
+ * orbx_comm_destroy unmaps and frees: call it on every rank once the last gather has completed EVERYWHERE (after a barrier of
+ * the job), because a rank may not free its window while another still writes to it.  Env ORBX_GATHER_STAGED=1 at the root
+ * turns the direct form off (for measurements).  No counterpart in the reference. */
+int orbx_comm_window(orbx_comm* comm, size_t bytes, void** base);
+/* How this communicator's gathers travelled so far: through the root's window / staged through ncclSend/ncclRecv. */
+int orbx_comm_stats(const orbx_comm* comm, int* direct_gathers, int* staged_gathers);
+
 /* ---- MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:366-448, for npoints map points per call: the observed
  *      descriptors of point p are rows [seg[p], seg[p+1]) of desc (seg: HOST array of npoints+1 offsets, at most 1024 rows
  *      per point); best[p] = row (relative to seg[p]) with the smallest median distance to the point's descriptors, first

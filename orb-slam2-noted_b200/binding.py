@@ -106,7 +106,7 @@ class ORBextractor:
         if rc:
             self._h = ctypes.c_void_p()
             raise OrbxError(f"orbx_create: {self._lib.orbx_strerror(rc).decode()} ({rc})")
-        self.nfeatures, self.nlevels, self.max_batch = nfeatures, nlevels, max_batch
+        self.nfeatures, self.nlevels, self.max_batch, self.device = nfeatures, nlevels, max_batch, device
         self.mvImagePyramid = _PyramidView(self)
 
     def _check(self, rc, what):

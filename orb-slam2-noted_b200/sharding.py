@@ -64,6 +64,8 @@ class Comm:
         for f in (L.orbx_comm_mark, L.orbx_comm_wait):
             f.argtypes = [vp, vp]
         L.orbx_comm_sync.argtypes = [vp]
+        L.orbx_comm_window.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(vp)]
+        L.orbx_comm_stats.argtypes = [vp, ctypes.POINTER(ci), ctypes.POINTER(ci)]
         L.orbx_gather_frames.argtypes = [vp, vp, ci, vp, vp, vp, ci, ci, ci, vp, vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_longlong)]
         L.orbx_gather_matches.argtypes = [vp, vp, ci, vp, vp, ci, ci, ci, vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_longlong)]
         self._L, self._ex, self.world, self.rank = L, ex, world, rank
@@ -107,6 +109,48 @@ class Comm:
 
     def sync(self):
         self._chk(self._L.orbx_comm_sync(self._h), "orbx_comm_sync")
+
+    def window(self, nbytes):
+        """Collective (orbx_comm_window): this rank's peer window of `nbytes` as a torch uint8 CUDA tensor (None for 0 bytes), or
+        None on every rank when the windows could not be set up (the gathers then go through ncclSend/ncclRecv).  Root-side
+        gather buffers carved out of it (`carve`) are written by the other ranks' compaction kernels directly."""
+        import torch
+        base = ctypes.c_void_p()
+        rc = self._L.orbx_comm_window(self._h, int(nbytes), ctypes.byref(base))
+        if rc == -5:                                  # ORBX_E_UNSUPPORTED, on every rank alike
+            return None
+        self._chk(rc, "orbx_comm_window")
+        if not base.value:
+            return None
+
+        class _Mem:                                   # the communicator owns the memory; the tensor is a view of it
+            pass
+        m = _Mem()
+        m.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (base.value, False), "version": 3}
+        m._owner = self
+        return torch.as_tensor(m, device=torch.device("cuda", self._ex.device))
+
+    @staticmethod
+    def carve(window, *shapes_dtypes):
+        """Views into a window tensor: carve(win, ((R, 28), torch.uint8), ((R, 32), torch.uint8)) -> tensors at 256-byte steps."""
+        out, off = [], 0
+        for shape, dtype in shapes_dtypes:
+            import math
+            nb = math.prod(shape) * dtype.itemsize
+            out.append(window[off:off + nb].view(dtype).view(*shape))
+            off += (nb + 255) & ~255
+        return out
+
+    @staticmethod
+    def carve_bytes(*shapes_dtypes):
+        import math
+        return sum(((math.prod(s) * d.itemsize + 255) & ~255) for s, d in shapes_dtypes)
+
+    def stats(self):
+        """(gathers that went through the root's window, gathers staged through ncclSend/ncclRecv)"""
+        a, b = ctypes.c_int(), ctypes.c_int()
+        self._chk(self._L.orbx_comm_stats(self._h, ctypes.byref(a), ctypes.byref(b)), "orbx_comm_stats")
+        return a.value, b.value
 
     def gather_frames(self, kps, desc, n, out, root=0, ticket=-1):
         """kps (B, cap, 28) u8, desc (B, cap, 32) u8, n (B,) i32: torch CUDA tensors of this rank.  out = (all_n (world * B,) i32,

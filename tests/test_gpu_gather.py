@@ -50,6 +50,15 @@ def test_gather_single_rank_compacts_frames_and_match_lists():
     want = [np.stack([np.flatnonzero(match[p, :rows[p]] >= 0), match[p, :rows[p]][match[p, :rows[p]] >= 0]], 1) for p in range(pairs)]
     assert np.array_equal(mo[0].cpu().numpy(), [len(x) for x in want]) and total == sum(len(x) for x in want)
     assert np.array_equal(mo[1][:total].cpu().numpy(), np.concatenate(want))
+    # a peer window on one rank is just memory owned by the communicator: gathers into it give the same records
+    win = comm.window(sh.Comm.carve_bytes(((B * cap, 28), torch.uint8), ((B * cap, 32), torch.uint8)))
+    assert win is not None and win.is_cuda and win.data_ptr() % 256 == 0
+    wk2, wd2 = sh.Comm.carve(win, ((B * cap, 28), torch.uint8), ((B * cap, 32), torch.uint8))
+    total = comm.gather_frames(kps, desc, n, (out[0], wk2, wd2))
+    comm.sync()
+    assert torch.equal(wk2[:total], out[1][:total]) and torch.equal(wd2[:total], out[2][:total])
+    with pytest.raises(RuntimeError, match="window"):
+        comm.window(1024)                                                           # one per communicator
     comm.close()
 
 
@@ -103,19 +112,55 @@ if rank == 0:
     rec = mo[1][:mt].cpu().numpy()
     assert mt == int(cnt.sum()) and np.array_equal(rec[:cnt[0, 0], 0], np.arange(0, 64, 7)) and set(rec[:, 1]) == set(range(100, 100 + world))
     print("GATHER_OK", world, total, mt)
+# the same two gathers through the root's peer window: the other rank's compaction kernel writes into rank 0's memory
+assert comm.stats() == (0, 2)
+shapes = (((rows_out, 28), torch.uint8), ((rows_out, 32), torch.uint8), ((world * 3 * 64, 2), torch.int32))
+win = comm.window(sh.Comm.carve_bytes(*shapes) if rank == 0 else 0)
+have = torch.tensor([0 if win is None else 1]); dist.broadcast(have, src=0)
+if not int(have):
+    if rank == 0:
+        print("WINDOW_UNSUPPORTED", comm._L.orbx_comm_last_error(comm._h).decode())
+else:
+    if rank == 0:
+        win.fill_(0xEE)
+        k2, d2, p2 = sh.Comm.carve(win, *shapes)
+        out2, mo2 = (torch.zeros_like(out[0]), k2, d2), (torch.zeros_like(mo[0]), p2)
+        torch.cuda.synchronize()
+    else:
+        out2, mo2 = out, mo
+    dist.barrier()
+    for rep in range(2):
+        t2 = comm.gather_frames(k, d, n, out2, root=0)
+        m2 = comm.gather_matches(match, torch.tensor([64, 10, 0], dtype=torch.int32, device=dev), mo2, root=0)
+        comm.sync()
+        assert (t2, m2) == (total, mt)
+        if rank == 0:
+            assert torch.equal(out2[0], out[0]) and torch.equal(out2[1][:total], out[1][:total]) and torch.equal(out2[2][:total], out[2][:total])
+            assert torch.equal(mo2[0], mo[0]) and torch.equal(mo2[1][:mt], mo[1][:mt])
+            assert bool((out2[1][total:total + 4] == 0xEE).all())               # nothing written past the records
+            k2[:total].zero_(); torch.cuda.synchronize()
+        dist.barrier()                                   # the root has looked before the next round overwrites
+    assert comm.stats() == (4, 2), comm.stats()
+    if rank == 0:
+        print("WINDOW_OK", world)
+dist.barrier()
 comm.close()
 dist.barrier()
 dist.destroy_process_group()
 '''
 
 
-def test_gather_two_ranks_over_nccl(tmp_path):
+@pytest.mark.parametrize("window_form", ["dma", "sm_stores"])
+def test_gather_two_ranks_over_nccl(tmp_path, window_form):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
-    env = dict(os.environ, ORBX_ROOT=ROOT)
+    env = dict(os.environ, ORBX_ROOT=ROOT, ORBX_GATHER_COPY="1" if window_form == "dma" else "0")
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                         "--master-port", "29617", str(script)], capture_output=True, text=True, env=env, timeout=300)
     assert r.returncode == 0 and "GATHER_OK 2" in r.stdout, (r.stdout[-2000:], r.stderr[-3000:])
+    assert "WINDOW_OK 2" in r.stdout or "WINDOW_UNSUPPORTED" in r.stdout, (r.stdout[-2000:], r.stderr[-3000:])
+    if "WINDOW_UNSUPPORTED" in r.stdout:
+        pytest.skip("peer windows are not available on this box: " + r.stdout[-300:])
