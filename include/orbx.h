@@ -300,6 +300,36 @@ int orbx_comm_window(orbx_comm* comm, size_t bytes, void** base);
 /* How this communicator's gathers travelled so far: through the root's window / staged through ncclSend/ncclRecv. */
 int orbx_comm_stats(const orbx_comm* comm, int* direct_gathers, int* staged_gathers);
 
+/* ---- KeyFrameDatabase, src/KeyFrameDatabase.cc: the place-recognition database behind loop closing and relocalisation.
+ *      Keyframes are named by the caller's ids (KeyFrame::mnId, 0 <= id < 2^28).  The reference keeps an inverted file of
+ *      std::list<KeyFrame*>; here every keyframe's BowVector lies in one device arena and a query is a forward scan against
+ *      a bitmap of the query's words (csrc/k_kfdb.cu) -- same candidates, same ORDER.  A database belongs to its ctx (device,
+ *      stream) and is used by one thread at a time, like the reference's under its mutex.  Only vocabularies scored with
+ *      L1_NORM (the ORB-SLAM2 vocabulary; see orbx_vocab_modes) are covered. ---- */
+typedef struct orbx_kfdb orbx_kfdb;
+int orbx_kfdb_create(orbx_ctx* ctx, int nwords, orbx_kfdb** out);            /* KeyFrameDatabase(voc) :38-42, nwords = voc.size() */
+void orbx_kfdb_destroy(orbx_kfdb* db);
+int orbx_kfdb_size(const orbx_kfdb* db);                                      /* keyframes currently held */
+/* add(pKF) :50-56: words = the ascending word ids of pKF->mBowVec, vals their weights (HOST arrays of n entries) */
+int orbx_kfdb_add(orbx_kfdb* db, int kf_id, const int32_t* words, const double* vals, int n);
+int orbx_kfdb_erase(orbx_kfdb* db, int kf_id);                                /* erase(pKF) :64-83; unknown ids are ignored */
+int orbx_kfdb_clear(orbx_kfdb* db);                                           /* clear() :85-89 */
+/* What pKF->GetBestCovisibilityKeyFrames(10) returns (src/KeyFrame.cc:248-258): ids, strongest first (the first 10 are
+ * kept).  Call it when the keyframe's ordered connections change; ids not in the database are fine (never met by a query). */
+int orbx_kfdb_set_covisible(orbx_kfdb* db, int kf_id, const int32_t* ids, int n);
+/* DetectLoopCandidates(pKF, minScore) :113-270: query_id = pKF->mnId, words / vals = pKF->mBowVec, connected = the ids of
+ * pKF->GetConnectedKeyFrames().  out_ids = candidate ids in the reference's order; *n_out = how many there are (the first
+ * cap are written).  The per-keyframe query state (mnLoopQuery, mnLoopWords, mLoopScore) persists between calls as in the
+ * reference, including its behaviour for a query id used twice. */
+int orbx_kfdb_detect_loop(orbx_kfdb* db, long long query_id, const int32_t* words, const double* vals, int nq, const int32_t* connected,
+                          int nconnected, float min_score, int32_t* out_ids, int cap, int* n_out);
+/* DetectRelocalizationCandidates(F) :275-399 for nqueries frames per call, in order (a later query sees the mRelocScore
+ * values an earlier one left, :351).  query_ids[q] = F->mnId; query q's BowVector is words / vals [seg[q], seg[q+1]) (HOST
+ * arrays; seg has nqueries + 1 entries, seg[0] = 0); its candidates go to out_ids[q * cap ...], their number to n_out[q].
+ * One synchronisation per call.  mLoopScore / mRelocScore start at 0 (the reference leaves them uninitialised). */
+int orbx_kfdb_detect_reloc(orbx_kfdb* db, int nqueries, const long long* query_ids, const int32_t* words, const double* vals,
+                           const int32_t* seg, int32_t* out_ids, int cap, int* n_out);
+
 /* ---- MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:366-448, for npoints map points per call: the observed
  *      descriptors of point p are rows [seg[p], seg[p+1]) of desc (seg: HOST array of npoints+1 offsets, at most 1024 rows
  *      per point); best[p] = row (relative to seg[p]) with the smallest median distance to the point's descriptors, first

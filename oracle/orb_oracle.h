@@ -142,6 +142,18 @@ int orc_stereo_matches(const orc_keypoint* kL, const uint8_t* dL, int N, const o
                        const uint8_t* pyrL, const uint8_t* pyrR, const int* lvl_w, const int* lvl_h, const size_t* lvl_off,
                        const float* scale, const float* inv_scale, float mbf, float mb, float* uRight, float* depth);
 
+/* ---- KeyFrameDatabase (src/KeyFrameDatabase.cc): orb_kfdb.c ---- */
+typedef struct orc_kfdb orc_kfdb;
+orc_kfdb* orc_kfdb_create(int nwords);
+void orc_kfdb_destroy(orc_kfdb* d);
+void orc_kfdb_clear(orc_kfdb* d);
+int orc_kfdb_new_keyframe(orc_kfdb* d, int id, const int32_t* word, const double* val, int n);
+int orc_kfdb_add(orc_kfdb* d, int id);
+int orc_kfdb_erase(orc_kfdb* d, int id);
+int orc_kfdb_set_covisible(orc_kfdb* d, int id, const int32_t* ids, int n);
+int orc_kfdb_detect_loop(orc_kfdb* d, int query_kf, const int32_t* conn, int nconn, float minScore, int32_t* out, int cap);
+int orc_kfdb_detect_reloc(orc_kfdb* d, long long frame_id, const int32_t* word, const double* val, int n, int32_t* out, int cap);
+
 #ifdef __cplusplus
 }
 #endif

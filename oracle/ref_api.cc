@@ -618,3 +618,85 @@ extern "C" int ref_run_matcher_scene(const char* in_path, const char* out_path)
     fclose(o);
     return 0;   // the scene's objects are left to the process (the Map owns raw pointers exactly as in the reference)
 }
+
+// ------------------------------------------------------------------------------------------------ KeyFrameDatabase
+// The reference's own KeyFrameDatabase (src/KeyFrameDatabase.cc) over keyframes that carry nothing but an id, a BowVector
+// and their covisibility lists.  The vocabulary is a default ORBVocabulary (L1_NORM scoring) whose word table is sized to
+// `nwords` -- the database only asks it for size() and score().  mLoopScore / mRelocScore have no initialiser in the
+// reference (src/KeyFrame.cc:43-60); they are set to 0 here, the value orb_kfdb.c and the device code start from.
+namespace {
+struct RefKfdb {
+    ORBVocabulary voc;
+    KeyFrameDatabase* db;
+    Map map;
+    Frame base;
+    std::map<int, KeyFrame*> kfs;
+};
+DBoW2::BowVector bowOf(const int32_t* w, const double* v, int n)
+{
+    DBoW2::BowVector b;
+    for (int i = 0; i < n; ++i) b.insert(b.end(), std::make_pair((DBoW2::WordId)w[i], v[i]));
+    return b;
+}
+}
+
+extern "C" {
+void* ref_kfdb_create(int nwords)
+{
+    RefKfdb* r = new RefKfdb();
+    r->voc.m_words.resize((size_t)nwords, NULL);
+    r->db = new KeyFrameDatabase(r->voc);
+    Frame& F = r->base;
+    F.N = 0; F.mnScaleLevels = 1; F.mfScaleFactor = 1.2f; F.mfLogScaleFactor = std::log(1.2f);
+    F.mK = cv::Mat::eye(3, 3, CV_32F); F.mDistCoef = cv::Mat::zeros(4, 1, CV_32F);
+    F.mbf = 40.f; F.mb = 0.1f; F.mThDepth = 0; F.mTimeStamp = 0; F.mnId = 0;
+    F.mpORBvocabulary = &r->voc; F.mpORBextractorLeft = F.mpORBextractorRight = NULL; F.mpReferenceKF = NULL;
+    F.SetPose(cv::Mat::eye(4, 4, CV_32F));
+    return r;
+}
+void ref_kfdb_destroy(void* h) { RefKfdb* r = (RefKfdb*)h; delete r->db; delete r; }   // keyframes stay with the process, as in the reference
+void ref_kfdb_clear(void* h) { ((RefKfdb*)h)->db->clear(); }
+int ref_kfdb_new_keyframe(void* h, int id, const int32_t* w, const double* v, int n)
+{
+    RefKfdb* r = (RefKfdb*)h;
+    if (r->kfs.count(id)) return -1;
+    KeyFrame* k = new KeyFrame(r->base, &r->map, r->db);
+    k->mnId = (long unsigned)id;
+    k->mBowVec = bowOf(w, v, n);
+    k->mLoopScore = 0.f; k->mRelocScore = 0.f;
+    r->kfs[id] = k;
+    return 0;
+}
+int ref_kfdb_add(void* h, int id) { RefKfdb* r = (RefKfdb*)h; if (!r->kfs.count(id)) return -1; r->db->add(r->kfs[id]); return 0; }
+int ref_kfdb_erase(void* h, int id) { RefKfdb* r = (RefKfdb*)h; if (!r->kfs.count(id)) return -1; r->db->erase(r->kfs[id]); return 0; }
+int ref_kfdb_set_covisible(void* h, int id, const int32_t* ids, int n)
+{
+    RefKfdb* r = (RefKfdb*)h;
+    if (!r->kfs.count(id)) return -1;
+    std::vector<KeyFrame*> v;
+    for (int i = 0; i < n; ++i) if (r->kfs.count(ids[i])) v.push_back(r->kfs[ids[i]]);
+    r->kfs[id]->mvpOrderedConnectedKeyFrames = v;          // what GetBestCovisibilityKeyFrames(10) reads (src/KeyFrame.cc:248-258)
+    return 0;
+}
+int ref_kfdb_detect_loop(void* h, int query, const int32_t* conn, int nconn, float minScore, int32_t* out, int cap)
+{
+    RefKfdb* r = (RefKfdb*)h;
+    if (!r->kfs.count(query)) return -1;
+    KeyFrame* q = r->kfs[query];
+    q->mConnectedKeyFrameWeights.clear();                  // GetConnectedKeyFrames returns its keys (src/KeyFrame.cc:225-233)
+    for (int i = 0; i < nconn; ++i) if (r->kfs.count(conn[i])) q->mConnectedKeyFrameWeights[r->kfs[conn[i]]] = 15;
+    std::vector<KeyFrame*> c = r->db->DetectLoopCandidates(q, minScore);
+    for (size_t i = 0; i < c.size() && (int)i < cap; ++i) out[i] = (int32_t)c[i]->mnId;
+    return (int)c.size();
+}
+int ref_kfdb_detect_reloc(void* h, long long frame_id, const int32_t* w, const double* v, int n, int32_t* out, int cap)
+{
+    RefKfdb* r = (RefKfdb*)h;
+    Frame F(r->base);
+    F.mnId = (long unsigned)frame_id;
+    F.mBowVec = bowOf(w, v, n);
+    std::vector<KeyFrame*> c = r->db->DetectRelocalizationCandidates(&F);
+    for (size_t i = 0; i < c.size() && (int)i < cap; ++i) out[i] = (int32_t)c[i]->mnId;
+    return (int)c.size();
+}
+}

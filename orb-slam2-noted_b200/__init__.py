@@ -14,6 +14,7 @@ from .binding import (KP_DTYPE, OrbxError, lib, lib_path, ORBextractor, descript
 from .matcher import (ORBmatcher, Vocabulary, FrameView, feature_vector, assign_features_to_grid, compute_stereo_matches,
                       compute_stereo_matches_batch, window_best, distinctive_descriptors, bow_score_l1, PROJ_QUERY_DTYPE)
 
-__all__ = ["ORBmatcher", "Vocabulary", "FrameView", "feature_vector", "assign_features_to_grid", "compute_stereo_matches", "compute_stereo_matches_batch",
+from .kfdb import KeyFrameDatabase
+__all__ = ["KeyFrameDatabase", "ORBmatcher", "Vocabulary", "FrameView", "feature_vector", "assign_features_to_grid", "compute_stereo_matches", "compute_stereo_matches_batch",
            "window_best", "distinctive_descriptors", "bow_score_l1", "PROJ_QUERY_DTYPE", "KP_DTYPE", "OrbxError", "lib", "lib_path", "ORBextractor", "descriptor_distance", "hamming_best2",
            "stage_names", "cvt_gray", "undistort_keypoints", "FMT_RGB", "FMT_BGR", "FMT_RGBA", "FMT_BGRA"]

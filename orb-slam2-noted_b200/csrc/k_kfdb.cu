@@ -1,0 +1,499 @@
+// KeyFrameDatabase on the device: add / erase / clear and the two candidate searches of
+// src/KeyFrameDatabase.cc -- DetectLoopCandidates :113-270 and DetectRelocalizationCandidates :275-399 -- with the
+// reference's results in the reference's ORDER (the output is an ordered vector<KeyFrame*>).
+//
+// The reference walks an inverted file (word -> std::list<KeyFrame*>): pointer chasing whose only products are, per keyframe,
+// the NUMBER of words shared with the query and the list order of first encounter.  On the GPU both come out of a forward
+// scan: the query's words are a bitmap over the vocabulary (1 M words = 128 KB, L1/L2-resident), every keyframe's BowVector
+// lies back to back in one arena in insertion order, and one warp per keyframe tests its words against the bitmap with
+// coalesced loads.  The order of first encounter is (smallest shared word, position in that word's list), and the position
+// in a list is the insertion order of the keyframes that carry the word -- so the sort key is (first shared word, slot),
+// with slots handed out in insertion order and never reused.  No inverted file is kept at all; add is an append, erase a flag.
+//   K1 kfdbBeginKernel   counters + query bitmap
+//   K2 kfdbSharedKernel  one warp per keyframe: shared-word count, first shared word, the mnLoopQuery / mnLoopWords state
+//                        machine of :120-146 (connected keyframes, repeated query ids), max common words
+//   K3 kfdbScoreKernel   one warp per keyframe above 0.8 * max: L1Scoring::score in double, summed in ascending word order
+//                        (the lanes find the common words, the sum runs in word order through shuffles) -> float score,
+//                        candidate list
+//   K4 kfdbGroupKernel   one thread per candidate: accumulate over its <= 10 best covisible keyframes :193-224 / :337-364
+//   K5 kfdbEmitKernel / kfdbWriteKernel   0.75 * best gate, first-occurrence de-duplication and output position, all by
+//                        rank among the candidates' keys (O(C^2) over a handful to a few thousand candidates)
+// The per-keyframe state the reference keeps in KeyFrame (mnLoopQuery, mnLoopWords, mLoopScore, mnRelocQuery, mnRelocWords,
+// mRelocScore; include/KeyFrame.h:322-333) lives in slot arrays here and persists between queries exactly like there: a
+// relocalisation query adds a neighbour's mRelocScore even when that score stems from an earlier query (:351).  The two
+// scores have no initialiser in the reference (src/KeyFrame.cc:43-60); they start at 0 here.
+#include "orbx_internal.h"
+#include <climits>
+#include <unordered_map>
+#include <vector>
+
+struct orbx_kfdb {
+    orbx_ctx* ctx = nullptr;
+    int nwords = 0;
+    // BowVector arena (insertion order)
+    int32_t* dIds = nullptr; double* dVals = nullptr; size_t entries = 0, entriesCap = 0;
+    // slots
+    int nslots = 0, slotsCap = 0;
+    int *dSeg = nullptr, *dLen = nullptr, *dKfId = nullptr, *dAlive = nullptr, *dNeigh = nullptr;     // dNeigh: 10 ids per slot, -1 padded
+    long long *dLoopQuery = nullptr, *dRelocQuery = nullptr;
+    int *dLoopWords = nullptr, *dRelocWords = nullptr;
+    float *dLoopScore = nullptr, *dRelocScore = nullptr;
+    int *dExclStamp = nullptr, *dInList = nullptr, *dFirstWord = nullptr;
+    // candidates of the current query
+    unsigned long long* dKey = nullptr; int *dCandSlot = nullptr, *dBest = nullptr, *dEmit = nullptr; float* dAcc = nullptr;
+    // id -> slot
+    int* dSlotOfId = nullptr; int idCap = 0;
+    // query
+    uint32_t* dBitmap = nullptr;
+    int32_t* dQIds = nullptr; double* dQVals = nullptr; int qCap = 0;
+    int* dConn = nullptr; int connCap = 0;
+    int* dCounters = nullptr;               // [0] max common words, [1] candidates, [2] best accumulated score (float bits), [3] outputs
+    int32_t* dOut = nullptr; int* dNOut = nullptr; int outCap = 0, outQueries = 0;
+    int stamp = 0;
+    std::unordered_map<int, int> slotOf;    // host mirror: keyframe id -> live slot
+    std::vector<int> idOfSlot;
+};
+
+namespace orbx {
+
+__global__ void kfdbInitSlotKernel(int slot, int seg, int len, int id, int* dSeg, int* dLen, int* dKfId, int* dAlive, int* dNeigh,
+                                   long long* lq, long long* rq, int* lw, int* rw, float* ls, float* rs, int* excl, int* slotOfId)
+{
+    if (threadIdx.x == 0) {
+        dSeg[slot] = seg; dLen[slot] = len; dKfId[slot] = id; dAlive[slot] = 1;
+        lq[slot] = 0; rq[slot] = 0; lw[slot] = 0; rw[slot] = 0; ls[slot] = 0.f; rs[slot] = 0.f; excl[slot] = 0;   // src/KeyFrame.cc:47
+        slotOfId[id] = slot;
+    }
+    if (threadIdx.x < 10) dNeigh[slot * 10 + threadIdx.x] = -1;
+}
+
+struct Neigh10 { int id[10]; };
+__global__ void kfdbSetNeighKernel(int slot, Neigh10 nb, int* dNeigh) { if (threadIdx.x < 10) dNeigh[slot * 10 + threadIdx.x] = nb.id[threadIdx.x]; }
+__global__ void kfdbEraseKernel(int slot, int id, int* dAlive, int* slotOfId) { dAlive[slot] = 0; slotOfId[id] = -1; }
+__global__ void kfdbFillKernel(int* p, int n, int v) { const int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) p[i] = v; }
+
+// K1: counters, exclusion stamps of the connected keyframes, and the query's bitmap (cleared by a memset before)
+__global__ void kfdbBeginKernel(const int32_t* __restrict__ qIds, int nq, int nwords, uint32_t* __restrict__ bitmap, const int* __restrict__ conn,
+                                int nconn, const int* __restrict__ slotOfId, int idCap, int* __restrict__ exclStamp, int stamp,
+                                int* __restrict__ counters, float bestAcc0)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { counters[0] = 0; counters[1] = 0; counters[2] = __float_as_int(bestAcc0); counters[3] = 0; }
+    if (i < nq) { const int w = qIds[i]; if (w >= 0 && w < nwords) atomicOr(&bitmap[w >> 5], 1u << (w & 31)); }
+    if (i < nconn) { const int id = conn[i]; if (id >= 0 && id < idCap) { const int s = slotOfId[id]; if (s >= 0) exclStamp[s] = stamp; } }
+}
+
+// K2: one warp per slot
+__global__ void __launch_bounds__(256)
+kfdbSharedKernel(int nslots, const int* __restrict__ dSeg, const int* __restrict__ dLen, const int* __restrict__ dAlive,
+                 const int32_t* __restrict__ ids, const uint32_t* __restrict__ bitmap, int loop, long long qid,
+                 const int* __restrict__ exclStamp, int stamp, long long* __restrict__ query, int* __restrict__ words,
+                 int* __restrict__ inList, int* __restrict__ firstWord, int* __restrict__ counters)
+{
+    const int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (s >= nslots) return;
+    if (!dAlive[s]) { if (lane == 0) inList[s] = 0; return; }
+    const int seg = dSeg[s], len = dLen[s];
+    int cnt = 0, first = INT_MAX;
+    for (int j = lane; j < len; j += 32) {
+        const int w = ids[seg + j];
+        if ((bitmap[w >> 5] >> (w & 31)) & 1u) { ++cnt; first = min(first, w); }
+    }
+    #pragma unroll
+    for (int o = 16; o; o >>= 1) { cnt += __shfl_xor_sync(0xffffffffu, cnt, o); first = min(first, __shfl_xor_sync(0xffffffffu, first, o)); }
+    if (lane) return;
+    int in = 0;
+    if (cnt) {                                                   // the keyframe is met `cnt` times while the query's words are walked
+        if (query[s] != qid) {
+            if (loop && exclStamp[s] == stamp) words[s] = 1;     // connected: mnLoopWords reset at every visit, then ++ (:131-141)
+            else { query[s] = qid; words[s] = cnt; in = 1; firstWord[s] = first; atomicMax(&counters[0], cnt); }
+        } else words[s] += cnt;                                  // a query id seen before: counted on, not listed again
+    }
+    inList[s] = in;
+}
+
+__device__ __forceinline__ void atomicMaxFloat(int* addr, float v)
+{
+    int old = *addr;
+    while (v > __int_as_float(old)) { const int assumed = old; old = atomicCAS(addr, assumed, __float_as_int(v)); if (old == assumed) break; }
+}
+
+// K3: one warp per listed slot with more than minCommon words
+__global__ void __launch_bounds__(256)
+kfdbScoreKernel(int nslots, const int* __restrict__ dSeg, const int* __restrict__ dLen, const int32_t* __restrict__ ids,
+                const double* __restrict__ vals, const uint32_t* __restrict__ bitmap, const int32_t* __restrict__ qIds,
+                const double* __restrict__ qVals, int nq, int loop, float minScore, const int* __restrict__ inList,
+                const int* __restrict__ words, const int* __restrict__ firstWord, float* __restrict__ score,
+                int* __restrict__ counters, unsigned long long* __restrict__ key, int* __restrict__ candSlot)
+{
+    const int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (s >= nslots || !inList[s]) return;
+    const int minCommon = (int)((float)counters[0] * 0.8f);      // int * float -> float -> int, :161 / :312
+    if (!(words[s] > minCommon)) return;
+    const int seg = dSeg[s], len = dLen[s];
+    double sum = 0.0;
+    for (int base = 0; base < len; base += 32) {                 // uniform trip count: every lane takes part in the shuffles
+        const int j = base + lane;
+        double term = 0.0;
+        bool hit = false;
+        if (j < len) {
+            const int w = ids[seg + j];
+            if ((bitmap[w >> 5] >> (w & 31)) & 1u) {
+                int lo = 0, hi = nq - 1;                          // the word is in the query: find its weight
+                while (lo < hi) { const int mid = (lo + hi) >> 1; if (qIds[mid] < w) lo = mid + 1; else hi = mid; }
+                const double vi = qVals[lo], wi = vals[seg + j];
+                term = fabs(vi - wi) - fabs(vi) - fabs(wi);      // ScoringObject.cpp:41
+                hit = true;
+            }
+        }
+        unsigned m = __ballot_sync(0xffffffffu, hit);
+        while (m) {                                               // ascending word order = ascending lane
+            const int l = __ffs(m) - 1;
+            m &= m - 1;
+            sum += __shfl_sync(0xffffffffu, term, l);
+        }
+    }
+    if (lane) return;
+    const float si = (float)(-sum / 2.0);
+    score[s] = si;
+    if (!loop || si >= minScore) {
+        const int c = atomicAdd(&counters[1], 1);
+        key[c] = ((unsigned long long)(unsigned)firstWord[s] << 32) | (unsigned)s;
+        candSlot[c] = s;
+    }
+}
+
+// K4: one thread per candidate
+__global__ void kfdbGroupKernel(const int* __restrict__ counters, const int* __restrict__ candSlot, const int* __restrict__ dNeigh,
+                                const int* __restrict__ slotOfId, int idCap, const int* __restrict__ dKfId, int loop, long long qid,
+                                const long long* __restrict__ query, const int* __restrict__ words, const float* __restrict__ score,
+                                float* __restrict__ acc, int* __restrict__ best, int* __restrict__ bestAcc)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= counters[1]) return;
+    const int minCommon = (int)((float)counters[0] * 0.8f);
+    const int s = candSlot[c];
+    float bestScore = score[s], a = bestScore;
+    int bestId = dKfId[s];
+    for (int j = 0; j < 10; ++j) {
+        const int id = dNeigh[s * 10 + j];
+        if (id < 0) break;
+        if (id >= idCap) continue;
+        const int s2 = slotOfId[id];
+        if (s2 < 0) continue;                                    // not (or no longer) in the database: never met by this query
+        if (query[s2] != qid) continue;
+        if (loop && !(words[s2] > minCommon)) continue;          // :206; the relocalisation form has no such test (:346-348)
+        const float sc = score[s2];
+        a += sc;
+        if (sc > bestScore) { bestId = id; bestScore = sc; }
+    }
+    acc[c] = a; best[c] = bestId;
+    atomicMaxFloat(bestAcc, a);
+}
+
+// K5a: kept by the 0.75 gate and not preceded (in list order) by a kept candidate with the same best keyframe
+__global__ void kfdbEmitKernel(const int* __restrict__ counters, const unsigned long long* __restrict__ key, const float* __restrict__ acc,
+                               const int* __restrict__ best, int* __restrict__ emit)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, n = counters[1];
+    if (c >= n) return;
+    const float retain = 0.75f * __int_as_float(counters[2]);
+    int e = acc[c] > retain;
+    if (e) {
+        const unsigned long long k = key[c];
+        const int b = best[c];
+        for (int j = 0; j < n && e; ++j) if (key[j] < k && best[j] == b && acc[j] > retain) e = 0;
+    }
+    emit[c] = e;
+}
+
+// K5b: output position = emitting candidates in front
+__global__ void kfdbWriteKernel(int* __restrict__ counters, const unsigned long long* __restrict__ key, const int* __restrict__ best,
+                                const int* __restrict__ emit, int32_t* __restrict__ out, int cap, int* __restrict__ nOut)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x, n = counters[1];
+    if (c >= n || !emit[c]) return;
+    const unsigned long long k = key[c];
+    int pos = 0;
+    for (int j = 0; j < n; ++j) pos += (emit[j] && key[j] < k);
+    if (pos < cap) out[pos] = best[c];
+    atomicAdd(nOut, 1);
+}
+
+template <typename T> static int growArray(Ctx* c, T*& p, size_t oldN, size_t newN)
+{
+    T* q = nullptr;
+    ORBX_CUDA(c, cudaMalloc(&q, sizeof(T) * newN));
+    if (p && oldN) ORBX_CUDA(c, cudaMemcpyAsync(q, p, sizeof(T) * oldN, cudaMemcpyDeviceToDevice, c->stream));
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (p) cudaFree(p);
+    p = q;
+    return ORBX_OK;
+}
+
+} // namespace orbx
+using namespace orbx;
+
+static int kfdbGrowSlots(orbx_kfdb* d, int need)
+{
+    if (need <= d->slotsCap) return ORBX_OK;
+    Ctx* c = &d->ctx->c;
+    size_t n = d->slotsCap ? (size_t)d->slotsCap : 1024;
+    while (n < (size_t)need) n *= 2;
+    const size_t o = (size_t)d->nslots;
+    int rc;
+#define G(p) if ((rc = growArray(c, d->p, o, n))) return rc
+    G(dSeg); G(dLen); G(dKfId); G(dAlive); G(dLoopQuery); G(dRelocQuery); G(dLoopWords); G(dRelocWords); G(dLoopScore); G(dRelocScore);
+    G(dExclStamp); G(dInList); G(dFirstWord); G(dKey); G(dCandSlot); G(dBest); G(dEmit); G(dAcc);
+#undef G
+    if ((rc = growArray(c, d->dNeigh, o * 10, n * 10))) return rc;
+    d->slotsCap = (int)n;
+    return ORBX_OK;
+}
+
+static int kfdbGrowIds(orbx_kfdb* d, int id)
+{
+    if (id < d->idCap) return ORBX_OK;
+    Ctx* c = &d->ctx->c;
+    size_t n = d->idCap ? (size_t)d->idCap : 1024;
+    while (n <= (size_t)id) n *= 2;
+    int rc = growArray(c, d->dSlotOfId, (size_t)d->idCap, n);
+    if (rc) return rc;
+    const int fresh = (int)n - d->idCap;
+    kfdbFillKernel<<<(fresh + 255) / 256, 256, 0, c->stream>>>(d->dSlotOfId + d->idCap, fresh, -1);
+    ORBX_CUDA(c, cudaGetLastError());
+    d->idCap = (int)n;
+    return ORBX_OK;
+}
+
+// KeyFrameDatabase::KeyFrameDatabase, src/KeyFrameDatabase.cc:38-42
+extern "C" int orbx_kfdb_create(orbx_ctx* h, int nwords, orbx_kfdb** out)
+{
+    if (!h || !out || nwords < 1) return ORBX_E_INVALID;
+    *out = nullptr;
+    Ctx* c = &h->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    orbx_kfdb* d = new (std::nothrow) orbx_kfdb();
+    if (!d) return ORBX_E_NOMEM;
+    d->ctx = h; d->nwords = nwords;
+    int rc = ORBX_OK;
+    if (cudaMalloc(&d->dBitmap, sizeof(uint32_t) * ((size_t)nwords / 32 + 1)) != cudaSuccess ||
+        cudaMalloc(&d->dCounters, sizeof(int) * 8) != cudaSuccess) rc = ORBX_E_CUDA;
+    if (!rc) rc = kfdbGrowSlots(d, 1);
+    if (!rc) rc = kfdbGrowIds(d, 0);
+    if (rc) { orbx_kfdb_destroy(d); return rc; }
+    *out = d;
+    return ORBX_OK;
+}
+
+extern "C" void orbx_kfdb_destroy(orbx_kfdb* d)
+{
+    if (!d) return;
+    Ctx* c = &d->ctx->c;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    void* all[] = {d->dIds, d->dVals, d->dSeg, d->dLen, d->dKfId, d->dAlive, d->dNeigh, d->dLoopQuery, d->dRelocQuery, d->dLoopWords,
+                   d->dRelocWords, d->dLoopScore, d->dRelocScore, d->dExclStamp, d->dInList, d->dFirstWord, d->dKey, d->dCandSlot, d->dBest,
+                   d->dEmit, d->dAcc, d->dSlotOfId, d->dBitmap, d->dQIds, d->dQVals, d->dConn, d->dCounters, d->dOut, d->dNOut};
+    for (void* p : all) if (p) cudaFree(p);
+    delete d;
+}
+
+extern "C" int orbx_kfdb_size(const orbx_kfdb* d) { return d ? (int)d->slotOf.size() : ORBX_E_INVALID; }
+
+// KeyFrameDatabase::add, :50-56.  words: ascending word ids of pKF->mBowVec, vals their weights (HOST arrays).
+extern "C" int orbx_kfdb_add(orbx_kfdb* d, int kf_id, const int32_t* words, const double* vals, int n)
+{
+    if (!d || kf_id < 0 || kf_id >= (1 << 28) || n < 0 || (n > 0 && (!words || !vals))) return ORBX_E_INVALID;
+    if (d->slotOf.count(kf_id)) return ORBX_E_INVALID;                        // the reference would list it twice; nothing does that
+    for (int i = 0; i < n; ++i) if (words[i] < 0 || words[i] >= d->nwords || (i && words[i] <= words[i - 1])) return ORBX_E_INVALID;
+    Ctx* c = &d->ctx->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    int rc;
+    if ((rc = kfdbGrowSlots(d, d->nslots + 1)) || (rc = kfdbGrowIds(d, kf_id))) return rc;
+    if (d->entries + (size_t)n > d->entriesCap) {
+        size_t cap = d->entriesCap ? d->entriesCap : ((size_t)1 << 20);
+        while (cap < d->entries + (size_t)n) cap *= 2;
+        if ((rc = growArray(c, d->dIds, d->entries, cap)) || (rc = growArray(c, d->dVals, d->entries, cap))) return rc;
+        d->entriesCap = cap;
+    }
+    if (n) {
+        ORBX_CUDA(c, cudaMemcpyAsync(d->dIds + d->entries, words, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+        ORBX_CUDA(c, cudaMemcpyAsync(d->dVals + d->entries, vals, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    }
+    const int slot = d->nslots;
+    kfdbInitSlotKernel<<<1, 32, 0, c->stream>>>(slot, (int)d->entries, n, kf_id, d->dSeg, d->dLen, d->dKfId, d->dAlive, d->dNeigh, d->dLoopQuery,
+                                                d->dRelocQuery, d->dLoopWords, d->dRelocWords, d->dLoopScore, d->dRelocScore, d->dExclStamp, d->dSlotOfId);
+    ORBX_CUDA(c, cudaGetLastError());
+    c->kernelLaunches++;
+    d->entries += (size_t)n; d->nslots++;
+    d->slotOf[kf_id] = slot; d->idOfSlot.push_back(kf_id);
+    return ORBX_OK;
+}
+
+// KeyFrameDatabase::erase, :64-83
+extern "C" int orbx_kfdb_erase(orbx_kfdb* d, int kf_id)
+{
+    if (!d) return ORBX_E_INVALID;
+    auto it = d->slotOf.find(kf_id);
+    if (it == d->slotOf.end()) return ORBX_OK;                                // like the reference: nothing to remove
+    Ctx* c = &d->ctx->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    kfdbEraseKernel<<<1, 1, 0, c->stream>>>(it->second, kf_id, d->dAlive, d->dSlotOfId);
+    ORBX_CUDA(c, cudaGetLastError());
+    c->kernelLaunches++;
+    d->slotOf.erase(it);
+    return ORBX_OK;
+}
+
+// KeyFrameDatabase::clear, :85-89
+extern "C" int orbx_kfdb_clear(orbx_kfdb* d)
+{
+    if (!d) return ORBX_E_INVALID;
+    Ctx* c = &d->ctx->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    if (d->idCap) { kfdbFillKernel<<<(d->idCap + 255) / 256, 256, 0, c->stream>>>(d->dSlotOfId, d->idCap, -1); ORBX_CUDA(c, cudaGetLastError()); }
+    d->nslots = 0; d->entries = 0; d->slotOf.clear(); d->idOfSlot.clear();
+    return ORBX_OK;
+}
+
+// The list pKF->GetBestCovisibilityKeyFrames(10) returns (src/KeyFrame.cc:248-258): keyframe ids, strongest first; the
+// database keeps the first 10.  Ids that are not in the database (yet, or any more) are fine: such a keyframe is never met
+// by a query.  Call it whenever the keyframe's ordered connections change (KeyFrame::UpdateBestCovisibles).
+extern "C" int orbx_kfdb_set_covisible(orbx_kfdb* d, int kf_id, const int32_t* ids, int n)
+{
+    if (!d || n < 0 || (n > 0 && !ids)) return ORBX_E_INVALID;
+    auto it = d->slotOf.find(kf_id);
+    if (it == d->slotOf.end()) return ORBX_E_INVALID;
+    Ctx* c = &d->ctx->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    Neigh10 nb;
+    int m = 0;
+    for (int i = 0; i < n && m < 10; ++i) if (ids[i] >= 0) nb.id[m++] = ids[i];   // the first 10 of the list
+    for (; m < 10; ++m) nb.id[m] = -1;
+    kfdbSetNeighKernel<<<1, 32, 0, c->stream>>>(it->second, nb, d->dNeigh);
+    ORBX_CUDA(c, cudaGetLastError());
+    c->kernelLaunches++;
+    return ORBX_OK;
+}
+
+namespace orbx {
+// enqueue one query; dQ* = the query's BowVector on the device; results to dOut[0, cap) / *dNOut
+static int kfdbEnqueue(orbx_kfdb* d, int loop, long long qid, const int32_t* dQIds, const double* dQVals, int nq, int nconn, float minScore,
+                       int32_t* dOut, int cap, int* dNOut)
+{
+    Ctx* c = &d->ctx->c;
+    const int N = d->nslots;
+    ORBX_CUDA(c, cudaMemsetAsync(dNOut, 0, sizeof(int), c->stream));
+    if (!N || !nq) return ORBX_OK;
+    d->stamp++;
+    ORBX_CUDA(c, cudaMemsetAsync(d->dBitmap, 0, sizeof(uint32_t) * ((size_t)d->nwords / 32 + 1), c->stream));
+    const int nb = std::max(std::max(nq, nconn), 1);
+    kfdbBeginKernel<<<(nb + 255) / 256, 256, 0, c->stream>>>(dQIds, nq, d->nwords, d->dBitmap, d->dConn, nconn, d->dSlotOfId, d->idCap,
+                                                            d->dExclStamp, d->stamp, d->dCounters, loop ? minScore : 0.f);
+    long long* query = loop ? d->dLoopQuery : d->dRelocQuery;
+    int* words = loop ? d->dLoopWords : d->dRelocWords;
+    float* score = loop ? d->dLoopScore : d->dRelocScore;
+    const int warpGrid = (N + 7) / 8, candGrid = (N + 127) / 128;
+    kfdbSharedKernel<<<warpGrid, 256, 0, c->stream>>>(N, d->dSeg, d->dLen, d->dAlive, d->dIds, d->dBitmap, loop, qid, d->dExclStamp, d->stamp,
+                                                     query, words, d->dInList, d->dFirstWord, d->dCounters);
+    kfdbScoreKernel<<<warpGrid, 256, 0, c->stream>>>(N, d->dSeg, d->dLen, d->dIds, d->dVals, d->dBitmap, dQIds, dQVals, nq, loop, minScore,
+                                                    d->dInList, words, d->dFirstWord, score, d->dCounters, d->dKey, d->dCandSlot);
+    // the candidate count stays on the device: the three candidate kernels are sized for the worst case and exit early
+    kfdbGroupKernel<<<candGrid, 128, 0, c->stream>>>(d->dCounters, d->dCandSlot, d->dNeigh, d->dSlotOfId, d->idCap, d->dKfId, loop, qid, query,
+                                                    words, score, d->dAcc, d->dBest, d->dCounters + 2);
+    kfdbEmitKernel<<<candGrid, 128, 0, c->stream>>>(d->dCounters, d->dKey, d->dAcc, d->dBest, d->dEmit);
+    kfdbWriteKernel<<<candGrid, 128, 0, c->stream>>>(d->dCounters, d->dKey, d->dBest, d->dEmit, dOut, cap, dNOut);
+    ORBX_CUDA(c, cudaGetLastError());
+    return ORBX_OK;
+}
+
+static int kfdbEnsureQuery(orbx_kfdb* d, int nq, int nconn, int outInts, int queries)
+{
+    Ctx* c = &d->ctx->c;
+    if (nq > d->qCap) {
+        if (d->dQIds) { cudaStreamSynchronize(c->stream); cudaFree(d->dQIds); cudaFree(d->dQVals); d->dQIds = nullptr; d->dQVals = nullptr; d->qCap = 0; }
+        const int cap = std::max(4096, nq + nq / 2);
+        ORBX_CUDA(c, cudaMalloc(&d->dQIds, sizeof(int32_t) * (size_t)cap));
+        ORBX_CUDA(c, cudaMalloc(&d->dQVals, sizeof(double) * (size_t)cap));
+        d->qCap = cap;
+    }
+    if (nconn > d->connCap) {
+        if (d->dConn) { cudaStreamSynchronize(c->stream); cudaFree(d->dConn); d->dConn = nullptr; d->connCap = 0; }
+        const int cap = std::max(1024, 2 * nconn);
+        ORBX_CUDA(c, cudaMalloc(&d->dConn, sizeof(int) * (size_t)cap));
+        d->connCap = cap;
+    }
+    if (outInts > d->outCap || queries > d->outQueries) {
+        if (d->dOut) { cudaStreamSynchronize(c->stream); cudaFree(d->dOut); cudaFree(d->dNOut); d->dOut = nullptr; d->dNOut = nullptr; }
+        d->outCap = std::max(outInts, 4096); d->outQueries = std::max(queries, 64);
+        ORBX_CUDA(c, cudaMalloc(&d->dOut, sizeof(int32_t) * (size_t)d->outCap));
+        ORBX_CUDA(c, cudaMalloc(&d->dNOut, sizeof(int) * (size_t)d->outQueries));
+    }
+    return ORBX_OK;
+}
+
+static bool ascending(const int32_t* w, int n) { for (int i = 1; i < n; ++i) if (w[i] <= w[i - 1]) return false; return true; }
+} // namespace orbx
+
+// KeyFrameDatabase::DetectLoopCandidates(pKF, minScore), :113-270.  query_id = pKF->mnId, words / vals = pKF->mBowVec (ascending
+// word ids), connected = ids of pKF->GetConnectedKeyFrames().  out_ids receives the candidates in the reference's order,
+// *n_out their number (which may exceed cap: the first cap are written).
+extern "C" int orbx_kfdb_detect_loop(orbx_kfdb* d, long long query_id, const int32_t* words, const double* vals, int nq, const int32_t* connected,
+                                     int nconnected, float min_score, int32_t* out_ids, int cap, int* n_out)
+{
+    if (!d || nq < 0 || nconnected < 0 || cap < 0 || !n_out || (nq > 0 && (!words || !vals)) || (nconnected > 0 && !connected) || (cap > 0 && !out_ids))
+        return ORBX_E_INVALID;
+    if (!ascending(words, nq)) return ORBX_E_INVALID;
+    Ctx* c = &d->ctx->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    int rc = kfdbEnsureQuery(d, nq, nconnected, std::max(cap, 1), 1);
+    if (rc) return rc;
+    if (nq) { ORBX_CUDA(c, cudaMemcpyAsync(d->dQIds, words, sizeof(int32_t) * (size_t)nq, cudaMemcpyHostToDevice, c->stream));
+              ORBX_CUDA(c, cudaMemcpyAsync(d->dQVals, vals, sizeof(double) * (size_t)nq, cudaMemcpyHostToDevice, c->stream)); }
+    if (nconnected) ORBX_CUDA(c, cudaMemcpyAsync(d->dConn, connected, sizeof(int) * (size_t)nconnected, cudaMemcpyHostToDevice, c->stream));
+    stageBegin(c, ST_BOW);
+    rc = kfdbEnqueue(d, 1, query_id, d->dQIds, d->dQVals, nq, nconnected, min_score, d->dOut, cap, d->dNOut);
+    stageEnd(c, ST_BOW, (d->nslots && nq) ? 6 : 0);
+    if (rc) return rc;
+    int n = 0;
+    ORBX_CUDA(c, cudaMemcpyAsync(&n, d->dNOut, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    if (cap) ORBX_CUDA(c, cudaMemcpyAsync(out_ids, d->dOut, sizeof(int32_t) * (size_t)cap, cudaMemcpyDeviceToHost, c->stream));
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    *n_out = n;
+    return ORBX_OK;
+}
+
+// KeyFrameDatabase::DetectRelocalizationCandidates(F), :275-399, for nqueries frames per call, in order (a later query sees the
+// mRelocScore values the earlier ones left, as it would in the reference).  query_ids[q] = F->mnId; the BowVector of query q
+// is words / vals [seg[q], seg[q + 1]) (HOST arrays, seg has nqueries + 1 entries).  Candidates of query q go to
+// out_ids[q * cap ...], their number to n_out[q].  One synchronisation for the whole batch.
+extern "C" int orbx_kfdb_detect_reloc(orbx_kfdb* d, int nqueries, const long long* query_ids, const int32_t* words, const double* vals,
+                                      const int32_t* seg, int32_t* out_ids, int cap, int* n_out)
+{
+    if (!d || nqueries < 0 || cap < 0 || (nqueries > 0 && (!query_ids || !seg || !n_out)) || (cap > 0 && nqueries > 0 && !out_ids)) return ORBX_E_INVALID;
+    if (nqueries == 0) return ORBX_OK;
+    const int total = seg[nqueries];
+    if (seg[0] != 0 || total < 0 || (total > 0 && (!words || !vals))) return ORBX_E_INVALID;
+    for (int q = 0; q < nqueries; ++q) if (seg[q + 1] < seg[q] || !ascending(words + seg[q], seg[q + 1] - seg[q])) return ORBX_E_INVALID;
+    if ((size_t)nqueries * (size_t)std::max(cap, 1) > ((size_t)1 << 30)) return ORBX_E_CAPACITY;
+    Ctx* c = &d->ctx->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    int rc = kfdbEnsureQuery(d, total, 0, nqueries * std::max(cap, 1), nqueries);
+    if (rc) return rc;
+    if (total) { ORBX_CUDA(c, cudaMemcpyAsync(d->dQIds, words, sizeof(int32_t) * (size_t)total, cudaMemcpyHostToDevice, c->stream));
+                 ORBX_CUDA(c, cudaMemcpyAsync(d->dQVals, vals, sizeof(double) * (size_t)total, cudaMemcpyHostToDevice, c->stream)); }
+    stageBegin(c, ST_BOW);
+    int launches = 0;
+    for (int q = 0; q < nqueries && !rc; ++q) {
+        const int nq = seg[q + 1] - seg[q];
+        rc = kfdbEnqueue(d, 0, query_ids[q], d->dQIds + seg[q], d->dQVals + seg[q], nq, 0, 0.f, d->dOut + (size_t)q * cap, cap, d->dNOut + q);
+        if (d->nslots && nq) launches += 6;
+    }
+    stageEnd(c, ST_BOW, launches);
+    if (rc) return rc;
+    ORBX_CUDA(c, cudaMemcpyAsync(n_out, d->dNOut, sizeof(int) * (size_t)nqueries, cudaMemcpyDeviceToHost, c->stream));
+    if (cap) ORBX_CUDA(c, cudaMemcpyAsync(out_ids, d->dOut, sizeof(int32_t) * (size_t)nqueries * cap, cudaMemcpyDeviceToHost, c->stream));
+    ORBX_CUDA(c, cudaStreamSynchronize(c->stream));
+    return ORBX_OK;
+}
