@@ -169,6 +169,43 @@ def cpu_ref_fps(frames, threads, nframes):
     return float(fps), int(nframes), dt
 
 
+def cpu_variants(frames, threads):
+    """The other CPU baselines BASELINE.md section 4 names, as bounded samples of the same workload: the reference build on ONE
+    thread, and the reference sources rebuilt with host-tuned flags (-march=x86-64-v3, oracle/Makefile ref_v3) on all
+    threads.  The tuned library runs in a process of its own (it carries its own copy of every reference symbol)."""
+    out = {}
+    try:
+        one = cpu_ref_fps(frames, 1, 8)
+        if one:
+            fps, n, dt = cpu_ref_fps(frames, 1, max(8, int(one[0] * 3.0)))
+            out["one_thread"] = {"value": fps, "unit": "frames/s", "cores": 1, "sample": f"{n} frames in {dt:.1f}s"}
+        so = os.path.join(ROOT, "oracle", "_ref", "liborb_ref_v3.so")
+        flags = open("/proc/cpuinfo").read()
+        if os.path.exists(so) and all(f in flags for f in (" avx2", " fma", " bmi2")):
+            code = ("import ctypes,sys,numpy as np\n"
+                    "L=ctypes.CDLL(sys.argv[1]); vp,ci,cf=ctypes.c_void_p,ctypes.c_int,ctypes.c_float\n"
+                    "L.ref_extract_throughput.argtypes=[ci,cf,ci,ci,ci,vp,ci,ci,ci,ci,ci,vp]; L.ref_extract_throughput.restype=ctypes.c_double\n"
+                    "L.ref_set_allocator.argtypes=[ci]; L.ref_set_allocator(0)\n"
+                    "fr=np.load(sys.argv[2]); t=ctypes.c_longlong(); a=[int(x) for x in sys.argv[3:]]\n"
+                    "f=L.ref_extract_throughput(a[0],1.2,a[1],a[2],a[3],fr.ctypes.data,len(fr),a[4],a[5],a[6],a[7],ctypes.byref(t))\n"
+                    "f=L.ref_extract_throughput(a[0],1.2,a[1],a[2],a[3],fr.ctypes.data,len(fr),a[4],a[5],a[6]*6,a[7],ctypes.byref(t))\n"
+                    "print(f)")
+            import tempfile
+            with tempfile.TemporaryDirectory() as td:
+                np.save(os.path.join(td, "f.npy"), np.ascontiguousarray(frames))
+                n = 8 * threads
+                r = subprocess.run([sys.executable, "-c", code, so, os.path.join(td, "f.npy")] +
+                                   [str(x) for x in (NFEAT, NLEVELS, INI, MINTH, W, H, n, threads)], capture_output=True, text=True, timeout=120)
+            if r.returncode == 0:
+                out["march_x86_64_v3"] = {"value": float(r.stdout.strip().splitlines()[-1]), "unit": "frames/s", "cores": threads,
+                                          "sample": f"{6 * n} frames; reference sources, -O3 -march=x86-64-v3 (AVX2, FMA), contraction allowed"}
+            else:
+                out["march_x86_64_v3"] = {"error": r.stderr[-200:]}
+    except Exception as e:
+        out["error"] = repr(e)[:200]
+    return out
+
+
 def cpu_baseline(frames, threads, seconds):
     """The CPU arm: the reference library when present (kind "reference"), else the oracle port (kind "port")."""
     probe = cpu_ref_fps(frames, threads, 4 * threads)
@@ -397,6 +434,19 @@ def cpp_latency():
                      "with_pyramid_mirror also downloads the eight bordered levels into mvImagePyramid, the reference's default surface")
         return d
     except Exception as e:  # the driver is a measurement aid, not part of the metric
+        return {"error": repr(e)[:200]}
+
+
+def kfdb_line(ex):
+    """KeyFrameDatabase queries on the device against the unmodified reference class on one host core."""
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_kfdb
+        d = bench_kfdb.measure(3000, 100, ex)
+        d["note"] = ("DetectRelocalizationCandidates / DetectLoopCandidates over 3000 keyframes of ~860 words (10^6-word vocabulary): "
+                     "host BowVector in, ordered candidate ids out, per query")
+        return d
+    except Exception as e:  # a measurement aid, not part of the metric
         return {"error": repr(e)[:200]}
 
 
@@ -633,9 +683,11 @@ def run_orbx(args, rank, world):
         cores = len(all_cpus) or 1
         lat = cpp_latency()
         hcpu = hamming_cpu_baseline(cores)
+        kf = kfdb_line(ex)
         fps_all, n_all, dt_all, kind, note = cpu_baseline(frames[:8], cores, 8.0)
         cpu = {"value": fps_all, "unit": "frames/s", "cores": cores, "kind": kind,
-               "sample": f"{n_all} frames of the same workload in {dt_all:.1f}s on {cores} host threads; {note}"}
+               "sample": f"{n_all} frames of the same workload in {dt_all:.1f}s on {cores} host threads; {note}",
+               "variants": cpu_variants(frames[:8], cores) if abs(SCALE - 1.2) < 1e-6 else {}}
         line = {"metric": "orb_extract_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic",
@@ -655,6 +707,7 @@ def run_orbx(args, rank, world):
                              "pipeline_frac": total_alg * value / world / 1e9 / hbm, "stage_ms_per_step": stage_ms},
                 "cpu_baseline": cpu,
                 "cpp_latency": lat,
+                "kfdb": kf,
                 "hamming": {"metric": "hamming_gmatch_per_s", "value": gm_total, "unit": "GMatch/s", "per_gpu": gm,
                             "cpu_baseline": hcpu, "match_e2e": me,
                             "workload": "brute force 10000 x 10000 descriptors per keyframe pair, 32 pairs per GPU per call, device resident",

@@ -10,7 +10,7 @@
 #include <vector>
 #include <opencv2/core.hpp>
 
-namespace DBoW2 { typedef std::map<unsigned int, std::vector<unsigned int> > FeatureVector; }
+namespace DBoW2 { typedef std::map<unsigned int, std::vector<unsigned int> > FeatureVector; typedef std::map<unsigned int, double> BowVector; }
 
 namespace ORB_SLAM2
 {
@@ -51,6 +51,8 @@ public:
 class Frame
 {
 public:
+    long unsigned int mnId = 0;
+    DBoW2::BowVector mBowVec;
     int N;
     cv::Mat mDescriptors;
     std::vector<cv::KeyPoint> mvKeys, mvKeysUn;
@@ -70,6 +72,13 @@ public:
 class KeyFrame
 {
 public:
+    long unsigned int mnId = 0;
+    DBoW2::BowVector mBowVec;
+    // covisibility graph, reduced to what KeyFrameDatabase reads (src/KeyFrame.cc:225-233, :248-258)
+    std::set<KeyFrame*> GetConnectedKeyFrames() { std::set<KeyFrame*> s; for (std::map<KeyFrame*, int>::iterator it = mConnectedKeyFrameWeights.begin(); it != mConnectedKeyFrameWeights.end(); ++it) s.insert(it->first); return s; }
+    std::vector<KeyFrame*> GetBestCovisibilityKeyFrames(const int& n) { return (int)mvpOrderedConnectedKeyFrames.size() < n ? mvpOrderedConnectedKeyFrames : std::vector<KeyFrame*>(mvpOrderedConnectedKeyFrames.begin(), mvpOrderedConnectedKeyFrames.begin() + n); }
+    std::map<KeyFrame*, int> mConnectedKeyFrameWeights;
+    std::vector<KeyFrame*> mvpOrderedConnectedKeyFrames;
     int N;
     cv::Mat mDescriptors;
     std::vector<cv::KeyPoint> mvKeysUn;

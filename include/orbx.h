@@ -195,7 +195,7 @@ typedef struct {          /* one side of a match job; all pointers host or devic
     const float* uright;          /* mvuRight, or NULL for monocular */
     int n;
     int nnodes;                   /* FeatureVector CSR (orbx_feature_vector layout) */
-    const int32_t* node_id; const int32_t* node_off; const int32_t* feat;
+    const int32_t* node_id; const int32_t* node_off; const int32_t* feat;   /* HOST arrays; a feat[] entry outside [0, n) -> ORBX_E_INVALID */
 } orbx_bow_side;
 typedef struct {          /* SearchForTriangulation geometry, computed by the caller as at :920-929 */
     float F12[9];                 /* row-major */
@@ -317,6 +317,9 @@ int orbx_kfdb_clear(orbx_kfdb* db);                                           /*
 /* What pKF->GetBestCovisibilityKeyFrames(10) returns (src/KeyFrame.cc:248-258): ids, strongest first (the first 10 are
  * kept).  Call it when the keyframe's ordered connections change; ids not in the database are fine (never met by a query). */
 int orbx_kfdb_set_covisible(orbx_kfdb* db, int kf_id, const int32_t* ids, int n);
+/* The same for n keyframes in one call: kf_ids[i]'s list is neigh[10 * i .. 10 * i + 10), padded with -1 (HOST arrays).  For a
+ * caller without a hook in KeyFrame::UpdateBestCovisibles: refresh every keyframe's list in front of a query. */
+int orbx_kfdb_set_covisible_bulk(orbx_kfdb* db, int n, const int32_t* kf_ids, const int32_t* neigh);
 /* DetectLoopCandidates(pKF, minScore) :113-270: query_id = pKF->mnId, words / vals = pKF->mBowVec, connected = the ids of
  * pKF->GetConnectedKeyFrames().  out_ids = candidate ids in the reference's order; *n_out = how many there are (the first
  * cap are written).  The per-keyframe query state (mnLoopQuery, mnLoopWords, mLoopScore) persists between calls as in the

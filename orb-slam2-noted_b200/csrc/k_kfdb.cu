@@ -69,6 +69,17 @@ __global__ void kfdbInitSlotKernel(int slot, int seg, int len, int id, int* dSeg
 
 struct Neigh10 { int id[10]; };
 __global__ void kfdbSetNeighKernel(int slot, Neigh10 nb, int* dNeigh) { if (threadIdx.x < 10) dNeigh[slot * 10 + threadIdx.x] = nb.id[threadIdx.x]; }
+// neigh: n x 10 ids (-1 padded) of the keyframes ids[0..n)
+__global__ void kfdbSetNeighBulkKernel(const int* __restrict__ ids, const int* __restrict__ neigh, int n, const int* __restrict__ slotOfId, int idCap,
+                                       int* __restrict__ dNeigh)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * 10) return;
+    const int id = ids[i / 10];
+    if (id < 0 || id >= idCap) return;
+    const int s = slotOfId[id];
+    if (s >= 0) dNeigh[s * 10 + i % 10] = neigh[i];
+}
 __global__ void kfdbEraseKernel(int slot, int id, int* dAlive, int* slotOfId) { dAlive[slot] = 0; slotOfId[id] = -1; }
 __global__ void kfdbFillKernel(int* p, int n, int v) { const int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) p[i] = v; }
 
@@ -372,6 +383,25 @@ extern "C" int orbx_kfdb_set_covisible(orbx_kfdb* d, int kf_id, const int32_t* i
     for (int i = 0; i < n && m < 10; ++i) if (ids[i] >= 0) nb.id[m++] = ids[i];   // the first 10 of the list
     for (; m < 10; ++m) nb.id[m] = -1;
     kfdbSetNeighKernel<<<1, 32, 0, c->stream>>>(it->second, nb, d->dNeigh);
+    ORBX_CUDA(c, cudaGetLastError());
+    c->kernelLaunches++;
+    return ORBX_OK;
+}
+
+// The same for n keyframes in one call (one copy, one launch): kf_ids[i]'s list is neigh[10 * i ... 10 * i + 10), -1 padded.
+// What a caller without a hook in KeyFrame::UpdateBestCovisibles does in front of a query: refresh every keyframe's list.
+extern "C" int orbx_kfdb_set_covisible_bulk(orbx_kfdb* d, int n, const int32_t* kf_ids, const int32_t* neigh)
+{
+    if (!d || n < 0 || (n > 0 && (!kf_ids || !neigh))) return ORBX_E_INVALID;
+    if (n == 0) return ORBX_OK;
+    Ctx* c = &d->ctx->c;
+    ORBX_CUDA(c, cudaSetDevice(c->device));
+    int rc = ensureScratch(c, sizeof(int) * (size_t)n * 11 + 256);
+    if (rc) return rc;
+    int* dI = (int*)c->dScratch; int* dN = dI + n;
+    ORBX_CUDA(c, cudaMemcpyAsync(dI, kf_ids, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    ORBX_CUDA(c, cudaMemcpyAsync(dN, neigh, sizeof(int) * (size_t)n * 10, cudaMemcpyHostToDevice, c->stream));
+    kfdbSetNeighBulkKernel<<<(n * 10 + 255) / 256, 256, 0, c->stream>>>(dI, dN, n, d->dSlotOfId, d->idCap, d->dNeigh);
     ORBX_CUDA(c, cudaGetLastError());
     c->kernelLaunches++;
     return ORBX_OK;

@@ -433,6 +433,9 @@ static int matchBowPairs(Ctx* c, int mode, int npairs, const orbx_bow_side* cons
         }
         P.nseg = (int)P.segs.size();
         P.len1 = s1->nnodes ? s1->node_off[s1->nnodes] : 0; P.len2 = s2->nnodes ? s2->node_off[s2->nnodes] : 0;
+        if ((P.len1 > 0 && !s1->feat) || (P.len2 > 0 && !s2->feat) || P.len1 < 0 || P.len2 < 0) return ORBX_E_INVALID;
+        for (int i = 0; i < P.len1; ++i) if ((unsigned)s1->feat[i] >= (unsigned)s1->n) return ORBX_E_INVALID;   // the kernels index desc / keys with these
+        for (int i = 0; i < P.len2; ++i) if ((unsigned)s2->feat[i] >= (unsigned)s2->n) return ORBX_E_INVALID;
         P.oSeg = B.take(sizeof(int4) * (size_t)std::max(P.nseg, 1)); P.oTp = B.take(sizeof(int32_t) * (size_t)(P.nseg + 1));
         P.oTop = B.take(sizeof(uint32_t) * kTopK * (size_t)std::max(P.len1, 1)); P.oHist = B.take(sizeof(int) * (kHisto + 1));
         P.oIdx1 = B.take(sizeof(int32_t) * (size_t)std::max(P.len1, 1)); P.oIdx2 = B.take(sizeof(int32_t) * (size_t)std::max(P.len2, 1));

@@ -73,3 +73,49 @@ def test_cpp_dropin_matcher(tmp_path):
 def pkg_mod():
     from gpu_util import pkg
     return pkg()
+
+
+def _kfdb_script_bytes(ops):
+    """tests/kfdb_scene.py operations in the record format of host/orbx_cpp_kfdb_driver.cc"""
+    import struct
+    import numpy as np
+    code = {"new": 0, "add": 1, "erase": 2, "covis": 3, "loop": 4, "reloc": 5, "clear": 6}
+    out = bytearray()
+    for op in ops:
+        k = op[0]
+        if k in ("new", "reloc"):
+            w, v = np.asarray(op[2], np.int32), np.asarray(op[3], np.float64)
+            out += struct.pack("<iii", code[k], op[1], len(w)) + w.tobytes() + v.tobytes()
+        elif k == "covis":
+            a = np.asarray(op[2], np.int32)
+            out += struct.pack("<iii", 3, op[1], len(a)) + a.tobytes()
+        elif k == "loop":
+            a = np.asarray(op[2], np.int32)
+            out += struct.pack("<iii", 4, op[1], len(a)) + a.tobytes() + struct.pack("<f", op[3])
+        else:
+            out += struct.pack("<iii", code[k], op[1] if len(op) > 1 else 0, 0)
+    return bytes(out)
+
+
+def test_cpp_dropin_keyframe_database(tmp_path):
+    """include/KeyFrameDatabase.h on KeyFrame / Frame stand-ins: add / erase / DetectLoopCandidates /
+    DetectRelocalizationCandidates return the keyframes the oracle (and, where oracle/_ref is here, the reference class)
+    returns, in the same order, on a generated script and on the hand-made quirk cases."""
+    import kfdb_scene as K
+    import ref_lib as R
+    from test_oracle_kfdb import quirk_script
+    subprocess.run(["make", "-C", os.path.join(ROOT, "host"), "-s"], check=True)
+    for name, (ops, nw) in {"script": K.make_script(21, nkf=400, spread=120.0, places=5), "quirks": quirk_script()}.items():
+        f = tmp_path / (name + ".bin")
+        f.write_bytes(_kfdb_script_bytes(ops))
+        r = subprocess.run([os.path.join(ROOT, "host", "orbx_cpp_kfdb_driver"), str(f), str(nw)], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[-2000:]
+        got = [(ln.split()[0], int(ln.split()[1].rstrip(":")), [int(x) for x in ln.split()[2:]]) for ln in r.stdout.splitlines()]
+        o = K.OracleBackend(nw)
+        want = K.replay(ops, o)
+        o.close()
+        assert got == want and len(got) > 5, [(a, b) for a, b in zip(got, want) if a != b][:3]
+        if os.path.exists(R.SO):
+            rb = K.RefBackend(nw)
+            assert K.replay(ops, rb) == got
+            rb.close()

@@ -173,6 +173,20 @@ def test_configs_geometry_1080p(P):
     assert_kps_equal(kps, okps, desc, odesc, "1080p")
 
 
+def test_1080p_batch_of_64_at_full_size(P):
+    """BASELINE.json configs[4] at its full size: 64 frames of 1920x1080 / 4000 features in one batch (512-thread quadtree CTAs,
+    the staged resize on every level), every frame against the oracle (8 distinct frames, tiled)."""
+    distinct = [synth.frame(900 + i, 1920, 1080, "texture" if i % 4 else "noise") for i in range(8)]
+    imgs = np.stack([distinct[i % 8] for i in range(64)])
+    ex = P.ORBextractor(4000, 1.2, 8, 20, 7, max_w=1920, max_h=1080, max_batch=64)
+    res = ex.extract_batch(imgs)
+    p = O.params(4000)
+    want = [O.extract(p, im) for im in distinct]
+    for b in range(64):
+        assert_kps_equal(res[b][0], want[b % 8][0], res[b][1], want[b % 8][1], b)
+    ex.close()
+
+
 def test_idempotent_and_deterministic(P):
     img = synth.frame(3, 752, 480)
     ex = P.ORBextractor(1200, 1.2, 8, 20, 7, max_w=752, max_h=480)

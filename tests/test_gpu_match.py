@@ -409,7 +409,7 @@ def test_stereo_matches_oracle(P, w, h, nf, seed):
     assert (got_u >= 0).sum() > 100, (int((got_u >= 0).sum()), nv)
 
 
-@pytest.mark.parametrize("w,h,nf,pairs", [(752, 480, 1200, 64), (1241, 376, 2000, 24)])
+@pytest.mark.parametrize("w,h,nf,pairs", [(752, 480, 1200, 64), (1241, 376, 2000, 24), (752, 480, 1200, 512)])   # 512 = configs[2] at full size
 def test_stereo_batch_matches_oracle_and_device_chain(P, w, h, nf, pairs):
     """configs[2] / configs[1] as batches: left and right extract_batch, then ONE orbx_stereo_match_batch, against
     orc_extract + orc_stereo_matches pair by pair (mvuRight / mvDepth as raw bits); then the same chain with everything left
@@ -460,6 +460,23 @@ def test_stereo_batch_matches_oracle_and_device_chain(P, w, h, nf, pairs):
     bad["x"][2::3] = 2.0; bad["y"][2::3] = 1.0
     u2, z2 = P.compute_stereo_matches(exl, exr, bad, d0, k1, d1, bf, b, frame=3)
     assert np.all(u2[::3] == -1) and np.all(u2[1::3] == -1) and np.all(z2[2::3] == -1)
+
+
+def test_feature_vector_indices_are_checked(P, ctx, vocs):
+    """feat[] entries index the descriptor / keypoint arrays on the device: anything outside [0, n) is refused on the host."""
+    _, vo, vg = vocs
+    d1, k1, d2, k2 = make_pair(31, 300, 280, 0.08, 0.0, KP=P.KP_DTYPE)
+    _, sg = sides(P, vo, vg, d1, k1, d2, k2, 2, 31)
+    m = P.ORBmatcher(ctx, 0.75, True)
+    good = m.SearchByBoW(sg[0], sg[1])
+    for side, bad_value in ((0, 300), (1, -1), (1, 1 << 30)):
+        keep = sg[side].feat.copy()
+        sg[side].feat[len(keep) // 2] = bad_value
+        with pytest.raises(P.OrbxError):
+            m.SearchByBoW(sg[0], sg[1])
+        sg[side].feat[:] = keep
+    again = m.SearchByBoW(sg[0], sg[1])
+    assert np.array_equal(good[0], again[0]) and good[1] == again[1]
 
 
 def test_search_by_bow_batch_equals_single_calls(P, ctx, vocs):

@@ -9,9 +9,7 @@ import kfdb_scene as K
 import ref_lib as R
 
 
-def main():
-    nkf = int(sys.argv[1]) if len(sys.argv) > 1 else 4000
-    nq = int(sys.argv[2]) if len(sys.argv) > 2 else 200
+def measure(nkf=4000, nq=200, ex=None):
     P = importlib.import_module("orb-slam2-noted_b200")
     nwords, per_kf, places = 1000000, 900, 60
     rng = np.random.default_rng(1)
@@ -19,7 +17,8 @@ def main():
     bows = [K.bow_vector(rng, nwords, centres[(k // 8) % places] + rng.normal(0, 300), per_kf, 2500.0) for k in range(nkf)]
     covis = [np.array([x for x in range(max(0, k - 10), k)][::-1], np.int32) for k in range(nkf)]
     queries = [K.bow_vector(rng, nwords, centres[int(rng.integers(0, places))] + rng.normal(0, 300), per_kf, 2500.0) for _ in range(nq)]
-    ex = P.ORBextractor(500, 1.2, 8, 20, 7, max_w=64, max_h=64, max_batch=1)
+    if ex is None:
+        ex = P.ORBextractor(500, 1.2, 8, 20, 7, max_w=64, max_h=64, max_batch=1)
     g = K.GpuBackend(nwords, ex)
     t0 = time.perf_counter()
     for k in range(nkf):
@@ -56,8 +55,10 @@ def main():
         out.update({"cpu_reference_reloc_ms_per_query": t_ref * 1e3, "cpu_reference_loop_ms_per_query": t_refl * 1e3,
                     "identical_to_reference": one == ref_one and batch == ref_batch and loops == ref_loops,
                     "cpu": "oracle/_ref: unmodified src/KeyFrameDatabase.cc, 1 thread (the reference holds a mutex for the whole walk)"})
-    print(json.dumps(out))
+        r.close()
+    g.close()
+    return out
 
 
 if __name__ == "__main__":
-    main()
+    print(json.dumps(measure(int(sys.argv[1]) if len(sys.argv) > 1 else 4000, int(sys.argv[2]) if len(sys.argv) > 2 else 200)))
