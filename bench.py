@@ -721,7 +721,7 @@ def run_orbx(args, rank, world):
                 "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": B * W * H,
                         "d2h_bytes_per_step": B * cap * 60 + 4 * B, "steps": e2e_steps,
                         "callers": f"{n_callers} host threads, one extractor handle each, alternate batches through orbx_extract_batch"},
-                "single_frame": {"latency_ms": single_ms, "note": "median of 50 orbx_extract calls, one 640x480 host image in, "
+                "single_frame": {"latency_ms": single_ms, "note": f"median of 50 orbx_extract calls, one {W}x{H} host image in, "
                                  "host keypoints + descriptors out (BASELINE.json configs[0])"},
                 "gpu_launches": int(launches), "clocks": sampler.summary()}
         if stereo:

@@ -3,9 +3,10 @@
 // :325-345, :828-843, :1013-1052; Frame::ComputeStereoMatches src/Frame.cc:937-978).
 //
 // Integer/POPC-pipe bound by design (8 x POPC32 per descriptor pair); no tensor cores.
-// One CTA = up to 256 query rows of one segment (2 per thread, descriptors held in 16 registers);
-// train descriptors stream through shared memory in 128-descriptor chunks and are read as
-// warp-broadcast 128-bit loads, so each LDS feeds 2 x 4 POPCs per thread.
+// One CTA = up to 256 query rows of one segment (kHamQPT = 1 per thread, its descriptor held in 8 registers);
+// the valid train descriptors stream through shared memory in compacted chunks of up to kHamChunk = 256
+// (one staged row per thread) and are read as warp-broadcast 128-bit loads: two LDS.128 feed one 256-bit
+// distance (18 LOP3 of the carry-save tree + 4 POPC, see hamming256 in orbx_internal.h).
 #include "orbx_internal.h"
 #include <algorithm>
 

@@ -509,7 +509,10 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
     // Chunked pipeline: the stages of one chunk run back to back (its pyramid/blur planes stay in the 126 MB L2), and
     // with host buffers the H2D of chunk i+1 and the D2H of chunk i-1 overlap the kernels of chunk i.
     // device-resident input: one pass over the whole batch (larger launches are more efficient and there is no copy to hide)
-    const int chunk = (!inDev && c->chunk > 0) ? c->chunk : batch;
+    // (env ORBX_DEVICE_CHUNK = frames: device-resident batches are cut too and alternate between the two compute streams, so the
+    // latency-bound stages of one chunk -- quadtree, describe -- run beside the ALU-bound FAST of the next)
+    static const int devChunk = getenv("ORBX_DEVICE_CHUNK") ? atoi(getenv("ORBX_DEVICE_CHUNK")) : 0;
+    const int chunk = (!inDev && c->chunk > 0) ? c->chunk : (inDev && devChunk > 0 ? devChunk : batch);
     if (!outDev && c->hPinnedBytes < sizeof(int) * (size_t)c->maxBatch) {   // pinned landing zone for n_out: keeps the D2H asynchronous
         if (c->hPinned) cudaFreeHost(c->hPinned);
         c->hPinned = nullptr; c->hPinnedBytes = 0;
@@ -523,15 +526,15 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
     const int nChunks = (int)cuts.size() - 1;
     while ((int)c->evIn.size() < nChunks) { cudaEvent_t e; ORBX_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); c->evIn.push_back(e); }
     while ((int)c->evDone.size() < nChunks) { cudaEvent_t e; ORBX_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); c->evDone.push_back(e); }
-    if (!inDev) {
+    if (!inDev || nChunks > 1) {
         if (!c->evFence) ORBX_CUDA(c, cudaEventCreateWithFlags(&c->evFence, cudaEventDisableTiming));
         ORBX_CUDA(c, cudaEventRecord(c->evFence, c->stream));
-        ORBX_CUDA(c, cudaStreamWaitEvent(c->sIn, c->evFence, 0));
+        if (!inDev) ORBX_CUDA(c, cudaStreamWaitEvent(c->sIn, c->evFence, 0));
         ORBX_CUDA(c, cudaStreamWaitEvent(c->stream2, c->evFence, 0));
     }
     cudaStream_t const mainStream = c->stream;
     struct StreamRestore { Ctx* c; cudaStream_t s; ~StreamRestore() { c->stream = s; } } restoreStream{c, mainStream};   // also on error returns
-    const bool twoStreams = !inDev && nChunks > 1;
+    const bool twoStreams = nChunks > 1;
     static const bool dbgTl = getenv("ORBX_DBG_TIMELINE") != nullptr;
     std::vector<cudaEvent_t> tl;
     auto mark = [&](cudaStream_t st) { if (!dbgTl) return; cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st); tl.push_back(e); };
