@@ -295,7 +295,7 @@ int orbx_create(orbx_ctx** out, int device, int nfeatures, float scale_factor, i
         if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (const char* e = getenv("ORBX_CHUNK")) c->chunk = atoi(e);
-        if (const char* e = getenv("ORBX_OVERLAP_BLUR")) c->overlapBlur = atoi(e) != 0;
+        if (const char* e = getenv("ORBX_OVERLAP_BLUR")) { c->overlapBlur = atoi(e) != 0; c->blurAfterFast = atoi(e) == 2; }
         if (const char* e = getenv("ORBX_RESIZE_WIDE")) c->resizeWide = atoi(e) != 0;
         if (const char* e = getenv("ORBX_FAST_THREADS")) c->fastThreads = atoi(e) == 128 ? 128 : 256;
         if (const char* e = getenv("ORBX_FAST_SEGW")) c->fastSegW = std::max(64, std::min(640, atoi(e)));
@@ -583,9 +583,12 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
                 ORBX_CUDA(c, cudaEventCreateWithFlags(&c->evFork, cudaEventDisableTiming));
                 ORBX_CUDA(c, cudaEventCreateWithFlags(&c->evBlur, cudaEventDisableTiming));
             }
+            // blurAfterFast: fork AFTER FAST, so the blur shares the GPU with the quadtree only (FAST fills the shared memory of
+            // every SM by itself; the quadtree waits on block scans most of the time and leaves issue slots)
+            if (c->blurAfterFast && !fewCtas) rc = launchFast(c, f0, n);
             ORBX_CUDA(c, cudaEventRecord(c->evFork, s0));
             ORBX_CUDA(c, cudaStreamWaitEvent(c->sBlur, c->evFork, 0));
-            rc = launchFast(c, f0, n);
+            if (!(c->blurAfterFast && !fewCtas)) rc = launchFast(c, f0, n);
             c->stream = c->sBlur;
             if (!rc) rc = launchBlur(c, f0, n);
             c->stream = s0;

@@ -71,6 +71,7 @@ struct Ctx {
     cudaStream_t stream2 = nullptr;               // odd chunks of the pipeline run here, so kernels of neighbouring chunks fill each other's tails
     cudaEvent_t evJoin = nullptr;
     cudaStream_t sBlur = nullptr; cudaEvent_t evFork = nullptr, evBlur = nullptr;   // blur next to FAST + quadtree (device-resident batches)
+    bool blurAfterFast = false;                    // ORBX_OVERLAP_BLUR=2: the blur forks after FAST and runs beside the quadtree only
     bool overlapBlur = false;                      // env ORBX_OVERLAP_BLUR=1: no gain at 640x480 (the kernels are throughput-bound), ~4 % at 1241x376
     std::vector<cudaEvent_t> evIn, evDone;
     cudaEvent_t evFence = nullptr;                // orders a new call's H2D after the previous call's kernels
