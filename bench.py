@@ -488,6 +488,9 @@ def run_orbx(args, rank, world):
         win = comm.window(sh.Comm.carve_bytes(*shapes) if rank == 0 else 0)
         g_k, g_d = sh.Comm.carve(win, *shapes) if win is not None else [torch.empty(s_, dtype=t_, device=dev) for s_, t_ in shapes]
         gather = (torch.empty(world * B, dtype=torch.int32, device=dev), g_k, g_d)
+    # several ranks: the describe stage writes DENSE records (ORBX_OUT_DENSE), so the gather is two peer copies per rank and no
+    # compaction pass; env ORBX_BENCH_PADDED=1 keeps the padded layout + compaction kernel (for A/B runs)
+    dense_out = world > 1 and not os.environ.get("ORBX_BENCH_PADDED")
     step_no = [0]
     pending = [None]                                  # (buffer index, ticket) of the step whose gather has not been issued yet
     gathered_records = [0]
@@ -495,7 +498,7 @@ def run_orbx(args, rank, world):
     def issue_gather():
         if pending[0] is not None:
             k, ticket = pending[0]
-            gathered_records[0] = comm.gather_frames(*bufs[k], gather, root=0, ticket=ticket)
+            gathered_records[0] = comm.gather_frames(*bufs[k], gather, root=0, ticket=ticket, dense=dense_out)
             pending[0] = None
 
     def step():
@@ -503,7 +506,7 @@ def run_orbx(args, rank, world):
         step_no[0] += 1
         if comm is not None and step_no[0] > nbuf:
             comm.wait()                               # the extraction stream waits (on the device) for the gather that read this buffer pair
-        ex.extract_batch_device(d_img, *bufs[k])
+        ex.extract_batch_device(d_img, *bufs[k], dense=dense_out)
         if comm is not None:
             ticket = comm.mark()
             issue_gather()                            # the previous step's, now that this step's kernels are queued behind it
@@ -698,7 +701,7 @@ def run_orbx(args, rank, world):
                                  else "no NUMA binding"),
                         **({"ranks": per_rank} if per_rank else {}),
                         "parallelism": f"frames sharded, {world} rank(s)" + (f", every step's results gathered to rank 0 as compact records (orbx_gather_frames on its own stream: device-side scan, then "
-                                                                                  + ("each rank compacts and writes its records into rank 0's peer window over NVLink (CUDA IPC, DMA engines)" if comm.stats()[0] else "compaction + grouped ncclSend/ncclRecv")
+                                                                                  + (("dense records (ORBX_OUT_DENSE), " if dense_out else "compaction kernel, ") + ("each rank writes its records into rank 0's peer window over NVLink (CUDA IPC, DMA engines)" if comm.stats()[0] else "grouped ncclSend/ncclRecv"))
                                                                                   + f"; {gathered_records[0]} records in the last step; gathers direct/staged: {comm.stats()})" if world > 1 else "")},
                 "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
                              "traffic": traffic, "traffic_source": traffic_src, "alu_frac": alu_frac,

@@ -33,7 +33,8 @@ typedef enum {
     ORBX_E_UNSUPPORTED = -5  /* geometry the reference itself cannot process (e.g. width/height < 0.5) */
 } orbx_status;
 
-enum { ORBX_IN_DEVICE = 1, ORBX_OUT_DEVICE = 2 }; /* flags: where image / result buffers live */
+enum { ORBX_IN_DEVICE = 1, ORBX_OUT_DEVICE = 2,   /* flags: where image / result buffers live */
+       ORBX_OUT_DENSE = 4 };                      /* orbx_extract_batch with both of the above: see there */
 
 #define ORBX_MAX_LEVELS 16
 
@@ -69,6 +70,9 @@ int orbx_extract(orbx_ctx* ctx, const uint8_t* img, int w, int h, size_t stride,
 /* B frames of identical geometry, frame b at imgs + b*frame_stride.  Results for frame b are written at
  * kps + b*cap_per_frame, desc + b*cap_per_frame*32, n_out[b].  With ORBX_OUT_DEVICE the call is
  * asynchronous on the ctx stream (use orbx_sync). */
+/* With ORBX_IN_DEVICE | ORBX_OUT_DEVICE | ORBX_OUT_DENSE the records are written DENSE: frame b's n_out[b] keypoints and
+ * descriptors start at row sum(n_out[0..b)) of kps / desc instead of row b * cap_per_frame (the buffers are sized as before;
+ * cap_per_frame still bounds a frame).  That is the layout orbx_gather_frames_dense sends without a compaction pass. */
 int orbx_extract_batch(orbx_ctx* ctx, const uint8_t* imgs, int batch, int w, int h, size_t stride,
                        size_t frame_stride, int flags, orbx_keypoint* kps, uint8_t* desc,
                        int cap_per_frame, int* n_out);
@@ -279,6 +283,12 @@ int orbx_comm_sync(orbx_comm* comm);
 int orbx_gather_frames(orbx_comm* comm, orbx_ctx* ctx, int ticket, const orbx_keypoint* kps, const uint8_t* desc, const int32_t* n,
                        int frames, int cap, int root, int32_t* all_n, orbx_keypoint* all_kps, uint8_t* all_desc,
                        size_t all_records_cap, long long* total_records);
+/* The same for records that are dense already (orbx_extract_batch with ORBX_OUT_DENSE): no compaction pass, the blocks go
+ * straight from kps / desc to the root (peer copy into its window, or ncclSend).  cap only clamps the counts. */
+int orbx_gather_frames_dense(orbx_comm* comm, orbx_ctx* ctx, int ticket, const orbx_keypoint* kps, const uint8_t* desc, const int32_t* n,
+                             int frames, int cap, int root, int32_t* all_n, orbx_keypoint* all_kps, uint8_t* all_desc,
+                             size_t all_records_cap, long long* total_records);
+
 /* Match lists: match = pairs x cap int32 (what orbx_match_bow_batch / orbx_search_by_projection write: row i matched to match[i],
  * -1 = none), rows[p] = rows in use of pair p; both DEVICE pointers.  At the root: all_n = nranks x pairs match counts and
  * all_pairs = the (row, match[row]) records (2 x int32 each, ascending row) of every pair in rank, then pair order. */

@@ -188,14 +188,15 @@ class ORBextractor:
         self._check(rc, "orbx_extract_batch")
         return [(kps[b, :n[b]].copy(), desc[b, :n[b]].copy()) for b in range(B)]
 
-    def extract_batch_device(self, images, kps, desc, n_out, in_device=True):
+    def extract_batch_device(self, images, kps, desc, n_out, in_device=True, dense=False):
         """Asynchronous device-resident path used by bench.py.  images: torch uint8 (B,H,W) on the ctx device
         (or pinned host tensor with in_device=False); kps: torch uint8 (B,cap,28); desc: torch uint8 (B,cap,32);
-        n_out: torch int32 (B,), all on the device.  Returns immediately; call sync()."""
+        n_out: torch int32 (B,), all on the device.  Returns immediately; call sync().  dense=True (ORBX_OUT_DENSE): frame b's
+        records start at row sum(n_out[:b]) of the flattened (B*cap, ...) buffers instead of row b*cap."""
         B, h, w = images.shape
         self._last_wh = (w, h)
         cap = kps.shape[1]
-        flags = OUT_DEVICE | (IN_DEVICE if in_device else 0)
+        flags = OUT_DEVICE | (IN_DEVICE if in_device else 0) | (4 if dense else 0)
         rc = self._lib.orbx_extract_batch(self._h, _ptr(images), B, w, h, images.stride(1), images.stride(0), flags,
                                           _ptr(kps), _ptr(desc), cap, _ptr(n_out))
         self._check(rc, "orbx_extract_batch(device)")

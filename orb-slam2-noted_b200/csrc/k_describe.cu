@@ -115,7 +115,7 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
                const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                const orbx_keypoint* __restrict__ selAll, const int* __restrict__ selCount,
                orbx_keypoint* __restrict__ outKp, uint8_t* __restrict__ outDesc, int cap, int* __restrict__ outN,
-               int* __restrict__ err, int kpPerWarp)
+               int* __restrict__ err, int kpPerWarp, const int* __restrict__ frameOff)
 {
     extern __shared__ __align__(16) uint32_t sBufAll[];                      // [kDescWarps][2][kPatchWords]; pass A uses it as [2][kRawWords]
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
@@ -129,6 +129,8 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
     const int total = __shfl_sync(0xffffffffu, incl, G.nlevels - 1);
     if (blockIdx.x == 0 && threadIdx.x == 0) outN[frame] = min(total, cap);
     const int i0 = (blockIdx.x * kDescWarps + wrp) * kpPerWarp;
+    // first output row of this frame: its padded block, or (ORBX_OUT_DENSE) right behind the previous frame's records
+    const size_t outBase = frameOff ? (size_t)frameOff[frame] : (size_t)frame * cap;
     if (i0 >= total) return;
     if (total > cap) { if (lane == 0) atomicExch(err, 5); if (i0 >= cap) return; }
     const int nkp = min(kpPerWarp, min(total, cap) - i0);
@@ -298,14 +300,14 @@ describeKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ lv
             const uint32_t t0 = sample(q.x, q.y), t1 = sample(q.z, q.w);
             val |= (t0 < t1) << j;
         }
-        outDesc[((size_t)frame * cap + (i0 + k)) * 32 + lane] = (uint8_t)val;
+        outDesc[(outBase + (i0 + k)) * 32 + lane] = (uint8_t)val;
         __syncwarp();                                              // everyone is done with this buffer
         if (k + kDepth < nkp) issueBlur(k + kDepth); else asm volatile("cp.async.commit_group;" ::: "memory");
     }
     if (lane < nkp) {
         kp.angle = myAngle;
         if (myLevel != 0) { const float sc = G.lv[myLevel].scale; kp.x = __fmul_rn(kp.x, sc); kp.y = __fmul_rn(kp.y, sc); }
-        outKp[(size_t)frame * cap + i0 + lane] = kp;
+        outKp[outBase + i0 + lane] = kp;
     }
 }
 
@@ -350,11 +352,49 @@ __global__ void undistortKernel(const orbx_keypoint* __restrict__ in, int n, con
     out[i] = kp;
 }
 
-int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN)
+// ORBX_OUT_DENSE: off[f] = sum over the frames before f of min(keypoints selected, cap); off[frames] = total.  One CTA.
+__global__ void __launch_bounds__(1024) frameOffsetsKernel(const int* __restrict__ selCount, int nlevels, int frames, int cap, int* __restrict__ off)
+{
+    __shared__ int warpSum[32];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int base = 0; base < frames; base += 1024) {
+        const int f = base + threadIdx.x;
+        int v = 0;
+        if (f < frames) { for (int l = 0; l < nlevels; ++l) v += selCount[f * nlevels + l]; v = min(v, cap); }
+        int s = v;
+        #pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += t; }
+        if (lane == 31) warpSum[w] = s;
+        __syncthreads();
+        if (w == 0) {
+            int t = warpSum[lane];
+            #pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(0xffffffffu, t, o); if (lane >= o) t += u; }
+            warpSum[lane] = t;
+        }
+        __syncthreads();
+        const int before = carry + (w ? warpSum[w - 1] : 0) + s - v;
+        if (f < frames) off[f] = before;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = before + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) off[frames] = carry;
+}
+
+int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN, bool dense)
 {
     GeomSet g = c->geom;
     g.frame0 = frame0;
+    if (dense) {
+        if (frame0 != 0) return ORBX_E_INVALID;                  // dense output is one pass over the whole batch
+        if (!c->dFrameOff) ORBX_CUDA(c, cudaMalloc(&c->dFrameOff, sizeof(int) * (size_t)(c->maxBatch + 1)));
+    }
     stageBegin(c, ST_DESCRIBE);
+    if (dense) frameOffsetsKernel<<<1, 1024, 0, c->stream>>>(c->dSelCount, g.nlevels, batch, capPerFrame, c->dFrameOff);
     // keypoints per warp: as many as keeps every SM busy (the pattern registers and the count prefix are per warp)
     const int slots = std::min(g.selPerFrame, capPerFrame);
     int kpw = kKpPerWarpMax;
@@ -369,8 +409,9 @@ int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* 
         c->smemCfg[SMEM_DESCRIBE] = smem;
     }
     describeKernel<<<grid, block, smem, c->stream>>>(g, c->lvl0, c->lvl0Pitch, c->lvl0FrameStride, c->dPyr, c->dBlur,
-                                                 c->dSel, c->dSelCount, dKps, dDesc, capPerFrame, dN, c->dErr, kpw);
-    stageEnd(c, ST_DESCRIBE, 1);
+                                                 c->dSel, c->dSelCount, dKps, dDesc, capPerFrame, dN, c->dErr, kpw,
+                                                 dense ? c->dFrameOff : nullptr);
+    stageEnd(c, ST_DESCRIBE, dense ? 2 : 1);
     ORBX_CUDA(c, cudaGetLastError());
     return ORBX_OK;
 }

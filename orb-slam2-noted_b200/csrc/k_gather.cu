@@ -17,6 +17,9 @@
 //         ingress is an in-cast, the stores back up into the writers' memory systems and their extraction kernels slow down
 //         by 0.1 - 0.6 ms per step, more the more CTAs store; few CTAs avoid that but stretch the chain (4 CTAs: 4.85);
 //      b. otherwise grouped ncclSend / ncclRecv of staged blocks with few CTAs (ncclConfig_t::maxCTAs): 4.60 ms per step.
+//   Records that are dense already (orbx_extract_batch with ORBX_OUT_DENSE: the describe stage writes frame b's records right
+//   behind frame b - 1's) skip step 1's copy: orbx_gather_frames_dense scans the counts for the total and sends the caller's
+//   blocks as they lie (4.49 ms per step on 8 B200s = 0.971 of 8 x one GPU).
 // NCCL is loaded at run time (dlopen "libnccl.so.2"): a single-GPU user of liborbx.so needs no NCCL, and inside a process that
 // already carries NCCL (torch) the same library is used.  The reference has no counterpart (it is single-process CPU code);
 // the contract is north_star's: "only a final NCCL gather of keypoint and match lists over NVLink".
@@ -194,8 +197,11 @@ matchListKernel(const int* __restrict__ match, const int* __restrict__ rows, int
 // its peer window (3a) -- otherwise the blocks are staged locally and sent (3b).
 template <typename Compact>
 static int gatherDense(orbx_comm* c, int root, const int* dCounts, int countsPerRank, int* allCounts, int nblocks, uint8_t* const* staging,
-                       uint8_t* const* atRoot, const size_t* bytesPerRecord, size_t capRecords, long long* totalOut, Compact compact)
+                       uint8_t* const* atRoot, const size_t* bytesPerRecord, size_t capRecords, long long* totalOut, Compact compact,
+                       const uint8_t* const* denseSrc = nullptr)
 {   // capRecords: this rank's output capacity (only the root's counts)
+    // denseSrc: the caller's records are dense already (block k at denseSrc[k]): nothing is compacted or staged, the blocks are
+    // copied / sent from where they lie
     // Every rank contributes (its total, the capacity of ITS output buffers, where ITS output buffers lie in its window): the
     // total was written to dTotals[kOwn * nranks] by the scan kernel; the rest travels along so that all ranks judge the ROOT's
     // buffers and take the same decisions (a rank that gave up alone would leave the others waiting in their receives).
@@ -226,19 +232,24 @@ static int gatherDense(orbx_comm* c, int root, const int* dCounts, int countsPer
         long long mineBefore = 0;
         for (int r = 0; r < c->rank; ++r) mineBefore += c->hTotals[r];
         const bool remote = direct && c->rank != root;
-        const bool byCopyEngine = remote && c->remoteByCopyEngine;
+        const bool byCopyEngine = remote && (c->remoteByCopyEngine || denseSrc);
         uint8_t* far[4];
         for (int k = 0; k < nblocks; ++k) {
             far[k] = remote ? c->winBase[root] + winOff[k] + (size_t)mineBefore * bytesPerRecord[k] : nullptr;
             dst[k] = c->rank == root ? atRoot[k] + (size_t)mineBefore * bytesPerRecord[k] : (remote && !byCopyEngine) ? far[k] : staging[k];
         }
-        if (total) compact(dst, remote && !byCopyEngine);
-        ORBX_CU(c, cudaGetLastError());
+        if (denseSrc) {
+            for (int k = 0; k < nblocks && total && c->rank == root; ++k)
+                ORBX_CU(c, cudaMemcpyAsync(dst[k], denseSrc[k], (size_t)total * bytesPerRecord[k], cudaMemcpyDeviceToDevice, c->stream));
+        } else {
+            if (total) compact(dst, remote && !byCopyEngine);
+            ORBX_CU(c, cudaGetLastError());
+        }
         for (int k = 0; k < nblocks && byCopyEngine && total; ++k)
-            ORBX_CU(c, cudaMemcpyAsync(far[k], staging[k], (size_t)total * bytesPerRecord[k], cudaMemcpyDefault, c->stream));
+            ORBX_CU(c, cudaMemcpyAsync(far[k], denseSrc ? denseSrc[k] : staging[k], (size_t)total * bytesPerRecord[k], cudaMemcpyDefault, c->stream));
     }
     (direct ? c->directGathers : c->stagedGathers)++;
-    const uint8_t* const* local = staging;
+    const uint8_t* const* local = denseSrc ? denseSrc : staging;
     if (c->nranks > 1) ORBX_NCCL(c, a->GroupStart());
     if (c->rank == root) {
         long long before = 0;
@@ -470,6 +481,25 @@ extern "C" int orbx_gather_frames(orbx_comm* c, orbx_ctx* ctx, int ticket, const
         const int grid = remote ? std::min(frames, remoteCtas) : frames;
         compactFramesKernel<<<grid, 256, 0, st>>>((const uint32_t*)kps, (const uint4*)desc, n, dOff, frames, cap, (uint32_t*)dst[0], (uint4*)dst[1]);
     });
+}
+
+extern "C" int orbx_gather_frames_dense(orbx_comm* c, orbx_ctx* ctx, int ticket, const orbx_keypoint* kps, const uint8_t* desc, const int32_t* n,
+                                        int frames, int cap, int root, int32_t* all_n, orbx_keypoint* all_kps, uint8_t* all_desc,
+                                        size_t all_records_cap, long long* total_records)
+{
+    if (!c || frames < 1 || cap < 1 || !kps || !desc || !n || root < 0 || root >= c->nranks) return ORBX_E_INVALID;
+    if (c->rank == root && (!all_n || !all_kps || !all_desc)) return ORBX_E_INVALID;
+    ORBX_CU(c, cudaSetDevice(c->device));
+    int rc = waitTicket(c, ctx, ticket);
+    if (rc) return rc;
+    if ((rc = ensureStage(c, sizeof(int) * (size_t)(frames + 1) + 256))) return rc;
+    scanCountsKernel<<<1, 1024, 0, c->stream>>>(n, frames, cap, (int*)c->dStage, c->dTotals + kOwn * (size_t)c->nranks);   // only the total is used
+    ORBX_CU(c, cudaGetLastError());
+    uint8_t* staging[2] = {nullptr, nullptr};
+    uint8_t* atRoot[2] = {(uint8_t*)all_kps, all_desc};
+    const uint8_t* dense[2] = {(const uint8_t*)kps, desc};
+    const size_t bpr[2] = {28, 32};
+    return gatherDense(c, root, n, frames, all_n, 2, staging, atRoot, bpr, all_records_cap, total_records, [](uint8_t* const*, bool) {}, dense);
 }
 
 extern "C" int orbx_gather_matches(orbx_comm* c, orbx_ctx* ctx, int ticket, const int32_t* match, const int32_t* rows, int pairs, int cap,

@@ -340,7 +340,7 @@ void orbx_destroy(orbx_ctx* h)
     drainEvents(c);
     for (cudaEvent_t e : c->eventPool) cudaEventDestroy(e);
     freeGeometry(c);
-    void* ptrs[] = {c->dGeom, c->dPyr, c->dBlur, c->dCand, c->dCandCount, c->dSel, c->dSelCount, c->dErr,
+    void* ptrs[] = {c->dGeom, c->dPyr, c->dBlur, c->dCand, c->dCandCount, c->dSel, c->dSelCount, c->dErr, c->dFrameOff,
                     c->dOutKp, c->dOutDesc, c->dOutN, c->dIn, c->dScratch, c->dTensorMaps, c->dStrips, c->dStereoN};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->hPinned) cudaFreeHost(c->hPinned);
@@ -480,6 +480,10 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
     const GeomSet& g = c->geom;
 
     const bool inDev = flags & ORBX_IN_DEVICE, outDev = flags & ORBX_OUT_DEVICE;
+    const bool dense = (flags & ORBX_OUT_DENSE) != 0;
+    if (dense && !(inDev && outDev)) return ORBX_E_INVALID;      // dense rows need the whole batch in one pass, results on the device
+    static const int devChunkEnv = getenv("ORBX_DEVICE_CHUNK") ? atoi(getenv("ORBX_DEVICE_CHUNK")) : 0;
+    if (dense && devChunkEnv > 0 && devChunkEnv < batch) return ORBX_E_UNSUPPORTED;
     uint8_t* d0 = c->dPyr + g.lv[0].planeOff;
     const size_t dp = (size_t)g.lv[0].pitch;
     // a device image whose rows are not 16-byte aligned (e.g. a dense 1241-wide frame) is repacked into the arena once:
@@ -600,7 +604,7 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
             if (!rc) rc = launchOctree(c, f0, n);
             if (!rc) rc = launchBlur(c, f0, n);
         }
-        if (!rc) rc = launchDescribe(c, f0, n, dK, dD, sc, dN);
+        if (!rc) rc = launchDescribe(c, f0, n, dK, dD, sc, dN, dense);
         if (rc) { c->stream = mainStream; return rc; }
         if (!outDev) {
             ORBX_CUDA(c, cudaEventRecord(c->evDone[i], c->stream));

@@ -104,6 +104,7 @@ struct Ctx {
     orbx_keypoint* dSel = nullptr; size_t selRecs = 0; // [B][selPerFrame] level-coord keypoints after the quadtree
     int* dSelCount = nullptr;            // [B][nlevels]
     int* dErr = nullptr;                 // device error flag
+    int* dFrameOff = nullptr;            // ORBX_OUT_DENSE: first output row of every frame (+ total), maxBatch + 1 entries
     orbx_keypoint* dOutKp = nullptr; uint8_t* dOutDesc = nullptr; int* dOutN = nullptr; int outCap = 0; // staging for host outputs
     uint8_t* hPinned = nullptr; size_t hPinnedBytes = 0;
     uint8_t* dIn = nullptr; size_t dInBytes = 0;       // H2D staging for level 0 when input is on host
@@ -156,7 +157,7 @@ int launchFast(Ctx* c, int frame0, int batch);
 void buildFastStrips(const GeomSet& g, std::vector<StripDesc>& out);
 int launchOctree(Ctx* c, int frame0, int batch);
 int launchBlur(Ctx* c, int frame0, int batch);
-int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN);
+int launchDescribe(Ctx* c, int frame0, int batch, orbx_keypoint* dKps, uint8_t* dDesc, int capPerFrame, int* dN, bool dense = false);
 int launchBorderedPyramid(Ctx* c, int frame, int border, uint8_t* dst, size_t* offsets, size_t* total);   // dst == NULL: sizes only
 int launchBorderCopy(Ctx* c, const uint8_t* src, int w, int h, size_t pitch, uint8_t* dst, size_t dpitch, int border);
 

@@ -67,6 +67,7 @@ class Comm:
         L.orbx_comm_window.argtypes = [vp, ctypes.c_size_t, ctypes.POINTER(vp)]
         L.orbx_comm_stats.argtypes = [vp, ctypes.POINTER(ci), ctypes.POINTER(ci)]
         L.orbx_gather_frames.argtypes = [vp, vp, ci, vp, vp, vp, ci, ci, ci, vp, vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_longlong)]
+        L.orbx_gather_frames_dense.argtypes = L.orbx_gather_frames.argtypes
         L.orbx_gather_matches.argtypes = [vp, vp, ci, vp, vp, ci, ci, ci, vp, vp, ctypes.c_size_t, ctypes.POINTER(ctypes.c_longlong)]
         self._L, self._ex, self.world, self.rank = L, ex, world, rank
         self._h = vp()
@@ -152,12 +153,13 @@ class Comm:
         self._chk(self._L.orbx_comm_stats(self._h, ctypes.byref(a), ctypes.byref(b)), "orbx_comm_stats")
         return a.value, b.value
 
-    def gather_frames(self, kps, desc, n, out, root=0, ticket=-1):
+    def gather_frames(self, kps, desc, n, out, root=0, ticket=-1, dense=False):
         """kps (B, cap, 28) u8, desc (B, cap, 32) u8, n (B,) i32: torch CUDA tensors of this rank.  out = (all_n (world * B,) i32,
-        all_kps (R, 28) u8, all_desc (R, 32) u8) CUDA tensors, used at the root.  Returns the total number of records."""
+        all_kps (R, 28) u8, all_desc (R, 32) u8) CUDA tensors, used at the root.  Returns the total number of records.
+        dense=True: kps / desc hold dense records already (extract_batch_device(dense=True)); no compaction pass."""
         P = lambda t: ctypes.c_void_p(t.data_ptr())
         total = ctypes.c_longlong()
-        self._chk(self._L.orbx_gather_frames(self._h, self._ex._h, ticket, P(kps), P(desc), P(n), kps.shape[0], kps.shape[1], root,
+        self._chk((self._L.orbx_gather_frames_dense if dense else self._L.orbx_gather_frames)(self._h, self._ex._h, ticket, P(kps), P(desc), P(n), kps.shape[0], kps.shape[1], root,
                                              P(out[0]), P(out[1]), P(out[2]), out[1].shape[0], ctypes.byref(total)), "orbx_gather_frames")
         return total.value
 

@@ -50,6 +50,20 @@ def test_gather_single_rank_compacts_frames_and_match_lists():
     want = [np.stack([np.flatnonzero(match[p, :rows[p]] >= 0), match[p, :rows[p]][match[p, :rows[p]] >= 0]], 1) for p in range(pairs)]
     assert np.array_equal(mo[0].cpu().numpy(), [len(x) for x in want]) and total == sum(len(x) for x in want)
     assert np.array_equal(mo[1][:total].cpu().numpy(), np.concatenate(want))
+    # dense extraction (ORBX_OUT_DENSE): the describe stage writes the records where the compaction would put them
+    kd = torch.full((B, cap, 28), 0xAB, dtype=torch.uint8, device=dev); dd = torch.full((B, cap, 32), 0xCD, dtype=torch.uint8, device=dev)
+    nd = torch.zeros(B, dtype=torch.int32, device=dev)
+    ex.extract_batch_device(imgs, kd, dd, nd, dense=True)
+    ex.sync()
+    total = int(n.sum())
+    assert torch.equal(nd, n) and torch.equal(kd.view(-1, 28)[:total], out[1][:total]) and torch.equal(dd.view(-1, 32)[:total], out[2][:total])
+    assert bool((kd.view(-1, 28)[total:] == 0xAB).all()) and bool((dd.view(-1, 32)[total:] == 0xCD).all())      # nothing behind the records
+    out_d = (torch.zeros_like(out[0]), torch.zeros_like(out[1]), torch.zeros_like(out[2]))
+    assert comm.gather_frames(kd, dd, nd, out_d, dense=True) == total
+    comm.sync()
+    assert torch.equal(out_d[0], out[0]) and torch.equal(out_d[1][:total], out[1][:total]) and torch.equal(out_d[2][:total], out[2][:total])
+    with pytest.raises(Exception):                                                  # dense output needs device images and device results
+        ex.extract_batch_device(imgs.cpu().pin_memory(), kd, dd, nd, in_device=False, dense=True)
     # a peer window on one rank is just memory owned by the communicator: gathers into it give the same records
     win = comm.window(sh.Comm.carve_bytes(((B * cap, 28), torch.uint8), ((B * cap, 32), torch.uint8)))
     assert win is not None and win.is_cuda and win.data_ptr() % 256 == 0
@@ -112,8 +126,17 @@ if rank == 0:
     rec = mo[1][:mt].cpu().numpy()
     assert mt == int(cnt.sum()) and np.array_equal(rec[:cnt[0, 0], 0], np.arange(0, 64, 7)) and set(rec[:, 1]) == set(range(100, 100 + world))
     print("GATHER_OK", world, total, mt)
-# the same two gathers through the root's peer window: the other rank's compaction kernel writes into rank 0's memory
-assert comm.stats() == (0, 2)
+# dense records (ORBX_OUT_DENSE) need no compaction: sent from where they lie (here still through ncclSend/ncclRecv)
+kd, dd, nd = torch.zeros_like(k), torch.zeros_like(d), torch.zeros_like(n)
+ex.extract_batch_device(torch.from_numpy(frames(rank)).to(dev), kd, dd, nd, dense=True)
+ex.sync()
+out3 = tuple(torch.zeros_like(t) for t in out)
+assert comm.gather_frames(kd, dd, nd, out3, root=0, dense=True) == total
+comm.sync()
+if rank == 0:
+    assert torch.equal(out3[0], out[0]) and torch.equal(out3[1][:total], out[1][:total]) and torch.equal(out3[2][:total], out[2][:total])
+# the same gathers through the root's peer window: the other rank writes into rank 0's memory
+assert comm.stats() == (0, 3)
 shapes = (((rows_out, 28), torch.uint8), ((rows_out, 32), torch.uint8), ((world * 3 * 64, 2), torch.int32))
 win = comm.window(sh.Comm.carve_bytes(*shapes) if rank == 0 else 0)
 have = torch.tensor([0 if win is None else 1]); dist.broadcast(have, src=0)
@@ -129,8 +152,8 @@ else:
     else:
         out2, mo2 = out, mo
     dist.barrier()
-    for rep in range(2):
-        t2 = comm.gather_frames(k, d, n, out2, root=0)
+    for rep in range(2):                                 # padded records through the compaction, then dense records as they lie
+        t2 = comm.gather_frames(kd, dd, nd, out2, root=0, dense=True) if rep else comm.gather_frames(k, d, n, out2, root=0)
         m2 = comm.gather_matches(match, torch.tensor([64, 10, 0], dtype=torch.int32, device=dev), mo2, root=0)
         comm.sync()
         assert (t2, m2) == (total, mt)
@@ -140,7 +163,7 @@ else:
             assert bool((out2[1][total:total + 4] == 0xEE).all())               # nothing written past the records
             k2[:total].zero_(); torch.cuda.synchronize()
         dist.barrier()                                   # the root has looked before the next round overwrites
-    assert comm.stats() == (4, 2), comm.stats()
+    assert comm.stats() == (4, 3), comm.stats()
     if rank == 0:
         print("WINDOW_OK", world)
 dist.barrier()
