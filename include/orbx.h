@@ -163,6 +163,9 @@ int orbx_vocab_load_text(orbx_ctx* ctx, const char* path, orbx_vocab** out);
 /* scoring / weighting of the text header (DBoW2 ScoringType / WeightingType; 0 / 0 = L1_NORM / TF_IDF, what ORBvoc uses and
  * what orbx_vocab_create assumes).  orbx_bow_vector returns ORBX_E_UNSUPPORTED unless scoring is L1_NORM and weighting is
  * TF_IDF or TF: the other modes accumulate and normalise differently (TemplatedVocabulary.h:1166-1221). */
+/* TemplatedVocabulary::saveToTextFile, Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1492-1517: the vocabulary back into the
+ * ORBvoc text format (byte for byte what the reference writes for the same tree). */
+int orbx_vocab_save_text(const orbx_vocab* v, const char* path);
 int orbx_vocab_modes(const orbx_vocab* v, int* scoring, int* weighting);
 void orbx_vocab_destroy(orbx_vocab* v);
 int orbx_vocab_info(const orbx_vocab* v, int* k, int* L, int* nnodes, int* nwords);

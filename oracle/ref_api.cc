@@ -224,6 +224,7 @@ void* ref_vocab_load_text(const char* path)
     if (!v->loadFromTextFile(path)) { delete v; return NULL; }
     return v;
 }
+void ref_vocab_save_text(void* v, const char* path) { ((ORBVocabulary*)v)->saveToTextFile(path); }   // TemplatedVocabulary.h:1492-1517
 void ref_vocab_free(void* v) { delete (ORBVocabulary*)v; }
 void ref_vocab_info(void* vv, int* k, int* L, int* nwords, int* nnodes, int* scoring, int* weighting)
 {

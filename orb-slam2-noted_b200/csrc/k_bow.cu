@@ -308,6 +308,44 @@ extern "C" int orbx_vocab_load_text(orbx_ctx* h, const char* path, orbx_vocab** 
     return orbx_vocab_set_word_weights(*out, ww.data(), wid);
 }
 
+// TemplatedVocabulary::saveToTextFile (TemplatedVocabulary.h:1492-1517): header "k L  scoring weighting" (the reference writes
+// two blanks there), then one line per node 1..N-1 in id order: parent, isLeaf (= no children), the 32 descriptor bytes each
+// followed by a blank, one more blank and the weight as ostream prints a double (6 significant digits = "%g").
+extern "C" int orbx_vocab_save_text(const orbx_vocab* v, const char* path)
+{
+    if (!v || !path) return ORBX_E_INVALID;
+    if (cudaSetDevice(v->device) != cudaSuccess) return ORBX_E_CUDA;
+    const int nn = v->nnodes;
+    std::vector<int32_t> off((size_t)nn + 1), child((size_t)std::max(nn - 1, 1)), word((size_t)nn);
+    std::vector<uint8_t> desc((size_t)32 * nn);
+    std::vector<float> weight((size_t)nn);
+    std::vector<double> ww((size_t)std::max(v->wordCap, 1), 0.0);
+    if (cudaMemcpy(off.data(), v->dChildOff, sizeof(int32_t) * (size_t)(nn + 1), cudaMemcpyDeviceToHost) != cudaSuccess ||
+        (nn > 1 && cudaMemcpy(child.data(), v->dChild, sizeof(int32_t) * (size_t)(nn - 1), cudaMemcpyDeviceToHost) != cudaSuccess) ||
+        cudaMemcpy(word.data(), v->dWord, sizeof(int32_t) * (size_t)nn, cudaMemcpyDeviceToHost) != cudaSuccess ||
+        cudaMemcpy(desc.data(), v->dDesc, (size_t)32 * nn, cudaMemcpyDeviceToHost) != cudaSuccess ||
+        cudaMemcpy(weight.data(), v->dWeight, sizeof(float) * (size_t)nn, cudaMemcpyDeviceToHost) != cudaSuccess ||
+        (v->dWordWeight && v->wordCap > 0 && cudaMemcpy(ww.data(), v->dWordWeight, sizeof(double) * (size_t)v->wordCap, cudaMemcpyDeviceToHost) != cudaSuccess))
+        return ORBX_E_CUDA;
+    std::vector<int32_t> parent((size_t)nn, 0);
+    for (int i = 0; i < nn; ++i) for (int j = off[i]; j < off[i + 1]; ++j) parent[child[j]] = i;
+    FILE* f = fopen(path, "w");
+    if (!f) return ORBX_E_INVALID;
+    fprintf(f, "%d %d  %d %d\n", v->k, v->L, v->scoring, v->weighting);
+    std::string line;
+    char num[64];
+    for (int i = 1; i < nn; ++i) {
+        const bool leaf = off[i + 1] == off[i];
+        line.clear();
+        snprintf(num, sizeof(num), "%d %d ", parent[i], leaf ? 1 : 0); line += num;
+        for (int b = 0; b < 32; ++b) { snprintf(num, sizeof(num), "%d ", (int)desc[(size_t)32 * i + b]); line += num; }
+        const double w = (leaf && v->dWordWeight && word[i] >= 0 && word[i] < v->wordCap) ? ww[word[i]] : (double)weight[i];
+        snprintf(num, sizeof(num), " %g\n", w); line += num;
+        fputs(line.c_str(), f);
+    }
+    return fclose(f) == 0 ? ORBX_OK : ORBX_E_INVALID;
+}
+
 extern "C" int orbx_vocab_modes(const orbx_vocab* v, int* scoring, int* weighting)
 {
     if (!v) return ORBX_E_INVALID;

@@ -50,6 +50,7 @@ def _mlib():
     L.orbx_vocab_load_text.argtypes = [vp, ctypes.c_char_p, ctypes.POINTER(vp)]
     L.orbx_vocab_destroy.argtypes = [vp]
     L.orbx_vocab_destroy.restype = None
+    L.orbx_vocab_save_text.argtypes = [vp, ctypes.c_char_p]
     L.orbx_vocab_info.argtypes = [vp, ip, ip, ip, ip]
     L.orbx_vocab_modes.argtypes = [vp, ip, ip]
     L.orbx_bow_transform.argtypes = [vp, vp, vp, ci, ci, ci, vp, vp, vp]
@@ -94,6 +95,10 @@ class Vocabulary:
         v = [ctypes.c_int() for _ in range(4)]
         _mlib().orbx_vocab_info(self._v, *[ctypes.byref(x) for x in v])
         return tuple(x.value for x in v)  # k, L, nnodes, nwords
+
+    def save_text(self, path):
+        """TemplatedVocabulary::saveToTextFile (TemplatedVocabulary.h:1492-1517)."""
+        _chk(self._ex, _mlib().orbx_vocab_save_text(self._v, path.encode()), "orbx_vocab_save_text")
 
     def modes(self):
         """(scoring, weighting) of the text header; (0, 0) = L1_NORM / TF_IDF."""

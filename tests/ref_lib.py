@@ -35,6 +35,8 @@ def lib():
         L.ref_stereo_frame.argtypes = [ci, cf, ci, ci, ci, vp, vp, ci, ci, cf, cf, cf, cf, vp, ci, cf, cf, vp, vp, vp, vp, vp, vp, ci, vp, vp, vp]
         L.ref_vocab_load_text.argtypes = [ctypes.c_char_p]
         L.ref_vocab_load_text.restype = vp
+        L.ref_vocab_save_text.argtypes = [vp, ctypes.c_char_p]
+        L.ref_vocab_save_text.restype = None
         L.ref_vocab_free.argtypes = [vp]
         L.ref_vocab_free.restype = None
         L.ref_vocab_info.argtypes = [vp] * 7

@@ -65,6 +65,42 @@ def test_vocab_text_loader_and_transform(P, ctx, vocs, tmp_path):
             assert np.array_equal(x.view(np.uint32), y.view(np.uint32)) and np.array_equal(y.view(np.uint32), z.view(np.uint32))
 
 
+def saved_text(v):
+    """What TemplatedVocabulary::saveToTextFile (TemplatedVocabulary.h:1492-1517) writes for this tree: the header with two
+    blanks, every descriptor byte followed by a blank, one more blank, the weight as ostream prints a double (%g)."""
+    out = [f"{v['k']} {v['L']}  0 0\n"]
+    for i in range(1, len(v["parent"])):
+        out.append(f"{v['parent'][i]} {v['leaf'][i]} " + "".join(f"{int(b)} " for b in v["desc"][i]) + " %g\n" % float(v["weight"][i]))
+    return "".join(out)
+
+
+def test_vocab_save_text_round_trip(P, ctx, vocs, tmp_path):
+    """orbx_vocab_save_text writes the file the reference's saveToTextFile writes (compared with oracle/_ref where it is here,
+    else with the format restated above), and loading it back gives the same vocabulary."""
+    import os, ref_lib as R
+    v, _, _ = vocs
+    src = tmp_path / "voc.txt"
+    src.write_text(synth.vocabulary_text(v).rstrip("\n"))   # the reference's loader turns a trailing newline into a phantom node
+    vt = P.Vocabulary(ctx, path=str(src))
+    out = tmp_path / "saved.txt"
+    vt.save_text(str(out))
+    got = out.read_text()
+    if os.path.exists(R.SO):
+        L = R.lib()
+        h = L.ref_vocab_load_text(str(src).encode())
+        assert h
+        L.ref_vocab_save_text(h, str(tmp_path / "ref.txt").encode())
+        L.ref_vocab_free(h)
+        assert got == (tmp_path / "ref.txt").read_text()
+    else:
+        assert got == saved_text(v)
+    again = P.Vocabulary(ctx, path=str(out))
+    d = synth.descriptors(9, 500)
+    assert again.info() == vt.info()
+    for a, b in zip(vt.transform(d, 2), again.transform(d, 2)):
+        assert np.array_equal(a, b) or np.allclose(a, b, rtol=1e-5)          # weights went through 6 significant digits
+
+
 @pytest.fixture(scope="module")
 def vocs6(P, ctx):
     """configs[3]'s vocabulary shape: k = 10, L = 6 (1 111 111 nodes = 35 MB of node descriptors, 10^6 words)."""
