@@ -9,15 +9,15 @@
 // coalesced loads.  The order of first encounter is (smallest shared word, position in that word's list), and the position
 // in a list is the insertion order of the keyframes that carry the word -- so the sort key is (first shared word, slot),
 // with slots handed out in insertion order and never reused.  No inverted file is kept at all; add is an append, erase a flag.
-//   K1 kfdbBeginKernel   counters + query bitmap
+//   K1 kfdbBeginKernel   counters, the query's bitmap and word -> query-position table, exclusion marks of the connected keyframes
 //   K2 kfdbSharedKernel  one warp per keyframe: shared-word count, first shared word, the mnLoopQuery / mnLoopWords state
 //                        machine of :120-146 (connected keyframes, repeated query ids), max common words
-//   K3 kfdbScoreKernel   one warp per keyframe above 0.8 * max: L1Scoring::score in double, summed in ascending word order
-//                        (the lanes find the common words, the sum runs in word order through shuffles) -> float score,
-//                        candidate list
-//   K4 kfdbGroupKernel   one thread per candidate: accumulate over its <= 10 best covisible keyframes :193-224 / :337-364
-//   K5 kfdbEmitKernel / kfdbWriteKernel   0.75 * best gate, first-occurrence de-duplication and output position, all by
-//                        rank among the candidates' keys (O(C^2) over a handful to a few thousand candidates)
+//   K3 kfdbScoreKernel   one CTA per keyframe above 0.8 * max: L1Scoring::score in double; all threads compute the terms of the
+//                        common words, one warp sums them in ascending word order through shuffles -> float score, candidate list
+//   K4 kfdbFinalKernel   one CTA: group accumulation over the <= 10 best covisible keyframes :193-224 / :337-364, the
+//                        0.75 * best gate, first-occurrence de-duplication and output position by rank among the candidates'
+//                        keys (O(C^2) over a handful to a few thousand candidates), then the query's bits leave the bitmap
+// Four launches per query and no memset: 0.07 ms per query in a batch, 0.11 ms for a single call (4000 keyframes x 860 words).
 // The per-keyframe state the reference keeps in KeyFrame (mnLoopQuery, mnLoopWords, mLoopScore, mnRelocQuery, mnRelocWords,
 // mRelocScore; include/KeyFrame.h:322-333) lives in slot arrays here and persists between queries exactly like there: a
 // relocalisation query adds a neighbour's mRelocScore even when that score stems from an earlier query (:351).  The two
@@ -45,6 +45,7 @@ struct orbx_kfdb {
     int* dSlotOfId = nullptr; int idCap = 0;
     // query
     uint32_t* dBitmap = nullptr;
+    int32_t* dQPos = nullptr;               // word -> index in the query's BowVector; valid where the bitmap bit is set (never cleared)
     int32_t* dQIds = nullptr; double* dQVals = nullptr; int qCap = 0;
     int* dConn = nullptr; int connCap = 0;
     int* dCounters = nullptr;               // [0] max common words, [1] candidates, [2] best accumulated score (float bits), [3] outputs
@@ -84,13 +85,14 @@ __global__ void kfdbEraseKernel(int slot, int id, int* dAlive, int* slotOfId) { 
 __global__ void kfdbFillKernel(int* p, int n, int v) { const int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) p[i] = v; }
 
 // K1: counters, exclusion stamps of the connected keyframes, and the query's bitmap (cleared by a memset before)
-__global__ void kfdbBeginKernel(const int32_t* __restrict__ qIds, int nq, int nwords, uint32_t* __restrict__ bitmap, const int* __restrict__ conn,
+__global__ void kfdbBeginKernel(const int32_t* __restrict__ qIds, int nq, int nwords, uint32_t* __restrict__ bitmap, int32_t* __restrict__ qpos,
+                                const int* __restrict__ conn,
                                 int nconn, const int* __restrict__ slotOfId, int idCap, int* __restrict__ exclStamp, int stamp,
                                 int* __restrict__ counters, float bestAcc0)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) { counters[0] = 0; counters[1] = 0; counters[2] = __float_as_int(bestAcc0); counters[3] = 0; }
-    if (i < nq) { const int w = qIds[i]; if (w >= 0 && w < nwords) atomicOr(&bitmap[w >> 5], 1u << (w & 31)); }
+    if (i < nq) { const int w = qIds[i]; if (w >= 0 && w < nwords) { atomicOr(&bitmap[w >> 5], 1u << (w & 31)); qpos[w] = i; } }
     if (i < nconn) { const int id = conn[i]; if (id >= 0 && id < idCap) { const int s = slotOfId[id]; if (s >= 0) exclStamp[s] = stamp; } }
 }
 
@@ -106,7 +108,8 @@ kfdbSharedKernel(int nslots, const int* __restrict__ dSeg, const int* __restrict
     if (!dAlive[s]) { if (lane == 0) inList[s] = 0; return; }
     const int seg = dSeg[s], len = dLen[s];
     int cnt = 0, first = INT_MAX;
-    for (int j = lane; j < len; j += 32) {
+    #pragma unroll 8
+    for (int j = lane; j < len; j += 32) {                       // independent iterations: eight pairs of loads in flight
         const int w = ids[seg + j];
         if ((bitmap[w >> 5] >> (w & 31)) & 1u) { ++cnt; first = min(first, w); }
     }
@@ -129,42 +132,57 @@ __device__ __forceinline__ void atomicMaxFloat(int* addr, float v)
     while (v > __int_as_float(old)) { const int assumed = old; old = atomicCAS(addr, assumed, __float_as_int(v)); if (old == assumed) break; }
 }
 
-// K3: one warp per listed slot with more than minCommon words
+// K3: one CTA per slot; the listed slots with more than minCommon words go on (a handful), the rest leave at once.  All 256
+// threads compute the terms of the common words (independent loads, so the keyframe's ~1000 entries cost two or three
+// round trips), then warp 0 adds them in ascending word order -- the order of L1Scoring::score's merge -- from shared memory.
+constexpr int kScoreTile = 2048;
 __global__ void __launch_bounds__(256)
 kfdbScoreKernel(int nslots, const int* __restrict__ dSeg, const int* __restrict__ dLen, const int32_t* __restrict__ ids,
-                const double* __restrict__ vals, const uint32_t* __restrict__ bitmap, const int32_t* __restrict__ qIds,
+                const double* __restrict__ vals, const uint32_t* __restrict__ bitmap, const int32_t* __restrict__ qpos,
                 const double* __restrict__ qVals, int nq, int loop, float minScore, const int* __restrict__ inList,
                 const int* __restrict__ words, const int* __restrict__ firstWord, float* __restrict__ score,
                 int* __restrict__ counters, unsigned long long* __restrict__ key, int* __restrict__ candSlot)
 {
-    const int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    __shared__ double sTerm[kScoreTile];
+    __shared__ uint32_t sHit[kScoreTile / 32];
+    const int s = blockIdx.x, lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
     if (s >= nslots || !inList[s]) return;
     const int minCommon = (int)((float)counters[0] * 0.8f);      // int * float -> float -> int, :161 / :312
     if (!(words[s] > minCommon)) return;
     const int seg = dSeg[s], len = dLen[s];
-    double sum = 0.0;
-    for (int base = 0; base < len; base += 32) {                 // uniform trip count: every lane takes part in the shuffles
-        const int j = base + lane;
-        double term = 0.0;
-        bool hit = false;
-        if (j < len) {
-            const int w = ids[seg + j];
-            if ((bitmap[w >> 5] >> (w & 31)) & 1u) {
-                int lo = 0, hi = nq - 1;                          // the word is in the query: find its weight
-                while (lo < hi) { const int mid = (lo + hi) >> 1; if (qIds[mid] < w) lo = mid + 1; else hi = mid; }
-                const double vi = qVals[lo], wi = vals[seg + j];
-                term = fabs(vi - wi) - fabs(vi) - fabs(wi);      // ScoringObject.cpp:41
-                hit = true;
+    double sum = 0.0;                                             // lives in warp 0
+    for (int t0 = 0; t0 < len; t0 += kScoreTile) {
+        const int tn = min(kScoreTile, len - t0);
+        for (int j = threadIdx.x; j < ((tn + 31) & ~31); j += 256) {
+            double term = 0.0;
+            bool hit = false;
+            if (j < tn) {
+                const int w = ids[seg + t0 + j];
+                if ((bitmap[w >> 5] >> (w & 31)) & 1u) {
+                    const double vi = qVals[qpos[w]], wi = vals[seg + t0 + j];   // the word is in the query: qpos holds its place there
+                    term = fabs(vi - wi) - fabs(vi) - fabs(wi);  // ScoringObject.cpp:41
+                    hit = true;
+                }
+            }
+            sTerm[j] = term;
+            const uint32_t m = __ballot_sync(0xffffffffu, hit);
+            if (lane == 0) sHit[j >> 5] = m;
+        }
+        __syncthreads();
+        if (wrp == 0) {
+            for (int base = 0; base < tn; base += 32) {
+                const double term = sTerm[base + lane];
+                uint32_t m = sHit[base >> 5];
+                while (m) {                                       // ascending word order = ascending lane
+                    const int l = __ffs(m) - 1;
+                    m &= m - 1;
+                    sum += __shfl_sync(0xffffffffu, term, l);
+                }
             }
         }
-        unsigned m = __ballot_sync(0xffffffffu, hit);
-        while (m) {                                               // ascending word order = ascending lane
-            const int l = __ffs(m) - 1;
-            m &= m - 1;
-            sum += __shfl_sync(0xffffffffu, term, l);
-        }
+        __syncthreads();
     }
-    if (lane) return;
+    if (threadIdx.x) return;
     const float si = (float)(-sum / 2.0);
     score[s] = si;
     if (!loop || si >= minScore) {
@@ -174,61 +192,64 @@ kfdbScoreKernel(int nslots, const int* __restrict__ dSeg, const int* __restrict_
     }
 }
 
-// K4: one thread per candidate
-__global__ void kfdbGroupKernel(const int* __restrict__ counters, const int* __restrict__ candSlot, const int* __restrict__ dNeigh,
-                                const int* __restrict__ slotOfId, int idCap, const int* __restrict__ dKfId, int loop, long long qid,
-                                const long long* __restrict__ query, const int* __restrict__ words, const float* __restrict__ score,
-                                float* __restrict__ acc, int* __restrict__ best, int* __restrict__ bestAcc)
+// K4 + K5 in one CTA: group accumulation :193-224 / :337-364 (one candidate per thread step), the 0.75 * best gate,
+// first-occurrence de-duplication and output position by rank among the candidates' keys, then the query's bits are wiped
+// from the bitmap so that the next query starts from zeros without a memset.  Candidates are a handful to a few hundred; the
+// O(C^2) rank loops of a single CTA stay below 40 us up to 8 k candidates.
+__global__ void __launch_bounds__(1024)
+kfdbFinalKernel(const int* __restrict__ counters, const int* __restrict__ candSlot, const unsigned long long* __restrict__ key,
+                const int* __restrict__ dNeigh, const int* __restrict__ slotOfId, int idCap, const int* __restrict__ dKfId, int loop,
+                long long qid, const long long* __restrict__ query, const int* __restrict__ words, const float* __restrict__ score,
+                float bestAcc0, float* __restrict__ acc, int* __restrict__ best, int* __restrict__ emit, int32_t* __restrict__ out, int cap,
+                int* __restrict__ nOut, const int32_t* __restrict__ qIds, int nq, int nwords, uint32_t* __restrict__ bitmap)
 {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= counters[1]) return;
-    const int minCommon = (int)((float)counters[0] * 0.8f);
-    const int s = candSlot[c];
-    float bestScore = score[s], a = bestScore;
-    int bestId = dKfId[s];
-    for (int j = 0; j < 10; ++j) {
-        const int id = dNeigh[s * 10 + j];
-        if (id < 0) break;
-        if (id >= idCap) continue;
-        const int s2 = slotOfId[id];
-        if (s2 < 0) continue;                                    // not (or no longer) in the database: never met by this query
-        if (query[s2] != qid) continue;
-        if (loop && !(words[s2] > minCommon)) continue;          // :206; the relocalisation form has no such test (:346-348)
-        const float sc = score[s2];
-        a += sc;
-        if (sc > bestScore) { bestId = id; bestScore = sc; }
+    __shared__ int sBestAcc, sOut;
+    const int n = counters[1];
+    if (threadIdx.x == 0) { sBestAcc = __float_as_int(bestAcc0); sOut = 0; }
+    __syncthreads();
+    const int minCommon = (int)((float)counters[0] * 0.8f);      // int * float -> float -> int, :161 / :312
+    for (int c = threadIdx.x; c < n; c += blockDim.x) {
+        const int s = candSlot[c];
+        float bestScore = score[s], a = bestScore;
+        int bestId = dKfId[s];
+        for (int j = 0; j < 10; ++j) {
+            const int id = dNeigh[s * 10 + j];
+            if (id < 0) break;
+            if (id >= idCap) continue;
+            const int s2 = slotOfId[id];
+            if (s2 < 0) continue;                                // not (or no longer) in the database: never met by this query
+            if (query[s2] != qid) continue;
+            if (loop && !(words[s2] > minCommon)) continue;      // :206; the relocalisation form has no such test (:346-348)
+            const float sc = score[s2];
+            a += sc;
+            if (sc > bestScore) { bestId = id; bestScore = sc; }
+        }
+        acc[c] = a; best[c] = bestId;
+        atomicMaxFloat(&sBestAcc, a);
     }
-    acc[c] = a; best[c] = bestId;
-    atomicMaxFloat(bestAcc, a);
-}
-
-// K5a: kept by the 0.75 gate and not preceded (in list order) by a kept candidate with the same best keyframe
-__global__ void kfdbEmitKernel(const int* __restrict__ counters, const unsigned long long* __restrict__ key, const float* __restrict__ acc,
-                               const int* __restrict__ best, int* __restrict__ emit)
-{
-    const int c = blockIdx.x * blockDim.x + threadIdx.x, n = counters[1];
-    if (c >= n) return;
-    const float retain = 0.75f * __int_as_float(counters[2]);
-    int e = acc[c] > retain;
-    if (e) {
+    __syncthreads();
+    const float retain = 0.75f * __int_as_float(sBestAcc);       // :227 / :368
+    for (int c = threadIdx.x; c < n; c += blockDim.x) {          // kept, and not preceded (in list order) by a kept candidate with the same best keyframe
+        int e = acc[c] > retain;
+        if (e) {
+            const unsigned long long k = key[c];
+            const int b = best[c];
+            for (int j = 0; j < n && e; ++j) if (key[j] < k && best[j] == b && acc[j] > retain) e = 0;
+        }
+        emit[c] = e;
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < n; c += blockDim.x) {          // output position = emitting candidates in front
+        if (!emit[c]) continue;
         const unsigned long long k = key[c];
-        const int b = best[c];
-        for (int j = 0; j < n && e; ++j) if (key[j] < k && best[j] == b && acc[j] > retain) e = 0;
+        int pos = 0;
+        for (int j = 0; j < n; ++j) pos += (emit[j] && key[j] < k);
+        if (pos < cap) out[pos] = best[c];
+        atomicAdd(&sOut, 1);
     }
-    emit[c] = e;
-}
-
-// K5b: output position = emitting candidates in front
-__global__ void kfdbWriteKernel(int* __restrict__ counters, const unsigned long long* __restrict__ key, const int* __restrict__ best,
-                                const int* __restrict__ emit, int32_t* __restrict__ out, int cap, int* __restrict__ nOut)
-{
-    const int c = blockIdx.x * blockDim.x + threadIdx.x, n = counters[1];
-    if (c >= n || !emit[c]) return;
-    const unsigned long long k = key[c];
-    int pos = 0;
-    for (int j = 0; j < n; ++j) pos += (emit[j] && key[j] < k);
-    if (pos < cap) out[pos] = best[c];
-    atomicAdd(nOut, 1);
+    for (int i = threadIdx.x; i < nq; i += blockDim.x) { const int w = qIds[i]; if (w >= 0 && w < nwords) bitmap[w >> 5] = 0u; }
+    __syncthreads();
+    if (threadIdx.x == 0) *nOut = sOut;
 }
 
 template <typename T> static int growArray(Ctx* c, T*& p, size_t oldN, size_t newN)
@@ -289,7 +310,9 @@ extern "C" int orbx_kfdb_create(orbx_ctx* h, int nwords, orbx_kfdb** out)
     d->ctx = h; d->nwords = nwords;
     int rc = ORBX_OK;
     if (cudaMalloc(&d->dBitmap, sizeof(uint32_t) * ((size_t)nwords / 32 + 1)) != cudaSuccess ||
+        cudaMalloc(&d->dQPos, sizeof(int32_t) * (size_t)nwords) != cudaSuccess ||
         cudaMalloc(&d->dCounters, sizeof(int) * 8) != cudaSuccess) rc = ORBX_E_CUDA;
+    if (!rc && cudaMemsetAsync(d->dBitmap, 0, sizeof(uint32_t) * ((size_t)nwords / 32 + 1), c->stream) != cudaSuccess) rc = ORBX_E_CUDA;
     if (!rc) rc = kfdbGrowSlots(d, 1);
     if (!rc) rc = kfdbGrowIds(d, 0);
     if (rc) { orbx_kfdb_destroy(d); return rc; }
@@ -305,7 +328,7 @@ extern "C" void orbx_kfdb_destroy(orbx_kfdb* d)
     cudaStreamSynchronize(c->stream);
     void* all[] = {d->dIds, d->dVals, d->dSeg, d->dLen, d->dKfId, d->dAlive, d->dNeigh, d->dLoopQuery, d->dRelocQuery, d->dLoopWords,
                    d->dRelocWords, d->dLoopScore, d->dRelocScore, d->dExclStamp, d->dInList, d->dFirstWord, d->dKey, d->dCandSlot, d->dBest,
-                   d->dEmit, d->dAcc, d->dSlotOfId, d->dBitmap, d->dQIds, d->dQVals, d->dConn, d->dCounters, d->dOut, d->dNOut};
+                   d->dEmit, d->dAcc, d->dSlotOfId, d->dBitmap, d->dQPos, d->dQIds, d->dQVals, d->dConn, d->dCounters, d->dOut, d->dNOut};
     for (void* p : all) if (p) cudaFree(p);
     delete d;
 }
@@ -414,26 +437,23 @@ static int kfdbEnqueue(orbx_kfdb* d, int loop, long long qid, const int32_t* dQI
 {
     Ctx* c = &d->ctx->c;
     const int N = d->nslots;
-    ORBX_CUDA(c, cudaMemsetAsync(dNOut, 0, sizeof(int), c->stream));
-    if (!N || !nq) return ORBX_OK;
+    if (!N || !nq) { ORBX_CUDA(c, cudaMemsetAsync(dNOut, 0, sizeof(int), c->stream)); return ORBX_OK; }
     d->stamp++;
-    ORBX_CUDA(c, cudaMemsetAsync(d->dBitmap, 0, sizeof(uint32_t) * ((size_t)d->nwords / 32 + 1), c->stream));
     const int nb = std::max(std::max(nq, nconn), 1);
-    kfdbBeginKernel<<<(nb + 255) / 256, 256, 0, c->stream>>>(dQIds, nq, d->nwords, d->dBitmap, d->dConn, nconn, d->dSlotOfId, d->idCap,
+    kfdbBeginKernel<<<(nb + 255) / 256, 256, 0, c->stream>>>(dQIds, nq, d->nwords, d->dBitmap, d->dQPos, d->dConn, nconn, d->dSlotOfId, d->idCap,
                                                             d->dExclStamp, d->stamp, d->dCounters, loop ? minScore : 0.f);
     long long* query = loop ? d->dLoopQuery : d->dRelocQuery;
     int* words = loop ? d->dLoopWords : d->dRelocWords;
     float* score = loop ? d->dLoopScore : d->dRelocScore;
-    const int warpGrid = (N + 7) / 8, candGrid = (N + 127) / 128;
+    const int warpGrid = (N + 7) / 8;
     kfdbSharedKernel<<<warpGrid, 256, 0, c->stream>>>(N, d->dSeg, d->dLen, d->dAlive, d->dIds, d->dBitmap, loop, qid, d->dExclStamp, d->stamp,
                                                      query, words, d->dInList, d->dFirstWord, d->dCounters);
-    kfdbScoreKernel<<<warpGrid, 256, 0, c->stream>>>(N, d->dSeg, d->dLen, d->dIds, d->dVals, d->dBitmap, dQIds, dQVals, nq, loop, minScore,
+    kfdbScoreKernel<<<N, 256, 0, c->stream>>>(N, d->dSeg, d->dLen, d->dIds, d->dVals, d->dBitmap, d->dQPos, dQVals, nq, loop, minScore,
                                                     d->dInList, words, d->dFirstWord, score, d->dCounters, d->dKey, d->dCandSlot);
-    // the candidate count stays on the device: the three candidate kernels are sized for the worst case and exit early
-    kfdbGroupKernel<<<candGrid, 128, 0, c->stream>>>(d->dCounters, d->dCandSlot, d->dNeigh, d->dSlotOfId, d->idCap, d->dKfId, loop, qid, query,
-                                                    words, score, d->dAcc, d->dBest, d->dCounters + 2);
-    kfdbEmitKernel<<<candGrid, 128, 0, c->stream>>>(d->dCounters, d->dKey, d->dAcc, d->dBest, d->dEmit);
-    kfdbWriteKernel<<<candGrid, 128, 0, c->stream>>>(d->dCounters, d->dKey, d->dBest, d->dEmit, dOut, cap, dNOut);
+    // the candidate count stays on the device: one CTA walks however many there are
+    kfdbFinalKernel<<<1, 1024, 0, c->stream>>>(d->dCounters, d->dCandSlot, d->dKey, d->dNeigh, d->dSlotOfId, d->idCap, d->dKfId, loop, qid, query,
+                                              words, score, loop ? minScore : 0.f, d->dAcc, d->dBest, d->dEmit, dOut, cap, dNOut, dQIds, nq,
+                                              d->nwords, d->dBitmap);
     ORBX_CUDA(c, cudaGetLastError());
     return ORBX_OK;
 }
@@ -484,7 +504,7 @@ extern "C" int orbx_kfdb_detect_loop(orbx_kfdb* d, long long query_id, const int
     if (nconnected) ORBX_CUDA(c, cudaMemcpyAsync(d->dConn, connected, sizeof(int) * (size_t)nconnected, cudaMemcpyHostToDevice, c->stream));
     stageBegin(c, ST_BOW);
     rc = kfdbEnqueue(d, 1, query_id, d->dQIds, d->dQVals, nq, nconnected, min_score, d->dOut, cap, d->dNOut);
-    stageEnd(c, ST_BOW, (d->nslots && nq) ? 6 : 0);
+    stageEnd(c, ST_BOW, (d->nslots && nq) ? 4 : 0);
     if (rc) return rc;
     int n = 0;
     ORBX_CUDA(c, cudaMemcpyAsync(&n, d->dNOut, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
@@ -518,7 +538,7 @@ extern "C" int orbx_kfdb_detect_reloc(orbx_kfdb* d, int nqueries, const long lon
     for (int q = 0; q < nqueries && !rc; ++q) {
         const int nq = seg[q + 1] - seg[q];
         rc = kfdbEnqueue(d, 0, query_ids[q], d->dQIds + seg[q], d->dQVals + seg[q], nq, 0, 0.f, d->dOut + (size_t)q * cap, cap, d->dNOut + q);
-        if (d->nslots && nq) launches += 6;
+        if (d->nslots && nq) launches += 4;
     }
     stageEnd(c, ST_BOW, launches);
     if (rc) return rc;
