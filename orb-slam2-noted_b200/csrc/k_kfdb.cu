@@ -38,7 +38,7 @@ struct orbx_kfdb {
     long long *dLoopQuery = nullptr, *dRelocQuery = nullptr;
     int *dLoopWords = nullptr, *dRelocWords = nullptr;
     float *dLoopScore = nullptr, *dRelocScore = nullptr;
-    int *dExclStamp = nullptr, *dInList = nullptr, *dFirstWord = nullptr;
+    int *dExclStamp = nullptr, *dInList = nullptr, *dFirstWord = nullptr, *dListed = nullptr;   // dListed: slots that share words with the query
     // candidates of the current query
     unsigned long long* dKey = nullptr; int *dCandSlot = nullptr, *dBest = nullptr, *dEmit = nullptr; float* dAcc = nullptr;
     // id -> slot
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(256)
 kfdbSharedKernel(int nslots, const int* __restrict__ dSeg, const int* __restrict__ dLen, const int* __restrict__ dAlive,
                  const int32_t* __restrict__ ids, const uint32_t* __restrict__ bitmap, int loop, long long qid,
                  const int* __restrict__ exclStamp, int stamp, long long* __restrict__ query, int* __restrict__ words,
-                 int* __restrict__ inList, int* __restrict__ firstWord, int* __restrict__ counters)
+                 int* __restrict__ inList, int* __restrict__ firstWord, int* __restrict__ counters, int* __restrict__ listed)
 {
     const int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (s >= nslots) return;
@@ -120,7 +120,10 @@ kfdbSharedKernel(int nslots, const int* __restrict__ dSeg, const int* __restrict
     if (cnt) {                                                   // the keyframe is met `cnt` times while the query's words are walked
         if (query[s] != qid) {
             if (loop && exclStamp[s] == stamp) words[s] = 1;     // connected: mnLoopWords reset at every visit, then ++ (:131-141)
-            else { query[s] = qid; words[s] = cnt; in = 1; firstWord[s] = first; atomicMax(&counters[0], cnt); }
+            else {
+                query[s] = qid; words[s] = cnt; in = 1; firstWord[s] = first; atomicMax(&counters[0], cnt);
+                listed[atomicAdd(&counters[3], 1)] = s;          // lKFsSharingWords, unordered (the order comes from the keys)
+            }
         } else words[s] += cnt;                                  // a query id seen before: counted on, not listed again
     }
     inList[s] = in;
@@ -132,8 +135,8 @@ __device__ __forceinline__ void atomicMaxFloat(int* addr, float v)
     while (v > __int_as_float(old)) { const int assumed = old; old = atomicCAS(addr, assumed, __float_as_int(v)); if (old == assumed) break; }
 }
 
-// K3: one CTA per slot; the listed slots with more than minCommon words go on (a handful), the rest leave at once.  All 256
-// threads compute the terms of the common words (independent loads, so the keyframe's ~1000 entries cost two or three
+// K3: the CTAs walk the list of keyframes that share words (K2) and take those with more than minCommon of them (a handful).
+// All 256 threads compute the terms of the common words (independent loads, so the keyframe's ~1000 entries cost two or three
 // round trips), then warp 0 adds them in ascending word order -- the order of L1Scoring::score's merge -- from shared memory.
 constexpr int kScoreTile = 2048;
 __global__ void __launch_bounds__(256)
@@ -141,14 +144,17 @@ kfdbScoreKernel(int nslots, const int* __restrict__ dSeg, const int* __restrict_
                 const double* __restrict__ vals, const uint32_t* __restrict__ bitmap, const int32_t* __restrict__ qpos,
                 const double* __restrict__ qVals, int nq, int loop, float minScore, const int* __restrict__ inList,
                 const int* __restrict__ words, const int* __restrict__ firstWord, float* __restrict__ score,
-                int* __restrict__ counters, unsigned long long* __restrict__ key, int* __restrict__ candSlot)
+                int* __restrict__ counters, unsigned long long* __restrict__ key, int* __restrict__ candSlot,
+                const int* __restrict__ listed)
 {
     __shared__ double sTerm[kScoreTile];
     __shared__ uint32_t sHit[kScoreTile / 32];
-    const int s = blockIdx.x, lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
-    if (s >= nslots || !inList[s]) return;
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
     const int minCommon = (int)((float)counters[0] * 0.8f);      // int * float -> float -> int, :161 / :312
-    if (!(words[s] > minCommon)) return;
+    const int nListed = counters[3];
+  for (int li = blockIdx.x; li < nListed; li += gridDim.x) {
+    const int s = listed[li];
+    if (!(words[s] > minCommon)) continue;                        // uniform over the CTA
     const int seg = dSeg[s], len = dLen[s];
     double sum = 0.0;                                             // lives in warp 0
     for (int t0 = 0; t0 < len; t0 += kScoreTile) {
@@ -182,14 +188,16 @@ kfdbScoreKernel(int nslots, const int* __restrict__ dSeg, const int* __restrict_
         }
         __syncthreads();
     }
-    if (threadIdx.x) return;
-    const float si = (float)(-sum / 2.0);
-    score[s] = si;
-    if (!loop || si >= minScore) {
-        const int c = atomicAdd(&counters[1], 1);
-        key[c] = ((unsigned long long)(unsigned)firstWord[s] << 32) | (unsigned)s;
-        candSlot[c] = s;
+    if (threadIdx.x == 0) {
+        const float si = (float)(-sum / 2.0);
+        score[s] = si;
+        if (!loop || si >= minScore) {
+            const int c = atomicAdd(&counters[1], 1);
+            key[c] = ((unsigned long long)(unsigned)firstWord[s] << 32) | (unsigned)s;
+            candSlot[c] = s;
+        }
     }
+  }
 }
 
 // K4 + K5 in one CTA: group accumulation :193-224 / :337-364 (one candidate per thread step), the 0.75 * best gate,
@@ -208,24 +216,30 @@ kfdbFinalKernel(const int* __restrict__ counters, const int* __restrict__ candSl
     if (threadIdx.x == 0) { sBestAcc = __float_as_int(bestAcc0); sOut = 0; }
     __syncthreads();
     const int minCommon = (int)((float)counters[0] * 0.8f);      // int * float -> float -> int, :161 / :312
-    for (int c = threadIdx.x; c < n; c += blockDim.x) {
-        const int s = candSlot[c];
-        float bestScore = score[s], a = bestScore;
-        int bestId = dKfId[s];
-        for (int j = 0; j < 10; ++j) {
-            const int id = dNeigh[s * 10 + j];
-            if (id < 0) break;
-            if (id >= idCap) continue;
-            const int s2 = slotOfId[id];
-            if (s2 < 0) continue;                                // not (or no longer) in the database: never met by this query
-            if (query[s2] != qid) continue;
-            if (loop && !(words[s2] > minCommon)) continue;      // :206; the relocalisation form has no such test (:346-348)
-            const float sc = score[s2];
-            a += sc;
-            if (sc > bestScore) { bestId = id; bestScore = sc; }
+    {   // one warp per candidate: lanes 0-9 fetch its covisible keyframes' state side by side, then the sum runs in list order
+        const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5, nWarps = blockDim.x >> 5;
+        for (int c = wrp; c < n; c += nWarps) {
+            const int s = candSlot[c];
+            const int id = lane < 10 ? dNeigh[s * 10 + lane] : -1;
+            float sc = 0.f;
+            bool use = false;
+            if (id >= 0 && id < idCap) {
+                const int s2 = slotOfId[id];                     // < 0: not (or no longer) in the database, never met by this query
+                if (s2 >= 0 && query[s2] == qid && !(loop && !(words[s2] > minCommon))) { sc = score[s2]; use = true; }   // :206 / :346-348
+            }
+            // the list ends at the first -1 (set_covisible pads with -1), so entries behind a gap do not exist
+            const uint32_t gap = __ballot_sync(0xffffffffu, lane < 10 && id < 0);
+            const uint32_t valid = __ballot_sync(0xffffffffu, use) & (gap ? ((1u << (__ffs(gap) - 1)) - 1u) : 0x3ffu);
+            float bestScore = score[s], a = bestScore;
+            int bestId = dKfId[s];
+            #pragma unroll
+            for (int j = 0; j < 10; ++j) {
+                const float scj = __shfl_sync(0xffffffffu, sc, j);
+                const int idj = __shfl_sync(0xffffffffu, id, j);
+                if ((valid >> j) & 1u) { a += scj; if (scj > bestScore) { bestId = idj; bestScore = scj; } }
+            }
+            if (lane == 0) { acc[c] = a; best[c] = bestId; atomicMaxFloat(&sBestAcc, a); }
         }
-        acc[c] = a; best[c] = bestId;
-        atomicMaxFloat(&sBestAcc, a);
     }
     __syncthreads();
     const float retain = 0.75f * __int_as_float(sBestAcc);       // :227 / :368
@@ -276,7 +290,7 @@ static int kfdbGrowSlots(orbx_kfdb* d, int need)
     int rc;
 #define G(p) if ((rc = growArray(c, d->p, o, n))) return rc
     G(dSeg); G(dLen); G(dKfId); G(dAlive); G(dLoopQuery); G(dRelocQuery); G(dLoopWords); G(dRelocWords); G(dLoopScore); G(dRelocScore);
-    G(dExclStamp); G(dInList); G(dFirstWord); G(dKey); G(dCandSlot); G(dBest); G(dEmit); G(dAcc);
+    G(dExclStamp); G(dInList); G(dFirstWord); G(dListed); G(dKey); G(dCandSlot); G(dBest); G(dEmit); G(dAcc);
 #undef G
     if ((rc = growArray(c, d->dNeigh, o * 10, n * 10))) return rc;
     d->slotsCap = (int)n;
@@ -327,7 +341,7 @@ extern "C" void orbx_kfdb_destroy(orbx_kfdb* d)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     void* all[] = {d->dIds, d->dVals, d->dSeg, d->dLen, d->dKfId, d->dAlive, d->dNeigh, d->dLoopQuery, d->dRelocQuery, d->dLoopWords,
-                   d->dRelocWords, d->dLoopScore, d->dRelocScore, d->dExclStamp, d->dInList, d->dFirstWord, d->dKey, d->dCandSlot, d->dBest,
+                   d->dRelocWords, d->dLoopScore, d->dRelocScore, d->dExclStamp, d->dInList, d->dFirstWord, d->dListed, d->dKey, d->dCandSlot, d->dBest,
                    d->dEmit, d->dAcc, d->dSlotOfId, d->dBitmap, d->dQPos, d->dQIds, d->dQVals, d->dConn, d->dCounters, d->dOut, d->dNOut};
     for (void* p : all) if (p) cudaFree(p);
     delete d;
@@ -447,9 +461,9 @@ static int kfdbEnqueue(orbx_kfdb* d, int loop, long long qid, const int32_t* dQI
     float* score = loop ? d->dLoopScore : d->dRelocScore;
     const int warpGrid = (N + 7) / 8;
     kfdbSharedKernel<<<warpGrid, 256, 0, c->stream>>>(N, d->dSeg, d->dLen, d->dAlive, d->dIds, d->dBitmap, loop, qid, d->dExclStamp, d->stamp,
-                                                     query, words, d->dInList, d->dFirstWord, d->dCounters);
-    kfdbScoreKernel<<<N, 256, 0, c->stream>>>(N, d->dSeg, d->dLen, d->dIds, d->dVals, d->dBitmap, d->dQPos, dQVals, nq, loop, minScore,
-                                                    d->dInList, words, d->dFirstWord, score, d->dCounters, d->dKey, d->dCandSlot);
+                                                     query, words, d->dInList, d->dFirstWord, d->dCounters, d->dListed);
+    kfdbScoreKernel<<<std::min(N, 296), 256, 0, c->stream>>>(N, d->dSeg, d->dLen, d->dIds, d->dVals, d->dBitmap, d->dQPos, dQVals, nq, loop, minScore,
+                                                            d->dInList, words, d->dFirstWord, score, d->dCounters, d->dKey, d->dCandSlot, d->dListed);
     // the candidate count stays on the device: one CTA walks however many there are
     kfdbFinalKernel<<<1, 1024, 0, c->stream>>>(d->dCounters, d->dCandSlot, d->dKey, d->dNeigh, d->dSlotOfId, d->idCap, d->dKfId, loop, qid, query,
                                               words, score, loop ? minScore : 0.f, d->dAcc, d->dBest, d->dEmit, dOut, cap, dNOut, dQIds, nq,
