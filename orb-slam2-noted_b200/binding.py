@@ -15,7 +15,8 @@ class OrbxError(RuntimeError):
 
 
 def lib_path():
-    return os.path.join(HERE, "liborbx.so")
+    """liborbx.so next to this file; env ORBX_LIB names another build of the same library (kernel A/B runs)."""
+    return os.environ.get("ORBX_LIB") or os.path.join(HERE, "liborbx.so")
 
 
 def lib():

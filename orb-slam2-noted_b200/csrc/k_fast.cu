@@ -26,6 +26,10 @@
 
 namespace orbx {
 
+#ifndef ORBX_P0_UNROLL
+#define ORBX_P0_UNROLL 1
+#endif
+constexpr int kP0Unroll = ORBX_P0_UNROLL;        // rows per trip of the pass-0 loop (A/B builds: tools/build_variant.sh)
 constexpr int kCornerCapW = 384;                 // per-warp corner list (scored and dropped when the next step could overflow it)
 constexpr int kMaxCellsPerStrip = 32;
 
@@ -253,7 +257,7 @@ fastStripKernel(const __grid_constant__ GeomSet G, const uint8_t* __restrict__ l
                 const uint32_t* const cSafe = W + 3 * wp + col;     // lanes past the last row read row 0 (masked by vm = 0)
                 const uint32_t* c = W + (y + 3) * wp + col;
                 uint32_t code = (uint32_t)(y << 10) | col;
-                #pragma unroll 1
+                #pragma unroll kP0Unroll
                 for (int yl = warp; yl < rh; yl += yStep, y += yStep, c += yStep * wp, code += (uint32_t)(yStep << 10))
                     quick(y < rh ? c : cSafe, y < rh ? vm : 0u, code);
             }
