@@ -29,6 +29,10 @@ namespace orbx {
 #ifndef ORBX_P0_UNROLL
 #define ORBX_P0_UNROLL 1
 #endif
+#ifndef ORBX_FAST_MINCTAS
+#define ORBX_FAST_MINCTAS 8
+#endif
+constexpr int kFastMinCtas128 = ORBX_FAST_MINCTAS;   // __launch_bounds__ of the 128-thread form: 8 -> 64 registers, 6 -> 80 (shared memory allows 6 CTAs per SM)
 constexpr int kP0Unroll = ORBX_P0_UNROLL;        // rows per trip of the pass-0 loop (A/B builds: tools/build_variant.sh)
 constexpr int kCornerCapW = 384;                 // per-warp corner list (scored and dropped when the next step could overflow it)
 constexpr int kMaxCellsPerStrip = 32;
@@ -442,7 +446,7 @@ int launchFast(Ctx* c, int frame0, int batch)
                                                            c->dCand, c->dCandCount, TP, TR, SP, groupCapW);
             return ORBX_OK;
         };
-        const int rc = fastThreads == 128 ? go(fastStripKernel<128, 8>, 128, &c->smemCfg[SMEM_FAST128])
+        const int rc = fastThreads == 128 ? go(fastStripKernel<128, kFastMinCtas128>, 128, &c->smemCfg[SMEM_FAST128])
                                              : go(fastStripKernel<256, 4>, 256, &c->smemCfg[SMEM_FAST256]);
         if (rc != ORBX_OK) return rc;
         launches = 1;
