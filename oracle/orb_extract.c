@@ -92,25 +92,32 @@ void orc_resize_linear(const uint8_t* src, int sw, int sh, size_t sstride, uint8
     short *cx1 = cx0 + dw, *cy0 = cx1 + dw, *cy1 = cy0 + dh;
     resize_tab(dw, sw, xo, cx0, cx1, 1);
     resize_tab(dh, sh, yo, cy0, cy1, 0); /* y axis: rows are clipped, beta is kept */
+    /* the horizontal pass of a source row is kept while the next destination row still needs it (OpenCV's resize does the
+     * same); values are unchanged */
     int* rows = (int*)malloc(sizeof(int) * 2 * (size_t)dw);
+    int* xo1 = (int*)malloc(sizeof(int) * (size_t)dw);
+    for (int x = 0; x < dw; ++x) xo1[x] = xo[x] + 1 < sw ? xo[x] + 1 : sw - 1;
+    int have[2] = {-1, -1};                 /* source row held by rows[0..dw) / rows[dw..2dw) */
+    int* T[2] = {rows, rows + dw};
     for (int y = 0; y < dh; ++y) {
+        int need[2];
+        for (int k = 0; k < 2; ++k) { int sy = yo[y] + k; if (sy < 0) sy = 0; if (sy > sh - 1) sy = sh - 1; need[k] = sy; }
+        if (have[1] == need[0] && have[0] != need[0]) { int* t = T[0]; T[0] = T[1]; T[1] = t; have[0] = have[1]; have[1] = -1; }
         for (int k = 0; k < 2; ++k) {
-            int sy = yo[y] + k;
-            if (sy < 0) sy = 0;
-            if (sy > sh - 1) sy = sh - 1;
-            const uint8_t* S = src + (size_t)sy * sstride;
-            int* T = rows + k * dw;
-            for (int x = 0; x < dw; ++x) {
-                int sx = xo[x], sx1 = sx + 1 < sw ? sx + 1 : sw - 1;
-                T[x] = S[sx] * cx0[x] + S[sx1] * cx1[x];
-            }
+            if (have[k] == need[k]) continue;
+            if (k == 1 && have[0] == need[1]) { memcpy(T[1], T[0], sizeof(int) * (size_t)dw); have[1] = need[1]; continue; }
+            const uint8_t* S = src + (size_t)need[k] * sstride;
+            int* Tk = T[k];
+            for (int x = 0; x < dw; ++x) Tk[x] = S[xo[x]] * cx0[x] + S[xo1[x]] * cx1[x];
+            have[k] = need[k];
         }
-        int b0 = cy0[y], b1 = cy1[y];
+        const int b0 = cy0[y], b1 = cy1[y];
+        const int *R0 = T[0], *R1 = T[1];
         uint8_t* D = dst + (size_t)y * dstride;
         for (int x = 0; x < dw; ++x)
-            D[x] = (uint8_t)((((b0 * (rows[x] >> 4)) >> 16) + ((b1 * (rows[dw + x] >> 4)) >> 16) + 2) >> 2);
+            D[x] = (uint8_t)((((b0 * (R0[x] >> 4)) >> 16) + ((b1 * (R1[x] >> 4)) >> 16) + 2) >> 2);
     }
-    free(rows); free(cx0); free(xo);
+    free(xo1); free(rows); free(cx0); free(xo);
 }
 
 /* ------- cv::copyMakeBorder BORDER_REFLECT_101 (:1704,1725) ------- */
@@ -138,27 +145,35 @@ void orc_gauss_blur(const uint8_t* src, int w, int h, size_t sstride, uint8_t* d
     static const int k7[7] = {18, 34, 48, 56, 48, 34, 18};
     const int* k = ksize == 9 ? k9 : k7;
     const int r = ksize / 2;
+    /* Same arithmetic as before, loops shaped so that the compiler vectorises them (the interior of a row has no border
+     * test, the kernel taps are the outer loop of the vertical pass): this file is also the CPU baseline's primitive. */
     uint16_t* H = (uint16_t*)malloc(sizeof(uint16_t) * (size_t)w * (size_t)h);
+    uint32_t* A = (uint32_t*)malloc(sizeof(uint32_t) * (size_t)w);
     for (int y = 0; y < h; ++y) {
         const uint8_t* S = src + (size_t)y * sstride;
-        for (int x = 0; x < w; ++x) {
-            int acc = 0;
-            if (x >= r && x < w - r) for (int i = 0; i < ksize; ++i) acc += k[i] * S[x + i - r];
-            else for (int i = 0; i < ksize; ++i) acc += k[i] * S[reflect101(x + i - r, w)];
-            H[(size_t)y * w + x] = (uint16_t)acc;
-        }
+        uint16_t* Hr = H + (size_t)y * w;
+        const int x0 = r < w ? r : w, x1 = w - r > x0 ? w - r : x0;
+        for (int x = 0; x < x0; ++x) { int acc = 0; for (int i = 0; i < ksize; ++i) acc += k[i] * S[reflect101(x + i - r, w)]; Hr[x] = (uint16_t)acc; }
+        if (ksize == 9)
+            for (int x = x0; x < x1; ++x) {
+                const uint8_t* q = S + x - 4;
+                Hr[x] = (uint16_t)(7 * (q[0] + q[8]) + 17 * (q[1] + q[7]) + 32 * (q[2] + q[6]) + 46 * (q[3] + q[5]) + 52 * q[4]);
+            }
+        else
+            for (int x = x0; x < x1; ++x) { int acc = 0; for (int i = 0; i < ksize; ++i) acc += k[i] * S[x + i - r]; Hr[x] = (uint16_t)acc; }
+        for (int x = x1; x < w; ++x) { int acc = 0; for (int i = 0; i < ksize; ++i) acc += k[i] * S[reflect101(x + i - r, w)]; Hr[x] = (uint16_t)acc; }
     }
     for (int y = 0; y < h; ++y) {
-        const uint16_t* R[9];
-        for (int i = 0; i < ksize; ++i) R[i] = H + (size_t)reflect101(y + i - r, h) * w;
         uint8_t* D = dst + (size_t)y * dstride;
-        for (int x = 0; x < w; ++x) {
-            uint32_t acc = 32768;
-            for (int i = 0; i < ksize; ++i) acc += (uint32_t)k[i] * R[i][x];
-            D[x] = (uint8_t)(acc >> 16);
+        for (int x = 0; x < w; ++x) A[x] = 32768;
+        for (int i = 0; i < ksize; ++i) {
+            const uint16_t* R = H + (size_t)reflect101(y + i - r, h) * w;
+            const uint32_t ki = (uint32_t)k[i];
+            for (int x = 0; x < w; ++x) A[x] += ki * R[x];
         }
+        for (int x = 0; x < w; ++x) D[x] = (uint8_t)(A[x] >> 16);
     }
-    free(H);
+    free(A); free(H);
 }
 
 /* ------- cv::fastAtan2 scalar (called at :140); no FMA ------- */
@@ -190,13 +205,18 @@ static const int kRingY[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 
 /* OpenCV cornerScore<16>: max(threshold, best arc-of-9 margin) - 1 */
 int orc_fast_score(const uint8_t* c, size_t stride, int threshold)
 {
-    int d[25], v = c[0];
+    int d[32], v = c[0];
     for (int k = 0; k < 16; ++k) d[k] = v - c[(ptrdiff_t)kRingY[k] * (ptrdiff_t)stride + kRingX[k]];
-    for (int k = 16; k < 25; ++k) d[k] = d[k - 16];
+    for (int k = 16; k < 32; ++k) d[k] = d[k - 16];
+    /* min / max over every arc of 9 by doubling (2, 4, 8 consecutive, then the ninth): the same values as the plain double loop */
+    int mn2[24], mx2[24], mn4[22], mx4[22];
+    for (int k = 0; k < 24; ++k) { mn2[k] = d[k] < d[k + 1] ? d[k] : d[k + 1]; mx2[k] = d[k] > d[k + 1] ? d[k] : d[k + 1]; }
+    for (int k = 0; k < 22; ++k) { mn4[k] = mn2[k] < mn2[k + 2] ? mn2[k] : mn2[k + 2]; mx4[k] = mx2[k] > mx2[k + 2] ? mx2[k] : mx2[k + 2]; }
     int best = threshold;
     for (int k = 0; k < 16; ++k) {
-        int mn = d[k], mx = d[k];
-        for (int i = 1; i < 9; ++i) { if (d[k + i] < mn) mn = d[k + i]; if (d[k + i] > mx) mx = d[k + i]; }
+        int mn = mn4[k] < mn4[k + 4] ? mn4[k] : mn4[k + 4], mx = mx4[k] > mx4[k + 4] ? mx4[k] : mx4[k + 4];
+        if (d[k + 8] < mn) mn = d[k + 8];
+        if (d[k + 8] > mx) mx = d[k + 8];
         if (mn > best) best = mn;       /* all 9 darker than centre by >= mn  */
         if (-mx > best) best = -mx;     /* all 9 brighter                     */
     }
@@ -206,6 +226,14 @@ int orc_fast_score(const uint8_t* c, size_t stride, int threshold)
 static inline int fast_is_corner(const uint8_t* c, size_t stride, int t)
 {
     int v = c[0];
+    /* cv::FAST's own early exits (a 9-arc holds ring pixel 0 or 8, and 4 or 12): same result, most pixels leave here */
+    {
+        const int hi = v + t, lo = v - t;
+        const int p0 = c[3 * (ptrdiff_t)stride], p8 = c[-3 * (ptrdiff_t)stride];
+        if (!((p0 > hi) | (p0 < lo) | (p8 > hi) | (p8 < lo))) return 0;
+        const int p4 = c[3], p12 = c[-3];
+        if (!((p4 > hi) | (p4 < lo) | (p12 > hi) | (p12 < lo))) return 0;
+    }
     unsigned br = 0, dk = 0; /* ring bitmasks: brighter than v+t / darker than v-t */
     for (int k = 0; k < 16; ++k) {
         int p = c[(ptrdiff_t)kRingY[k] * (ptrdiff_t)stride + kRingX[k]];
