@@ -295,6 +295,7 @@ int orbx_create(orbx_ctx** out, int device, int nfeatures, float scale_factor, i
         if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (cudaEventCreateWithFlags(&c->evJoin, cudaEventDisableTiming) != cudaSuccess) { rc = ORBX_E_CUDA; break; }
         if (const char* e = getenv("ORBX_CHUNK")) c->chunk = atoi(e);
+        if (const char* e = getenv("ORBX_FRAME_GRAPH")) c->frameGraphOff = atoi(e) == 0;
         if (const char* e = getenv("ORBX_OVERLAP_BLUR")) { c->overlapBlur = atoi(e) != 0; c->blurAfterFast = atoi(e) == 2; }
         if (const char* e = getenv("ORBX_RESIZE_WIDE")) c->resizeWide = atoi(e) != 0;
         if (const char* e = getenv("ORBX_FAST_THREADS")) c->fastThreads = atoi(e) == 128 ? 128 : 256;
@@ -350,6 +351,7 @@ void orbx_destroy(orbx_ctx* h)
     for (cudaEvent_t e : c->evDone) cudaEventDestroy(e);
     if (c->sIn) cudaStreamDestroy(c->sIn);
     if (c->sOut) cudaStreamDestroy(c->sOut);
+    if (c->frameGraph) cudaGraphExecDestroy(c->frameGraph);
     if (c->stream2) cudaStreamDestroy(c->stream2);
     if (c->evJoin) cudaEventDestroy(c->evJoin);
     if (c->evFork) cudaEventDestroy(c->evFork);
@@ -576,7 +578,11 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
             mark(c->sIn);
             ORBX_CUDA(c, cudaStreamWaitEvent(c->stream, c->evIn[i], 0));
         }
-        rc = launchPyramid(c, f0, n);
+        // The five stages of this chunk.  For ONE frame from and to host buffers (the per-frame call of a tracking thread) the
+        // dozen launches are the latency, so their sequence is captured once per geometry into a CUDA graph and replayed
+        // (the first call with a geometry runs eagerly: it sets function attributes and sizes arenas; the second captures).
+        auto runStages = [&]() -> int {
+        int rc = launchPyramid(c, f0, n);
         const bool fewCtas = (long long)n * c->nStrips < 148 * 8;   // a frame or two: kernels leave most SMs idle, so the blur runs beside FAST
         if (!rc && (c->overlapBlur || fewCtas) && !twoStreams) {
             // the blur only needs the pyramid: it runs on a side stream next to FAST + quadtree (FAST is limited to 5 CTAs per
@@ -605,6 +611,37 @@ int orbx_extract_batch(orbx_ctx* h, const uint8_t* imgs, int batch, int w, int h
             if (!rc) rc = launchBlur(c, f0, n);
         }
         if (!rc) rc = launchDescribe(c, f0, n, dK, dD, sc, dN, dense);
+        return rc;
+        };
+        const bool graphable = batch == 1 && !inDev && !outDev && !c->profiling && !c->frameGraphOff && !dbgTl;
+        if (graphable) {
+            const unsigned long long key[6] = {(unsigned long long)c->geomStamp, (unsigned long long)(uintptr_t)dK, (unsigned long long)(uintptr_t)dD,
+                                               (unsigned long long)(uintptr_t)dN, (unsigned long long)sc,
+                                               (unsigned long long)(uintptr_t)c->lvl0 ^ ((unsigned long long)c->lvl0Pitch << 48)};
+            if (c->frameGraph && !memcmp(key, c->frameGraphKey, sizeof(key))) {
+                if (cudaGraphLaunch(c->frameGraph, c->stream) != cudaSuccess) { cudaGetLastError(); c->frameGraphOff = true; rc = runStages(); }
+                else c->kernelLaunches += c->frameGraphLaunches;
+            } else if (!memcmp(key, c->frameGraphSeen, sizeof(key))) {          // second call with these buffers: capture
+                if (c->frameGraph) { cudaGraphExecDestroy(c->frameGraph); c->frameGraph = nullptr; }
+                const long long l0 = c->kernelLaunches;
+                cudaGraph_t g = nullptr;
+                bool ok = cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+                int crc = ok ? runStages() : ORBX_OK;
+                if (ok) ok = cudaStreamEndCapture(c->stream, &g) == cudaSuccess && g && crc == ORBX_OK;
+                const int captured = (int)(c->kernelLaunches - l0);
+                c->kernelLaunches = l0;
+                if (ok) ok = cudaGraphInstantiate(&c->frameGraph, g, 0) == cudaSuccess;
+                if (g) cudaGraphDestroy(g);
+                if (ok) ok = cudaGraphLaunch(c->frameGraph, c->stream) == cudaSuccess;
+                if (ok) { memcpy(c->frameGraphKey, key, sizeof(key)); c->frameGraphLaunches = captured; c->kernelLaunches += captured; }
+                else {                                                          // whatever went wrong: no graphs on this context, run as always
+                    cudaGetLastError();
+                    if (c->frameGraph) { cudaGraphExecDestroy(c->frameGraph); c->frameGraph = nullptr; }
+                    c->frameGraphOff = true;
+                    rc = runStages();
+                }
+            } else { memcpy(c->frameGraphSeen, key, sizeof(key)); rc = runStages(); }
+        } else rc = runStages();
         if (rc) { c->stream = mainStream; return rc; }
         if (!outDev) {
             ORBX_CUDA(c, cudaEventRecord(c->evDone[i], c->stream));

@@ -110,6 +110,11 @@ struct Ctx {
     uint8_t* dIn = nullptr; size_t dInBytes = 0;       // H2D staging for level 0 when input is on host
     const uint8_t* lvl0 = nullptr; size_t lvl0Pitch = 0, lvl0FrameStride = 0; // where level 0 of the last batch lives
     int lastBatch = 0;
+    // the stages of a single host frame as a CUDA graph (orbx_api.cu); env ORBX_FRAME_GRAPH=0 turns it off
+    cudaGraphExec_t frameGraph = nullptr;
+    unsigned long long frameGraphKey[6] = {}, frameGraphSeen[6] = {};
+    int frameGraphLaunches = 0;
+    bool frameGraphOff = false;
     // instrumentation
     bool profiling = false;
     double stageMs[ST_COUNT] = {};
