@@ -50,7 +50,16 @@ def test_cpp_dropin_matcher(tmp_path):
     (oracle/_ref) run on the same file."""
     import matcher_scene, ref_lib
     subprocess.run(["make", "-C", os.path.join(ROOT, "host"), "-s"], check=True)
+    import hashlib, json
+    golden = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_outputs.json")))["matcher_scenes"]
     got = matcher_scene.check_scene(_dropin_driver, tmp_path)
+    assert hashlib.sha256(got).hexdigest() == golden["scene11"]["sha256"]          # the reference's output file, committed as a hash
+    for k, name in enumerate(("general21", "general22")):
+        g = golden[name]
+        d = tmp_path / f"golden{k}"
+        d.mkdir()
+        out = matcher_scene.check_scene(_dropin_driver, d, g["seed"], g["n1"], g["n2"], general_poses=True)
+        assert len(out) == g["bytes"] and hashlib.sha256(out).hexdigest() == g["sha256"], name
     if ref_lib.available():
         rin, rout = str(tmp_path / "m_in.bin"), str(tmp_path / "ref_out.bin")
         assert ref_lib.lib().ref_run_matcher_scene(rin.encode(), rout.encode()) == 0
