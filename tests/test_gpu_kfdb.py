@@ -80,3 +80,38 @@ def test_kfdb_batched_relocalisation_and_limits(ctx):
     g.db.add(3, base[2], base[3])
     assert g.db.DetectRelocalizationCandidates(901, base[2], base[3]) == [3]
     g.close(); o.close()
+
+
+def test_kfdb_thousands_of_candidates_and_degenerate_inputs(ctx):
+    """3000 near-identical keyframes: every one passes the 0.8 gate, so the one-CTA final stage walks thousands of candidates
+    (groups, duplicates of best keyframes, output ranks) instead of a handful; plus empty BowVectors, an empty database and
+    query words that no keyframe holds."""
+    P = pkg()
+    nw = 5000
+    rng = np.random.default_rng(11)
+    base_w = np.sort(rng.choice(nw, 120, replace=False)).astype(np.int32)
+    g, o = K.GpuBackend(nw, ctx), K.OracleBackend(nw)
+    assert g.reloc(1, base_w, np.full(len(base_w), 1.0 / len(base_w))) == []           # empty database
+    kfs = []
+    for k in range(3000):
+        w = base_w.copy()
+        if k % 7 == 3:                                                                # a few differ in some words
+            w = np.unique(np.concatenate([w[: 100 + k % 15], rng.integers(0, nw, 10).astype(np.int32)])).astype(np.int32)
+        v = np.abs(np.sin(np.arange(len(w)) * 0.37 + k * 0.01)) + 0.05
+        kfs.append((w, v / v.sum()))
+    for b in (g, o):
+        for k, (w, v) in enumerate(kfs):
+            b.new(k, w, v); b.add(k)
+            b.covis(k, np.array([(k * 13 + j * 101) % 3000 for j in range(k % 11)], np.int32))
+        b.new(5000, np.zeros(0, np.int32), np.zeros(0)); b.add(5000)                  # a keyframe without words
+    qv = np.full(len(base_w), 1.0 / len(base_w))
+    for qid, (w, v) in enumerate([(base_w, qv), (base_w[::2], qv[::2] * 2), (np.zeros(0, np.int32), np.zeros(0)),
+                                  (np.array([nw - 1], np.int32) if (nw - 1) not in base_w else np.array([nw - 2], np.int32), np.ones(1))], 100):
+        got, want = g.reloc(qid, w, v, cap=4096), o.reloc(qid, w, v, cap=4096)
+        assert got == want, (qid, len(got), len(want))
+    assert len(g.reloc(200, base_w, qv, cap=4096)) > 100
+    lg = g.db.DetectLoopCandidates(7000, base_w, qv, np.arange(0, 3000, 3, dtype=np.int32), 0.2, cap=4096)
+    for b in (o,):
+        b.new(7000, base_w, qv)
+    assert lg == o.loop(7000, np.arange(0, 3000, 3, dtype=np.int32), 0.2, cap=4096) and len(lg) > 50
+    g.close(); o.close()
