@@ -126,6 +126,17 @@ if rank == 0:
     rec = mo[1][:mt].cpu().numpy()
     assert mt == int(cnt.sum()) and np.array_equal(rec[:cnt[0, 0], 0], np.arange(0, 64, 7)) and set(rec[:, 1]) == set(range(100, 100 + world))
     print("GATHER_OK", world, total, mt)
+# a rank with nothing to send (every count zero): nothing is staged, sent or received for it, the others are unaffected
+nz = n if rank == 0 else torch.zeros_like(n)
+outz = tuple(torch.zeros_like(t) for t in out)
+tz = comm.gather_frames(k, d, nz, outz, root=0)
+comm.sync()
+if rank == 0:
+    mine = int(n.sum())
+    assert tz == mine and torch.equal(outz[0][:B], n) and int(outz[0][B:].sum()) == 0
+    assert torch.equal(outz[1][:mine], out[1][:mine]) and torch.equal(outz[2][:mine], out[2][:mine])
+else:
+    assert tz > 1000                                     # every rank learns the same total (rank 0's records)
 # dense records (ORBX_OUT_DENSE) need no compaction: sent from where they lie (here still through ncclSend/ncclRecv)
 kd, dd, nd = torch.zeros_like(k), torch.zeros_like(d), torch.zeros_like(n)
 ex.extract_batch_device(torch.from_numpy(frames(rank)).to(dev), kd, dd, nd, dense=True)
@@ -136,7 +147,7 @@ comm.sync()
 if rank == 0:
     assert torch.equal(out3[0], out[0]) and torch.equal(out3[1][:total], out[1][:total]) and torch.equal(out3[2][:total], out[2][:total])
 # the same gathers through the root's peer window: the other rank writes into rank 0's memory
-assert comm.stats() == (0, 3)
+assert comm.stats() == (0, 4)
 shapes = (((rows_out, 28), torch.uint8), ((rows_out, 32), torch.uint8), ((world * 3 * 64, 2), torch.int32))
 win = comm.window(sh.Comm.carve_bytes(*shapes) if rank == 0 else 0)
 have = torch.tensor([0 if win is None else 1]); dist.broadcast(have, src=0)
@@ -163,7 +174,7 @@ else:
             assert bool((out2[1][total:total + 4] == 0xEE).all())               # nothing written past the records
             k2[:total].zero_(); torch.cuda.synchronize()
         dist.barrier()                                   # the root has looked before the next round overwrites
-    assert comm.stats() == (4, 3), comm.stats()
+    assert comm.stats() == (4, 4), comm.stats()
     if rank == 0:
         print("WINDOW_OK", world)
 dist.barrier()
