@@ -11,8 +11,10 @@ A step = one pass of ORBextractor::operator() over a batch of B synthetic frames
            Two host threads, one extractor handle and one set of pinned buffers each, take alternate
            batches through the synchronous orbx_extract_batch, so the PCIe link stays busy between calls;
            every step's input copy and result read-back is inside the timed region.
-           With N > 1 every step's results are also all-gathered over NCCL (side stream, inside the
-           timed region of `value`).
+           With N > 1 every step's results are gathered to rank 0 as dense records (orbx_gather_frames_dense:
+           peer copies into rank 0's NVLink window on the communicator's own stream, inside the timed region
+           of `value`).
+  python bench.py --config tum|kitti|euroc|1080p|match     the other BASELINE.json workloads (match: Hamming GMatch/s headline)
 `--impl reference`: the reference's OWN ORBextractor (oracle/_ref/liborb_ref.so: /root/reference/src/ORBextractor.cc compiled
            unmodified against the cv:: shim of oracle/cvshim) on all host cores, one extractor and one frame per thread,
            bounded sample per step; `cpu_baseline.kind` is "reference".  Falls back to the oracle port (kind "port") only

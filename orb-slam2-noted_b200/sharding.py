@@ -1,8 +1,11 @@
 """Multi-GPU plumbing for the ORB front end: frames and keyframe-pair jobs are independent, so they
 are dealt round-robin to the ranks (frame f -> rank f mod G) with NO collective on the data path; the only exchange
-is one final all_gather of fixed-size padded result records over NCCL/NVLink (gloo in the CPU tests).
+is one final gather of what each rank found to one root rank.
 
-Record layout per frame (cap = ORBextractor.max_keypoints()): n (int32), cap x 28 B keypoints, cap x 32 B descriptors.
+Two forms.  `Comm` (below) is the product path: the C ABI's orbx_comm_* / orbx_gather_* (csrc/k_gather.cu) -- dense records,
+peer window over NVLink, its own stream.  The torch.distributed helpers at the top (gather_frames: an all_gather of padded
+records; global_order) are the portable form the world-size-2 gloo tests run on CPU.
+Padded record layout per frame (cap = ORBextractor.max_keypoints()): n (int32), cap x 28 B keypoints, cap x 32 B descriptors.
 """
 import torch
 import torch.distributed as dist
