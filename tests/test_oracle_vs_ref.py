@@ -219,3 +219,27 @@ def test_vocabulary_orbvoc_size_equals_reference(tmp_path):
     h = _ref_vocab(tmp_path, v, synth.vocabulary_text_fixed(v))
     _check_vocab(h, v, _voc_queries(v, 7, 10000), (4, 6, 0))
     R.lib().ref_vocab_free(h)
+
+
+def test_extract_fuzz_sizes_and_parameters():
+    """Random frame sizes (odd widths included), feature budgets, scale factors, level counts and FAST thresholds: the oracle
+    equals the reference's ORBextractor::operator() byte for byte on each.  Sizes keep every level at least 62 px wide / high
+    (below that the reference divides by zero at src/ORBextractor.cc:1080)."""
+    rng = np.random.default_rng(2024)
+    R.set_allocator(1)
+    kinds = ["texture", "noise", "blocks", "gradient"]
+    done = 0
+    while done < 14:
+        sc = float(rng.choice([1.1, 1.2, 1.25, 1.4, 1.5, 2.0]))
+        nl = int(rng.integers(2, 9))
+        w, h = int(rng.integers(150, 900)), int(rng.integers(150, 700))
+        if min(w, h) / sc ** (nl - 1) < 70:
+            continue
+        nf = int(rng.integers(100, 2500))
+        ini = int(rng.integers(8, 40)); mn = int(rng.integers(3, ini + 1))
+        img = synth.frame(int(rng.integers(0, 10000)), w, h, kinds[done % 4])
+        p = O.params(nf, sc, nl, ini, mn)
+        ok, od = O.extract(p, img)
+        rk, rd = R.extract(img, nf, sc, nl, ini, mn)
+        assert _same_kps(ok, rk) and np.array_equal(od, rd), (w, h, nf, sc, nl, ini, mn, len(ok), len(rk))
+        done += 1
