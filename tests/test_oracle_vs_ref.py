@@ -88,7 +88,7 @@ def test_distribute_octree_equals_reference():
         assert _same_kps(want, got), (n, W, H, N, len(want), len(got))
 
 
-@pytest.mark.parametrize("w,h,nf,seed", [(752, 480, 1200, 3), (1241, 376, 2000, 5)])
+@pytest.mark.parametrize("w,h,nf,seed", [(752, 480, 1200, 3), (1241, 376, 2000, 5), (640, 480, 1000, 17), (501, 333, 800, 23)])
 def test_stereo_frame_equals_reference(w, h, nf, seed):
     """Frame::Frame(imLeft, imRight, ...) of the reference (two extractions, ComputeStereoMatches, src/Frame.cc:119-217,
     :831-1128) == orc_extract x2 + orc_stereo_matches: mvuRight and mvDepth as raw bits."""
@@ -117,7 +117,7 @@ def test_stereo_frame_equals_reference(w, h, nf, seed):
     assert n == int((want_z > 0).sum()) and n > 100
 
 
-@pytest.mark.parametrize("seed,n1,n2", [(11, 1500, 1300), (12, 700, 900)])
+@pytest.mark.parametrize("seed,n1,n2", [(11, 1500, 1300), (12, 700, 900), (13, 2000, 1900), (14, 300, 350)])
 def test_matcher_scene_equals_reference(tmp_path, seed, n1, n2):
     """Every ORBmatcher method of the reference (src/ORBmatcher.cc, unmodified, over the reference's own Frame / KeyFrame /
     MapPoint / Map) on one scene file == the oracle's loops (+ a Python replay of Fuse's map updates)."""
